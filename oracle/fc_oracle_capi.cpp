@@ -1,0 +1,273 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY. Never linked into or called by the product library.
+// C ABI over the CPU restatement so that tests/, __graft_entry__.smoke() and bench.py's
+// cpu_baseline / --impl reference legs can drive it through ctypes.
+#include <chrono>
+#include <cstring>
+
+#include "fc_oracle_assemble.hpp"
+
+using namespace fc_oracle;
+
+namespace
+{
+  struct JobState
+  {
+    Job job;
+    std::vector<std::vector<double>> u_row, f_row, K_values;
+  };
+  void finish_job(JobState* js)
+  {
+    const int nr = js->job.part.nranks;
+    js->job.sys.resize(nr);
+    for (int r = 0; r < nr; ++r) build_rank_system(js->job.mesh, js->job.part, r, js->job.sys[r]);
+    js->u_row.resize(nr);
+    js->f_row.resize(nr);
+    js->K_values.resize(nr);
+    for (int r = 0; r < nr; ++r)
+    {
+      js->u_row[r].assign(js->job.sys[r].row_dof_gid.size(), 0.0);
+      js->f_row[r].assign(js->job.sys[r].row_dof_gid.size(), 0.0);
+    }
+  }
+  template <class T>
+  void copy_out(const std::vector<T>& v, T* out)
+  {
+    if (out && !v.empty()) std::memcpy(out, v.data(), v.size() * sizeof(T));
+  }
+}  // namespace
+
+extern "C"
+{
+  // ---- unit-level entry points (golden vector checks) -----------------------------------------
+  void oracle_calculate_gamma_delta(
+      const double* prinv, const double* dPI, const double* ddPII, double* gamma, double* delta)
+  {
+    calculate_gamma_delta(gamma, delta, prinv, dPI, ddPII);
+  }
+  void oracle_material_evaluate(int kind, double young, double nue, const double* F,
+      const double* glstrain, double* S, double* cmat)
+  {
+    MaterialParams mp{kind, young, nue};
+    material_evaluate(mp, F, glstrain, S, cmat);
+  }
+  double oracle_svk_strain_energy(double young, double nue, const double* glstrain)
+  {
+    return svk_strain_energy(young, nue, glstrain);
+  }
+  void oracle_rcg_strain_like(const double* E, double* C)
+  {
+    for (int i = 0; i < 6; ++i) C[i] = 2.0 * E[i];
+    for (int i = 0; i < 3; ++i) C[i] += 1.0;
+  }
+  double oracle_voigt_determinant(int strain, const double* t)
+  {
+    return strain ? voigt_determinant_strain(t) : voigt_determinant_stress(t);
+  }
+  void oracle_voigt_invariants(int strain, const double* t, double* prinv)
+  {
+    if (strain)
+      voigt_invariants_principal_strain(prinv, t);
+    else
+      voigt_invariants_principal_stress(prinv, t);
+  }
+  void oracle_voigt_inverse(int strain, const double* t, double* ti)
+  {
+    if (strain)
+      voigt_inverse_tensor<true>(t, ti);
+    else
+      voigt_inverse_tensor<false>(t, ti);
+  }
+  void oracle_voigt_to_stress_like(const double* in, double* out) { voigt_strain_to_stress_like(in, out); }
+  void oracle_voigt_matrix_to_vector_strain(const double* m, double* v) { voigt_matrix_to_vector_strain(m, v); }
+  void oracle_add_holzapfel_product(double* cmat, const double* invc, double scalar)
+  {
+    add_holzapfel_product(cmat, invc, scalar);
+  }
+  double oracle_invert3x3(const double* in, double* out) { return invert3x3(out, in, nullptr); }
+  double oracle_determinant3x3(const double* in) { return determinant3x3(in); }
+  // generic small products for the bit-exact check against the reference header (oracle/_ref)
+  void oracle_multiply_nn_6_6_24(double* out, const double* l, const double* r) { multiply_nn<6, 6, 24>(out, l, r); }
+  void oracle_multiply_tn_24_6_24(double fac, double* out, const double* l, const double* r)
+  {
+    multiply_tn_scaled<24, 6, 24>(fac, out, l, r, 1.0);
+  }
+  void oracle_multiply_nt_3_8_3(double* out, const double* l, const double* r) { multiply_nt<3, 8, 3>(out, l, r); }
+  void oracle_multiply_tn_3_3_3(double* out, const double* l, const double* r) { multiply_tn<3, 3, 3>(out, l, r); }
+
+  int oracle_num_nodes(int ct) { return num_nodes(ct); }
+  int oracle_num_gp(int ct) { return num_gp(ct); }
+  void oracle_shape(int ct, const double* xi, double* N, double* dN)
+  {
+    if (N) shape_function(ct, xi, N);
+    if (dN) shape_function_deriv1(ct, xi, dN);
+  }
+  void oracle_gauss_rule(int ct, double* xi, double* w)
+  {
+    double x[27][3];
+    gauss_rule(ct, x, w);
+    for (int g = 0; g < num_gp(ct); ++g)
+      for (int d = 0; d < 3; ++d) xi[3 * g + d] = x[g][d];
+  }
+  void oracle_node_param_coords(int ct, double* xi)
+  {
+    for (int a = 0; a < num_nodes(ct); ++a) node_param_coords(ct, a, xi + 3 * a);
+  }
+  int oracle_element_evaluate(int ct, int form, int kind, double young, double nue, const double* X,
+      const double* u, double* fe, double* Ke, double* Me, double rho)
+  {
+    MaterialParams mp{kind, young, nue};
+    return element_evaluate(ct, form, mp, X, u, fe, Ke, Me, rho);
+  }
+  // batch of independent elements (X,u: [n][3*nen]); used as the checker for the CUDA
+  // element-level entry point.  returns the number of failing elements.
+  int oracle_element_evaluate_batch(int ct, int form, int kind, double young, double nue, int n,
+      const double* X, const double* u, double* fe, double* Ke)
+  {
+    MaterialParams mp{kind, young, nue};
+    const int nd = 3 * num_nodes(ct);
+    int bad = 0;
+    for (int e = 0; e < n; ++e)
+    {
+      std::memset(fe + (size_t)e * nd, 0, sizeof(double) * nd);
+      if (Ke) std::memset(Ke + (size_t)e * nd * nd, 0, sizeof(double) * nd * nd);
+      bad += 0 != element_evaluate(ct, form, mp, X + (size_t)e * nd, u + (size_t)e * nd,
+                      fe + (size_t)e * nd, Ke ? Ke + (size_t)e * nd * nd : nullptr);
+    }
+    return bad;
+  }
+
+  // ---- job-level entry points -------------------------------------------------------------------
+  void* oracle_job_create_cuboid(int ct, int nx, int ny, int nz, const double* lo, const double* hi,
+      int nranks, int node_offset)
+  {
+    auto* js = new JobState;
+    const int interval[3] = {nx, ny, nz};
+    create_cuboid(ct, interval, lo, hi, nranks, node_offset, js->job.mesh, js->job.part);
+    finish_job(js);
+    return js;
+  }
+  void* oracle_job_create_mesh(int ct, int n_nodes, const int* node_gid, const double* X, int n_ele,
+      const int* ele_gid, const int* conn)
+  {
+    auto* js = new JobState;
+    Mesh& m = js->job.mesh;
+    m.ct = ct;
+    m.nen = num_nodes(ct);
+    std::vector<int> order(n_nodes);
+    for (int i = 0; i < n_nodes; ++i) order[i] = i;
+    std::sort(order.begin(), order.end(), [&](int a, int b) { return node_gid[a] < node_gid[b]; });
+    m.node_gid.resize(n_nodes);
+    m.node_X.resize(3 * (size_t)n_nodes);
+    for (int i = 0; i < n_nodes; ++i)
+    {
+      m.node_gid[i] = node_gid[order[i]];
+      for (int d = 0; d < 3; ++d) m.node_X[3 * (size_t)i + d] = X[3 * (size_t)order[i] + d];
+    }
+    m.ele_gid.assign(ele_gid, ele_gid + n_ele);
+    m.ele_nodes.assign(conn, conn + (size_t)n_ele * m.nen);
+    m.finalize();
+    trivial_partition(m, js->job.part);
+    finish_job(js);
+    return js;
+  }
+  void oracle_job_destroy(void* h) { delete (JobState*)h; }
+  void oracle_job_set_problem(void* h, int form, int kind, double young, double nue)
+  {
+    auto* js = (JobState*)h;
+    js->job.form = form;
+    js->job.mp = MaterialParams{kind, young, nue};
+  }
+  int oracle_job_nranks(void* h) { return ((JobState*)h)->job.part.nranks; }
+  void oracle_job_subdivisions(void* h, int* s)
+  {
+    for (int d = 0; d < 3; ++d) s[d] = ((JobState*)h)->job.part.subdiv[d];
+  }
+  int oracle_job_n_nodes(void* h) { return (int)((JobState*)h)->job.mesh.node_gid.size(); }
+  int oracle_job_n_eles(void* h) { return (int)((JobState*)h)->job.mesh.ele_gid.size(); }
+  void oracle_job_get_nodes(void* h, int* gid, double* X, int* owner)
+  {
+    auto* js = (JobState*)h;
+    copy_out(js->job.mesh.node_gid, gid);
+    copy_out(js->job.mesh.node_X, X);
+    copy_out(js->job.part.node_owner, owner);
+  }
+  void oracle_job_get_eles(void* h, int* gid, int* conn, int* owner)
+  {
+    auto* js = (JobState*)h;
+    copy_out(js->job.mesh.ele_gid, gid);
+    copy_out(js->job.mesh.ele_nodes, conn);
+    copy_out(js->job.part.ele_owner, owner);
+  }
+  // sizes[0..7] = n_row_nodes, n_col_nodes, n_row_eles, n_col_eles, n_row_dof, n_col_dof, nnz_lo, nnz_hi
+  void oracle_job_rank_sizes(void* h, int rank, int64_t* sizes)
+  {
+    auto* js = (JobState*)h;
+    const RankSystem& rs = js->job.sys[rank];
+    sizes[0] = rs.n_row_nodes;
+    sizes[1] = (int64_t)rs.col_node_gid.size();
+    sizes[2] = js->job.part.n_row_eles[rank];
+    sizes[3] = (int64_t)js->job.part.col_eles[rank].size();
+    sizes[4] = (int64_t)rs.row_dof_gid.size();
+    sizes[5] = (int64_t)rs.col_dof_gid.size();
+    sizes[6] = (int64_t)rs.colind.size();
+  }
+  void oracle_job_rank_maps(void* h, int rank, int* col_node_gid, int* col_eles, int* row_dof_gid,
+      int* col_dof_gid, int64_t* rowptr, int* colind)
+  {
+    auto* js = (JobState*)h;
+    const RankSystem& rs = js->job.sys[rank];
+    copy_out(rs.col_node_gid, col_node_gid);
+    copy_out(js->job.part.col_eles[rank], col_eles);
+    copy_out(rs.row_dof_gid, row_dof_gid);
+    copy_out(rs.col_dof_gid, col_dof_gid);
+    copy_out(rs.rowptr, rowptr);
+    copy_out(rs.colind, colind);
+  }
+  void oracle_job_set_dirichlet_rows(void* h, int rank, int n, const int* row_lids)
+  {
+    auto* js = (JobState*)h;
+    auto& d = js->job.sys[rank].dbc_row;
+    std::fill(d.begin(), d.end(), 0);
+    for (int i = 0; i < n; ++i) d[row_lids[i]] = 1;
+  }
+  void oracle_job_set_u(void* h, int rank, const double* u_row)
+  {
+    auto* js = (JobState*)h;
+    std::memcpy(js->u_row[rank].data(), u_row, js->u_row[rank].size() * sizeof(double));
+  }
+  // u given per global node (mesh node order, 3 per node): scattered to every rank's row layout
+  void oracle_job_set_u_nodal(void* h, const double* u_nodes)
+  {
+    auto* js = (JobState*)h;
+    const Mesh& m = js->job.mesh;
+    for (int r = 0; r < js->job.part.nranks; ++r)
+    {
+      const auto& rn = js->job.part.row_nodes[r];
+      for (size_t i = 0; i < rn.size(); ++i)
+      {
+        const int ni = m.node_index.at(rn[i]);
+        for (int j = 0; j < 3; ++j) js->u_row[r][3 * i + j] = u_nodes[3 * (size_t)ni + j];
+      }
+    }
+  }
+  // zero f and K (reset(), sparsematrix.cpp:353-378), then evaluate all ranks.
+  // returns #failing elements; seconds = wall time of the evaluate+assemble region only.
+  int oracle_job_evaluate(void* h, int action, int max_threads, int* first_bad, double* seconds)
+  {
+    auto* js = (JobState*)h;
+    const int nr = js->job.part.nranks;
+    for (int r = 0; r < nr; ++r)
+    {
+      std::fill(js->f_row[r].begin(), js->f_row[r].end(), 0.0);
+      if (action == 0) js->K_values[r].assign(js->job.sys[r].colind.size(), 0.0);
+    }
+    const auto t0 = std::chrono::steady_clock::now();
+    const int bad =
+        evaluate_job(js->job, action, js->u_row, js->f_row, js->K_values, max_threads, first_bad);
+    const auto t1 = std::chrono::steady_clock::now();
+    if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+    return bad;
+  }
+  void oracle_job_get_f(void* h, int rank, double* f) { copy_out(((JobState*)h)->f_row[rank], f); }
+  void oracle_job_get_K(void* h, int rank, double* K) { copy_out(((JobState*)h)->K_values[rank], K); }
+}

@@ -1,0 +1,286 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY. Never linked into or called by the product library.
+//
+// Restatement of SolidEleCalc<celltype,Formulation>::evaluate_nonlinear_force_stiffness_mass
+// (src/solid_3D_ele/4C_solid_3D_ele_calc.cpp:110-240) for hex8/hex27/tet10 with the
+// displacement-based (4C_solid_3D_ele_calc_displacement_based.hpp:45-72, 228-250) and F-bar
+// (4C_solid_3D_ele_calc_fbar.hpp:55-111, 164-190; 4C_solid_3D_ele_calc_lib_fbar.hpp:49-154)
+// formulations.  Library functions followed, all in src/solid_3D_ele/4C_solid_3D_ele_calc_lib.hpp:
+//   evaluate_element_nodes :152-203            evaluate_jacobian_mapping :435-448
+//   ensure_positive_jacobian_determinant_at_element_nodes :475-496
+//   evaluate_deformation_gradient :585-602     (hex8: F = x N_XYZ^T, others: F = I + u N_XYZ^T)
+//   evaluate_spatial_material_mapping :548-567 evaluate_cauchy_green :655-667
+//   evaluate_green_lagrange_strain :639-652    evaluate_strain_gradient :708-760
+//   add_internal_force_vector :851-860         add_elastic_stiffness_matrix :872-885
+//   add_geometric_stiffness_matrix :898-927    add_mass_matrix :940-958
+//   for_each_gauss_point :974-993
+//
+// Parity status: element-level K_e/f_e values are pinned by NO reference test ("parity
+// unpinned" at that granularity); they are pinned at solve level by the reference's
+// RESULT DESCRIPTION vectors (tests/golden/*.json, TOLERANCE 1e-12) and cross-checked by finite
+// differences (K = df/du) in tests/test_oracle_element.py.
+#pragma once
+#include <vector>
+
+#include "fc_oracle_dense.hpp"
+#include "fc_oracle_fem.hpp"
+#include "fc_oracle_material.hpp"
+
+namespace fc_oracle
+{
+  enum Formulation
+  {
+    FORM_DISP = 0,
+    FORM_FBAR = 1
+  };
+
+  enum EleError
+  {
+    ELE_OK = 0,
+    ELE_ERR_NEG_JAC_AT_NODE = 1,  // FOUR_C_ASSERT_ALWAYS in calc_lib.hpp:492-494
+    ELE_ERR_SINGULAR = 2          // invert3x3 throw, fixedsizematrix.hpp:1319
+  };
+
+  template <int NEN>
+  struct JacobianMapping
+  {
+    double det;
+    double J[9], iJ[9];
+    double N_XYZ[3 * NEN];  // 3 x NEN col-major
+  };
+
+  template <int NEN>
+  struct SpatialMaterialMapping
+  {
+    double F[9], iF[9], detF;
+  };
+
+  // jacobian_ = deriv * X^T ; inverse ; N_XYZ = J^-1 deriv         calc_lib.hpp:435-448
+  template <int NEN>
+  inline void evaluate_jacobian_mapping(
+      const double* dN, const double* X, JacobianMapping<NEN>& jm, bool* singular)
+  {
+    multiply_nt<3, NEN, 3>(jm.J, dN, X);
+    jm.det = invert3x3(jm.iJ, jm.J, singular);
+    multiply_nn<3, 3, NEN>(jm.N_XYZ, jm.iJ, dN);
+  }
+
+  // calc_lib.hpp:548-605
+  template <int NEN>
+  inline void evaluate_spatial_material_mapping(int ct, const JacobianMapping<NEN>& jm,
+      const double* x, const double* u, double scale, SpatialMaterialMapping<NEN>& sm,
+      bool* singular)
+  {
+    if (ct == HEX8)
+    {
+      multiply_nt_scaled<3, NEN, 3>(scale, sm.F, x, jm.N_XYZ, 0.0);
+    }
+    else
+    {
+      for (int i = 0; i < 9; ++i) sm.F[i] = 0.0;
+      sm.F[0] = sm.F[4] = sm.F[8] = 1.0;
+      multiply_nt_scaled<3, NEN, 3>(scale, sm.F, u, jm.N_XYZ, scale);
+    }
+    invert3x3(sm.iF, sm.F, singular);
+    sm.detF = determinant3x3(sm.F);
+  }
+
+  // B-operator (6 x 3*NEN col-major)                              calc_lib.hpp:708-760
+  template <int NEN>
+  inline void evaluate_strain_gradient(const double* N_XYZ, const double* F, double* B)
+  {
+    auto Fm = [&](int r, int c) { return F[r + 3 * c]; };
+    auto Nx = [&](int d, int i) { return N_XYZ[d + 3 * i]; };
+    for (int i = 0; i < NEN; ++i)
+    {
+      for (int d = 0; d < 3; ++d)
+        for (int e = 0; e < 3; ++e) B[d + 6 * (3 * i + e)] = Fm(e, d) * Nx(d, i);
+      for (int e = 0; e < 3; ++e)
+      {
+        B[3 + 6 * (3 * i + e)] = Fm(e, 0) * Nx(1, i) + Fm(e, 1) * Nx(0, i);
+        B[4 + 6 * (3 * i + e)] = Fm(e, 1) * Nx(2, i) + Fm(e, 2) * Nx(1, i);
+        B[5 + 6 * (3 * i + e)] = Fm(e, 2) * Nx(0, i) + Fm(e, 0) * Nx(2, i);
+      }
+    }
+  }
+
+  // E (strain-like Voigt) from C                                   calc_lib.hpp:639-652
+  inline void evaluate_green_lagrange_strain(const double* C, double* E)
+  {
+    E[0] = 0.5 * (C[0] - 1.0);
+    E[1] = 0.5 * (C[4] - 1.0);
+    E[2] = 0.5 * (C[8] - 1.0);
+    E[3] = C[0 + 3 * 1];
+    E[4] = C[1 + 3 * 2];
+    E[5] = C[2 + 3 * 0];
+  }
+
+  // kgeo                                                           calc_lib.hpp:898-927
+  template <int NEN>
+  inline void add_geometric_stiffness_matrix(
+      const double* B_L, const double* S, double fac, double* K)
+  {
+    constexpr int ND = 3 * NEN;
+    double SmB_L[3];
+    for (int inod = 0; inod < NEN; ++inod)
+    {
+      SmB_L[0] = S[0] * B_L[0 + 3 * inod] + S[3] * B_L[1 + 3 * inod] + S[5] * B_L[2 + 3 * inod];
+      SmB_L[1] = S[3] * B_L[0 + 3 * inod] + S[1] * B_L[1 + 3 * inod] + S[4] * B_L[2 + 3 * inod];
+      SmB_L[2] = S[5] * B_L[0 + 3 * inod] + S[4] * B_L[1 + 3 * inod] + S[2] * B_L[2 + 3 * inod];
+      for (int jnod = 0; jnod < NEN; ++jnod)
+      {
+        double bopstrbop = 0.0;
+        for (int idim = 0; idim < 3; ++idim) bopstrbop += B_L[idim + 3 * jnod] * SmB_L[idim];
+        for (int d = 0; d < 3; ++d) K[(3 * inod + d) + ND * (3 * jnod + d)] += fac * bopstrbop;
+      }
+    }
+  }
+
+  // One element.  X,u: node-major [3*a+d] == 3 x NEN col-major.  fe[ND], Ke[ND*ND] col-major,
+  // Me optional (consistent mass, density rho).  Outputs are ADDED to (caller zeroes them, like
+  // AssembleStrategy::clear_element_storage, 4C_fem_general_assemblestrategy.cpp:74-111).
+  template <int NEN, int NGP>
+  inline int element_evaluate_t(int ct, int form, const MaterialParams& mp, const double* X,
+      const double* u, double* fe, double* Ke, double* Me, double rho)
+  {
+    constexpr int ND = 3 * NEN;
+    double x[ND];
+    for (int i = 0; i < ND; ++i) x[i] = X[i] + u[i];  // current_coordinates.update(1,disp,1)
+
+    bool singular = false;
+
+    // F-bar preparation: centroid jacobian mapping + centroid F          calc_fbar.hpp:55-63
+    JacobianMapping<NEN> jm0;
+    SpatialMaterialMapping<NEN> sm0;
+    if (form == FORM_FBAR)
+    {
+      double xi0[3], dN0[3 * NEN];
+      centroid_param(ct, xi0);
+      shape_function_deriv1(ct, xi0, dN0);
+      evaluate_jacobian_mapping<NEN>(dN0, X, jm0, &singular);
+      evaluate_spatial_material_mapping<NEN>(ct, jm0, x, u, 1.0, sm0, &singular);
+    }
+
+    // negative Jacobian check at the element nodes                   calc_lib.hpp:475-496
+    for (int a = 0; a < NEN; ++a)
+    {
+      double xi[3], dN[3 * NEN];
+      node_param_coords(ct, a, xi);
+      shape_function_deriv1(ct, xi, dN);
+      JacobianMapping<NEN> jm;
+      evaluate_jacobian_mapping<NEN>(dN, X, jm, &singular);
+      if (!(jm.det > 0)) return ELE_ERR_NEG_JAC_AT_NODE;
+    }
+
+    double gxi[NGP][3], gw[NGP];
+    gauss_rule(ct, gxi, gw);
+
+    std::vector<double> Bv(6 * ND), cbv(6 * ND);
+    double* B = Bv.data();
+    double* cb = cbv.data();
+
+    for (int gp = 0; gp < NGP; ++gp)
+    {
+      double N[NEN], dN[3 * NEN];
+      shape_function(ct, gxi[gp], N);
+      shape_function_deriv1(ct, gxi[gp], dN);
+      JacobianMapping<NEN> jm;
+      evaluate_jacobian_mapping<NEN>(dN, X, jm, &singular);
+      const double integration_factor = jm.det * gw[gp];
+
+      SpatialMaterialMapping<NEN> sm;
+      evaluate_spatial_material_mapping<NEN>(ct, jm, x, u, 1.0, sm, &singular);
+
+      double Fmat[9], C[9], E[6];  // what the material sees
+      double fbar_factor = 1.0, Hop[ND], Cg[9];
+      if (form == FORM_DISP)
+      {
+        for (int i = 0; i < 9; ++i) Fmat[i] = sm.F[i];
+        multiply_tn<3, 3, 3>(C, sm.F, sm.F);
+        evaluate_green_lagrange_strain(C, E);
+        evaluate_strain_gradient<NEN>(jm.N_XYZ, sm.F, B);
+      }
+      else
+      {
+        fbar_factor = std::pow(sm0.detF / sm.detF, 1.0 / 3.0);  // lib_fbar.hpp:49-53
+        evaluate_strain_gradient<NEN>(jm.N_XYZ, sm.F, B);
+        // H operator                                                 lib_fbar.hpp:71-104
+        double iF0[9], iFg[9];
+        invert3x3(iF0, sm0.F, &singular);
+        invert3x3(iFg, sm.F, &singular);
+        for (int idof = 0; idof < ND; ++idof)
+        {
+          Hop[idof] = 0.0;
+          for (int idim = 0; idim < 3; ++idim)
+          {
+            Hop[idof] += iF0[idim + 3 * (idof % 3)] * jm0.N_XYZ[idim + 3 * (idof / 3)];
+            Hop[idof] -= iFg[idim + 3 * (idof % 3)] * jm.N_XYZ[idim + 3 * (idof / 3)];
+          }
+        }
+        multiply_tn<3, 3, 3>(Cg, sm.F, sm.F);  // linearization.cauchygreen (unmodified F)
+        SpatialMaterialMapping<NEN> smbar;
+        evaluate_spatial_material_mapping<NEN>(ct, jm, x, u, fbar_factor, smbar, &singular);
+        for (int i = 0; i < 9; ++i) Fmat[i] = smbar.F[i];
+        multiply_tn<3, 3, 3>(C, smbar.F, smbar.F);
+        evaluate_green_lagrange_strain(C, E);
+      }
+
+      double S[6], cmat[36];
+      material_evaluate(mp, Fmat, E, S, cmat);
+
+      const double fac_force = form == FORM_FBAR ? integration_factor / fbar_factor : integration_factor;
+      // f += fac * B^T S                                               calc_lib.hpp:851-860
+      if (fe) multiply_tn_scaled<ND, 6, 1>(fac_force, fe, B, S, 1.0);
+
+      if (Ke)
+      {
+        const double fac_mat = form == FORM_FBAR ? integration_factor * fbar_factor : integration_factor;
+        const double fac_geo = form == FORM_FBAR ? integration_factor / fbar_factor : integration_factor;
+        multiply_nn<6, 6, ND>(cb, cmat, B);                              // cb = C B
+        multiply_tn_scaled<ND, 6, ND>(fac_mat, Ke, B, cb, 1.0);          // K += fac B^T cb
+        add_geometric_stiffness_matrix<NEN>(jm.N_XYZ, S, fac_geo, Ke);
+        if (form == FORM_FBAR)
+        {
+          // add_fbar_stiffness_matrix                                   lib_fbar.hpp:120-154
+          double rcg[6], ccg[6];
+          voigt_matrix_to_vector_strain(Cg, rcg);
+          multiply_nn<6, 6, 1>(ccg, cmat, rcg);
+          double bopccg[ND], bops[ND];
+          multiply_tn_scaled<ND, 6, 1>(integration_factor * fbar_factor / 3.0, bopccg, B, ccg, 0.0);
+          multiply_tn_scaled<ND, 6, 1>(-integration_factor / fbar_factor / 3.0, bops, B, S, 0.0);
+          for (int idof = 0; idof < ND; ++idof)
+            for (int jdof = 0; jdof < ND; ++jdof)
+              Ke[idof + ND * jdof] += Hop[jdof] * (bops[idof] + bopccg[idof]);
+        }
+      }
+      if (Me)
+      {
+        // add_mass_matrix                                               calc_lib.hpp:940-958
+        for (int inod = 0; inod < NEN; ++inod)
+        {
+          const double ifactor = N[inod] * integration_factor * rho;
+          for (int jnod = 0; jnod < NEN; ++jnod)
+          {
+            const double massfactor = N[jnod] * ifactor;
+            for (int d = 0; d < 3; ++d) Me[(3 * inod + d) + ND * (3 * jnod + d)] += massfactor;
+          }
+        }
+      }
+    }
+    return singular ? ELE_ERR_SINGULAR : ELE_OK;
+  }
+
+  inline int element_evaluate(int ct, int form, const MaterialParams& mp, const double* X,
+      const double* u, double* fe, double* Ke, double* Me = nullptr, double rho = 0.0)
+  {
+    switch (ct)
+    {
+      case HEX8:
+        return element_evaluate_t<8, 8>(ct, form, mp, X, u, fe, Ke, Me, rho);
+      case HEX27:
+        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho);
+      case TET10:
+        return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho);
+    }
+    return -1;
+  }
+}  // namespace fc_oracle

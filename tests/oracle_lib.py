@@ -1,0 +1,206 @@
+"""ctypes binding of the CPU oracle (oracle/liboracle.so) — TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  The product package (4c_b200/) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+
+HEX8, HEX27, TET10 = 0, 1, 2
+FORM_DISP, FORM_FBAR = 0, 1
+MAT_SVK, MAT_NEOHOOKE = 0, 1
+ACTION_NLNSTIFF, ACTION_INTERNALFORCE = 0, 1
+NEN = {HEX8: 8, HEX27: 27, TET10: 10}
+NGP = {HEX8: 8, HEX27: 27, TET10: 4}
+
+_dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
+_ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+_lp = np.ctypeslib.ndpointer(dtype=np.int64, flags="C_CONTIGUOUS")
+
+
+def build():
+    """(Re)build liboracle.so (and oracle/_ref when /root/reference is present)."""
+    subprocess.run(["make", "-s", "-C", ORACLE_DIR], check=True, stdout=subprocess.DEVNULL)
+
+
+def _load():
+    path = os.path.join(ORACLE_DIR, "liboracle.so")
+    if not os.path.exists(path):
+        build()
+    lib = C.CDLL(path)
+    lib.oracle_svk_strain_energy.restype = C.c_double
+    lib.oracle_voigt_determinant.restype = C.c_double
+    lib.oracle_invert3x3.restype = C.c_double
+    lib.oracle_determinant3x3.restype = C.c_double
+    for name in ("oracle_job_create_cuboid", "oracle_job_create_mesh"):
+        getattr(lib, name).restype = C.c_void_p
+    return lib
+
+
+lib = _load()
+
+
+def _d(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def gamma_delta(prinv, dPI, ddPII):
+    g, d = np.zeros(3), np.zeros(8)
+    lib.oracle_calculate_gamma_delta(_p(_d(prinv)), _p(_d(dPI)), _p(_d(ddPII)), _p(g), _p(d))
+    return g, d
+
+
+def material_evaluate(kind, young, nue, F, E):
+    S, cmat = np.zeros(6), np.zeros(36)
+    F = _d(np.asarray(F).T.reshape(-1)) if F is not None else np.zeros(9)
+    lib.oracle_material_evaluate(C.c_int(kind), C.c_double(young), C.c_double(nue), _p(F), _p(_d(E)), _p(S), _p(cmat))
+    return S, cmat.reshape(6, 6).T.copy()  # col-major -> [r, c]
+
+
+def element_evaluate(ct, form, kind, young, nue, X, u, want_K=True, want_M=False, rho=0.0):
+    """X, u: (nen, 3).  Returns err, fe (3*nen), Ke (nd, nd) [r, c], Me."""
+    nd = 3 * NEN[ct]
+    X, u = _d(X).reshape(-1), _d(u).reshape(-1)
+    fe = np.zeros(nd)
+    Ke = np.zeros(nd * nd) if want_K else None
+    Me = np.zeros(nd * nd) if want_M else None
+    err = lib.oracle_element_evaluate(C.c_int(ct), C.c_int(form), C.c_int(kind), C.c_double(young),
+                                      C.c_double(nue), _p(X), _p(u), _p(fe), _p(Ke), _p(Me), C.c_double(rho))
+    Ke = Ke.reshape(nd, nd).T.copy() if want_K else None
+    Me = Me.reshape(nd, nd).T.copy() if want_M else None
+    return err, fe, Ke, Me
+
+
+def element_evaluate_batch(ct, form, kind, young, nue, X, u, want_K=True):
+    """X, u: (n, nen, 3).  Returns nbad, fe (n, nd), Ke (n, nd, nd) indexed [e, r, c]."""
+    n = X.shape[0]
+    nd = 3 * NEN[ct]
+    X, u = _d(X).reshape(-1), _d(u).reshape(-1)
+    fe = np.zeros((n, nd))
+    Ke = np.zeros((n, nd, nd)) if want_K else None
+    bad = lib.oracle_element_evaluate_batch(C.c_int(ct), C.c_int(form), C.c_int(kind), C.c_double(young),
+                                            C.c_double(nue), C.c_int(n), _p(X), _p(u), _p(fe), _p(Ke))
+    if want_K:
+        Ke = np.ascontiguousarray(Ke.transpose(0, 2, 1))
+    return bad, fe, Ke
+
+
+class Job:
+    """Mesh + decomposition + per-rank CSR systems held by the oracle."""
+
+    def __init__(self, handle):
+        self.h = C.c_void_p(handle)
+        self.nranks = lib.oracle_job_nranks(self.h)
+        nn, ne = lib.oracle_job_n_nodes(self.h), lib.oracle_job_n_eles(self.h)
+        self.node_gid = np.zeros(nn, np.int32)
+        self.X = np.zeros((nn, 3))
+        self.node_owner = np.zeros(nn, np.int32)
+        lib.oracle_job_get_nodes(self.h, _p(self.node_gid), _p(self.X), _p(self.node_owner))
+        self.ele_gid = np.zeros(ne, np.int32)
+        self.ele_owner = np.zeros(ne, np.int32)
+        self._conn_flat = None
+        self._ne = ne
+
+    @classmethod
+    def cuboid(cls, ct, n, lo=(0, 0, 0), hi=(1, 1, 1), nranks=1, node_offset=0):
+        lo, hi = _d(lo), _d(hi)
+        h = lib.oracle_job_create_cuboid(C.c_int(ct), C.c_int(n[0]), C.c_int(n[1]), C.c_int(n[2]), _p(lo), _p(hi),
+                                         C.c_int(nranks), C.c_int(node_offset))
+        j = cls(h)
+        j.ct = ct
+        j._fetch_eles()
+        return j
+
+    @classmethod
+    def from_mesh(cls, ct, node_gid, X, ele_gid, conn):
+        node_gid, X, ele_gid, conn = _i(node_gid), _d(X), _i(ele_gid), _i(conn)
+        h = lib.oracle_job_create_mesh(C.c_int(ct), C.c_int(len(node_gid)), _p(node_gid), _p(X),
+                                       C.c_int(len(ele_gid)), _p(ele_gid), _p(conn))
+        j = cls(h)
+        j.ct = ct
+        j._fetch_eles()
+        return j
+
+    def _fetch_eles(self):
+        self.conn = np.zeros((self._ne, NEN[self.ct]), np.int32)
+        lib.oracle_job_get_eles(self.h, _p(self.ele_gid), _p(self.conn), _p(self.ele_owner))
+
+    def subdivisions(self):
+        s = np.zeros(3, np.int32)
+        lib.oracle_job_subdivisions(self.h, _p(s))
+        return tuple(int(x) for x in s)
+
+    def set_problem(self, form, kind, young, nue):
+        lib.oracle_job_set_problem(self.h, C.c_int(form), C.c_int(kind), C.c_double(young), C.c_double(nue))
+
+    def rank(self, r):
+        sizes = np.zeros(8, np.int64)
+        lib.oracle_job_rank_sizes(self.h, C.c_int(r), _p(sizes))
+        out = dict(n_row_nodes=int(sizes[0]), n_col_nodes=int(sizes[1]), n_row_eles=int(sizes[2]),
+                   n_col_eles=int(sizes[3]), n_row_dof=int(sizes[4]), n_col_dof=int(sizes[5]), nnz=int(sizes[6]))
+        out["col_node_gid"] = np.zeros(out["n_col_nodes"], np.int32)
+        out["col_eles"] = np.zeros(out["n_col_eles"], np.int32)
+        out["row_dof_gid"] = np.zeros(out["n_row_dof"], np.int32)
+        out["col_dof_gid"] = np.zeros(out["n_col_dof"], np.int32)
+        out["rowptr"] = np.zeros(out["n_row_dof"] + 1, np.int64)
+        out["colind"] = np.zeros(out["nnz"], np.int32)
+        lib.oracle_job_rank_maps(self.h, C.c_int(r), _p(out["col_node_gid"]), _p(out["col_eles"]),
+                                 _p(out["row_dof_gid"]), _p(out["col_dof_gid"]), _p(out["rowptr"]), _p(out["colind"]))
+        return out
+
+    def set_dirichlet_rows(self, r, row_lids):
+        row_lids = _i(row_lids)
+        lib.oracle_job_set_dirichlet_rows(self.h, C.c_int(r), C.c_int(len(row_lids)), _p(row_lids))
+
+    def set_u_nodal(self, u_nodes):
+        """u_nodes: (n_nodes, 3) in the order of self.node_gid."""
+        lib.oracle_job_set_u_nodal(self.h, _p(_d(u_nodes)))
+
+    def set_u(self, r, u_row):
+        lib.oracle_job_set_u(self.h, C.c_int(r), _p(_d(u_row)))
+
+    def evaluate(self, action=ACTION_NLNSTIFF, max_threads=1):
+        fb = C.c_int(-1)
+        sec = C.c_double(0)
+        bad = lib.oracle_job_evaluate(self.h, C.c_int(action), C.c_int(max_threads), C.byref(fb), C.byref(sec))
+        self.seconds = sec.value
+        return bad, fb.value
+
+    def get_f(self, r, n):
+        f = np.zeros(n)
+        lib.oracle_job_get_f(self.h, C.c_int(r), _p(f))
+        return f
+
+    def get_K(self, r, nnz):
+        K = np.zeros(nnz)
+        lib.oracle_job_get_K(self.h, C.c_int(r), _p(K))
+        return K
+
+    def __del__(self):
+        try:
+            lib.oracle_job_destroy(self.h)
+        except Exception:
+            pass
+
+
+def smooth_displacement(X, h, seed=12345, amp=0.02, noise=1e-3):
+    """The synthetic displacement state of SURVEY §8d: affine + sine + uniform noise U(-noise,noise)*h."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    A = np.array([[0.03, 0.01, -0.02], [0.00, -0.02, 0.015], [0.01, 0.02, 0.025]])
+    u = X @ A.T + amp * np.sin(2 * np.pi * X[:, [1, 2, 0]])
+    u += rng.uniform(-noise, noise, size=X.shape) * h
+    return u

@@ -1,0 +1,247 @@
+"""ctypes binding of libfourc_b200.so (include/fourc_b200.h).
+
+Plumbing only: the library is the product.  Buffers may be numpy arrays (host), torch tensors
+(host or CUDA; passed by data_ptr) or raw integer addresses.  There is no fallback of any kind: if the
+shared library is missing this module raises, and without a CUDA device Solid() raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
+
+FC_HEX8, FC_HEX27, FC_TET10 = 0, 1, 2
+FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
+FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
+FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
+FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA = 1, 2, 4
+FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
+FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
+NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10}
+
+EXPORTS = [
+    "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
+    "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_graph", "fc_solid_build_graph",
+    "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
+    "fc_solid_error_state", "fc_solid_zero", "fc_solid_evaluate_elements",
+    "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack",
+    "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
+    "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
+    "fc_grid_halo_counts", "fc_grid_halo_send_nodes",
+]
+
+
+class FourCError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"fourc_b200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(make -C 4c_b200/csrc).  There is no CPU fallback.")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.fc_version.restype = C.c_char_p
+        _lib.fc_last_error.restype = C.c_char_p
+        _lib.fc_last_error.argtypes = [C.c_void_p]
+        _lib.fc_solid_destroy.restype = None
+        _lib.fc_solid_destroy.argtypes = [C.c_void_p]
+        _lib.fc_grid_destroy.restype = None
+        _lib.fc_grid_destroy.argtypes = [C.c_void_p]
+    return _lib
+
+
+def _ptr(x):
+    """address of a numpy array / torch tensor / int / None as c_void_p"""
+    if x is None:
+        return C.c_void_p(None)
+    if isinstance(x, int):
+        return C.c_void_p(x)
+    if isinstance(x, np.ndarray):
+        assert x.flags["C_CONTIGUOUS"]
+        return C.c_void_p(x.ctypes.data)
+    if hasattr(x, "data_ptr"):
+        assert x.is_contiguous()
+        return C.c_void_p(x.data_ptr())
+    raise TypeError(type(x))
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+class Grid:
+    """Structured cuboid + reference decomposition for one rank (fc_grid_*)."""
+
+    def __init__(self, celltype, n, lo=(0.0, 0.0, 0.0), hi=(1.0, 1.0, 1.0), nranks=1, rank=0, node_offset=0):
+        L = lib()
+        h = C.c_void_p()
+        lo, hi = _f64(lo), _f64(hi)
+        rc = L.fc_grid_create(C.byref(h), C.c_int(celltype), C.c_int(n[0]), C.c_int(n[1]), C.c_int(n[2]),
+                              _ptr(lo), _ptr(hi), C.c_int(nranks), C.c_int(rank), C.c_int(node_offset))
+        if rc != 0:
+            raise FourCError(rc, "fc_grid_create")
+        self.h, self.celltype, self.n, self.nranks, self.rank = h, celltype, tuple(n), nranks, rank
+        s = np.zeros(6, np.int64)
+        L.fc_grid_sizes(h, _ptr(s))
+        self.n_row_nodes, self.n_col_nodes, self.n_row_eles, self.n_col_eles = (int(v) for v in s[:4])
+        self.min_node_gid, self.nen = int(s[4]), int(s[5])
+        self.node_gid = np.zeros(self.n_col_nodes, np.int32)
+        self.node_owner = np.zeros(self.n_col_nodes, np.int32)
+        self.X = np.zeros((self.n_col_nodes, 3))
+        L.fc_grid_get_nodes(h, _ptr(self.node_gid), _ptr(self.node_owner), _ptr(self.X))
+        self.ele_gid = np.zeros(self.n_col_eles, np.int32)
+        self.ele_owner = np.zeros(self.n_col_eles, np.int32)
+        self.conn = np.zeros((self.n_col_eles, self.nen), np.int32)
+        L.fc_grid_get_elements(h, _ptr(self.ele_gid), _ptr(self.ele_owner), _ptr(self.conn))
+        sub = np.zeros(3, np.int32)
+        L.fc_grid_subdivisions(h, _ptr(sub))
+        self.subdivisions = tuple(int(v) for v in sub)
+        self.send_count = np.zeros(nranks, np.int32)
+        self.recv_count = np.zeros(nranks, np.int32)
+        L.fc_grid_halo_counts(h, _ptr(self.send_count), _ptr(self.recv_count))
+        self.send_nodes = np.zeros(int(self.send_count.sum()), np.int32)
+        if len(self.send_nodes):
+            L.fc_grid_halo_send_nodes(h, _ptr(self.send_nodes))
+
+    def dof_gid(self, node_gid):
+        """4C_fem_dofset.cpp:344-352: 3 (gid - min gid) + j"""
+        g = (np.asarray(node_gid, np.int64) - self.min_node_gid) * 3
+        return (g[:, None] + np.arange(3)[None, :]).reshape(-1)
+
+    def __del__(self):
+        try:
+            lib().fc_grid_destroy(self.h)
+        except Exception:
+            pass
+
+
+class Solid:
+    """One rank's context (fc_solid_*)."""
+
+    def __init__(self, device=0, rank=0, nranks=1):
+        L = lib()
+        self.h = C.c_void_p()
+        rc = L.fc_solid_create(C.byref(self.h), C.c_int(device), C.c_int(rank), C.c_int(nranks))
+        if rc != 0:
+            self.h = C.c_void_p()
+            raise FourCError(rc, L.fc_last_error(None).decode() or "fc_solid_create failed")
+        self.rank, self.nranks, self.device = rank, nranks, device
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise FourCError(rc, lib().fc_last_error(self.h).decode())
+
+    def set_stream(self, stream_handle):
+        self._chk(lib().fc_solid_set_stream(self.h, C.c_void_p(stream_handle)))
+
+    def set_mesh(self, celltype, formulation, X, node_gid, node_owner, conn, ele_gid):
+        X, node_gid, node_owner, conn, ele_gid = _f64(X), _i32(node_gid), _i32(node_owner), _i32(conn), _i32(ele_gid)
+        self.celltype, self.nen = celltype, NEN[celltype]
+        self.n_col_nodes, self.n_ele = len(node_gid), len(ele_gid)
+        self.n_col_dof = 3 * self.n_col_nodes
+        self.n_row_dof = 3 * int(np.sum(node_owner == self.rank))
+        self._chk(lib().fc_solid_set_mesh(self.h, C.c_int(celltype), C.c_int(formulation), C.c_int(self.n_col_nodes),
+                                          _ptr(X), _ptr(node_gid), _ptr(node_owner), C.c_int(self.n_ele), _ptr(conn),
+                                          _ptr(ele_gid)))
+
+    def set_material(self, kind, young, nue):
+        p = _f64([young, nue])
+        self._chk(lib().fc_solid_set_material(self.h, C.c_int(kind), _ptr(p), C.c_int(2)))
+
+    def build_graph(self):
+        self._chk(lib().fc_solid_build_graph(self.h))
+        return self.graph_sizes()
+
+    def set_graph(self, rowptr, colind):
+        rowptr, colind = np.ascontiguousarray(rowptr, np.int64), _i32(colind)
+        self._chk(lib().fc_solid_set_graph(self.h, C.c_int(len(rowptr) - 1), _ptr(rowptr), _ptr(colind),
+                                           C.c_int(self.n_col_dof)))
+        return self.graph_sizes()
+
+    def graph_sizes(self):
+        a, b, n = C.c_int(), C.c_int(), C.c_int64()
+        self._chk(lib().fc_solid_graph_sizes(self.h, C.byref(a), C.byref(b), C.byref(n)))
+        self.n_row_dof, self.n_col_dof, self.nnz = a.value, b.value, n.value
+        return a.value, b.value, n.value
+
+    def get_graph(self):
+        rowptr = np.zeros(self.n_row_dof + 1, np.int64)
+        colind = np.zeros(self.nnz, np.int32)
+        self._chk(lib().fc_solid_get_graph(self.h, _ptr(rowptr), _ptr(colind)))
+        return rowptr, colind
+
+    def set_dirichlet_rows(self, rows):
+        rows = _i32(rows)
+        self._chk(lib().fc_solid_set_dirichlet_rows(self.h, C.c_int(len(rows)), _ptr(rows)))
+
+    def evaluate(self, action, u_col, f_row=None, K_values=None, flags=0, want_errors=True):
+        """returns (ele_error_count, first_bad_gid) or None when want_errors is False (asynchronous)."""
+        cnt, gid = C.c_int(0), C.c_int(-1)
+        rc = lib().fc_solid_evaluate(self.h, C.c_int(action), C.c_int(flags), _ptr(u_col), _ptr(f_row), _ptr(K_values),
+                                     C.byref(cnt) if want_errors else None, C.byref(gid) if want_errors else None)
+        if rc == FC_ERR_NEGATIVE_JACOBIAN and want_errors:
+            return cnt.value, gid.value
+        self._chk(rc)
+        return (cnt.value, gid.value) if want_errors else None
+
+    def error_state(self):
+        cnt, gid = C.c_int(0), C.c_int(-1)
+        rc = lib().fc_solid_error_state(self.h, C.byref(cnt), C.byref(gid))
+        if rc not in (FC_OK, FC_ERR_NEGATIVE_JACOBIAN):
+            self._chk(rc)
+        return cnt.value, gid.value
+
+    def zero(self, f_row=None, K_values=None):
+        self._chk(lib().fc_solid_zero(self.h, _ptr(f_row), _ptr(K_values)))
+
+    def evaluate_elements(self, u_col, want_K=True, flags=0):
+        nd = 3 * self.nen
+        fe = np.zeros((self.n_ele, nd))
+        Ke = np.zeros((self.n_ele, nd, nd)) if want_K else None
+        self._chk(lib().fc_solid_set_element_kernel_flags(self.h, C.c_int(flags)))
+        self._chk(lib().fc_solid_evaluate_elements(self.h, _ptr(u_col), _ptr(fe), _ptr(Ke)))
+        if want_K:
+            Ke = np.ascontiguousarray(Ke.transpose(0, 2, 1))  # column-major per element -> [e, r, c]
+        return fe, Ke
+
+    def halo_set_send(self, send_row_lids):
+        s = _i32(send_row_lids)
+        self._chk(lib().fc_solid_halo_set_send(self.h, C.c_int(len(s)), _ptr(s)))
+
+    def halo_pack(self, u_dev, sendbuf_dev):
+        self._chk(lib().fc_solid_halo_pack(self.h, _ptr(u_dev), _ptr(sendbuf_dev)))
+
+    def last_kernel_ms(self):
+        a, b = C.c_float(), C.c_float()
+        self._chk(lib().fc_solid_last_kernel_ms(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def launch_count(self):
+        n = C.c_int64()
+        self._chk(lib().fc_solid_kernel_launch_count(self.h, C.byref(n)))
+        return n.value
+
+    def close(self):
+        if self.h:
+            lib().fc_solid_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

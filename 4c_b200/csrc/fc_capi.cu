@@ -1,0 +1,164 @@
+// libfourc_b200.so — C ABI implementation (host side).  See include/fourc_b200.h.
+// There is no CPU fallback anywhere in this file: every compute entry point launches CUDA
+// kernels on the context's device or fails.
+#include <algorithm>
+#include <climits>
+#include <cstdio>
+#include <cstring>
+#include <thread>
+
+#include "../../include/fourc_b200.h"
+#include "fc_context.hpp"
+#include "fc_host_util.hpp"
+#include "fc_kernels_setup.cuh"
+
+
+extern "C"
+{
+  const char* fc_version(void) { return "fourc_b200 0.1 (sm_100a)"; }
+
+  const char* fc_last_error(const fc_ctx* ctx) { return ctx ? ctx->last_error.c_str() : g_create_error.c_str(); }
+
+  int fc_solid_create(fc_ctx** out, int device, int rank, int nranks)
+  {
+    if (!out || nranks < 1 || rank < 0 || rank >= nranks) return FC_ERR_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+    {
+      cudaGetLastError();
+      g_create_error = "no CUDA device visible: libfourc_b200 has no CPU fallback";
+      return FC_ERR_NO_DEVICE;
+    }
+    if (device < 0 || device >= ndev) return FC_ERR_INVALID;
+    if (cudaSetDevice(device) != cudaSuccess) return FC_ERR_CUDA;
+    fc_ctx* ctx = new fc_ctx;
+    ctx->device = device;
+    ctx->rank = rank;
+    ctx->nranks = nranks;
+    if (cudaMalloc((void**)&ctx->d_err, 2 * sizeof(int)) != cudaSuccess ||
+        cudaMallocHost((void**)&ctx->h_err_pinned, 2 * sizeof(int)) != cudaSuccess)
+    {
+      delete ctx;
+      return FC_ERR_CUDA;
+    }
+    for (auto& e : ctx->ev) cudaEventCreate(&e);
+    *out = ctx;
+    return FC_OK;
+  }
+
+  void fc_solid_destroy(fc_ctx* ctx)
+  {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    dev_free(ctx->d_X);
+    dev_free(ctx->d_conn);
+    dev_free(ctx->d_ele_gid);
+    dev_free(ctx->d_dNtab);
+    dev_free(ctx->d_gpw);
+    dev_free(ctx->d_ele_bad);
+    dev_free(ctx->d_node_rowbase);
+    dev_free(ctx->d_node_rowlen);
+    dev_free(ctx->d_slots);
+    dev_free(ctx->d_dbc);
+    dev_free(ctx->d_send_lids);
+    dev_free(ctx->d_stage_u);
+    dev_free(ctx->d_stage_f);
+    dev_free(ctx->d_stage_K);
+    dev_free(ctx->d_err);
+    if (ctx->h_err_pinned) cudaFreeHost(ctx->h_err_pinned);
+    for (auto& e : ctx->ev)
+      if (e) cudaEventDestroy(e);
+    delete ctx;
+  }
+
+  int fc_solid_set_stream(fc_ctx* ctx, void* cuda_stream)
+  {
+    if (!ctx) return FC_ERR_INVALID;
+    ctx->stream = (cudaStream_t)cuda_stream;
+    return FC_OK;
+  }
+
+  int fc_solid_set_material(fc_ctx* ctx, int kind, const double* params, int n_params)
+  {
+    if (!ctx || !params || n_params < 2) return FC_ERR_INVALID;
+    if (kind != FC_MAT_STVENANTKIRCHHOFF && kind != FC_MAT_ELASTHYPER_COUPNEOHOOKE)
+      return fail(ctx, FC_ERR_UNSUPPORTED, "material kind not on the path");
+    const double young = params[0], nue = params[1];
+    // parameter checks of the reference's input spec: YOUNG > 0, NUE in (-1, 0.5)
+    if (!(young > 0.0) || !(nue > -1.0) || !(nue < 0.5)) return fail(ctx, FC_ERR_INVALID, "YOUNG must be > 0 and NUE in (-1, 0.5)");
+    ctx->mat.kind = kind == FC_MAT_STVENANTKIRCHHOFF ? fc::MAT_SVK : fc::MAT_NEOHOOKE;
+    ctx->mat.young = young;
+    ctx->mat.nue = nue;
+    ctx->have_material = true;
+    return FC_OK;
+  }
+
+  int fc_solid_set_mesh(fc_ctx* ctx, int celltype, int formulation, int n_col_nodes, const double* X,
+      const int* node_gid, const int* node_owner, int n_col_ele, const int* conn, const int* ele_gid)
+  {
+    if (!ctx || !X || !node_owner || !conn || !ele_gid || n_col_nodes <= 0 || n_col_ele < 0) return FC_ERR_INVALID;
+    (void)node_gid;
+    if (celltype != FC_HEX8 && celltype != FC_HEX27 && celltype != FC_TET10)
+      return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
+    if (formulation != FC_FORM_DISPLACEMENT && !(formulation == FC_FORM_FBAR && celltype == FC_HEX8))
+      return fail(ctx, FC_ERR_UNSUPPORTED, "F-bar exists for hex8 only (4C_solid_3D_ele_factory.hpp:49-50)");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    const int nen = fc::cell_nen(celltype);
+    // owned nodes first (Epetra column-map convention)
+    int n_row = 0;
+    while (n_row < n_col_nodes && node_owner[n_row] == ctx->rank) ++n_row;
+    for (int i = n_row; i < n_col_nodes; ++i)
+      if (node_owner[i] == ctx->rank) return fail(ctx, FC_ERR_INVALID, "owned nodes must precede ghost nodes");
+    for (size_t i = 0; i < (size_t)n_col_ele * nen; ++i)
+      if (conn[i] < 0 || conn[i] >= n_col_nodes) return fail(ctx, FC_ERR_INVALID, "connectivity entry out of range");
+    ctx->celltype = celltype;
+    ctx->formulation = formulation;
+    ctx->nen = nen;
+    ctx->n_col_nodes = n_col_nodes;
+    ctx->n_row_nodes = n_row;
+    ctx->n_ele = n_col_ele;
+    ctx->h_conn.assign(conn, conn + (size_t)n_col_ele * nen);
+    ctx->h_node_owner.assign(node_owner, node_owner + n_col_nodes);
+    ctx->h_ele_gid.assign(ele_gid, ele_gid + n_col_ele);
+    ctx->have_graph = false;
+    ctx->n_col_dof = 3 * n_col_nodes;
+    ctx->n_row_dof = 3 * n_row;
+    FC_CUDA(dev_upload(ctx->d_X, X, (size_t)3 * n_col_nodes, ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_conn, conn, (size_t)n_col_ele * nen, ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_ele_gid, ele_gid, (size_t)n_col_ele, ctx->stream));
+    std::vector<double> dN, w;
+    if (celltype == FC_HEX8) fill_tables<fc::HEX8>(dN, w);
+    if (celltype == FC_HEX27) fill_tables<fc::HEX27>(dN, w);
+    if (celltype == FC_TET10) fill_tables<fc::TET10>(dN, w);
+    FC_CUDA(dev_upload(ctx->d_dNtab, dN.data(), dN.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_gpw, w.data(), w.size(), ctx->stream));
+    dev_free(ctx->d_ele_bad);
+    ctx->geom_bad_count = 0;
+    ctx->geom_first_bad_gid = -1;
+    if (n_col_ele > 0)
+    {
+      FC_CUDA(cudaMalloc((void**)&ctx->d_ele_bad, (size_t)n_col_ele));
+      ctx->h_err_pinned[0] = 0;
+      ctx->h_err_pinned[1] = INT_MAX;
+      FC_CUDA(cudaMemcpyAsync(ctx->d_err, ctx->h_err_pinned, 2 * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+      const int bs = 128, gs = (n_col_ele + bs - 1) / bs;
+      if (celltype == FC_HEX8)
+        fc::k_check_node_jacobians<fc::HEX8><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_ele_gid, n_col_ele, ctx->d_dNtab, ctx->d_ele_bad, ctx->d_err);
+      else if (celltype == FC_HEX27)
+        fc::k_check_node_jacobians<fc::HEX27><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_ele_gid, n_col_ele, ctx->d_dNtab, ctx->d_ele_bad, ctx->d_err);
+      else
+        fc::k_check_node_jacobians<fc::TET10><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_ele_gid, n_col_ele, ctx->d_dNtab, ctx->d_ele_bad, ctx->d_err);
+      ctx->launches++;
+      FC_CUDA(cudaGetLastError());
+      FC_CUDA(cudaMemcpyAsync(ctx->h_err_pinned, ctx->d_err, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (n_col_ele > 0 && ctx->h_err_pinned[0] > 0)
+    {
+      ctx->geom_bad_count = ctx->h_err_pinned[0];
+      ctx->geom_first_bad_gid = ctx->h_err_pinned[1];
+    }
+    return FC_OK;
+  }
+}

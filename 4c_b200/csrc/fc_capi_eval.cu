@@ -1,0 +1,276 @@
+// The hot path: fc_solid_evaluate and friends.  Kernel selection:
+//   hex8 + displacement-based + CoupNeoHooke -> closed-form kernel on FP64 tensor cores
+//                                               (fc_kernels_hex8nh_mma.cuh), or its FP64-FMA
+//                                               sibling with FC_EVAL_CLOSED_FORM_FMA
+//   everything else (and FC_EVAL_FORCE_GENERIC) -> generic B-operator kernel (fc_kernels_generic.cuh)
+#include <climits>
+
+#include "fc_host_util.hpp"
+#include "fc_kernels_generic.cuh"
+#include "fc_kernels_hex8nh.cuh"
+#include "fc_kernels_hex8nh_mma.cuh"
+#include "fc_kernels_setup.cuh"
+
+namespace
+{
+  template <int CT, int FORM, bool WANT_K>
+  cudaError_t launch_generic(fc_ctx* ctx, const fc::EvalArgs& A)
+  {
+    using Cfg = fc::GenCfg<CT, FORM>;
+    auto kern = fc::k_generic<CT, FORM, WANT_K>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+    if (e != cudaSuccess) return e;
+    const int grid = (A.n_ele + Cfg::epb - 1) / Cfg::epb;
+    kern<<<grid, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
+  template <bool WANT_K>
+  cudaError_t launch_hex8nh(fc_ctx* ctx, const fc::EvalArgs& A, bool fma_variant)
+  {
+    if (fma_variant)
+    {
+      using Cfg = fc::Hex8NHCfg;
+      auto kern = fc::k_hex8_neohooke<WANT_K>;
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+      if (e != cudaSuccess) return e;
+      kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+    }
+    else
+    {
+      using Cfg = fc::Hex8MmaCfg;
+      auto kern = fc::k_hex8_neohooke_mma<WANT_K>;
+      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+      if (e != cudaSuccess) return e;
+      kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+    }
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
+  template <bool WANT_K>
+  cudaError_t dispatch(fc_ctx* ctx, const fc::EvalArgs& A, int flags)
+  {
+    const bool fbar = ctx->formulation == FC_FORM_FBAR;
+    if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC))
+      return launch_hex8nh<WANT_K>(ctx, A, (flags & FC_EVAL_CLOSED_FORM_FMA) != 0);
+    if (ctx->celltype == FC_HEX8) return fbar ? launch_generic<fc::HEX8, fc::FORM_FBAR, WANT_K>(ctx, A) : launch_generic<fc::HEX8, fc::FORM_DISP, WANT_K>(ctx, A);
+    if (ctx->celltype == FC_HEX27) return launch_generic<fc::HEX27, fc::FORM_DISP, WANT_K>(ctx, A);
+    return launch_generic<fc::TET10, fc::FORM_DISP, WANT_K>(ctx, A);
+  }
+
+  fc::EvalArgs base_args(const fc_ctx* ctx)
+  {
+    fc::EvalArgs A{};
+    A.X = ctx->d_X;
+    A.conn = ctx->d_conn;
+    A.ele_gid = ctx->d_ele_gid;
+    A.n_ele = ctx->n_ele;
+    A.n_row_nodes = ctx->n_row_nodes;
+    A.dNtab = ctx->d_dNtab;
+    A.gpw = ctx->d_gpw;
+    A.node_rowbase = ctx->d_node_rowbase;
+    A.node_rowlen = ctx->d_node_rowlen;
+    A.slots = ctx->d_slots;
+    A.dbc = ctx->have_dbc ? ctx->d_dbc : nullptr;
+    A.err = ctx->d_err;
+    A.mat = ctx->mat;
+    return A;
+  }
+
+  int reset_err(fc_ctx* ctx)
+  {
+    ctx->h_err_pinned[0] = 0;
+    ctx->h_err_pinned[1] = INT_MAX;
+    FC_CUDA(cudaMemcpyAsync(ctx->d_err, ctx->h_err_pinned, 2 * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    return FC_OK;
+  }
+
+  int read_err(fc_ctx* ctx, int* count, int* first_gid)
+  {
+    FC_CUDA(cudaMemcpyAsync(ctx->h_err_pinned, ctx->d_err, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (count) *count = ctx->h_err_pinned[0];
+    if (first_gid) *first_gid = ctx->h_err_pinned[0] > 0 ? ctx->h_err_pinned[1] : -1;
+    return FC_OK;
+  }
+}  // namespace
+
+extern "C"
+{
+  int fc_solid_zero(fc_ctx* ctx, double* f_row_dev, double* K_values_dev)
+  {
+    if (!ctx || !ctx->have_graph) return fail(ctx, FC_ERR_INVALID, "graph required");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    if (f_row_dev) FC_CUDA(cudaMemsetAsync(f_row_dev, 0, sizeof(double) * (size_t)ctx->n_row_dof, ctx->stream));
+    if (K_values_dev) FC_CUDA(cudaMemsetAsync(K_values_dev, 0, sizeof(double) * (size_t)ctx->nnz, ctx->stream));
+    ctx->launches += (f_row_dev ? 1 : 0) + (K_values_dev ? 1 : 0);
+    return FC_OK;
+  }
+
+  int fc_solid_evaluate(fc_ctx* ctx, int action, int flags, const double* u_col, double* f_row,
+      double* K_values, int* ele_error_count, int* first_bad_ele_gid)
+  {
+    if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede evaluate");
+    if (!ctx->have_material) return fail(ctx, FC_ERR_INVALID, "set_material must precede evaluate");
+    if (!u_col) return fail(ctx, FC_ERR_INVALID, "u_col is required");
+    if (action != FC_ACTION_NLNSTIFF && action != FC_ACTION_INTERNALFORCE) return fail(ctx, FC_ERR_UNSUPPORTED, "action not on the path");
+    const bool want_K = action == FC_ACTION_NLNSTIFF;
+    if (want_K && !K_values) return fail(ctx, FC_ERR_INVALID, "K_values is required for struct_calc_nlnstiff");
+    if (want_K && !ctx->have_graph) return fail(ctx, FC_ERR_INVALID, "set_graph/build_graph must precede struct_calc_nlnstiff");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+
+    // host callers: stage through device buffers (copies are part of the call)
+    const bool u_dev = is_device_ptr(u_col), f_dev = !f_row || is_device_ptr(f_row), K_dev = !want_K || is_device_ptr(K_values);
+    const double* d_u = u_col;
+    double* d_f = f_row;
+    double* d_K = want_K ? K_values : nullptr;
+    if (!u_dev)
+    {
+      FC_CUDA(ensure_cap(ctx->d_stage_u, ctx->stage_u_cap, (size_t)ctx->n_col_dof));
+      FC_CUDA(cudaMemcpyAsync(ctx->d_stage_u, u_col, sizeof(double) * (size_t)ctx->n_col_dof, cudaMemcpyHostToDevice, s));
+      d_u = ctx->d_stage_u;
+    }
+    if (!f_dev)
+    {
+      FC_CUDA(ensure_cap(ctx->d_stage_f, ctx->stage_f_cap, (size_t)ctx->n_row_dof));
+      if (!(flags & FC_EVAL_ZERO_FIRST))
+        FC_CUDA(cudaMemcpyAsync(ctx->d_stage_f, f_row, sizeof(double) * (size_t)ctx->n_row_dof, cudaMemcpyHostToDevice, s));
+      d_f = ctx->d_stage_f;
+    }
+    if (!K_dev)
+    {
+      FC_CUDA(ensure_cap(ctx->d_stage_K, ctx->stage_K_cap, (size_t)ctx->nnz));
+      if (!(flags & FC_EVAL_ZERO_FIRST))
+        FC_CUDA(cudaMemcpyAsync(ctx->d_stage_K, K_values, sizeof(double) * (size_t)ctx->nnz, cudaMemcpyHostToDevice, s));
+      d_K = ctx->d_stage_K;
+    }
+
+    FC_CUDA(cudaEventRecord(ctx->ev[0], s));
+    if (flags & FC_EVAL_ZERO_FIRST)
+    {
+      if (d_f) FC_CUDA(cudaMemsetAsync(d_f, 0, sizeof(double) * (size_t)ctx->n_row_dof, s));
+      if (d_K) FC_CUDA(cudaMemsetAsync(d_K, 0, sizeof(double) * (size_t)ctx->nnz, s));
+      ctx->launches += (d_f ? 1 : 0) + (d_K ? 1 : 0);
+    }
+    FC_CUDA(cudaEventRecord(ctx->ev[1], s));
+    if (int rc = reset_err(ctx)) return rc;
+    fc::EvalArgs A = base_args(ctx);
+    A.u = d_u;
+    A.f = d_f;
+    A.K = d_K;
+    if (ctx->n_ele > 0) FC_CUDA(want_K ? dispatch<true>(ctx, A, flags) : dispatch<false>(ctx, A, flags));
+    FC_CUDA(cudaEventRecord(ctx->ev[2], s));
+    ctx->ev_valid = true;
+
+    if (!f_dev) FC_CUDA(cudaMemcpyAsync(f_row, d_f, sizeof(double) * (size_t)ctx->n_row_dof, cudaMemcpyDeviceToHost, s));
+    if (!K_dev) FC_CUDA(cudaMemcpyAsync(K_values, d_K, sizeof(double) * (size_t)ctx->nnz, cudaMemcpyDeviceToHost, s));
+    const bool must_sync = !f_dev || !K_dev || ele_error_count || first_bad_ele_gid;
+    if (must_sync)
+    {
+      int cnt = 0, gid = -1;
+      if (int rc = read_err(ctx, &cnt, &gid)) return rc;
+      if (ele_error_count) *ele_error_count = cnt;
+      if (first_bad_ele_gid) *first_bad_ele_gid = gid;
+      if (ctx->geom_bad_count > 0)
+        return fail(ctx, FC_ERR_NEGATIVE_JACOBIAN, "determinant of jacobian is <= 0 at one node of an element");
+    }
+    return FC_OK;
+  }
+
+  int fc_solid_error_state(fc_ctx* ctx, int* ele_error_count, int* first_bad_ele_gid)
+  {
+    if (!ctx) return FC_ERR_INVALID;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    if (int rc = read_err(ctx, ele_error_count, first_bad_ele_gid)) return rc;
+    if (ctx->geom_bad_count > 0) return fail(ctx, FC_ERR_NEGATIVE_JACOBIAN, "determinant of jacobian is <= 0 at one node of an element");
+    return FC_OK;
+  }
+
+  int fc_solid_evaluate_elements(fc_ctx* ctx, const double* u_col, double* fe, double* Ke)
+  {
+    if (!ctx || ctx->celltype < 0 || !ctx->have_material || !u_col || !fe) return fail(ctx, FC_ERR_INVALID, "mesh, material, u_col and fe are required");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = ctx->stream;
+    const size_t nd = 3 * (size_t)ctx->nen, ne = (size_t)ctx->n_ele;
+    const bool u_dev = is_device_ptr(u_col), fe_dev = is_device_ptr(fe), Ke_dev = !Ke || is_device_ptr(Ke);
+    double *d_u = nullptr, *d_fe = nullptr, *d_Ke = nullptr;
+    if (!u_dev)
+    {
+      FC_CUDA(cudaMalloc((void**)&d_u, sizeof(double) * (size_t)ctx->n_col_dof));
+      FC_CUDA(cudaMemcpyAsync(d_u, u_col, sizeof(double) * (size_t)ctx->n_col_dof, cudaMemcpyHostToDevice, s));
+    }
+    if (!fe_dev) FC_CUDA(cudaMalloc((void**)&d_fe, sizeof(double) * ne * nd));
+    if (!Ke_dev) FC_CUDA(cudaMalloc((void**)&d_Ke, sizeof(double) * ne * nd * nd));
+    if (int rc = reset_err(ctx)) return rc;
+    fc::EvalArgs A = base_args(ctx);
+    A.u = u_dev ? u_col : d_u;
+    A.node_rowbase = nullptr;
+    A.node_rowlen = nullptr;
+    A.slots = nullptr;
+    A.dbc = nullptr;
+    A.fe_out = fe_dev ? fe : d_fe;
+    A.Ke_out = Ke ? (Ke_dev ? Ke : d_Ke) : nullptr;
+    // failing elements leave their slots untouched: define them as zero
+    FC_CUDA(cudaMemsetAsync(A.fe_out, 0, sizeof(double) * ne * nd, s));
+    if (A.Ke_out) FC_CUDA(cudaMemsetAsync(A.Ke_out, 0, sizeof(double) * ne * nd * nd, s));
+    const int flags = ctx->eval_elements_flags;
+    if (ne > 0) FC_CUDA(Ke ? dispatch<true>(ctx, A, flags) : dispatch<false>(ctx, A, flags));
+    if (!fe_dev) FC_CUDA(cudaMemcpyAsync(fe, d_fe, sizeof(double) * ne * nd, cudaMemcpyDeviceToHost, s));
+    if (!Ke_dev) FC_CUDA(cudaMemcpyAsync(Ke, d_Ke, sizeof(double) * ne * nd * nd, cudaMemcpyDeviceToHost, s));
+    FC_CUDA(cudaStreamSynchronize(s));
+    if (d_u) cudaFree(d_u);
+    if (d_fe) cudaFree(d_fe);
+    if (d_Ke) cudaFree(d_Ke);
+    return FC_OK;
+  }
+
+  int fc_solid_set_element_kernel_flags(fc_ctx* ctx, int flags)
+  {
+    if (!ctx) return FC_ERR_INVALID;
+    ctx->eval_elements_flags = flags;
+    return FC_OK;
+  }
+
+  int fc_solid_halo_set_send(fc_ctx* ctx, int n_send, const int* send_row_lids)
+  {
+    if (!ctx || n_send < 0 || (n_send > 0 && !send_row_lids)) return FC_ERR_INVALID;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    for (int i = 0; i < n_send; ++i)
+      if (send_row_lids[i] < 0 || send_row_lids[i] >= 3 * ctx->n_row_nodes) return fail(ctx, FC_ERR_INVALID, "send DOF is not an owned row");
+    FC_CUDA(dev_upload(ctx->d_send_lids, send_row_lids, (size_t)n_send, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->n_send = n_send;
+    return FC_OK;
+  }
+
+  int fc_solid_halo_pack(fc_ctx* ctx, const double* u_dev, double* sendbuf_dev)
+  {
+    if (!ctx || !u_dev || (ctx->n_send > 0 && !sendbuf_dev)) return FC_ERR_INVALID;
+    if (ctx->n_send == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    const int bs = 256;
+    fc::k_halo_pack<<<(ctx->n_send + bs - 1) / bs, bs, 0, ctx->stream>>>(u_dev, ctx->d_send_lids, ctx->n_send, sendbuf_dev);
+    ctx->launches++;
+    FC_CUDA(cudaGetLastError());
+    return FC_OK;
+  }
+
+  int fc_solid_last_kernel_ms(fc_ctx* ctx, float* zero_ms, float* element_ms)
+  {
+    if (!ctx || !ctx->ev_valid) return FC_ERR_INVALID;
+    FC_CUDA(cudaEventSynchronize(ctx->ev[2]));
+    if (zero_ms) FC_CUDA(cudaEventElapsedTime(zero_ms, ctx->ev[0], ctx->ev[1]));
+    if (element_ms) FC_CUDA(cudaEventElapsedTime(element_ms, ctx->ev[1], ctx->ev[2]));
+    return FC_OK;
+  }
+
+  int fc_solid_kernel_launch_count(const fc_ctx* ctx, int64_t* launches)
+  {
+    if (!ctx || !launches) return FC_ERR_INVALID;
+    *launches = ctx->launches;
+    return FC_OK;
+  }
+}

@@ -1,0 +1,63 @@
+// Context of one rank/GPU: mesh, graph and scatter maps resident in HBM.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "fc_material.cuh"
+
+struct fc_ctx
+{
+  int device = 0, rank = 0, nranks = 1;
+  cudaStream_t stream = nullptr;
+  std::string last_error;
+
+  // mesh
+  int celltype = -1, formulation = 0, nen = 0;
+  int n_col_nodes = 0, n_row_nodes = 0, n_ele = 0;
+  std::vector<int> h_conn;        // caller order, column-node LIDs
+  std::vector<int> h_node_owner;  // per column node
+  std::vector<int> h_ele_gid;
+  double* d_X = nullptr;     // [n_col_nodes][3]
+  int* d_conn = nullptr;     // [n_ele][nen]
+  int* d_ele_gid = nullptr;  // [n_ele]
+  double* d_dNtab = nullptr; // [ngp + nen + 1][nen][3]: Gauss points, node positions, centroid
+  double* d_gpw = nullptr;   // [ngp] weights
+  unsigned char* d_ele_bad = nullptr;  // [n_ele] 1 = det J <= 0 at an element node
+  int geom_bad_count = 0, geom_first_bad_gid = -1;
+
+  // material
+  fc::MatParams mat{fc::MAT_NEOHOOKE, 10.0, 0.25};
+  bool have_material = false;
+
+  // graph (node-block CSR: every owned node row lists its coupled column nodes, ascending LID)
+  bool have_graph = false;
+  int n_row_dof = 0, n_col_dof = 0;
+  int64_t nnz = 0;
+  std::vector<int64_t> h_nodeptr;  // [n_row_nodes+1] in units of nodes
+  std::vector<int> h_nodeadj;      // column-node LIDs
+  int64_t* d_node_rowbase = nullptr;  // [n_col_nodes] CSR offset of DOF row 3*n, -1 for ghosts
+  int* d_node_rowlen = nullptr;       // [n_col_nodes] entries per DOF row (3*neighbours)
+  unsigned char* d_slots = nullptr;   // [n_ele][nen][nen] position of node b in the row of node a
+  unsigned char* d_dbc = nullptr;     // [n_row_dof] 1 = row skipped by the matrix scatter
+  bool have_dbc = false;
+
+  // halo send plan
+  int n_send = 0;
+  int* d_send_lids = nullptr;
+
+  // scratch + error state
+  double* d_stage_u = nullptr;  // staging for host callers
+  double* d_stage_f = nullptr;
+  double* d_stage_K = nullptr;
+  size_t stage_u_cap = 0, stage_f_cap = 0, stage_K_cap = 0;
+  int* d_err = nullptr;  // [0] = #failing elements, [1] = min failing gid (INT_MAX if none)
+  int* h_err_pinned = nullptr;
+
+  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  bool ev_valid = false;
+  int64_t launches = 0;
+  int eval_elements_flags = 0;
+};

@@ -1,0 +1,194 @@
+// Shape-function derivatives, Gauss rules and small dense helpers shared by host setup code and
+// device kernels (all __host__ __device__).  Definitions follow the reference (paths relative
+// to the reference tree):
+//   shape functions  src/core/fem/src/general/utils/4C_fem_general_utils_fem_shapefunctions.hpp
+//                    hex8 :53-72/:386-427, hex27 :190-230/:683-792, tet10 :244-259/:808-850
+//   Gauss rules      src/core/fem/src/general/utils/4C_fem_general_utils_integration.cpp
+//                    hex_8point :74-105, hex_27point :130-243, tet_4point :331-350
+//   rule selection   src/solid_3D_ele/4C_solid_3D_ele_calc_lib_integration.hpp:39-62
+#pragma once
+#include <cmath>
+
+#if defined(__CUDACC__)
+#define FC_HD __host__ __device__ __forceinline__
+#else
+#define FC_HD inline
+#endif
+
+namespace fc
+{
+  enum
+  {
+    HEX8 = 0,
+    HEX27 = 1,
+    TET10 = 2
+  };
+
+  template <int CT>
+  struct Cell;
+  template <>
+  struct Cell<HEX8>
+  {
+    static constexpr int nen = 8, ngp = 8;
+  };
+  template <>
+  struct Cell<HEX27>
+  {
+    static constexpr int nen = 27, ngp = 27;
+  };
+  template <>
+  struct Cell<TET10>
+  {
+    static constexpr int nen = 10, ngp = 4;
+  };
+
+  FC_HD int cell_nen(int ct) { return ct == HEX8 ? 8 : (ct == HEX27 ? 27 : 10); }
+  FC_HD int cell_ngp(int ct) { return ct == HEX8 ? 8 : (ct == HEX27 ? 27 : 4); }
+
+  // Parameter-space sign/position of hex node a in direction d as an integer in {-1,0,1}.
+  // Reference numbering: corners 0-7, edge mids 8-19, face centres 20-25, centre 26.
+  FC_HD int hex_node_pos(int a, int d)
+  {
+    // packed as base-3 digits (value+1) for (r,s,t)
+    const unsigned char tab[27] = {
+        0 + 0 * 3 + 0 * 9, 2 + 0 * 3 + 0 * 9, 2 + 2 * 3 + 0 * 9, 0 + 2 * 3 + 0 * 9,  // 0-3
+        0 + 0 * 3 + 2 * 9, 2 + 0 * 3 + 2 * 9, 2 + 2 * 3 + 2 * 9, 0 + 2 * 3 + 2 * 9,  // 4-7
+        1 + 0 * 3 + 0 * 9, 2 + 1 * 3 + 0 * 9, 1 + 2 * 3 + 0 * 9, 0 + 1 * 3 + 0 * 9,  // 8-11
+        0 + 0 * 3 + 1 * 9, 2 + 0 * 3 + 1 * 9, 2 + 2 * 3 + 1 * 9, 0 + 2 * 3 + 1 * 9,  // 12-15
+        1 + 0 * 3 + 2 * 9, 2 + 1 * 3 + 2 * 9, 1 + 2 * 3 + 2 * 9, 0 + 1 * 3 + 2 * 9,  // 16-19
+        1 + 1 * 3 + 0 * 9, 1 + 0 * 3 + 1 * 9, 2 + 1 * 3 + 1 * 9, 1 + 2 * 3 + 1 * 9,  // 20-23
+        0 + 1 * 3 + 1 * 9, 1 + 1 * 3 + 2 * 9, 1 + 1 * 3 + 1 * 9};                    // 24-26
+    int v = tab[a];
+    if (d == 1) v /= 3;
+    if (d == 2) v /= 9;
+    return v % 3 - 1;
+  }
+
+  FC_HD void node_param_coords(int ct, int a, double* xi)
+  {
+    if (ct == TET10)
+    {
+      // corners (0,0,0),(1,0,0),(0,1,0),(0,0,1); mids 4:(01) 5:(12) 6:(02) 7:(03) 8:(13) 9:(23)
+      const double t[10][3] = {{0, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {.5, 0, 0}, {.5, .5, 0},
+          {0, .5, 0}, {0, 0, .5}, {.5, 0, .5}, {0, .5, .5}};
+      xi[0] = t[a][0];
+      xi[1] = t[a][1];
+      xi[2] = t[a][2];
+    }
+    else
+    {
+      for (int d = 0; d < 3; ++d) xi[d] = (double)hex_node_pos(a, d);
+    }
+  }
+
+  // dN[3*a+d] = dN_a/dxi_d
+  template <int CT>
+  FC_HD void shape_deriv1(const double* xi, double* dN)
+  {
+    const double r = xi[0], s = xi[1], t = xi[2];
+    if constexpr (CT == HEX8)
+    {
+      const double q = 0.125;
+      const double rf[2] = {1.0 - r, 1.0 + r}, sf[2] = {1.0 - s, 1.0 + s}, tf[2] = {1.0 - t, 1.0 + t};
+#pragma unroll
+      for (int a = 0; a < 8; ++a)
+      {
+        const int ir = hex_node_pos(a, 0) > 0, is = hex_node_pos(a, 1) > 0, it = hex_node_pos(a, 2) > 0;
+        dN[3 * a + 0] = (ir ? q : -q) * sf[is] * tf[it];
+        dN[3 * a + 1] = (is ? q : -q) * tf[it] * rf[ir];
+        dN[3 * a + 2] = (it ? q : -q) * rf[ir] * sf[is];
+      }
+    }
+    else if constexpr (CT == HEX27)
+    {
+      const double R[3] = {0.5 * r * (r - 1.0), 1.0 - r * r, 0.5 * r * (r + 1.0)};
+      const double S[3] = {0.5 * s * (s - 1.0), 1.0 - s * s, 0.5 * s * (s + 1.0)};
+      const double T[3] = {0.5 * t * (t - 1.0), 1.0 - t * t, 0.5 * t * (t + 1.0)};
+      const double dR[3] = {r - 0.5, -2.0 * r, r + 0.5};
+      const double dS[3] = {s - 0.5, -2.0 * s, s + 0.5};
+      const double dT[3] = {t - 0.5, -2.0 * t, t + 0.5};
+      for (int a = 0; a < 27; ++a)
+      {
+        const int ir = hex_node_pos(a, 0) + 1, is = hex_node_pos(a, 1) + 1, it = hex_node_pos(a, 2) + 1;
+        dN[3 * a + 0] = S[is] * T[it] * dR[ir];
+        dN[3 * a + 1] = R[ir] * T[it] * dS[is];
+        dN[3 * a + 2] = R[ir] * S[is] * dT[it];
+      }
+    }
+    else
+    {
+      const double u = 1.0 - r - s - t;
+      const double d0 = -4.0 * u + 1.0;
+      const double v[30] = {d0, d0, d0, 4.0 * r - 1.0, 0, 0, 0, 4.0 * s - 1.0, 0, 0, 0, 4.0 * t - 1.0,
+          4.0 * (u - r), -4.0 * r, -4.0 * r, 4.0 * s, 4.0 * r, 0, -4.0 * s, 4.0 * (u - s), -4.0 * s,
+          -4.0 * t, -4.0 * t, 4.0 * (u - t), 4.0 * t, 0, 4.0 * r, 0, 4.0 * t, 4.0 * s};
+      for (int i = 0; i < 30; ++i) dN[i] = v[i];
+    }
+  }
+
+  // Gauss rule of the stiffness/force integral: point g of cell type CT
+  template <int CT>
+  FC_HD void gauss_point(int g, double* xi, double* w)
+  {
+    if constexpr (CT == HEX8)
+    {
+      const double p = 0.57735026918962576451;  // 1/sqrt(3)
+      for (int d = 0; d < 3; ++d) xi[d] = hex_node_pos(g, d) > 0 ? p : -p;
+      *w = 1.0;
+    }
+    else if constexpr (CT == HEX27)
+    {
+      // the reference's truncated 13-digit constants (integration.cpp:133,214-215)
+      const double p = 0.7745966692415, w1 = 0.5555555555556, w2 = 0.8888888888889;
+      double ww = 1.0;
+      for (int d = 0; d < 3; ++d)
+      {
+        const int s = hex_node_pos(g, d);
+        xi[d] = s == 0 ? 0.0 : (s > 0 ? p : -p);
+        ww *= (s == 0 ? w2 : w1);
+      }
+      // reference multiplies the three 1D weights left to right in (r,s,t) order
+      *w = ww;
+    }
+    else
+    {
+      const double pa = (5.0 + 3.0 * 2.2360679774997896964) / 20.0;
+      const double pb = (5.0 - 2.2360679774997896964) / 20.0;
+      xi[0] = xi[1] = xi[2] = pb;
+      if (g > 0) xi[g - 1] = pa;
+      *w = 1.0 / 24.0;
+    }
+  }
+
+  FC_HD void centroid_param(int ct, double* xi)
+  {
+    const double c = ct == TET10 ? 0.25 : 0.0;
+    xi[0] = xi[1] = xi[2] = c;
+  }
+
+  // ---- 3x3 helpers, row-major a[3*r+c] ------------------------------------------------------------
+  FC_HD double det3(const double* a)
+  {
+    return a[0] * (a[4] * a[8] - a[5] * a[7]) - a[1] * (a[3] * a[8] - a[5] * a[6]) +
+           a[2] * (a[3] * a[7] - a[4] * a[6]);
+  }
+  // inv = a^-1, returns det
+  FC_HD double inv3(const double* a, double* inv)
+  {
+    const double c0 = a[4] * a[8] - a[5] * a[7];
+    const double c1 = a[5] * a[6] - a[3] * a[8];
+    const double c2 = a[3] * a[7] - a[4] * a[6];
+    const double det = a[0] * c0 + a[1] * c1 + a[2] * c2;
+    const double id = 1.0 / det;
+    inv[0] = c0 * id;
+    inv[1] = (a[2] * a[7] - a[1] * a[8]) * id;
+    inv[2] = (a[1] * a[5] - a[2] * a[4]) * id;
+    inv[3] = c1 * id;
+    inv[4] = (a[0] * a[8] - a[2] * a[6]) * id;
+    inv[5] = (a[2] * a[3] - a[0] * a[5]) * id;
+    inv[6] = c2 * id;
+    inv[7] = (a[1] * a[6] - a[0] * a[7]) * id;
+    inv[8] = (a[0] * a[4] - a[1] * a[3]) * id;
+    return det;
+  }
+}  // namespace fc

@@ -1,0 +1,262 @@
+// Specialised element kernel, tensor-core variant: hex8, displacement-based, CoupNeoHooke.
+//
+// Same closed form as fc_kernels_hex8nh.cuh,
+//   K_ab[i][j] = 2 beta W_ij[a][b] + W_ji[a][b] + delta_ij s[a][b]
+//   W_ij[a][b] = sum_gp ghat[gp][a][i] ghat[gp][b][j]      ghat = sqrt(kappa) g
+//   s[a][b]    = sum_gp sum_i nhat[gp][a][i] nhat[gp][b][i] nhat = sqrt(lambda) grad N
+//   f_a        = sum_b s[a][b] x_b - sum_gp sqrt(kappa) ghat[gp][a]
+// but the contractions over Gauss points are dense 8x8x8 products per component pair (i,j): nine
+// for W, three accumulated into s.  They run on the FP64 tensor cores (mma.sync m8n8k4 f64, DMMA):
+// one warp multiplies one element at a time, A and B fragments are the same registers, and the
+// accumulator layout leaves every lane holding the two complete 3x3 blocks K_{a,b0}, K_{a,b0+1}
+// (a = lane/4, b0 = 2 (lane%4)), so the epilogue and the CSR scatter need no data exchange.
+//
+// Work decomposition: a warp owns 4 elements.
+//   phase 0  lane (el, t) gathers node t of element el (coordinates relative to node 0)
+//   phase 1  lane (el, g) evaluates Gauss point g of element el -> ghat, nhat in fragment layout (smem)
+//   phase 2  for each of the 4 elements: 12 fragment loads, 24 DMMA (6 for the force-only action)
+//   phase 3  epilogue + fire-and-forget FP64 reductions into the CSR rows / residual
+#pragma once
+#include "fc_kernels_common.cuh"
+
+namespace fc
+{
+  struct Hex8MmaCfg
+  {
+    static constexpr int warps = 4;
+    static constexpr int threads = 32 * warps;
+    static constexpr int epw = 4;                       // elements per warp
+    static constexpr int epb = warps * epw;             // elements per CTA
+    // per element: 6 component planes of 64 (fragment layout), sqrt(kappa)[8], x rel [8][3], pad
+    static constexpr int oSk = 384, oX = 392, ele_doubles = 392 + 24 + 1;
+    static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles;
+  };
+
+  __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
+  {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+  }
+
+  // position of (gp, node) inside a 64-entry component plane: one k-step (4 Gauss points) of one
+  // half of the nodes is a contiguous, bank-conflict-free 128-byte line for the fragment loads
+  __device__ __forceinline__ int frag_idx(int gp, int node) { return 32 * (gp >> 2) + 16 * (node >> 2) + 4 * (gp & 3) + (node & 3); }
+
+  template <bool WANT_K>
+  __global__ void __launch_bounds__(Hex8MmaCfg::threads) k_hex8_neohooke_mma(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
+  {
+    using Cfg = Hex8MmaCfg;
+    extern __shared__ double smem[];
+    __shared__ long long s_rowbase[Cfg::epb][8];
+    __shared__ int s_rowlen[Cfg::epb][8];
+    __shared__ int s_node[Cfg::epb][8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int el = lane >> 3, t = lane & 7;   // phase 0/1 role
+    const int wel = warp * Cfg::epw;          // first element slot of this warp inside the CTA
+    const int e = blockIdx.x * Cfg::epb + wel + el;
+    const bool active = e < A.n_ele;
+    double* E = smem + (size_t)(wel + el) * Cfg::ele_doubles;
+
+    // ---- phase 0 ----------------------------------------------------------------------------------
+    double Xr[3] = {0, 0, 0}, xr[3] = {0, 0, 0};
+    int node = 0;
+    if (active)
+    {
+      node = __ldg(A.conn + (size_t)e * 8 + t);
+      for (int i = 0; i < 3; ++i)
+      {
+        Xr[i] = __ldg(A.X + 3 * (size_t)node + i);
+        xr[i] = __ldg(A.u + 3 * (size_t)node + i);
+      }
+    }
+    {
+      const bool owned = active && node < A.n_row_nodes;
+      long long rb = -1;
+      int rl = 0;
+      if (WANT_K && owned && A.K)
+      {
+        rb = __ldg(A.node_rowbase + node);
+        rl = __ldg(A.node_rowlen + node);
+      }
+      s_rowbase[wel + el][t] = rb;
+      s_rowlen[wel + el][t] = rl;
+      s_node[wel + el][t] = owned ? node : -1;
+    }
+    // coordinates relative to node 0 of the element (sum_a dN_a = 0, so J and F are unchanged)
+    for (int i = 0; i < 3; ++i)
+    {
+      const double X0 = __shfl_sync(0xFFFFFFFFu, Xr[i], lane & 24);
+      const double u0 = __shfl_sync(0xFFFFFFFFu, xr[i], lane & 24);
+      Xr[i] -= X0;
+      xr[i] = Xr[i] + (xr[i] - u0);
+    }
+    // phase 1 needs all 8 nodes of the element: exchange through registers (shuffles inside the group)
+    // ---- phase 1: Gauss point t of element el ----------------------------------------------------
+    bool bad = false;
+    {
+      const double p = 0.57735026918962576451;
+      const double xi0 = (hex_node_pos(t, 0) > 0) ? p : -p;
+      const double xi1 = (hex_node_pos(t, 1) > 0) ? p : -p;
+      const double xi2 = (hex_node_pos(t, 2) > 0) ? p : -p;
+      double jm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Jm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      double dN[24];
+#pragma unroll
+      for (int a = 0; a < 8; ++a)
+      {
+        const int src = (lane & 24) | a;
+        double xa[3], Xa[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+        {
+          xa[i] = __shfl_sync(0xFFFFFFFFu, xr[i], src);
+          Xa[i] = __shfl_sync(0xFFFFFFFFu, Xr[i], src);
+        }
+        const double s0 = hex_node_pos(a, 0), s1 = hex_node_pos(a, 1), s2 = hex_node_pos(a, 2);
+        const double r = 1.0 + s0 * xi0, s = 1.0 + s1 * xi1, q = 1.0 + s2 * xi2;
+        dN[3 * a + 0] = 0.125 * s0 * s * q;
+        dN[3 * a + 1] = 0.125 * s1 * q * r;
+        dN[3 * a + 2] = 0.125 * s2 * r * s;
+#pragma unroll
+        for (int d = 0; d < 3; ++d)
+#pragma unroll
+          for (int i = 0; i < 3; ++i)
+          {
+            jm[3 * d + i] += dN[3 * a + d] * xa[i];
+            Jm[3 * d + i] += dN[3 * a + d] * Xa[i];
+          }
+      }
+      double ji[9], Ji[9];
+      const double detj = inv3(jm, ji);
+      const double detJ = inv3(Jm, Ji);
+      const double detF = detj / detJ;
+      const double I3 = detF * detF;
+      const double c2 = A.mat.young / (2.0 * (1.0 + A.mat.nue));  // 2c
+      const double beta = A.mat.nue / (1.0 - 2.0 * A.mat.nue);
+      const double lambda = detJ * c2;  // Gauss weight of hex_8point is 1
+      const double kappa = lambda * exp(-beta * log(I3));
+      bad = active && (!(detJ > 0.0) || !(I3 > 0.0) || !isfinite(kappa) || (ele_bad && ele_bad[e]));
+      const double sk = sqrt(kappa), sl = sqrt(lambda);
+      if (active)
+      {
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+        {
+          const double d0 = dN[3 * a], d1 = dN[3 * a + 1], d2 = dN[3 * a + 2];
+          const int ix = frag_idx(t, a);
+          E[0 * 64 + ix] = sk * (ji[0] * d0 + ji[1] * d1 + ji[2] * d2);
+          E[1 * 64 + ix] = sk * (ji[3] * d0 + ji[4] * d1 + ji[5] * d2);
+          E[2 * 64 + ix] = sk * (ji[6] * d0 + ji[7] * d1 + ji[8] * d2);
+          E[3 * 64 + ix] = sl * (Ji[0] * d0 + Ji[1] * d1 + Ji[2] * d2);
+          E[4 * 64 + ix] = sl * (Ji[3] * d0 + Ji[4] * d1 + Ji[5] * d2);
+          E[5 * 64 + ix] = sl * (Ji[6] * d0 + Ji[7] * d1 + Ji[8] * d2);
+        }
+        E[Cfg::oSk + t] = sk;
+        for (int i = 0; i < 3; ++i) E[Cfg::oX + 3 * t + i] = xr[i];
+      }
+    }
+    const unsigned badmask = __ballot_sync(0xFFFFFFFFu, bad);
+    const unsigned actmask = __ballot_sync(0xFFFFFFFFu, active);
+    if (active && t == 0 && ((badmask >> (lane & 24)) & 0xFFu)) report_error(A.err, __ldg(A.ele_gid + e));
+    __syncwarp();
+
+    // ---- phase 2 + 3: one element at a time, whole warp ------------------------------------------
+    const int a = lane >> 2, q = lane & 3, b0 = 2 * q;
+    const double beta2 = 2.0 * A.mat.nue / (1.0 - 2.0 * A.mat.nue);
+#pragma unroll 1
+    for (int k = 0; k < Cfg::epw; ++k)
+    {
+      if (!((actmask >> (8 * k)) & 1u) || ((badmask >> (8 * k)) & 0xFFu)) continue;  // warp-uniform
+      const int ek = blockIdx.x * Cfg::epb + wel + k;
+      const double* G = smem + (size_t)(wel + k) * Cfg::ele_doubles;
+      const int fo = 16 * (lane >> 4) + 4 * q + (a & 3);  // frag_idx(q, a)
+      double fg[6][2];
+#pragma unroll
+      for (int c = 0; c < 6; ++c)
+      {
+        fg[c][0] = G[c * 64 + fo];
+        fg[c][1] = G[c * 64 + 32 + fo];
+      }
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+      {
+        dmma884(s0, s1, fg[3 + i][0], fg[3 + i][0]);
+        dmma884(s0, s1, fg[3 + i][1], fg[3 + i][1]);
+      }
+      // internal force: lanes of the same row node a reduce over their column pairs / Gauss points
+      {
+        const double* xk = G + Cfg::oX;
+        const double sk0 = G[Cfg::oSk + q], sk1 = G[Cfg::oSk + 4 + q];
+        double fpart[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+        {
+          fpart[i] = s0 * xk[3 * b0 + i] + s1 * xk[3 * b0 + 3 + i] - (sk0 * fg[i][0] + sk1 * fg[i][1]);
+          fpart[i] += __shfl_xor_sync(0xFFFFFFFFu, fpart[i], 1);
+          fpart[i] += __shfl_xor_sync(0xFFFFFFFFu, fpart[i], 2);
+        }
+        const int na = s_node[wel + k][a];
+        if (q < 3)
+        {
+          const double v = q == 0 ? fpart[0] : (q == 1 ? fpart[1] : fpart[2]);
+          if (A.fe_out) A.fe_out[(size_t)ek * 24 + 3 * a + q] = v;
+          if (A.f && na >= 0) red_add(A.f + 3 * (size_t)na + q, v);
+        }
+      }
+      if (!WANT_K) continue;
+      double W[3][3][2];
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+        {
+          W[i][j][0] = 0.0;
+          W[i][j][1] = 0.0;
+          dmma884(W[i][j][0], W[i][j][1], fg[i][0], fg[j][0]);
+          dmma884(W[i][j][0], W[i][j][1], fg[i][1], fg[j][1]);
+        }
+      double Kb[2][9];
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+        {
+          Kb[0][3 * i + j] = beta2 * W[i][j][0] + W[j][i][0] + (i == j ? s0 : 0.0);
+          Kb[1][3 * i + j] = beta2 * W[i][j][1] + W[j][i][1] + (i == j ? s1 : 0.0);
+        }
+      if (A.Ke_out)
+      {
+        double* Ke = A.Ke_out + (size_t)ek * 576;
+        for (int c = 0; c < 2; ++c)
+          for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) Ke[(3 * a + i) + 24 * (3 * (b0 + c) + j)] = Kb[c][3 * i + j];
+      }
+      if (A.K)
+      {
+        const long long rb = s_rowbase[wel + k][a];
+        if (rb >= 0)
+        {
+          const int rl = s_rowlen[wel + k][a];
+          const int na = s_node[wel + k][a];
+          const unsigned short sl2 = __ldg(reinterpret_cast<const unsigned short*>(A.slots + (size_t)ek * 64) + lane);
+          const int slot0 = sl2 & 0xFF, slot1 = sl2 >> 8;
+#pragma unroll
+          for (int i = 0; i < 3; ++i)
+          {
+            if (A.dbc && A.dbc[3 * na + i]) continue;
+            double* row = A.K + rb + (long long)i * rl;
+            double* p0 = row + 3 * slot0;
+            double* p1 = row + 3 * slot1;
+            red_add(p0 + 0, Kb[0][3 * i + 0]);
+            red_add(p0 + 1, Kb[0][3 * i + 1]);
+            red_add(p0 + 2, Kb[0][3 * i + 2]);
+            red_add(p1 + 0, Kb[1][3 * i + 0]);
+            red_add(p1 + 1, Kb[1][3 * i + 1]);
+            red_add(p1 + 2, Kb[1][3 * i + 2]);
+          }
+        }
+      }
+    }
+  }
+}  // namespace fc

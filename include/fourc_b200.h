@@ -1,0 +1,185 @@
+/* fourc_b200.h — C ABI of libfourc_b200.so
+ *
+ * B200-native (CUDA sm_100a) replacement for ONE hot path of 4C: the per-Newton-iteration
+ * evaluation of internal force + tangent stiffness of all 3D solid elements of a rank and the
+ * scatter into the rank's CSR system.  Paths below are relative to the reference tree.
+ *
+ * Reference seam this library is called from:
+ *   Solid::ModelEvaluator::Structure::evaluate_internal
+ *     src/structure_new/src/model_evaluator/4C_structure_new_model_evaluator_structure.cpp:1293-1312
+ *   -> Core::FE::Discretization::evaluate(params, K, 0, f, 0, 0)
+ *     src/core/fem/src/discretization/4C_fem_discretization_evaluate.cpp:31-103
+ *
+ * Conventions
+ *   - all entry points return 0 (FC_OK) or a negative fc_status; no exceptions cross the ABI.
+ *   - plain pointers + sizes only.  Pointers marked "host|device" are classified with
+ *     cudaPointerGetAttributes; host buffers are staged inside the call.
+ *   - one fc_ctx per rank/GPU, driven from one host thread.  All device work is enqueued on the
+ *     context's stream (fc_solid_set_stream); calls with host output buffers synchronise.
+ *   - there is NO CPU fallback: without a CUDA device fc_solid_create fails with
+ *     FC_ERR_NO_DEVICE.  The fc_grid_* / fc_graph_* helpers are pure host integer code.
+ *   - local node numbering follows the Epetra column-map convention: the n_row_nodes owned nodes
+ *     come first (ascending GID), ghosts after them grouped by owner rank.  Local DOF id =
+ *     3*node_lid + j; row DOF lid == column DOF lid for owned DOFs.
+ */
+#ifndef FOURC_B200_H
+#define FOURC_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C"
+{
+#endif
+
+  typedef struct fc_ctx fc_ctx;
+
+  typedef enum
+  {
+    FC_OK = 0,
+    FC_ERR_INVALID = -1,           /* bad argument / call order */
+    FC_ERR_NO_DEVICE = -2,         /* no CUDA device: there is no CPU fallback */
+    FC_ERR_CUDA = -3,              /* CUDA runtime error, see fc_last_error() */
+    FC_ERR_NEGATIVE_JACOBIAN = -4, /* det J <= 0 at an element node (4C_solid_3D_ele_calc_lib.hpp:492-494) */
+    FC_ERR_GRAPH = -5,             /* element couples DOFs that are not in the CSR graph */
+    FC_ERR_UNSUPPORTED = -6        /* cell type / formulation / material combination not on the path */
+  } fc_status;
+
+  /* cell types on the path: src/solid_3D_ele/4C_solid_3D_ele_factory.hpp:36-82 */
+  enum
+  {
+    FC_HEX8 = 0,
+    FC_HEX27 = 1,
+    FC_TET10 = 2
+  };
+  /* element technology (TECH none | fbar): src/solid_3D_ele/4C_solid_3D_ele.cpp:71-138 */
+  enum
+  {
+    FC_FORM_DISPLACEMENT = 0, /* 4C_solid_3D_ele_calc_displacement_based.hpp:35-251 */
+    FC_FORM_FBAR = 1          /* 4C_solid_3D_ele_calc_fbar.hpp:43-191 (hex8 only) */
+  };
+  /* materials: MAT_Struct_StVenantKirchhoff (src/mat/4C_mat_stvenantkirchhoff.cpp) and
+   * MAT_ElastHyper with one ELAST_CoupNeoHooke summand (src/mat/4C_mat_elasthyper.cpp,
+   * src/mat/elast/4C_mat_elast_coupneohooke.cpp).  params = {YOUNG, NUE}. */
+  enum
+  {
+    FC_MAT_STVENANTKIRCHHOFF = 0,
+    FC_MAT_ELASTHYPER_COUPNEOHOOKE = 1
+  };
+  /* element actions: src/solid_3D_ele/4C_solid_3D_ele_evaluate.cpp:82-134 */
+  enum
+  {
+    FC_ACTION_NLNSTIFF = 0,     /* struct_calc_nlnstiff: f += fint, K += stiffness */
+    FC_ACTION_INTERNALFORCE = 1 /* struct_calc_internalforce: f += fint */
+  };
+  /* evaluate flags */
+  enum
+  {
+    FC_EVAL_ZERO_FIRST = 1, /* zero K values and f before adding (SparseMatrix::zero +
+                               Vector::put_scalar(0), 4C_structure_new_model_evaluator_structure.cpp:136-159) */
+    FC_EVAL_FORCE_GENERIC = 2, /* use the generic B-operator kernel even where a specialised
+                                  closed-form kernel exists (testing / comparison) */
+    FC_EVAL_CLOSED_FORM_FMA = 4 /* hex8 Neo-Hooke closed form on the FP64 FMA pipe instead of the
+                                   FP64 tensor cores (comparison) */
+  };
+
+  /* ---- context ------------------------------------------------------------------------------ */
+  int fc_solid_create(fc_ctx** ctx, int device, int rank, int nranks);
+  void fc_solid_destroy(fc_ctx* ctx);
+  /* cudaStream_t passed as void*; NULL = legacy default stream */
+  int fc_solid_set_stream(fc_ctx* ctx, void* cuda_stream);
+  const char* fc_last_error(const fc_ctx* ctx);
+  const char* fc_version(void);
+
+  /* ---- problem definition ------------------------------------------------------------------- */
+  /* Replaces the per-element node/material pointers of Core::Elements::Element
+   * (location_vector, 4C_fem_general_element.cpp:474-541; evaluate_element_nodes,
+   * 4C_solid_3D_ele_calc_lib.hpp:152-203).
+   *   X          [3*n_col_nodes] reference coordinates, node-major (host)
+   *   node_gid   [n_col_nodes]   (host)
+   *   node_owner [n_col_nodes]   owner rank of each column node (host)
+   *   conn       [nen*n_col_ele] column-node LIDs in the reference's node order (host)
+   *   ele_gid    [n_col_ele]     (host)
+   * Runs the node-Jacobian check of ensure_positive_jacobian_determinant_at_element_nodes once
+   * on the device (the result only depends on X); a failure is reported by every evaluate. */
+  int fc_solid_set_mesh(fc_ctx* ctx, int celltype, int formulation, int n_col_nodes, const double* X,
+      const int* node_gid, const int* node_owner, int n_col_ele, const int* conn, const int* ele_gid);
+
+  int fc_solid_set_material(fc_ctx* ctx, int kind, const double* params, int n_params);
+
+  /* CSR graph of the rank's rows, the state of Epetra_CrsMatrix after FillComplete on the saved
+   * graph (4C_linalg_sparsematrix.cpp:353-378,843-865): rows = owned DOFs, column ids local and
+   * ascending per row.  set_graph adopts a caller-provided graph (host arrays); build_graph
+   * creates the full element-connectivity pattern "zeros included" (4C_linalg_sparsematrix.cpp:
+   * 578-611) from the mesh.  Either one precomputes the per-element scatter slot map on the device. */
+  int fc_solid_set_graph(fc_ctx* ctx, int n_row_dof, const int64_t* rowptr, const int* colind, int n_col_dof);
+  int fc_solid_build_graph(fc_ctx* ctx);
+  int fc_solid_graph_sizes(const fc_ctx* ctx, int* n_row_dof, int* n_col_dof, int64_t* nnz);
+  /* copy the graph out (host buffers: rowptr [n_row_dof+1], colind [nnz]) */
+  int fc_solid_get_graph(const fc_ctx* ctx, int64_t* rowptr, int* colind);
+
+  /* rows skipped by the scatter, like the dbcmaps_ test in SparseMatrix::assemble
+   * (4C_linalg_sparsematrix.cpp:480).  Only K rows are skipped; f is assembled for all rows. */
+  int fc_solid_set_dirichlet_rows(fc_ctx* ctx, int n, const int* row_lids);
+
+  /* ---- the hot path ---------------------------------------------------------------------------
+   * One Discretization::evaluate(params, K, 0, f, 0, 0) over all column elements.
+   *   u_col    [n_col_dof]  displacement in column layout (after set_state), host|device
+   *   f_row    [n_row_dof]  += internal force of owned rows, host|device, may be NULL
+   *   K_values [nnz]        += stiffness in CSR order (NLNSTIFF only), host|device
+   *   ele_error_count   (host, may be NULL)  number of elements that failed
+   *   first_bad_ele_gid (host, may be NULL)  lowest GID among them, -1 if none
+   * Reading the error counters synchronises the stream; pass NULL for both to stay asynchronous
+   * (device buffers only) and poll later with fc_solid_error_state. */
+  int fc_solid_evaluate(fc_ctx* ctx, int action, int flags, const double* u_col, double* f_row,
+      double* K_values, int* ele_error_count, int* first_bad_ele_gid);
+  int fc_solid_error_state(fc_ctx* ctx, int* ele_error_count, int* first_bad_ele_gid);
+
+  /* SparseMatrix::zero / Vector::put_scalar(0) on device buffers (4C_linalg_sparsematrix.cpp:353-378) */
+  int fc_solid_zero(fc_ctx* ctx, double* f_row_dev, double* K_values_dev);
+
+  /* Element-local evaluation without scatter (Solid::evaluate seam, 4C_solid_3D_ele.hpp:120-124):
+   * fe [n_col_ele][3*nen], Ke [n_col_ele][3*nen][3*nen] column-major per element, in the caller's
+   * element order.  host|device.  Ke may be NULL. */
+  int fc_solid_evaluate_elements(fc_ctx* ctx, const double* u_col, double* fe, double* Ke);
+  /* FC_EVAL_* kernel-selection flags used by fc_solid_evaluate_elements (default 0) */
+  int fc_solid_set_element_kernel_flags(fc_ctx* ctx, int flags);
+
+  /* ---- halo plan for Discretization::set_state (4C_fem_discretization.cpp:503-558) -----------
+   * The forward import row layout -> column layout.  Ghost DOFs sit behind the owned ones grouped
+   * by owner rank, so the receive side needs no unpack: rank p's message lands at
+   * u_col + recv_offset[p].  The send side is a gather of owned DOFs (fc_solid_halo_pack).
+   * The exchange itself (NCCL grouped send/recv) is issued by the caller between pack and evaluate. */
+  int fc_solid_halo_set_send(fc_ctx* ctx, int n_send, const int* send_row_lids);
+  int fc_solid_halo_pack(fc_ctx* ctx, const double* u_dev, double* sendbuf_dev);
+
+  /* ---- timing helpers (device time of the last evaluate, CUDA events on the ctx stream) ----- */
+  int fc_solid_last_kernel_ms(fc_ctx* ctx, float* zero_ms, float* element_ms);
+  int fc_solid_kernel_launch_count(const fc_ctx* ctx, int64_t* launches);
+
+  /* ---- structured cuboid generator + reference decomposition (host, integer arithmetic) ------
+   * Core::IO::GridGenerator::create_rectangular_cuboid_discretization with PARTITION structured
+   * (src/core/io/src/4C_io_gridgenerator.cpp:41-323,328-393), unique node ownership
+   * (src/core/rebalance/src/4C_rebalance_graph_based.cpp:159-214), element owner / ghosting rule
+   * (src/core/fem/src/discretization/4C_fem_discretization_partition.cpp:510-587) and DOF numbering
+   * (src/core/fem/src/dofset/4C_fem_dofset.cpp:344-352), evaluated for ONE rank in closed form. */
+  typedef struct fc_grid fc_grid;
+  int fc_grid_create(fc_grid** g, int celltype, int nx, int ny, int nz, const double* lo,
+      const double* hi, int nranks, int rank, int node_offset);
+  void fc_grid_destroy(fc_grid* g);
+  /* sizes[0..5] = n_row_nodes, n_col_nodes, n_row_eles, n_col_eles, min_node_gid (global), nen */
+  int fc_grid_sizes(const fc_grid* g, int64_t* sizes);
+  int fc_grid_subdivisions(const fc_grid* g, int* sub3);
+  /* column nodes (owned first, ascending GID; ghosts grouped by owner, ascending GID) */
+  int fc_grid_get_nodes(const fc_grid* g, int* node_gid, int* node_owner, double* X);
+  /* column elements (row elements first); conn = column-node LIDs */
+  int fc_grid_get_elements(const fc_grid* g, int* ele_gid, int* ele_owner, int* conn);
+  /* halo plan: counts per peer, then the lists.  send lists are row-node LIDs in ascending GID
+   * per peer; recv lists are implicit (ghost nodes grouped by owner). */
+  int fc_grid_halo_counts(const fc_grid* g, int* send_node_count /*[nranks]*/, int* recv_node_count /*[nranks]*/);
+  int fc_grid_halo_send_nodes(const fc_grid* g, int* send_node_lids /*[sum send counts]*/);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FOURC_B200_H */

@@ -29,7 +29,7 @@ EXPORTS = [
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack",
     "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
-    "fc_grid_halo_counts", "fc_grid_halo_send_nodes",
+    "fc_grid_halo_counts", "fc_grid_halo_send_nodes", "fc_probe_fp64_fma", "fc_probe_fp64_mma",
 ]
 
 
@@ -81,6 +81,16 @@ def _i32(a):
 
 def _f64(a):
     return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def probe_fp64(device=0):
+    """(FMA TFLOP/s, tensor-core TFLOP/s) measured with the library's probe kernels"""
+    a, b = C.c_double(), C.c_double()
+    for f, o in ((lib().fc_probe_fp64_fma, a), (lib().fc_probe_fp64_mma, b)):
+        rc = f(C.c_int(device), C.byref(o))
+        if rc != 0:
+            raise FourCError(rc, "fp64 probe")
+    return a.value, b.value
 
 
 class Grid:

@@ -157,6 +157,11 @@ extern "C"
   int fc_solid_last_kernel_ms(fc_ctx* ctx, float* zero_ms, float* element_ms);
   int fc_solid_kernel_launch_count(const fc_ctx* ctx, int64_t* launches);
 
+  /* FP64 peak probes (TFLOP/s, best of 5) for the roofline denominators: DFMA loop and
+   * mma.sync.m8n8k4.f64 loop on all SMs */
+  int fc_probe_fp64_fma(int device, double* tflops);
+  int fc_probe_fp64_mma(int device, double* tflops);
+
   /* ---- structured cuboid generator + reference decomposition (host, integer arithmetic) ------
    * Core::IO::GridGenerator::create_rectangular_cuboid_discretization with PARTITION structured
    * (src/core/io/src/4C_io_gridgenerator.cpp:41-323,328-393), unique node ownership

@@ -29,7 +29,8 @@ namespace fc
     static constexpr int epb = warps * epw;             // elements per CTA
     // per element: 6 component planes of 64 (fragment layout), sqrt(kappa)[8], x rel [8][3], pad
     static constexpr int oSk = 384, oX = 392, ele_doubles = 392 + 24 + 1;
-    static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles;
+    static constexpr int ks_stride = 24, ks_doubles = 24 * ks_stride;  // per-warp K_e staging for the scatter
+    static constexpr size_t smem_bytes = sizeof(double) * ((size_t)epb * ele_doubles + (size_t)warps * ks_doubles);
   };
 
   __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
@@ -234,28 +235,39 @@ namespace fc
       }
       if (A.K)
       {
-        const long long rb = s_rowbase[wel + k][a];
-        if (rb >= 0)
-        {
-          const int rl = s_rowlen[wel + k][a];
-          const int na = s_node[wel + k][a];
-          const unsigned short sl2 = __ldg(reinterpret_cast<const unsigned short*>(A.slots + (size_t)ek * 64) + lane);
-          const int slot0 = sl2 & 0xFF, slot1 = sl2 >> 8;
+        // stage K_e row-major in shared memory, then let 3 adjacent lanes add the 3 contiguous doubles
+        // of one CSR node block in ONE instruction: the memory system processes reductions per 32-byte
+        // request, so lane-contiguous triples run 2.3x faster than one scattered double per lane
+        // (profiles/r01_red_patterns.md)
+        double* Ks = smem + (size_t)Cfg::epb * Cfg::ele_doubles + (size_t)warp * Cfg::ks_doubles;
 #pragma unroll
-          for (int i = 0; i < 3; ++i)
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+          for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) Ks[(3 * a + i) * Cfg::ks_stride + 3 * (b0 + c) + j] = Kb[c][3 * i + j];
+        __syncwarp();
+        if (lane < 24)
+        {
+          const int b = lane / 3;
+          const unsigned char* sl = A.slots + (size_t)ek * 64 + b;
+#pragma unroll 1
+          for (int aa = 0; aa < 8; ++aa)
           {
-            if (A.dbc && A.dbc[3 * na + i]) continue;
-            double* row = A.K + rb + (long long)i * rl;
-            double* p0 = row + 3 * slot0;
-            double* p1 = row + 3 * slot1;
-            red_add(p0 + 0, Kb[0][3 * i + 0]);
-            red_add(p0 + 1, Kb[0][3 * i + 1]);
-            red_add(p0 + 2, Kb[0][3 * i + 2]);
-            red_add(p1 + 0, Kb[1][3 * i + 0]);
-            red_add(p1 + 1, Kb[1][3 * i + 1]);
-            red_add(p1 + 2, Kb[1][3 * i + 2]);
+            const long long rb = s_rowbase[wel + k][aa];
+            if (rb < 0) continue;  // row node not owned by this rank (warp-uniform)
+            const int rl = s_rowlen[wel + k][aa];
+            const int na = s_node[wel + k][aa];
+            double* p = A.K + rb + 3 * (int)__ldg(sl + 8 * aa) + (lane - 3 * b);
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+            {
+              if (A.dbc && A.dbc[3 * na + i]) continue;
+              red_add(p + (long long)i * rl, Ks[(3 * aa + i) * Cfg::ks_stride + lane]);
+            }
           }
         }
+        __syncwarp();
       }
     }
   }

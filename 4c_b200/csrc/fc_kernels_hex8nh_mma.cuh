@@ -29,8 +29,8 @@ namespace fc
     static constexpr int epb = warps * epw;             // elements per CTA
     // per element: 6 component planes of 64 (fragment layout), sqrt(kappa)[8], x rel [8][3], pad
     static constexpr int oSk = 384, oX = 392, ele_doubles = 392 + 24 + 1;
-    static constexpr int ks_stride = 24, ks_doubles = 24 * ks_stride;  // per-warp K_e staging for the scatter
-    static constexpr size_t smem_bytes = sizeof(double) * ((size_t)epb * ele_doubles + (size_t)warps * ks_doubles);
+    static constexpr int ks_stride = 24;  // K_e staging for the scatter: 12 rows x 24 inside the element's own area
+    static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles;
   };
 
   __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
@@ -239,35 +239,44 @@ namespace fc
         // of one CSR node block in ONE instruction: the memory system processes reductions per 32-byte
         // request, so lane-contiguous triples run 2.3x faster than one scattered double per lane
         // (profiles/r01_red_patterns.md)
-        double* Ks = smem + (size_t)Cfg::epb * Cfg::ele_doubles + (size_t)warp * Cfg::ks_doubles;
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
-#pragma unroll
-          for (int c = 0; c < 2; ++c)
-#pragma unroll
-            for (int j = 0; j < 3; ++j) Ks[(3 * a + i) * Cfg::ks_stride + 3 * (b0 + c) + j] = Kb[c][3 * i + j];
-        __syncwarp();
-        if (lane < 24)
-        {
-          const int b = lane / 3;
-          const unsigned char* sl = A.slots + (size_t)ek * 64 + b;
+        // The staging buffer is the element's own fragment area (already consumed into registers),
+        // filled in two halves of 4 row nodes: no extra shared memory, 4 CTAs per SM.
+        double* Ks = smem + (size_t)(wel + k) * Cfg::ele_doubles;
+        const int b = lane / 3;
+        const unsigned char* sl = A.slots + (size_t)ek * 64 + b;
 #pragma unroll 1
-          for (int aa = 0; aa < 8; ++aa)
+        for (int half = 0; half < 2; ++half)
+        {
+          __syncwarp();
+          if ((a >> 2) == half)
           {
-            const long long rb = s_rowbase[wel + k][aa];
-            if (rb < 0) continue;  // row node not owned by this rank (warp-uniform)
-            const int rl = s_rowlen[wel + k][aa];
-            const int na = s_node[wel + k][aa];
-            double* p = A.K + rb + 3 * (int)__ldg(sl + 8 * aa) + (lane - 3 * b);
 #pragma unroll
             for (int i = 0; i < 3; ++i)
+#pragma unroll
+              for (int c = 0; c < 2; ++c)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) Ks[(3 * (a & 3) + i) * Cfg::ks_stride + 3 * (b0 + c) + j] = Kb[c][3 * i + j];
+          }
+          __syncwarp();
+          if (lane < 24)
+          {
+#pragma unroll 1
+            for (int aa = 4 * half; aa < 4 * half + 4; ++aa)
             {
-              if (A.dbc && A.dbc[3 * na + i]) continue;
-              red_add(p + (long long)i * rl, Ks[(3 * aa + i) * Cfg::ks_stride + lane]);
+              const long long rb = s_rowbase[wel + k][aa];
+              if (rb < 0) continue;  // row node not owned by this rank (warp-uniform)
+              const int rl = s_rowlen[wel + k][aa];
+              const int na = s_node[wel + k][aa];
+              double* p = A.K + rb + 3 * (int)__ldg(sl + 8 * aa) + (lane - 3 * b);
+#pragma unroll
+              for (int i = 0; i < 3; ++i)
+              {
+                if (A.dbc && A.dbc[3 * na + i]) continue;
+                red_add(p + (long long)i * rl, Ks[(3 * (aa & 3) + i) * Cfg::ks_stride + lane]);
+              }
             }
           }
         }
-        __syncwarp();
       }
     }
   }

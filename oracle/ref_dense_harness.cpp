@@ -15,9 +15,9 @@
 // src/core/utils/src/exceptions/4C_utils_exceptions.cpp)
 namespace FourC::Core::Internal
 {
-  [[noreturn]] void throw_error(const char* file, const char* func, int line, const std::string& msg)
+  [[noreturn]] void throw_error(const ErrorHelper& error_helper, const std::string& formatted_message)
   {
-    throw std::runtime_error(msg);
+    throw std::runtime_error(std::string(error_helper.file_name) + ": " + formatted_message);
   }
 }  // namespace FourC::Core::Internal
 

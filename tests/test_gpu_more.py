@@ -1,0 +1,155 @@
+"""More GPU tests through the C ABI: device-pointer path, multi-rank decomposition emulated on one GPU
+(one context per rank, halo pack kernel + peer copies), error reporting, full-size invariants."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+HEX8, DISP, FBAR, SVK, NH = 0, 0, 1, 0, 1
+
+
+def field(X, h):
+    A = np.array([[0.03, 0.01, -0.02], [0.00, -0.02, 0.015], [0.01, 0.02, 0.025]])
+    return X @ A.T + 0.01 * np.sin(2 * np.pi * X[:, [1, 2, 0]])
+
+
+def make_ctx(fc, grid, form=DISP, mat=NH, nue=0.25, rank=0, nranks=1):
+    s = fc.Solid(0, rank, nranks)
+    s.set_mesh(fc.FC_HEX8, form, grid.X, grid.node_gid, grid.node_owner, grid.conn, grid.ele_gid)
+    s.set_material(mat, 10.0, nue)
+    s.build_graph()
+    return s
+
+
+@pytest.mark.parametrize("nranks,n", [(2, (8, 6, 5)), (4, (8, 8, 4)), (8, (6, 6, 6))])
+def test_multi_rank_on_one_gpu_matches_oracle(fc, oracle, nranks, n):
+    """Variant A of SURVEY 8e: halo import of u, redundant ghost elements, owner rows only."""
+    import torch
+    job = oracle.Job.cuboid(HEX8, n, nranks=nranks)
+    job.set_problem(DISP, NH, 10.0, 0.25)
+    u_nodes = field(job.X, 1.0 / max(n))
+    job.set_u_nodal(u_nodes)
+    assert job.evaluate(oracle.ACTION_NLNSTIFF, max_threads=4)[0] == 0
+    grids = [fc.Grid(HEX8, n, nranks=nranks, rank=r) for r in range(nranks)]
+    ctxs = [make_ctx(fc, grids[r], rank=r, nranks=nranks) for r in range(nranks)]
+    dev = torch.device("cuda", 0)
+    # row-layout state per rank on the device; ghost part poisoned
+    u_col, sendbuf = [], []
+    for r, g in enumerate(grids):
+        u = torch.full((3 * g.n_col_nodes,), float("nan"), dtype=torch.float64, device=dev)
+        u[:3 * g.n_row_nodes] = torch.from_numpy(field(g.X[:g.n_row_nodes], 0).reshape(-1)).to(dev)
+        u_col.append(u)
+        lids = (3 * g.send_nodes[:, None] + np.arange(3)).reshape(-1)
+        ctxs[r].halo_set_send(lids)
+        sendbuf.append(torch.empty(len(lids), dtype=torch.float64, device=dev))
+        ctxs[r].halo_pack(u, sendbuf[r])
+    torch.cuda.synchronize()
+    # the exchange (NCCL all-to-all in bench.py) as device copies: p's message for q lands behind q's owned DOFs
+    for q, gq in enumerate(grids):
+        off = 3 * gq.n_row_nodes
+        for p in range(nranks):
+            cnt = 3 * int(gq.recv_count[p])
+            s0 = 3 * int(grids[p].send_count[:q].sum())
+            u_col[q][off:off + cnt] = sendbuf[p][s0:s0 + cnt]
+            off += cnt
+    for r, g in enumerate(grids):
+        assert not torch.isnan(u_col[r]).any()
+        n_row, n_col, nnz = ctxs[r].graph_sizes()
+        K = torch.zeros(nnz, dtype=torch.float64, device=dev)
+        f = torch.zeros(n_row, dtype=torch.float64, device=dev)
+        assert ctxs[r].evaluate(fc.FC_ACTION_NLNSTIFF, u_col[r], f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+        o = job.rank(r)
+        Kr, fr = job.get_K(r, o["nnz"]), job.get_f(r, o["n_row_dof"])
+        if nnz:
+            assert np.max(np.abs(K.cpu().numpy() - Kr)) <= 1e-12 * np.max(np.abs(Kr))
+            assert np.max(np.abs(f.cpu().numpy() - fr)) <= 1e-12 * np.max(np.abs(Kr)) / max(n)
+        ctxs[r].close()
+
+
+def test_negative_jacobian_and_bad_state_are_reported(fc):
+    g = fc.Grid(HEX8, (4, 3, 3))
+    conn = g.conn.copy()
+    conn[5, [0, 1]] = conn[5, [1, 0]]  # tangle element 5
+    s = fc.Solid(0)
+    s.set_mesh(fc.FC_HEX8, DISP, g.X, g.node_gid, g.node_owner, conn, g.ele_gid)
+    s.set_material(NH, 10.0, 0.25)
+    n_row, n_col, nnz = s.build_graph()
+    K, f = np.zeros(nnz), np.zeros(n_row)
+    cnt, gid = s.evaluate(fc.FC_ACTION_NLNSTIFF, np.zeros(n_col), f, K)
+    assert cnt == 1 and gid == int(g.ele_gid[5])
+    s.close()
+    # inverted state (det F < 0 everywhere): disp-based Neo-Hooke sees I3 > 0 and must NOT flag it (as the reference),
+    # a collapsed state (F = 0) must
+    s = make_ctx(fc, g)
+    n_row, n_col, nnz = s.graph_sizes()
+    u = (-g.X).reshape(-1).copy()  # x = 0 for all nodes
+    cnt, gid = s.evaluate(fc.FC_ACTION_NLNSTIFF, u, np.zeros(n_row), np.zeros(nnz))
+    assert cnt == g.n_col_eles and gid == int(g.ele_gid.min())
+    s.close()
+
+
+def test_argument_errors(fc):
+    g = fc.Grid(HEX8, (2, 2, 2))
+    s = fc.Solid(0)
+    with pytest.raises(fc.FourCError):
+        s.evaluate(fc.FC_ACTION_NLNSTIFF, np.zeros(3), np.zeros(3), np.zeros(3))  # no mesh
+    with pytest.raises(fc.FourCError):
+        s.set_mesh(fc.FC_HEX27, FBAR, g.X, g.node_gid, g.node_owner, g.conn, g.ele_gid)  # F-bar is hex8 only
+    s.set_mesh(fc.FC_HEX8, DISP, g.X, g.node_gid, g.node_owner, g.conn, g.ele_gid)
+    with pytest.raises(fc.FourCError):
+        s.set_material(NH, 10.0, 0.5)
+    s.set_material(NH, 10.0, 0.25)
+    with pytest.raises(fc.FourCError):
+        s.evaluate(fc.FC_ACTION_NLNSTIFF, np.zeros(81), np.zeros(81), np.zeros(10))  # no graph yet
+    # a graph that misses couplings is rejected
+    rowptr = np.arange(0, 82 * 3, 3, dtype=np.int64)[:82]
+    colind = np.repeat(np.arange(27) * 3, 3 * 3).reshape(27, 3, 3) + np.arange(3)
+    with pytest.raises(fc.FourCError) as ei:
+        s.set_graph(rowptr, colind.reshape(-1))
+    assert ei.value.code == fc.FC_ERR_GRAPH
+    s.close()
+
+
+def test_c2_full_size_invariants(fc):
+    """BASELINE C2 (100^3): size-independent properties of the assembled system on the device."""
+    import torch
+    n = (100, 100, 100)
+    g = fc.Grid(HEX8, n)
+    s = make_ctx(fc, g)
+    n_row, n_col, nnz = s.graph_sizes()
+    assert nnz == 9 * 301 ** 3 == 245_438_109
+    dev = torch.device("cuda", 0)
+    u = torch.from_numpy(field(g.X, 0.01).reshape(-1)).to(dev)
+    K = torch.empty(nnz, dtype=torch.float64, device=dev)
+    f = torch.empty(n_row, dtype=torch.float64, device=dev)
+    assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+    rowptr, colind = s.get_graph()
+    rp = torch.from_numpy(rowptr).to(dev)
+    ci = torch.from_numpy(colind).to(dev).long()
+    # (1) translations are in the null space of K: row sums over each displacement component vanish
+    rows = torch.repeat_interleave(torch.arange(n_row, device=dev), (rp[1:] - rp[:-1]))
+    kmax = K.abs().max()
+    for d in range(3):
+        m = (ci % 3) == d
+        rs = torch.zeros(n_row, dtype=torch.float64, device=dev).index_add_(0, rows[m], K[m])
+        assert rs.abs().max() <= 1e-12 * kmax
+    # (2) symmetry: sum_ij K_ij x_i y_j == sum_ij K_ij y_i x_j for random x, y
+    gen = torch.Generator(device=dev).manual_seed(1)
+    x = torch.rand(n_row, dtype=torch.float64, device=dev, generator=gen)
+    y = torch.rand(n_row, dtype=torch.float64, device=dev, generator=gen)
+    a = (K * x[rows] * y[ci]).sum()
+    b = (K * y[rows] * x[ci]).sum()
+    assert abs(a - b) <= 1e-11 * (K.abs() * x[rows] * y[ci]).sum()
+    # (3) total internal force vanishes (self-equilibrated) and K dx ~ f(u+dx) - f(u)
+    assert f.view(-1, 3).sum(0).abs().max() <= 1e-10 * f.abs().max() * 1e3
+    dx = 1e-7 * (torch.rand(n_col, dtype=torch.float64, device=dev, generator=gen) - 0.5)
+    f2 = torch.empty_like(f)
+    s.evaluate(fc.FC_ACTION_INTERNALFORCE, u + dx, f2, None, flags=fc.FC_EVAL_ZERO_FIRST)
+    Kdx = torch.zeros(n_row, dtype=torch.float64, device=dev).index_add_(0, rows, K * dx[ci])
+    assert (f2 - f - Kdx).abs().max() <= 1e-5 * Kdx.abs().max()
+    # (4) the two closed-form kernels and the generic kernel agree at full size
+    K2 = torch.empty_like(K)
+    for flags in (fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC):
+        s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f2, K2, flags=flags | fc.FC_EVAL_ZERO_FIRST)
+        assert (K2 - K).abs().max() <= 1e-12 * kmax
+        assert (f2 - f).abs().max() <= 1e-12 * kmax * 0.01
+    s.close()

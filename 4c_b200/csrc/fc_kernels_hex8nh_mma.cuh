@@ -52,6 +52,7 @@ namespace fc
     __shared__ long long s_rowbase[Cfg::epb][8];
     __shared__ int s_rowlen[Cfg::epb][8];
     __shared__ int s_node[Cfg::epb][8];
+    __shared__ unsigned long long s_slots[Cfg::epb][8];  // slot row of node t: position of every b in its CSR row
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int el = lane >> 3, t = lane & 7;   // phase 0/1 role
     const int wel = warp * Cfg::epw;          // first element slot of this warp inside the CTA
@@ -75,13 +76,18 @@ namespace fc
       const bool owned = active && node < A.n_row_nodes;
       long long rb = -1;
       int rl = 0;
+      unsigned long long sl = 0;
       if (WANT_K && owned && A.K)
       {
         rb = __ldg(A.node_rowbase + node);
         rl = __ldg(A.node_rowlen + node);
+        sl = __ldg(reinterpret_cast<const unsigned long long*>(A.slots + (size_t)e * 64) + t);
+        if (A.dbc)  // Dirichlet flags of the 3 DOF rows ride in the top bits of the row length
+          for (int i = 0; i < 3; ++i) rl |= (A.dbc[3 * node + i] ? 1 : 0) << (28 + i);
       }
       s_rowbase[wel + el][t] = rb;
       s_rowlen[wel + el][t] = rl;
+      s_slots[wel + el][t] = sl;
       s_node[wel + el][t] = owned ? node : -1;
     }
     // coordinates relative to node 0 of the element (sum_a dN_a = 0, so J and F are unchanged)
@@ -242,9 +248,9 @@ namespace fc
         // The staging buffer is the element's own fragment area (already consumed into registers),
         // filled in two halves of 4 row nodes: no extra shared memory, 4 CTAs per SM.
         double* Ks = smem + (size_t)(wel + k) * Cfg::ele_doubles;
-        const int b = lane / 3;
-        const unsigned char* sl = A.slots + (size_t)ek * 64 + b;
-#pragma unroll 1
+        const int ln = lane < 24 ? lane : 23;  // lanes 24..31 idle in the scatter
+        const int b = ln / 3;
+#pragma unroll
         for (int half = 0; half < 2; ++half)
         {
           __syncwarp();
@@ -258,24 +264,26 @@ namespace fc
                 for (int j = 0; j < 3; ++j) Ks[(3 * (a & 3) + i) * Cfg::ks_stride + 3 * (b0 + c) + j] = Kb[c][3 * i + j];
           }
           __syncwarp();
-          if (lane < 24)
-          {
-#pragma unroll 1
-            for (int aa = 4 * half; aa < 4 * half + 4; ++aa)
-            {
-              const long long rb = s_rowbase[wel + k][aa];
-              if (rb < 0) continue;  // row node not owned by this rank (warp-uniform)
-              const int rl = s_rowlen[wel + k][aa];
-              const int na = s_node[wel + k][aa];
-              double* p = A.K + rb + 3 * (int)__ldg(sl + 8 * aa) + (lane - 3 * b);
+          // all row data of the 4 row nodes first (independent broadcast loads), then 12 reductions
+          double v[12];
+          double* ptr[4];
+          int rl[4];
 #pragma unroll
-              for (int i = 0; i < 3; ++i)
-              {
-                if (A.dbc && A.dbc[3 * na + i]) continue;
-                red_add(p + (long long)i * rl, Ks[(3 * (aa & 3) + i) * Cfg::ks_stride + lane]);
-              }
-            }
+          for (int r = 0; r < 4; ++r)
+          {
+            const int aa = 4 * half + r;
+            const long long rb = s_rowbase[wel + k][aa];
+            const int slot = (int)((s_slots[wel + k][aa] >> (8 * b)) & 0xFF);
+            rl[r] = s_rowlen[wel + k][aa];
+            ptr[r] = (rb >= 0 && lane < 24) ? A.K + rb + 3 * slot + (ln - 3 * b) : nullptr;
+#pragma unroll
+            for (int i = 0; i < 3; ++i) v[3 * r + i] = Ks[(3 * r + i) * Cfg::ks_stride + ln];
           }
+#pragma unroll
+          for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+              if (ptr[r] && !((rl[r] >> (28 + i)) & 1)) red_add(ptr[r] + (long long)i * (rl[r] & 0x0FFFFFFF), v[3 * r + i]);
         }
       }
     }

@@ -38,6 +38,16 @@ namespace fc
   // fire-and-forget FP64 add (RED.E.ADD.F64)
   __device__ __forceinline__ void red_add(double* p, double v) { atomicAdd(p, v); }
 
+  // predicated form: no branch around the reduction
+  __device__ __forceinline__ void red_add_if(bool pred, double* p, double v)
+  {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\tsetp.ne.s32 q, %0, 0;\n\t@q red.global.add.f64 [%1], %2;\n\t}"
+        :
+        : "r"((int)pred), "l"(p), "d"(v)
+        : "memory");
+  }
+
   __device__ __forceinline__ void report_error(int* err, int gid)
   {
     atomicAdd(&err[0], 1);

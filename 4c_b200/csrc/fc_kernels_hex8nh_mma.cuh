@@ -42,13 +42,15 @@ namespace fc
 
   // position of (gp, node) inside a 64-entry component plane: one k-step (4 Gauss points) of one
   // half of the nodes is a contiguous, bank-conflict-free 128-byte line for the fragment loads
-  __device__ __forceinline__ int frag_idx(int gp, int node) { return 32 * (gp >> 2) + 16 * (node >> 2) + 4 * (gp & 3) + (node & 3); }
+  // (the node field is XOR-swizzled with the k-step so that the 8 Gauss-point lanes of phase 1 store conflict-free)
+  __device__ __forceinline__ int frag_idx(int gp, int node) { return 32 * (gp >> 2) + 16 * (node >> 2) + 4 * (gp & 3) + ((node & 3) ^ (2 * (gp >> 2))); }
 
   template <bool WANT_K>
   __global__ void __launch_bounds__(Hex8MmaCfg::threads) k_hex8_neohooke_mma(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
   {
     using Cfg = Hex8MmaCfg;
-    extern __shared__ double smem[];
+    extern __shared__ __align__(16) double smem_mma[];
+    double* const smem = smem_mma;
     __shared__ long long s_rowbase[Cfg::epb][8];
     __shared__ int s_rowlen[Cfg::epb][8];
     __shared__ int s_node[Cfg::epb][8];
@@ -176,13 +178,13 @@ namespace fc
       if (!((actmask >> (8 * k)) & 1u) || ((badmask >> (8 * k)) & 0xFFu)) continue;  // warp-uniform
       const int ek = blockIdx.x * Cfg::epb + wel + k;
       const double* G = smem + (size_t)(wel + k) * Cfg::ele_doubles;
-      const int fo = 16 * (lane >> 4) + 4 * q + (a & 3);  // frag_idx(q, a)
+      const int fo0 = frag_idx(q, a), fo1 = frag_idx(q + 4, a);
       double fg[6][2];
 #pragma unroll
       for (int c = 0; c < 6; ++c)
       {
-        fg[c][0] = G[c * 64 + fo];
-        fg[c][1] = G[c * 64 + 32 + fo];
+        fg[c][0] = G[c * 64 + fo0];
+        fg[c][1] = G[c * 64 + fo1];
       }
       double s0 = 0.0, s1 = 0.0;
 #pragma unroll
@@ -247,7 +249,8 @@ namespace fc
         // (profiles/r01_red_patterns.md)
         // The staging buffer is the element's own fragment area (already consumed into registers),
         // filled in two halves of 4 row nodes: no extra shared memory, 4 CTAs per SM.
-        double* Ks = smem + (size_t)(wel + k) * Cfg::ele_doubles;
+        // (+1 double for odd elements: ele_doubles is odd, the 16-byte staging stores need an even offset)
+        double* Ks = smem + (size_t)(wel + k) * Cfg::ele_doubles + ((wel + k) & 1);
         const int ln = lane < 24 ? lane : 23;  // lanes 24..31 idle in the scatter
         const int b = ln / 3;
 #pragma unroll
@@ -256,12 +259,15 @@ namespace fc
           __syncwarp();
           if ((a >> 2) == half)
           {
+            // 6 contiguous doubles per row as three 16-byte stores: conflict-free for row stride 24
 #pragma unroll
             for (int i = 0; i < 3; ++i)
-#pragma unroll
-              for (int c = 0; c < 2; ++c)
-#pragma unroll
-                for (int j = 0; j < 3; ++j) Ks[(3 * (a & 3) + i) * Cfg::ks_stride + 3 * (b0 + c) + j] = Kb[c][3 * i + j];
+            {
+              double2* row = reinterpret_cast<double2*>(Ks + (3 * (a & 3) + i) * Cfg::ks_stride + 6 * q);
+              row[0] = make_double2(Kb[0][3 * i + 0], Kb[0][3 * i + 1]);
+              row[1] = make_double2(Kb[0][3 * i + 2], Kb[1][3 * i + 0]);
+              row[2] = make_double2(Kb[1][3 * i + 1], Kb[1][3 * i + 2]);
+            }
           }
           __syncwarp();
           // all row data of the 4 row nodes first (independent broadcast loads), then 12 reductions
@@ -283,7 +289,7 @@ namespace fc
           for (int r = 0; r < 4; ++r)
 #pragma unroll
             for (int i = 0; i < 3; ++i)
-              if (ptr[r] && !((rl[r] >> (28 + i)) & 1)) red_add(ptr[r] + (long long)i * (rl[r] & 0x0FFFFFFF), v[3 * r + i]);
+              red_add_if(ptr[r] != nullptr && !((rl[r] >> (28 + i)) & 1), ptr[r] + (long long)i * (rl[r] & 0x0FFFFFFF), v[3 * r + i]);
         }
       }
     }

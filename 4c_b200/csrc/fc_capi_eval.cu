@@ -40,7 +40,7 @@ namespace
     else
     {
       using Cfg = fc::Hex8MmaCfg;
-      auto kern = fc::k_hex8_neohooke_mma<WANT_K>;
+      auto kern = A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true> : fc::k_hex8_neohooke_mma<WANT_K, false>;
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
       if (e != cudaSuccess) return e;
       kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);

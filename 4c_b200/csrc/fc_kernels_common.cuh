@@ -48,6 +48,17 @@ namespace fc
         : "memory");
   }
 
+  // three rows of one node block (row stride in bytes), one predicate, no branches
+  __device__ __forceinline__ void red_add3_if(bool pred, double* p0, long long stride_bytes, double v0, double v1, double v2)
+  {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t.reg .b64 p1, p2;\n\tsetp.ne.s32 q, %0, 0;\n\tadd.s64 p1, %1, %2;\n\tadd.s64 p2, p1, %2;\n\t"
+        "@q red.global.add.f64 [%1], %3;\n\t@q red.global.add.f64 [p1], %4;\n\t@q red.global.add.f64 [p2], %5;\n\t}"
+        :
+        : "r"((int)pred), "l"(p0), "l"(stride_bytes), "d"(v0), "d"(v1), "d"(v2)
+        : "memory");
+  }
+
   __device__ __forceinline__ void report_error(int* err, int gid)
   {
     atomicAdd(&err[0], 1);

@@ -45,7 +45,7 @@ namespace fc
   // (the node field is XOR-swizzled with the k-step so that the 8 Gauss-point lanes of phase 1 store conflict-free)
   __device__ __forceinline__ int frag_idx(int gp, int node) { return 32 * (gp >> 2) + 16 * (node >> 2) + 4 * (gp & 3) + ((node & 3) ^ (2 * (gp >> 2))); }
 
-  template <bool WANT_K>
+  template <bool WANT_K, bool HAS_DBC>
   __global__ void __launch_bounds__(Hex8MmaCfg::threads) k_hex8_neohooke_mma(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
   {
     using Cfg = Hex8MmaCfg;
@@ -84,7 +84,7 @@ namespace fc
         rb = __ldg(A.node_rowbase + node);
         rl = __ldg(A.node_rowlen + node);
         sl = __ldg(reinterpret_cast<const unsigned long long*>(A.slots + (size_t)e * 64) + t);
-        if (A.dbc)  // Dirichlet flags of the 3 DOF rows ride in the top bits of the row length
+        if (HAS_DBC)  // Dirichlet flags of the 3 DOF rows ride in the top bits of the row length
           for (int i = 0; i < 3; ++i) rl |= (A.dbc[3 * node + i] ? 1 : 0) << (28 + i);
       }
       s_rowbase[wel + el][t] = rb;
@@ -186,13 +186,15 @@ namespace fc
         fg[c][0] = G[c * 64 + fo0];
         fg[c][1] = G[c * 64 + fo1];
       }
-      double s0 = 0.0, s1 = 0.0;
+      // three independent accumulator pairs (short dependency chains), summed afterwards
+      double sa[3][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
 #pragma unroll
       for (int i = 0; i < 3; ++i)
       {
-        dmma884(s0, s1, fg[3 + i][0], fg[3 + i][0]);
-        dmma884(s0, s1, fg[3 + i][1], fg[3 + i][1]);
+        dmma884(sa[i][0], sa[i][1], fg[3 + i][0], fg[3 + i][0]);
+        dmma884(sa[i][0], sa[i][1], fg[3 + i][1], fg[3 + i][1]);
       }
+      const double s0 = sa[0][0] + sa[1][0] + sa[2][0], s1 = sa[0][1] + sa[1][1] + sa[2][1];
       // internal force: lanes of the same row node a reduce over their column pairs / Gauss points
       {
         const double* xk = G + Cfg::oX;
@@ -287,9 +289,16 @@ namespace fc
           }
 #pragma unroll
           for (int r = 0; r < 4; ++r)
+          {
+            if (HAS_DBC)
+            {
 #pragma unroll
-            for (int i = 0; i < 3; ++i)
-              red_add_if(ptr[r] != nullptr && !((rl[r] >> (28 + i)) & 1), ptr[r] + (long long)i * (rl[r] & 0x0FFFFFFF), v[3 * r + i]);
+              for (int i = 0; i < 3; ++i)
+                red_add_if(ptr[r] != nullptr && !((rl[r] >> (28 + i)) & 1), ptr[r] + (long long)i * (rl[r] & 0x0FFFFFFF), v[3 * r + i]);
+            }
+            else
+              red_add3_if(ptr[r] != nullptr, ptr[r], 8ll * rl[r], v[3 * r], v[3 * r + 1], v[3 * r + 2]);
+          }
         }
       }
     }

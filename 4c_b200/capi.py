@@ -16,7 +16,7 @@ FC_HEX8, FC_HEX27, FC_TET10 = 0, 1, 2
 FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
-FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA = 1, 2, 4
+FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_NO_SLAB_PIPELINE = 1, 2, 4, 8
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
 NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10}
@@ -24,7 +24,7 @@ NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10}
 EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
     "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_graph", "fc_solid_build_graph",
-    "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
+    "fc_solid_graph_sizes", "fc_solid_set_slab_count", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
     "fc_solid_error_state", "fc_solid_zero", "fc_solid_evaluate_elements",
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack",
     "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
@@ -187,6 +187,9 @@ class Solid:
         self._chk(lib().fc_solid_graph_sizes(self.h, C.byref(a), C.byref(b), C.byref(n)))
         self.n_row_dof, self.n_col_dof, self.nnz = a.value, b.value, n.value
         return a.value, b.value, n.value
+
+    def set_slab_count(self, n):
+        self._chk(lib().fc_solid_set_slab_count(self.h, C.c_int(n)))
 
     def get_graph(self):
         rowptr = np.zeros(self.n_row_dof + 1, np.int64)

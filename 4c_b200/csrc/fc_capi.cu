@@ -43,6 +43,9 @@ extern "C"
       return FC_ERR_CUDA;
     }
     for (auto& e : ctx->ev) cudaEventCreate(&e);
+    cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
+    for (auto& e : ctx->ev_slab) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming);
     *out = ctx;
     return FC_OK;
   }
@@ -69,6 +72,10 @@ extern "C"
     if (ctx->h_err_pinned) cudaFreeHost(ctx->h_err_pinned);
     for (auto& e : ctx->ev)
       if (e) cudaEventDestroy(e);
+    for (auto& e : ctx->ev_slab)
+      if (e) cudaEventDestroy(e);
+    if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     delete ctx;
   }
 

@@ -43,7 +43,7 @@ namespace
       auto kern = A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true> : fc::k_hex8_neohooke_mma<WANT_K, false>;
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
       if (e != cudaSuccess) return e;
-      kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+      kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
     }
     ctx->launches++;
     return cudaGetLastError();
@@ -148,12 +148,16 @@ extern "C"
       d_K = ctx->d_stage_K;
     }
 
+    // slab pipeline: only the tensor-core closed-form kernel takes an element range
+    const bool mma_path = ctx->celltype == FC_HEX8 && ctx->formulation == FC_FORM_DISPLACEMENT && ctx->mat.kind == fc::MAT_NEOHOOKE &&
+                          !(flags & (FC_EVAL_FORCE_GENERIC | FC_EVAL_CLOSED_FORM_FMA));
+    const bool pipelined = (flags & FC_EVAL_ZERO_FIRST) && want_K && mma_path && ctx->n_slabs > 1 && !(flags & FC_EVAL_NO_SLAB_PIPELINE);
     FC_CUDA(cudaEventRecord(ctx->ev[0], s));
     if (flags & FC_EVAL_ZERO_FIRST)
     {
       if (d_f) FC_CUDA(cudaMemsetAsync(d_f, 0, sizeof(double) * (size_t)ctx->n_row_dof, s));
-      if (d_K) FC_CUDA(cudaMemsetAsync(d_K, 0, sizeof(double) * (size_t)ctx->nnz, s));
-      ctx->launches += (d_f ? 1 : 0) + (d_K ? 1 : 0);
+      if (d_K && !pipelined) FC_CUDA(cudaMemsetAsync(d_K, 0, sizeof(double) * (size_t)ctx->nnz, s));
+      ctx->launches += (d_f ? 1 : 0) + (d_K && !pipelined ? 1 : 0);
     }
     FC_CUDA(cudaEventRecord(ctx->ev[1], s));
     if (int rc = reset_err(ctx)) return rc;
@@ -161,7 +165,35 @@ extern "C"
     A.u = d_u;
     A.f = d_f;
     A.K = d_K;
-    if (ctx->n_ele > 0) FC_CUDA(want_K ? dispatch<true>(ctx, A, flags) : dispatch<false>(ctx, A, flags));
+    if (pipelined)
+    {
+      // zero the rows a slab touches first on stream2 while the previous slab computes on the main stream
+      FC_CUDA(cudaEventRecord(ctx->ev_start, s));
+      FC_CUDA(cudaStreamWaitEvent(ctx->stream2, ctx->ev_start, 0));
+      int64_t off = 0;
+      for (int k = 0; k < ctx->n_slabs; ++k)
+      {
+        const int64_t end = ctx->slab_off_end[k];
+        if (end > off)
+        {
+          FC_CUDA(cudaMemsetAsync(d_K + off, 0, sizeof(double) * (size_t)(end - off), ctx->stream2));
+          ctx->launches++;
+          off = end;
+        }
+        FC_CUDA(cudaEventRecord(ctx->ev_slab[k], ctx->stream2));
+      }
+      int e0 = 0;
+      for (int k = 0; k < ctx->n_slabs; ++k)
+      {
+        FC_CUDA(cudaStreamWaitEvent(s, ctx->ev_slab[k], 0));
+        A.ele_offset = e0;
+        A.n_ele = ctx->slab_ele_end[k];
+        if (A.n_ele > e0) FC_CUDA(dispatch<true>(ctx, A, flags));
+        e0 = A.n_ele;
+      }
+    }
+    else if (ctx->n_ele > 0)
+      FC_CUDA(want_K ? dispatch<true>(ctx, A, flags) : dispatch<false>(ctx, A, flags));
     FC_CUDA(cudaEventRecord(ctx->ev[2], s));
     ctx->ev_valid = true;
 

@@ -77,6 +77,27 @@ namespace
     }
   }
 
+  // slab plan: rows first touched by slab k end at the prefix maximum of the owned nodes its elements touch
+  void compute_slab_plan(fc_ctx* ctx, int S)
+  {
+    const int ne = ctx->n_ele, nen = ctx->nen, nrow = ctx->n_row_nodes;
+    if (S > fc_ctx::max_slabs) S = fc_ctx::max_slabs;
+    if (S < 1) S = 1;
+    ctx->n_slabs = S;
+    int maxnode = -1;
+    for (int k = 0; k < S; ++k)
+    {
+      const int e0 = (int)((int64_t)ne * k / S) / 16 * 16, e1 = k == S - 1 ? ne : (int)((int64_t)ne * (k + 1) / S) / 16 * 16;
+      for (size_t i = (size_t)e0 * nen; i < (size_t)e1 * nen; ++i)
+      {
+        const int n = ctx->h_conn[i];
+        if (n < nrow && n > maxnode) maxnode = n;
+      }
+      ctx->slab_ele_end[k] = e1;
+      ctx->slab_off_end[k] = k == S - 1 ? ctx->nnz : 9 * ctx->h_nodeptr[maxnode + 1];
+    }
+  }
+
   int finalize_graph(fc_ctx* ctx)
   {
     const int nrow = ctx->n_row_nodes, ncol = ctx->n_col_nodes;
@@ -128,6 +149,7 @@ namespace
     dev_free(ctx->d_dbc);
     ctx->have_dbc = false;
     if (bad > 0) return fail(ctx, FC_ERR_GRAPH, "elements couple DOFs that are missing from the CSR graph");
+    compute_slab_plan(ctx, ctx->n_ele >= 8 * 65536 ? 8 : (ctx->n_ele >= 2 * 65536 ? ctx->n_ele / 65536 : 1));
     ctx->have_graph = true;
     return FC_OK;
   }
@@ -168,6 +190,13 @@ extern "C"
       ctx->h_nodeptr[n + 1] = (int64_t)ctx->h_nodeadj.size();
     }
     return finalize_graph(ctx);
+  }
+
+  int fc_solid_set_slab_count(fc_ctx* ctx, int n_slabs)
+  {
+    if (!ctx || !ctx->have_graph) return FC_ERR_INVALID;
+    compute_slab_plan(ctx, n_slabs);
+    return FC_OK;
   }
 
   int fc_solid_graph_sizes(const fc_ctx* ctx, int* n_row_dof, int* n_col_dof, int64_t* nnz)

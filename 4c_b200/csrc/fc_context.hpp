@@ -44,6 +44,17 @@ struct fc_ctx
   unsigned char* d_dbc = nullptr;     // [n_row_dof] 1 = row skipped by the matrix scatter
   bool have_dbc = false;
 
+  // slab pipeline for FC_EVAL_ZERO_FIRST: slab k = elements [slab_ele_end[k-1], slab_ele_end[k]); before it runs,
+  // the CSR range [slab_off_end[k-1], slab_off_end[k]) (rows first touched by this slab) is zeroed on a second
+  // stream while slab k-1 computes
+  static constexpr int max_slabs = 16;
+  int n_slabs = 0;
+  int slab_ele_end[max_slabs] = {};
+  int64_t slab_off_end[max_slabs] = {};
+  cudaStream_t stream2 = nullptr;
+  cudaEvent_t ev_slab[max_slabs] = {};
+  cudaEvent_t ev_start = nullptr;
+
   // halo send plan
   int n_send = 0;
   int* d_send_lids = nullptr;

@@ -14,7 +14,8 @@ namespace fc
     const double* X;       // [n_col_nodes][3]
     const int* conn;       // [n_ele][nen]
     const int* ele_gid;    // [n_ele]
-    int n_ele;
+    int n_ele;             // end of the element range of this launch
+    int ele_offset;        // first element of this launch (slab-pipelined evaluation), 0 otherwise
     int n_row_nodes;       // column nodes [0, n_row_nodes) are owned (their DOF rows are assembled)
     // tables
     const double* dNtab;   // [ngp + nen + 1][nen][3]

@@ -58,7 +58,7 @@ namespace fc
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int el = lane >> 3, t = lane & 7;   // phase 0/1 role
     const int wel = warp * Cfg::epw;          // first element slot of this warp inside the CTA
-    const int e = blockIdx.x * Cfg::epb + wel + el;
+    const int e = A.ele_offset + blockIdx.x * Cfg::epb + wel + el;
     const bool active = e < A.n_ele;
     double* E = smem + (size_t)(wel + el) * Cfg::ele_doubles;
 
@@ -176,7 +176,7 @@ namespace fc
     for (int k = 0; k < Cfg::epw; ++k)
     {
       if (!((actmask >> (8 * k)) & 1u) || ((badmask >> (8 * k)) & 0xFFu)) continue;  // warp-uniform
-      const int ek = blockIdx.x * Cfg::epb + wel + k;
+      const int ek = A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
       const double* G = smem + (size_t)(wel + k) * Cfg::ele_doubles;
       const int fo0 = frag_idx(q, a), fo1 = frag_idx(q + 4, a);
       double fg[6][2];

@@ -79,8 +79,10 @@ extern "C"
                                Vector::put_scalar(0), 4C_structure_new_model_evaluator_structure.cpp:136-159) */
     FC_EVAL_FORCE_GENERIC = 2, /* use the generic B-operator kernel even where a specialised
                                   closed-form kernel exists (testing / comparison) */
-    FC_EVAL_CLOSED_FORM_FMA = 4 /* hex8 Neo-Hooke closed form on the FP64 FMA pipe instead of the
-                                   FP64 tensor cores (comparison) */
+    FC_EVAL_CLOSED_FORM_FMA = 4, /* hex8 Neo-Hooke closed form on the FP64 FMA pipe instead of the
+                                    FP64 tensor cores (comparison) */
+    FC_EVAL_NO_SLAB_PIPELINE = 8 /* with ZERO_FIRST: one memset + one launch instead of zeroing slab k+1 on a
+                                    second stream while slab k computes (comparison) */
   };
 
   /* ---- context ------------------------------------------------------------------------------ */
@@ -115,6 +117,9 @@ extern "C"
   int fc_solid_set_graph(fc_ctx* ctx, int n_row_dof, const int64_t* rowptr, const int* colind, int n_col_dof);
   int fc_solid_build_graph(fc_ctx* ctx);
   int fc_solid_graph_sizes(const fc_ctx* ctx, int* n_row_dof, int* n_col_dof, int64_t* nnz);
+  /* number of element slabs of the zero-fill pipeline (FC_EVAL_ZERO_FIRST); default: 8 above 524288 elements,
+   * 1 below 131072.  Any count is correct for any mesh (slab k zeroes the rows not touched by slabs < k). */
+  int fc_solid_set_slab_count(fc_ctx* ctx, int n_slabs);
   /* copy the graph out (host buffers: rowptr [n_row_dof+1], colind [nnz]) */
   int fc_solid_get_graph(const fc_ctx* ctx, int64_t* rowptr, int* colind);
 

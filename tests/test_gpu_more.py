@@ -153,3 +153,27 @@ def test_c2_full_size_invariants(fc):
         assert (K2 - K).abs().max() <= 1e-12 * kmax
         assert (f2 - f).abs().max() <= 1e-12 * kmax * 0.01
     s.close()
+
+
+@pytest.mark.parametrize("n_slabs", [2, 5, 16])
+def test_slab_pipelined_zero_fill(fc, oracle, n_slabs):
+    """FC_EVAL_ZERO_FIRST with the zero-fill pipelined slab by slab on a second stream: same result as one
+    memset + one launch, for a shuffled element order too (slab row ranges are prefix maxima)."""
+    n = (9, 8, 7)
+    g = fc.Grid(HEX8, n)
+    rng = np.random.default_rng(0)
+    for perm in (np.arange(g.n_col_eles), rng.permutation(g.n_col_eles)):
+        s = fc.Solid(0)
+        s.set_mesh(fc.FC_HEX8, DISP, g.X, g.node_gid, g.node_owner, g.conn[perm], g.ele_gid[perm])
+        s.set_material(NH, 10.0, 0.25)
+        n_row, n_col, nnz = s.build_graph()
+        u = field(g.X, 0).reshape(-1).copy()
+        K0, f0 = np.full(nnz, 3.0), np.full(n_row, 3.0)
+        s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f0, K0, flags=fc.FC_EVAL_ZERO_FIRST | fc.FC_EVAL_NO_SLAB_PIPELINE)
+        s.set_slab_count(n_slabs)
+        for _ in range(2):
+            K1, f1 = np.full(nnz, 5.0), np.full(n_row, 5.0)
+            assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f1, K1, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+            assert np.max(np.abs(K1 - K0)) <= 1e-13 * np.max(np.abs(K0))
+            assert np.max(np.abs(f1 - f0)) <= 1e-13 * np.max(np.abs(K0))
+        s.close()

@@ -25,7 +25,7 @@ EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
     "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_graph", "fc_solid_build_graph",
     "fc_solid_graph_sizes", "fc_solid_set_slab_count", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
-    "fc_solid_error_state", "fc_solid_zero", "fc_solid_evaluate_elements",
+    "fc_solid_error_state", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_elements",
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack",
     "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
@@ -220,6 +220,10 @@ class Solid:
 
     def zero(self, f_row=None, K_values=None):
         self._chk(lib().fc_solid_zero(self.h, _ptr(f_row), _ptr(K_values)))
+
+    def evaluate_mass(self, density, M_values, flags=FC_EVAL_ZERO_FIRST):
+        """consistent mass (struct_calc_nlnstiffmass) into M_values [nnz], layout of the stiffness graph"""
+        self._chk(lib().fc_solid_evaluate_mass(self.h, C.c_double(density), C.c_int(flags), _ptr(M_values)))
 
     def evaluate_elements(self, u_col, want_K=True, flags=0):
         nd = 3 * self.nen

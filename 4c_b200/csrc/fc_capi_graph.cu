@@ -149,7 +149,7 @@ namespace
     dev_free(ctx->d_dbc);
     ctx->have_dbc = false;
     if (bad > 0) return fail(ctx, FC_ERR_GRAPH, "elements couple DOFs that are missing from the CSR graph");
-    compute_slab_plan(ctx, ctx->n_ele >= 8 * 65536 ? 8 : (ctx->n_ele >= 2 * 65536 ? ctx->n_ele / 65536 : 1));
+    compute_slab_plan(ctx, 1);  // measured: overlapping the zero-fill with the kernel gains nothing, so one slab
     ctx->have_graph = true;
     return FC_OK;
   }

@@ -126,6 +126,41 @@ namespace fc
     }
   }
 
+  // N[a] (4C_fem_general_utils_fem_shapefunctions.hpp:53-72 hex8, :190-230 hex27, :244-259 tet10)
+  template <int CT>
+  FC_HD void shape_function(const double* xi, double* N)
+  {
+    const double r = xi[0], s = xi[1], t = xi[2];
+    if constexpr (CT == HEX8)
+    {
+      const double rf[2] = {1.0 - r, 1.0 + r}, sf[2] = {1.0 - s, 1.0 + s}, tf[2] = {1.0 - t, 1.0 + t};
+      for (int a = 0; a < 8; ++a)
+        N[a] = 0.125 * rf[hex_node_pos(a, 0) > 0] * sf[hex_node_pos(a, 1) > 0] * tf[hex_node_pos(a, 2) > 0];
+    }
+    else if constexpr (CT == HEX27)
+    {
+      const double R[3] = {0.5 * r * (r - 1.0), 1.0 - r * r, 0.5 * r * (r + 1.0)};
+      const double S[3] = {0.5 * s * (s - 1.0), 1.0 - s * s, 0.5 * s * (s + 1.0)};
+      const double T[3] = {0.5 * t * (t - 1.0), 1.0 - t * t, 0.5 * t * (t + 1.0)};
+      for (int a = 0; a < 27; ++a) N[a] = R[hex_node_pos(a, 0) + 1] * S[hex_node_pos(a, 1) + 1] * T[hex_node_pos(a, 2) + 1];
+    }
+    else
+    {
+      const double u = 1.0 - r - s - t;
+      const double v[10] = {u * (2.0 * u - 1.0), r * (2.0 * r - 1.0), s * (2.0 * s - 1.0), t * (2.0 * t - 1.0), 4.0 * r * u,
+          4.0 * r * s, 4.0 * s * u, 4.0 * t * u, 4.0 * r * t, 4.0 * s * t};
+      for (int a = 0; a < 10; ++a) N[a] = v[a];
+    }
+  }
+
+  // Gauss rule of the mass integral (get_gauss_rule_mass_matrix, 4C_solid_3D_ele_calc_lib_integration.hpp:40-44):
+  // the stiffness rule for the hexes, tet_11point for tet10 (4C_fem_general_utils_integration.cpp:447-495)
+  template <int CT>
+  struct MassRule
+  {
+    static constexpr int ngp = CT == TET10 ? 11 : Cell<CT>::ngp;
+  };
+
   // Gauss rule of the stiffness/force integral: point g of cell type CT
   template <int CT>
   FC_HD void gauss_point(int g, double* xi, double* w)
@@ -157,6 +192,22 @@ namespace fc
       xi[0] = xi[1] = xi[2] = pb;
       if (g > 0) xi[g - 1] = pa;
       *w = 1.0 / 24.0;
+    }
+  }
+
+  template <int CT>
+  FC_HD void mass_gauss_point(int g, double* xi, double* w)
+  {
+    if constexpr (CT != TET10)
+      gauss_point<CT>(g, xi, w);
+    else
+    {
+      const double a = 0.2500000000000000, b = 0.7857142857142857, c = 0.0714285714285714;
+      const double d = 0.1005964238332008, e = 0.3994035761667992;
+      const double p[11][3] = {{a, a, a}, {b, c, c}, {c, c, c}, {c, c, b}, {c, b, c}, {d, e, e}, {e, d, e}, {e, e, d},
+          {e, d, d}, {d, e, d}, {d, d, e}};
+      for (int k = 0; k < 3; ++k) xi[k] = p[g][k];
+      *w = (g == 0 ? -0.0789333333333333 : (g < 5 ? 0.0457333333333333 : 0.1493333333333333)) * (1.0 / 6.0);
     }
   }
 

@@ -117,8 +117,9 @@ extern "C"
   int fc_solid_set_graph(fc_ctx* ctx, int n_row_dof, const int64_t* rowptr, const int* colind, int n_col_dof);
   int fc_solid_build_graph(fc_ctx* ctx);
   int fc_solid_graph_sizes(const fc_ctx* ctx, int* n_row_dof, int* n_col_dof, int64_t* nnz);
-  /* number of element slabs of the zero-fill pipeline (FC_EVAL_ZERO_FIRST); default: 8 above 524288 elements,
-   * 1 below 131072.  Any count is correct for any mesh (slab k zeroes the rows not touched by slabs < k). */
+  /* number of element slabs of the zero-fill pipeline (FC_EVAL_ZERO_FIRST, tensor-core hex8 kernel); default 1 = one
+   * memset + one launch (on B200 the overlap gained nothing: the kernel slows by what the concurrent memset costs).
+   * Any count <= 16 is correct for any mesh (slab k zeroes the rows not touched by slabs < k). */
   int fc_solid_set_slab_count(fc_ctx* ctx, int n_slabs);
   /* copy the graph out (host buffers: rowptr [n_row_dof+1], colind [nnz]) */
   int fc_solid_get_graph(const fc_ctx* ctx, int64_t* rowptr, int* colind);
@@ -142,6 +143,12 @@ extern "C"
 
   /* SparseMatrix::zero / Vector::put_scalar(0) on device buffers (4C_linalg_sparsematrix.cpp:353-378) */
   int fc_solid_zero(fc_ctx* ctx, double* f_row_dev, double* K_values_dev);
+
+  /* Consistent mass matrix (struct_calc_nlnstiffmass branch, 4C_solid_3D_ele_evaluate.cpp:107-119; add_mass_matrix,
+   * 4C_solid_3D_ele_calc_lib.hpp:940-958; tet10 integrates it with tet_11point, 4C_solid_3D_ele_calc.cpp:228-240)
+   * added into M_values [nnz] (host|device) in the layout of the stiffness graph, owned rows only.  flags:
+   * FC_EVAL_ZERO_FIRST.  Constant for a mesh: call once, not per Newton iteration. */
+  int fc_solid_evaluate_mass(fc_ctx* ctx, double density, int flags, double* M_values);
 
   /* Element-local evaluation without scatter (Solid::evaluate seam, 4C_solid_3D_ele.hpp:120-124):
    * fe [n_col_ele][3*nen], Ke [n_col_ele][3*nen][3*nen] column-major per element, in the caller's

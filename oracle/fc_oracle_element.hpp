@@ -135,6 +135,22 @@ namespace fc_oracle
     }
   }
 
+  // add_mass_matrix                                                       calc_lib.hpp:940-958
+  template <int NEN>
+  inline void add_mass_matrix(const double* N, double integration_factor, double density, double* Me)
+  {
+    constexpr int ND = 3 * NEN;
+    for (int inod = 0; inod < NEN; ++inod)
+    {
+      const double ifactor = N[inod] * integration_factor * density;
+      for (int jnod = 0; jnod < NEN; ++jnod)
+      {
+        const double massfactor = N[jnod] * ifactor;
+        for (int d = 0; d < 3; ++d) Me[(3 * inod + d) + ND * (3 * jnod + d)] += massfactor;
+      }
+    }
+  }
+
   // One element.  X,u: node-major [3*a+d] == 3 x NEN col-major.  fe[ND], Ke[ND*ND] col-major,
   // Me optional (consistent mass, density rho).  Outputs are ADDED to (caller zeroes them, like
   // AssembleStrategy::clear_element_storage, 4C_fem_general_assemblestrategy.cpp:74-111).
@@ -173,6 +189,7 @@ namespace fc_oracle
 
     double gxi[NGP][3], gw[NGP];
     gauss_rule(ct, gxi, gw);
+    double element_mass = 0.0, element_volume = 0.0;
 
     std::vector<double> Bv(6 * ND), cbv(6 * ND);
     double* B = Bv.data();
@@ -254,16 +271,28 @@ namespace fc_oracle
       }
       if (Me)
       {
-        // add_mass_matrix                                               calc_lib.hpp:940-958
-        for (int inod = 0; inod < NEN; ++inod)
+        if (ct != TET10)
+          add_mass_matrix<NEN>(N, integration_factor, rho, Me);  // same rule as the stiffness integral
+        else
         {
-          const double ifactor = N[inod] * integration_factor * rho;
-          for (int jnod = 0; jnod < NEN; ++jnod)
-          {
-            const double massfactor = N[jnod] * ifactor;
-            for (int d = 0; d < 3; ++d) Me[(3 * inod + d) + ND * (3 * jnod + d)] += massfactor;
-          }
+          element_mass += rho * integration_factor;  // solid_3D_ele_calc.cpp:201-205
+          element_volume += integration_factor;
         }
+      }
+    }
+    if (Me && ct == TET10)
+    {
+      // mass rule differs from the stiffness rule: second loop with the mean density   solid_3D_ele_calc.cpp:228-240
+      double mxi[11][3], mw[11];
+      const int nm = gauss_rule_mass_tet10(mxi, mw);
+      for (int gp = 0; gp < nm; ++gp)
+      {
+        double N[NEN], dN[3 * NEN];
+        shape_function(ct, mxi[gp], N);
+        shape_function_deriv1(ct, mxi[gp], dN);
+        JacobianMapping<NEN> jm;
+        evaluate_jacobian_mapping<NEN>(dN, X, jm, &singular);
+        add_mass_matrix<NEN>(N, jm.det * mw[gp], element_mass / element_volume, Me);
       }
     }
     return singular ? ELE_ERR_SINGULAR : ELE_OK;

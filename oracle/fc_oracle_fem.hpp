@@ -186,6 +186,24 @@ namespace fc_oracle
     }
   }
 
+  // Gauss rule of the mass matrix where it differs from the stiffness rule: tet10 -> tet_11point
+  // (4C_solid_3D_ele_calc_lib_integration.hpp:40-44 + 4C_fem_general_element_integration_select.hpp:64-67;
+  //  table 4C_fem_general_utils_integration.cpp:447-495, Q16 = 1/6).  Returns the number of points.
+  inline int gauss_rule_mass_tet10(double (*xi)[3], double* w)
+  {
+    const double a = 0.2500000000000000, b = 0.7857142857142857, c = 0.0714285714285714;
+    const double d = 0.1005964238332008, e = 0.3994035761667992;
+    const double p[11][3] = {{a, a, a}, {b, c, c}, {c, c, c}, {c, c, b}, {c, b, c}, {d, e, e}, {e, d, e}, {e, e, d}, {e, d, d},
+        {d, e, d}, {d, d, e}};
+    const double Q16 = 1.0 / 6.0;
+    for (int g = 0; g < 11; ++g)
+    {
+      for (int k = 0; k < 3; ++k) xi[g][k] = p[g][k];
+      w[g] = (g == 0 ? -0.0789333333333333 : (g < 5 ? 0.0457333333333333 : 0.1493333333333333)) * Q16;
+    }
+    return 11;
+  }
+
   // centroid in parameter space (used by F-bar): hex -> origin, tet -> (1/4,1/4,1/4)
   inline void centroid_param(int ct, double* xi)
   {

@@ -1,0 +1,152 @@
+#!/usr/bin/env python
+"""Extracts the solve-level golden vectors of the reference into JSON fixtures.
+
+Run in the build container (the reference tree is not on the GPU box):
+    python tests/golden/make_golden.py [/root/reference]
+Each fixture holds the *input data* of one reference test (nodes, connectivity, material, surface
+conditions, time stepping) and its RESULT DESCRIPTION (node, quantity, value, tolerance).  No reference
+code is copied; tests/structure_driver.py replays the problem on the oracle and on the CUDA library.
+"""
+import json
+import os
+import re
+import sys
+
+import yaml
+
+REF = sys.argv[1] if len(sys.argv) > 1 else "/root/reference"
+INP = os.path.join(REF, "tests", "input_files")
+OUT = os.path.dirname(os.path.abspath(__file__))
+
+CASES = [
+    "solid_ele_hex8_Standard_eas_none_stressout.4C.yaml",
+    "solid_ele_hex8_Standard_eas_none_dynamic.dat",
+    "solid_ele_hex27_Standard_stressout.dat",
+    "solid_ele_hex27_Standard_dynamic.dat",
+    "solid_ele_tet10_Standard_stressout.dat",
+    "solid_ele_tet10_Standard_dynamic.dat",
+]
+
+
+def dat_sections(path):
+    sec, cur = {}, None
+    for line in open(path):
+        line = line.rstrip("\n")
+        m = re.match(r"^-{3,}(.*)$", line)
+        if m:
+            cur = m.group(1).strip()
+            sec[cur] = []
+        elif cur is not None and line.strip() and not line.startswith("//"):
+            sec[cur].append(line.strip())
+    return sec
+
+
+def keyvals(lines):
+    out = {}
+    for l in lines:
+        parts = l.split()
+        out[parts[0]] = " ".join(parts[1:])
+    return out
+
+
+def parse_condition_dat(line):
+    t = line.split()
+    e = int(t[t.index("E") + 1])
+    n = int(t[t.index("NUMDOF") + 1])
+    i = t.index("ONOFF")
+    onoff = [int(x) for x in t[i + 1:i + 1 + n]]
+    i = t.index("VAL")
+    val = [float(x) for x in t[i + 1:i + 1 + n]]
+    i = t.index("FUNCT")
+    funct = [int(x) if x.lstrip("-").isdigit() else 0 for x in t[i + 1:i + 1 + n]]
+    typ = t[t.index("TYPE") + 1] if "TYPE" in t else "Live"
+    return {"E": e, "onoff": onoff, "val": val, "funct": funct, "type": typ}
+
+
+def from_dat(path):
+    s = dat_sections(path)
+    dyn = keyvals(s["STRUCTURAL DYNAMIC"])
+    mats = {}
+    for l in s["MATERIALS"]:
+        t = l.split()
+        mats[int(t[1])] = t[2:]
+    functs = {int(k[5:]): v[0].split("SYMBOLIC_FUNCTION_OF_SPACE_TIME")[1].strip() for k, v in s.items() if k.startswith("FUNCT")}
+    results = []
+    for l in s["RESULT DESCRIPTION"]:
+        t = l.split()
+        results.append({"node": int(t[t.index("NODE") + 1]), "quantity": t[t.index("QUANTITY") + 1],
+                        "value": float(t[t.index("VALUE") + 1]), "tolerance": float(t[t.index("TOLERANCE") + 1])})
+    surf = {}
+    for l in s["DSURF-NODE TOPOLOGY"]:
+        t = l.split()
+        surf.setdefault(int(t[3]), []).append(int(t[1]))
+    nodes = {}
+    for l in s["NODE COORDS"]:
+        t = l.split()
+        nodes[int(t[1])] = [float(t[3]), float(t[4]), float(t[5])]
+    eles = []
+    for l in s["STRUCTURE ELEMENTS"]:
+        t = l.split()
+        i = t.index("MAT")
+        eles.append({"id": int(t[0]), "type": t[2], "nodes": [int(x) for x in t[3:i]], "mat": int(t[i + 1]),
+                     "opts": " ".join(t[i + 2:])})
+    return {"dynamic": dyn, "materials": mats, "functs": functs, "results": results, "dsurf": surf,
+            "dirich": [parse_condition_dat(l) for l in s.get("DESIGN SURF DIRICH CONDITIONS", [])],
+            "neumann": [parse_condition_dat(l) for l in s.get("DESIGN SURF NEUMANN CONDITIONS", [])],
+            "nodes": nodes, "elements": eles}
+
+
+def from_yaml(path):
+    y = yaml.safe_load(open(path))
+    dyn = {k: str(v) for k, v in y["STRUCTURAL DYNAMIC"].items()}
+    mats = {}
+    for m in y["MATERIALS"]:
+        mid = m["MAT"]
+        name = [k for k in m if k != "MAT"][0]
+        flat = [name]
+        for k, v in m[name].items():
+            flat += [k] + ([str(x) for x in v] if isinstance(v, list) else [str(v)])
+        mats[mid] = flat
+    functs = {int(k[5:]): v[0]["SYMBOLIC_FUNCTION_OF_SPACE_TIME"] for k, v in y.items() if k.startswith("FUNCT")}
+    results = [{"node": r["STRUCTURE"]["NODE"], "quantity": r["STRUCTURE"]["QUANTITY"], "value": float(r["STRUCTURE"]["VALUE"]),
+                "tolerance": float(r["STRUCTURE"]["TOLERANCE"])} for r in y["RESULT DESCRIPTION"]]
+    surf = {}
+    for l in y["DSURF-NODE TOPOLOGY"]:
+        t = l.split()
+        surf.setdefault(int(t[3]), []).append(int(t[1]))
+    nodes = {}
+    for l in y["NODE COORDS"]:
+        t = l.split()
+        nodes[int(t[1])] = [float(t[3]), float(t[4]), float(t[5])]
+    eles = []
+    for l in y["STRUCTURE ELEMENTS"]:
+        t = l.split()
+        i = t.index("MAT")
+        eles.append({"id": int(t[0]), "type": t[2], "nodes": [int(x) for x in t[3:i]], "mat": int(t[i + 1]),
+                     "opts": " ".join(t[i + 2:])})
+
+    def cond(c):
+        return {"E": c["E"], "onoff": c["ONOFF"], "val": [float(v) for v in c["VAL"]],
+                "funct": [int(f) if f else 0 for f in c["FUNCT"]], "type": c.get("TYPE", "Live")}
+    return {"dynamic": dyn, "materials": mats, "functs": functs, "results": results, "dsurf": surf,
+            "dirich": [cond(c) for c in y.get("DESIGN SURF DIRICH CONDITIONS", [])],
+            "neumann": [cond(c) for c in y.get("DESIGN SURF NEUMANN CONDITIONS", [])],
+            "nodes": nodes, "elements": eles}
+
+
+def main():
+    for name in CASES:
+        path = os.path.join(INP, name)
+        d = from_yaml(path) if name.endswith(".yaml") else from_dat(path)
+        d["source"] = "tests/input_files/" + name
+        # keep only what the in-scope path can replay: ElastHyper + one CoupNeoHooke summand
+        m1 = d["materials"][1]
+        assert m1[0] == "MAT_ElastHyper" and m1[m1.index("NUMMAT") + 1] == "1", name
+        out = os.path.join(OUT, re.sub(r"\.(dat|4C\.yaml)$", "", name) + ".json")
+        with open(out, "w") as f:
+            json.dump(d, f, indent=0, sort_keys=True)
+        print(out, len(d["nodes"]), "nodes", len(d["elements"]), "elements", len(d["results"]), "results")
+
+
+if __name__ == "__main__":
+    main()

@@ -85,6 +85,12 @@ def element_evaluate(ct, form, kind, young, nue, X, u, want_K=True, want_M=False
     return err, fe, Ke, Me
 
 
+def node_param_coords(ct):
+    xi = np.zeros((NEN[ct], 3))
+    lib.oracle_node_param_coords(C.c_int(ct), _p(xi))
+    return xi
+
+
 def element_evaluate_batch(ct, form, kind, young, nue, X, u, want_K=True):
     """X, u: (n, nen, 3).  Returns nbad, fe (n, nd), Ke (n, nd, nd) indexed [e, r, c]."""
     n = X.shape[0]

@@ -1,0 +1,252 @@
+"""Mock of the caller of the path for the reference's solve-level golden vectors (tests/golden/*.json):
+what src/structure_new does around Discretization::evaluate, restated in numpy for 1-rank problems.
+
+  * surface Neumann loads, TYPE Live          src/solid_3D_ele/4C_solid_3D_ele_surface_evaluate.cpp:225-330
+    (rules quad_4point / quad_9point / tri_6point with the reference's truncated constants,
+     4C_fem_general_utils_integration.cpp:6151-6183, 6185-6231, 6374-6396; rule choice 4C_solid_3D_ele_surface.cpp:58-77)
+  * statics: f_int(d_{n+1}) = f_ext(t_{n+1})  src/structure_new/src/implicit/4C_structure_new_impl_statics.cpp
+  * GenAlpha, TR-like mid-averaging           .../implicit/4C_structure_new_impl_genalpha.cpp:255-296, 380-410, 468-485
+    parameters from RHO_INF (default 1)       .../utils/4C_structure_new_utils.cpp:372-410
+    consistent initial acceleration           .../4C_structure_new_integrator.cpp:175-300
+    force assembly                            .../model_evaluator/4C_structure_new_model_evaluator_structure.cpp:244-262, 1486-1520
+  * full Newton, Dirichlet rows replaced by identity (dense solve; the problems have <= 207 DOFs)
+
+The element work (f_int, K, M) comes from a backend: the CPU oracle or the CUDA library.  Test infrastructure.
+"""
+import json
+import os
+
+import numpy as np
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CT = {"HEX8": 0, "HEX27": 1, "TET10": 2}
+
+
+def load(name):
+    with open(os.path.join(GOLDEN, name + ".json")) as f:
+        return json.load(f)
+
+
+class Problem:
+    def __init__(self, fx, node_param_coords):
+        """node_param_coords(ct) -> (nen, 3) parameter coordinates of the element nodes (reference numbering)"""
+        self.fx = fx
+        ids = sorted(int(k) for k in fx["nodes"])
+        self.ids = ids
+        self.index = {nid: i for i, nid in enumerate(ids)}
+        self.X = np.array([fx["nodes"][str(i)] for i in ids], float)
+        self.node_gid = np.array([i - 1 for i in ids], np.int32)
+        types = {e["type"] for e in fx["elements"]}
+        assert len(types) == 1
+        self.ct = CT[types.pop()]
+        self.conn = np.array([[self.index[n] for n in e["nodes"]] for e in fx["elements"]], np.int32)
+        self.ele_gid = np.array([e["id"] - 1 for e in fx["elements"]], np.int32)
+        m1, m10 = fx["materials"]["1"], fx["materials"]["10"]
+        assert m1[0] == "MAT_ElastHyper" and m10[0] == "ELAST_CoupNeoHooke"
+        self.dens = float(m1[m1.index("DENS") + 1])
+        self.young = float(m10[m10.index("YOUNG") + 1])
+        self.nue = float(m10[m10.index("NUE") + 1])
+        self.n_dof = 3 * len(ids)
+        dyn = fx["dynamic"]
+        self.dt, self.numstep = float(dyn["TIMESTEP"]), int(dyn["NUMSTEP"])
+        self.dynamic = dyn["DYNAMICTYPE"]
+        # Dirichlet: all values are zero in these inputs
+        fixed = []
+        for c in fx["dirich"]:
+            assert not any(c["val"])
+            for n in fx["dsurf"][str(c["E"])]:
+                fixed += [3 * self.index[n] + d for d in range(3) if c["onoff"][d]]
+        self.fixed = np.array(sorted(set(fixed)), np.int64)
+        self.xi_nodes = np.asarray(node_param_coords(self.ct), float)
+        self.faces = []
+        for c in fx["neumann"]:
+            assert c["type"] == "Live" and not any(c["onoff"][3:])
+            sset = {self.index[n] for n in fx["dsurf"][str(c["E"])]}
+            for en in self.conn:
+                for loc, rs in self._element_faces():
+                    if all(int(en[a]) in sset for a in loc):
+                        self.faces.append((c, en[loc], rs))
+        assert self.faces or not fx["neumann"]
+
+    # faces of the parent cell as (local node ids, in-face parameter coordinates of those nodes)
+    def _element_faces(self):
+        xi = self.xi_nodes
+        out = []
+        if self.ct in (0, 1):
+            for ax in range(3):
+                for side in (-1.0, 1.0):
+                    loc = [a for a in range(len(xi)) if xi[a, ax] == side]
+                    other = [d for d in range(3) if d != ax]
+                    out.append((loc, xi[loc][:, other]))
+        else:
+            corners = xi[:4]
+            for skip in range(4):
+                tri = [c for c in range(4) if c != skip]
+                # barycentric coordinates of every node w.r.t. the three corners of this face
+                loc, lam = [], []
+                for a in range(10):
+                    A = np.vstack([corners[tri].T, np.ones(3)])
+                    l, res, *_ = np.linalg.lstsq(A, np.append(xi[a], 1.0), rcond=None)
+                    if np.allclose(A @ l, np.append(xi[a], 1.0), atol=1e-12) and np.all(l > -1e-12):
+                        loc.append(a)
+                        lam.append(l)
+                assert len(loc) == 6
+                out.append((loc, np.array(lam)))
+        return out
+
+    def _surface_shape(self, rs_nodes, pt):
+        """shape functions + derivatives w.r.t. the two surface parameters at pt, for the nodes of a face"""
+        if self.ct in (0, 1):
+            def lag(a, x):
+                if self.ct == 0:
+                    return 0.5 * (1 + a * x), 0.5 * a
+                if a == 0:
+                    return 1 - x * x, -2 * x
+                return 0.5 * x * (x + a), x + 0.5 * a
+            N, dr, ds = [], [], []
+            for ra, sa in rs_nodes:
+                Lr, dLr = lag(ra, pt[0])
+                Ls, dLs = lag(sa, pt[1])
+                N.append(Lr * Ls), dr.append(dLr * Ls), ds.append(Lr * dLs)
+            return np.array(N), np.array(dr), np.array(ds)
+        # tri6: rs_nodes holds barycentric coordinates (l0,l1,l2) of the nodes; pt = (r,s), l = (1-r-s, r, s)
+        l = np.array([1 - pt[0] - pt[1], pt[0], pt[1]])
+        dl = np.array([[-1.0, -1.0], [1.0, 0.0], [0.0, 1.0]])
+        N, dr, ds = [], [], []
+        for lam in rs_nodes:
+            nz = [i for i in range(3) if lam[i] > 1e-9]
+            if len(nz) == 1:
+                i = nz[0]
+                N.append(l[i] * (2 * l[i] - 1))
+                d = (4 * l[i] - 1) * dl[i]
+            else:
+                i, j = nz
+                N.append(4 * l[i] * l[j])
+                d = 4 * (l[i] * dl[j] + l[j] * dl[i])
+            dr.append(d[0]), ds.append(d[1])
+        return np.array(N), np.array(dr), np.array(ds)
+
+    def _surface_rule(self):
+        if self.ct == 0:
+            g = 0.5773502691896
+            return [((-g, -g), 1.0), ((g, -g), 1.0), ((g, g), 1.0), ((-g, g), 1.0)]
+        if self.ct == 1:
+            g, w1, w2 = 0.7745966692415, 0.5555555555556, 0.8888888888889
+            pts = [(-g, -g), (g, -g), (g, g), (-g, g), (0.0, -g), (g, 0.0), (0.0, g), (-g, 0.0), (0.0, 0.0)]
+            return [(p, (w2 if p[0] == 0 else w1) * (w2 if p[1] == 0 else w1)) for p in pts]
+        a, b, c, d = 0.0915762135098, 0.8168475729805, 0.4459484909160, 0.1081030181681
+        wa, wc = 0.0549758718277, 0.1116907948390
+        return [((a, a), wa), ((b, a), wa), ((a, b), wa), ((c, d), wc), ((c, c), wc), ((d, c), wc)]
+
+    def funct(self, fid, x, t):
+        if fid <= 0:
+            return 1.0
+        expr = self.fx["functs"][str(fid)]
+        return float(eval(expr, {"__builtins__": {}}, {"x": x[0], "y": x[1], "z": x[2], "t": t}))
+
+    def f_ext(self, t):
+        f = np.zeros((len(self.ids), 3))
+        for c, nodes, rs in self.faces:
+            P = self.X[nodes]
+            for pt, w in self._surface_rule():
+                N, dr, ds = self._surface_shape(rs, pt)
+                g1, g2 = dr @ P, ds @ P
+                m11, m22, m12 = g1 @ g1, g2 @ g2, g1 @ g2
+                detA = np.sqrt(m11 * m22 - m12 * m12)
+                xgp = N @ P
+                for dof in range(3):
+                    if c["onoff"][dof]:
+                        fac = w * detA * c["val"][dof] * self.funct(c["funct"][dof], xgp, t)
+                        f[nodes, dof] += N * fac
+        return f.reshape(-1)
+
+    def result_error(self, d):
+        """max |d - VALUE| over the displacement results, and the number compared"""
+        err, n = 0.0, 0
+        comp = {"dispx": 0, "dispy": 1, "dispz": 2}
+        for r in self.fx["results"]:
+            if r["quantity"] in comp:
+                v = d[3 * self.index[r["node"]] + comp[r["quantity"]]]
+                err = max(err, abs(v - r["value"]))
+                n += 1
+        return err, n
+
+
+def _solve(A, rhs, fixed):
+    A = A.copy()
+    rhs = rhs.copy()
+    A[fixed, :] = 0.0
+    A[fixed, fixed] = 1.0
+    rhs[fixed] = 0.0
+    return np.linalg.solve(A, rhs)
+
+
+def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30):
+    """assemble(d) -> (f_int [n], K dense [n, n]); mass() -> M dense.  Returns d at MAXTIME and the residual
+    norm history of every step (list of lists)."""
+    p = problem
+    n, fixed, dt = p.n_dof, p.fixed, p.dt
+    d = np.zeros(n)
+    history = []
+    if p.dynamic == "Statics":
+        for step in range(1, p.numstep + 1):
+            fext = p.f_ext(step * dt)
+            norms = []
+            for _ in range(maxiter):
+                fint, K = assemble(d)
+                r = fint - fext
+                r[fixed] = 0.0
+                norms.append(float(np.linalg.norm(r)))
+                inc = _solve(K, -r, fixed)
+                d = d + inc
+                if norms[-1] < 1e-10 and np.linalg.norm(inc) < newton_tol:
+                    break
+            history.append(norms)
+        return d, history
+
+    assert p.dynamic == "GenAlpha"
+    rho_inf = 1.0
+    am = (2.0 * rho_inf - 1.0) / (rho_inf + 1.0)
+    af = rho_inf / (rho_inf + 1.0)
+    beta = 0.25 * (1.0 - am + af) ** 2
+    gamma = 0.5 - am + af
+    M = mass()
+    v, t = np.zeros(n), 0.0
+    fint_n, _ = assemble(d)
+    fext_n = p.f_ext(t)
+    a = _solve(M, -(fint_n - fext_n), fixed)  # consistent initial acceleration, zero on Dirichlet DOFs
+    for step in range(1, p.numstep + 1):
+        t_np = step * dt
+        fext_np = p.f_ext(t_np)
+        fstruct_old = af * (fint_n - fext_n)
+        finert_n = M @ a
+        cv = (beta - gamma) / beta * v + (2.0 * beta - gamma) * dt / (2.0 * beta) * a - gamma / (beta * dt) * d
+        ca = (2.0 * beta - 1.0) / (2.0 * beta) * a - 1.0 / (beta * dt) * v - 1.0 / (beta * dt * dt) * d
+        d_np = d.copy()  # PREDICT ConstDis
+        norms = []
+        for _ in range(maxiter):
+            a_np = ca + d_np / (beta * dt * dt)
+            fint, K = assemble(d_np)
+            r = (1.0 - af) * (fint - fext_np) + fstruct_old + (1.0 - am) * (M @ a_np) + am * finert_n
+            r[fixed] = 0.0
+            norms.append(float(np.linalg.norm(r)))
+            J = (1.0 - af) * K + (1.0 - am) / (beta * dt * dt) * M
+            inc = _solve(J, -r, fixed)
+            d_np = d_np + inc
+            if norms[-1] < 1e-10 and np.linalg.norm(inc) < newton_tol:
+                break
+        history.append(norms)
+        a_np = ca + d_np / (beta * dt * dt)
+        v_np = cv + gamma / (beta * dt) * d_np
+        fint_n, _ = assemble(d_np)
+        fext_n = fext_np
+        d, v, a, t = d_np, v_np, a_np, t_np
+    return d, history
+
+
+def csr_to_dense(rowptr, colind, vals, n):
+    A = np.zeros((n, n))
+    for r in range(n):
+        s, e = rowptr[r], rowptr[r + 1]
+        A[r, colind[s:e]] = vals[s:e]
+    return A

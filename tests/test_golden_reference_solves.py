@@ -1,0 +1,90 @@
+"""Solve-level golden vectors of the reference's own regression inputs (RESULT DESCRIPTION, TOLERANCE 1e-12),
+replayed with the mock structure driver on (a) the CPU oracle and (b) the CUDA library.  These pin the
+Neo-Hooke internal force of hex8 / hex27 / tet10 (and the consistent mass matrix for the GenAlpha cases)
+against numbers produced by the reference itself.  Fixtures: tests/golden/*.json (made by make_golden.py)."""
+import numpy as np
+import pytest
+import structure_driver as sd
+
+CASES = [
+    "solid_ele_hex8_Standard_eas_none_stressout",
+    "solid_ele_hex8_Standard_eas_none_dynamic",
+    "solid_ele_hex27_Standard_stressout",
+    "solid_ele_hex27_Standard_dynamic",
+    "solid_ele_tet10_Standard_stressout",
+    "solid_ele_tet10_Standard_dynamic",
+]
+TOL = 1e-12  # the reference's TOLERANCE for every displacement value
+
+
+def oracle_backend(oracle, p):
+    job = oracle.Job.from_mesh(p.ct, p.node_gid, p.X, p.ele_gid, p.node_gid[p.conn])
+    job.set_problem(0, 1, p.young, p.nue)
+    o = job.rank(0)
+    assert np.array_equal(job.node_gid, p.node_gid)
+
+    def assemble(d):
+        job.set_u_nodal(d.reshape(-1, 3))
+        bad, _ = job.evaluate(oracle.ACTION_NLNSTIFF)
+        assert bad == 0
+        return job.get_f(0, p.n_dof), sd.csr_to_dense(o["rowptr"], o["colind"], job.get_K(0, o["nnz"]), p.n_dof)
+
+    def mass():
+        M = np.zeros((p.n_dof, p.n_dof))
+        for en in p.conn:
+            err, _, _, Me = oracle.element_evaluate(p.ct, 0, 1, p.young, p.nue, p.X[en], np.zeros((len(en), 3)), want_K=False,
+                                                    want_M=True, rho=p.dens)
+            assert err == 0
+            dofs = (3 * en[:, None] + np.arange(3)).reshape(-1)
+            M[np.ix_(dofs, dofs)] += Me
+        return M
+    return assemble, mass
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_reference_result_description_oracle(oracle, case):
+    p = sd.Problem(sd.load(case), oracle.node_param_coords)
+    assemble, mass = oracle_backend(oracle, p)
+    d, hist = sd.run(p, assemble, mass)
+    err, n = p.result_error(d)
+    assert n >= 12
+    assert err <= TOL, (case, err, hist)
+
+
+def cuda_backend(fc, p):
+    s = fc.Solid(0)
+    s.set_mesh(p.ct, fc.FC_FORM_DISPLACEMENT, p.X, p.node_gid, np.zeros(len(p.node_gid), np.int32), p.conn, p.ele_gid)
+    s.set_material(fc.FC_MAT_ELASTHYPER_COUPNEOHOOKE, p.young, p.nue)
+    n_row, n_col, nnz = s.build_graph()
+    assert n_row == p.n_dof
+    rowptr, colind = s.get_graph()
+
+    def assemble(d):
+        K, f = np.zeros(nnz), np.zeros(n_row)
+        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, d, f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+        return f, sd.csr_to_dense(rowptr, colind, K, n_row)
+
+    def mass():
+        M = np.zeros(nnz)
+        s.evaluate_mass(p.dens, M)
+        return sd.csr_to_dense(rowptr, colind, M, n_row)
+    return s, assemble, mass
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", CASES)
+def test_reference_result_description_cuda(fc, oracle, case):
+    p = sd.Problem(sd.load(case), oracle.node_param_coords)
+    s, assemble, mass = cuda_backend(fc, p)
+    d, hist = sd.run(p, assemble, mass)
+    err, n = p.result_error(d)
+    assert err <= TOL, (case, err, hist)
+    # same Newton history as the oracle-driven solve (north_star: iteration counts and residual norms match)
+    a2, m2 = oracle_backend(oracle, p)
+    d2, hist2 = sd.run(p, a2, m2)
+    assert [len(h) for h in hist] == [len(h) for h in hist2]
+    for h, h2 in zip(hist, hist2):
+        for x, y in zip(h, h2):
+            assert abs(x - y) <= 1e-9 * max(h2[0], 1e-300) + 1e-12
+    assert np.max(np.abs(d - d2)) <= 1e-12 * np.max(np.abs(d2))
+    s.close()

@@ -177,3 +177,35 @@ def test_slab_pipelined_zero_fill(fc, oracle, n_slabs):
             assert np.max(np.abs(K1 - K0)) <= 1e-13 * np.max(np.abs(K0))
             assert np.max(np.abs(f1 - f0)) <= 1e-13 * np.max(np.abs(K0))
         s.close()
+
+
+@pytest.mark.parametrize("ct,n", [(0, (4, 3, 2)), (1, (2, 2, 2)), (2, None)])
+def test_mass_matrix_parity(fc, oracle, ct, n):
+    """consistent mass (struct_calc_nlnstiffmass / add_mass_matrix, tet10 with the 11-point rule) against the
+    oracle's element mass matrices assembled on the host; rows sum to the nodal share of the total mass."""
+    import structure_driver as sd
+    if ct == 2:
+        p = sd.Problem(sd.load("solid_ele_tet10_Standard_dynamic"), oracle.node_param_coords)
+        X, gid, conn, egid = p.X, p.node_gid, p.conn, p.ele_gid
+    else:
+        g = fc.Grid(ct, n)
+        X, gid, conn, egid = g.X * np.array([1.0, 1.3, 0.7]), g.node_gid, g.conn, g.ele_gid
+    rho = 0.37
+    s = fc.Solid(0)
+    s.set_mesh(ct, DISP, X, gid, np.zeros(len(gid), np.int32), conn, egid)
+    s.set_material(NH, 10.0, 0.25)
+    n_row, n_col, nnz = s.build_graph()
+    rowptr, colind = s.get_graph()
+    M = np.full(nnz, 7.0)
+    s.evaluate_mass(rho, M)
+    Md = sd.csr_to_dense(rowptr, colind, M, n_row)
+    Mo = np.zeros((n_row, n_row))
+    for en in conn:
+        err, _, _, Me = oracle.element_evaluate(ct, 0, 1, 10.0, 0.25, X[en], np.zeros((len(en), 3)), want_K=False, want_M=True, rho=rho)
+        dofs = (3 * en[:, None] + np.arange(3)).reshape(-1)
+        Mo[np.ix_(dofs, dofs)] += Me
+    assert np.max(np.abs(Md - Mo)) <= 1e-13 * np.max(np.abs(Mo))
+    # adding a second time doubles it (+= semantics without ZERO_FIRST)
+    s.evaluate_mass(rho, M, flags=0)
+    assert np.max(np.abs(sd.csr_to_dense(rowptr, colind, M, n_row) - 2 * Mo)) <= 1e-13 * np.max(np.abs(Mo))
+    s.close()

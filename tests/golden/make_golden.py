@@ -25,6 +25,7 @@ CASES = [
     "solid_ele_hex27_Standard_dynamic.dat",
     "solid_ele_tet10_Standard_stressout.dat",
     "solid_ele_tet10_Standard_dynamic.dat",
+    "sohex8fbar_cooks_nl_new_struc.dat",  # 64 hex8 TECH fbar, CoupNeoHooke NUE 0.4999, statics, 20 load steps
 ]
 
 
@@ -70,11 +71,11 @@ def from_dat(path):
     for l in s["MATERIALS"]:
         t = l.split()
         mats[int(t[1])] = t[2:]
-    functs = {int(k[5:]): v[0].split("SYMBOLIC_FUNCTION_OF_SPACE_TIME")[1].strip() for k, v in s.items() if k.startswith("FUNCT")}
+    functs = {int(k[5:]): v[0].split("SYMBOLIC_FUNCTION_OF_SPACE_TIME")[1].strip() for k, v in s.items() if re.match(r"FUNCT\d+$", k)}
     results = []
     for l in s["RESULT DESCRIPTION"]:
         t = l.split()
-        results.append({"node": int(t[t.index("NODE") + 1]), "quantity": t[t.index("QUANTITY") + 1],
+        results.append({"node": int(t[t.index("NODE") + 1]) if "NODE" in t else -1, "quantity": t[t.index("QUANTITY") + 1],
                         "value": float(t[t.index("VALUE") + 1]), "tolerance": float(t[t.index("TOLERANCE") + 1])})
     surf = {}
     for l in s["DSURF-NODE TOPOLOGY"]:

@@ -13,13 +13,13 @@ CASES = [
     "solid_ele_hex27_Standard_dynamic",
     "solid_ele_tet10_Standard_stressout",
     "solid_ele_tet10_Standard_dynamic",
+    "sohex8fbar_cooks_nl_new_struc",  # F-bar + Neo-Hooke NUE 0.4999 (BASELINE config C4's element), TOLERANCE 1e-8
 ]
-TOL = 1e-12  # the reference's TOLERANCE for every displacement value
 
 
 def oracle_backend(oracle, p):
     job = oracle.Job.from_mesh(p.ct, p.node_gid, p.X, p.ele_gid, p.node_gid[p.conn])
-    job.set_problem(0, 1, p.young, p.nue)
+    job.set_problem(p.form, 1, p.young, p.nue)
     o = job.rank(0)
     assert np.array_equal(job.node_gid, p.node_gid)
 
@@ -46,14 +46,14 @@ def test_reference_result_description_oracle(oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     assemble, mass = oracle_backend(oracle, p)
     d, hist = sd.run(p, assemble, mass)
-    err, n = p.result_error(d)
-    assert n >= 12
-    assert err <= TOL, (case, err, hist)
+    err, n = p.result_error(d)  # in units of the reference's TOLERANCE of each value (1e-12; Cook: 1e-8)
+    assert n >= 1
+    assert err <= 1.0, (case, err, hist)
 
 
 def cuda_backend(fc, p):
     s = fc.Solid(0)
-    s.set_mesh(p.ct, fc.FC_FORM_DISPLACEMENT, p.X, p.node_gid, np.zeros(len(p.node_gid), np.int32), p.conn, p.ele_gid)
+    s.set_mesh(p.ct, p.form, p.X, p.node_gid, np.zeros(len(p.node_gid), np.int32), p.conn, p.ele_gid)
     s.set_material(fc.FC_MAT_ELASTHYPER_COUPNEOHOOKE, p.young, p.nue)
     n_row, n_col, nnz = s.build_graph()
     assert n_row == p.n_dof
@@ -78,7 +78,7 @@ def test_reference_result_description_cuda(fc, oracle, case):
     s, assemble, mass = cuda_backend(fc, p)
     d, hist = sd.run(p, assemble, mass)
     err, n = p.result_error(d)
-    assert err <= TOL, (case, err, hist)
+    assert err <= 1.0, (case, err, hist)
     # same Newton history as the oracle-driven solve (north_star: iteration counts and residual norms match)
     a2, m2 = oracle_backend(oracle, p)
     d2, hist2 = sd.run(p, a2, m2)

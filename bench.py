@@ -57,30 +57,45 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, device):
         super().__init__(daemon=True)
-        self.device, self.rows, self.stop_flag = device, [], False
+        self.device, self.rows, self.proc = device, [], None
+        self.window = [None, None]  # monotonic time stamps of the timed region
 
     def run(self):
-        while not self.stop_flag:
+        # one long-lived nvidia-smi sampling every 20 ms (a fresh process per sample takes ~100 ms and would
+        # miss a timed region of a few dozen ms); lines are stamped when read
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.device),
+                                          "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append((time.monotonic(), [c.strip() for c in line.strip().split(",")]))
+        except Exception:
+            pass
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.device)],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                self.proc.wait(timeout=5)
             except Exception:
-                pass
-            time.sleep(0.1)
+                self.proc.kill()
+        self.join(timeout=5)
 
     def summary(self):
-        sm = [float(r[1]) for r in self.rows if len(r) > 8 and r[1].replace(".", "").isdigit()]
-        mx = [float(r[2]) for r in self.rows if len(r) > 8 and r[2].replace(".", "").isdigit()]
+        t0, t1 = self.window
+        rows = [r for t, r in self.rows if len(r) > 8 and t0 is not None and t0 <= t <= t1]
+        where = "timed region"
+        if len(rows) < 3:  # region shorter than a few sampling periods: add the identical steps run right after it
+            rows = [r for t, r in self.rows if len(r) > 8 and t0 is not None and t >= t0]
+            where = "timed region + the identical steps after it"
+        sm = [float(r[1]) for r in rows if r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in rows if r[2].replace(".", "").isdigit()]
         reasons = set()
-        for r in self.rows:
-            if len(r) > 8:
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
-                    if v.lower().startswith("active"):
-                        reasons.add(name)
+        for r in rows:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "sampled": where}
 
 
 def load_peaks():
@@ -188,20 +203,23 @@ def run_ours(args):
     l0 = s.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kernel_ms = []
+    time.sleep(0.1)  # let the sampler come up
     barrier()
+    sampler.window[0] = time.monotonic()
     ev0.record()
     for _ in range(args.steps):
         step()
     ev1.record()
     barrier()
+    sampler.window[1] = time.monotonic()
     total_ms = ev0.elapsed_time(ev1)
     launches = s.launch_count() - l0 + (args.steps if world > 1 else 0)  # + NCCL all-to-all per step
     # dominant-kernel duration: events bracketing the element kernel inside evaluate (ctx stream)
-    for _ in range(min(args.steps, 10)):
+    t_more = time.monotonic()
+    while len(kernel_ms) < min(args.steps, 10) or time.monotonic() - t_more < 0.25:
         step()
         kernel_ms.append(s.last_kernel_ms())
-    sampler.stop_flag = True
-    sampler.join()
+    sampler.stop()
     t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -216,8 +234,11 @@ def run_ours(args):
     ele_ms = float(np.mean([k[1] for k in kernel_ms]))
     alg_bytes = 8 * nnz + 72 * grid.n_col_nodes + 32 * grid.n_col_eles  # K once, X/u/f once, conn once
     achieved = alg_bytes / (ele_ms * 1e-3) / 1e9
+    traffic = args.traffic
+    if traffic is None and args.edge == 100 and world == 1 and not args.kernel_flags:
+        traffic = 4.083e9  # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, profiles/r01_mma_kernel_ncu_full_c.md
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": args.traffic, "peak_source": peak_src, "kernel": "k_hex8_neohooke_mma<true>" if not args.kernel_flags else f"flags={args.kernel_flags}",
+                "traffic": traffic, "peak_source": peak_src, "kernel": "k_hex8_neohooke_mma<true>" if not args.kernel_flags else f"flags={args.kernel_flags}",
                 "kernel_ms": ele_ms, "zero_fill_ms": zero_ms, "algorithmic_bytes_per_launch": alg_bytes}
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",

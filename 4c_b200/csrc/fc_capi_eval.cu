@@ -9,6 +9,7 @@
 #include "fc_kernels_generic.cuh"
 #include "fc_kernels_hex8nh.cuh"
 #include "fc_kernels_hex8nh_mma.cuh"
+#include "fc_kernels_hex8_mma_ext.cuh"
 #include "fc_kernels_setup.cuh"
 
 namespace
@@ -49,12 +50,28 @@ namespace
     return cudaGetLastError();
   }
 
+  template <int VAR, bool WANT_K>
+  cudaError_t launch_hex8_ext(fc_ctx* ctx, const fc::EvalArgs& A)
+  {
+    using Cfg = fc::Hex8MmaExtCfg;
+    auto kern = A.dbc ? fc::k_hex8_mma_ext<VAR, WANT_K, true> : fc::k_hex8_mma_ext<VAR, WANT_K, false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+    if (e != cudaSuccess) return e;
+    kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
   template <bool WANT_K>
   cudaError_t dispatch(fc_ctx* ctx, const fc::EvalArgs& A, int flags)
   {
     const bool fbar = ctx->formulation == FC_FORM_FBAR;
     if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC))
       return launch_hex8nh<WANT_K>(ctx, A, (flags & FC_EVAL_CLOSED_FORM_FMA) != 0);
+    if (ctx->celltype == FC_HEX8 && fbar && ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC))
+      return launch_hex8_ext<fc::VAR_NH_FBAR, WANT_K>(ctx, A);
+    if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_SVK && !(flags & FC_EVAL_FORCE_GENERIC))
+      return launch_hex8_ext<fc::VAR_SVK_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_HEX8) return fbar ? launch_generic<fc::HEX8, fc::FORM_FBAR, WANT_K>(ctx, A) : launch_generic<fc::HEX8, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_HEX27) return launch_generic<fc::HEX27, fc::FORM_DISP, WANT_K>(ctx, A);
     return launch_generic<fc::TET10, fc::FORM_DISP, WANT_K>(ctx, A);

@@ -58,16 +58,27 @@ class ClockSampler(threading.Thread):
     def __init__(self, device):
         super().__init__(daemon=True)
         self.device, self.rows, self.proc = device, [], None
-        self.window = [None, None]  # monotonic time stamps of the timed region
+        self.window = [None, None]  # wall-clock stamps of the timed region
 
     def run(self):
         # one long-lived nvidia-smi sampling every 20 ms (a fresh process per sample takes ~100 ms and would
-        # miss a timed region of a few dozen ms); lines are stamped when read
+        # miss a timed region of a few dozen ms).  stdout is a pty so that it is line-buffered; every line carries
+        # nvidia-smi's own wall-clock timestamp, which places it relative to the timed region.
+        import datetime
+        import pty
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.device),
-                                          "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            for line in self.proc.stdout:
-                self.rows.append((time.monotonic(), [c.strip() for c in line.strip().split(",")]))
+            master, slave = pty.openpty()
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu=timestamp,{self.Q}", "--format=csv,noheader,nounits", "-i",
+                                          str(self.device), "-lms", "20"], stdout=slave, stderr=subprocess.DEVNULL, close_fds=True)
+            os.close(slave)
+            with os.fdopen(master, "r", errors="ignore") as f:
+                for line in f:
+                    c = [x.strip() for x in line.strip().split(",")]
+                    try:
+                        ts = datetime.datetime.strptime(c[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                    except Exception:
+                        continue
+                    self.rows.append((ts, c[1:]))
         except Exception:
             pass
 
@@ -205,13 +216,13 @@ def run_ours(args):
     kernel_ms = []
     time.sleep(0.1)  # let the sampler come up
     barrier()
-    sampler.window[0] = time.monotonic()
+    sampler.window[0] = time.time()
     ev0.record()
     for _ in range(args.steps):
         step()
     ev1.record()
     barrier()
-    sampler.window[1] = time.monotonic()
+    sampler.window[1] = time.time()
     total_ms = ev0.elapsed_time(ev1)
     launches = s.launch_count() - l0 + (args.steps if world > 1 else 0)  # + NCCL all-to-all per step
     # dominant-kernel duration: events bracketing the element kernel inside evaluate (ctx stream)

@@ -73,6 +73,15 @@ def setup_rank(fc, job, r, ct, form, mat, young, nue, use_set_graph=False):
     return s, o, col
 
 
+def kernel_variants(fc, ct, form, mat):
+    """kernel-selection flags to cover: the default kernel of the combination plus its alternatives"""
+    if ct == HEX8 and form == DISP and mat == NH:
+        return [0, fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC]  # DMMA closed form, FMA closed form, generic
+    if ct == HEX8 and ((form == FBAR and mat == NH) or (form == DISP and mat == SVK)):
+        return [0, fc.FC_EVAL_FORCE_GENERIC]  # tensor-core closed form (k_hex8_mma_ext), generic
+    return [0]
+
+
 def rel(a, b):
     return np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300)
 
@@ -99,9 +108,7 @@ def test_element_level_parity(fc, oracle, ct, form, mat, nue, n):
     bad, fe_ref, Ke_ref = oracle.element_evaluate_batch(ct, form, mat, 10.0, nue, job.X[conn], u[conn])
     assert bad == 0
     ucol = np.ascontiguousarray(u[col].reshape(-1))
-    variants = [0]
-    if ct == HEX8 and form == DISP and mat == NH:
-        variants = [0, fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC]
+    variants = kernel_variants(fc, ct, form, mat)
     eidx = {int(g): i for i, g in enumerate(job.ele_gid)}
     order = np.array([eidx[int(g)] for g in o["col_eles"]])
     for flags in variants:
@@ -136,9 +143,7 @@ def test_assembled_parity(fc, oracle, ct, form, mat, nue, n, nranks):
         assert np.array_equal(rp, o["rowptr"]) and np.array_equal(ci, o["colind"])  # sparsity pattern bit-exact
         ucol = np.ascontiguousarray(u[col].reshape(-1))
         K_ref, f_ref = job.get_K(r, o["nnz"]), job.get_f(r, o["n_row_dof"])
-        variants = [0]
-        if ct == HEX8 and form == DISP and mat == NH:
-            variants = [0, fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC]
+        variants = kernel_variants(fc, ct, form, mat)
         for flags in variants:
             K, f = np.full(o["nnz"], 7.0), np.full(o["n_row_dof"], 7.0)
             cnt, gid = s.evaluate(fc.FC_ACTION_NLNSTIFF, ucol, f, K, flags=flags | fc.FC_EVAL_ZERO_FIRST)

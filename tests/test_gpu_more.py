@@ -209,3 +209,37 @@ def test_mass_matrix_parity(fc, oracle, ct, n):
     s.evaluate_mass(rho, M, flags=0)
     assert np.max(np.abs(sd.csr_to_dense(rowptr, colind, M, n_row) - 2 * Mo)) <= 1e-13 * np.max(np.abs(Mo))
     s.close()
+
+
+@pytest.mark.parametrize("form,mat,nue", [(FBAR, NH, 0.499), (DISP, SVK, 0.3)])
+def test_full_size_kernel_agreement_fbar_svk(fc, form, mat, nue):
+    """BASELINE C4's element (F-bar Neo-Hooke nu=0.499) and C1's (SVK) at 10^6 elements: the tensor-core closed form
+    and the generic B-operator kernel agree, translations are in the null space, f is self-equilibrated."""
+    import torch
+    n = (100, 100, 100)
+    g = fc.Grid(HEX8, n)
+    s = fc.Solid(0)
+    s.set_mesh(fc.FC_HEX8, form, g.X, g.node_gid, g.node_owner, g.conn, g.ele_gid)
+    s.set_material(mat, 10.0, nue)
+    n_row, n_col, nnz = s.build_graph()
+    dev = torch.device("cuda", 0)
+    u = torch.from_numpy(field(g.X, 0.01).reshape(-1)).to(dev)
+    K = torch.empty(nnz, dtype=torch.float64, device=dev)
+    f = torch.empty(n_row, dtype=torch.float64, device=dev)
+    assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+    kmax = K.abs().max()
+    rowptr, colind = s.get_graph()
+    rp = torch.from_numpy(rowptr).to(dev)
+    ci = torch.from_numpy(colind).to(dev).long()
+    rows = torch.repeat_interleave(torch.arange(n_row, device=dev), (rp[1:] - rp[:-1]))
+    for d in range(3):
+        m = (ci % 3) == d
+        rs = torch.zeros(n_row, dtype=torch.float64, device=dev).index_add_(0, rows[m], K[m])
+        assert rs.abs().max() <= 1e-12 * kmax
+    assert f.view(-1, 3).sum(0).abs().max() <= 1e-10 * f.abs().max() * 1e3
+    del rows, ci, rp
+    K2, f2 = torch.empty_like(K), torch.empty_like(f)
+    assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f2, K2, flags=fc.FC_EVAL_FORCE_GENERIC | fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+    assert (K2 - K).abs().max() <= 1e-12 * kmax
+    assert (f2 - f).abs().max() <= 1e-12 * kmax * 0.01
+    s.close()

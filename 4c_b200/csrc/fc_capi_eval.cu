@@ -10,6 +10,7 @@
 #include "fc_kernels_hex8nh.cuh"
 #include "fc_kernels_hex8nh_mma.cuh"
 #include "fc_kernels_hex8_mma_ext.cuh"
+#include "fc_kernels_nh_mma_gen.cuh"
 #include "fc_kernels_setup.cuh"
 
 namespace
@@ -62,6 +63,18 @@ namespace
     return cudaGetLastError();
   }
 
+  template <int CT, bool WANT_K>
+  cudaError_t launch_nh_gen(fc_ctx* ctx, const fc::EvalArgs& A)
+  {
+    using Cfg = fc::NhGenCfg<CT>;
+    auto kern = A.dbc ? fc::k_nh_mma_gen<CT, WANT_K, true> : fc::k_nh_mma_gen<CT, WANT_K, false>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+    if (e != cudaSuccess) return e;
+    kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
   template <bool WANT_K>
   cudaError_t dispatch(fc_ctx* ctx, const fc::EvalArgs& A, int flags)
   {
@@ -73,8 +86,9 @@ namespace
     if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_SVK && !(flags & FC_EVAL_FORCE_GENERIC))
       return launch_hex8_ext<fc::VAR_SVK_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_HEX8) return fbar ? launch_generic<fc::HEX8, fc::FORM_FBAR, WANT_K>(ctx, A) : launch_generic<fc::HEX8, fc::FORM_DISP, WANT_K>(ctx, A);
-    if (ctx->celltype == FC_HEX27) return launch_generic<fc::HEX27, fc::FORM_DISP, WANT_K>(ctx, A);
-    return launch_generic<fc::TET10, fc::FORM_DISP, WANT_K>(ctx, A);
+    const bool nh_gen = ctx->mat.kind == fc::MAT_NEOHOOKE && !fbar && !(flags & FC_EVAL_FORCE_GENERIC);
+    if (ctx->celltype == FC_HEX27) return nh_gen ? launch_nh_gen<fc::HEX27, WANT_K>(ctx, A) : launch_generic<fc::HEX27, fc::FORM_DISP, WANT_K>(ctx, A);
+    return nh_gen ? launch_nh_gen<fc::TET10, WANT_K>(ctx, A) : launch_generic<fc::TET10, fc::FORM_DISP, WANT_K>(ctx, A);
   }
 
   fc::EvalArgs base_args(const fc_ctx* ctx)

@@ -35,11 +35,7 @@ namespace fc
     static constexpr int oX = oInv + GP4 * 20;       // [NP][3] current coordinates rel. node 0, zero padded
     static constexpr int oXm = oX + 3 * NP;          // [nen][3] material coordinates rel. node 0
     static constexpr int ele_doubles = (oXm + 3 * nen + 1) & ~1;
-    // scatter staging per warp: cells whose 3 nen columns fit one warp (tet10) stage the 24 complete rows of a row
-    // tile and add whole CSR row segments; the others stage one 8x8 node tile pair in two halves of 12 rows x 24
-    static constexpr bool rowmode = 3 * nen <= 32;
-    static constexpr int rs = 33;                    // row stride of the row-mode staging
-    static constexpr int stage = rowmode ? 24 * rs : 288;
+    static constexpr int stage = 288;                // per warp: 12 rows x 24
     static constexpr size_t smem_bytes = sizeof(double) * ((size_t)epb * ele_doubles + warps * stage);
   };
 
@@ -265,7 +261,7 @@ namespace fc
                 for (int j = 0; j < 3; ++j) Ke[(3 * arow + i) + (size_t)(3 * NEN) * (3 * bcol + j)] = Kb[c][3 * i + j];
           }
         }
-        if (A.K && !Cfg::rowmode)
+        if (A.K)
         {
           const int ln = lane < 24 ? lane : 23;
           const int b = ln / 3;
@@ -316,49 +312,6 @@ namespace fc
             }
           }
         }
-        if (A.K && Cfg::rowmode)
-        {
-          // rows 3 a8 + i of this row tile, columns of the two column nodes of this lane
-#pragma unroll
-          for (int c = 0; c < 2; ++c)
-          {
-            const int bcol = 8 * nt + b0 + c;
-            if (bcol < NEN)
-            {
-#pragma unroll
-              for (int i = 0; i < 3; ++i)
-#pragma unroll
-                for (int j = 0; j < 3; ++j) Ks[(3 * a8 + i) * Cfg::rs + 3 * bcol + j] = Kb[c][3 * i + j];
-            }
-          }
-        }
-      }
-      if (WANT_K && A.K && Cfg::rowmode)
-      {
-        // the 24 rows of this row tile are complete: one reduction instruction per CSR row segment (3 nen lanes)
-        __syncwarp();
-        const int bl = lane < 3 * NEN ? lane / 3 : 0;
-#pragma unroll 1
-        for (int rr = 0; rr < 8; ++rr)
-        {
-          const int aa = 8 * mt + rr;
-          if (aa >= NEN) break;
-          const long long rb = s_rowbase[el][aa];
-          const int rl = s_rowlen[el][aa];
-          const bool ok = rb >= 0 && lane < 3 * NEN;
-          double* ptr = ok ? A.K + rb + 3 * (int)s_slots[warp][rr][bl] + (lane - 3 * bl) : nullptr;
-          const int ls = lane < 3 * NEN ? lane : 0;
-          const double v0 = Ks[(3 * rr) * Cfg::rs + ls], v1 = Ks[(3 * rr + 1) * Cfg::rs + ls], v2 = Ks[(3 * rr + 2) * Cfg::rs + ls];
-          if (HAS_DBC)
-          {
-            red_add_if(ok && !((rl >> 28) & 1), ptr, v0);
-            red_add_if(ok && !((rl >> 29) & 1), ptr + (long long)(rl & 0x0FFFFFFF), v1);
-            red_add_if(ok && !((rl >> 30) & 1), ptr + 2ll * (rl & 0x0FFFFFFF), v2);
-          }
-          else
-            red_add3_if(ok, ptr, 8ll * rl, v0, v1, v2);
-        }
-        __syncwarp();
       }
       // residual rows of this tile: f_a = sum_b s_ab x_b - sum_gp sqrt(kappa) ghat_a
 #pragma unroll

@@ -41,7 +41,7 @@ def tet10_cube(n):
         pts = [c[:, a] for a in range(4)] + [(c[:, a] + c[:, b]) // 2 for a, b in mids]
         ids = np.stack([(q[:, 2] * N + q[:, 1]) * N + q[:, 0] for q in pts], axis=1)
         conn.append(ids)
-    conn = np.concatenate(conn, axis=0)
+    conn = np.stack(conn, axis=1).reshape(-1, 10)  # the 6 tets of a cell are consecutive (cell-major element order)
     used, inv = np.unique(conn, return_inverse=True)
     X = np.stack([(used % N), (used // N) % N, used // (N * N)], axis=1) / (2.0 * n)
     return used.astype(np.int32), X, inv.reshape(conn.shape).astype(np.int32)

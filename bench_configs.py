@@ -115,6 +115,8 @@ def main():
         ("C2 hex8 NeoHooke 100^3 (FMA closed form)", H8, D, NH, 0.25, (100, 100, 100), fc.FC_EVAL_CLOSED_FORM_FMA),
         ("C2 hex8 NeoHooke 100^3 (generic B-operator)", H8, D, NH, 0.25, (100, 100, 100), fc.FC_EVAL_FORCE_GENERIC),
         ("C3a hex27 NeoHooke 48^3", H27, D, NH, 0.25, (48, 48, 48), 0),
+        ("C3a-96 hex27 NeoHooke 96^3", H27, D, NH, 0.25, (96, 96, 96), 0),
+        ("C3a-full hex27 NeoHooke 126^3 (K values 74.6 GB)", H27, D, NH, 0.25, (126, 126, 126), 0),
         ("C3b tet10 NeoHooke 70^3x6", T10, D, NH, 0.25, (70, 70, 70), 0),
         ("C4 hex8 F-bar NeoHooke nu=0.499 200^3", H8, FB, NH, 0.499, (200, 200, 200), 0),
         ("C5/8 hex8 NeoHooke 200^3 (one GPU's share of 400^3)", H8, D, NH, 0.25, (200, 200, 200), 0),
@@ -122,6 +124,8 @@ def main():
     for c in cfgs:
         if args.only and args.only not in c[0]:
             continue
+        if not args.only and ("C3a-96" in c[0] or "C3a-full" in c[0]):
+            continue  # large hex27 cases only on request
         run(fc, c[0], c[1], c[2], c[3], c[4], c[5], args.steps, c[6])
 
 

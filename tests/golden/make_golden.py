@@ -73,7 +73,7 @@ def from_dat(path):
         mats[int(t[1])] = t[2:]
     functs = {int(k[5:]): v[0].split("SYMBOLIC_FUNCTION_OF_SPACE_TIME")[1].strip() for k, v in s.items() if re.match(r"FUNCT\d+$", k)}
     results = []
-    for l in s["RESULT DESCRIPTION"]:
+    for l in s.get("RESULT DESCRIPTION", []):
         t = l.split()
         results.append({"node": int(t[t.index("NODE") + 1]) if "NODE" in t else -1, "quantity": t[t.index("QUANTITY") + 1],
                         "value": float(t[t.index("VALUE") + 1]), "tolerance": float(t[t.index("TOLERANCE") + 1])})
@@ -149,5 +149,63 @@ def main():
         print(out, len(d["nodes"]), "nodes", len(d["elements"]), "elements", len(d["results"]), "results")
 
 
+
+
+# ---- solid_runtime_ghosting_output.dat: reference result = runtime VTK output (binary .vtu per rank) -------------
+def _vtu_arrays(path):
+    """DataArrays of a vtkZLibDataCompressor / base64 .vtu (header: nblocks, blocksize, lastsize, csizes...; uint32)"""
+    import base64
+    import struct
+    import zlib
+    import xml.etree.ElementTree as ET
+    import numpy as np
+    out = {}
+    root = ET.parse(path).getroot()
+    dt = {"Float64": np.float64, "Int32": np.int32, "UInt8": np.uint8}
+    for da in root.iter("DataArray"):
+        if da.get("format") != "binary":
+            continue
+        txt = "".join(da.text.split())
+        nb = struct.unpack("<I", base64.b64decode(txt[:8])[:4])[0]
+        hlen = 4 * (3 + nb)
+        henc = (hlen + 2) // 3 * 4
+        hdr = struct.unpack("<%dI" % (3 + nb), base64.b64decode(txt[:henc])[:hlen])
+        raw = base64.b64decode(txt[henc:])
+        data, pos = b"", 0
+        for cs in hdr[3:]:
+            data += zlib.decompress(raw[pos:pos + cs])
+            pos += cs
+        arr = np.frombuffer(data, dtype=dt[da.get("type")])
+        nc = int(da.get("NumberOfComponents", "1"))
+        out[da.get("Name") or "points"] = arr.reshape(-1, nc) if nc > 1 else arr
+    return out
+
+
+def ghosting_case():
+    import glob
+    import numpy as np
+    name = "solid_runtime_ghosting_output.dat"
+    d = from_dat(os.path.join(INP, name))
+    assert d["materials"][1][0] == "MAT_Struct_StVenantKirchhoff"
+    d["source"] = "tests/input_files/" + name + " + tests/input_files/ref/solid_runtime_ghosting_output-vtk/vtk-files/structure-000002-*.vtu"
+    coords = {tuple(np.round(v, 9)): k for k, v in d["nodes"].items()}
+    disp = {}
+    for f in sorted(glob.glob(os.path.join(INP, "ref", "solid_runtime_ghosting_output-vtk", "vtk-files", "structure-000002-*.vtu"))):
+        a = _vtu_arrays(f)
+        for x, u in zip(a["points"], a["displacement"]):
+            nid = coords[tuple(np.round(x, 9))]
+            if nid in disp:
+                assert np.allclose(disp[nid], u, atol=1e-13)
+            disp[nid] = [float(v) for v in u]
+    assert len(disp) == len(d["nodes"])
+    d["results"] = [{"node": nid, "quantity": q, "value": disp[nid][c], "tolerance": 1e-8}
+                    for nid in sorted(disp) if nid % 4 == 1 for c, q in enumerate(("dispx", "dispy", "dispz"))]  # every 4th node
+    out = os.path.join(OUT, "solid_runtime_ghosting_output.json")
+    with open(out, "w") as f:
+        json.dump(d, f, indent=0, sort_keys=True)
+    print(out, len(d["nodes"]), "nodes", len(d["elements"]), "elements", len(d["results"]), "results")
+
+
 if __name__ == "__main__":
     main()
+    ghosting_case()

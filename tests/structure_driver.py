@@ -42,8 +42,11 @@ class Problem:
         self.conn = np.array([[self.index[n] for n in e["nodes"]] for e in fx["elements"]], np.int32)
         self.ele_gid = np.array([e["id"] - 1 for e in fx["elements"]], np.int32)
         m1 = fx["materials"]["1"]
-        m10 = fx["materials"][m1[m1.index("MATIDS") + 1]]
-        assert m1[0] == "MAT_ElastHyper" and m10[0] == "ELAST_CoupNeoHooke"
+        if m1[0] == "MAT_Struct_StVenantKirchhoff":
+            m10, self.mat = m1, 0  # FC_MAT_STVENANTKIRCHHOFF
+        else:
+            m10, self.mat = fx["materials"][m1[m1.index("MATIDS") + 1]], 1  # FC_MAT_ELASTHYPER_COUPNEOHOOKE
+            assert m1[0] == "MAT_ElastHyper" and m10[0] == "ELAST_CoupNeoHooke"
         techs = {"TECH fbar" in e["opts"] for e in fx["elements"]}
         assert len(techs) == 1
         self.form = 1 if techs.pop() else 0  # FC_FORM_FBAR / FC_FORM_DISPLACEMENT

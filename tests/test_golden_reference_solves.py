@@ -14,12 +14,13 @@ CASES = [
     "solid_ele_tet10_Standard_stressout",
     "solid_ele_tet10_Standard_dynamic",
     "sohex8fbar_cooks_nl_new_struc",  # F-bar + Neo-Hooke NUE 0.4999 (BASELINE config C4's element), TOLERANCE 1e-8
+    "solid_runtime_ghosting_output",  # 640 hex8 SVK (BASELINE config C1's mesh), reference = its runtime VTK output, 1e-8
 ]
 
 
 def oracle_backend(oracle, p):
     job = oracle.Job.from_mesh(p.ct, p.node_gid, p.X, p.ele_gid, p.node_gid[p.conn])
-    job.set_problem(p.form, 1, p.young, p.nue)
+    job.set_problem(p.form, p.mat, p.young, p.nue)
     o = job.rank(0)
     assert np.array_equal(job.node_gid, p.node_gid)
 
@@ -32,7 +33,7 @@ def oracle_backend(oracle, p):
     def mass():
         M = np.zeros((p.n_dof, p.n_dof))
         for en in p.conn:
-            err, _, _, Me = oracle.element_evaluate(p.ct, 0, 1, p.young, p.nue, p.X[en], np.zeros((len(en), 3)), want_K=False,
+            err, _, _, Me = oracle.element_evaluate(p.ct, 0, p.mat, p.young, p.nue, p.X[en], np.zeros((len(en), 3)), want_K=False,
                                                     want_M=True, rho=p.dens)
             assert err == 0
             dofs = (3 * en[:, None] + np.arange(3)).reshape(-1)
@@ -54,7 +55,7 @@ def test_reference_result_description_oracle(oracle, case):
 def cuda_backend(fc, p):
     s = fc.Solid(0)
     s.set_mesh(p.ct, p.form, p.X, p.node_gid, np.zeros(len(p.node_gid), np.int32), p.conn, p.ele_gid)
-    s.set_material(fc.FC_MAT_ELASTHYPER_COUPNEOHOOKE, p.young, p.nue)
+    s.set_material(p.mat, p.young, p.nue)
     n_row, n_col, nnz = s.build_graph()
     assert n_row == p.n_dof
     rowptr, colind = s.get_graph()

@@ -118,6 +118,7 @@ def main():
         ("C3a-96 hex27 NeoHooke 96^3", H27, D, NH, 0.25, (96, 96, 96), 0),
         ("C3a-full hex27 NeoHooke 126^3 (K values 74.6 GB)", H27, D, NH, 0.25, (126, 126, 126), 0),
         ("C3b tet10 NeoHooke 70^3x6", T10, D, NH, 0.25, (70, 70, 70), 0),
+        ("C4s hex8 F-bar NeoHooke nu=0.499 100^3", H8, FB, NH, 0.499, (100, 100, 100), 0),
         ("C4 hex8 F-bar NeoHooke nu=0.499 200^3", H8, FB, NH, 0.499, (200, 200, 200), 0),
         ("C5/8 hex8 NeoHooke 200^3 (one GPU's share of 400^3)", H8, D, NH, 0.25, (200, 200, 200), 0),
     ]

@@ -2,7 +2,9 @@
 // and displacement-based St.Venant-Kirchhoff (BASELINE C1).  Same organisation as fc_kernels_hex8nh_mma.cuh
 // (a warp owns 4 elements; Gauss-point quantities in m8n8k4 fragment layout in shared memory; every lane ends
 // up with the two complete 3x3 blocks K_{a,b0}, K_{a,b0+1}; staged scatter with lane-contiguous FP64 reductions),
-// with nine 8x8 component planes per element instead of six.
+// with THREE 8x8 planes per element (the material gradients) and one 3x3 matrix set per Gauss point: every other
+// quantity of the closed forms is such a matrix times the material gradient and is applied to the fragments in
+// registers, which keeps the shared-memory footprint at the Neo-Hooke kernel's (4 CTAs per SM).
 //
 // Closed forms (g_a = F^-T grad N_a, p_a = F grad N_a = sum_b x_b (grad N_b . grad N_a), all per Gauss point,
 // w detJ = integration factor; reference: 4C_solid_3D_ele_calc_lib.hpp:851-927, 4C_solid_3D_ele_calc_fbar.hpp:65-190,
@@ -37,15 +39,20 @@ namespace fc
     static constexpr int threads = 32 * warps;
     static constexpr int epw = 4;
     static constexpr int epb = warps * epw;
-    // per element: 9 component planes of 64 (fragment layout), sqrt(kappa)[8], x rel [8][3], then g0 [8][3] (F-bar)
-    // or mu w detJ b_ij [8][6] (SVK)
-    static constexpr int oSk = 576, oX = 584, oG0 = 608, oM = 608, ele_doubles = 657;
+    // per element: 3 planes of 64 with the MATERIAL gradients n_a = J^-1 dN_a in fragment layout - every other
+    // Gauss-point quantity of the closed forms is a 3x3 matrix (per Gauss point) times n_a and is applied to the
+    // fragments in registers - then one record of 24 doubles per Gauss point, then x rel [8][3]:
+    //   F-bar: [0..8] sqrt(kappa) j^-1 J (-> ghat), [9..17] (-> v / sqrt(kappa)), [18] sqrt(lambda), [19] sqrt(kappa),
+    //          [20..22] centroid gradient g0 of node gp
+    //   SVK:   [0..8] sqrt(w detJ) F (-> phat), [9..17] w detJ S (-> t), [18..23] mu w detJ b_ij
+    // 409 doubles per element (the 6-plane Neo-Hooke kernel: 417) -> 4 CTAs per SM
+    static constexpr int oR = 192, rec = 24, oX = 384, ele_doubles = 409;
     static constexpr int ks_stride = 24;
     static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles;
   };
 
   template <int VAR, bool WANT_K, bool HAS_DBC>
-  __global__ void __launch_bounds__(Hex8MmaExtCfg::threads, 2) k_hex8_mma_ext(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
+  __global__ void __launch_bounds__(Hex8MmaExtCfg::threads, 4) k_hex8_mma_ext(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
   {
     using Cfg = Hex8MmaExtCfg;
     extern __shared__ __align__(16) double smem_mma_ext[];
@@ -109,9 +116,38 @@ namespace fc
       const double xi0 = (hex_node_pos(t, 0) > 0) ? p : -p;
       const double xi1 = (hex_node_pos(t, 1) > 0) ? p : -p;
       const double xi2 = (hex_node_pos(t, 2) > 0) ? p : -p;
+      double* R = E + Cfg::oR + Cfg::rec * t;
+      double detF0 = 1.0;
+      if (VAR == VAR_NH_FBAR)
+      {
+        // centroid pass first (its own sweep over the nodes: 18 accumulators less in the Gauss-point sweep below)
+        double jc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Jc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+        {
+          const int src = (lane & 24) | a;
+          const double dc[3] = {0.125 * hex_node_pos(a, 0), 0.125 * hex_node_pos(a, 1), 0.125 * hex_node_pos(a, 2)};
+#pragma unroll
+          for (int i = 0; i < 3; ++i)
+          {
+            const double xa = __shfl_sync(0xFFFFFFFFu, xr[i], src), Xa = __shfl_sync(0xFFFFFFFFu, Xr[i], src);
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+            {
+              jc[3 * d + i] += dc[d] * xa;
+              Jc[3 * d + i] += dc[d] * Xa;
+            }
+          }
+        }
+        double jci[9];
+        const double detjc = inv3(jc, jci);
+        detF0 = detjc / det3(Jc);
+        // centroid gradient of node t: g0_t = jc^-1 dN0_t
+        const double c0 = 0.125 * hex_node_pos(t, 0), c1 = 0.125 * hex_node_pos(t, 1), c2 = 0.125 * hex_node_pos(t, 2);
+        if (active)
+          for (int i = 0; i < 3; ++i) R[20 + i] = jci[3 * i] * c0 + jci[3 * i + 1] * c1 + jci[3 * i + 2] * c2;
+      }
       double jm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Jm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-      double jc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Jc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // centroid (F-bar)
-      double dN[24];
 #pragma unroll
       for (int a = 0; a < 8; ++a)
       {
@@ -125,22 +161,14 @@ namespace fc
         }
         const double s0 = hex_node_pos(a, 0), s1 = hex_node_pos(a, 1), s2 = hex_node_pos(a, 2);
         const double r = 1.0 + s0 * xi0, s = 1.0 + s1 * xi1, q = 1.0 + s2 * xi2;
-        dN[3 * a + 0] = 0.125 * s0 * s * q;
-        dN[3 * a + 1] = 0.125 * s1 * q * r;
-        dN[3 * a + 2] = 0.125 * s2 * r * s;
-        const double dc[3] = {0.125 * s0, 0.125 * s1, 0.125 * s2};
+        const double dNa[3] = {0.125 * s0 * s * q, 0.125 * s1 * q * r, 0.125 * s2 * r * s};
 #pragma unroll
         for (int d = 0; d < 3; ++d)
 #pragma unroll
           for (int i = 0; i < 3; ++i)
           {
-            jm[3 * d + i] += dN[3 * a + d] * xa[i];
-            Jm[3 * d + i] += dN[3 * a + d] * Xa[i];
-            if (VAR == VAR_NH_FBAR)
-            {
-              jc[3 * d + i] += dc[d] * xa[i];
-              Jc[3 * d + i] += dc[d] * Xa[i];
-            }
+            jm[3 * d + i] += dNa[d] * xa[i];
+            Jm[3 * d + i] += dNa[d] * Xa[i];
           }
       }
       double ji[9], Ji[9];
@@ -154,12 +182,24 @@ namespace fc
 #pragma unroll
         for (int I = 0; I < 3; ++I) F[3 * i + I] = jm[i] * Ji[3 * I] + jm[3 + i] * Ji[3 * I + 1] + jm[6 + i] * Ji[3 * I + 2];
 
+      // material gradients of all nodes at this Gauss point, fragment layout
+      if (active)
+      {
+#pragma unroll
+        for (int a = 0; a < 8; ++a)
+        {
+          // shape function derivatives recomputed (6 flops) instead of kept in 48 registers across the inversions
+          const double s0 = hex_node_pos(a, 0), s1 = hex_node_pos(a, 1), s2 = hex_node_pos(a, 2);
+          const double r = 1.0 + s0 * xi0, s = 1.0 + s1 * xi1, q = 1.0 + s2 * xi2;
+          const double d0 = 0.125 * s0 * s * q, d1 = 0.125 * s1 * q * r, d2 = 0.125 * s2 * r * s;
+          const int ix = frag_idx(t, a);
+#pragma unroll
+          for (int I = 0; I < 3; ++I) E[I * 64 + ix] = Ji[3 * I] * d0 + Ji[3 * I + 1] * d1 + Ji[3 * I + 2] * d2;
+        }
+      }
       if (VAR == VAR_NH_FBAR)
       {
-        double jci[9];
-        const double detjc = inv3(jc, jci);
-        const double detF0 = detjc / det3(Jc);
-        const double fbar = pow(detF0 / detF, 1.0 / 3.0);
+        const double fbar = cbrt(detF0 / detF);  // reference: std::pow(x, 1/3.) - equal to an ulp
         const double jb = fbar * fbar * fbar * detF;
         const double I3b = jb * jb;
         const double lambda = detJ * mu / fbar;
@@ -170,31 +210,18 @@ namespace fc
         const double cg = sk * (2.0 * beta + 1.0), cp = -lambda / (3.0 * sk);  // v_a / sk = cg g_a + cp p_a
         if (active)
         {
+          // g_a = (j^-1 J) n_a, p_a = F n_a
 #pragma unroll
-          for (int a = 0; a < 8; ++a)
-          {
-            const double d0 = dN[3 * a], d1 = dN[3 * a + 1], d2 = dN[3 * a + 2];
-            const int ix = frag_idx(t, a);
-            double g[3], n[3];
+          for (int i = 0; i < 3; ++i)
 #pragma unroll
-            for (int i = 0; i < 3; ++i)
+            for (int I = 0; I < 3; ++I)
             {
-              g[i] = ji[3 * i] * d0 + ji[3 * i + 1] * d1 + ji[3 * i + 2] * d2;
-              n[i] = Ji[3 * i] * d0 + Ji[3 * i + 1] * d1 + Ji[3 * i + 2] * d2;
+              const double gm = ji[3 * i] * Jm[I] + ji[3 * i + 1] * Jm[3 + I] + ji[3 * i + 2] * Jm[6 + I];
+              R[3 * i + I] = sk * gm;
+              R[9 + 3 * i + I] = cg * gm + cp * F[3 * i + I];
             }
-#pragma unroll
-            for (int i = 0; i < 3; ++i)
-            {
-              const double pa = F[3 * i] * n[0] + F[3 * i + 1] * n[1] + F[3 * i + 2] * n[2];
-              E[i * 64 + ix] = sk * g[i];
-              E[(3 + i) * 64 + ix] = sl * n[i];
-              E[(6 + i) * 64 + ix] = cg * g[i] + cp * pa;
-            }
-          }
-          E[Cfg::oSk + t] = sk;
-          // centroid gradient of node t: g0_t = jc^-1 dN0_t
-          const double c0 = 0.125 * hex_node_pos(t, 0), c1 = 0.125 * hex_node_pos(t, 1), c2 = 0.125 * hex_node_pos(t, 2);
-          for (int i = 0; i < 3; ++i) E[Cfg::oG0 + 3 * t + i] = jci[3 * i] * c0 + jci[3 * i + 1] * c1 + jci[3 * i + 2] * c2;
+          R[18] = sl;
+          R[19] = sk;
         }
       }
       else
@@ -218,25 +245,12 @@ namespace fc
         if (active)
         {
 #pragma unroll
-          for (int a = 0; a < 8; ++a)
-          {
-            const double d0 = dN[3 * a], d1 = dN[3 * a + 1], d2 = dN[3 * a + 2];
-            const int ix = frag_idx(t, a);
-            double n[3];
+          for (int i = 0; i < 9; ++i) R[i] = sw * F[i];
+          const int sym[9] = {0, 3, 5, 3, 1, 4, 5, 4, 2};
 #pragma unroll
-            for (int i = 0; i < 3; ++i) n[i] = Ji[3 * i] * d0 + Ji[3 * i + 1] * d1 + Ji[3 * i + 2] * d2;
-            E[0 * 64 + ix] = sw * (F[0] * n[0] + F[1] * n[1] + F[2] * n[2]);
-            E[1 * 64 + ix] = sw * (F[3] * n[0] + F[4] * n[1] + F[5] * n[2]);
-            E[2 * 64 + ix] = sw * (F[6] * n[0] + F[7] * n[1] + F[8] * n[2]);
-            E[3 * 64 + ix] = n[0];
-            E[4 * 64 + ix] = n[1];
-            E[5 * 64 + ix] = n[2];
-            E[6 * 64 + ix] = detJ * (S[0] * n[0] + S[3] * n[1] + S[5] * n[2]);
-            E[7 * 64 + ix] = detJ * (S[3] * n[0] + S[1] * n[1] + S[4] * n[2]);
-            E[8 * 64 + ix] = detJ * (S[5] * n[0] + S[4] * n[1] + S[2] * n[2]);
-          }
+          for (int i = 0; i < 9; ++i) R[9 + i] = detJ * S[sym[i]];
 #pragma unroll
-          for (int v = 0; v < 6; ++v) E[Cfg::oM + 6 * t + v] = mu * detJ * b[v];
+          for (int v = 0; v < 6; ++v) R[18 + v] = mu * detJ * b[v];
         }
       }
       if (active)
@@ -256,24 +270,55 @@ namespace fc
       const int ek = A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
       const double* G = smem + (size_t)(wel + k) * Cfg::ele_doubles;
       const int fo0 = frag_idx(q, a), fo1 = frag_idx(q + 4, a);
-      double fg[9][2];
+      const double* R0 = G + Cfg::oR + Cfg::rec * q;
+      const double* R1 = G + Cfg::oR + Cfg::rec * (q + 4);
+      double fn[3][2];  // material gradient fragments: node a, Gauss points q and q+4
 #pragma unroll
-      for (int c = 0; c < 9; ++c)
+      for (int I = 0; I < 3; ++I)
       {
-        fg[c][0] = G[c * 64 + fo0];
-        fg[c][1] = G[c * 64 + fo1];
+        fn[I][0] = G[I * 64 + fo0];
+        fn[I][1] = G[I * 64 + fo1];
       }
+      // fragment of (3x3 matrix at offset o of the Gauss-point record) * n_a
+      auto apply = [&](int o, double(&out)[3][2])
+      {
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+        {
+          out[i][0] = R0[o + 3 * i] * fn[0][0] + R0[o + 3 * i + 1] * fn[1][0] + R0[o + 3 * i + 2] * fn[2][0];
+          out[i][1] = R1[o + 3 * i] * fn[0][1] + R1[o + 3 * i + 1] * fn[1][1] + R1[o + 3 * i + 2] * fn[2][1];
+        }
+      };
+      double fg[3][2];  // ghat (F-bar) or phat (SVK)
+      apply(0, fg);
       // s_ab: lambda-weighted (F-bar) or S-weighted (SVK) gradient products
       double sa[3][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
-#pragma unroll
-      for (int i = 0; i < 3; ++i)
+      double sk0 = 0.0, sk1 = 0.0;
+      if (VAR == VAR_NH_FBAR)
       {
-        const int ca = VAR == VAR_NH_FBAR ? 3 + i : 6 + i;
-        dmma884(sa[i][0], sa[i][1], fg[ca][0], fg[3 + i][0]);
-        dmma884(sa[i][0], sa[i][1], fg[ca][1], fg[3 + i][1]);
+        const double sl0 = R0[18], sl1 = R1[18];
+        sk0 = R0[19];
+        sk1 = R1[19];
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+        {
+          const double n0 = sl0 * fn[i][0], n1 = sl1 * fn[i][1];
+          dmma884(sa[i][0], sa[i][1], n0, n0);
+          dmma884(sa[i][0], sa[i][1], n1, n1);
+        }
+      }
+      else
+      {
+        double ft[3][2];
+        apply(9, ft);
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+        {
+          dmma884(sa[i][0], sa[i][1], ft[i][0], fn[i][0]);
+          dmma884(sa[i][0], sa[i][1], ft[i][1], fn[i][1]);
+        }
       }
       const double s0 = sa[0][0] + sa[1][0] + sa[2][0], s1 = sa[0][1] + sa[1][1] + sa[2][1];
-      const double sk0 = VAR == VAR_NH_FBAR ? G[Cfg::oSk + q] : 0.0, sk1 = VAR == VAR_NH_FBAR ? G[Cfg::oSk + 4 + q] : 0.0;
       {
         const double* xk = G + Cfg::oX;
         double fpart[3];
@@ -319,41 +364,42 @@ namespace fc
       }
       if (VAR == VAR_NH_FBAR)
       {
-        // H-operator term: (sum_gp v_a) g0_b^T - sum_gp v_a g_b^T with v / sqrt(kappa) in planes 6..8
-        const double* g0 = G + Cfg::oG0 + 3 * b0;
+        // H-operator term: (sum_gp v_a) g0_b^T - sum_gp v_a g_b^T
+        double fv[3][2];
+        apply(9, fv);
+        const double* g0a = G + Cfg::oR + Cfg::rec * b0 + 20;
+        const double* g0b = g0a + Cfg::rec;
 #pragma unroll
         for (int i = 0; i < 3; ++i)
         {
           double vs0 = 0.0, vs1 = 0.0;
-          dmma884(vs0, vs1, fg[6 + i][0], sk0);
-          dmma884(vs0, vs1, fg[6 + i][1], sk1);
+          dmma884(vs0, vs1, fv[i][0], sk0);
+          dmma884(vs0, vs1, fv[i][1], sk1);
 #pragma unroll
           for (int j = 0; j < 3; ++j)
           {
             double v0 = 0.0, v1 = 0.0;
-            dmma884(v0, v1, fg[6 + i][0], fg[j][0]);
-            dmma884(v0, v1, fg[6 + i][1], fg[j][1]);
-            Kb[0][3 * i + j] += vs0 * g0[j] - v0;
-            Kb[1][3 * i + j] += vs1 * g0[3 + j] - v1;
+            dmma884(v0, v1, fv[i][0], fg[j][0]);
+            dmma884(v0, v1, fv[i][1], fg[j][1]);
+            Kb[0][3 * i + j] += vs0 * g0a[j] - v0;
+            Kb[1][3 * i + j] += vs1 * g0b[j] - v1;
           }
         }
       }
       else
       {
         // mu w detJ b_ij (grad N_a . grad N_b): six weighted tiles, the weight rides on the A fragment
-        const double* m0 = G + Cfg::oM + 6 * q;
-        const double* m1 = G + Cfg::oM + 6 * (q + 4);
         const int vi[6] = {0, 1, 2, 0, 1, 0}, vj[6] = {0, 1, 2, 1, 2, 2};
 #pragma unroll
         for (int v = 0; v < 6; ++v)
         {
           double t0 = 0.0, t1 = 0.0;
-          const double w0 = m0[v], w1 = m1[v];
+          const double w0 = R0[18 + v], w1 = R1[18 + v];
 #pragma unroll
           for (int J = 0; J < 3; ++J)
           {
-            dmma884(t0, t1, w0 * fg[3 + J][0], fg[3 + J][0]);
-            dmma884(t0, t1, w1 * fg[3 + J][1], fg[3 + J][1]);
+            dmma884(t0, t1, w0 * fn[J][0], fn[J][0]);
+            dmma884(t0, t1, w1 * fn[J][1], fn[J][1]);
           }
           Kb[0][3 * vi[v] + vj[v]] += t0;
           Kb[1][3 * vi[v] + vj[v]] += t1;

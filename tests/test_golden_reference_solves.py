@@ -95,5 +95,6 @@ def test_reference_result_description_cuda(fc, oracle, case):
         assert abs(n1 - n2) <= 1, (h, h2)
         for x, y in zip(h[:min(n1, n2)], h2[:min(n1, n2)]):
             assert abs(x - y) <= 1e-3 * y + floor, (h, h2)
-    assert np.max(np.abs(d - d2)) <= 1e-10 * np.max(np.abs(d2))
+    tol = min(r["tolerance"] for r in p.fx["results"] if r["quantity"].startswith("disp"))
+    assert np.max(np.abs(d - d2)) <= max(1e-10 * np.max(np.abs(d2)), tol)  # CUDA-driven vs oracle-driven solution
     s.close()

@@ -65,6 +65,7 @@ extern "C"
     dev_free(ctx->d_slots);
     dev_free(ctx->d_dbc);
     dev_free(ctx->d_send_lids);
+    dev_free(ctx->d_halo_sendbuf);
     dev_free(ctx->d_stage_u);
     dev_free(ctx->d_stage_f);
     dev_free(ctx->d_stage_K);

@@ -58,6 +58,9 @@ struct fc_ctx
   // halo send plan
   int n_send = 0;
   int* d_send_lids = nullptr;
+  std::vector<int> halo_send_count, halo_recv_count;  // DOFs per peer rank (fc_solid_halo_set_counts)
+  double* d_halo_sendbuf = nullptr;
+  size_t halo_sendbuf_cap = 0;
 
   // scratch + error state
   double* d_stage_u = nullptr;  // staging for host callers

@@ -164,6 +164,14 @@ extern "C"
    * The exchange itself (NCCL grouped send/recv) is issued by the caller between pack and evaluate. */
   int fc_solid_halo_set_send(fc_ctx* ctx, int n_send, const int* send_row_lids);
   int fc_solid_halo_pack(fc_ctx* ctx, const double* u_dev, double* sendbuf_dev);
+  /* The whole forward import inside the library (what Epetra_Import does in set_state, 4C_fem_discretization.cpp:546-551):
+   * send_dof_count[p] DOFs of the send list go to rank p (the list is ordered by peer), recv_dof_count[p] ghost DOFs
+   * arrive from rank p.  fc_solid_halo_exchange packs, then issues one grouped ncclSend/ncclRecv per peer on the
+   * context's stream; rank p's message lands at u_col_dev + n_row_dof + sum_{r<p} recv_dof_count[r].
+   * nccl_comm is the caller's ncclComm_t whose rank ids equal the ranks given to fc_solid_create.  The library
+   * does not link NCCL: the symbols are resolved from the process (or libnccl.so.2) at the first call. */
+  int fc_solid_halo_set_counts(fc_ctx* ctx, const int* send_dof_count, const int* recv_dof_count);
+  int fc_solid_halo_exchange(fc_ctx* ctx, void* nccl_comm, double* u_col_dev);
 
   /* ---- timing helpers (device time of the last evaluate, CUDA events on the ctx stream) ----- */
   int fc_solid_last_kernel_ms(fc_ctx* ctx, float* zero_ms, float* element_ms);

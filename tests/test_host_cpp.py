@@ -57,3 +57,33 @@ def test_host_mirror_matches_ctypes_binding(fc):
     assert abs(float(m.group(2)) - 2 * np.abs(K).sum()) <= 1e-11 * np.abs(K).sum()
     assert abs(float(m.group(3)) - 2 * np.abs(f).sum()) <= 1e-11 * np.abs(f).sum() + 1e-13 * np.abs(K).sum()
     s.close()
+
+
+HALO_EXE = os.path.join(ROOT, "examples", "_build", "halo_example")
+
+
+def build_halo_example():
+    os.makedirs(os.path.dirname(HALO_EXE), exist_ok=True)
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    lib = os.path.join(ROOT, "4c_b200", "lib")
+    cmd = ["g++", "-std=c++17", "-O1", os.path.join(ROOT, "examples", "halo_example.cpp"), "-I" + ROOT, "-I" + cuda + "/include",
+           "-L" + lib, "-lfourc_b200", "-L" + cuda + "/lib64", "-lcudart", "-lnccl", "-lpthread", "-Wl,-rpath," + lib,
+           "-Wl,-rpath," + cuda + "/lib64", "-o", HALO_EXE]
+    subprocess.run(cmd, check=True, capture_output=True, text=True)
+
+
+def test_nccl_halo_example_compiles_and_links():
+    build_halo_example()
+    assert os.path.exists(HALO_EXE)
+
+
+@pytest.mark.gpu
+def test_nccl_halo_exchange_two_gpus():
+    """fc_solid_halo_exchange with a caller-made ncclComm_t (2 ranks = 2 GPUs of one box, one thread per rank):
+    ghosts receive the owners' values bit for bit, both ranks evaluate, the assembled forces are self-equilibrated."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    build_halo_example()
+    r = subprocess.run([HALO_EXE], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "HALO OK" in r.stdout, r.stdout + r.stderr

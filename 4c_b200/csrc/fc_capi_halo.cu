@@ -23,9 +23,12 @@ namespace
     static NcclApi api = []
     {
       NcclApi a;
-      void* h = RTLD_DEFAULT;
-      if (!dlsym(h, "ncclSend")) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
-      if (!h) return a;
+      void* h = RTLD_DEFAULT;  // note: RTLD_DEFAULT is a null handle
+      if (!dlsym(h, "ncclSend"))
+      {
+        h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) return a;
+      }
       a.send = (decltype(a.send))dlsym(h, "ncclSend");
       a.recv = (decltype(a.recv))dlsym(h, "ncclRecv");
       a.group_start = (decltype(a.group_start))dlsym(h, "ncclGroupStart");

@@ -17,6 +17,7 @@ FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
 FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_NO_SLAB_PIPELINE = 1, 2, 4, 8
+FC_STRESS_2PK, FC_STRESS_CAUCHY = 0, 1
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
 NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10}
@@ -25,7 +26,7 @@ EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
     "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_graph", "fc_solid_build_graph",
     "fc_solid_graph_sizes", "fc_solid_set_slab_count", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
-    "fc_solid_error_state", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_elements",
+    "fc_solid_error_state", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_elements",
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack", "fc_solid_halo_set_counts", "fc_solid_halo_exchange",
     "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
@@ -224,6 +225,14 @@ class Solid:
     def evaluate_mass(self, density, M_values, flags=FC_EVAL_ZERO_FIRST):
         """consistent mass (struct_calc_nlnstiffmass) into M_values [nnz], layout of the stiffness graph"""
         self._chk(lib().fc_solid_evaluate_mass(self.h, C.c_double(density), C.c_int(flags), _ptr(M_values)))
+
+    def evaluate_stress(self, u_col, stress_type=1, want_gp=True, want_nodal=True):
+        """struct_calc_stress: (gp_stress [n_ele, ngp, 6], nodal_stress [n_row_nodes, 6]); 0 = 2PK, 1 = Cauchy"""
+        ngp = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4}[self.celltype]
+        gp = np.zeros((self.n_ele, ngp, 6)) if want_gp else None
+        nodal = np.zeros((self.n_row_dof // 3, 6)) if want_nodal else None
+        self._chk(lib().fc_solid_evaluate_stress(self.h, _ptr(u_col), C.c_int(stress_type), _ptr(gp), _ptr(nodal)))
+        return gp, nodal
 
     def evaluate_elements(self, u_col, want_K=True, flags=0):
         nd = 3 * self.nen

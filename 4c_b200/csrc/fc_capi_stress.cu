@@ -1,0 +1,184 @@
+// fc_solid_evaluate_stress: struct_calc_stress post-processing.
+#include <cmath>
+
+#include "fc_host_util.hpp"
+#include "fc_kernels_stress.cuh"
+
+namespace
+{
+  // in-place inverse of a dense n x n matrix (row-major), Gauss-Jordan with partial pivoting
+  bool invert_dense(std::vector<double>& M, int n)
+  {
+    std::vector<double> I((size_t)n * n, 0.0);
+    for (int i = 0; i < n; ++i) I[(size_t)i * n + i] = 1.0;
+    for (int c = 0; c < n; ++c)
+    {
+      int piv = c;
+      for (int r = c + 1; r < n; ++r)
+        if (std::fabs(M[(size_t)r * n + c]) > std::fabs(M[(size_t)piv * n + c])) piv = r;
+      if (M[(size_t)piv * n + c] == 0.0) return false;
+      if (piv != c)
+        for (int k = 0; k < n; ++k)
+        {
+          std::swap(M[(size_t)piv * n + k], M[(size_t)c * n + k]);
+          std::swap(I[(size_t)piv * n + k], I[(size_t)c * n + k]);
+        }
+      const double d = 1.0 / M[(size_t)c * n + c];
+      for (int k = 0; k < n; ++k)
+      {
+        M[(size_t)c * n + k] *= d;
+        I[(size_t)c * n + k] *= d;
+      }
+      for (int r = 0; r < n; ++r)
+        if (r != c)
+        {
+          const double f = M[(size_t)r * n + c];
+          if (f != 0.0)
+            for (int k = 0; k < n; ++k)
+            {
+              M[(size_t)r * n + k] -= f * M[(size_t)c * n + k];
+              I[(size_t)r * n + k] -= f * I[(size_t)c * n + k];
+            }
+        }
+    }
+    M = I;
+    return true;
+  }
+
+  // Gauss points -> nodes: base cell = hex8 / hex27 / tet4 (4C_fem_general_utils_gauss_point_extrapolation.cpp:29-44)
+  template <int CT>
+  bool extrapolation_matrix(std::vector<double>& E)
+  {
+    constexpr int NEN = fc::Cell<CT>::nen, NGP = fc::Cell<CT>::ngp;
+    constexpr int NB = CT == fc::TET10 ? 4 : NEN;  // nodes of the base cell; NB == NGP for all three
+    static_assert(NB == NGP, "square base system");
+    std::vector<double> M((size_t)NGP * NB);
+    auto base_shape = [](const double* xi, double* N)
+    {
+      if (CT == fc::TET10)
+      {
+        N[0] = 1.0 - xi[0] - xi[1] - xi[2];
+        N[1] = xi[0];
+        N[2] = xi[1];
+        N[3] = xi[2];
+      }
+      else
+        fc::shape_function<CT>(xi, N);
+    };
+    for (int g = 0; g < NGP; ++g)
+    {
+      double xi[3], w;
+      fc::gauss_point<CT>(g, xi, &w);
+      base_shape(xi, &M[(size_t)g * NB]);
+    }
+    if (!invert_dense(M, NB)) return false;  // M^-1: [base node][gp]
+    E.assign((size_t)NEN * NGP, 0.0);
+    for (int a = 0; a < NEN; ++a)
+    {
+      double xi[3], Nb[NB > 0 ? NB : 1];
+      fc::node_param_coords(CT, a, xi);
+      if (CT == fc::TET10)
+        base_shape(xi, Nb);
+      else
+        for (int c = 0; c < NB; ++c) Nb[c] = c == a ? 1.0 : 0.0;
+      for (int g = 0; g < NGP; ++g)
+      {
+        double v = 0.0;
+        for (int c = 0; c < NB; ++c) v += Nb[c] * M[(size_t)c * NGP + g];
+        E[(size_t)a * NGP + g] = v;
+      }
+    }
+    return true;
+  }
+
+  template <int CT, int FORM>
+  int stress_impl(fc_ctx* ctx, const fc::EvalArgs& A, int stress_type, double* d_gp, double* d_nodal)
+  {
+    constexpr int NEN = fc::Cell<CT>::nen, NGP = fc::Cell<CT>::ngp;
+    const long long n1 = (long long)ctx->n_ele * NGP;
+    if (n1 > 0)
+    {
+      fc::k_gp_stress<CT, FORM><<<(unsigned)((n1 + 63) / 64), 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      ctx->launches++;
+      FC_CUDA(cudaGetLastError());
+    }
+    if (!d_nodal) return FC_OK;
+    std::vector<double> E;
+    if (!extrapolation_matrix<CT>(E)) return fail(ctx, FC_ERR_INVALID, "singular Gauss point extrapolation matrix");
+    std::vector<int> count((size_t)ctx->n_col_nodes, 0);
+    for (int n : ctx->h_conn) count[n]++;
+    double* d_E = nullptr;
+    int* d_count = nullptr;
+    FC_CUDA(dev_upload(d_E, E.data(), E.size(), ctx->stream));
+    FC_CUDA(dev_upload(d_count, count.data(), count.size(), ctx->stream));
+    FC_CUDA(cudaMemsetAsync(d_nodal, 0, sizeof(double) * 6 * (size_t)ctx->n_row_nodes, ctx->stream));
+    const long long n2 = (long long)ctx->n_ele * NEN;
+    if (n2 > 0)
+    {
+      fc::k_extrapolate_to_nodes<CT><<<(unsigned)((n2 + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, ctx->n_row_nodes, d_E,
+          d_count, d_gp, d_nodal);
+      ctx->launches += 2;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_E);
+    cudaFree(d_count);
+    FC_CUDA(e);
+    return FC_OK;
+  }
+}  // namespace
+
+extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int stress_type, double* gp_stress, double* nodal_stress)
+{
+  if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede evaluate_stress");
+  if (!ctx->have_material) return fail(ctx, FC_ERR_INVALID, "set_material must precede evaluate_stress");
+  if (!u_col || (!gp_stress && !nodal_stress)) return fail(ctx, FC_ERR_INVALID, "u_col and one output are required");
+  if (stress_type != FC_STRESS_2PK && stress_type != FC_STRESS_CAUCHY) return fail(ctx, FC_ERR_UNSUPPORTED, "stress type");
+  FC_CUDA(cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->stream;
+  const int ngp = fc::cell_ngp(ctx->celltype);
+  const size_t n_gp = 6 * (size_t)ctx->n_ele * ngp, n_nod = 6 * (size_t)ctx->n_row_nodes;
+  const bool u_dev = is_device_ptr(u_col), g_dev = gp_stress && is_device_ptr(gp_stress), n_dev = nodal_stress && is_device_ptr(nodal_stress);
+  const double* d_u = u_col;
+  if (!u_dev)
+  {
+    FC_CUDA(ensure_cap(ctx->d_stage_u, ctx->stage_u_cap, (size_t)ctx->n_col_dof));
+    FC_CUDA(cudaMemcpyAsync(ctx->d_stage_u, u_col, sizeof(double) * (size_t)ctx->n_col_dof, cudaMemcpyHostToDevice, s));
+    d_u = ctx->d_stage_u;
+  }
+  double *d_gp = g_dev ? gp_stress : nullptr, *d_nodal = n_dev ? nodal_stress : nullptr;
+  double *tmp_gp = nullptr, *tmp_nodal = nullptr;
+  if (!d_gp)
+  {
+    FC_CUDA(cudaMalloc((void**)&tmp_gp, sizeof(double) * (n_gp ? n_gp : 1)));
+    d_gp = tmp_gp;
+  }
+  if (nodal_stress && !d_nodal)
+  {
+    FC_CUDA(cudaMalloc((void**)&tmp_nodal, sizeof(double) * (n_nod ? n_nod : 1)));
+    d_nodal = tmp_nodal;
+  }
+  fc::EvalArgs A{};
+  A.X = ctx->d_X;
+  A.conn = ctx->d_conn;
+  A.n_ele = ctx->n_ele;
+  A.dNtab = ctx->d_dNtab;
+  A.u = d_u;
+  A.mat = ctx->mat;
+  const bool fbar = ctx->formulation == FC_FORM_FBAR;
+  int rc = FC_ERR_UNSUPPORTED;
+  if (ctx->celltype == FC_HEX8)
+    rc = fbar ? stress_impl<fc::HEX8, fc::FORM_FBAR>(ctx, A, stress_type, d_gp, d_nodal) : stress_impl<fc::HEX8, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
+  else if (ctx->celltype == FC_HEX27)
+    rc = stress_impl<fc::HEX27, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
+  else if (ctx->celltype == FC_TET10)
+    rc = stress_impl<fc::TET10, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
+  if (rc == FC_OK && gp_stress && !g_dev) FC_CUDA(cudaMemcpyAsync(gp_stress, d_gp, sizeof(double) * n_gp, cudaMemcpyDeviceToHost, s));
+  if (rc == FC_OK && nodal_stress && !n_dev) FC_CUDA(cudaMemcpyAsync(nodal_stress, d_nodal, sizeof(double) * n_nod, cudaMemcpyDeviceToHost, s));
+  cudaError_t e = cudaStreamSynchronize(s);
+  if (tmp_gp) cudaFree(tmp_gp);
+  if (tmp_nodal) cudaFree(tmp_nodal);
+  if (rc != FC_OK) return rc;
+  FC_CUDA(e);
+  return FC_OK;
+}

@@ -150,6 +150,19 @@ extern "C"
    * FC_EVAL_ZERO_FIRST.  Constant for a mesh: call once, not per Newton iteration. */
   int fc_solid_evaluate_mass(fc_ctx* ctx, double density, int flags, double* M_values);
 
+  /* struct_calc_stress post-processing: Gauss-point stresses (calculate_stress,
+   * 4C_solid_3D_ele_calc.cpp:347-390; Cauchy = F S F^T / det F, 4C_solid_3D_ele_utils.cpp:20-33) and their extrapolation
+   * to the nodes with nodal averaging (4C_fem_general_utils_gauss_point_extrapolation.cpp:260-320, 418-427).
+   * gp_stress [n_col_ele][ngp][6], nodal_stress [n_row_nodes][6] (host|device, either may be NULL); stress-Voigt
+   * xx,yy,zz,xy,yz,zx.  With several ranks the nodal values of owned nodes are complete (every element at an owned
+   * node is a column element). */
+  enum fc_stress_type
+  {
+    FC_STRESS_2PK = 0,
+    FC_STRESS_CAUCHY = 1
+  };
+  int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int stress_type, double* gp_stress, double* nodal_stress);
+
   /* Element-local evaluation without scatter (Solid::evaluate seam, 4C_solid_3D_ele.hpp:120-124):
    * fe [n_col_ele][3*nen], Ke [n_col_ele][3*nen][3*nen] column-major per element, in the caller's
    * element order.  host|device.  Ke may be NULL. */

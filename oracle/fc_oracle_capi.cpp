@@ -118,6 +118,13 @@ extern "C"
     MaterialParams mp{kind, young, nue};
     return element_evaluate(ct, form, mp, X, u, fe, Ke, Me, rho);
   }
+  // Gauss-point stresses of one element ([ngp][6], stress-Voigt xx,yy,zz,xy,yz,zx); stress_type 0 = 2PK, 1 = Cauchy
+  int oracle_element_gp_stress(int ct, int form, int kind, double young, double nue, const double* X, const double* u,
+      int stress_type, double* gp_stress)
+  {
+    MaterialParams mp{kind, young, nue};
+    return element_evaluate(ct, form, mp, X, u, nullptr, nullptr, nullptr, 0.0, gp_stress, stress_type);
+  }
   // batch of independent elements (X,u: [n][3*nen]); used as the checker for the CUDA
   // element-level entry point.  returns the number of failing elements.
   int oracle_element_evaluate_batch(int ct, int form, int kind, double young, double nue, int n,

@@ -154,9 +154,34 @@ namespace fc_oracle
   // One element.  X,u: node-major [3*a+d] == 3 x NEN col-major.  fe[ND], Ke[ND*ND] col-major,
   // Me optional (consistent mass, density rho).  Outputs are ADDED to (caller zeroes them, like
   // AssembleStrategy::clear_element_storage, 4C_fem_general_assemblestrategy.cpp:74-111).
+  // 2nd Piola-Kirchhoff -> Cauchy, stress-Voigt (xx,yy,zz,xy,yz,zx)      4C_solid_3D_ele_utils.cpp:20-33
+  inline void pk2_to_cauchy(const double* S, const double* F, double* cauchy)
+  {
+    const double Sm[9] = {S[0], S[3], S[5], S[3], S[1], S[4], S[5], S[4], S[2]};  // col-major == row-major (symmetric)
+    double FS[9], cm[9];
+    multiply_nn<3, 3, 3>(FS, F, Sm);
+    const double idet = 1.0 / determinant3x3(F);
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j)
+      {
+        double v = 0.0;
+        for (int k = 0; k < 3; ++k) v += FS[i + 3 * k] * F[j + 3 * k];  // multiply_nt
+        cm[i + 3 * j] = idet * v;
+      }
+    cauchy[0] = cm[0]; cauchy[1] = cm[4]; cauchy[2] = cm[8];
+    cauchy[3] = cm[0 + 3 * 1]; cauchy[4] = cm[1 + 3 * 2]; cauchy[5] = cm[0 + 3 * 2];
+  }
+
+  enum StressType
+  {
+    STRESS_2PK = 0,
+    STRESS_CAUCHY = 1
+  };
+
   template <int NEN, int NGP>
   inline int element_evaluate_t(int ct, int form, const MaterialParams& mp, const double* X,
-      const double* u, double* fe, double* Ke, double* Me, double rho)
+      const double* u, double* fe, double* Ke, double* Me, double rho, double* gp_stress = nullptr,
+      int stress_type = STRESS_CAUCHY)
   {
     constexpr int ND = 3 * NEN;
     double x[ND];
@@ -243,6 +268,14 @@ namespace fc_oracle
 
       double S[6], cmat[36];
       material_evaluate(mp, Fmat, E, S, cmat);
+      if (gp_stress)
+      {
+        // calculate_stress / assemble_stress_type_to_matrix_row: solid_3D_ele_calc.cpp:347-390, calc_lib_io.hpp:167-190
+        if (stress_type == STRESS_CAUCHY)
+          pk2_to_cauchy(S, Fmat, gp_stress + 6 * gp);
+        else
+          for (int v = 0; v < 6; ++v) gp_stress[6 * gp + v] = S[v];
+      }
 
       const double fac_force = form == FORM_FBAR ? integration_factor / fbar_factor : integration_factor;
       // f += fac * B^T S                                               calc_lib.hpp:851-860
@@ -299,16 +332,17 @@ namespace fc_oracle
   }
 
   inline int element_evaluate(int ct, int form, const MaterialParams& mp, const double* X,
-      const double* u, double* fe, double* Ke, double* Me = nullptr, double rho = 0.0)
+      const double* u, double* fe, double* Ke, double* Me = nullptr, double rho = 0.0, double* gp_stress = nullptr,
+      int stress_type = STRESS_CAUCHY)
   {
     switch (ct)
     {
       case HEX8:
-        return element_evaluate_t<8, 8>(ct, form, mp, X, u, fe, Ke, Me, rho);
+        return element_evaluate_t<8, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type);
       case HEX27:
-        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho);
+        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type);
       case TET10:
-        return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho);
+        return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type);
     }
     return -1;
   }

@@ -85,6 +85,27 @@ def element_evaluate(ct, form, kind, young, nue, X, u, want_K=True, want_M=False
     return err, fe, Ke, Me
 
 
+def element_gp_stress(ct, form, kind, young, nue, X, u, stress_type=1):
+    """Gauss-point stresses (ngp, 6) of one element; stress_type 0 = 2nd Piola-Kirchhoff, 1 = Cauchy"""
+    X, u = _d(X), _d(u)
+    out = np.zeros((NGP[ct], 6))
+    err = lib.oracle_element_gp_stress(C.c_int(ct), C.c_int(form), C.c_int(kind), C.c_double(young), C.c_double(nue), _p(X), _p(u),
+                                       C.c_int(stress_type), _p(out))
+    return err, out
+
+
+def gauss_rule(ct):
+    xi, w = np.zeros((NGP[ct], 3)), np.zeros(NGP[ct])
+    lib.oracle_gauss_rule(C.c_int(ct), _p(xi), _p(w))
+    return xi, w
+
+
+def shape(ct, xi):
+    N = np.zeros(NEN[ct])
+    lib.oracle_shape(C.c_int(ct), _p(_d(xi)), _p(N), None)
+    return N
+
+
 def node_param_coords(ct):
     xi = np.zeros((NEN[ct], 3))
     lib.oracle_node_param_coords(C.c_int(ct), _p(xi))

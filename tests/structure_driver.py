@@ -265,3 +265,45 @@ def csr_to_dense(rowptr, colind, vals, n):
         s, e = rowptr[r], rowptr[r + 1]
         A[r, colind[s:e]] = vals[s:e]
     return A
+
+
+def extrapolation_matrix(ct, gauss_xi, shape, xi_nodes):
+    """Gauss points -> nodes (4C_fem_general_utils_gauss_point_extrapolation.cpp:29-44, 90-260, 288-320): invert
+    M = [N^base_i(xi_gp)] of the base cell (hex8/8 gp -> hex8, hex27/27 gp -> hex27, tet10/4 gp -> tet4), then interpolate the
+    remaining nodes with the base cell's shape functions.  shape(ct, xi) -> N of the full cell."""
+    if ct in (0, 1):
+        M = np.array([shape(ct, x) for x in gauss_xi])  # [gp][node]
+        return np.linalg.inv(M)  # [node][gp]
+    tet4 = lambda x: np.array([1.0 - x[0] - x[1] - x[2], x[0], x[1], x[2]])  # noqa: E731
+    M = np.array([tet4(x) for x in gauss_xi])
+    base = np.linalg.inv(M)  # [4][gp]
+    B = np.array([tet4(x) for x in xi_nodes])  # [10][4]
+    return B @ base
+
+
+def nodal_stresses(problem, gp_stress_of_element, E):
+    """assemble_extrapolated_nodal_values with nodal_average = true: every adjacent element adds
+    (E gp_stress)[a] / (number of elements at the node).  gp_stress_of_element(e) -> (ngp, 6)."""
+    p = problem
+    nn = len(p.ids)
+    count = np.zeros(nn)
+    for en in p.conn:
+        count[en] += 1
+    out = np.zeros((nn, 6))
+    for e, en in enumerate(p.conn):
+        out[en] += (E @ gp_stress_of_element(e)) / count[en][:, None]
+    return out
+
+
+STRESS_COMP = {"stress_xx": 0, "stress_yy": 1, "stress_zz": 2, "stress_xy": 3, "stress_yz": 4, "stress_xz": 5}
+
+
+def stress_result_error(problem, nodal):
+    """max (|nodal stress - VALUE| / TOLERANCE) over the stress results of the fixture, and the number compared"""
+    err, n = 0.0, 0
+    for r in problem.fx["results"]:
+        if r["quantity"] in STRESS_COMP:
+            v = nodal[problem.index[r["node"]], STRESS_COMP[r["quantity"]]]
+            err = max(err, abs(v - r["value"]) / r["tolerance"])
+            n += 1
+    return err, n

@@ -98,3 +98,40 @@ def test_reference_result_description_cuda(fc, oracle, case):
     tol = min(r["tolerance"] for r in p.fx["results"] if r["quantity"].startswith("disp"))
     assert np.max(np.abs(d - d2)) <= max(1e-10 * np.max(np.abs(d2)), tol)  # CUDA-driven vs oracle-driven solution
     s.close()
+
+
+STRESS_CASES = ["solid_ele_hex8_Standard_eas_none_stressout", "solid_ele_hex27_Standard_stressout", "solid_ele_tet10_Standard_stressout"]
+
+
+@pytest.mark.parametrize("case", STRESS_CASES)
+def test_reference_nodal_stresses_oracle(oracle, case):
+    """stress_xx ... at nodes (STRUCT_STRESS Cauchy, TOLERANCE 1e-12): Gauss-point Cauchy stresses extrapolated to the
+    nodes and averaged like the reference's post-processing (24 / 54 / 78 values)."""
+    p = sd.Problem(sd.load(case), oracle.node_param_coords)
+    assemble, mass = oracle_backend(oracle, p)
+    d, _ = sd.run(p, assemble, mass)
+    E = sd.extrapolation_matrix(p.ct, oracle.gauss_rule(p.ct)[0], oracle.shape, oracle.node_param_coords(p.ct))
+    U = d.reshape(-1, 3)
+    nodal = sd.nodal_stresses(p, lambda e: oracle.element_gp_stress(p.ct, p.form, p.mat, p.young, p.nue, p.X[p.conn[e]], U[p.conn[e]], 1)[1], E)
+    err, n = sd.stress_result_error(p, nodal)
+    assert n >= 24 and err <= 1.0, (case, err, n)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", STRESS_CASES)
+def test_reference_nodal_stresses_cuda(fc, oracle, case):
+    """the same values from fc_solid_evaluate_stress (device Gauss-point stresses + device extrapolation/averaging);
+    Gauss-point stresses also compared with the oracle's, Cauchy and 2nd Piola-Kirchhoff."""
+    p = sd.Problem(sd.load(case), oracle.node_param_coords)
+    s, assemble, mass = cuda_backend(fc, p)
+    d, _ = sd.run(p, assemble, mass)
+    gp, nodal = s.evaluate_stress(d, fc.FC_STRESS_CAUCHY)
+    err, n = sd.stress_result_error(p, nodal)
+    assert n >= 24 and err <= 1.0, (case, err, n)
+    U = d.reshape(-1, 3)
+    for st in (fc.FC_STRESS_2PK, fc.FC_STRESS_CAUCHY):
+        gp, _ = s.evaluate_stress(d, st, want_nodal=False)
+        for e in range(len(p.conn)):
+            _, ref = oracle.element_gp_stress(p.ct, p.form, p.mat, p.young, p.nue, p.X[p.conn[e]], U[p.conn[e]], st)
+            assert np.max(np.abs(gp[e] - ref)) <= 1e-12 * np.max(np.abs(ref))
+    s.close()

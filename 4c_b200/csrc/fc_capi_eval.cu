@@ -4,6 +4,7 @@
 //                                               sibling with FC_EVAL_CLOSED_FORM_FMA
 //   everything else (and FC_EVAL_FORCE_GENERIC) -> generic B-operator kernel (fc_kernels_generic.cuh)
 #include <climits>
+#include <cstdlib>
 
 #include "fc_host_util.hpp"
 #include "fc_kernels_generic.cuh"
@@ -45,7 +46,14 @@ namespace
       auto kern = A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true> : fc::k_hex8_neohooke_mma<WANT_K, false>;
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
       if (e != cudaSuccess) return e;
-      kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+      size_t smem = Cfg::smem_bytes;
+      if (const char* x = getenv("FC_DEBUG_EXTRA_SMEM"))  // experiments only: lowers the CTAs per SM
+      {
+        smem += (size_t)atoi(x);
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+      }
+      kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, smem, ctx->stream>>>(A, ctx->d_ele_bad);
     }
     ctx->launches++;
     return cudaGetLastError();
@@ -107,6 +115,7 @@ namespace
     A.dbc = ctx->have_dbc ? ctx->d_dbc : nullptr;
     A.err = ctx->d_err;
     A.mat = ctx->mat;
+    if (const char* d = getenv("FC_DEBUG")) A.debug = atoi(d);
     return A;
   }
 

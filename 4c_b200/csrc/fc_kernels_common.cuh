@@ -34,6 +34,7 @@ namespace fc
     double* Ke_out;
     int* err;              // [2]
     MatParams mat;
+    int debug;             // FC_DEBUG env (experiments only): 1 = K reductions predicated off, 2 = no staging, no reductions
   };
 
   // fire-and-forget FP64 add (RED.E.ADD.F64)
@@ -49,7 +50,18 @@ namespace fc
         : "memory");
   }
 
-  // three rows of one node block (row stride in bytes), one predicate, no branches
+  // three rows of one node block (row stride in bytes), unconditional
+  __device__ __forceinline__ void red_add3(double* p0, long long stride_bytes, double v0, double v1, double v2)
+  {
+    asm volatile(
+        "{\n\t.reg .b64 p1, p2;\n\tadd.s64 p1, %0, %1;\n\tadd.s64 p2, p1, %1;\n\t"
+        "red.global.add.f64 [%0], %2;\n\tred.global.add.f64 [p1], %3;\n\tred.global.add.f64 [p2], %4;\n\t}"
+        :
+        : "l"(p0), "l"(stride_bytes), "d"(v0), "d"(v1), "d"(v2)
+        : "memory");
+  }
+
+  // three rows of one node block (row stride in bytes), one predicate (ptxas emits a branch region per reduction)
   __device__ __forceinline__ void red_add3_if(bool pred, double* p0, long long stride_bytes, double v0, double v1, double v2)
   {
     asm volatile(

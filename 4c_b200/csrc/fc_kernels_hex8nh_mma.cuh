@@ -28,7 +28,9 @@ namespace fc
     static constexpr int epw = 4;                       // elements per warp
     static constexpr int epb = warps * epw;             // elements per CTA
     // per element: 6 component planes of 64 (fragment layout), sqrt(kappa)[8], x rel [8][3], pad
-    static constexpr int oSk = 384, oX = 392, ele_doubles = 392 + 24 + 1;
+    // (odd stride 419: the 4 element groups of a warp store their fragments to disjoint banks, and with the parity
+    // shift below the 16-byte coordinate loads of the 4 groups fall into 4 different bank groups)
+    static constexpr int oSk = 384, oX = 392, ele_doubles = 392 + 24 + 3;
     static constexpr int ks_stride = 24;  // K_e staging for the scatter: 12 rows x 24 inside the element's own area
     static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles;
   };
@@ -51,10 +53,11 @@ namespace fc
     using Cfg = Hex8MmaCfg;
     extern __shared__ __align__(16) double smem_mma[];
     double* const smem = smem_mma;
-    __shared__ long long s_rowbase[Cfg::epb][8];
-    __shared__ int s_rowlen[Cfg::epb][8];
+    // scatter record of node t: x = CSR offset of DOF row 3n (bits 0..43) | entries per DOF row (bits 44..59) |
+    // Dirichlet flags of the 3 DOF rows (bits 60..62), all ones = not an owned row; y = slot row (position of
+    // every b in the CSR row of this node)
+    __shared__ ulonglong2 s_info[Cfg::epb][8];
     __shared__ int s_node[Cfg::epb][8];
-    __shared__ unsigned long long s_slots[Cfg::epb][8];  // slot row of node t: position of every b in its CSR row
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int el = lane >> 3, t = lane & 7;   // phase 0/1 role
     const int wel = warp * Cfg::epw;          // first element slot of this warp inside the CTA
@@ -74,23 +77,28 @@ namespace fc
         xr[i] = __ldg(A.u + 3 * (size_t)node + i);
       }
     }
+    unsigned fastmask;  // bit 8k: all 8 nodes of element k are owned rows without Dirichlet flags
     {
       const bool owned = active && node < A.n_row_nodes;
-      long long rb = -1;
-      int rl = 0;
-      unsigned long long sl = 0;
-      if (WANT_K && owned && A.K)
+      ulonglong2 inf = make_ulonglong2(~0ull, 0ull);
+      bool plain = false;
+      if (WANT_K && owned && A.K && !(A.debug & 1))
       {
-        rb = __ldg(A.node_rowbase + node);
-        rl = __ldg(A.node_rowlen + node);
-        sl = __ldg(reinterpret_cast<const unsigned long long*>(A.slots + (size_t)e * 64) + t);
-        if (HAS_DBC)  // Dirichlet flags of the 3 DOF rows ride in the top bits of the row length
-          for (int i = 0; i < 3; ++i) rl |= (A.dbc[3 * node + i] ? 1 : 0) << (28 + i);
+        const unsigned long long rb = (unsigned long long)__ldg(A.node_rowbase + node);
+        const unsigned long long rl = (unsigned long long)__ldg(A.node_rowlen + node);
+        inf.y = __ldg(reinterpret_cast<const unsigned long long*>(A.slots + (size_t)e * 64) + t);
+        unsigned long long fl = 0;
+        if (HAS_DBC)
+          for (int i = 0; i < 3; ++i) fl |= (unsigned long long)(A.dbc[3 * node + i] ? 1 : 0) << (60 + i);
+        inf.x = rb | (rl << 44) | fl;
+        plain = fl == 0;
       }
-      s_rowbase[wel + el][t] = rb;
-      s_rowlen[wel + el][t] = rl;
-      s_slots[wel + el][t] = sl;
+      s_info[wel + el][t] = inf;
       s_node[wel + el][t] = owned ? node : -1;
+      const unsigned pm = __ballot_sync(0xFFFFFFFFu, plain);
+      fastmask = pm & (pm >> 1);
+      fastmask &= fastmask >> 2;
+      fastmask &= fastmask >> 4;
     }
     // coordinates relative to node 0 of the element (sum_a dN_a = 0, so J and F are unchanged)
     for (int i = 0; i < 3; ++i)
@@ -100,27 +108,29 @@ namespace fc
       Xr[i] -= X0;
       xr[i] = Xr[i] + (xr[i] - u0);
     }
-    // phase 1 needs all 8 nodes of the element: exchange through registers (shuffles inside the group)
+    // phase 1 needs all 8 nodes of the element: exchanged through the (not yet written) fragment area of the
+    // element, 48 bytes per node, read back as broadcast 16-byte loads (a register shuffle costs the LSU 1.5
+    // wavefronts per 32-bit half: 40 wavefronts per element instead of 9)
+    double2* const Ec = reinterpret_cast<double2*>(E + ((wel + el) & 1));
+    Ec[3 * t + 0] = make_double2(Xr[0], Xr[1]);
+    Ec[3 * t + 1] = make_double2(Xr[2], xr[0]);
+    Ec[3 * t + 2] = make_double2(xr[1], xr[2]);
+    __syncwarp();
     // ---- phase 1: Gauss point t of element el ----------------------------------------------------
     bool bad = false;
     {
       const double p = 0.57735026918962576451;
-      const double xi0 = (hex_node_pos(t, 0) > 0) ? p : -p;
-      const double xi1 = (hex_node_pos(t, 1) > 0) ? p : -p;
-      const double xi2 = (hex_node_pos(t, 2) > 0) ? p : -p;
+      // Gauss point t sits in the octant of node t: signs (x, y, z) of hex8 node t = (bit0 ^ bit1, bit1, bit2)
+      const double xi0 = ((t ^ (t >> 1)) & 1) ? p : -p;
+      const double xi1 = (t & 2) ? p : -p;
+      const double xi2 = (t & 4) ? p : -p;
       double jm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Jm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
       double dN[24];
 #pragma unroll
       for (int a = 0; a < 8; ++a)
       {
-        const int src = (lane & 24) | a;
-        double xa[3], Xa[3];
-#pragma unroll
-        for (int i = 0; i < 3; ++i)
-        {
-          xa[i] = __shfl_sync(0xFFFFFFFFu, xr[i], src);
-          Xa[i] = __shfl_sync(0xFFFFFFFFu, Xr[i], src);
-        }
+        const double2 c0 = Ec[3 * a], c1 = Ec[3 * a + 1], c2 = Ec[3 * a + 2];
+        const double Xa[3] = {c0.x, c0.y, c1.x}, xa[3] = {c1.y, c2.x, c2.y};
         const double s0 = hex_node_pos(a, 0), s1 = hex_node_pos(a, 1), s2 = hex_node_pos(a, 2);
         const double r = 1.0 + s0 * xi0, s = 1.0 + s1 * xi1, q = 1.0 + s2 * xi2;
         dN[3 * a + 0] = 0.125 * s0 * s * q;
@@ -146,6 +156,7 @@ namespace fc
       const double kappa = lambda * exp(-beta * log(I3));
       bad = active && (!(detJ > 0.0) || !(I3 > 0.0) || !isfinite(kappa) || (ele_bad && ele_bad[e]));
       const double sk = sqrt(kappa), sl = sqrt(lambda);
+      __syncwarp();  // every lane has read the coordinates: the fragment area may be overwritten
       if (active)
       {
 #pragma unroll
@@ -243,7 +254,14 @@ namespace fc
           for (int i = 0; i < 3; ++i)
             for (int j = 0; j < 3; ++j) Ke[(3 * a + i) + 24 * (3 * (b0 + c) + j)] = Kb[c][3 * i + j];
       }
-      if (A.K)
+      if (A.K && (A.debug & 2))
+      {
+        double sum = 0.0;
+        for (int c = 0; c < 2; ++c)
+          for (int i = 0; i < 9; ++i) sum += Kb[c][i];
+        if (sum == 1.2345e300) A.K[0] = sum;
+      }
+      else if (A.K)
       {
         // stage K_e row-major in shared memory, then let 3 adjacent lanes add the 3 contiguous doubles
         // of one CSR node block in ONE instruction: the memory system processes reductions per 32-byte
@@ -253,8 +271,8 @@ namespace fc
         // filled in two halves of 4 row nodes: no extra shared memory, 4 CTAs per SM.
         // (+1 double for odd elements: ele_doubles is odd, the 16-byte staging stores need an even offset)
         double* Ks = smem + (size_t)(wel + k) * Cfg::ele_doubles + ((wel + k) & 1);
-        const int ln = lane < 24 ? lane : 23;  // lanes 24..31 idle in the scatter
-        const int b = ln / 3;
+        const bool fast = (fastmask >> (8 * k)) & 1u;  // warp-uniform
+        const int b = lane / 3, jj = lane - 3 * b;     // scatter role of lanes 0..23: column node b, component jj
 #pragma unroll
         for (int half = 0; half < 2; ++half)
         {
@@ -272,32 +290,42 @@ namespace fc
             }
           }
           __syncwarp();
-          // all row data of the 4 row nodes first (independent broadcast loads), then 12 reductions
-          double v[12];
-          double* ptr[4];
-          int rl[4];
-#pragma unroll
-          for (int r = 0; r < 4; ++r)
+          // ptxas turns every predicated reduction into its own branch region (BSSY/BRA/REDG/BSYNC), so the lanes
+          // that scatter sit inside ONE divergent region per half and the reductions of an element whose 8 nodes
+          // are all owned rows without Dirichlet flags (the common case) carry no predicate at all
+          if (lane < 24)
           {
-            const int aa = 4 * half + r;
-            const long long rb = s_rowbase[wel + k][aa];
-            const int slot = (int)((s_slots[wel + k][aa] >> (8 * b)) & 0xFF);
-            rl[r] = s_rowlen[wel + k][aa];
-            ptr[r] = (rb >= 0 && lane < 24) ? A.K + rb + 3 * slot + (ln - 3 * b) : nullptr;
+            double v[12];
+            ulonglong2 inf[4];
 #pragma unroll
-            for (int i = 0; i < 3; ++i) v[3 * r + i] = Ks[(3 * r + i) * Cfg::ks_stride + ln];
-          }
+            for (int r = 0; r < 4; ++r)
+            {
+              inf[r] = s_info[wel + k][4 * half + r];
 #pragma unroll
-          for (int r = 0; r < 4; ++r)
-          {
-            if (HAS_DBC)
+              for (int i = 0; i < 3; ++i) v[3 * r + i] = Ks[(3 * r + i) * Cfg::ks_stride + lane];
+            }
+            if (fast)
             {
 #pragma unroll
-              for (int i = 0; i < 3; ++i)
-                red_add_if(ptr[r] != nullptr && !((rl[r] >> (28 + i)) & 1), ptr[r] + (long long)i * (rl[r] & 0x0FFFFFFF), v[3 * r + i]);
+              for (int r = 0; r < 4; ++r)
+              {
+                const long long off = (long long)(inf[r].x & 0xFFFFFFFFFFFull) + 3 * (int)((inf[r].y >> (8 * b)) & 0xFF) + jj;
+                red_add3(A.K + off, (long long)((inf[r].x >> 44) & 0xFFFF) * 8, v[3 * r], v[3 * r + 1], v[3 * r + 2]);
+              }
             }
             else
-              red_add3_if(ptr[r] != nullptr, ptr[r], 8ll * rl[r], v[3 * r], v[3 * r + 1], v[3 * r + 2]);
+            {
+#pragma unroll
+              for (int r = 0; r < 4; ++r)
+              {
+                if ((long long)inf[r].x < 0) continue;  // not an owned row (warp-uniform)
+                const long long off = (long long)(inf[r].x & 0xFFFFFFFFFFFull) + 3 * (int)((inf[r].y >> (8 * b)) & 0xFF) + jj;
+                const long long rl = (long long)((inf[r].x >> 44) & 0xFFFF);
+#pragma unroll
+                for (int i = 0; i < 3; ++i)
+                  if (!((inf[r].x >> (60 + i)) & 1)) red_add(A.K + off + i * rl, v[3 * r + i]);
+              }
+            }
           }
         }
       }

@@ -60,6 +60,7 @@ extern "C"
     dev_free(ctx->d_dNtab);
     dev_free(ctx->d_gpw);
     dev_free(ctx->d_ele_bad);
+    dev_free(ctx->d_geom);
     dev_free(ctx->d_node_rowbase);
     dev_free(ctx->d_node_rowlen);
     dev_free(ctx->d_slots);
@@ -142,6 +143,7 @@ extern "C"
     FC_CUDA(dev_upload(ctx->d_dNtab, dN.data(), dN.size(), ctx->stream));
     FC_CUDA(dev_upload(ctx->d_gpw, w.data(), w.size(), ctx->stream));
     dev_free(ctx->d_ele_bad);
+    dev_free(ctx->d_geom);
     ctx->geom_bad_count = 0;
     ctx->geom_first_bad_gid = -1;
     if (n_col_ele > 0)

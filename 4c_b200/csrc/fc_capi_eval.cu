@@ -43,6 +43,15 @@ namespace
     else
     {
       using Cfg = fc::Hex8MmaCfg;
+      if (!ctx->d_geom)  // geometry cache: once per mesh
+      {
+        cudaError_t eg = cudaMalloc((void**)&ctx->d_geom, sizeof(double) * Cfg::geom_doubles * (size_t)ctx->n_ele);
+        if (eg != cudaSuccess) return eg;
+        fc::k_hex8_geom_cache<<<ctx->n_ele, 64, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->n_ele, ctx->d_geom);
+        ctx->launches++;
+      }
+      fc::EvalArgs Ag = A;
+      Ag.geom = ctx->d_geom;
       auto kern = A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true> : fc::k_hex8_neohooke_mma<WANT_K, false>;
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
       if (e != cudaSuccess) return e;
@@ -53,7 +62,7 @@ namespace
         e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
       }
-      kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, smem, ctx->stream>>>(A, ctx->d_ele_bad);
+      kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, smem, ctx->stream>>>(Ag, ctx->d_ele_bad);
     }
     ctx->launches++;
     return cudaGetLastError();

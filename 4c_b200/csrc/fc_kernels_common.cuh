@@ -27,6 +27,7 @@ namespace fc
     const int* node_rowlen;       // [n_col_nodes]
     const unsigned char* slots;   // [n_ele][nen][nen]
     const unsigned char* dbc;     // [n_row_dof] or nullptr
+    const double* geom;           // hex8 geometry cache [n_ele][72] (k_hex8_geom_cache) or nullptr
     // outputs
     double* f;             // [n_row_dof] or nullptr
     double* K;             // [nnz] or nullptr

@@ -14,8 +14,14 @@
 // Work decomposition: a warp owns 4 elements.
 //   phase 0  lane (el, t) gathers node t of element el (coordinates relative to node 0)
 //   phase 1  lane (el, g) evaluates Gauss point g of element el -> ghat, nhat in fragment layout (smem)
-//   phase 2  for each of the 4 elements: 12 fragment loads, 24 DMMA (6 for the force-only action)
+//   phase 2  for each of the 4 elements: 6 fragment loads, 18 DMMA (none for the force-only action)
 //   phase 3  epilogue + fire-and-forget FP64 reductions into the CSR rows / residual
+//
+// Geometry cache: s[a][b] / (2c) = sum_gp w detJ grad N_a . grad N_b and detJ at the Gauss points depend on the
+// reference coordinates only.  The reference recomputes them in every Newton iteration
+// (4C_solid_3D_ele_calc_lib.hpp:435-448); here k_hex8_geom_cache stores them once per mesh (72 doubles per element,
+// in the accumulator layout of phase 2) and the evaluation reads them back: 6 DMMA, the material Jacobian, its
+// inverse, three fragment planes and 42 % of the shared memory per element less.
 #pragma once
 #include "fc_kernels_common.cuh"
 
@@ -27,10 +33,12 @@ namespace fc
     static constexpr int threads = 32 * warps;
     static constexpr int epw = 4;                       // elements per warp
     static constexpr int epb = warps * epw;             // elements per CTA
-    // per element: 6 component planes of 64 (fragment layout), sqrt(kappa)[8], x rel [8][3], pad
-    // (odd stride 419: the 4 element groups of a warp store their fragments to disjoint banks, and with the parity
+    // per element: 3 component planes of 64 (fragment layout), sqrt(kappa)[8], x rel [8][3]; the K_e staging of the
+    // scatter (12 rows x 24) overlays the element's area and sets its size
+    // (odd stride 291: the 4 element groups of a warp store their fragments to disjoint banks, and with the parity
     // shift below the 16-byte coordinate loads of the 4 groups fall into 4 different bank groups)
-    static constexpr int oSk = 384, oX = 392, ele_doubles = 392 + 24 + 3;
+    static constexpr int oSk = 192, oX = 200, ele_doubles = 12 * 24 + 3;
+    static constexpr int geom_doubles = 72;  // geometry cache per element: G[8][8], detJ[8]
     static constexpr int ks_stride = 24;  // K_e staging for the scatter: 12 rows x 24 inside the element's own area
     static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles;
   };
@@ -48,7 +56,7 @@ namespace fc
   __device__ __forceinline__ int frag_idx(int gp, int node) { return 32 * (gp >> 2) + 16 * (node >> 2) + 4 * (gp & 3) + ((node & 3) ^ (2 * (gp >> 2))); }
 
   template <bool WANT_K, bool HAS_DBC>
-  __global__ void __launch_bounds__(Hex8MmaCfg::threads) k_hex8_neohooke_mma(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
+  __global__ void __launch_bounds__(Hex8MmaCfg::threads, 5) k_hex8_neohooke_mma(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
   {
     using Cfg = Hex8MmaCfg;
     extern __shared__ __align__(16) double smem_mma[];
@@ -109,12 +117,11 @@ namespace fc
       xr[i] = Xr[i] + (xr[i] - u0);
     }
     // phase 1 needs all 8 nodes of the element: exchanged through the (not yet written) fragment area of the
-    // element, 48 bytes per node, read back as broadcast 16-byte loads (a register shuffle costs the LSU 1.5
+    // element, 32 bytes per node (current coordinates only), read back as broadcast 16-byte loads (a register shuffle costs the LSU 1.5
     // wavefronts per 32-bit half: 40 wavefronts per element instead of 9)
     double2* const Ec = reinterpret_cast<double2*>(E + ((wel + el) & 1));
-    Ec[3 * t + 0] = make_double2(Xr[0], Xr[1]);
-    Ec[3 * t + 1] = make_double2(Xr[2], xr[0]);
-    Ec[3 * t + 2] = make_double2(xr[1], xr[2]);
+    Ec[2 * t + 0] = make_double2(xr[0], xr[1]);
+    Ec[2 * t + 1] = make_double2(xr[2], 0.0);
     __syncwarp();
     // ---- phase 1: Gauss point t of element el ----------------------------------------------------
     bool bad = false;
@@ -124,13 +131,14 @@ namespace fc
       const double xi0 = ((t ^ (t >> 1)) & 1) ? p : -p;
       const double xi1 = (t & 2) ? p : -p;
       const double xi2 = (t & 4) ? p : -p;
-      double jm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Jm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      const double detJ = active ? __ldg(A.geom + (size_t)e * Cfg::geom_doubles + 64 + t) : 1.0;
+      double jm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
       double dN[24];
 #pragma unroll
       for (int a = 0; a < 8; ++a)
       {
-        const double2 c0 = Ec[3 * a], c1 = Ec[3 * a + 1], c2 = Ec[3 * a + 2];
-        const double Xa[3] = {c0.x, c0.y, c1.x}, xa[3] = {c1.y, c2.x, c2.y};
+        const double2 c0 = Ec[2 * a], c1 = Ec[2 * a + 1];
+        const double xa[3] = {c0.x, c0.y, c1.x};
         const double s0 = hex_node_pos(a, 0), s1 = hex_node_pos(a, 1), s2 = hex_node_pos(a, 2);
         const double r = 1.0 + s0 * xi0, s = 1.0 + s1 * xi1, q = 1.0 + s2 * xi2;
         dN[3 * a + 0] = 0.125 * s0 * s * q;
@@ -140,14 +148,10 @@ namespace fc
         for (int d = 0; d < 3; ++d)
 #pragma unroll
           for (int i = 0; i < 3; ++i)
-          {
             jm[3 * d + i] += dN[3 * a + d] * xa[i];
-            Jm[3 * d + i] += dN[3 * a + d] * Xa[i];
-          }
       }
-      double ji[9], Ji[9];
+      double ji[9];
       const double detj = inv3(jm, ji);
-      const double detJ = inv3(Jm, Ji);
       const double detF = detj / detJ;
       const double I3 = detF * detF;
       const double c2 = A.mat.young / (2.0 * (1.0 + A.mat.nue));  // 2c
@@ -155,7 +159,7 @@ namespace fc
       const double lambda = detJ * c2;  // Gauss weight of hex_8point is 1
       const double kappa = lambda * exp(-beta * log(I3));
       bad = active && (!(detJ > 0.0) || !(I3 > 0.0) || !isfinite(kappa) || (ele_bad && ele_bad[e]));
-      const double sk = sqrt(kappa), sl = sqrt(lambda);
+      const double sk = sqrt(kappa);
       __syncwarp();  // every lane has read the coordinates: the fragment area may be overwritten
       if (active)
       {
@@ -167,9 +171,6 @@ namespace fc
           E[0 * 64 + ix] = sk * (ji[0] * d0 + ji[1] * d1 + ji[2] * d2);
           E[1 * 64 + ix] = sk * (ji[3] * d0 + ji[4] * d1 + ji[5] * d2);
           E[2 * 64 + ix] = sk * (ji[6] * d0 + ji[7] * d1 + ji[8] * d2);
-          E[3 * 64 + ix] = sl * (Ji[0] * d0 + Ji[1] * d1 + Ji[2] * d2);
-          E[4 * 64 + ix] = sl * (Ji[3] * d0 + Ji[4] * d1 + Ji[5] * d2);
-          E[5 * 64 + ix] = sl * (Ji[6] * d0 + Ji[7] * d1 + Ji[8] * d2);
         }
         E[Cfg::oSk + t] = sk;
         for (int i = 0; i < 3; ++i) E[Cfg::oX + 3 * t + i] = xr[i];
@@ -183,29 +184,30 @@ namespace fc
     // ---- phase 2 + 3: one element at a time, whole warp ------------------------------------------
     const int a = lane >> 2, q = lane & 3, b0 = 2 * q;
     const double beta2 = 2.0 * A.mat.nue / (1.0 - 2.0 * A.mat.nue);
+    const double c2 = A.mat.young / (2.0 * (1.0 + A.mat.nue));  // 2c
+    // cached geometric part of s[a][2q], s[a][2q+1], one element ahead of its use
+    auto load_sg = [&](int k) -> double2 {
+      const int ek = A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
+      return (k < Cfg::epw && ek < A.n_ele) ? __ldg(reinterpret_cast<const double2*>(A.geom + (size_t)ek * Cfg::geom_doubles) + lane) : make_double2(0.0, 0.0);
+    };
+    double2 sg_next = load_sg(0);
 #pragma unroll 1
     for (int k = 0; k < Cfg::epw; ++k)
     {
+      const double2 sg = sg_next;
+      sg_next = load_sg(k + 1);
       if (!((actmask >> (8 * k)) & 1u) || ((badmask >> (8 * k)) & 0xFFu)) continue;  // warp-uniform
       const int ek = A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
       const double* G = smem + (size_t)(wel + k) * Cfg::ele_doubles;
       const int fo0 = frag_idx(q, a), fo1 = frag_idx(q + 4, a);
-      double fg[6][2];
+      double fg[3][2];
 #pragma unroll
-      for (int c = 0; c < 6; ++c)
+      for (int c = 0; c < 3; ++c)
       {
         fg[c][0] = G[c * 64 + fo0];
         fg[c][1] = G[c * 64 + fo1];
       }
-      // three independent accumulator pairs (short dependency chains), summed afterwards
-      double sa[3][2] = {{0.0, 0.0}, {0.0, 0.0}, {0.0, 0.0}};
-#pragma unroll
-      for (int i = 0; i < 3; ++i)
-      {
-        dmma884(sa[i][0], sa[i][1], fg[3 + i][0], fg[3 + i][0]);
-        dmma884(sa[i][0], sa[i][1], fg[3 + i][1], fg[3 + i][1]);
-      }
-      const double s0 = sa[0][0] + sa[1][0] + sa[2][0], s1 = sa[0][1] + sa[1][1] + sa[2][1];
+      const double s0 = c2 * sg.x, s1 = c2 * sg.y;
       // internal force: lanes of the same row node a reduce over their column pairs / Gauss points
       {
         const double* xk = G + Cfg::oX;

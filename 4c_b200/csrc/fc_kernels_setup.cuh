@@ -32,6 +32,49 @@ namespace fc
     if (bad) report_error(err, ele_gid[e]);
   }
 
+  // Geometry cache of the hex8 closed-form tensor-core kernel (fc_kernels_hex8nh_mma.cuh): per element
+  //   geom[0..63]  G[a][b] = sum_gp w detJ grad N_a . grad N_b   (hex_8point, w = 1; row-major = accumulator layout)
+  //   geom[64..71] detJ at the 8 Gauss points
+  // evaluate_jacobian_mapping (4C_solid_3D_ele_calc_lib.hpp:435-448) on the reference coordinates: constant for a
+  // mesh, computed once.  One block of 64 threads per element.
+  static __global__ void k_hex8_geom_cache(const double* __restrict__ X, const int* __restrict__ conn, int n_ele, double* __restrict__ geom)
+  {
+    __shared__ double sX[8][3];
+    __shared__ double sN[8][8][3];  // [gp][a] sqrt(detJ) grad N_a
+    const int e = blockIdx.x, tid = threadIdx.x;
+    if (e >= n_ele) return;
+    if (tid < 24)
+    {
+      const int a = tid / 3, i = tid % 3;
+      const int n = conn[(size_t)e * 8 + a], n0 = conn[(size_t)e * 8];
+      sX[a][i] = X[3 * (size_t)n + i] - X[3 * (size_t)n0 + i];
+    }
+    __syncthreads();
+    if (tid < 8)
+    {
+      const double p = 0.57735026918962576451;
+      const double xi[3] = {hex_node_pos(tid, 0) > 0 ? p : -p, hex_node_pos(tid, 1) > 0 ? p : -p, hex_node_pos(tid, 2) > 0 ? p : -p};
+      double dN[24], J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Ji[9];
+      shape_deriv1<HEX8>(xi, dN);
+      for (int a = 0; a < 8; ++a)
+        for (int d = 0; d < 3; ++d)
+          for (int i = 0; i < 3; ++i) J[3 * d + i] += dN[3 * a + d] * sX[a][i];
+      const double detJ = inv3(J, Ji);
+      const double sd = sqrt(detJ > 0.0 ? detJ : 0.0);
+      for (int a = 0; a < 8; ++a)
+        for (int d = 0; d < 3; ++d) sN[tid][a][d] = sd * (Ji[3 * d] * dN[3 * a] + Ji[3 * d + 1] * dN[3 * a + 1] + Ji[3 * d + 2] * dN[3 * a + 2]);
+      geom[(size_t)e * 72 + 64 + tid] = detJ;
+    }
+    __syncthreads();
+    {
+      const int a = tid >> 3, b = tid & 7;
+      double g = 0.0;
+      for (int gp = 0; gp < 8; ++gp)
+        for (int d = 0; d < 3; ++d) g += sN[gp][a][d] * sN[gp][b][d];
+      geom[(size_t)e * 72 + tid] = g;
+    }
+  }
+
   // slots[e][a][b] = position of column node conn[e][b] in the (ascending) neighbour list of row
   // node conn[e][a]; 0xFF where a is not owned.  Replaces the per-element lower_bound searches of
   // SparseMatrix::assemble (src/core/linalg/src/sparse/4C_linalg_sparsematrix.cpp:512-543) by a

@@ -16,7 +16,7 @@ FC_HEX8, FC_HEX27, FC_TET10 = 0, 1, 2
 FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
-FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_NO_SLAB_PIPELINE = 1, 2, 4, 8
+FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_NO_SLAB_PIPELINE, FC_EVAL_TILE = 1, 2, 4, 8, 16
 FC_STRESS_2PK, FC_STRESS_CAUCHY = 0, 1
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
@@ -31,6 +31,7 @@ EXPORTS = [
     "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
     "fc_grid_halo_counts", "fc_grid_halo_send_nodes", "fc_probe_fp64_fma", "fc_probe_fp64_mma",
+    "fc_tile_plan_create", "fc_tile_plan_sizes", "fc_tile_plan_get", "fc_tile_plan_destroy",
 ]
 
 
@@ -92,6 +93,30 @@ def probe_fp64(device=0):
         if rc != 0:
             raise FourCError(rc, "fp64 probe")
     return a.value, b.value
+
+
+def tile_plan(X, conn, n_row_nodes, nodeptr, nodeadj):
+    """hex8 tile plan as plain arrays (fc_tile_plan_*; host integer code, no device needed): dict with n_tiles,
+    max_blocks, tile_ele [n_tiles,16], tile_blk [n_tiles,16,32], tile_ptr, rec, rownode; None if the mesh has no plan"""
+    L = lib()
+    X, conn = _f64(X), _i32(conn)
+    nodeptr, nodeadj = np.ascontiguousarray(nodeptr, dtype=np.int64), _i32(nodeadj)
+    h = C.c_void_p()
+    rc = L.fc_tile_plan_create(C.c_int(X.size // 3), _ptr(X), C.c_int(conn.size // 8), _ptr(conn), C.c_int(n_row_nodes),
+                               _ptr(nodeptr), _ptr(nodeadj), C.byref(h))
+    if rc == FC_ERR_GRAPH:
+        return None
+    if rc != 0:
+        raise FourCError(rc, "fc_tile_plan_create")
+    nt, nb, mb = C.c_int(), C.c_int64(), C.c_int()
+    L.fc_tile_plan_sizes(h, C.byref(nt), C.byref(nb), C.byref(mb))
+    out = dict(n_tiles=nt.value, max_blocks=mb.value,
+               tile_ele=np.zeros((nt.value, 16), np.int32), tile_blk=np.zeros((nt.value, 16, 32), np.uint32),
+               tile_ptr=np.zeros(nt.value + 1, np.int64), rec=np.zeros(nb.value, np.uint64), rownode=np.zeros(nb.value, np.int32))
+    L.fc_tile_plan_get(h, _ptr(out["tile_ele"]), _ptr(out["tile_blk"]), _ptr(out["tile_ptr"]), _ptr(out["rec"]), _ptr(out["rownode"]))
+    L.fc_tile_plan_destroy.restype = None
+    L.fc_tile_plan_destroy(h)
+    return out
 
 
 class Grid:

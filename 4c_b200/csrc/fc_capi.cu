@@ -64,6 +64,11 @@ extern "C"
     dev_free(ctx->d_node_rowbase);
     dev_free(ctx->d_node_rowlen);
     dev_free(ctx->d_slots);
+    dev_free(ctx->d_tile_ele);
+    dev_free(ctx->d_tile_blk);
+    dev_free(ctx->d_tile_ptr);
+    dev_free(ctx->d_tile_rec);
+    dev_free(ctx->d_tile_rownode);
     dev_free(ctx->d_dbc);
     dev_free(ctx->d_send_lids);
     dev_free(ctx->d_halo_sendbuf);
@@ -144,6 +149,8 @@ extern "C"
     FC_CUDA(dev_upload(ctx->d_gpw, w.data(), w.size(), ctx->stream));
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
+    ctx->n_tiles = 0;  // the tile plan belongs to the graph of the previous mesh
+    ctx->tile_plan_tried = false;
     ctx->geom_bad_count = 0;
     ctx->geom_first_bad_gid = -1;
     if (n_col_ele > 0)

@@ -10,9 +10,12 @@
 #include "fc_kernels_generic.cuh"
 #include "fc_kernels_hex8nh.cuh"
 #include "fc_kernels_hex8nh_mma.cuh"
+#include "fc_kernels_hex8nh_tile.cuh"
 #include "fc_kernels_hex8_mma_ext.cuh"
 #include "fc_kernels_nh_mma_gen.cuh"
 #include "fc_kernels_setup.cuh"
+
+int fc_build_tile_plan(fc_ctx* ctx);  // fc_capi_graph.cu
 
 namespace
 {
@@ -30,7 +33,7 @@ namespace
   }
 
   template <bool WANT_K>
-  cudaError_t launch_hex8nh(fc_ctx* ctx, const fc::EvalArgs& A, bool fma_variant)
+  cudaError_t launch_hex8nh(fc_ctx* ctx, const fc::EvalArgs& A, bool fma_variant, bool allow_tile)
   {
     if (fma_variant)
     {
@@ -52,6 +55,20 @@ namespace
       }
       fc::EvalArgs Ag = A;
       Ag.geom = ctx->d_geom;
+      // assembled stiffness of the whole mesh: tile kernel (element matrices of a 16-element tile pre-reduced in smem)
+      if (WANT_K && allow_tile && A.K && !A.Ke_out && !A.fe_out && A.ele_offset == 0 && A.n_ele == ctx->n_ele && fc_build_tile_plan(ctx) == FC_OK &&
+          ctx->n_tiles > 0)
+      {
+        using TCfg = fc::Hex8TileCfg;
+        fc::TilePlanDev P{ctx->d_tile_ele, ctx->d_tile_blk, ctx->d_tile_ptr, ctx->d_tile_rec, 0, ctx->n_tiles};
+        auto tkern = A.dbc ? fc::k_hex8_nh_tile<true> : fc::k_hex8_nh_tile<false>;
+        const size_t tsmem = TCfg::smem_bytes(ctx->tile_max_blocks);
+        cudaError_t e = cudaFuncSetAttribute(tkern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
+        if (e != cudaSuccess) return e;
+        tkern<<<ctx->n_tiles, TCfg::threads, tsmem, ctx->stream>>>(Ag, P, ctx->d_ele_bad);
+        ctx->launches++;
+        return cudaGetLastError();
+      }
       auto kern = A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true> : fc::k_hex8_neohooke_mma<WANT_K, false>;
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
       if (e != cudaSuccess) return e;
@@ -97,7 +114,7 @@ namespace
   {
     const bool fbar = ctx->formulation == FC_FORM_FBAR;
     if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC))
-      return launch_hex8nh<WANT_K>(ctx, A, (flags & FC_EVAL_CLOSED_FORM_FMA) != 0);
+      return launch_hex8nh<WANT_K>(ctx, A, (flags & FC_EVAL_CLOSED_FORM_FMA) != 0, (flags & FC_EVAL_TILE) != 0);
     if (ctx->celltype == FC_HEX8 && fbar && ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC))
       return launch_hex8_ext<fc::VAR_NH_FBAR, WANT_K>(ctx, A);
     if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_SVK && !(flags & FC_EVAL_FORCE_GENERIC))

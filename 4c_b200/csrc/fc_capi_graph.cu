@@ -8,10 +8,13 @@
 // and the scatter positions are precomputed on the device.
 #include <algorithm>
 #include <climits>
+#include <cstdlib>
 #include <thread>
 
 #include "fc_host_util.hpp"
+#include "fc_kernels_hex8nh_tile.cuh"
 #include "fc_kernels_setup.cuh"
+#include "fc_tile_plan.hpp"
 
 namespace
 {
@@ -98,6 +101,53 @@ namespace
     }
   }
 
+  void free_tile_plan(fc_ctx* ctx)
+  {
+    dev_free(ctx->d_tile_ele);
+    dev_free(ctx->d_tile_blk);
+    dev_free(ctx->d_tile_ptr);
+    dev_free(ctx->d_tile_rec);
+    dev_free(ctx->d_tile_rownode);
+    ctx->n_tiles = 0;
+    ctx->tile_max_blocks = 0;
+    ctx->n_tile_blocks = 0;
+    ctx->tile_plan_tried = false;
+  }
+
+  // hex8: group the elements into tiles and precompute the tile blocks (fc_tile_plan.hpp); a mesh without a plan
+  // (an element lists a node twice) keeps the per-element scatter
+  int build_tile_plan(fc_ctx* ctx)
+  {
+    if (ctx->tile_plan_tried) return FC_OK;
+    ctx->tile_plan_tried = true;
+    if (ctx->celltype != FC_HEX8 || ctx->n_ele == 0 || ctx->n_row_nodes == 0 || getenv("FC_NO_TILE_PLAN")) return FC_OK;
+    std::vector<double> X((size_t)3 * ctx->n_col_nodes);
+    FC_CUDA(cudaMemcpyAsync(X.data(), ctx->d_X, sizeof(double) * X.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    fc_host::TilePlanHost plan;
+    if (!fc_host::build_tile_plan_host(ctx->n_col_nodes, X.data(), ctx->n_ele, ctx->h_conn.data(), ctx->n_row_nodes, ctx->h_nodeptr.data(),
+            ctx->h_nodeadj.data(), plan))
+      return FC_OK;
+    static_assert(sizeof(long long) == sizeof(int64_t), "");
+    FC_CUDA(dev_upload(ctx->d_tile_ele, plan.tile_ele.data(), plan.tile_ele.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_tile_blk, plan.tile_blk.data(), plan.tile_blk.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_tile_ptr, plan.tile_ptr.data(), plan.tile_ptr.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_tile_rec, plan.rec.data(), plan.rec.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_tile_rownode, plan.rownode.data(), plan.rownode.size(), ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->n_tiles = plan.n_tiles;
+    ctx->tile_max_blocks = plan.max_blocks;
+    ctx->n_tile_blocks = (long long)plan.rec.size();
+    if (ctx->have_dbc)
+    {
+      const int bs = 256;
+      fc::k_tile_set_dbc<<<(unsigned)((ctx->n_tile_blocks + bs - 1) / bs), bs, 0, ctx->stream>>>(ctx->d_tile_rec, ctx->d_tile_rownode, ctx->n_tile_blocks, ctx->d_dbc);
+      ctx->launches++;
+      FC_CUDA(cudaGetLastError());
+    }
+    return FC_OK;
+  }
+
   int finalize_graph(fc_ctx* ctx)
   {
     const int nrow = ctx->n_row_nodes, ncol = ctx->n_col_nodes;
@@ -149,11 +199,14 @@ namespace
     dev_free(ctx->d_dbc);
     ctx->have_dbc = false;
     if (bad > 0) return fail(ctx, FC_ERR_GRAPH, "elements couple DOFs that are missing from the CSR graph");
+    free_tile_plan(ctx);  // built by the first FC_EVAL_TILE evaluation (fc_build_tile_plan)
     compute_slab_plan(ctx, 1);  // measured: overlapping the zero-fill with the kernel gains nothing, so one slab
     ctx->have_graph = true;
     return FC_OK;
   }
 }  // namespace
+
+int fc_build_tile_plan(fc_ctx* ctx) { return build_tile_plan(ctx); }
 
 extern "C"
 {
@@ -238,7 +291,20 @@ extern "C"
     FC_CUDA(cudaSetDevice(ctx->device));
     dev_free(ctx->d_dbc);
     ctx->have_dbc = false;
-    if (n == 0) return FC_OK;
+    auto refresh_tile_flags = [&]() -> cudaError_t {
+      if (ctx->n_tile_blocks == 0) return cudaSuccess;
+      const int bs = 256;
+      fc::k_tile_set_dbc<<<(unsigned)((ctx->n_tile_blocks + bs - 1) / bs), bs, 0, ctx->stream>>>(
+          ctx->d_tile_rec, ctx->d_tile_rownode, ctx->n_tile_blocks, ctx->d_dbc);
+      ctx->launches++;
+      return cudaGetLastError();
+    };
+    if (n == 0)
+    {
+      FC_CUDA(refresh_tile_flags());
+      FC_CUDA(cudaStreamSynchronize(ctx->stream));
+      return FC_OK;
+    }
     std::vector<unsigned char> flags((size_t)ctx->n_row_dof, 0);
     for (int i = 0; i < n; ++i)
     {
@@ -246,6 +312,7 @@ extern "C"
       flags[row_lids[i]] = 1;
     }
     FC_CUDA(dev_upload(ctx->d_dbc, flags.data(), flags.size(), ctx->stream));
+    FC_CUDA(refresh_tile_flags());
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->have_dbc = true;
     return FC_OK;

@@ -45,6 +45,16 @@ struct fc_ctx
   unsigned char* d_dbc = nullptr;     // [n_row_dof] 1 = row skipped by the matrix scatter
   bool have_dbc = false;
 
+  // hex8 tile plan (fc_tile_plan.hpp): built by the first FC_EVAL_TILE evaluation; n_tiles == 0 = no plan, per-element scatter
+  int n_tiles = 0, tile_max_blocks = 0;
+  bool tile_plan_tried = false;
+  long long n_tile_blocks = 0;
+  int* d_tile_ele = nullptr;                 // [n_tiles][16]
+  unsigned* d_tile_blk = nullptr;            // [n_tiles][16][32]
+  long long* d_tile_ptr = nullptr;           // [n_tiles + 1]
+  unsigned long long* d_tile_rec = nullptr;  // [n_tile_blocks]
+  int* d_tile_rownode = nullptr;             // [n_tile_blocks]
+
   // slab pipeline for FC_EVAL_ZERO_FIRST: slab k = elements [slab_ele_end[k-1], slab_ele_end[k]); before it runs,
   // the CSR range [slab_off_end[k-1], slab_off_end[k]) (rows first touched by this slab) is zeroed on a second
   // stream while slab k-1 computes

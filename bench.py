@@ -152,6 +152,12 @@ def run_reference(args):
     }))
 
 
+# dominant kernel per --kernel-flags and its dram__bytes_read.sum + dram__bytes_write.sum per launch at C2 from the committed
+# ncu captures (profiles/)
+KERNEL_NAME = {0: "k_hex8_neohooke_mma<true,false>", 16: "k_hex8_nh_tile<false>", 4: "k_hex8_neohooke<true>", 2: "k_generic<HEX8,DISP,true>"}
+TRAFFIC = {0: 4.083e9, 16: 5.115e9}  # profiles/r01_mma_kernel_ncu_full_c.md, profiles/r01_tile_kernel_ncu.md
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -247,10 +253,10 @@ def run_ours(args):
     alg_bytes = 8 * nnz + 72 * grid.n_col_nodes + 32 * grid.n_col_eles  # K once, X/u/f once, conn once
     achieved = alg_bytes / (ele_ms * 1e-3) / 1e9
     traffic = args.traffic
-    if traffic is None and args.edge == 100 and world == 1 and not args.kernel_flags:
-        traffic = 4.083e9  # dram__bytes_read.sum + dram__bytes_write.sum of this kernel, profiles/r01_mma_kernel_ncu_full_c.md
+    if traffic is None and args.edge == 100 and world == 1 and args.kernel_flags in TRAFFIC:
+        traffic = TRAFFIC[args.kernel_flags]
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": traffic, "peak_source": peak_src, "kernel": "k_hex8_neohooke_mma<true>" if not args.kernel_flags else f"flags={args.kernel_flags}",
+                "traffic": traffic, "peak_source": peak_src, "kernel": KERNEL_NAME.get(args.kernel_flags, f"flags={args.kernel_flags}"),
                 "kernel_ms": ele_ms, "zero_fill_ms": zero_ms, "algorithmic_bytes_per_launch": alg_bytes}
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -333,7 +339,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ref-edge", type=int, default=100, help="edge of the cube the CPU arm evaluates (100 = the full C2 workload)")
     ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--kernel-flags", type=int, default=0, help="FC_EVAL_* kernel selection (2 generic, 4 closed-form FMA)")
+    ap.add_argument("--kernel-flags", type=int, default=0, help="FC_EVAL_* kernel selection (0 default, 16 tile scatter, 4 closed-form FMA, 2 generic)")
     ap.add_argument("--traffic", type=float, default=None, help="dram bytes per launch from the committed ncu capture")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -81,8 +81,12 @@ extern "C"
                                   closed-form kernel exists (testing / comparison) */
     FC_EVAL_CLOSED_FORM_FMA = 4, /* hex8 Neo-Hooke closed form on the FP64 FMA pipe instead of the
                                     FP64 tensor cores (comparison) */
-    FC_EVAL_NO_SLAB_PIPELINE = 8 /* with ZERO_FIRST: one memset + one launch instead of zeroing slab k+1 on a
-                                    second stream while slab k computes (comparison) */
+    FC_EVAL_NO_SLAB_PIPELINE = 8, /* with ZERO_FIRST: one memset + one launch instead of zeroing slab k+1 on a
+                                     second stream while slab k computes (comparison) */
+    FC_EVAL_TILE = 16 /* hex8 Neo-Hooke, assembled stiffness: tile kernel (k_hex8_nh_tile) that sums the element matrices of
+                         a 16-element tile in shared memory and adds every node-pair block once (43 % fewer reduction
+                         sectors, but shared-memory bound: slower than the per-element scatter on B200, DESIGN.md 4.6;
+                         kept for comparison).  The tile plan is built by the first evaluation that asks for it. */
   };
 
   /* ---- context ------------------------------------------------------------------------------ */
@@ -216,6 +220,27 @@ extern "C"
    * per peer; recv lists are implicit (ghost nodes grouped by owner). */
   int fc_grid_halo_counts(const fc_grid* g, int* send_node_count /*[nranks]*/, int* recv_node_count /*[nranks]*/);
   int fc_grid_halo_send_nodes(const fc_grid* g, int* send_node_lids /*[sum send counts]*/);
+
+  /* ---- tile plan of the hex8 scatter (host integer code; exposed for inspection and tests) ------
+   * Replaces the per-element row loop of SparseMatrix::assemble (4C_linalg_sparsematrix.cpp:474-543): elements are
+   * grouped into spatially compact tiles of <= 16, every (row node, column node) pair inside a tile is one block that
+   * the tile kernel sums in shared memory and adds to the CSR values once.  the first FC_EVAL_TILE evaluation of a hex8
+   * context creates its plan; these entry points build the same plan from plain arrays.
+   *   nodeptr [n_row_nodes+1], nodeadj: node-block graph of the owned nodes, ascending column-node LIDs
+   *   tile_ele [16*n_tiles]     element of every tile slot, -1 = empty
+   *   tile_blk [512*n_tiles]    per slot and accumulator lane (a = lane/4, q = lane%4): block of (a, 2q) | block of
+   *                             (a, 2q+1) << 16, tile-local; 0xFFFF = row node not owned
+   *   tile_ptr [n_tiles+1]      first block record of a tile
+   *   rec      [n_blocks]       CSR offset of (DOF row 3a, column 3b) | entries per DOF row << 44
+   *   rownode  [n_blocks]       row node a
+   * create returns FC_ERR_GRAPH when the mesh has no plan (an element lists a node twice, or a pair is missing from
+   * the graph); the library then scatters element by element. */
+  typedef struct fc_tile_plan fc_tile_plan;
+  int fc_tile_plan_create(int n_col_nodes, const double* X, int n_ele, const int* conn, int n_row_nodes, const int64_t* nodeptr,
+      const int* nodeadj, fc_tile_plan** out);
+  int fc_tile_plan_sizes(const fc_tile_plan* p, int* n_tiles, int64_t* n_blocks, int* max_blocks);
+  int fc_tile_plan_get(const fc_tile_plan* p, int* tile_ele, uint32_t* tile_blk, int64_t* tile_ptr, uint64_t* rec, int* rownode);
+  void fc_tile_plan_destroy(fc_tile_plan* p);
 
 #ifdef __cplusplus
 }

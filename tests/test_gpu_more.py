@@ -148,7 +148,7 @@ def test_c2_full_size_invariants(fc):
     assert (f2 - f - Kdx).abs().max() <= 1e-5 * Kdx.abs().max()
     # (4) the two closed-form kernels and the generic kernel agree at full size
     K2 = torch.empty_like(K)
-    for flags in (fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC):
+    for flags in (fc.FC_EVAL_TILE, fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC):
         s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f2, K2, flags=flags | fc.FC_EVAL_ZERO_FIRST)
         assert (K2 - K).abs().max() <= 1e-12 * kmax
         assert (f2 - f).abs().max() <= 1e-12 * kmax * 0.01

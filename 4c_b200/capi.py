@@ -20,6 +20,8 @@ FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_NO_S
 FC_STRESS_2PK, FC_STRESS_CAUCHY = 0, 1
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
+FC_ERR_SOLVER, FC_ERR_SOLVER_NOT_CONVERGED = -7, -8
+FC_SOLVER_CG, FC_SOLVER_BICGSTAB = 0, 1
 NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10}
 
 EXPORTS = [
@@ -31,6 +33,7 @@ EXPORTS = [
     "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
     "fc_grid_halo_counts", "fc_grid_halo_send_nodes", "fc_probe_fp64_fma", "fc_probe_fp64_mma",
+    "fc_solid_set_dirichlet_toggle", "fc_solid_apply_dirichlet", "fc_solid_apply_dirichlet_to_system", "fc_solid_spmv", "fc_solid_linear_solve",
     "fc_tile_plan_create", "fc_tile_plan_sizes", "fc_tile_plan_get", "fc_tile_plan_destroy",
 ]
 
@@ -226,6 +229,29 @@ class Solid:
     def set_dirichlet_rows(self, rows):
         rows = _i32(rows)
         self._chk(lib().fc_solid_set_dirichlet_rows(self.h, C.c_int(len(rows)), _ptr(rows)))
+
+    # ---- Dirichlet application + linear solve on the device (all buffers are device tensors) ----
+    def set_dirichlet_toggle(self, rows):
+        rows = _i32(rows)
+        self._chk(lib().fc_solid_set_dirichlet_toggle(self.h, C.c_int(len(rows)), _ptr(rows)))
+
+    def apply_dirichlet(self, K_values, diagonalblock=True):
+        self._chk(lib().fc_solid_apply_dirichlet(self.h, _ptr(K_values), C.c_int(1 if diagonalblock else 0)))
+
+    def apply_dirichlet_to_system(self, x=None, b=None, dbcval=None):
+        self._chk(lib().fc_solid_apply_dirichlet_to_system(self.h, _ptr(x), _ptr(b), _ptr(dbcval)))
+
+    def spmv(self, K_values, x_col, y_row):
+        self._chk(lib().fc_solid_spmv(self.h, _ptr(K_values), _ptr(x_col), _ptr(y_row)))
+
+    def linear_solve(self, K_values, b, x, method=FC_SOLVER_CG, rel_tol=1e-10, max_iter=10000, check=True):
+        """K x = b; x holds the initial guess.  Returns (iterations, relative residual)."""
+        it, rr = C.c_int(0), C.c_double(0.0)
+        rc = lib().fc_solid_linear_solve(self.h, C.c_int(method), _ptr(K_values), _ptr(b), _ptr(x), C.c_double(rel_tol), C.c_int(max_iter),
+                                         C.byref(it), C.byref(rr))
+        if rc != FC_ERR_SOLVER_NOT_CONVERGED or check:
+            self._chk(rc)
+        return it.value, rr.value
 
     def evaluate(self, action, u_col, f_row=None, K_values=None, flags=0, want_errors=True):
         """returns (ele_error_count, first_bad_gid) or None when want_errors is False (asynchronous)."""

@@ -70,6 +70,14 @@ extern "C"
     dev_free(ctx->d_tile_rec);
     dev_free(ctx->d_tile_rownode);
     dev_free(ctx->d_dbc);
+    dev_free(ctx->d_nodeptr);
+    dev_free(ctx->d_nodeadj);
+    dev_free(ctx->d_node_diagpos);
+    dev_free(ctx->d_toggle_rows);
+    dev_free(ctx->d_solver_ws);
+    dev_free(ctx->d_Dinv);
+    dev_free(ctx->d_dot);
+    if (ctx->h_dot_pinned) cudaFreeHost(ctx->h_dot_pinned);
     dev_free(ctx->d_send_lids);
     dev_free(ctx->d_halo_sendbuf);
     dev_free(ctx->d_stage_u);

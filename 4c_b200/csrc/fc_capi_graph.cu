@@ -168,11 +168,26 @@ namespace
     FC_CUDA(cudaSetDevice(ctx->device));
     FC_CUDA(dev_upload(ctx->d_node_rowbase, rowbase.data(), rowbase.size(), ctx->stream));
     FC_CUDA(dev_upload(ctx->d_node_rowlen, rowlen.data(), rowlen.size(), ctx->stream));
-    long long* d_nodeptr = nullptr;
-    int* d_nodeadj = nullptr;
     static_assert(sizeof(long long) == sizeof(int64_t), "");
-    FC_CUDA(dev_upload(d_nodeptr, (const long long*)ctx->h_nodeptr.data(), ctx->h_nodeptr.size(), ctx->stream));
-    FC_CUDA(dev_upload(d_nodeadj, ctx->h_nodeadj.data(), ctx->h_nodeadj.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_nodeptr, (const long long*)ctx->h_nodeptr.data(), ctx->h_nodeptr.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_nodeadj, ctx->h_nodeadj.data(), ctx->h_nodeadj.size(), ctx->stream));
+    long long* const d_nodeptr = ctx->d_nodeptr;
+    int* const d_nodeadj = ctx->d_nodeadj;
+    {
+      // position of every owned node in its own neighbour list (diagonal block: apply_dirichlet, block Jacobi)
+      std::vector<int> diagpos((size_t)nrow, 0);
+      for (int n = 0; n < nrow; ++n)
+      {
+        const int* b = ctx->h_nodeadj.data() + ctx->h_nodeptr[n];
+        const int* e = ctx->h_nodeadj.data() + ctx->h_nodeptr[n + 1];
+        const int* p = std::lower_bound(b, e, n);
+        diagpos[n] = (p != e && *p == n) ? (int)(p - b) : -1;
+      }
+      FC_CUDA(dev_upload(ctx->d_node_diagpos, diagpos.data(), diagpos.size(), ctx->stream));
+      FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    dev_free(ctx->d_toggle_rows);  // refers to rows of the previous graph
+    ctx->n_toggle = 0;
     dev_free(ctx->d_slots);
     const size_t nslots = (size_t)ctx->n_ele * ctx->nen * ctx->nen;
     int bad = 0;
@@ -193,8 +208,6 @@ namespace
       bad = ctx->h_err_pinned[0];
     }
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
-    cudaFree(d_nodeptr);
-    cudaFree(d_nodeadj);
     // Dirichlet flags refer to rows of the previous graph
     dev_free(ctx->d_dbc);
     ctx->have_dbc = false;

@@ -1,0 +1,257 @@
+// Dirichlet application and the linear-solve hand-off on the device.
+//
+//   fc_solid_set_dirichlet_toggle      the dbcmap of Solid::Dbc (src/structure_new/src/utils/4C_structure_new_dbc.cpp)
+//   fc_solid_apply_dirichlet           SparseMatrix::apply_dirichlet (src/core/linalg/src/sparse/4C_linalg_sparsematrix.cpp:978-1100)
+//   fc_solid_apply_dirichlet_to_system apply_dirichlet_to_system (src/core/linalg/src/sparse/4C_linalg_utils_sparse_algebra_assemble.cpp:126-199)
+//   fc_solid_spmv                      SparseMatrix::multiply on the rank's rows
+//   fc_solid_linear_solve              stands where Solid::Nln::LinSystem hands K and the residual to core/linear_solver:
+//                                      preconditioned CG / BiCGStab with node-block Jacobi, everything resident in HBM
+#include <cmath>
+
+#include "fc_host_util.hpp"
+#include "fc_kernels_linsolve.cuh"
+
+namespace
+{
+  int ensure_dot(fc_ctx* ctx)
+  {
+    if (!ctx->d_dot) FC_CUDA(cudaMalloc((void**)&ctx->d_dot, sizeof(double) * (3 * fc::dot_blocks + 3)));
+    if (!ctx->h_dot_pinned) FC_CUDA(cudaMallocHost((void**)&ctx->h_dot_pinned, sizeof(double) * 3));
+    return FC_OK;
+  }
+
+  // up to three dot products in one pass and one read-back (synchronises the stream)
+  int dots(fc_ctx* ctx, int n, const double* a0, const double* b0, const double* a1, const double* b1, const double* a2, const double* b2, double* out)
+  {
+    fc::k_dot3_partial<<<fc::dot_blocks, fc::dot_threads, 0, ctx->stream>>>(n, a0, b0, a1, b1, a2, b2, ctx->d_dot);
+    fc::k_dot3_final<<<3, 256, 0, ctx->stream>>>(ctx->d_dot, fc::dot_blocks, ctx->d_dot + 3 * fc::dot_blocks);
+    ctx->launches += 2;
+    FC_CUDA(cudaGetLastError());
+    FC_CUDA(cudaMemcpyAsync(ctx->h_dot_pinned, ctx->d_dot + 3 * fc::dot_blocks, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < 3; ++i) out[i] = ctx->h_dot_pinned[i];
+    return FC_OK;
+  }
+
+  inline unsigned grid_for(long long n, int bs) { return (unsigned)((n + bs - 1) / bs); }
+
+  void spmv(fc_ctx* ctx, const double* K, const double* x, double* y)
+  {
+    const int bs = 256;
+    fc::k_spmv<<<grid_for(32LL * ctx->n_row_nodes, bs), bs, 0, ctx->stream>>>(ctx->d_nodeptr, ctx->d_nodeadj, ctx->n_row_nodes, K, x, y);
+    ctx->launches++;
+  }
+
+  void precond(fc_ctx* ctx, const double* r, double* z)
+  {
+    const int bs = 256;
+    fc::k_block_jacobi_apply<<<grid_for(ctx->n_row_nodes, bs), bs, 0, ctx->stream>>>(ctx->d_Dinv, ctx->n_row_nodes, r, z);
+    ctx->launches++;
+  }
+
+  void axpby(fc_ctx* ctx, int n, double a, const double* x, double b, double* y)
+  {
+    fc::k_axpby<<<grid_for(n, 256), 256, 0, ctx->stream>>>(n, a, x, b, y);
+    ctx->launches++;
+  }
+
+  void xpaypbw(fc_ctx* ctx, int n, const double* x, double a, const double* y, double b, const double* w, double* z)
+  {
+    fc::k_xpaypbw<<<grid_for(n, 256), 256, 0, ctx->stream>>>(n, x, a, y, b, w, z);
+    ctx->launches++;
+  }
+}  // namespace
+
+extern "C"
+{
+  int fc_solid_set_dirichlet_toggle(fc_ctx* ctx, int n, const int* row_lids)
+  {
+    if (!ctx || !ctx->have_graph || n < 0 || (n > 0 && !row_lids)) return fail(ctx, FC_ERR_INVALID, "graph required");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    for (int i = 0; i < n; ++i)
+      if (row_lids[i] < 0 || row_lids[i] >= ctx->n_row_dof) return fail(ctx, FC_ERR_INVALID, "Dirichlet row out of range");
+    FC_CUDA(dev_upload(ctx->d_toggle_rows, row_lids, (size_t)n, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->n_toggle = n;
+    return FC_OK;
+  }
+
+  int fc_solid_apply_dirichlet(fc_ctx* ctx, double* K_values, int diagonalblock)
+  {
+    if (!ctx || !ctx->have_graph || !K_values) return fail(ctx, FC_ERR_INVALID, "graph and K_values required");
+    if (!is_device_ptr(K_values)) return fail(ctx, FC_ERR_INVALID, "apply_dirichlet works on the device-resident matrix");
+    if (ctx->n_toggle == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    const int bs = 256;
+    fc::k_apply_dirichlet<<<grid_for(32LL * ctx->n_toggle, bs), bs, 0, ctx->stream>>>(ctx->d_toggle_rows, ctx->n_toggle, ctx->d_nodeptr, ctx->d_node_diagpos,
+        K_values, diagonalblock);
+    ctx->launches++;
+    FC_CUDA(cudaGetLastError());
+    return FC_OK;
+  }
+
+  int fc_solid_apply_dirichlet_to_system(fc_ctx* ctx, double* x, double* b, const double* dbcval)
+  {
+    if (!ctx || !ctx->have_graph) return fail(ctx, FC_ERR_INVALID, "graph required");
+    if ((x && !is_device_ptr(x)) || (b && !is_device_ptr(b)) || (dbcval && !is_device_ptr(dbcval)))
+      return fail(ctx, FC_ERR_INVALID, "apply_dirichlet_to_system works on device vectors");
+    if (ctx->n_toggle == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    fc::k_apply_dirichlet_vec<<<grid_for(ctx->n_toggle, 256), 256, 0, ctx->stream>>>(ctx->d_toggle_rows, ctx->n_toggle, x, b, dbcval);
+    ctx->launches++;
+    FC_CUDA(cudaGetLastError());
+    return FC_OK;
+  }
+
+  int fc_solid_spmv(fc_ctx* ctx, const double* K_values, const double* x_col, double* y_row)
+  {
+    if (!ctx || !ctx->have_graph || !K_values || !x_col || !y_row) return fail(ctx, FC_ERR_INVALID, "graph, K_values, x and y required");
+    if (!is_device_ptr(K_values) || !is_device_ptr(x_col) || !is_device_ptr(y_row)) return fail(ctx, FC_ERR_INVALID, "spmv works on device buffers");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    FC_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
+    FC_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+    spmv(ctx, K_values, x_col, y_row);
+    FC_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
+    ctx->ev_valid = true;
+    FC_CUDA(cudaGetLastError());
+    return FC_OK;
+  }
+
+  int fc_solid_linear_solve(fc_ctx* ctx, int method, const double* K_values, const double* b, double* x, double rel_tol, int max_iter,
+      int* iters, double* rel_residual)
+  {
+    if (!ctx || !ctx->have_graph || !K_values || !b || !x) return fail(ctx, FC_ERR_INVALID, "graph, K_values, b and x required");
+    if (method != FC_SOLVER_CG && method != FC_SOLVER_BICGSTAB) return fail(ctx, FC_ERR_UNSUPPORTED, "solver method");
+    if (ctx->n_col_dof != ctx->n_row_dof)
+      return fail(ctx, FC_ERR_UNSUPPORTED, "the solver hand-off is built for one rank per system (all columns owned); the multi-rank solve needs "
+                                            "the halo import of the search direction and an all-reduce per dot product");
+    if (!is_device_ptr(K_values) || !is_device_ptr(b) || !is_device_ptr(x)) return fail(ctx, FC_ERR_INVALID, "linear_solve works on device buffers");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    if (int rc = ensure_dot(ctx)) return rc;
+    const int n = ctx->n_row_dof;
+    const size_t nvec = method == FC_SOLVER_CG ? 4 : 8;
+    FC_CUDA(ensure_cap(ctx->d_solver_ws, ctx->solver_ws_cap, nvec * (size_t)n));
+    if (!ctx->d_Dinv) FC_CUDA(cudaMalloc((void**)&ctx->d_Dinv, sizeof(double) * 9 * (size_t)ctx->n_row_nodes));
+    fc::k_block_jacobi_setup<<<grid_for(ctx->n_row_nodes, 256), 256, 0, ctx->stream>>>(ctx->d_nodeptr, ctx->d_node_diagpos, ctx->n_row_nodes, K_values, ctx->d_Dinv);
+    ctx->launches++;
+    FC_CUDA(cudaGetLastError());
+    double* W = ctx->d_solver_ws;
+    double d[3];
+    int it = 0;
+    double relres = 0.0;
+    if (int rc = dots(ctx, n, b, b, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+    const double bnorm = std::sqrt(d[0]);
+    auto finish = [&](int rc) {
+      if (iters) *iters = it;
+      if (rel_residual) *rel_residual = relres;
+      return rc;
+    };
+    if (!(bnorm > 0.0))
+    {
+      FC_CUDA(cudaMemsetAsync(x, 0, sizeof(double) * (size_t)n, ctx->stream));
+      return finish(FC_OK);
+    }
+    if (method == FC_SOLVER_CG)
+    {
+      // preconditioned CG.  With Dirichlet rows applied (identity rows, columns kept) the operator is symmetric on the
+      // free DOFs as long as the iterates keep x = b on the Dirichlet rows: pass x with those entries set
+      // (fc_solid_apply_dirichlet_to_system does) and the residual, hence every search direction, is zero there.
+      double *r = W, *z = W + n, *p = W + 2 * (size_t)n, *Ap = W + 3 * (size_t)n;
+      spmv(ctx, K_values, x, Ap);
+      xpaypbw(ctx, n, b, -1.0, Ap, 0.0, nullptr, r);
+      precond(ctx, r, z);
+      FC_CUDA(cudaMemcpyAsync(p, z, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, ctx->stream));
+      if (int rc = dots(ctx, n, r, z, r, r, nullptr, nullptr, d)) return rc;
+      double rz = d[0];
+      relres = std::sqrt(d[1]) / bnorm;
+      while (relres > rel_tol && it < max_iter)
+      {
+        spmv(ctx, K_values, p, Ap);
+        if (int rc = dots(ctx, n, p, Ap, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+        if (!(d[0] > 0.0)) return finish(fail(ctx, FC_ERR_SOLVER, "CG breakdown: p.Ap <= 0 (matrix not positive definite on the free DOFs)"));
+        const double alpha = rz / d[0];
+        axpby(ctx, n, alpha, p, 1.0, x);
+        axpby(ctx, n, -alpha, Ap, 1.0, r);
+        precond(ctx, r, z);
+        if (int rc = dots(ctx, n, r, z, r, r, nullptr, nullptr, d)) return rc;
+        const double beta = d[0] / rz;
+        rz = d[0];
+        relres = std::sqrt(d[1]) / bnorm;
+        axpby(ctx, n, 1.0, z, beta, p);
+        ++it;
+      }
+    }
+    else
+    {
+      // right-preconditioned BiCGStab (van der Vorst): non-symmetric tangents (F-bar) and non-zero Dirichlet values
+      const size_t N = (size_t)n;
+      double *r = W, *r0 = W + N, *p = W + 2 * N, *v = W + 3 * N, *s = W + 4 * N, *t = W + 5 * N, *ph = W + 6 * N, *sh = W + 7 * N;
+      spmv(ctx, K_values, x, v);
+      xpaypbw(ctx, n, b, -1.0, v, 0.0, nullptr, r);
+      FC_CUDA(cudaMemcpyAsync(r0, r, sizeof(double) * N, cudaMemcpyDeviceToDevice, ctx->stream));
+      FC_CUDA(cudaMemsetAsync(p, 0, sizeof(double) * N, ctx->stream));
+      FC_CUDA(cudaMemsetAsync(v, 0, sizeof(double) * N, ctx->stream));
+      if (int rc = dots(ctx, n, r, r, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+      relres = std::sqrt(d[0]) / bnorm;
+      double rho = 1.0, alpha = 1.0, omega = 1.0;
+      int restarts = 0;
+      // a vanishing rho, omega or r0.v is a breakdown of the recurrence, not of the problem: restart from the current
+      // iterate with a fresh shadow residual
+      auto restart = [&]() -> int {
+        if (++restarts > 20) return fail(ctx, FC_ERR_SOLVER, "BiCGStab breakdown (20 restarts)");
+        spmv(ctx, K_values, x, v);
+        xpaypbw(ctx, n, b, -1.0, v, 0.0, nullptr, r);
+        FC_CUDA(cudaMemcpyAsync(r0, r, sizeof(double) * N, cudaMemcpyDeviceToDevice, ctx->stream));
+        FC_CUDA(cudaMemsetAsync(p, 0, sizeof(double) * N, ctx->stream));
+        FC_CUDA(cudaMemsetAsync(v, 0, sizeof(double) * N, ctx->stream));
+        rho = alpha = omega = 1.0;
+        return FC_OK;
+      };
+      while (relres > rel_tol && it < max_iter)
+      {
+        if (int rc = dots(ctx, n, r0, r, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+        const double rho_new = d[0];
+        if (rho_new == 0.0 || omega == 0.0 || !std::isfinite(rho_new))
+        {
+          if (int rc = restart()) return finish(rc);
+          ++it;
+          continue;
+        }
+        const double beta = (rho_new / rho) * (alpha / omega);
+        rho = rho_new;
+        // p = r + beta (p - omega v)
+        axpby(ctx, n, -omega, v, 1.0, p);
+        axpby(ctx, n, 1.0, r, beta, p);
+        precond(ctx, p, ph);
+        spmv(ctx, K_values, ph, v);
+        if (int rc = dots(ctx, n, r0, v, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+        if (d[0] == 0.0 || !std::isfinite(d[0]))
+        {
+          if (int rc = restart()) return finish(rc);
+          ++it;
+          continue;
+        }
+        alpha = rho / d[0];
+        xpaypbw(ctx, n, r, -alpha, v, 0.0, nullptr, s);
+        precond(ctx, s, sh);
+        spmv(ctx, K_values, sh, t);
+        if (int rc = dots(ctx, n, t, s, t, t, s, s, d)) return rc;
+        ++it;
+        if (!(d[1] > 0.0))
+        {
+          // s = 0: x + alpha phat is the solution
+          axpby(ctx, n, alpha, ph, 1.0, x);
+          relres = std::sqrt(d[2]) / bnorm;
+          break;
+        }
+        omega = d[0] / d[1];
+        xpaypbw(ctx, n, x, alpha, ph, omega, sh, x);
+        xpaypbw(ctx, n, s, -omega, t, 0.0, nullptr, r);
+        if (int rc = dots(ctx, n, r, r, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+        relres = std::sqrt(d[0]) / bnorm;
+      }
+    }
+    FC_CUDA(cudaGetLastError());
+    return finish(relres <= rel_tol ? FC_OK : FC_ERR_SOLVER_NOT_CONVERGED);
+  }
+}

@@ -44,6 +44,18 @@ struct fc_ctx
   unsigned char* d_slots = nullptr;   // [n_ele][nen][nen] position of node b in the row of node a
   unsigned char* d_dbc = nullptr;     // [n_row_dof] 1 = row skipped by the matrix scatter
   bool have_dbc = false;
+  long long* d_nodeptr = nullptr;     // [n_row_nodes+1] node-block graph on the device (SpMV, Dirichlet application)
+  int* d_nodeadj = nullptr;
+  int* d_node_diagpos = nullptr;      // [n_row_nodes] position of node a in its own neighbour list
+
+  // Dirichlet toggle (Solid::Dbc's dbcmap) and linear-solver workspace
+  int n_toggle = 0;
+  int* d_toggle_rows = nullptr;       // [n_toggle] DOF row lids
+  double* d_solver_ws = nullptr;      // Krylov vectors
+  size_t solver_ws_cap = 0;
+  double* d_Dinv = nullptr;           // [n_row_nodes][9] inverse diagonal blocks
+  double* d_dot = nullptr;            // block partials [3][592] + results [3]
+  double* h_dot_pinned = nullptr;
 
   // hex8 tile plan (fc_tile_plan.hpp): built by the first FC_EVAL_TILE evaluation; n_tiles == 0 = no plan, per-element scatter
   int n_tiles = 0, tile_max_blocks = 0;

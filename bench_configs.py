@@ -99,6 +99,68 @@ def run(fc, name, ct, form, mat, nue, n, steps, flags=0):
     torch.cuda.empty_cache()
 
 
+def run_newton(fc, edge, steps):
+    """SURVEY 8f F1 at C2 size: one load step of a clamped hex8 Neo-Hooke cube under a nodal load on the x+ face, full Newton with
+    every stage on the device (element evaluation, Dirichlet application, CG with node-block Jacobi): times per stage, the
+    y = K x kernel against the HBM roofline, CG iterations."""
+    import torch
+    dev = torch.device("cuda", 0)
+    g = fc.Grid(fc.FC_HEX8, (edge, edge, edge))
+    s = fc.Solid(0)
+    s.set_stream(torch.cuda.current_stream().cuda_stream)
+    s.set_mesh(fc.FC_HEX8, fc.FC_FORM_DISPLACEMENT, g.X, g.node_gid, g.node_owner, g.conn, g.ele_gid)
+    s.set_material(fc.FC_MAT_ELASTHYPER_COUPNEOHOOKE, 10.0, 0.25)
+    n_row, n_col, nnz = s.build_graph()
+    fixed = np.flatnonzero(np.repeat(g.X[:, 0] < 1e-12, 3)).astype(np.int32)
+    s.set_dirichlet_toggle(fixed)
+    fext = np.zeros(n_row)
+    loaded = np.flatnonzero(g.X[:, 0] > 1.0 - 1e-12)
+    fext[3 * loaded + 2] = 0.02 / len(loaded)  # total transverse force 0.02 on the x+ face
+    fext = torch.from_numpy(fext).to(dev)
+    u = torch.zeros(n_col, dtype=torch.float64, device=dev)
+    K = torch.empty(nnz, dtype=torch.float64, device=dev)
+    f = torch.empty(n_row, dtype=torch.float64, device=dev)
+    r = torch.empty(n_row, dtype=torch.float64, device=dev)
+    x = torch.empty(n_row, dtype=torch.float64, device=dev)
+    # y = K x alone
+    s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f, K, flags=fc.FC_EVAL_ZERO_FIRST, want_errors=False)
+    for _ in range(3):
+        s.spmv(K, fext, x)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        s.spmv(K, fext, x)
+    e1.record()
+    torch.cuda.synchronize()
+    spmv_ms = e0.elapsed_time(e1) / steps
+    spmv_bytes = 8 * nnz + 4 * (nnz // 9) + 16 * n_row  # K once, one column-node id per 3x3 block, x and y once
+    hist = []
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    for it in range(12):
+        ev[0].record()
+        s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f, K, flags=fc.FC_EVAL_ZERO_FIRST, want_errors=False)
+        torch.sub(fext, f, out=r)
+        s.apply_dirichlet(K)
+        x.zero_()
+        s.apply_dirichlet_to_system(x, r, None)
+        ev[1].record()
+        rn = float(r.norm())
+        cg_it, rr = s.linear_solve(K, r, x, method=fc.FC_SOLVER_CG, rel_tol=1e-8, max_iter=5000, check=False)
+        u += x
+        ev[2].record()
+        torch.cuda.synchronize()
+        hist.append({"residual": rn, "eval_ms": ev[0].elapsed_time(ev[1]), "solve_ms": ev[1].elapsed_time(ev[2]), "cg_iterations": cg_it, "cg_rel_residual": rr})
+        if rn < 1e-9 * hist[0]["residual"]:
+            break
+    assert s.error_state() == (0, -1)
+    peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    out = {"config": f"F1 device Newton step, hex8 NeoHooke {edge}^3, clamped x-, load on x+", "elements": edge ** 3, "n_dof": n_row, "nnz": int(nnz),
+           "spmv_ms": spmv_ms, "spmv_algorithmic_GBps": spmv_bytes / (spmv_ms * 1e-3) / 1e9, "measured_peaks": peak,
+           "newton": hist, "max_displacement": float(u.abs().max())}
+    print(json.dumps(out), flush=True)
+    s.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default=None)
@@ -122,6 +184,9 @@ def main():
         ("C4 hex8 F-bar NeoHooke nu=0.499 200^3", H8, FB, NH, 0.499, (200, 200, 200), 0),
         ("C5/8 hex8 NeoHooke 200^3 (one GPU's share of 400^3)", H8, D, NH, 0.25, (200, 200, 200), 0),
     ]
+    if args.only and args.only.startswith("newton"):
+        run_newton(fc, int(args.only[6:] or 100), args.steps)
+        return
     for c in cfgs:
         if args.only and args.only not in c[0]:
             continue

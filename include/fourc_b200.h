@@ -42,7 +42,9 @@ extern "C"
     FC_ERR_CUDA = -3,              /* CUDA runtime error, see fc_last_error() */
     FC_ERR_NEGATIVE_JACOBIAN = -4, /* det J <= 0 at an element node (4C_solid_3D_ele_calc_lib.hpp:492-494) */
     FC_ERR_GRAPH = -5,             /* element couples DOFs that are not in the CSR graph */
-    FC_ERR_UNSUPPORTED = -6        /* cell type / formulation / material combination not on the path */
+    FC_ERR_UNSUPPORTED = -6,       /* cell type / formulation / material combination not on the path */
+    FC_ERR_SOLVER = -7,            /* Krylov breakdown in fc_solid_linear_solve */
+    FC_ERR_SOLVER_NOT_CONVERGED = -8 /* max_iter reached; x holds the last iterate, rel_residual its residual */
   } fc_status;
 
   /* cell types on the path: src/solid_3D_ele/4C_solid_3D_ele_factory.hpp:36-82 */
@@ -220,6 +222,33 @@ extern "C"
    * per peer; recv lists are implicit (ghost nodes grouped by owner). */
   int fc_grid_halo_counts(const fc_grid* g, int* send_node_count /*[nranks]*/, int* recv_node_count /*[nranks]*/);
   int fc_grid_halo_send_nodes(const fc_grid* g, int* send_node_lids /*[sum send counts]*/);
+
+  /* ---- Dirichlet application and linear-solve hand-off, K resident in HBM ---------------------
+   * Stand where Solid::Dbc::apply_dirichlet_to_local_jacobian / apply_dirichlet_to_rhs
+   * (src/structure_new/src/utils/4C_structure_new_dbc.cpp:244-290) and the Newton linear system hand K and the
+   * residual to core/linear_solver.  All vectors and K_values are DEVICE buffers.
+   *   set_dirichlet_toggle   the dbcmap (owned DOF row lids, host array); independent of set_dirichlet_rows, which
+   *                          is the dbcmaps_ of the matrix that makes the scatter skip rows
+   *   apply_dirichlet        SparseMatrix::apply_dirichlet (4C_linalg_sparsematrix.cpp:978-1100, non-explicit
+   *                          branch :1066-1092): zero the rows, 1.0 on the diagonal if diagonalblock
+   *   apply_dirichlet_to_system  x[i] = b[i] = dbcval[i] on the toggled rows
+   *                          (4C_linalg_utils_sparse_algebra_assemble.cpp:126-140); x or b may be NULL, dbcval NULL = zeros
+   *   spmv                   y_row = K x_col on the rank's rows
+   *   linear_solve           K x = b, preconditioned (node-block Jacobi) CG or BiCGStab; x holds the initial guess on
+   *                          entry.  CG needs a tangent that is symmetric positive definite on the free DOFs and x = b
+   *                          on the Dirichlet rows on entry (apply_dirichlet_to_system sets that); BiCGStab has no such
+   *                          requirement (F-bar tangents are not symmetric).  One rank per system. */
+  enum
+  {
+    FC_SOLVER_CG = 0,
+    FC_SOLVER_BICGSTAB = 1
+  };
+  int fc_solid_set_dirichlet_toggle(fc_ctx* ctx, int n, const int* row_lids);
+  int fc_solid_apply_dirichlet(fc_ctx* ctx, double* K_values, int diagonalblock);
+  int fc_solid_apply_dirichlet_to_system(fc_ctx* ctx, double* x, double* b, const double* dbcval);
+  int fc_solid_spmv(fc_ctx* ctx, const double* K_values, const double* x_col, double* y_row);
+  int fc_solid_linear_solve(fc_ctx* ctx, int method, const double* K_values, const double* b, double* x, double rel_tol, int max_iter,
+      int* iters, double* rel_residual);
 
   /* ---- tile plan of the hex8 scatter (host integer code; exposed for inspection and tests) ------
    * Replaces the per-element row loop of SparseMatrix::assemble (4C_linalg_sparsematrix.cpp:474-543): elements are

@@ -196,9 +196,11 @@ def _converged(norms, inc, newton_tol):
     return len(norms) > 2 and norms[-1] < 1e-9 * max(norms) and norms[-1] > 0.5 * norms[-2]
 
 
-def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30):
+def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None):
     """assemble(d) -> (f_int [n], K dense [n, n]); mass() -> M dense.  Returns d at MAXTIME and the residual
-    norm history of every step (list of lists)."""
+    norm history of every step (list of lists).  solve(A, rhs, fixed) replaces the dense direct solve (A is then
+    whatever assemble/mass return, e.g. device-resident CSR values supporting a*A + b*B and A @ x)."""
+    _solve = solve or globals()["_solve"]
     p = problem
     n, fixed, dt = p.n_dof, p.fixed, p.dt
     d = np.zeros(n)

@@ -154,8 +154,9 @@ def test_reference_golden_solves_with_device_linear_solver(fc, oracle, case, met
         b = torch.from_numpy(np.ascontiguousarray(rhs)).to(dev)
         x = torch.zeros_like(b)
         s.apply_dirichlet_to_system(x, b, None)
-        it, rr = s.linear_solve(J, b, x, method=method, rel_tol=1e-13, max_iter=20000, check=False)
-        assert rr <= 1e-8, (it, rr)
+        # BiCGStab's recursive residual drifts from the true one below ~1e-12: ask it for 1e-11, CG for 1e-13
+        it, rr = s.linear_solve(J, b, x, method=method, rel_tol=1e-13 if method == 0 else 1e-11, max_iter=20000, check=False)
+        assert rr <= 1e-8, (case, it, rr)
         iters.append(it)
         return x.cpu().numpy()
 

@@ -14,6 +14,7 @@ namespace
     int (*recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
     int (*group_start)() = nullptr;
     int (*group_end)() = nullptr;
+    int (*all_reduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
     const char* (*error_string)(int) = nullptr;
     bool ok = false;
   };
@@ -33,6 +34,7 @@ namespace
       a.recv = (decltype(a.recv))dlsym(h, "ncclRecv");
       a.group_start = (decltype(a.group_start))dlsym(h, "ncclGroupStart");
       a.group_end = (decltype(a.group_end))dlsym(h, "ncclGroupEnd");
+      a.all_reduce = (decltype(a.all_reduce))dlsym(h, "ncclAllReduce");
       a.error_string = (decltype(a.error_string))dlsym(h, "ncclGetErrorString");
       a.ok = a.send && a.recv && a.group_start && a.group_end;
       return a;
@@ -40,7 +42,21 @@ namespace
     return api;
   }
   constexpr int kNcclFloat64 = 8;  // ncclDataType_t::ncclFloat64 (nccl.h), stable across NCCL 2.x
+  constexpr int kNcclSum = 0;      // ncclRedOp_t::ncclSum
 }  // namespace
+
+// sum of n doubles over the ranks of the context's communicator, in place, on the context's stream (linear solve)
+int fc_allreduce_sum(fc_ctx* ctx, double* buf_dev, int n)
+{
+  if (ctx->nranks == 1) return FC_OK;
+  NcclApi& api = nccl();
+  if (!api.ok || !api.all_reduce) return fail(ctx, FC_ERR_UNSUPPORTED, "NCCL entry points not found in the process and libnccl.so.2 cannot be loaded");
+  if (!ctx->nccl_comm) return fail(ctx, FC_ERR_INVALID, "fc_solid_set_comm must precede a multi-rank linear solve");
+  const int rc = api.all_reduce(buf_dev, buf_dev, (size_t)n, kNcclFloat64, kNcclSum, ctx->nccl_comm, ctx->stream);
+  if (rc != 0) return fail(ctx, FC_ERR_CUDA, std::string("NCCL: ") + (api.error_string ? api.error_string(rc) : "error"));
+  ctx->launches++;
+  return FC_OK;
+}
 
 extern "C"
 {
@@ -60,6 +76,13 @@ extern "C"
       return fail(ctx, FC_ERR_INVALID, "receive counts do not add up to the ghost DOFs of the mesh");
     ctx->halo_send_count.assign(send_dof_count, send_dof_count + ctx->nranks);
     ctx->halo_recv_count.assign(recv_dof_count, recv_dof_count + ctx->nranks);
+    return FC_OK;
+  }
+
+  int fc_solid_set_comm(fc_ctx* ctx, void* nccl_comm)
+  {
+    if (!ctx) return FC_ERR_INVALID;
+    ctx->nccl_comm = nccl_comm;
     return FC_OK;
   }
 

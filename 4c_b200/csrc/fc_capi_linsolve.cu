@@ -11,6 +11,8 @@
 #include "fc_host_util.hpp"
 #include "fc_kernels_linsolve.cuh"
 
+int fc_allreduce_sum(fc_ctx* ctx, double* buf_dev, int n);  // fc_capi_halo.cu
+
 namespace
 {
   int ensure_dot(fc_ctx* ctx)
@@ -27,6 +29,7 @@ namespace
     fc::k_dot3_final<<<3, 256, 0, ctx->stream>>>(ctx->d_dot, fc::dot_blocks, ctx->d_dot + 3 * fc::dot_blocks);
     ctx->launches += 2;
     FC_CUDA(cudaGetLastError());
+    if (int rc = fc_allreduce_sum(ctx, ctx->d_dot + 3 * fc::dot_blocks, 3)) return rc;
     FC_CUDA(cudaMemcpyAsync(ctx->h_dot_pinned, ctx->d_dot + 3 * fc::dot_blocks, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
     for (int i = 0; i < 3; ++i) out[i] = ctx->h_dot_pinned[i];
@@ -40,6 +43,15 @@ namespace
     const int bs = 128;  // measured: 0.425 ms at C2 (256: 0.437, 512: 0.456)
     fc::k_spmv<<<grid_for(32LL * ctx->n_row_nodes, bs), bs, 0, ctx->stream>>>(ctx->d_nodeptr, ctx->d_nodeadj, ctx->n_row_nodes, K, x, y);
     ctx->launches++;
+  }
+
+  // y = K v for a vector in column layout whose owned part is current: import the ghosts first (numproc > 1)
+  int spmv_col(fc_ctx* ctx, const double* K, double* vcol, double* y)
+  {
+    if (ctx->nranks > 1)
+      if (int rc = fc_solid_halo_exchange(ctx, ctx->nccl_comm, vcol)) return rc;
+    spmv(ctx, K, vcol, y);
+    return FC_OK;
   }
 
   void precond(fc_ctx* ctx, const double* r, double* z)
@@ -122,15 +134,17 @@ extern "C"
   {
     if (!ctx || !ctx->have_graph || !K_values || !b || !x) return fail(ctx, FC_ERR_INVALID, "graph, K_values, b and x required");
     if (method != FC_SOLVER_CG && method != FC_SOLVER_BICGSTAB) return fail(ctx, FC_ERR_UNSUPPORTED, "solver method");
-    if (ctx->n_col_dof != ctx->n_row_dof)
-      return fail(ctx, FC_ERR_UNSUPPORTED, "the solver hand-off is built for one rank per system (all columns owned); the multi-rank solve needs "
-                                            "the halo import of the search direction and an all-reduce per dot product");
+    const bool multi = ctx->nranks > 1;
+    if (!multi && ctx->n_col_dof != ctx->n_row_dof) return fail(ctx, FC_ERR_INVALID, "ghost columns on a single rank");
+    if (multi && (!ctx->nccl_comm || (int)ctx->halo_send_count.size() != ctx->nranks))
+      return fail(ctx, FC_ERR_INVALID, "numproc > 1: fc_solid_set_comm and the halo plan (fc_solid_halo_set_send/_set_counts) must precede linear_solve");
     if (!is_device_ptr(K_values) || !is_device_ptr(b) || !is_device_ptr(x)) return fail(ctx, FC_ERR_INVALID, "linear_solve works on device buffers");
     FC_CUDA(cudaSetDevice(ctx->device));
     if (int rc = ensure_dot(ctx)) return rc;
     const int n = ctx->n_row_dof;
     const size_t nvec = method == FC_SOLVER_CG ? 4 : 8;
-    FC_CUDA(ensure_cap(ctx->d_solver_ws, ctx->solver_ws_cap, nvec * (size_t)n));
+    const size_t NC = (size_t)ctx->n_col_dof;  // every work vector is column-sized: the ones K multiplies carry ghosts
+    FC_CUDA(ensure_cap(ctx->d_solver_ws, ctx->solver_ws_cap, nvec * NC));
     if (!ctx->d_Dinv) FC_CUDA(cudaMalloc((void**)&ctx->d_Dinv, sizeof(double) * 9 * (size_t)ctx->n_row_nodes));
     fc::k_block_jacobi_setup<<<grid_for(ctx->n_row_nodes, 256), 256, 0, ctx->stream>>>(ctx->d_nodeptr, ctx->d_node_diagpos, ctx->n_row_nodes, K_values, ctx->d_Dinv);
     ctx->launches++;
@@ -156,8 +170,9 @@ extern "C"
       // preconditioned CG.  With Dirichlet rows applied (identity rows, columns kept) the operator is symmetric on the
       // free DOFs as long as the iterates keep x = b on the Dirichlet rows: pass x with those entries set
       // (fc_solid_apply_dirichlet_to_system does) and the residual, hence every search direction, is zero there.
-      double *r = W, *z = W + n, *p = W + 2 * (size_t)n, *Ap = W + 3 * (size_t)n;
-      spmv(ctx, K_values, x, Ap);
+      double *r = W, *z = W + NC, *p = W + 2 * NC, *Ap = W + 3 * NC;
+      FC_CUDA(cudaMemcpyAsync(p, x, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, ctx->stream));
+      if (int rc = spmv_col(ctx, K_values, p, Ap)) return rc;
       xpaypbw(ctx, n, b, -1.0, Ap, 0.0, nullptr, r);
       precond(ctx, r, z);
       FC_CUDA(cudaMemcpyAsync(p, z, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -171,16 +186,30 @@ extern "C"
         FC_CUDA(cudaMemcpyAsync(sc, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
         FC_CUDA(cudaStreamSynchronize(ctx->stream));
       }
+      // block partials -> sc: one kernel on one rank; sum, all-reduce, derive on numproc > 1
+      auto reduce_scalars = [&](int mode) -> int {
+        if (!multi)
+        {
+          fc::k_cg_scalars<<<1, 256, 0, ctx->stream>>>(ctx->d_dot, fc::dot_blocks, mode, sc);
+          return FC_OK;
+        }
+        double* t = ctx->d_dot + 3 * fc::dot_blocks;
+        fc::k_dot3_final<<<3, 256, 0, ctx->stream>>>(ctx->d_dot, fc::dot_blocks, t);
+        if (int rc = fc_allreduce_sum(ctx, t, 2)) return rc;
+        fc::k_cg_derive<<<1, 32, 0, ctx->stream>>>(mode, t, sc);
+        ctx->launches++;
+        return FC_OK;
+      };
       const int check_every = 8;
       while (relres > rel_tol && it < max_iter)
       {
         for (int k = 0; k < check_every && it < max_iter; ++k, ++it)
         {
-          spmv(ctx, K_values, p, Ap);
+          if (int rc = spmv_col(ctx, K_values, p, Ap)) return rc;
           fc::k_dot3_partial<<<fc::dot_blocks, fc::dot_threads, 0, ctx->stream>>>(n, p, Ap, nullptr, nullptr, nullptr, nullptr, ctx->d_dot);
-          fc::k_cg_scalars<<<1, 256, 0, ctx->stream>>>(ctx->d_dot, fc::dot_blocks, 1, sc);
+          if (int rc = reduce_scalars(1)) return rc;
           fc::k_cg_update<<<fc::dot_blocks, fc::dot_threads, 0, ctx->stream>>>(ctx->n_row_nodes, sc, p, Ap, ctx->d_Dinv, x, r, z, ctx->d_dot);
-          fc::k_cg_scalars<<<1, 256, 0, ctx->stream>>>(ctx->d_dot, fc::dot_blocks, 0, sc);
+          if (int rc = reduce_scalars(0)) return rc;
           fc::k_cg_direction<<<grid_for(n, 256), 256, 0, ctx->stream>>>(n, sc, z, p);
           ctx->launches += 5;
         }
@@ -196,8 +225,9 @@ extern "C"
     {
       // right-preconditioned BiCGStab (van der Vorst): non-symmetric tangents (F-bar) and non-zero Dirichlet values
       const size_t N = (size_t)n;
-      double *r = W, *r0 = W + N, *p = W + 2 * N, *v = W + 3 * N, *s = W + 4 * N, *t = W + 5 * N, *ph = W + 6 * N, *sh = W + 7 * N;
-      spmv(ctx, K_values, x, v);
+      double *r = W, *r0 = W + NC, *p = W + 2 * NC, *v = W + 3 * NC, *s = W + 4 * NC, *t = W + 5 * NC, *ph = W + 6 * NC, *sh = W + 7 * NC;
+      FC_CUDA(cudaMemcpyAsync(ph, x, sizeof(double) * N, cudaMemcpyDeviceToDevice, ctx->stream));
+      if (int rc = spmv_col(ctx, K_values, ph, v)) return rc;
       xpaypbw(ctx, n, b, -1.0, v, 0.0, nullptr, r);
       FC_CUDA(cudaMemcpyAsync(r0, r, sizeof(double) * N, cudaMemcpyDeviceToDevice, ctx->stream));
       FC_CUDA(cudaMemsetAsync(p, 0, sizeof(double) * N, ctx->stream));
@@ -210,7 +240,8 @@ extern "C"
       // iterate with a fresh shadow residual
       auto restart = [&]() -> int {
         if (++restarts > 20) return fail(ctx, FC_ERR_SOLVER, "BiCGStab breakdown (20 restarts)");
-        spmv(ctx, K_values, x, v);
+        FC_CUDA(cudaMemcpyAsync(ph, x, sizeof(double) * N, cudaMemcpyDeviceToDevice, ctx->stream));
+        if (int rc = spmv_col(ctx, K_values, ph, v)) return rc;
         xpaypbw(ctx, n, b, -1.0, v, 0.0, nullptr, r);
         FC_CUDA(cudaMemcpyAsync(r0, r, sizeof(double) * N, cudaMemcpyDeviceToDevice, ctx->stream));
         FC_CUDA(cudaMemsetAsync(p, 0, sizeof(double) * N, ctx->stream));
@@ -234,7 +265,7 @@ extern "C"
         axpby(ctx, n, -omega, v, 1.0, p);
         axpby(ctx, n, 1.0, r, beta, p);
         precond(ctx, p, ph);
-        spmv(ctx, K_values, ph, v);
+        if (int rc = spmv_col(ctx, K_values, ph, v)) return rc;
         if (int rc = dots(ctx, n, r0, v, nullptr, nullptr, nullptr, nullptr, d)) return rc;
         if (d[0] == 0.0 || !std::isfinite(d[0]))
         {
@@ -245,7 +276,7 @@ extern "C"
         alpha = rho / d[0];
         xpaypbw(ctx, n, r, -alpha, v, 0.0, nullptr, s);
         precond(ctx, s, sh);
-        spmv(ctx, K_values, sh, t);
+        if (int rc = spmv_col(ctx, K_values, sh, t)) return rc;
         if (int rc = dots(ctx, n, t, s, t, t, s, s, d)) return rc;
         ++it;
         if (!(d[1] > 0.0))

@@ -83,6 +83,7 @@ struct fc_ctx
   int* d_send_lids = nullptr;
   std::vector<int> halo_send_count, halo_recv_count;  // DOFs per peer rank (fc_solid_halo_set_counts)
   double* d_halo_sendbuf = nullptr;
+  void* nccl_comm = nullptr;  // caller's ncclComm_t for the collectives of the linear solve (fc_solid_set_comm)
   size_t halo_sendbuf_cap = 0;
 
   // scratch + error state

@@ -264,6 +264,20 @@ namespace fc
     }
   }
 
+  // numproc > 1: the sums arrive all-reduced in t[0..1]; same bookkeeping as k_cg_scalars
+  static __global__ void k_cg_derive(int mode, const double* __restrict__ t, double* __restrict__ sc)
+  {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (mode == 1)
+      sc[1] = t[0];
+    else
+    {
+      sc[4] = sc[0] > 0.0 ? t[0] / sc[0] : 0.0;
+      sc[0] = t[0];
+      sc[2] = t[1];
+    }
+  }
+
   // p = z + beta p, beta = sc[4]
   static __global__ void k_cg_direction(int n, const double* __restrict__ sc, const double* __restrict__ z, double* __restrict__ p)
   {

@@ -280,6 +280,15 @@ def run_ours(args):
 
     # ---- e2e: same call with HOST buffers (pinned), H2D of u and D2H of f, K inside the timed region --
     e2e_steps = max(1, min(args.steps, args.e2e_steps))
+    if args.no_e2e:
+        out["e2e"] = None
+        out["clocks"] = sampler.summary()
+        if rank == 0:
+            print(json.dumps(out))
+        s.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
     u_pin = torch.from_numpy(u_host).pin_memory()
     f_pin = torch.empty(n_row_dof, dtype=torch.float64).pin_memory()
     K_pin = torch.empty(nnz, dtype=torch.float64).pin_memory()
@@ -342,6 +351,7 @@ def main():
     ap.add_argument("--kernel-flags", type=int, default=0, help="FC_EVAL_* kernel selection (0 default, 16 tile scatter, 4 closed-form FMA, 2 generic)")
     ap.add_argument("--traffic", type=float, default=None, help="dram bytes per launch from the committed ncu capture")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (large --edge: K alone is 15.7 GB of pinned memory per rank at 200)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

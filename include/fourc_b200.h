@@ -191,6 +191,9 @@ extern "C"
    * does not link NCCL: the symbols are resolved from the process (or libnccl.so.2) at the first call. */
   int fc_solid_halo_set_counts(fc_ctx* ctx, const int* send_dof_count, const int* recv_dof_count);
   int fc_solid_halo_exchange(fc_ctx* ctx, void* nccl_comm, double* u_col_dev);
+  /* communicator (ncclComm_t, rank ids = the ranks of fc_solid_create) used by fc_solid_linear_solve on numproc > 1: halo
+   * import of the search direction before every y = K x, one all-reduce per dot product */
+  int fc_solid_set_comm(fc_ctx* ctx, void* nccl_comm);
 
   /* ---- timing helpers (device time of the last evaluate, CUDA events on the ctx stream) ----- */
   int fc_solid_last_kernel_ms(fc_ctx* ctx, float* zero_ms, float* element_ms);
@@ -237,7 +240,8 @@ extern "C"
    *   linear_solve           K x = b, preconditioned (node-block Jacobi) CG or BiCGStab; x holds the initial guess on
    *                          entry.  CG needs a tangent that is symmetric positive definite on the free DOFs and x = b
    *                          on the Dirichlet rows on entry (apply_dirichlet_to_system sets that); BiCGStab has no such
-   *                          requirement (F-bar tangents are not symmetric).  One rank per system. */
+   *                          requirement (F-bar tangents are not symmetric).  numproc > 1: b and x are the rank's rows, the halo plan
+   *                          (fc_solid_halo_set_send/_set_counts) and fc_solid_set_comm must be in place; every rank calls. */
   enum
   {
     FC_SOLVER_CG = 0,

@@ -34,7 +34,7 @@ EXPORTS = [
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
     "fc_grid_halo_counts", "fc_grid_halo_send_nodes", "fc_probe_fp64_fma", "fc_probe_fp64_mma",
     "fc_solid_set_comm", "fc_solid_set_dirichlet_toggle", "fc_solid_apply_dirichlet", "fc_solid_apply_dirichlet_to_system", "fc_solid_spmv", "fc_solid_linear_solve",
-    "fc_tile_plan_create", "fc_tile_plan_sizes", "fc_tile_plan_get", "fc_tile_plan_destroy",
+    "fc_l2_sweep_order", "fc_tile_plan_create", "fc_tile_plan_sizes", "fc_tile_plan_get", "fc_tile_plan_destroy",
 ]
 
 
@@ -120,6 +120,16 @@ def tile_plan(X, conn, n_row_nodes, nodeptr, nodeadj):
     L.fc_tile_plan_destroy.restype = None
     L.fc_tile_plan_destroy(h)
     return out
+
+
+def l2_sweep_order(X, conn, layer_elems):
+    """(changed, perm): element order of the hex8 assembled-path kernels on large meshes (fc_l2_sweep_order)"""
+    X, conn = _f64(X), _i32(conn)
+    perm = np.zeros(conn.shape[0], np.int32)
+    rc = lib().fc_l2_sweep_order(C.c_int(X.size // 3), _ptr(X), C.c_int(conn.shape[0]), C.c_int(conn.shape[1]), _ptr(conn), C.c_int64(layer_elems), _ptr(perm))
+    if rc < 0:
+        raise FourCError(rc, "fc_l2_sweep_order")
+    return bool(rc), perm
 
 
 class Grid:

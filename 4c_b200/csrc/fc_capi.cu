@@ -9,7 +9,10 @@
 
 #include "../../include/fourc_b200.h"
 #include "fc_context.hpp"
+#include <cstdlib>
+
 #include "fc_host_util.hpp"
+#include "fc_tile_plan.hpp"
 #include "fc_kernels_setup.cuh"
 
 
@@ -61,6 +64,7 @@ extern "C"
     dev_free(ctx->d_gpw);
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
+    dev_free(ctx->d_ele_perm);
     dev_free(ctx->d_node_rowbase);
     dev_free(ctx->d_node_rowlen);
     dev_free(ctx->d_slots);
@@ -157,6 +161,15 @@ extern "C"
     FC_CUDA(dev_upload(ctx->d_gpw, w.data(), w.size(), ctx->stream));
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
+    dev_free(ctx->d_ele_perm);
+    if (celltype == FC_HEX8 && !getenv("FC_NO_L2_ORDER"))
+    {
+      // large meshes: visit the elements so that a row's contributions arrive while the row is still in L2
+      std::vector<int> perm;
+      const char* le = getenv("FC_L2_LAYER_ELEMS");
+      if (fc_host::l2_sweep_order(n_col_nodes, X, n_col_ele, nen, conn, le ? atoll(le) : 12000, perm))
+        FC_CUDA(dev_upload(ctx->d_ele_perm, perm.data(), perm.size(), ctx->stream));
+    }
     ctx->n_tiles = 0;  // the tile plan belongs to the graph of the previous mesh
     ctx->tile_plan_tried = false;
     ctx->geom_bad_count = 0;

@@ -231,6 +231,7 @@ extern "C"
     A.u = d_u;
     A.f = d_f;
     A.K = d_K;
+    if (!pipelined && !getenv("FC_NO_L2_ORDER")) A.ele_perm = ctx->d_ele_perm;
     if (pipelined)
     {
       // zero the rows a slab touches first on stream2 while the previous slab computes on the main stream

@@ -14,6 +14,7 @@ namespace fc
     const double* X;       // [n_col_nodes][3]
     const int* conn;       // [n_ele][nen]
     const int* ele_gid;    // [n_ele]
+    const int* ele_perm;   // [n_ele] element visited by launch slot k (L2 sweep order) or nullptr = k
     int n_ele;             // end of the element range of this launch
     int ele_offset;        // first element of this launch (slab-pipelined evaluation), 0 otherwise
     int n_row_nodes;       // column nodes [0, n_row_nodes) are owned (their DOF rows are assembled)

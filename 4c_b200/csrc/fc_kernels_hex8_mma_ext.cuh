@@ -64,8 +64,10 @@ namespace fc
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int el = lane >> 3, t = lane & 7;
     const int wel = warp * Cfg::epw;
-    const int e = A.ele_offset + blockIdx.x * Cfg::epb + wel + el;
-    const bool active = e < A.n_ele;
+    const int slot_e = A.ele_offset + blockIdx.x * Cfg::epb + wel + el;
+    const bool active = slot_e < A.n_ele;
+    // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_tile_plan.hpp)
+    const int e = active ? (A.ele_perm ? __ldg(A.ele_perm + slot_e) : slot_e) : -1;
     double* E = smem + (size_t)(wel + el) * Cfg::ele_doubles;
 
     // ---- phase 0: lane (el, t) gathers node t of element el ------------------------------------------
@@ -267,7 +269,7 @@ namespace fc
     for (int k = 0; k < Cfg::epw; ++k)
     {
       if (!((actmask >> (8 * k)) & 1u) || ((badmask >> (8 * k)) & 0xFFu)) continue;  // warp-uniform
-      const int ek = A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
+      const int ek = __shfl_sync(0xFFFFFFFFu, e, 8 * k);
       const double* G = smem + (size_t)(wel + k) * Cfg::ele_doubles;
       const int fo0 = frag_idx(q, a), fo1 = frag_idx(q + 4, a);
       const double* R0 = G + Cfg::oR + Cfg::rec * q;

@@ -69,8 +69,10 @@ namespace fc
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int el = lane >> 3, t = lane & 7;   // phase 0/1 role
     const int wel = warp * Cfg::epw;          // first element slot of this warp inside the CTA
-    const int e = A.ele_offset + blockIdx.x * Cfg::epb + wel + el;
-    const bool active = e < A.n_ele;
+    const int slot_e = A.ele_offset + blockIdx.x * Cfg::epb + wel + el;
+    const bool active = slot_e < A.n_ele;
+    // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_tile_plan.hpp)
+    const int e = active ? (A.ele_perm ? __ldg(A.ele_perm + slot_e) : slot_e) : -1;
     double* E = smem + (size_t)(wel + el) * Cfg::ele_doubles;
 
     // ---- phase 0 ----------------------------------------------------------------------------------
@@ -187,8 +189,8 @@ namespace fc
     const double c2 = A.mat.young / (2.0 * (1.0 + A.mat.nue));  // 2c
     // cached geometric part of s[a][2q], s[a][2q+1], one element ahead of its use
     auto load_sg = [&](int k) -> double2 {
-      const int ek = A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
-      return (k < Cfg::epw && ek < A.n_ele) ? __ldg(reinterpret_cast<const double2*>(A.geom + (size_t)ek * Cfg::geom_doubles) + lane) : make_double2(0.0, 0.0);
+      const int ek = __shfl_sync(0xFFFFFFFFu, e, (8 * k) & 31);
+      return (k < Cfg::epw && ek >= 0) ? __ldg(reinterpret_cast<const double2*>(A.geom + (size_t)ek * Cfg::geom_doubles) + lane) : make_double2(0.0, 0.0);
     };
     double2 sg_next = load_sg(0);
 #pragma unroll 1
@@ -197,7 +199,7 @@ namespace fc
       const double2 sg = sg_next;
       sg_next = load_sg(k + 1);
       if (!((actmask >> (8 * k)) & 1u) || ((badmask >> (8 * k)) & 0xFFu)) continue;  // warp-uniform
-      const int ek = A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
+      const int ek = __shfl_sync(0xFFFFFFFFu, e, 8 * k);
       const double* G = smem + (size_t)(wel + k) * Cfg::ele_doubles;
       const int fo0 = frag_idx(q, a), fo1 = frag_idx(q + 4, a);
       double fg[3][2];

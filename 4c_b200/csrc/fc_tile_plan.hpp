@@ -26,6 +26,14 @@ namespace fc_host
     std::vector<int> rownode;             // per block: row node a
   };
 
+  // Element order for L2 locality of the per-element scatter on large meshes.  A matrix row receives its element
+  // contributions between the first and the last element that touches the node; if the elements in between write more
+  // K values than L2 holds, the partially summed rows are evicted and fetched again.  On a z-major sweep that distance is
+  // one layer (nx * ny elements, 2 KB of K each).  This order cuts the layers into y blocks of at most `layer_elems`
+  // elements and sweeps block by block: (y block, z, y, x) on the lattice of the mean element extent.  Returns false
+  // (perm left empty) when a layer already fits, i.e. the caller's order is kept.  nen = nodes per element.
+  bool l2_sweep_order(int n_col_nodes, const double* X, int n_ele, int nen, const int* conn, long long layer_elems, std::vector<int>& perm);
+
   // X [n_col_nodes][3]; conn [n_ele][8] column-node ids; nodes [0, n_row_nodes) own rows; nodeptr/nodeadj = node-block
   // graph of the owned nodes (ascending column-node ids).  Returns false (plan left empty) if an element lists a node
   // twice or couples a pair that is missing from the graph: the caller then stays on the per-element scatter.

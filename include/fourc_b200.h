@@ -274,6 +274,10 @@ extern "C"
   int fc_tile_plan_sizes(const fc_tile_plan* p, int* n_tiles, int64_t* n_blocks, int* max_blocks);
   int fc_tile_plan_get(const fc_tile_plan* p, int* tile_ele, uint32_t* tile_blk, int64_t* tile_ptr, uint64_t* rec, int* rownode);
   void fc_tile_plan_destroy(fc_tile_plan* p);
+  /* element order the hex8 assembled-path kernels visit on large meshes (host integer code): y blocks of z layers of at
+   * most layer_elems elements, so that a matrix row's element contributions arrive while the row is still in L2.
+   * perm [n_ele] = element visited by launch slot k; returns 1 if the order differs from the caller's, 0 if it is kept. */
+  int fc_l2_sweep_order(int n_col_nodes, const double* X, int n_ele, int nen, const int* conn, int64_t layer_elems, int* perm);
 
 #ifdef __cplusplus
 }

@@ -243,3 +243,29 @@ def test_full_size_kernel_agreement_fbar_svk(fc, form, mat, nue):
     assert (K2 - K).abs().max() <= 1e-12 * kmax
     assert (f2 - f).abs().max() <= 1e-12 * kmax * 0.01
     s.close()
+
+
+@pytest.mark.gpu
+def test_l2_sweep_order_gives_same_assembly(fc, monkeypatch):
+    """FC_L2_LAYER_ELEMS small: the hex8 Neo-Hooke kernel visits the elements in (y block, z, y, x) order; K and f
+    must equal the result in the caller's order (reduction order changes: rounding only)"""
+    g = fc.Grid(HEX8, (9, 8, 7))
+    u = field(g.X, 0).reshape(-1).copy()
+    res = []
+    for env in ("40", None):
+        if env:
+            monkeypatch.setenv("FC_L2_LAYER_ELEMS", env)
+        else:
+            monkeypatch.delenv("FC_L2_LAYER_ELEMS")
+            monkeypatch.setenv("FC_NO_L2_ORDER", "1")
+        s = fc.Solid(0)
+        s.set_mesh(fc.FC_HEX8, DISP, g.X, g.node_gid, g.node_owner, g.conn, g.ele_gid)
+        s.set_material(NH, 10.0, 0.25)
+        n_row, n_col, nnz = s.build_graph()
+        K, f = np.zeros(nnz), np.zeros(n_row)
+        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+        res.append((K, f))
+        s.close()
+    assert np.max(np.abs(res[0][0] - res[1][0])) <= 1e-13 * np.max(np.abs(res[1][0]))
+    assert np.max(np.abs(res[0][1] - res[1][1])) <= 1e-13 * np.max(np.abs(res[1][0]))
+    assert fc.capi.l2_sweep_order(g.X, g.conn, 40)[0]

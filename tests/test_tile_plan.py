@@ -122,3 +122,18 @@ def test_degenerate_element_has_no_plan(fc):
     conn[3, 5] = conn[3, 4]  # collapsed edge: two accumulator lanes of one element would hit the same block
     nodeptr, nodeadj = node_graph(conn, g.n_row_nodes)
     assert fc.capi.tile_plan(g.X, conn, g.n_row_nodes, nodeptr, nodeadj) is None
+
+
+def test_l2_sweep_order(fc):
+    """large meshes: (y block, z, y, x) sweep; a permutation, blocks of W element rows, identity when a z layer fits"""
+    g = fc.Grid(fc.FC_HEX8, (10, 12, 6))
+    changed, perm = fc.capi.l2_sweep_order(g.X, g.conn, 40)  # W = max(4, 40 // 10) = 4 element rows per y block
+    assert changed and sorted(perm.tolist()) == list(range(720))
+    c = g.X[g.conn[perm]].mean(axis=1)
+    iy = np.floor(c[:, 1] * 12).astype(int)
+    iz = np.floor(c[:, 2] * 6).astype(int)
+    ix = np.floor(c[:, 0] * 10).astype(int)
+    key = ((iy // 4) * 6 + iz) * 12 * 10 + iy * 10 + ix
+    assert np.all(np.diff(key) > 0)
+    assert fc.capi.l2_sweep_order(g.X, g.conn, 120)[0] is False     # a layer (120 elements) fits
+    assert fc.capi.l2_sweep_order(g.X, g.conn, 10 ** 6)[0] is False  # small mesh

@@ -87,3 +87,33 @@ def test_nccl_halo_exchange_two_gpus():
     build_halo_example()
     r = subprocess.run([HALO_EXE], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "HALO OK" in r.stdout, r.stdout + r.stderr
+
+
+SOLVE_EXE = os.path.join(ROOT, "examples", "_build", "solve_example")
+
+
+def build_solve_example():
+    os.makedirs(os.path.dirname(SOLVE_EXE), exist_ok=True)
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    lib = os.path.join(ROOT, "4c_b200", "lib")
+    cmd = ["g++", "-std=c++17", "-O1", os.path.join(ROOT, "examples", "solve_example.cpp"), "-I" + ROOT, "-I" + cuda + "/include",
+           "-L" + lib, "-lfourc_b200", "-L" + cuda + "/lib64", "-lcudart", "-lnccl", "-lpthread", "-Wl,-rpath," + lib,
+           "-Wl,-rpath," + cuda + "/lib64", "-o", SOLVE_EXE]
+    subprocess.run(cmd, check=True, capture_output=True, text=True)
+
+
+def test_two_rank_solve_example_compiles_and_links():
+    build_solve_example()
+    assert os.path.exists(SOLVE_EXE)
+
+
+@pytest.mark.gpu
+def test_linear_solve_two_gpus_matches_one_rank():
+    """fc_solid_linear_solve on a system partitioned over 2 ranks = 2 GPUs (halo import of the search direction, NCCL all-reduce
+    per dot product) gives the solution of the same system held by one rank, CG and BiCGStab"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    build_solve_example()
+    r = subprocess.run([SOLVE_EXE], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "SOLVE OK" in r.stdout, r.stdout + r.stderr

@@ -162,12 +162,14 @@ extern "C"
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
     dev_free(ctx->d_ele_perm);
-    if (celltype == FC_HEX8 && !getenv("FC_NO_L2_ORDER"))
+    if (!getenv("FC_NO_L2_ORDER"))
     {
-      // large meshes: visit the elements so that a row's contributions arrive while the row is still in L2
+      // large meshes: visit the elements so that a row's contributions arrive while the row is still in L2; a layer of
+      // the sweep may write about 24 MB of K values (hex8 2 KB, tet10 2.8 KB, hex27 37 KB per element)
       std::vector<int> perm;
       const char* le = getenv("FC_L2_LAYER_ELEMS");
-      if (fc_host::l2_sweep_order(n_col_nodes, X, n_col_ele, nen, conn, le ? atoll(le) : 12000, perm))
+      const long long budget = celltype == FC_HEX8 ? 12000 : (celltype == FC_TET10 ? 8500 : 650);
+      if (fc_host::l2_sweep_order(n_col_nodes, X, n_col_ele, nen, conn, le ? atoll(le) : budget, perm))
         FC_CUDA(dev_upload(ctx->d_ele_perm, perm.data(), perm.size(), ctx->stream));
     }
     ctx->n_tiles = 0;  // the tile plan belongs to the graph of the previous mesh

@@ -59,12 +59,13 @@ namespace fc
     for (int it = tid; it < EPB * NP; it += Cfg::threads)
     {
       const int el = it / NP, a = it % NP;
-      const int e = ebase + el;
+      // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_tile_plan.hpp)
+      const int e = ebase + el < A.n_ele ? (A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el) : -1;
       double* E = smem_nhg + (size_t)el * Cfg::ele_doubles;
       long long rb = -1;
       int rl = 0, nd = -1;
       double xc[3] = {0, 0, 0};
-      if (e < A.n_ele && a < NEN)
+      if (e >= 0 && a < NEN)
       {
         const int node = __ldg(A.conn + (size_t)e * NEN + a), n0 = __ldg(A.conn + (size_t)e * NEN);
         for (int i = 0; i < 3; ++i)
@@ -89,7 +90,7 @@ namespace fc
       s_rowbase[el][a] = rb;
       s_rowlen[el][a] = rl;
       s_node[el][a] = nd;
-      if (a == 0) s_bad[el] = (e < A.n_ele && ele_bad && ele_bad[e]) ? 1 : 0;
+      if (a == 0) s_bad[el] = (e >= 0 && ele_bad && ele_bad[e]) ? 1 : 0;
     }
     __syncthreads();
 
@@ -179,8 +180,8 @@ namespace fc
     for (int item = warp; item < EPB * MT; item += Cfg::warps)
     {
       const int mt = item % MT, el = item / MT;
-      const int e = ebase + el;
-      if (e >= A.n_ele) continue;
+      if (ebase + el >= A.n_ele) continue;
+      const int e = A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el;
       if (s_bad[el])
       {
         if (mt == 0 && lane == 0) report_error(A.err, __ldg(A.ele_gid + e));

@@ -172,8 +172,10 @@ namespace fc_host
       nd[d] = std::min(nd[d], 1LL << 20);
       hd[d] = ext > 0.0 ? ext / (double)nd[d] : 1.0;
     }
-    if (nd[0] * nd[1] <= layer_elems) return false;  // a z layer fits: keep the caller's order
-    const long long W = std::max(4LL, layer_elems / nd[0]);
+    // elements per lattice cell (6 for a Kuhn-split tet mesh)
+    const long long per_cell = std::max(1LL, (long long)std::llround((double)n_ele / ((double)nd[0] * (double)nd[1] * (double)nd[2])));
+    if (nd[0] * nd[1] * per_cell <= layer_elems) return false;  // a z layer fits: keep the caller's order
+    const long long W = std::max(4LL, layer_elems / (nd[0] * per_cell));
     if (W >= nd[1]) return false;
     std::vector<std::pair<unsigned long long, int>> keyed((size_t)n_ele);
     for (int e = 0; e < n_ele; ++e)

@@ -17,6 +17,7 @@ FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
 FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_NO_SLAB_PIPELINE, FC_EVAL_TILE = 1, 2, 4, 8, 16
+FC_EVAL_INTERIOR, FC_EVAL_BOUNDARY = 32, 64
 FC_STRESS_2PK, FC_STRESS_CAUCHY = 0, 1
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6

@@ -162,15 +162,31 @@ extern "C"
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
     dev_free(ctx->d_ele_perm);
-    if (!getenv("FC_NO_L2_ORDER"))
     {
-      // large meshes: visit the elements so that a row's contributions arrive while the row is still in L2; a layer of
-      // the sweep may write about 24 MB of K values (hex8 2 KB, tet10 2.8 KB, hex27 37 KB per element)
+      // launch-slot order of the tensor-core kernels.  Large meshes: visit the elements so that a row's contributions arrive
+      // while the row is still in L2; a layer of the sweep may write about 24 MB of K values (hex8 2 KB, tet10 2.8 KB, hex27
+      // 37 KB per element).  More than one rank: elements without ghost nodes first, so that they can be evaluated while the
+      // halo import is in flight (FC_EVAL_INTERIOR, then FC_EVAL_BOUNDARY).
       std::vector<int> perm;
       const char* le = getenv("FC_L2_LAYER_ELEMS");
       const long long budget = celltype == FC_HEX8 ? 12000 : (celltype == FC_TET10 ? 8500 : 650);
-      if (fc_host::l2_sweep_order(n_col_nodes, X, n_col_ele, nen, conn, le ? atoll(le) : budget, perm))
-        FC_CUDA(dev_upload(ctx->d_ele_perm, perm.data(), perm.size(), ctx->stream));
+      if (!getenv("FC_NO_L2_ORDER")) fc_host::l2_sweep_order(n_col_nodes, X, n_col_ele, nen, conn, le ? atoll(le) : budget, perm);
+      ctx->n_interior_ele = n_col_ele;
+      if (n_row < n_col_nodes)
+      {
+        if (perm.empty())
+        {
+          perm.resize((size_t)n_col_ele);
+          for (int e = 0; e < n_col_ele; ++e) perm[e] = e;
+        }
+        auto interior = [&](int e) {
+          for (int a = 0; a < nen; ++a)
+            if (conn[(size_t)e * nen + a] >= n_row) return false;
+          return true;
+        };
+        ctx->n_interior_ele = (int)(std::stable_partition(perm.begin(), perm.end(), interior) - perm.begin());
+      }
+      if (!perm.empty()) FC_CUDA(dev_upload(ctx->d_ele_perm, perm.data(), perm.size(), ctx->stream));
     }
     ctx->n_tiles = 0;  // the tile plan belongs to the graph of the previous mesh
     ctx->tile_plan_tried = false;

@@ -104,9 +104,18 @@ namespace
     auto kern = A.dbc ? fc::k_nh_mma_gen<CT, WANT_K, true> : fc::k_nh_mma_gen<CT, WANT_K, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
     if (e != cudaSuccess) return e;
-    kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+    kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
     ctx->launches++;
     return cudaGetLastError();
+  }
+
+  // true if dispatch() picks a kernel that visits the elements through EvalArgs::ele_perm and the launch-slot range
+  bool follows_launch_order(const fc_ctx* ctx, int flags)
+  {
+    if (flags & FC_EVAL_FORCE_GENERIC) return false;
+    const bool fbar = ctx->formulation == FC_FORM_FBAR, nh = ctx->mat.kind == fc::MAT_NEOHOOKE;
+    if (ctx->celltype == FC_HEX8) return nh ? (fbar || !(flags & FC_EVAL_CLOSED_FORM_FMA)) : !fbar;  // k_hex8_neohooke_mma, k_hex8_mma_ext
+    return nh && !fbar;                                                                            // k_nh_mma_gen
   }
 
   template <bool WANT_K>
@@ -232,6 +241,16 @@ extern "C"
     A.f = d_f;
     A.K = d_K;
     if (!pipelined && !getenv("FC_NO_L2_ORDER")) A.ele_perm = ctx->d_ele_perm;
+    if (flags & (FC_EVAL_INTERIOR | FC_EVAL_BOUNDARY))
+    {
+      // elements without / with ghost nodes: the interior needs no halo import and can run while it is in flight.
+      // The split lives in the launch-slot order (ele_perm), which only the tensor-core kernels follow.
+      const bool perm_kernel = follows_launch_order(ctx, flags);
+      if (!perm_kernel || pipelined) return fail(ctx, FC_ERR_UNSUPPORTED, "FC_EVAL_INTERIOR/BOUNDARY need one of the tensor-core kernels");
+      A.ele_perm = ctx->d_ele_perm;
+      if ((flags & FC_EVAL_INTERIOR) && !(flags & FC_EVAL_BOUNDARY)) A.n_ele = ctx->n_interior_ele;
+      if ((flags & FC_EVAL_BOUNDARY) && !(flags & FC_EVAL_INTERIOR)) A.ele_offset = ctx->n_interior_ele;
+    }
     if (pipelined)
     {
       // zero the rows a slab touches first on stream2 while the previous slab computes on the main stream
@@ -259,7 +278,7 @@ extern "C"
         e0 = A.n_ele;
       }
     }
-    else if (ctx->n_ele > 0)
+    else if (A.n_ele > A.ele_offset)
       FC_CUDA(want_K ? dispatch<true>(ctx, A, flags) : dispatch<false>(ctx, A, flags));
     FC_CUDA(cudaEventRecord(ctx->ev[2], s));
     ctx->ev_valid = true;

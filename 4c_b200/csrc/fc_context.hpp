@@ -27,6 +27,7 @@ struct fc_ctx
   double* d_gpw = nullptr;   // [ngp] weights
   unsigned char* d_ele_bad = nullptr;  // [n_ele] 1 = det J <= 0 at an element node
   int* d_ele_perm = nullptr; // element order of the tensor-core assembled-path kernels (L2 sweep order, fc_tile_plan.hpp) or nullptr = caller's order
+  int n_interior_ele = 0;    // launch slots [0, n_interior_ele) hold the elements without ghost nodes (FC_EVAL_INTERIOR / _BOUNDARY)
   double* d_geom = nullptr;  // hex8 geometry cache [n_ele][72], built by the first evaluation that uses it
   int geom_bad_count = 0, geom_first_bad_gid = -1;
 

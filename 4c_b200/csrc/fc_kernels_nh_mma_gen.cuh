@@ -51,7 +51,7 @@ namespace fc
     __shared__ int s_bad[EPB];
     __shared__ unsigned char s_slots[Cfg::warps][8][NP];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int ebase = blockIdx.x * EPB;
+    const int ebase = A.ele_offset + blockIdx.x * EPB;  // launch slots [ele_offset, n_ele)
     const double c2 = A.mat.young / (2.0 * (1.0 + A.mat.nue));  // 2c
     const double beta = A.mat.nue / (1.0 - 2.0 * A.mat.nue);
 

@@ -85,6 +85,10 @@ extern "C"
                                     FP64 tensor cores (comparison) */
     FC_EVAL_NO_SLAB_PIPELINE = 8, /* with ZERO_FIRST: one memset + one launch instead of zeroing slab k+1 on a
                                      second stream while slab k computes (comparison) */
+    FC_EVAL_INTERIOR = 32, /* numproc > 1: only the elements without ghost nodes (they need no halo import: evaluate them while
+                              fc_solid_halo_exchange is in flight on another stream) ... */
+    FC_EVAL_BOUNDARY = 64, /* ... then only the elements with ghost nodes, after the import; without FC_EVAL_ZERO_FIRST.
+                              Tensor-core kernels only (FC_ERR_UNSUPPORTED otherwise); both or neither = all elements */
     FC_EVAL_TILE = 16 /* hex8 Neo-Hooke, assembled stiffness: tile kernel (k_hex8_nh_tile) that sums the element matrices of
                          a 16-element tile in shared memory and adds every node-pair block once (43 % fewer reduction
                          sectors, but shared-memory bound: slower than the per-element scatter on B200, DESIGN.md 4.6;

@@ -269,3 +269,35 @@ def test_l2_sweep_order_gives_same_assembly(fc, monkeypatch):
     assert np.max(np.abs(res[0][0] - res[1][0])) <= 1e-13 * np.max(np.abs(res[1][0]))
     assert np.max(np.abs(res[0][1] - res[1][1])) <= 1e-13 * np.max(np.abs(res[1][0]))
     assert fc.capi.l2_sweep_order(g.X, g.conn, 40)[0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ct,form,mat,n,nranks", [(0, DISP, NH, (7, 6, 5), 4), (0, FBAR, NH, (6, 5, 4), 2), (0, DISP, SVK, (6, 5, 4), 3),
+                                                  (1, DISP, NH, (3, 3, 2), 3), (1, DISP, NH, (3, 2, 2), 2)])
+def test_interior_then_boundary_equals_full_evaluation(fc, ct, form, mat, n, nranks):
+    """FC_EVAL_INTERIOR evaluates the elements without ghost nodes (ghost displacements poisoned with NaN: they must not be
+    read), FC_EVAL_BOUNDARY the rest after the halo import; together they give the full evaluation"""
+    for r in range(nranks):
+        g = fc.Grid(ct, n, nranks=nranks, rank=r)
+        s = fc.Solid(0, r, nranks)
+        s.set_mesh(ct, form, g.X, g.node_gid, g.node_owner, g.conn, g.ele_gid)
+        s.set_material(mat, 10.0, 0.3)
+        n_row, n_col, nnz = s.build_graph()
+        u = field(g.X, 0).reshape(-1).copy()
+        K0, f0 = np.zeros(nnz), np.zeros(n_row)
+        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f0, K0, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+        up = u.copy()
+        up[n_row:] = np.nan
+        K1, f1 = np.full(nnz, 9.0), np.full(n_row, 9.0)
+        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, up, f1, K1, flags=fc.FC_EVAL_ZERO_FIRST | fc.FC_EVAL_INTERIOR) == (0, -1)
+        assert np.all(np.isfinite(K1)) and np.all(np.isfinite(f1))
+        if n_col > n_row:
+            assert np.max(np.abs(K1 - K0)) > 0  # the boundary elements are still missing
+        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f1, K1, flags=fc.FC_EVAL_BOUNDARY) == (0, -1)
+        assert np.max(np.abs(K1 - K0)) <= 1e-13 * np.max(np.abs(K0))
+        assert np.max(np.abs(f1 - f0)) <= 1e-13 * np.max(np.abs(K0))
+        # kernels that do not follow the launch-slot order refuse the split
+        with pytest.raises(fc.FourCError) as ei:
+            s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f1, K1, flags=fc.FC_EVAL_INTERIOR | fc.FC_EVAL_FORCE_GENERIC)
+        assert ei.value.code == fc.FC_ERR_UNSUPPORTED
+        s.close()

@@ -49,7 +49,11 @@ namespace fc
     __shared__ int s_rowlen[EPB][NP];
     __shared__ int s_node[EPB][NP];
     __shared__ int s_bad[EPB];
-    __shared__ unsigned char s_slots[Cfg::warps][8][NP];
+    // slot of column node b in the row of node a.  hex27: the whole element map is loaded once in phase 0 (measured 5.77 -> 5.03 ms
+    // at 48^3: inside the tile loop the byte loads' latency was exposed 4 times per element); tet10: per row tile inside the loop
+    // (phase-0 loading measured slower there, 9.9 -> 10.4 ms)
+    constexpr bool SLOTS_PHASE0 = CT == HEX27;
+    __shared__ unsigned char s_slots[SLOTS_PHASE0 ? EPB * NEN : Cfg::warps * 8][NP];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ebase = A.ele_offset + blockIdx.x * EPB;  // launch slots [ele_offset, n_ele)
     const double c2 = A.mat.young / (2.0 * (1.0 + A.mat.nue));  // 2c
@@ -91,6 +95,21 @@ namespace fc
       s_rowlen[el][a] = rl;
       s_node[el][a] = nd;
       if (a == 0) s_bad[el] = (e >= 0 && ele_bad && ele_bad[e]) ? 1 : 0;
+    }
+    if (SLOTS_PHASE0 && WANT_K && A.K)
+    {
+      for (int it = tid; it < EPB * NEN * NP; it += Cfg::threads)
+      {
+        const int el = it / (NEN * NP), aa = (it / NP) % NEN, b = it % NP;
+        const int slot_e = ebase + el;
+        unsigned char v = 0xFF;
+        if (slot_e < A.n_ele && b < NEN)
+        {
+          const int e = A.ele_perm ? __ldg(A.ele_perm + slot_e) : slot_e;
+          v = __ldg(A.slots + ((size_t)e * NEN + aa) * NEN + b);
+        }
+        s_slots[el * NEN + aa][b] = v;
+      }
     }
     __syncthreads();
 
@@ -189,7 +208,7 @@ namespace fc
       }
       const double* E = smem_nhg + (size_t)el * Cfg::ele_doubles;
       const int arow = 8 * mt + a8;  // this lane's row node
-      if (WANT_K && A.K)
+      if (!SLOTS_PHASE0 && WANT_K && A.K)
       {
         // slot rows of the 8 row nodes of this tile
         __syncwarp();
@@ -197,7 +216,7 @@ namespace fc
         {
           const int r = i / NP, b = i % NP;
           const int aa = 8 * mt + r;
-          s_slots[warp][r][b] = (aa < NEN && b < NEN) ? __ldg(A.slots + ((size_t)e * NEN + aa) * NEN + b) : (unsigned char)0xFF;
+          s_slots[warp * 8 + r][b] = (aa < NEN && b < NEN) ? __ldg(A.slots + ((size_t)e * NEN + aa) * NEN + b) : (unsigned char)0xFF;
         }
         __syncwarp();
       }
@@ -293,7 +312,7 @@ namespace fc
               const int rr = 4 * half + r, aa = 8 * mt + rr;
               const bool ok = aa < NEN && bcol < NEN && lane < 24;
               const long long rb = ok ? s_rowbase[el][aa] : -1;
-              const int slot = ok ? (int)s_slots[warp][rr][bcol] : 0;
+              const int slot = ok ? (int)s_slots[SLOTS_PHASE0 ? el * NEN + aa : warp * 8 + rr][bcol] : 0;
               rl[r] = ok ? s_rowlen[el][aa] : 0;
               ptr[r] = rb >= 0 ? A.K + rb + 3 * slot + (ln - 3 * b) : nullptr;
 #pragma unroll

@@ -45,8 +45,12 @@ namespace fc
     //   F-bar: [0..8] sqrt(kappa) j^-1 J (-> ghat), [9..17] (-> v / sqrt(kappa)), [18] sqrt(lambda), [19] sqrt(kappa),
     //          [20..22] centroid gradient g0 of node gp
     //   SVK:   [0..8] sqrt(w detJ) F (-> phat), [9..17] w detJ S (-> t), [18..23] mu w detJ b_ij
-    // 409 doubles per element (the 6-plane Neo-Hooke kernel: 417) -> 4 CTAs per SM
-    static constexpr int oR = 192, rec = 24, oX = 384, ele_doubles = 409;
+    // Record stride 25, not 24: in phase 2 the 8 lanes of a quad column read the same record and the 4 columns read records q
+    // (or 2q) apart; with 24 doubles = 48 words the four addresses fall on banks 0/16/0/16 (0/0/0/0 for 2q) - ncu counted 152 M
+    // excess wavefronts per 10^6 elements, 36 % of the shared-memory traffic of a kernel that sits at 84 % of the l1tex peak.
+    // 25 doubles = 50 words: banks 0/18/4/22 (0/4/8/12).
+    // 417 doubles per element -> still 4 CTAs per SM
+    static constexpr int oR = 192, rec = 25, oX = oR + 8 * rec, ele_doubles = oX + 24 + 1;
     static constexpr int ks_stride = 24;
     static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles;
   };

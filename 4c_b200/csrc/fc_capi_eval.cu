@@ -69,7 +69,8 @@ namespace
         ctx->launches++;
         return cudaGetLastError();
       }
-      auto kern = A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true> : fc::k_hex8_neohooke_mma<WANT_K, false>;
+      auto kern = Ag.ele_perm ? (A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true, true> : fc::k_hex8_neohooke_mma<WANT_K, false, true>)
+                              : (A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true, false> : fc::k_hex8_neohooke_mma<WANT_K, false, false>);
       cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
       if (e != cudaSuccess) return e;
       size_t smem = Cfg::smem_bytes;
@@ -89,7 +90,8 @@ namespace
   cudaError_t launch_hex8_ext(fc_ctx* ctx, const fc::EvalArgs& A)
   {
     using Cfg = fc::Hex8MmaExtCfg;
-    auto kern = A.dbc ? fc::k_hex8_mma_ext<VAR, WANT_K, true> : fc::k_hex8_mma_ext<VAR, WANT_K, false>;
+    auto kern = A.ele_perm ? (A.dbc ? fc::k_hex8_mma_ext<VAR, WANT_K, true, true> : fc::k_hex8_mma_ext<VAR, WANT_K, false, true>)
+                           : (A.dbc ? fc::k_hex8_mma_ext<VAR, WANT_K, true, false> : fc::k_hex8_mma_ext<VAR, WANT_K, false, false>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
     if (e != cudaSuccess) return e;
     kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);

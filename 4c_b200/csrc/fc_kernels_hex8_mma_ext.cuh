@@ -55,7 +55,7 @@ namespace fc
     static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles;
   };
 
-  template <int VAR, bool WANT_K, bool HAS_DBC>
+  template <int VAR, bool WANT_K, bool HAS_DBC, bool HAS_PERM>
   __global__ void __launch_bounds__(Hex8MmaExtCfg::threads, 4) k_hex8_mma_ext(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
   {
     using Cfg = Hex8MmaExtCfg;
@@ -71,7 +71,7 @@ namespace fc
     const int slot_e = A.ele_offset + blockIdx.x * Cfg::epb + wel + el;
     const bool active = slot_e < A.n_ele;
     // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_tile_plan.hpp)
-    const int e = active ? (A.ele_perm ? __ldg(A.ele_perm + slot_e) : slot_e) : -1;
+    const int e = active ? (HAS_PERM ? __ldg(A.ele_perm + slot_e) : slot_e) : -1;  // HAS_PERM: see k_hex8_neohooke_mma
     double* E = smem + (size_t)(wel + el) * Cfg::ele_doubles;
 
     // ---- phase 0: lane (el, t) gathers node t of element el ------------------------------------------
@@ -273,7 +273,7 @@ namespace fc
     for (int k = 0; k < Cfg::epw; ++k)
     {
       if (!((actmask >> (8 * k)) & 1u) || ((badmask >> (8 * k)) & 0xFFu)) continue;  // warp-uniform
-      const int ek = __shfl_sync(0xFFFFFFFFu, e, 8 * k);
+      const int ek = HAS_PERM ? __shfl_sync(0xFFFFFFFFu, e, 8 * k) : A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
       const double* G = smem + (size_t)(wel + k) * Cfg::ele_doubles;
       const int fo0 = frag_idx(q, a), fo1 = frag_idx(q + 4, a);
       const double* R0 = G + Cfg::oR + Cfg::rec * q;

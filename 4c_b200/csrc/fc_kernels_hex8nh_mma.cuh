@@ -55,7 +55,10 @@ namespace fc
   // (the node field is XOR-swizzled with the k-step so that the 8 Gauss-point lanes of phase 1 store conflict-free)
   __device__ __forceinline__ int frag_idx(int gp, int node) { return 32 * (gp >> 2) + 16 * (node >> 2) + 4 * (gp & 3) + ((node & 3) ^ (2 * (gp >> 2))); }
 
-  template <bool WANT_K, bool HAS_DBC>
+  // HAS_PERM: launch slot -> element through EvalArgs::ele_perm (L2 sweep order of large meshes, interior-first order of a
+  // partitioned mesh).  Without it the element is the slot and its index is recomputed instead of kept: measured on one box at C2,
+  // 1.430 ms against 1.466 ms for the variant that carries the indirection (2 more spilled registers at the 96-register limit).
+  template <bool WANT_K, bool HAS_DBC, bool HAS_PERM>
   __global__ void __launch_bounds__(Hex8MmaCfg::threads, 5) k_hex8_neohooke_mma(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
   {
     using Cfg = Hex8MmaCfg;
@@ -72,7 +75,7 @@ namespace fc
     const int slot_e = A.ele_offset + blockIdx.x * Cfg::epb + wel + el;
     const bool active = slot_e < A.n_ele;
     // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_tile_plan.hpp)
-    const int e = active ? (A.ele_perm ? __ldg(A.ele_perm + slot_e) : slot_e) : -1;
+    const int e = active ? (HAS_PERM ? __ldg(A.ele_perm + slot_e) : slot_e) : -1;
     double* E = smem + (size_t)(wel + el) * Cfg::ele_doubles;
 
     // ---- phase 0 ----------------------------------------------------------------------------------
@@ -189,7 +192,14 @@ namespace fc
     const double c2 = A.mat.young / (2.0 * (1.0 + A.mat.nue));  // 2c
     // cached geometric part of s[a][2q], s[a][2q+1], one element ahead of its use
     auto load_sg = [&](int k) -> double2 {
-      const int ek = __shfl_sync(0xFFFFFFFFu, e, (8 * k) & 31);
+      int ek;
+      if (HAS_PERM)
+        ek = __shfl_sync(0xFFFFFFFFu, e, (8 * k) & 31);
+      else
+      {
+        ek = A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
+        if (ek >= A.n_ele) ek = -1;
+      }
       return (k < Cfg::epw && ek >= 0) ? __ldg(reinterpret_cast<const double2*>(A.geom + (size_t)ek * Cfg::geom_doubles) + lane) : make_double2(0.0, 0.0);
     };
     double2 sg_next = load_sg(0);
@@ -199,7 +209,7 @@ namespace fc
       const double2 sg = sg_next;
       sg_next = load_sg(k + 1);
       if (!((actmask >> (8 * k)) & 1u) || ((badmask >> (8 * k)) & 0xFFu)) continue;  // warp-uniform
-      const int ek = __shfl_sync(0xFFFFFFFFu, e, 8 * k);
+      const int ek = HAS_PERM ? __shfl_sync(0xFFFFFFFFu, e, 8 * k) : A.ele_offset + blockIdx.x * Cfg::epb + wel + k;
       const double* G = smem + (size_t)(wel + k) * Cfg::ele_doubles;
       const int fo0 = frag_idx(q, a), fo1 = frag_idx(q + 4, a);
       double fg[3][2];

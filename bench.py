@@ -154,7 +154,7 @@ def run_reference(args):
 
 # dominant kernel per --kernel-flags and its dram__bytes_read.sum + dram__bytes_write.sum per launch at C2 from the committed
 # ncu captures (profiles/)
-KERNEL_NAME = {0: "k_hex8_neohooke_mma<true,false>", 16: "k_hex8_nh_tile<false>", 4: "k_hex8_neohooke<true>", 2: "k_generic<HEX8,DISP,true>"}
+KERNEL_NAME = {0: "k_hex8_neohooke_mma<true,false,false>", 16: "k_hex8_nh_tile<false>", 4: "k_hex8_neohooke<true>", 2: "k_generic<HEX8,DISP,true>"}
 TRAFFIC = {0: 4.083e9, 16: 5.115e9}  # profiles/r01_mma_kernel_ncu_full_c.md, profiles/r01_tile_kernel_ncu.md
 
 

@@ -58,8 +58,10 @@ namespace fc
   // HAS_PERM: launch slot -> element through EvalArgs::ele_perm (L2 sweep order of large meshes, interior-first order of a
   // partitioned mesh).  Without it the element is the slot and its index is recomputed instead of kept: measured on one box at C2,
   // 1.430 ms against 1.466 ms for the variant that carries the indirection (2 more spilled registers at the 96-register limit).
+  // Occupancy: 4 CTAs per SM for the stiffness kernel (123 registers, nothing spilled; with 5 CTAs the 96-register limit spilled 8
+  // registers: same box at C2 1.404 -> 1.366 ms), 5 for the force-only kernel (0.58 vs 0.62 ms).
   template <bool WANT_K, bool HAS_DBC, bool HAS_PERM>
-  __global__ void __launch_bounds__(Hex8MmaCfg::threads, 5) k_hex8_neohooke_mma(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
+  __global__ void __launch_bounds__(Hex8MmaCfg::threads, WANT_K ? 4 : 5) k_hex8_neohooke_mma(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
   {
     using Cfg = Hex8MmaCfg;
     extern __shared__ __align__(16) double smem_mma[];

@@ -103,10 +103,22 @@ namespace
   cudaError_t launch_nh_gen(fc_ctx* ctx, const fc::EvalArgs& A)
   {
     using Cfg = fc::NhGenCfg<CT>;
+    fc::EvalArgs Ag = A;
+    if (Cfg::geom)
+    {
+      if (!ctx->d_geom)  // geometry cache: once per mesh
+      {
+        cudaError_t eg = cudaMalloc((void**)&ctx->d_geom, sizeof(double) * Cfg::geom_doubles * (size_t)ctx->n_ele);
+        if (eg != cudaSuccess) return eg;
+        fc::k_gen_geom_cache<CT><<<ctx->n_ele, 128, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->n_ele, ctx->d_dNtab, ctx->d_gpw, ctx->d_geom);
+        ctx->launches++;
+      }
+      Ag.geom = ctx->d_geom;
+    }
     auto kern = A.dbc ? fc::k_nh_mma_gen<CT, WANT_K, true> : fc::k_nh_mma_gen<CT, WANT_K, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
     if (e != cudaSuccess) return e;
-    kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+    kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(Ag, ctx->d_ele_bad);
     ctx->launches++;
     return cudaGetLastError();
   }

@@ -31,13 +31,65 @@ namespace fc
     static constexpr int epb = CT == TET10 ? 8 : (CT == HEX27 ? 1 : 4);
     static constexpr int warps = 4, threads = 32 * warps;
     static constexpr int plane = KS * MT * 32;
-    static constexpr int oInv = 6 * plane;           // [GP4][20]: sk*j^-1 (9), sl*J^-1 (9) | scratch: inv, det
+    // hex27 reads s_ab / 2c = sum_gp w detJ grad N_a . grad N_b and detJ from a geometry cache (k_gen_geom_cache, once per
+    // mesh, like the hex8 kernel): the three nhat planes, J^-1 and 3 of the 12 DMMA per tile step go away, the element needs
+    // 22 KB of shared memory less.  tet10 recomputes them (its cache would add 28 % to the bytes the kernel moves).
+    static constexpr bool geom = CT == HEX27;
+    static constexpr int nplanes = geom ? 3 : 6;
+    static constexpr int geom_doubles = 2 * 32 * MT * MT + ((ngp + 7) & ~7);  // [mt][nt][lane][2] accumulator layout, then detJ[gp]
+    static constexpr int oInv = nplanes * plane;     // [GP4][20]: sk*j^-1 (9), sl*J^-1 (9) | scratch: inv, det
     static constexpr int oX = oInv + GP4 * 20;       // [NP][3] current coordinates rel. node 0, zero padded
     static constexpr int oXm = oX + 3 * NP;          // [nen][3] material coordinates rel. node 0
     static constexpr int ele_doubles = (oXm + 3 * nen + 1) & ~1;
     static constexpr int stage = 288;                // per warp: 12 rows x 24
     static constexpr size_t smem_bytes = sizeof(double) * ((size_t)epb * ele_doubles + warps * stage);
   };
+
+  // geometry cache of k_nh_mma_gen (cells with NhGenCfg::geom): per element G[a][b] = sum_gp w detJ grad N_a . grad N_b in the
+  // accumulator layout of the (mt, nt) tiles - lane (a8, q) holds (8 mt + a8, 8 nt + 2 q + {0, 1}) - followed by detJ at the Gauss
+  // points.  evaluate_jacobian_mapping (4C_solid_3D_ele_calc_lib.hpp:435-448) on the reference coordinates: constant for a mesh.
+  template <int CT>
+  __global__ void __launch_bounds__(128) k_gen_geom_cache(const double* __restrict__ X, const int* __restrict__ conn, int n_ele,
+      const double* __restrict__ dNtab, const double* __restrict__ gpw, double* __restrict__ geom)
+  {
+    using Cfg = NhGenCfg<CT>;
+    constexpr int NEN = Cfg::nen, NGP = Cfg::ngp, MT = Cfg::MT;
+    __shared__ double sX[NEN][3];
+    __shared__ double sN[NGP][NEN][3];  // sqrt(w detJ) J^-1 dN_a
+    const int e = blockIdx.x, tid = threadIdx.x;
+    if (e >= n_ele) return;
+    double* out = geom + (size_t)e * Cfg::geom_doubles;
+    for (int i = tid; i < 3 * NEN; i += blockDim.x)
+    {
+      const int a = i / 3, d = i % 3;
+      sX[a][d] = X[3 * (size_t)conn[(size_t)e * NEN + a] + d] - X[3 * (size_t)conn[(size_t)e * NEN] + d];
+    }
+    __syncthreads();
+    for (int gp = tid; gp < NGP; gp += blockDim.x)
+    {
+      const double* dN = dNtab + (size_t)gp * NEN * 3;
+      double M[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Mi[9];
+      for (int a = 0; a < NEN; ++a)
+        for (int d = 0; d < 3; ++d)
+          for (int i = 0; i < 3; ++i) M[3 * d + i] += dN[3 * a + d] * sX[a][i];
+      const double detJ = inv3(M, Mi);
+      const double wd = gpw[gp] * detJ, sd = sqrt(wd > 0.0 ? wd : 0.0);
+      for (int a = 0; a < NEN; ++a)
+        for (int i = 0; i < 3; ++i) sN[gp][a][i] = sd * (Mi[3 * i] * dN[3 * a] + Mi[3 * i + 1] * dN[3 * a + 1] + Mi[3 * i + 2] * dN[3 * a + 2]);
+      out[2 * 32 * MT * MT + gp] = detJ;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < 2 * 32 * MT * MT; idx += blockDim.x)
+    {
+      const int c = idx & 1, ln = (idx >> 1) & 31, tile = idx >> 6;
+      const int a = 8 * (tile / MT) + (ln >> 2), b = 8 * (tile % MT) + 2 * (ln & 3) + c;
+      double g = 0.0;
+      if (a < NEN && b < NEN)
+        for (int gp = 0; gp < NGP; ++gp)
+          for (int d = 0; d < 3; ++d) g += sN[gp][a][d] * sN[gp][b][d];
+      out[idx] = g;
+    }
+  }
 
   template <int CT, bool WANT_K, bool HAS_DBC>
   __global__ void __launch_bounds__(NhGenCfg<CT>::threads) k_nh_mma_gen(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
@@ -119,6 +171,12 @@ namespace fc
       const int which = it & 1, gp = (it >> 1) % NGP, el = (it >> 1) / NGP;
       if (ebase + el >= A.n_ele) continue;
       double* E = smem_nhg + (size_t)el * Cfg::ele_doubles;
+      if (Cfg::geom && which == 0)
+      {
+        const int eg = A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el;
+        E[Cfg::oInv + gp * 20 + 18] = __ldg(A.geom + (size_t)eg * Cfg::geom_doubles + 2 * 32 * MT * MT + gp);  // detJ
+        continue;
+      }
       const double* crd = E + (which ? Cfg::oX : Cfg::oXm);
       const double* dN = A.dNtab + (size_t)gp * NEN * 3;
       double M[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
@@ -159,7 +217,7 @@ namespace fc
       for (int i = 0; i < 9; ++i)
       {
         R[i] *= sk;
-        R[9 + i] *= sl;
+        if (!Cfg::geom) R[9 + i] *= sl;
       }
       R[18] = sk;
     }
@@ -182,12 +240,12 @@ namespace fc
         for (int i = 0; i < 3; ++i)
         {
           out[i] = R[3 * i] * d0 + R[3 * i + 1] * d1 + R[3 * i + 2] * d2;
-          out[3 + i] = R[9 + 3 * i] * d0 + R[9 + 3 * i + 1] * d1 + R[9 + 3 * i + 2] * d2;
+          if (!Cfg::geom) out[3 + i] = R[9 + 3 * i] * d0 + R[9 + 3 * i + 1] * d1 + R[9 + 3 * i + 2] * d2;
         }
       }
       const int off = (ks * MT + mt) * 32 + lane;
 #pragma unroll
-      for (int c = 0; c < 6; ++c) E[c * Cfg::plane + off] = out[c];
+      for (int c = 0; c < Cfg::nplanes; ++c) E[c * Cfg::plane + off] = out[c];
     }
     __syncthreads();
 
@@ -221,9 +279,13 @@ namespace fc
         __syncwarp();
       }
       double fpart[3] = {0.0, 0.0, 0.0};
+      const double2* const gtile = Cfg::geom ? reinterpret_cast<const double2*>(A.geom + (size_t)e * Cfg::geom_doubles) + (size_t)mt * MT * 32 + lane : nullptr;
+      double2 sg_next = Cfg::geom ? __ldg(gtile) : make_double2(0.0, 0.0);
 #pragma unroll 1
       for (int nt = 0; nt < MT; ++nt)
       {
+        const double2 sg = sg_next;
+        if (Cfg::geom && nt + 1 < MT) sg_next = __ldg(gtile + 32 * (nt + 1));
         double W[3][3][2], sa[3][2];
 #pragma unroll
         for (int i = 0; i < 3; ++i)
@@ -238,7 +300,7 @@ namespace fc
           double fa[6], fb[6];
           const int oa = (ks * MT + mt) * 32 + lane, ob = (ks * MT + nt) * 32 + lane;
 #pragma unroll
-          for (int c = 0; c < 6; ++c)
+          for (int c = 0; c < Cfg::nplanes; ++c)
           {
             fa[c] = E[c * Cfg::plane + oa];
             fb[c] = E[c * Cfg::plane + ob];
@@ -246,7 +308,7 @@ namespace fc
 #pragma unroll
           for (int i = 0; i < 3; ++i)
           {
-            dmma884(sa[i][0], sa[i][1], fa[3 + i], fb[3 + i]);
+            if (!Cfg::geom) dmma884(sa[i][0], sa[i][1], fa[3 + i], fb[3 + i]);
             if (WANT_K)
             {
 #pragma unroll
@@ -254,7 +316,7 @@ namespace fc
             }
           }
         }
-        const double s0 = sa[0][0] + sa[1][0] + sa[2][0], s1 = sa[0][1] + sa[1][1] + sa[2][1];
+        const double s0 = Cfg::geom ? c2 * sg.x : sa[0][0] + sa[1][0] + sa[2][0], s1 = Cfg::geom ? c2 * sg.y : sa[0][1] + sa[1][1] + sa[2][1];
         {
           const double* xk = E + Cfg::oX + 3 * (8 * nt + b0);
 #pragma unroll

@@ -54,9 +54,9 @@ namespace fc
     {
       const int k = m / 3;
       const double xv = __ldg(x + 3 * (long long)__ldg(adj + k) + (m - 3 * k));
-      s0 += __ldcs(r0 + m) * xv;
-      s1 += __ldcs(r0 + L3 + m) * xv;
-      s2 += __ldcs(r0 + 2 * L3 + m) * xv;
+      s0 += __ldg(r0 + m) * xv;
+      s1 += __ldg(r0 + L3 + m) * xv;
+      s2 += __ldg(r0 + 2 * L3 + m) * xv;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1)
@@ -68,8 +68,9 @@ namespace fc
     if (lane < 3) y[3 * (long long)a + lane] = lane == 0 ? s0 : (lane == 1 ? s1 : s2);
   }
 
-  // (measured on B200 at C2: this kernel with 128-thread blocks 0.425 ms = 4.99 TB/s; a variant striding over the 9 L
-  // contiguous values of a node: 0.80 ms; a variant issuing the loads of all three passes first: 0.55 ms)
+  // (measured on B200 at C2: this kernel with 128-thread blocks 0.408 ms = 5.21 TB/s; with streaming loads (ld.global.cs) of K
+  // 0.428 ms - the 8-byte aligned rows share sectors between passes, L1 keeps them; a variant striding over the 9 L contiguous
+  // values of a node: 0.80 ms; a variant issuing the loads of all three passes first: 0.55 ms)
 
   // inverse of the 3x3 diagonal block of every owned node (node-block Jacobi); a singular block falls back to identity
   static __global__ void k_block_jacobi_setup(const long long* __restrict__ nodeptr, const int* __restrict__ diagpos, int n_row_nodes,

@@ -29,7 +29,7 @@ EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
     "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_graph", "fc_solid_build_graph",
     "fc_solid_graph_sizes", "fc_solid_set_slab_count", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
-    "fc_solid_error_state", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_elements",
+    "fc_solid_error_state", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_evaluate_elements",
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack", "fc_solid_halo_set_counts", "fc_solid_halo_exchange",
     "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
@@ -295,6 +295,11 @@ class Solid:
         nodal = np.zeros((self.n_row_dof // 3, 6)) if want_nodal else None
         self._chk(lib().fc_solid_evaluate_stress(self.h, _ptr(u_col), C.c_int(stress_type), _ptr(gp), _ptr(nodal)))
         return gp, nodal
+
+    def evaluate_stress_noalloc(self, u_col_dev, nodal_dev, stress_type=1):
+        """fc_solid_evaluate_stress_noalloc: nodal stresses into the device tensor nodal_dev [n_row_nodes, 6]; allocates
+        nothing, does not synchronise (fixed scratch inside the library, see include/fourc_b200.h for the limits)"""
+        self._chk(lib().fc_solid_evaluate_stress_noalloc(self.h, _ptr(u_col_dev), C.c_int(stress_type), _ptr(nodal_dev)))
 
     def evaluate_elements(self, u_col, want_K=True, flags=0):
         nd = 3 * self.nen

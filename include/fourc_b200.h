@@ -173,6 +173,21 @@ extern "C"
   };
   int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int stress_type, double* gp_stress, double* nodal_stress);
 
+  /* Nodal stresses as fc_solid_evaluate_stress computes them (Gauss-point stresses extrapolated to the nodes and averaged),
+   * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+   * NO COUNTERPART IN THE REFERENCE.
+   * The call allocates nothing (no cudaMalloc / cudaFree / pinned or library allocation) and does not synchronise: its
+   * scratch (Gauss-point stresses, extrapolation matrix, elements-per-node counts) is one fixed device array of about
+   * 1.7 MB inside the library, held by every GPU that loads it until exit.  Limits: n_col_ele * ngp <=
+   * FC_NOALLOC_MAX_GAUSS_POINTS and n_col_nodes <= FC_NOALLOC_MAX_COL_NODES; beyond them the call returns FC_ERR_INVALID
+   * with a message naming the limit (use fc_solid_evaluate_stress then).  u_col_dev [n_col_dof] and nodal_stress_dev
+   * [n_row_nodes][6] must be DEVICE buffers (a host buffer would need staging, i.e. an allocation).  All calls on one GPU
+   * share the array, which keeps the previous call's contents (the call clears what must start at zero): calls that
+   * overlap on the GPU (different streams or contexts of one device) race; serialise them. */
+#define FC_NOALLOC_MAX_GAUSS_POINTS 32768
+#define FC_NOALLOC_MAX_COL_NODES 32768
+  int fc_solid_evaluate_stress_noalloc(fc_ctx* ctx, const double* u_col_dev, int stress_type, double* nodal_stress_dev);
+
   /* Element-local evaluation without scatter (Solid::evaluate seam, 4C_solid_3D_ele.hpp:120-124):
    * fe [n_col_ele][3*nen], Ke [n_col_ele][3*nen][3*nen] column-major per element, in the caller's
    * element order.  host|device.  Ke may be NULL. */

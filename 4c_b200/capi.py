@@ -16,7 +16,7 @@ FC_HEX8, FC_HEX27, FC_TET10 = 0, 1, 2
 FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
-FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_NO_SLAB_PIPELINE, FC_EVAL_TILE = 1, 2, 4, 8, 16
+FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_OWNER_COMPUTED = 1, 2, 4, 8
 FC_EVAL_INTERIOR, FC_EVAL_BOUNDARY = 32, 64
 FC_STRESS_2PK, FC_STRESS_CAUCHY = 0, 1
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
@@ -28,14 +28,14 @@ NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10}
 EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
     "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_graph", "fc_solid_build_graph",
-    "fc_solid_graph_sizes", "fc_solid_set_slab_count", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
-    "fc_solid_error_state", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_evaluate_elements",
+    "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
+    "fc_solid_error_state", "fc_solid_error_allreduce", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_evaluate_elements",
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack", "fc_solid_halo_set_counts", "fc_solid_halo_exchange",
     "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
     "fc_grid_halo_counts", "fc_grid_halo_send_nodes", "fc_probe_fp64_fma", "fc_probe_fp64_mma",
     "fc_solid_set_comm", "fc_solid_set_dirichlet_toggle", "fc_solid_apply_dirichlet", "fc_solid_apply_dirichlet_to_system", "fc_solid_spmv", "fc_solid_linear_solve",
-    "fc_l2_sweep_order", "fc_tile_plan_create", "fc_tile_plan_sizes", "fc_tile_plan_get", "fc_tile_plan_destroy",
+    "fc_l2_sweep_order", "fc_brick_plan_create", "fc_brick_plan_sizes", "fc_brick_plan_get", "fc_brick_plan_destroy",
 ]
 
 
@@ -99,27 +99,29 @@ def probe_fp64(device=0):
     return a.value, b.value
 
 
-def tile_plan(X, conn, n_row_nodes, nodeptr, nodeadj):
-    """hex8 tile plan as plain arrays (fc_tile_plan_*; host integer code, no device needed): dict with n_tiles,
-    max_blocks, tile_ele [n_tiles,16], tile_blk [n_tiles,16,32], tile_ptr, rec, rownode; None if the mesh has no plan"""
+def brick_plan(X, conn, n_row_nodes, max_row_nodes=27, chunk=0):
+    """brick plan of the owner-computed hex8 assembly as plain arrays (fc_brick_plan_*; host integer code, no device needed):
+    dict with n_units, n_interior_units, chunk, n_element_instances, unit_planes, unit_node_off, unit_ele_off, node_tab,
+    ele_tab, rowidx_tab [entries, 8] (bytes); None if the mesh is not a lattice of hex cells"""
     L = lib()
     X, conn = _f64(X), _i32(conn)
-    nodeptr, nodeadj = np.ascontiguousarray(nodeptr, dtype=np.int64), _i32(nodeadj)
     h = C.c_void_p()
-    rc = L.fc_tile_plan_create(C.c_int(X.size // 3), _ptr(X), C.c_int(conn.size // 8), _ptr(conn), C.c_int(n_row_nodes),
-                               _ptr(nodeptr), _ptr(nodeadj), C.byref(h))
+    rc = L.fc_brick_plan_create(C.c_int(X.size // 3), _ptr(X), C.c_int(conn.size // 8), _ptr(conn), C.c_int(n_row_nodes),
+                                C.c_int(max_row_nodes), C.c_int(chunk), C.byref(h))
     if rc == FC_ERR_GRAPH:
         return None
     if rc != 0:
-        raise FourCError(rc, "fc_tile_plan_create")
-    nt, nb, mb = C.c_int(), C.c_int64(), C.c_int()
-    L.fc_tile_plan_sizes(h, C.byref(nt), C.byref(nb), C.byref(mb))
-    out = dict(n_tiles=nt.value, max_blocks=mb.value,
-               tile_ele=np.zeros((nt.value, 16), np.int32), tile_blk=np.zeros((nt.value, 16, 32), np.uint32),
-               tile_ptr=np.zeros(nt.value + 1, np.int64), rec=np.zeros(nb.value, np.uint64), rownode=np.zeros(nb.value, np.int32))
-    L.fc_tile_plan_get(h, _ptr(out["tile_ele"]), _ptr(out["tile_blk"]), _ptr(out["tile_ptr"]), _ptr(out["rec"]), _ptr(out["rownode"]))
-    L.fc_tile_plan_destroy.restype = None
-    L.fc_tile_plan_destroy(h)
+        raise FourCError(rc, "fc_brick_plan_create")
+    nu, ni, ch, nn, ne, inst = C.c_int(), C.c_int(), C.c_int(), C.c_int64(), C.c_int64(), C.c_int64()
+    L.fc_brick_plan_sizes(h, C.byref(nu), C.byref(ni), C.byref(ch), C.byref(nn), C.byref(ne), C.byref(inst))
+    out = dict(n_units=nu.value, n_interior_units=ni.value, chunk=ch.value, n_element_instances=inst.value,
+               unit_planes=np.zeros(nu.value, np.int32), unit_node_off=np.zeros(nu.value, np.int64), unit_ele_off=np.zeros(nu.value, np.int64),
+               node_tab=np.zeros(nn.value, np.int32), ele_tab=np.zeros(ne.value, np.int32), rowidx_tab=np.zeros(ne.value, np.uint64))
+    L.fc_brick_plan_get(h, _ptr(out["unit_planes"]), _ptr(out["unit_node_off"]), _ptr(out["unit_ele_off"]), _ptr(out["node_tab"]),
+                        _ptr(out["ele_tab"]), _ptr(out["rowidx_tab"]))
+    L.fc_brick_plan_destroy.restype = None
+    L.fc_brick_plan_destroy(h)
+    out["rowidx_tab"] = out["rowidx_tab"].view(np.uint8).reshape(-1, 8)  # little endian: byte a = local node a
     return out
 
 
@@ -228,9 +230,6 @@ class Solid:
         self.n_row_dof, self.n_col_dof, self.nnz = a.value, b.value, n.value
         return a.value, b.value, n.value
 
-    def set_slab_count(self, n):
-        self._chk(lib().fc_solid_set_slab_count(self.h, C.c_int(n)))
-
     def get_graph(self):
         rowptr = np.zeros(self.n_row_dof + 1, np.int64)
         colind = np.zeros(self.nnz, np.int32)
@@ -280,6 +279,22 @@ class Solid:
         if rc not in (FC_OK, FC_ERR_NEGATIVE_JACOBIAN):
             self._chk(rc)
         return cnt.value, gid.value
+
+    def error_allreduce(self):
+        """eval_error_check: 1 if any rank of the communicator (set_comm) had an element failure in its last evaluation"""
+        flag = C.c_int(0)
+        self._chk(lib().fc_solid_error_allreduce(self.h, C.byref(flag)))
+        return flag.value
+
+    def set_comm(self, nccl_comm):
+        self._chk(lib().fc_solid_set_comm(self.h, C.c_void_p(nccl_comm)))
+
+    def halo_set_counts(self, send_dof_count, recv_dof_count):
+        s_, r_ = _i32(send_dof_count), _i32(recv_dof_count)
+        self._chk(lib().fc_solid_halo_set_counts(self.h, _ptr(s_), _ptr(r_)))
+
+    def halo_exchange(self, nccl_comm, u_col_dev):
+        self._chk(lib().fc_solid_halo_exchange(self.h, C.c_void_p(nccl_comm), _ptr(u_col_dev)))
 
     def zero(self, f_row=None, K_values=None):
         self._chk(lib().fc_solid_zero(self.h, _ptr(f_row), _ptr(K_values)))

@@ -9,12 +9,11 @@
 
 #include "../../include/fourc_b200.h"
 #include "fc_context.hpp"
-#include <cstdlib>
-
 #include "fc_host_util.hpp"
-#include "fc_tile_plan.hpp"
 #include "fc_kernels_setup.cuh"
+#include "fc_sweep_order.hpp"
 
+void fc_free_brick_plan(fc_ctx* ctx);  // fc_capi_graph.cu
 
 extern "C"
 {
@@ -39,16 +38,13 @@ extern "C"
     ctx->device = device;
     ctx->rank = rank;
     ctx->nranks = nranks;
-    if (cudaMalloc((void**)&ctx->d_err, 2 * sizeof(int)) != cudaSuccess ||
+    if (cudaMalloc((void**)&ctx->d_err, 3 * sizeof(int)) != cudaSuccess ||
         cudaMallocHost((void**)&ctx->h_err_pinned, 2 * sizeof(int)) != cudaSuccess)
     {
       delete ctx;
       return FC_ERR_CUDA;
     }
     for (auto& e : ctx->ev) cudaEventCreate(&e);
-    cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking);
-    for (auto& e : ctx->ev_slab) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&ctx->ev_start, cudaEventDisableTiming);
     *out = ctx;
     return FC_OK;
   }
@@ -68,11 +64,7 @@ extern "C"
     dev_free(ctx->d_node_rowbase);
     dev_free(ctx->d_node_rowlen);
     dev_free(ctx->d_slots);
-    dev_free(ctx->d_tile_ele);
-    dev_free(ctx->d_tile_blk);
-    dev_free(ctx->d_tile_ptr);
-    dev_free(ctx->d_tile_rec);
-    dev_free(ctx->d_tile_rownode);
+    fc_free_brick_plan(ctx);
     dev_free(ctx->d_dbc);
     dev_free(ctx->d_nodeptr);
     dev_free(ctx->d_nodeadj);
@@ -91,10 +83,6 @@ extern "C"
     if (ctx->h_err_pinned) cudaFreeHost(ctx->h_err_pinned);
     for (auto& e : ctx->ev)
       if (e) cudaEventDestroy(e);
-    for (auto& e : ctx->ev_slab)
-      if (e) cudaEventDestroy(e);
-    if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
-    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     delete ctx;
   }
 
@@ -135,7 +123,12 @@ extern "C"
     int n_row = 0;
     while (n_row < n_col_nodes && node_owner[n_row] == ctx->rank) ++n_row;
     for (int i = n_row; i < n_col_nodes; ++i)
+    {
       if (node_owner[i] == ctx->rank) return fail(ctx, FC_ERR_INVALID, "owned nodes must precede ghost nodes");
+      if (node_owner[i] < 0 || node_owner[i] >= ctx->nranks) return fail(ctx, FC_ERR_INVALID, "node owner out of range");
+      // the halo import lands rank p's message behind the messages of the ranks below p (fc_solid_halo_exchange)
+      if (i > n_row && node_owner[i] < node_owner[i - 1]) return fail(ctx, FC_ERR_INVALID, "ghost nodes must be grouped by ascending owner rank");
+    }
     for (size_t i = 0; i < (size_t)n_col_ele * nen; ++i)
       if (conn[i] < 0 || conn[i] >= n_col_nodes) return fail(ctx, FC_ERR_INVALID, "connectivity entry out of range");
     ctx->celltype = celltype;
@@ -147,7 +140,15 @@ extern "C"
     ctx->h_conn.assign(conn, conn + (size_t)n_col_ele * nen);
     ctx->h_node_owner.assign(node_owner, node_owner + n_col_nodes);
     ctx->h_ele_gid.assign(ele_gid, ele_gid + n_col_ele);
+    // everything that describes the previous mesh goes: graph, halo plan, solver state, plans
     ctx->have_graph = false;
+    ctx->n_send = 0;
+    ctx->halo_send_count.clear();
+    ctx->halo_recv_count.clear();
+    dev_free(ctx->d_Dinv);
+    ctx->Dinv_cap = 0;
+    ctx->n_toggle = 0;
+    fc_free_brick_plan(ctx);
     ctx->n_col_dof = 3 * n_col_nodes;
     ctx->n_row_dof = 3 * n_row;
     FC_CUDA(dev_upload(ctx->d_X, X, (size_t)3 * n_col_nodes, ctx->stream));
@@ -168,9 +169,8 @@ extern "C"
       // 37 KB per element).  More than one rank: elements without ghost nodes first, so that they can be evaluated while the
       // halo import is in flight (FC_EVAL_INTERIOR, then FC_EVAL_BOUNDARY).
       std::vector<int> perm;
-      const char* le = getenv("FC_L2_LAYER_ELEMS");
       const long long budget = celltype == FC_HEX8 ? 12000 : (celltype == FC_TET10 ? 8500 : 650);
-      if (!getenv("FC_NO_L2_ORDER")) fc_host::l2_sweep_order(n_col_nodes, X, n_col_ele, nen, conn, le ? atoll(le) : budget, perm);
+      fc_host::l2_sweep_order(n_col_nodes, X, n_col_ele, nen, conn, budget, perm);
       ctx->n_interior_ele = n_col_ele;
       if (n_row < n_col_nodes)
       {
@@ -188,8 +188,6 @@ extern "C"
       }
       if (!perm.empty()) FC_CUDA(dev_upload(ctx->d_ele_perm, perm.data(), perm.size(), ctx->stream));
     }
-    ctx->n_tiles = 0;  // the tile plan belongs to the graph of the previous mesh
-    ctx->tile_plan_tried = false;
     ctx->geom_bad_count = 0;
     ctx->geom_first_bad_gid = -1;
     if (n_col_ele > 0)

@@ -1,21 +1,21 @@
 // The hot path: fc_solid_evaluate and friends.  Kernel selection:
-//   hex8 + displacement-based + CoupNeoHooke -> closed-form kernel on FP64 tensor cores
-//                                               (fc_kernels_hex8nh_mma.cuh), or its FP64-FMA
-//                                               sibling with FC_EVAL_CLOSED_FORM_FMA
+//   hex8 + displacement-based + CoupNeoHooke -> closed-form kernel on FP64 tensor cores with per-element reductions
+//                                               (fc_kernels_hex8nh_mma.cuh); with FC_EVAL_OWNER_COMPUTED on a lattice
+//                                               mesh owner-computed rows with plain stores (fc_kernels_hex8nh_brick.cuh);
+//                                               or the FP64-FMA sibling with FC_EVAL_CLOSED_FORM_FMA
 //   everything else (and FC_EVAL_FORCE_GENERIC) -> generic B-operator kernel (fc_kernels_generic.cuh)
 #include <climits>
-#include <cstdlib>
 
 #include "fc_host_util.hpp"
 #include "fc_kernels_generic.cuh"
 #include "fc_kernels_hex8nh.cuh"
+#include "fc_kernels_hex8nh_brick.cuh"
 #include "fc_kernels_hex8nh_mma.cuh"
-#include "fc_kernels_hex8nh_tile.cuh"
 #include "fc_kernels_hex8_mma_ext.cuh"
 #include "fc_kernels_nh_mma_gen.cuh"
 #include "fc_kernels_setup.cuh"
 
-int fc_build_tile_plan(fc_ctx* ctx);  // fc_capi_graph.cu
+int fc_build_brick_plan(fc_ctx* ctx);  // fc_capi_graph.cu
 
 namespace
 {
@@ -32,8 +32,18 @@ namespace
     return cudaGetLastError();
   }
 
+  cudaError_t ensure_hex8_geom(fc_ctx* ctx)
+  {
+    if (ctx->d_geom) return cudaSuccess;  // geometry cache: once per mesh
+    cudaError_t eg = cudaMalloc((void**)&ctx->d_geom, sizeof(double) * fc::Hex8MmaCfg::geom_doubles * (size_t)ctx->n_ele);
+    if (eg != cudaSuccess) return eg;
+    fc::k_hex8_geom_cache<<<ctx->n_ele, 64, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->n_ele, ctx->d_geom);
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
   template <bool WANT_K>
-  cudaError_t launch_hex8nh(fc_ctx* ctx, const fc::EvalArgs& A, bool fma_variant, bool allow_tile)
+  cudaError_t launch_hex8nh(fc_ctx* ctx, const fc::EvalArgs& A, bool fma_variant)
   {
     if (fma_variant)
     {
@@ -46,42 +56,36 @@ namespace
     else
     {
       using Cfg = fc::Hex8MmaCfg;
-      if (!ctx->d_geom)  // geometry cache: once per mesh
-      {
-        cudaError_t eg = cudaMalloc((void**)&ctx->d_geom, sizeof(double) * Cfg::geom_doubles * (size_t)ctx->n_ele);
-        if (eg != cudaSuccess) return eg;
-        fc::k_hex8_geom_cache<<<ctx->n_ele, 64, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->n_ele, ctx->d_geom);
-        ctx->launches++;
-      }
+      cudaError_t e = ensure_hex8_geom(ctx);
+      if (e != cudaSuccess) return e;
       fc::EvalArgs Ag = A;
       Ag.geom = ctx->d_geom;
-      // assembled stiffness of the whole mesh: tile kernel (element matrices of a 16-element tile pre-reduced in smem)
-      if (WANT_K && allow_tile && A.K && !A.Ke_out && !A.fe_out && A.ele_offset == 0 && A.n_ele == ctx->n_ele && fc_build_tile_plan(ctx) == FC_OK &&
-          ctx->n_tiles > 0)
-      {
-        using TCfg = fc::Hex8TileCfg;
-        fc::TilePlanDev P{ctx->d_tile_ele, ctx->d_tile_blk, ctx->d_tile_ptr, ctx->d_tile_rec, 0, ctx->n_tiles};
-        auto tkern = A.dbc ? fc::k_hex8_nh_tile<true> : fc::k_hex8_nh_tile<false>;
-        const size_t tsmem = TCfg::smem_bytes(ctx->tile_max_blocks);
-        cudaError_t e = cudaFuncSetAttribute(tkern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
-        if (e != cudaSuccess) return e;
-        tkern<<<ctx->n_tiles, TCfg::threads, tsmem, ctx->stream>>>(Ag, P, ctx->d_ele_bad);
-        ctx->launches++;
-        return cudaGetLastError();
-      }
       auto kern = Ag.ele_perm ? (A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true, true> : fc::k_hex8_neohooke_mma<WANT_K, false, true>)
                               : (A.dbc ? fc::k_hex8_neohooke_mma<WANT_K, true, false> : fc::k_hex8_neohooke_mma<WANT_K, false, false>);
-      cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+      e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
       if (e != cudaSuccess) return e;
-      size_t smem = Cfg::smem_bytes;
-      if (const char* x = getenv("FC_DEBUG_EXTRA_SMEM"))  // experiments only: lowers the CTAs per SM
-      {
-        smem += (size_t)atoi(x);
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-      }
-      kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, smem, ctx->stream>>>(Ag, ctx->d_ele_bad);
+      kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(Ag, ctx->d_ele_bad);
     }
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
+  // owner-computed assembly of the units [u0, u1) of the brick plan; store = the rows are written (FC_EVAL_ZERO_FIRST),
+  // otherwise added to what the caller's K and f hold
+  cudaError_t launch_hex8_brick(fc_ctx* ctx, const fc::EvalArgs& A, int u0, int u1, bool store)
+  {
+    using Cfg = fc::Hex8BrickCfg;
+    if (u1 <= u0) return cudaSuccess;
+    cudaError_t e = ensure_hex8_geom(ctx);
+    if (e != cudaSuccess) return e;
+    fc::EvalArgs Ag = A;
+    Ag.geom = ctx->d_geom;
+    fc::BrickPlanDev P{ctx->d_brick_planes, ctx->d_brick_node_off, ctx->d_brick_ele_off, ctx->d_brick_nodes, ctx->d_brick_eles, ctx->d_brick_rows, u0};
+    auto kern = store ? (A.dbc ? fc::k_hex8_nh_brick<true, true> : fc::k_hex8_nh_brick<true, false>)
+                      : (A.dbc ? fc::k_hex8_nh_brick<false, true> : fc::k_hex8_nh_brick<false, false>);
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+    if (e != cudaSuccess) return e;
+    kern<<<u1 - u0, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(Ag, P, ctx->d_ele_bad);
     ctx->launches++;
     return cudaGetLastError();
   }
@@ -137,7 +141,7 @@ namespace
   {
     const bool fbar = ctx->formulation == FC_FORM_FBAR;
     if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC))
-      return launch_hex8nh<WANT_K>(ctx, A, (flags & FC_EVAL_CLOSED_FORM_FMA) != 0, (flags & FC_EVAL_TILE) != 0);
+      return launch_hex8nh<WANT_K>(ctx, A, (flags & FC_EVAL_CLOSED_FORM_FMA) != 0);
     if (ctx->celltype == FC_HEX8 && fbar && ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC))
       return launch_hex8_ext<fc::VAR_NH_FBAR, WANT_K>(ctx, A);
     if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_SVK && !(flags & FC_EVAL_FORCE_GENERIC))
@@ -164,7 +168,6 @@ namespace
     A.dbc = ctx->have_dbc ? ctx->d_dbc : nullptr;
     A.err = ctx->d_err;
     A.mat = ctx->mat;
-    if (const char* d = getenv("FC_DEBUG")) A.debug = atoi(d);
     return A;
   }
 
@@ -237,16 +240,25 @@ extern "C"
       d_K = ctx->d_stage_K;
     }
 
-    // slab pipeline: only the tensor-core closed-form kernel takes an element range
-    const bool mma_path = ctx->celltype == FC_HEX8 && ctx->formulation == FC_FORM_DISPLACEMENT && ctx->mat.kind == fc::MAT_NEOHOOKE &&
-                          !(flags & (FC_EVAL_FORCE_GENERIC | FC_EVAL_CLOSED_FORM_FMA));
-    const bool pipelined = (flags & FC_EVAL_ZERO_FIRST) && want_K && mma_path && ctx->n_slabs > 1 && !(flags & FC_EVAL_NO_SLAB_PIPELINE);
+    // owner-computed assembly (brick kernel): hex8 displacement-based Neo-Hooke on a lattice mesh.  It writes every row of
+    // K and f itself, so FC_EVAL_ZERO_FIRST costs no memset; without the flag it adds to the caller's values.
+    bool brick = (flags & FC_EVAL_OWNER_COMPUTED) && want_K && ctx->celltype == FC_HEX8 && ctx->formulation == FC_FORM_DISPLACEMENT &&
+                 ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & (FC_EVAL_FORCE_GENERIC | FC_EVAL_CLOSED_FORM_FMA));
+    if (brick)
+    {
+      if (int rc = fc_build_brick_plan(ctx)) return rc;
+      brick = ctx->n_brick_units > 0;
+    }
+    const bool only_interior = (flags & FC_EVAL_INTERIOR) && !(flags & FC_EVAL_BOUNDARY);
+    const bool only_boundary = (flags & FC_EVAL_BOUNDARY) && !(flags & FC_EVAL_INTERIOR);
+    // the boundary half completes an evaluation whose interior half stored its rows: it stores the remaining rows
+    const bool store = (flags & FC_EVAL_ZERO_FIRST) || (brick && only_boundary && ctx->split_store);
     FC_CUDA(cudaEventRecord(ctx->ev[0], s));
-    if (flags & FC_EVAL_ZERO_FIRST)
+    if ((flags & FC_EVAL_ZERO_FIRST) && !brick)
     {
       if (d_f) FC_CUDA(cudaMemsetAsync(d_f, 0, sizeof(double) * (size_t)ctx->n_row_dof, s));
-      if (d_K && !pipelined) FC_CUDA(cudaMemsetAsync(d_K, 0, sizeof(double) * (size_t)ctx->nnz, s));
-      ctx->launches += (d_f ? 1 : 0) + (d_K && !pipelined ? 1 : 0);
+      if (d_K) FC_CUDA(cudaMemsetAsync(d_K, 0, sizeof(double) * (size_t)ctx->nnz, s));
+      ctx->launches += (d_f ? 1 : 0) + (d_K ? 1 : 0);
     }
     FC_CUDA(cudaEventRecord(ctx->ev[1], s));
     if (int rc = reset_err(ctx)) return rc;
@@ -254,46 +266,25 @@ extern "C"
     A.u = d_u;
     A.f = d_f;
     A.K = d_K;
-    if (!pipelined && !getenv("FC_NO_L2_ORDER")) A.ele_perm = ctx->d_ele_perm;
-    if (flags & (FC_EVAL_INTERIOR | FC_EVAL_BOUNDARY))
+    A.ele_perm = ctx->d_ele_perm;
+    if (brick)
     {
-      // elements without / with ghost nodes: the interior needs no halo import and can run while it is in flight.
-      // The split lives in the launch-slot order (ele_perm), which only the tensor-core kernels follow.
-      const bool perm_kernel = follows_launch_order(ctx, flags);
-      if (!perm_kernel || pipelined) return fail(ctx, FC_ERR_UNSUPPORTED, "FC_EVAL_INTERIOR/BOUNDARY need one of the tensor-core kernels");
-      A.ele_perm = ctx->d_ele_perm;
-      if ((flags & FC_EVAL_INTERIOR) && !(flags & FC_EVAL_BOUNDARY)) A.n_ele = ctx->n_interior_ele;
-      if ((flags & FC_EVAL_BOUNDARY) && !(flags & FC_EVAL_INTERIOR)) A.ele_offset = ctx->n_interior_ele;
+      const int u0 = only_boundary ? ctx->n_brick_interior : 0, u1 = only_interior ? ctx->n_brick_interior : ctx->n_brick_units;
+      FC_CUDA(launch_hex8_brick(ctx, A, u0, u1, store));
+      ctx->split_store = only_interior && (flags & FC_EVAL_ZERO_FIRST);
     }
-    if (pipelined)
+    else
     {
-      // zero the rows a slab touches first on stream2 while the previous slab computes on the main stream
-      FC_CUDA(cudaEventRecord(ctx->ev_start, s));
-      FC_CUDA(cudaStreamWaitEvent(ctx->stream2, ctx->ev_start, 0));
-      int64_t off = 0;
-      for (int k = 0; k < ctx->n_slabs; ++k)
+      if (flags & (FC_EVAL_INTERIOR | FC_EVAL_BOUNDARY))
       {
-        const int64_t end = ctx->slab_off_end[k];
-        if (end > off)
-        {
-          FC_CUDA(cudaMemsetAsync(d_K + off, 0, sizeof(double) * (size_t)(end - off), ctx->stream2));
-          ctx->launches++;
-          off = end;
-        }
-        FC_CUDA(cudaEventRecord(ctx->ev_slab[k], ctx->stream2));
+        // elements without / with ghost nodes: the interior needs no halo import and can run while it is in flight.
+        // The split lives in the launch-slot order (ele_perm), which only the tensor-core kernels follow.
+        if (!follows_launch_order(ctx, flags)) return fail(ctx, FC_ERR_UNSUPPORTED, "FC_EVAL_INTERIOR/BOUNDARY need one of the tensor-core kernels");
+        if (only_interior) A.n_ele = ctx->n_interior_ele;
+        if (only_boundary) A.ele_offset = ctx->n_interior_ele;
       }
-      int e0 = 0;
-      for (int k = 0; k < ctx->n_slabs; ++k)
-      {
-        FC_CUDA(cudaStreamWaitEvent(s, ctx->ev_slab[k], 0));
-        A.ele_offset = e0;
-        A.n_ele = ctx->slab_ele_end[k];
-        if (A.n_ele > e0) FC_CUDA(dispatch<true>(ctx, A, flags));
-        e0 = A.n_ele;
-      }
+      if (A.n_ele > A.ele_offset) FC_CUDA(want_K ? dispatch<true>(ctx, A, flags) : dispatch<false>(ctx, A, flags));
     }
-    else if (A.n_ele > A.ele_offset)
-      FC_CUDA(want_K ? dispatch<true>(ctx, A, flags) : dispatch<false>(ctx, A, flags));
     FC_CUDA(cudaEventRecord(ctx->ev[2], s));
     ctx->ev_valid = true;
 
@@ -306,9 +297,9 @@ extern "C"
       if (int rc = read_err(ctx, &cnt, &gid)) return rc;
       if (ele_error_count) *ele_error_count = cnt;
       if (first_bad_ele_gid) *first_bad_ele_gid = gid;
-      if (ctx->geom_bad_count > 0)
-        return fail(ctx, FC_ERR_NEGATIVE_JACOBIAN, "determinant of jacobian is <= 0 at one node of an element");
     }
+    // the node-Jacobian check of set_mesh is a host value: reported by every evaluate, synchronous or not
+    if (ctx->geom_bad_count > 0) return fail(ctx, FC_ERR_NEGATIVE_JACOBIAN, "determinant of jacobian is <= 0 at one node of an element");
     return FC_OK;
   }
 

@@ -11,10 +11,11 @@
 #include <cstdlib>
 #include <thread>
 
+#include "fc_brick_plan.hpp"
 #include "fc_host_util.hpp"
-#include "fc_kernels_hex8nh_tile.cuh"
 #include "fc_kernels_setup.cuh"
-#include "fc_tile_plan.hpp"
+
+void fc_free_brick_plan(fc_ctx* ctx);
 
 namespace
 {
@@ -80,77 +81,41 @@ namespace
     }
   }
 
-  // slab plan: rows first touched by slab k end at the prefix maximum of the owned nodes its elements touch
-  void compute_slab_plan(fc_ctx* ctx, int S)
+  // hex8: units of node lines for the owner-computed assembly (fc_brick_plan.hpp); a mesh that is not a lattice of
+  // hex cells has no plan and keeps the per-element reductions
+  int build_brick_plan(fc_ctx* ctx)
   {
-    const int ne = ctx->n_ele, nen = ctx->nen, nrow = ctx->n_row_nodes;
-    if (S > fc_ctx::max_slabs) S = fc_ctx::max_slabs;
-    if (S < 1) S = 1;
-    ctx->n_slabs = S;
-    int maxnode = -1;
-    for (int k = 0; k < S; ++k)
-    {
-      const int e0 = (int)((int64_t)ne * k / S) / 16 * 16, e1 = k == S - 1 ? ne : (int)((int64_t)ne * (k + 1) / S) / 16 * 16;
-      for (size_t i = (size_t)e0 * nen; i < (size_t)e1 * nen; ++i)
-      {
-        const int n = ctx->h_conn[i];
-        if (n < nrow && n > maxnode) maxnode = n;
-      }
-      ctx->slab_ele_end[k] = e1;
-      ctx->slab_off_end[k] = k == S - 1 ? ctx->nnz : 9 * ctx->h_nodeptr[maxnode + 1];
-    }
-  }
-
-  void free_tile_plan(fc_ctx* ctx)
-  {
-    dev_free(ctx->d_tile_ele);
-    dev_free(ctx->d_tile_blk);
-    dev_free(ctx->d_tile_ptr);
-    dev_free(ctx->d_tile_rec);
-    dev_free(ctx->d_tile_rownode);
-    ctx->n_tiles = 0;
-    ctx->tile_max_blocks = 0;
-    ctx->n_tile_blocks = 0;
-    ctx->tile_plan_tried = false;
-  }
-
-  // hex8: group the elements into tiles and precompute the tile blocks (fc_tile_plan.hpp); a mesh without a plan
-  // (an element lists a node twice) keeps the per-element scatter
-  int build_tile_plan(fc_ctx* ctx)
-  {
-    if (ctx->tile_plan_tried) return FC_OK;
-    ctx->tile_plan_tried = true;
-    if (ctx->celltype != FC_HEX8 || ctx->n_ele == 0 || ctx->n_row_nodes == 0 || getenv("FC_NO_TILE_PLAN")) return FC_OK;
+    if (ctx->brick_tried) return FC_OK;
+    ctx->brick_tried = true;
+    if (ctx->celltype != FC_HEX8 || ctx->n_ele == 0 || ctx->n_row_nodes == 0 || !ctx->have_graph) return FC_OK;
+    int maxnb = 0;
+    for (int n = 0; n < ctx->n_row_nodes; ++n) maxnb = std::max(maxnb, (int)(ctx->h_nodeptr[n + 1] - ctx->h_nodeptr[n]));
     std::vector<double> X((size_t)3 * ctx->n_col_nodes);
     FC_CUDA(cudaMemcpyAsync(X.data(), ctx->d_X, sizeof(double) * X.size(), cudaMemcpyDeviceToHost, ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
-    fc_host::TilePlanHost plan;
-    if (!fc_host::build_tile_plan_host(ctx->n_col_nodes, X.data(), ctx->n_ele, ctx->h_conn.data(), ctx->n_row_nodes, ctx->h_nodeptr.data(),
-            ctx->h_nodeadj.data(), plan))
-      return FC_OK;
+    fc_host::BrickPlanHost plan;
+    if (!fc_host::build_brick_plan_host(ctx->n_col_nodes, X.data(), ctx->n_ele, ctx->h_conn.data(), ctx->n_row_nodes, maxnb, 0, plan)) return FC_OK;
     static_assert(sizeof(long long) == sizeof(int64_t), "");
-    FC_CUDA(dev_upload(ctx->d_tile_ele, plan.tile_ele.data(), plan.tile_ele.size(), ctx->stream));
-    FC_CUDA(dev_upload(ctx->d_tile_blk, plan.tile_blk.data(), plan.tile_blk.size(), ctx->stream));
-    FC_CUDA(dev_upload(ctx->d_tile_ptr, plan.tile_ptr.data(), plan.tile_ptr.size(), ctx->stream));
-    FC_CUDA(dev_upload(ctx->d_tile_rec, plan.rec.data(), plan.rec.size(), ctx->stream));
-    FC_CUDA(dev_upload(ctx->d_tile_rownode, plan.rownode.data(), plan.rownode.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_brick_planes, plan.unit_planes.data(), plan.unit_planes.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_brick_node_off, plan.unit_node_off.data(), plan.unit_node_off.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_brick_ele_off, plan.unit_ele_off.data(), plan.unit_ele_off.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_brick_nodes, plan.node_tab.data(), plan.node_tab.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_brick_eles, plan.ele_tab.data(), plan.ele_tab.size(), ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_brick_rows, plan.rowidx_tab.data(), plan.rowidx_tab.size(), ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
-    ctx->n_tiles = plan.n_tiles;
-    ctx->tile_max_blocks = plan.max_blocks;
-    ctx->n_tile_blocks = (long long)plan.rec.size();
-    if (ctx->have_dbc)
-    {
-      const int bs = 256;
-      fc::k_tile_set_dbc<<<(unsigned)((ctx->n_tile_blocks + bs - 1) / bs), bs, 0, ctx->stream>>>(ctx->d_tile_rec, ctx->d_tile_rownode, ctx->n_tile_blocks, ctx->d_dbc);
-      ctx->launches++;
-      FC_CUDA(cudaGetLastError());
-    }
+    ctx->n_brick_units = plan.n_units;
+    ctx->n_brick_interior = plan.n_interior_units;
     return FC_OK;
   }
 
   int finalize_graph(fc_ctx* ctx)
   {
     const int nrow = ctx->n_row_nodes, ncol = ctx->n_col_nodes;
+    // whatever was derived from the previous graph goes before anything can fail
+    ctx->have_graph = false;
+    fc_free_brick_plan(ctx);
+    dev_free(ctx->d_Dinv);
+    ctx->Dinv_cap = 0;
     ctx->nnz = 9 * ctx->h_nodeptr[nrow];
     ctx->n_row_dof = 3 * nrow;
     ctx->n_col_dof = 3 * ncol;
@@ -212,14 +177,25 @@ namespace
     dev_free(ctx->d_dbc);
     ctx->have_dbc = false;
     if (bad > 0) return fail(ctx, FC_ERR_GRAPH, "elements couple DOFs that are missing from the CSR graph");
-    free_tile_plan(ctx);  // built by the first FC_EVAL_TILE evaluation (fc_build_tile_plan)
-    compute_slab_plan(ctx, 1);  // measured: overlapping the zero-fill with the kernel gains nothing, so one slab
     ctx->have_graph = true;
     return FC_OK;
   }
 }  // namespace
 
-int fc_build_tile_plan(fc_ctx* ctx) { return build_tile_plan(ctx); }
+int fc_build_brick_plan(fc_ctx* ctx) { return build_brick_plan(ctx); }
+
+void fc_free_brick_plan(fc_ctx* ctx)
+{
+  dev_free(ctx->d_brick_planes);
+  dev_free(ctx->d_brick_node_off);
+  dev_free(ctx->d_brick_ele_off);
+  dev_free(ctx->d_brick_nodes);
+  dev_free(ctx->d_brick_eles);
+  dev_free(ctx->d_brick_rows);
+  ctx->n_brick_units = ctx->n_brick_interior = 0;
+  ctx->brick_tried = false;
+  ctx->split_store = false;
+}
 
 extern "C"
 {
@@ -236,8 +212,9 @@ extern "C"
     if (n_row_dof != 3 * ctx->n_row_nodes || n_col_dof != 3 * ctx->n_col_nodes)
       return fail(ctx, FC_ERR_INVALID, "graph dimensions do not match the mesh (3 DOFs per node)");
     const int nrow = ctx->n_row_nodes;
-    ctx->h_nodeptr.assign((size_t)nrow + 1, 0);
-    ctx->h_nodeadj.clear();
+    std::vector<int64_t> nodeptr((size_t)nrow + 1, 0);
+    std::vector<int> nodeadj;
+    nodeadj.reserve((size_t)(rowptr[3 * (size_t)nrow] / 9));
     for (int n = 0; n < nrow; ++n)
     {
       const int64_t b0 = rowptr[3 * n], len = rowptr[3 * n + 1] - b0;
@@ -251,18 +228,13 @@ extern "C"
         if (k > 0 && colind[b0 + k - 1] >= c) return fail(ctx, FC_ERR_GRAPH, "column ids must ascend within a row");
         if (colind[b0 + len + k] != c || colind[b0 + 2 * len + k] != c)
           return fail(ctx, FC_ERR_GRAPH, "graph is not node-blocked: the 3 DOF rows of a node differ");
-        ctx->h_nodeadj.push_back(c / 3);
+        nodeadj.push_back(c / 3);
       }
-      ctx->h_nodeptr[n + 1] = (int64_t)ctx->h_nodeadj.size();
+      nodeptr[n + 1] = (int64_t)nodeadj.size();
     }
+    ctx->h_nodeptr.swap(nodeptr);
+    ctx->h_nodeadj.swap(nodeadj);
     return finalize_graph(ctx);
-  }
-
-  int fc_solid_set_slab_count(fc_ctx* ctx, int n_slabs)
-  {
-    if (!ctx || !ctx->have_graph) return FC_ERR_INVALID;
-    compute_slab_plan(ctx, n_slabs);
-    return FC_OK;
   }
 
   int fc_solid_graph_sizes(const fc_ctx* ctx, int* n_row_dof, int* n_col_dof, int64_t* nnz)
@@ -304,20 +276,7 @@ extern "C"
     FC_CUDA(cudaSetDevice(ctx->device));
     dev_free(ctx->d_dbc);
     ctx->have_dbc = false;
-    auto refresh_tile_flags = [&]() -> cudaError_t {
-      if (ctx->n_tile_blocks == 0) return cudaSuccess;
-      const int bs = 256;
-      fc::k_tile_set_dbc<<<(unsigned)((ctx->n_tile_blocks + bs - 1) / bs), bs, 0, ctx->stream>>>(
-          ctx->d_tile_rec, ctx->d_tile_rownode, ctx->n_tile_blocks, ctx->d_dbc);
-      ctx->launches++;
-      return cudaGetLastError();
-    };
-    if (n == 0)
-    {
-      FC_CUDA(refresh_tile_flags());
-      FC_CUDA(cudaStreamSynchronize(ctx->stream));
-      return FC_OK;
-    }
+    if (n == 0) return FC_OK;
     std::vector<unsigned char> flags((size_t)ctx->n_row_dof, 0);
     for (int i = 0; i < n; ++i)
     {
@@ -325,7 +284,6 @@ extern "C"
       flags[row_lids[i]] = 1;
     }
     FC_CUDA(dev_upload(ctx->d_dbc, flags.data(), flags.size(), ctx->stream));
-    FC_CUDA(refresh_tile_flags());
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->have_dbc = true;
     return FC_OK;

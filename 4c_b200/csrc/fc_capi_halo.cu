@@ -42,7 +42,12 @@ namespace
     return api;
   }
   constexpr int kNcclFloat64 = 8;  // ncclDataType_t::ncclFloat64 (nccl.h), stable across NCCL 2.x
+  constexpr int kNcclInt32 = 2;    // ncclDataType_t::ncclInt32
   constexpr int kNcclSum = 0;      // ncclRedOp_t::ncclSum
+  constexpr int kNcclMax = 2;      // ncclRedOp_t::ncclMax
+
+  // err[2] = 1 if this rank saw an element failure in the last evaluation (err[0] > 0) or its mesh failed the node-Jacobian check
+  __global__ void k_error_flag(int* err, int geom_bad) { err[2] = (err[0] > 0 || geom_bad > 0) ? 1 : 0; }
 }  // namespace
 
 // sum of n doubles over the ranks of the context's communicator, in place, on the context's stream (linear solve)
@@ -74,6 +79,14 @@ extern "C"
     if (ns != ctx->n_send) return fail(ctx, FC_ERR_INVALID, "send counts do not add up to the send list (fc_solid_halo_set_send)");
     if (ctx->n_col_nodes > 0 && nr != 3ll * (ctx->n_col_nodes - ctx->n_row_nodes))
       return fail(ctx, FC_ERR_INVALID, "receive counts do not add up to the ghost DOFs of the mesh");
+    if (ctx->n_col_nodes > 0)
+    {
+      // rank p's message lands behind the messages of the ranks below p: it must be exactly p's ghost nodes
+      std::vector<long long> ghosts((size_t)ctx->nranks, 0);
+      for (int n = ctx->n_row_nodes; n < ctx->n_col_nodes; ++n) ghosts[ctx->h_node_owner[n]] += 3;
+      for (int p = 0; p < ctx->nranks; ++p)
+        if (ghosts[p] != recv_dof_count[p]) return fail(ctx, FC_ERR_INVALID, "receive count of a rank differs from 3 x the ghost nodes it owns");
+    }
     ctx->halo_send_count.assign(send_dof_count, send_dof_count + ctx->nranks);
     ctx->halo_recv_count.assign(recv_dof_count, recv_dof_count + ctx->nranks);
     return FC_OK;
@@ -83,6 +96,32 @@ extern "C"
   {
     if (!ctx) return FC_ERR_INVALID;
     ctx->nccl_comm = nccl_comm;
+    return FC_OK;
+  }
+
+  // eval_error_check (src/structure_new/src/model_evaluator/4C_structure_new_model_evaluator_generic.cpp:225-258): the
+  // element error flag of the last evaluation, maximum over the ranks of the communicator given to fc_solid_set_comm
+  // (one 4-byte ncclAllReduce).  Synchronises the stream.  One rank: the local flag.
+  int fc_solid_error_allreduce(fc_ctx* ctx, int* any_error)
+  {
+    if (!ctx || !any_error) return FC_ERR_INVALID;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    k_error_flag<<<1, 1, 0, ctx->stream>>>(ctx->d_err, ctx->geom_bad_count);
+    ctx->launches++;
+    FC_CUDA(cudaGetLastError());
+    if (ctx->nranks > 1)
+    {
+      NcclApi& api = nccl();
+      if (!api.ok || !api.all_reduce) return fail(ctx, FC_ERR_UNSUPPORTED, "NCCL entry points not found in the process and libnccl.so.2 cannot be loaded");
+      if (!ctx->nccl_comm) return fail(ctx, FC_ERR_INVALID, "fc_solid_set_comm must precede fc_solid_error_allreduce on numproc > 1");
+      const int rc = api.all_reduce(ctx->d_err + 2, ctx->d_err + 2, 1, kNcclInt32, kNcclMax, ctx->nccl_comm, ctx->stream);
+      if (rc != 0) return fail(ctx, FC_ERR_CUDA, std::string("NCCL: ") + (api.error_string ? api.error_string(rc) : "error"));
+      ctx->launches++;
+    }
+    int flag = 0;
+    FC_CUDA(cudaMemcpyAsync(&flag, ctx->d_err + 2, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    *any_error = flag;
     return FC_OK;
   }
 

@@ -145,7 +145,7 @@ extern "C"
     const size_t nvec = method == FC_SOLVER_CG ? 4 : 8;
     const size_t NC = (size_t)ctx->n_col_dof;  // every work vector is column-sized: the ones K multiplies carry ghosts
     FC_CUDA(ensure_cap(ctx->d_solver_ws, ctx->solver_ws_cap, nvec * NC));
-    if (!ctx->d_Dinv) FC_CUDA(cudaMalloc((void**)&ctx->d_Dinv, sizeof(double) * 9 * (size_t)ctx->n_row_nodes));
+    FC_CUDA(ensure_cap(ctx->d_Dinv, ctx->Dinv_cap, 9 * (size_t)ctx->n_row_nodes));
     fc::k_block_jacobi_setup<<<grid_for(ctx->n_row_nodes, 256), 256, 0, ctx->stream>>>(ctx->d_nodeptr, ctx->d_node_diagpos, ctx->n_row_nodes, K_values, ctx->d_Dinv);
     ctx->launches++;
     FC_CUDA(cudaGetLastError());

@@ -26,7 +26,7 @@ struct fc_ctx
   double* d_dNtab = nullptr; // [ngp + nen + 1][nen][3]: Gauss points, node positions, centroid
   double* d_gpw = nullptr;   // [ngp] weights
   unsigned char* d_ele_bad = nullptr;  // [n_ele] 1 = det J <= 0 at an element node
-  int* d_ele_perm = nullptr; // element order of the tensor-core assembled-path kernels (L2 sweep order, fc_tile_plan.hpp) or nullptr = caller's order
+  int* d_ele_perm = nullptr; // element order of the tensor-core assembled-path kernels (L2 sweep order, fc_sweep_order.hpp) or nullptr = caller's order
   int n_interior_ele = 0;    // launch slots [0, n_interior_ele) hold the elements without ghost nodes (FC_EVAL_INTERIOR / _BOUNDARY)
   double* d_geom = nullptr;  // hex8 geometry cache [n_ele][72], built by the first evaluation that uses it
   int geom_bad_count = 0, geom_first_bad_gid = -1;
@@ -56,29 +56,22 @@ struct fc_ctx
   double* d_solver_ws = nullptr;      // Krylov vectors
   size_t solver_ws_cap = 0;
   double* d_Dinv = nullptr;           // [n_row_nodes][9] inverse diagonal blocks
+  size_t Dinv_cap = 0;
   double* d_dot = nullptr;            // block partials [3][592] + results [3]
   double* h_dot_pinned = nullptr;
 
-  // hex8 tile plan (fc_tile_plan.hpp): built by the first FC_EVAL_TILE evaluation; n_tiles == 0 = no plan, per-element scatter
-  int n_tiles = 0, tile_max_blocks = 0;
-  bool tile_plan_tried = false;
-  long long n_tile_blocks = 0;
-  int* d_tile_ele = nullptr;                 // [n_tiles][16]
-  unsigned* d_tile_blk = nullptr;            // [n_tiles][16][32]
-  long long* d_tile_ptr = nullptr;           // [n_tiles + 1]
-  unsigned long long* d_tile_rec = nullptr;  // [n_tile_blocks]
-  int* d_tile_rownode = nullptr;             // [n_tile_blocks]
-
-  // slab pipeline for FC_EVAL_ZERO_FIRST: slab k = elements [slab_ele_end[k-1], slab_ele_end[k]); before it runs,
-  // the CSR range [slab_off_end[k-1], slab_off_end[k]) (rows first touched by this slab) is zeroed on a second
-  // stream while slab k-1 computes
-  static constexpr int max_slabs = 16;
-  int n_slabs = 0;
-  int slab_ele_end[max_slabs] = {};
-  int64_t slab_off_end[max_slabs] = {};
-  cudaStream_t stream2 = nullptr;
-  cudaEvent_t ev_slab[max_slabs] = {};
-  cudaEvent_t ev_start = nullptr;
+  // brick plan of the owner-computed hex8 assembly (fc_brick_plan.hpp): built by the first evaluation that can use it;
+  // n_brick_units == 0 = no plan (not a lattice of hex cells), per-element reductions
+  bool brick_tried = false;
+  int n_brick_units = 0, n_brick_interior = 0;
+  int* d_brick_planes = nullptr;
+  long long* d_brick_node_off = nullptr;
+  long long* d_brick_ele_off = nullptr;
+  int* d_brick_nodes = nullptr;
+  int* d_brick_eles = nullptr;
+  unsigned long long* d_brick_rows = nullptr;
+  bool split_store = false;  // an FC_EVAL_INTERIOR evaluation with FC_EVAL_ZERO_FIRST ran on the brick kernel: the
+                             // FC_EVAL_BOUNDARY evaluation that completes it stores its rows as well
 
   // halo send plan
   int n_send = 0;
@@ -93,7 +86,7 @@ struct fc_ctx
   double* d_stage_f = nullptr;
   double* d_stage_K = nullptr;
   size_t stage_u_cap = 0, stage_f_cap = 0, stage_K_cap = 0;
-  int* d_err = nullptr;  // [0] = #failing elements, [1] = min failing gid (INT_MAX if none)
+  int* d_err = nullptr;  // [0] = #failing elements, [1] = min failing gid (INT_MAX if none), [2] = flag of the cross-rank reduction
   int* h_err_pinned = nullptr;
 
   cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};

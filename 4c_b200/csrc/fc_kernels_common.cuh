@@ -16,7 +16,7 @@ namespace fc
     const int* ele_gid;    // [n_ele]
     const int* ele_perm;   // [n_ele] element visited by launch slot k (L2 sweep order) or nullptr = k
     int n_ele;             // end of the element range of this launch
-    int ele_offset;        // first element of this launch (slab-pipelined evaluation), 0 otherwise
+    int ele_offset;        // first launch slot of this launch (FC_EVAL_BOUNDARY), 0 otherwise
     int n_row_nodes;       // column nodes [0, n_row_nodes) are owned (their DOF rows are assembled)
     // tables
     const double* dNtab;   // [ngp + nen + 1][nen][3]
@@ -36,7 +36,6 @@ namespace fc
     double* Ke_out;
     int* err;              // [2]
     MatParams mat;
-    int debug;             // FC_DEBUG env (experiments only): 1 = K reductions predicated off, 2 = no staging, no reductions
   };
 
   // fire-and-forget FP64 add (RED.E.ADD.F64)

@@ -70,7 +70,7 @@ namespace fc
     const int wel = warp * Cfg::epw;
     const int slot_e = A.ele_offset + blockIdx.x * Cfg::epb + wel + el;
     const bool active = slot_e < A.n_ele;
-    // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_tile_plan.hpp)
+    // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_sweep_order.hpp)
     const int e = active ? (HAS_PERM ? __ldg(A.ele_perm + slot_e) : slot_e) : -1;  // HAS_PERM: see k_hex8_neohooke_mma
     double* E = smem + (size_t)(wel + el) * Cfg::ele_doubles;
 

@@ -76,7 +76,7 @@ namespace fc
     const int wel = warp * Cfg::epw;          // first element slot of this warp inside the CTA
     const int slot_e = A.ele_offset + blockIdx.x * Cfg::epb + wel + el;
     const bool active = slot_e < A.n_ele;
-    // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_tile_plan.hpp)
+    // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_sweep_order.hpp)
     const int e = active ? (HAS_PERM ? __ldg(A.ele_perm + slot_e) : slot_e) : -1;
     double* E = smem + (size_t)(wel + el) * Cfg::ele_doubles;
 
@@ -97,7 +97,7 @@ namespace fc
       const bool owned = active && node < A.n_row_nodes;
       ulonglong2 inf = make_ulonglong2(~0ull, 0ull);
       bool plain = false;
-      if (WANT_K && owned && A.K && !(A.debug & 1))
+      if (WANT_K && owned && A.K)
       {
         const unsigned long long rb = (unsigned long long)__ldg(A.node_rowbase + node);
         const unsigned long long rl = (unsigned long long)__ldg(A.node_rowlen + node);
@@ -270,14 +270,7 @@ namespace fc
           for (int i = 0; i < 3; ++i)
             for (int j = 0; j < 3; ++j) Ke[(3 * a + i) + 24 * (3 * (b0 + c) + j)] = Kb[c][3 * i + j];
       }
-      if (A.K && (A.debug & 2))
-      {
-        double sum = 0.0;
-        for (int c = 0; c < 2; ++c)
-          for (int i = 0; i < 9; ++i) sum += Kb[c][i];
-        if (sum == 1.2345e300) A.K[0] = sum;
-      }
-      else if (A.K)
+      if (A.K)
       {
         // stage K_e row-major in shared memory, then let 3 adjacent lanes add the 3 contiguous doubles
         // of one CSR node block in ONE instruction: the memory system processes reductions per 32-byte

@@ -116,7 +116,7 @@ namespace fc
     for (int it = tid; it < EPB * NP; it += Cfg::threads)
     {
       const int el = it / NP, a = it % NP;
-      // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_tile_plan.hpp)
+      // launch slot -> element: the caller's order, or the L2 sweep order of large meshes (fc_sweep_order.hpp)
       const int e = ebase + el < A.n_ele ? (A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el) : -1;
       double* E = smem_nhg + (size_t)el * Cfg::ele_doubles;
       long long rb = -1;

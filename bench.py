@@ -152,10 +152,32 @@ def run_reference(args):
     }))
 
 
-# dominant kernel per --kernel-flags and its dram__bytes_read.sum + dram__bytes_write.sum per launch at C2 from the committed
-# ncu captures (profiles/)
-KERNEL_NAME = {0: "k_hex8_neohooke_mma<true,false,false>", 16: "k_hex8_nh_tile<false>", 4: "k_hex8_neohooke<true>", 2: "k_generic<HEX8,DISP,true>"}
-TRAFFIC = {0: 4.083e9, 16: 5.115e9}  # profiles/r01_mma_kernel_ncu_full_c.md, profiles/r01_tile_kernel_ncu.md
+# dominant kernel per --kernel-flags, its source files and the committed ncu capture (profiles/extract_ncu.py) that holds
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch at C2.  The capture is keyed by the hash of the kernel's
+# source: when the source has changed since, the capture describes another kernel and `traffic` is null.
+KERNELS = {
+    0: ("k_hex8_neohooke_mma<true,false,false>", "profiles/r02_hex8nh_mma_c2.json"),
+    8: ("k_hex8_nh_brick<true,false>", "profiles/r02_hex8nh_brick_c2.json"),
+    4: ("k_hex8_neohooke<true>", None),
+    2: ("k_generic<HEX8,DISP,true>", None),
+}
+
+
+def committed_traffic(kernel_flags):
+    """(dram bytes per launch, note) from the committed capture of the kernel, None when absent or stale"""
+    import hashlib
+    name, path = KERNELS.get(kernel_flags, (None, None))
+    if not path or not os.path.exists(os.path.join(ROOT, path)):
+        return None, "no committed ncu capture of this kernel"
+    with open(os.path.join(ROOT, path)) as f:
+        cap = json.load(f)
+    h = hashlib.sha256()
+    for src in cap.get("sources", []):
+        with open(os.path.join(ROOT, src), "rb") as fh:
+            h.update(fh.read())
+    if not cap.get("sources") or h.hexdigest()[:16] != cap.get("sources_sha16"):
+        return None, f"{path} is a capture of an older version of the kernel source"
+    return cap["dram_bytes"], f"{path} ({cap['report']}, sources {cap['sources_sha16']})"
 
 
 def run_ours(args):
@@ -270,11 +292,12 @@ def run_ours(args):
     ele_ms = float(np.mean([k[1] for k in kernel_ms]))
     alg_bytes = 8 * nnz + 72 * grid.n_col_nodes + 32 * grid.n_col_eles  # K once, X/u/f once, conn once
     achieved = alg_bytes / (ele_ms * 1e-3) / 1e9
-    traffic = args.traffic
-    if traffic is None and args.edge == 100 and world == 1 and args.kernel_flags in TRAFFIC:
-        traffic = TRAFFIC[args.kernel_flags]
+    traffic, traffic_src = (args.traffic, "--traffic") if args.traffic is not None else (None, "capture is of C2 on one GPU; this is another workload")
+    if args.traffic is None and args.edge == 100 and world == 1:
+        traffic, traffic_src = committed_traffic(args.kernel_flags)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": traffic, "peak_source": peak_src, "kernel": KERNEL_NAME.get(args.kernel_flags, f"flags={args.kernel_flags}"),
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+                "kernel": KERNELS.get(args.kernel_flags, (f"flags={args.kernel_flags}", None))[0],
                 "kernel_ms": ele_ms, "zero_fill_ms": zero_ms, "algorithmic_bytes_per_launch": alg_bytes}
     out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
@@ -366,7 +389,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ref-edge", type=int, default=100, help="edge of the cube the CPU arm evaluates (100 = the full C2 workload)")
     ap.add_argument("--e2e-steps", type=int, default=3)
-    ap.add_argument("--kernel-flags", type=int, default=0, help="FC_EVAL_* kernel selection (0 default, 16 tile scatter, 4 closed-form FMA, 2 generic)")
+    ap.add_argument("--kernel-flags", type=int, default=0, help="FC_EVAL_* kernel selection (0 default = per-element reductions, 8 owner-computed store-only kernel, 4 closed-form FMA, 2 generic)")
     ap.add_argument("--traffic", type=float, default=None, help="dram bytes per launch from the committed ncu capture")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-overlap", action="store_true", help="N > 1: halo import before the evaluation instead of overlapped with the interior elements")

@@ -174,6 +174,7 @@ def main():
         ("C1 hex8 SVK 10^3", H8, D, SVK, 0.3, (10, 10, 10), 0),
         ("C1b hex8 SVK 100^3", H8, D, SVK, 0.3, (100, 100, 100), 0),
         ("C2 hex8 NeoHooke 100^3 (tensor-core closed form)", H8, D, NH, 0.25, (100, 100, 100), 0),
+        ("C2 hex8 NeoHooke 100^3 (owner-computed rows, tensor-core closed form)", H8, D, NH, 0.25, (100, 100, 100), fc.FC_EVAL_OWNER_COMPUTED),
         ("C2 hex8 NeoHooke 100^3 (FMA closed form)", H8, D, NH, 0.25, (100, 100, 100), fc.FC_EVAL_CLOSED_FORM_FMA),
         ("C2 hex8 NeoHooke 100^3 (generic B-operator)", H8, D, NH, 0.25, (100, 100, 100), fc.FC_EVAL_FORCE_GENERIC),
         ("C3a hex27 NeoHooke 48^3", H27, D, NH, 0.25, (48, 48, 48), 0),
@@ -183,6 +184,7 @@ def main():
         ("C4s hex8 F-bar NeoHooke nu=0.499 100^3", H8, FB, NH, 0.499, (100, 100, 100), 0),
         ("C4 hex8 F-bar NeoHooke nu=0.499 200^3", H8, FB, NH, 0.499, (200, 200, 200), 0),
         ("C5/8 hex8 NeoHooke 200^3 (one GPU's share of 400^3)", H8, D, NH, 0.25, (200, 200, 200), 0),
+        ("C5/8-oc hex8 NeoHooke 200^3, owner-computed rows", H8, D, NH, 0.25, (200, 200, 200), fc.FC_EVAL_OWNER_COMPUTED),
     ]
     if args.only and args.only.startswith("newton"):
         run_newton(fc, int(args.only[6:] or 100), args.steps)

@@ -83,16 +83,17 @@ extern "C"
                                   closed-form kernel exists (testing / comparison) */
     FC_EVAL_CLOSED_FORM_FMA = 4, /* hex8 Neo-Hooke closed form on the FP64 FMA pipe instead of the
                                     FP64 tensor cores (comparison) */
-    FC_EVAL_NO_SLAB_PIPELINE = 8, /* with ZERO_FIRST: one memset + one launch instead of zeroing slab k+1 on a
-                                     second stream while slab k computes (comparison) */
+    FC_EVAL_OWNER_COMPUTED = 8, /* hex8 displacement-based Neo-Hooke, struct_calc_nlnstiff on a lattice mesh: owner-computed
+                             store-only kernel (k_hex8_nh_brick): no zero-fill, no atomics, every CSR row written once, results
+                             bit-identical from run to run, 2.8 GB instead of 6.6 GB of DRAM traffic per evaluation at C2 -
+                             but 1.9x slower than memset + per-element reductions on B200, so opt-in.
+                             Ignored (per-element reductions) where the mesh has no brick plan */
     FC_EVAL_INTERIOR = 32, /* numproc > 1: only the elements without ghost nodes (they need no halo import: evaluate them while
                               fc_solid_halo_exchange is in flight on another stream) ... */
-    FC_EVAL_BOUNDARY = 64, /* ... then only the elements with ghost nodes, after the import; without FC_EVAL_ZERO_FIRST.
-                              Tensor-core kernels only (FC_ERR_UNSUPPORTED otherwise); both or neither = all elements */
-    FC_EVAL_TILE = 16 /* hex8 Neo-Hooke, assembled stiffness: tile kernel (k_hex8_nh_tile) that sums the element matrices of
-                         a 16-element tile in shared memory and adds every node-pair block once (43 % fewer reduction
-                         sectors, but shared-memory bound: slower than the per-element scatter on B200, DESIGN.md 4.6;
-                         kept for comparison).  The tile plan is built by the first evaluation that asks for it. */
+    FC_EVAL_BOUNDARY = 64 /* ... then only the elements with ghost nodes, after the import; without FC_EVAL_ZERO_FIRST (the
+                             rows it completes are stored if the interior half ran with FC_EVAL_ZERO_FIRST on the store-only
+                             kernel, added otherwise).  Tensor-core kernels only (FC_ERR_UNSUPPORTED otherwise); both or
+                             neither = all elements */
   };
 
   /* ---- context ------------------------------------------------------------------------------ */
@@ -127,10 +128,6 @@ extern "C"
   int fc_solid_set_graph(fc_ctx* ctx, int n_row_dof, const int64_t* rowptr, const int* colind, int n_col_dof);
   int fc_solid_build_graph(fc_ctx* ctx);
   int fc_solid_graph_sizes(const fc_ctx* ctx, int* n_row_dof, int* n_col_dof, int64_t* nnz);
-  /* number of element slabs of the zero-fill pipeline (FC_EVAL_ZERO_FIRST, tensor-core hex8 kernel); default 1 = one
-   * memset + one launch (on B200 the overlap gained nothing: the kernel slows by what the concurrent memset costs).
-   * Any count <= 16 is correct for any mesh (slab k zeroes the rows not touched by slabs < k). */
-  int fc_solid_set_slab_count(fc_ctx* ctx, int n_slabs);
   /* copy the graph out (host buffers: rowptr [n_row_dof+1], colind [nnz]) */
   int fc_solid_get_graph(const fc_ctx* ctx, int64_t* rowptr, int* colind);
 
@@ -150,6 +147,12 @@ extern "C"
   int fc_solid_evaluate(fc_ctx* ctx, int action, int flags, const double* u_col, double* f_row,
       double* K_values, int* ele_error_count, int* first_bad_ele_gid);
   int fc_solid_error_state(fc_ctx* ctx, int* ele_error_count, int* first_bad_ele_gid);
+  /* eval_error_check (src/structure_new/src/model_evaluator/4C_structure_new_model_evaluator_generic.cpp:225-258): the
+   * reference sums one int error flag over all ranks (Core::Communication::sum_all, :253-257) before it lets NOX go on.
+   * any_error (host) = 1 if any rank's last evaluation had a failing element or its mesh failed the node-Jacobian
+   * check: one 4-byte ncclAllReduce(max) on the communicator of fc_solid_set_comm.  Synchronises the stream; every
+   * rank calls.  One rank: the local flag, no communicator needed. */
+  int fc_solid_error_allreduce(fc_ctx* ctx, int* any_error);
 
   /* SparseMatrix::zero / Vector::put_scalar(0) on device buffers (4C_linalg_sparsematrix.cpp:353-378) */
   int fc_solid_zero(fc_ctx* ctx, double* f_row_dev, double* K_values_dev);
@@ -273,26 +276,29 @@ extern "C"
   int fc_solid_linear_solve(fc_ctx* ctx, int method, const double* K_values, const double* b, double* x, double rel_tol, int max_iter,
       int* iters, double* rel_residual);
 
-  /* ---- tile plan of the hex8 scatter (host integer code; exposed for inspection and tests) ------
-   * Replaces the per-element row loop of SparseMatrix::assemble (4C_linalg_sparsematrix.cpp:474-543): elements are
-   * grouped into spatially compact tiles of <= 16, every (row node, column node) pair inside a tile is one block that
-   * the tile kernel sums in shared memory and adds to the CSR values once.  the first FC_EVAL_TILE evaluation of a hex8
-   * context creates its plan; these entry points build the same plan from plain arrays.
-   *   nodeptr [n_row_nodes+1], nodeadj: node-block graph of the owned nodes, ascending column-node LIDs
-   *   tile_ele [16*n_tiles]     element of every tile slot, -1 = empty
-   *   tile_blk [512*n_tiles]    per slot and accumulator lane (a = lane/4, q = lane%4): block of (a, 2q) | block of
-   *                             (a, 2q+1) << 16, tile-local; 0xFFFF = row node not owned
-   *   tile_ptr [n_tiles+1]      first block record of a tile
-   *   rec      [n_blocks]       CSR offset of (DOF row 3a, column 3b) | entries per DOF row << 44
-   *   rownode  [n_blocks]       row node a
-   * create returns FC_ERR_GRAPH when the mesh has no plan (an element lists a node twice, or a pair is missing from
-   * the graph); the library then scatters element by element. */
-  typedef struct fc_tile_plan fc_tile_plan;
-  int fc_tile_plan_create(int n_col_nodes, const double* X, int n_ele, const int* conn, int n_row_nodes, const int64_t* nodeptr,
-      const int* nodeadj, fc_tile_plan** out);
-  int fc_tile_plan_sizes(const fc_tile_plan* p, int* n_tiles, int64_t* n_blocks, int* max_blocks);
-  int fc_tile_plan_get(const fc_tile_plan* p, int* tile_ele, uint32_t* tile_blk, int64_t* tile_ptr, uint64_t* rec, int* rownode);
-  void fc_tile_plan_destroy(fc_tile_plan* p);
+  /* ---- brick plan of the owner-computed hex8 assembly (host integer code; exposed for inspection and tests) ------
+   * Replaces the per-element row loop of SparseMatrix::assemble (4C_linalg_sparsematrix.cpp:471-575) and the zero-fill
+   * of SparseMatrix::zero (:353-378): the owned nodes of a lattice mesh are cut into units of 7 x 5 node lines x
+   * `chunk` node planes; the CTA that owns a unit evaluates every element touching it, sums in shared memory and
+   * stores each CSR row once.  The first evaluation that can use it creates the context's plan; these entry points
+   * build the same plan from plain arrays.
+   *   unit_planes [n_units], unit_node_off [n_units], unit_ele_off [n_units]
+   *   node_tab  [sum planes * 35]        node of (plane, line) or -1
+   *   ele_tab   [sum (planes + 1) * 48]  element of (layer, slot) or -1; slot = 12 * colour + warp, the 12 elements of a
+   *                                      colour share no node
+   *   rowidx_tab  same shape             byte a = accumulator row of local node a = (plane & 1) * 35 + line, 0xFF = the
+   *                                      node is not a row of this unit
+   * units [0, n_interior_units) contain no element with a ghost node.  max_row_nodes = largest number of nodes a row
+   * couples to (27 on a lattice); chunk = 0 lets the library choose.  create returns FC_ERR_GRAPH when the mesh is
+   * not a lattice of hex cells; the library then scatters element by element. */
+  typedef struct fc_brick_plan fc_brick_plan;
+  int fc_brick_plan_create(int n_col_nodes, const double* X, int n_ele, const int* conn, int n_row_nodes, int max_row_nodes, int chunk,
+      fc_brick_plan** out);
+  int fc_brick_plan_sizes(const fc_brick_plan* p, int* n_units, int* n_interior_units, int* chunk, int64_t* n_node_entries,
+      int64_t* n_ele_entries, int64_t* n_element_instances);
+  int fc_brick_plan_get(const fc_brick_plan* p, int* unit_planes, int64_t* unit_node_off, int64_t* unit_ele_off, int* node_tab, int* ele_tab,
+      uint64_t* rowidx_tab);
+  void fc_brick_plan_destroy(fc_brick_plan* p);
   /* element order the hex8 assembled-path kernels visit on large meshes (host integer code): y blocks of z layers of at
    * most layer_elems elements, so that a matrix row's element contributions arrive while the row is still in L2.
    * perm [n_ele] = element visited by launch slot k; returns 1 if the order differs from the caller's, 0 if it is kept. */

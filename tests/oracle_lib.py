@@ -33,7 +33,10 @@ def _load():
     path = os.path.join(ORACLE_DIR, "liboracle.so")
     if not os.path.exists(path):
         build()
-    lib = C.CDLL(path)
+    return _bind(C.CDLL(path))
+
+
+def _bind(lib):
     lib.oracle_svk_strain_energy.restype = C.c_double
     lib.oracle_voigt_determinant.restype = C.c_double
     lib.oracle_invert3x3.restype = C.c_double
@@ -44,6 +47,30 @@ def _load():
 
 
 lib = _load()
+
+
+def use_fast_build():
+    """Rebind this module to the TIMING build of the oracle (bench.py's cpu_baseline / --impl reference legs only):
+    -O3 -march=native with FMA contraction, compiled on the machine it runs on (one file per CPU model; falls back to
+    x86-64-v3 with contraction if the native build fails).  Returns the compiler flags used.  Parity tests never call this."""
+    global lib
+    import hashlib
+    try:
+        with open("/proc/cpuinfo") as f:
+            flags = next((ln for ln in f if ln.startswith("flags")), "")
+    except OSError:
+        flags = ""
+    tag = hashlib.sha256(flags.encode()).hexdigest()[:10]
+    base = "-std=c++20 -O3 -fPIC -Wall -Wno-unused-function"
+    for name, fl in ((f"liboracle_fast_{tag}.so", base + " -march=native"), ("liboracle_fast_v3.so", base + " -march=x86-64-v3")):
+        path = os.path.join(ORACLE_DIR, name)
+        if not os.path.exists(path):
+            r = subprocess.run(["make", "-s", "-C", ORACLE_DIR, "fast", f"FAST_OUT={name}", f"FASTFLAGS={fl}"], capture_output=True)
+            if r.returncode != 0:
+                continue
+        lib = _bind(C.CDLL(path))
+        return fl
+    raise RuntimeError("the timing build of the oracle could not be compiled")
 
 
 def _d(a):

@@ -146,37 +146,13 @@ def test_c2_full_size_invariants(fc):
     s.evaluate(fc.FC_ACTION_INTERNALFORCE, u + dx, f2, None, flags=fc.FC_EVAL_ZERO_FIRST)
     Kdx = torch.zeros(n_row, dtype=torch.float64, device=dev).index_add_(0, rows, K * dx[ci])
     assert (f2 - f - Kdx).abs().max() <= 1e-5 * Kdx.abs().max()
-    # (4) the two closed-form kernels and the generic kernel agree at full size
+    # (4) the owner-computed kernel, the FMA closed form and the generic kernel agree with the default at full size
     K2 = torch.empty_like(K)
-    for flags in (fc.FC_EVAL_TILE, fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC):
+    for flags in (fc.FC_EVAL_OWNER_COMPUTED, fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC):
         s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f2, K2, flags=flags | fc.FC_EVAL_ZERO_FIRST)
         assert (K2 - K).abs().max() <= 1e-12 * kmax
         assert (f2 - f).abs().max() <= 1e-12 * kmax * 0.01
     s.close()
-
-
-@pytest.mark.parametrize("n_slabs", [2, 5, 16])
-def test_slab_pipelined_zero_fill(fc, oracle, n_slabs):
-    """FC_EVAL_ZERO_FIRST with the zero-fill pipelined slab by slab on a second stream: same result as one
-    memset + one launch, for a shuffled element order too (slab row ranges are prefix maxima)."""
-    n = (9, 8, 7)
-    g = fc.Grid(HEX8, n)
-    rng = np.random.default_rng(0)
-    for perm in (np.arange(g.n_col_eles), rng.permutation(g.n_col_eles)):
-        s = fc.Solid(0)
-        s.set_mesh(fc.FC_HEX8, DISP, g.X, g.node_gid, g.node_owner, g.conn[perm], g.ele_gid[perm])
-        s.set_material(NH, 10.0, 0.25)
-        n_row, n_col, nnz = s.build_graph()
-        u = field(g.X, 0).reshape(-1).copy()
-        K0, f0 = np.full(nnz, 3.0), np.full(n_row, 3.0)
-        s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f0, K0, flags=fc.FC_EVAL_ZERO_FIRST | fc.FC_EVAL_NO_SLAB_PIPELINE)
-        s.set_slab_count(n_slabs)
-        for _ in range(2):
-            K1, f1 = np.full(nnz, 5.0), np.full(n_row, 5.0)
-            assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f1, K1, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
-            assert np.max(np.abs(K1 - K0)) <= 1e-13 * np.max(np.abs(K0))
-            assert np.max(np.abs(f1 - f0)) <= 1e-13 * np.max(np.abs(K0))
-        s.close()
 
 
 @pytest.mark.parametrize("ct,n", [(0, (4, 3, 2)), (1, (2, 2, 2)), (2, None)])
@@ -246,28 +222,31 @@ def test_full_size_kernel_agreement_fbar_svk(fc, form, mat, nue):
 
 
 @pytest.mark.gpu
-def test_l2_sweep_order_gives_same_assembly(fc, monkeypatch):
-    """FC_L2_LAYER_ELEMS small: the hex8 Neo-Hooke kernel visits the elements in (y block, z, y, x) order; K and f
-    must equal the result in the caller's order (reduction order changes: rounding only)"""
-    g = fc.Grid(HEX8, (9, 8, 7))
+def test_element_order_and_kernel_choice_give_the_same_assembly(fc):
+    """the caller's element order (here shuffled) changes the order of the reductions of the per-element kernel and the
+    contents of the brick plan, not the result: rounding only.  The owner-computed kernel is bit-reproducible."""
+    g = fc.Grid(HEX8, (15, 9, 8))
     u = field(g.X, 0).reshape(-1).copy()
-    res = []
-    for env in ("40", None):
-        if env:
-            monkeypatch.setenv("FC_L2_LAYER_ELEMS", env)
-        else:
-            monkeypatch.delenv("FC_L2_LAYER_ELEMS")
-            monkeypatch.setenv("FC_NO_L2_ORDER", "1")
+    rng = np.random.default_rng(3)
+    res = {}
+    for name, perm in (("caller", np.arange(g.n_col_eles)), ("shuffled", rng.permutation(g.n_col_eles))):
         s = fc.Solid(0)
-        s.set_mesh(fc.FC_HEX8, DISP, g.X, g.node_gid, g.node_owner, g.conn, g.ele_gid)
+        s.set_mesh(fc.FC_HEX8, DISP, g.X, g.node_gid, g.node_owner, g.conn[perm], g.ele_gid[perm])
         s.set_material(NH, 10.0, 0.25)
         n_row, n_col, nnz = s.build_graph()
-        K, f = np.zeros(nnz), np.zeros(n_row)
-        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
-        res.append((K, f))
+        for flags in (fc.FC_EVAL_OWNER_COMPUTED, 0):
+            K, f = np.zeros(nnz), np.zeros(n_row)
+            assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f, K, flags=flags | fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+            res[name, flags] = (K, f)
+        K2, f2 = np.zeros(nnz), np.zeros(n_row)
+        s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f2, K2, flags=fc.FC_EVAL_ZERO_FIRST | fc.FC_EVAL_OWNER_COMPUTED)
+        oc = res[name, fc.FC_EVAL_OWNER_COMPUTED]
+        assert np.array_equal(K2, oc[0]) and np.array_equal(f2, oc[1])  # no atomics: bit-identical reruns
         s.close()
-    assert np.max(np.abs(res[0][0] - res[1][0])) <= 1e-13 * np.max(np.abs(res[1][0]))
-    assert np.max(np.abs(res[0][1] - res[1][1])) <= 1e-13 * np.max(np.abs(res[1][0]))
+    K0, f0 = res["caller", 0]
+    for key, (K, f) in res.items():
+        assert np.max(np.abs(K - K0)) <= 1e-13 * np.max(np.abs(K0)), key
+        assert np.max(np.abs(f - f0)) <= 1e-13 * np.max(np.abs(K0)), key
     assert fc.capi.l2_sweep_order(g.X, g.conn, 40)[0]
 
 
@@ -286,18 +265,31 @@ def test_interior_then_boundary_equals_full_evaluation(fc, ct, form, mat, n, nra
         u = field(g.X, 0).reshape(-1).copy()
         K0, f0 = np.zeros(nnz), np.zeros(n_row)
         assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f0, K0, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
-        up = u.copy()
-        up[n_row:] = np.nan
-        K1, f1 = np.full(nnz, 9.0), np.full(n_row, 9.0)
-        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, up, f1, K1, flags=fc.FC_EVAL_ZERO_FIRST | fc.FC_EVAL_INTERIOR) == (0, -1)
-        assert np.all(np.isfinite(K1)) and np.all(np.isfinite(f1))
-        if n_col > n_row:
-            assert np.max(np.abs(K1 - K0)) > 0  # the boundary elements are still missing
-        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f1, K1, flags=fc.FC_EVAL_BOUNDARY) == (0, -1)
-        assert np.max(np.abs(K1 - K0)) <= 1e-13 * np.max(np.abs(K0))
-        assert np.max(np.abs(f1 - f0)) <= 1e-13 * np.max(np.abs(K0))
+        # device buffers: what the interior half does not write keeps the caller's 9.0
+        import torch
+        variants = (0, fc.FC_EVAL_OWNER_COMPUTED) if (ct, form, mat) == (0, DISP, NH) else (0,)
+        for extra in variants:
+            up = u.copy()
+            up[n_row:] = np.nan
+            up_d, u_d = torch.from_numpy(up).cuda(), torch.from_numpy(u).cuda()
+            K1 = torch.full((nnz,), 9.0, dtype=torch.float64, device="cuda")
+            f1 = torch.full((n_row,), 9.0, dtype=torch.float64, device="cuda")
+            assert s.evaluate(fc.FC_ACTION_NLNSTIFF, up_d, f1, K1, flags=extra | fc.FC_EVAL_ZERO_FIRST | fc.FC_EVAL_INTERIOR) == (0, -1)
+            assert bool(torch.isfinite(K1).all()) and bool(torch.isfinite(f1).all())  # the poisoned ghosts were not read
+            if n_col > n_row:
+                assert float((K1.cpu() - torch.from_numpy(K0)).abs().max()) > 0  # the boundary elements are still missing
+            assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u_d, f1, K1, flags=extra | fc.FC_EVAL_BOUNDARY) == (0, -1)
+            assert np.max(np.abs(K1.cpu().numpy() - K0)) <= 1e-13 * np.max(np.abs(K0))
+            assert np.max(np.abs(f1.cpu().numpy() - f0)) <= 1e-13 * np.max(np.abs(K0))
+            # without FC_EVAL_ZERO_FIRST both halves add to what the caller holds (SparseMatrix::assemble semantics)
+            K1.fill_(0.5)
+            f1.fill_(0.25)
+            s.evaluate(fc.FC_ACTION_NLNSTIFF, u_d, f1, K1, flags=extra | fc.FC_EVAL_INTERIOR)
+            s.evaluate(fc.FC_ACTION_NLNSTIFF, u_d, f1, K1, flags=extra | fc.FC_EVAL_BOUNDARY)
+            assert np.max(np.abs(K1.cpu().numpy() - 0.5 - K0)) <= 1e-13 * max(np.max(np.abs(K0)), 1.0)
+            assert np.max(np.abs(f1.cpu().numpy() - 0.25 - f0)) <= 1e-13 * max(np.max(np.abs(K0)), 1.0)
         # kernels that do not follow the launch-slot order refuse the split
         with pytest.raises(fc.FourCError) as ei:
-            s.evaluate(fc.FC_ACTION_NLNSTIFF, u, f1, K1, flags=fc.FC_EVAL_INTERIOR | fc.FC_EVAL_FORCE_GENERIC)
+            s.evaluate(fc.FC_ACTION_NLNSTIFF, u_d, f1, K1, flags=fc.FC_EVAL_INTERIOR | fc.FC_EVAL_FORCE_GENERIC)
         assert ei.value.code == fc.FC_ERR_UNSUPPORTED
         s.close()

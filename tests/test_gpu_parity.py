@@ -76,8 +76,9 @@ def setup_rank(fc, job, r, ct, form, mat, young, nue, use_set_graph=False):
 def kernel_variants(fc, ct, form, mat):
     """kernel-selection flags to cover: the default kernel of the combination plus its alternatives"""
     if ct == HEX8 and form == DISP and mat == NH:
-        # DMMA closed form, DMMA closed form with the tile scatter (assembled K only), FMA closed form, generic
-        return [0, fc.FC_EVAL_TILE, fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC]
+        # DMMA closed form: per-element reductions (default) and owner-computed rows (lattice meshes, assembled K only);
+        # FMA closed form; generic
+        return [0, fc.FC_EVAL_OWNER_COMPUTED, fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC]
     if ct == HEX8 and ((form == FBAR and mat == NH) or (form == DISP and mat == SVK)):
         return [0, fc.FC_EVAL_FORCE_GENERIC]  # tensor-core closed form (k_hex8_mma_ext), generic
     if ct in (HEX27, TET10) and form == DISP and mat == NH:

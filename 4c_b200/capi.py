@@ -31,7 +31,7 @@ EXPORTS = [
     "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
     "fc_solid_error_state", "fc_solid_error_allreduce", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_evaluate_elements",
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack", "fc_solid_halo_set_counts", "fc_solid_halo_exchange",
-    "fc_solid_last_kernel_ms", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
+    "fc_solid_last_kernel_ms", "fc_solid_kernel_ms_history", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
     "fc_grid_halo_counts", "fc_grid_halo_send_nodes", "fc_probe_fp64_fma", "fc_probe_fp64_mma",
     "fc_solid_set_comm", "fc_solid_set_dirichlet_toggle", "fc_solid_apply_dirichlet", "fc_solid_apply_dirichlet_to_system", "fc_solid_spmv", "fc_solid_linear_solve",
@@ -133,6 +133,42 @@ def l2_sweep_order(X, conn, layer_elems):
     if rc < 0:
         raise FourCError(rc, "fc_l2_sweep_order")
     return bool(rc), perm
+
+
+class _NcclUniqueId(C.Structure):
+    _fields_ = [("internal", C.c_byte * 128)]
+
+
+def nccl_comm_init(rank, world, device_index):
+    """An ncclComm_t (as int) for fc_solid_halo_exchange / fc_solid_set_comm, created with the NCCL that torch ships
+    (the library resolves the same symbols at run time).  The unique id travels from rank 0 through torch.distributed,
+    which must be initialised.  Plumbing for bench.py and the examples; a 4C build hands over its own communicator."""
+    import torch
+    import torch.distributed as dist
+    nccl = None
+    for cand in (os.path.join(os.path.dirname(torch.__file__), "..", "nvidia", "nccl", "lib", "libnccl.so.2"), "libnccl.so.2"):
+        try:
+            nccl = C.CDLL(cand, mode=C.RTLD_GLOBAL)
+            break
+        except OSError:
+            continue
+    if nccl is None:
+        raise ImportError("libnccl.so.2 not found")
+    uid = _NcclUniqueId()
+    if rank == 0:
+        rc = nccl.ncclGetUniqueId(C.byref(uid))
+        if rc != 0:
+            raise FourCError(rc, "ncclGetUniqueId")
+    t = torch.tensor(list(bytes(uid)), dtype=torch.uint8, device=torch.device("cuda", device_index))
+    dist.broadcast(t, 0)
+    C.memmove(C.byref(uid), bytes(t.cpu().tolist()), 128)
+    comm = C.c_void_p()
+    nccl.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, _NcclUniqueId, C.c_int]
+    torch.cuda.set_device(device_index)
+    rc = nccl.ncclCommInitRank(C.byref(comm), C.c_int(world), uid, C.c_int(rank))
+    if rc != 0:
+        raise FourCError(rc, "ncclCommInitRank")
+    return comm.value
 
 
 class Grid:
@@ -337,6 +373,12 @@ class Solid:
         a, b = C.c_float(), C.c_float()
         self._chk(lib().fc_solid_last_kernel_ms(self.h, C.byref(a), C.byref(b)))
         return a.value, b.value
+
+    def kernel_ms_history(self, n):
+        """(zero_ms [n], element_ms [n]) of the last n evaluate / spmv calls, oldest first"""
+        z, e = np.zeros(n, np.float32), np.zeros(n, np.float32)
+        self._chk(lib().fc_solid_kernel_ms_history(self.h, C.c_int(n), _ptr(z), _ptr(e)))
+        return z, e
 
     def launch_count(self):
         n = C.c_int64()

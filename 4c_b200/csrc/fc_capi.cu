@@ -44,7 +44,8 @@ extern "C"
       delete ctx;
       return FC_ERR_CUDA;
     }
-    for (auto& e : ctx->ev) cudaEventCreate(&e);
+    for (auto& t : ctx->ev_hist)
+      for (auto& e : t) cudaEventCreate(&e);
     *out = ctx;
     return FC_OK;
   }
@@ -81,8 +82,9 @@ extern "C"
     dev_free(ctx->d_stage_K);
     dev_free(ctx->d_err);
     if (ctx->h_err_pinned) cudaFreeHost(ctx->h_err_pinned);
-    for (auto& e : ctx->ev)
-      if (e) cudaEventDestroy(e);
+    for (auto& t : ctx->ev_hist)
+      for (auto& e : t)
+        if (e) cudaEventDestroy(e);
     delete ctx;
   }
 

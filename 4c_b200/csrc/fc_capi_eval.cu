@@ -253,6 +253,7 @@ extern "C"
     const bool only_boundary = (flags & FC_EVAL_BOUNDARY) && !(flags & FC_EVAL_INTERIOR);
     // the boundary half completes an evaluation whose interior half stored its rows: it stores the remaining rows
     const bool store = (flags & FC_EVAL_ZERO_FIRST) || (brick && only_boundary && ctx->split_store);
+    ctx->ev = ctx->ev_hist[ctx->ev_count++ % fc_ctx::ev_ring];
     FC_CUDA(cudaEventRecord(ctx->ev[0], s));
     if ((flags & FC_EVAL_ZERO_FIRST) && !brick)
     {
@@ -387,6 +388,19 @@ extern "C"
     FC_CUDA(cudaEventSynchronize(ctx->ev[2]));
     if (zero_ms) FC_CUDA(cudaEventElapsedTime(zero_ms, ctx->ev[0], ctx->ev[1]));
     if (element_ms) FC_CUDA(cudaEventElapsedTime(element_ms, ctx->ev[1], ctx->ev[2]));
+    return FC_OK;
+  }
+
+  int fc_solid_kernel_ms_history(fc_ctx* ctx, int n, float* zero_ms, float* element_ms)
+  {
+    if (!ctx || !ctx->ev_valid || n < 1 || n > fc_ctx::ev_ring || n > ctx->ev_count) return FC_ERR_INVALID;
+    FC_CUDA(cudaEventSynchronize(ctx->ev[2]));
+    for (int k = 0; k < n; ++k)
+    {
+      cudaEvent_t* t = ctx->ev_hist[(ctx->ev_count - n + k) % fc_ctx::ev_ring];
+      if (zero_ms) FC_CUDA(cudaEventElapsedTime(zero_ms + k, t[0], t[1]));
+      if (element_ms) FC_CUDA(cudaEventElapsedTime(element_ms + k, t[1], t[2]));
+    }
     return FC_OK;
   }
 

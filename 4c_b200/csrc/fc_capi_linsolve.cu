@@ -120,6 +120,7 @@ extern "C"
     if (!ctx || !ctx->have_graph || !K_values || !x_col || !y_row) return fail(ctx, FC_ERR_INVALID, "graph, K_values, x and y required");
     if (!is_device_ptr(K_values) || !is_device_ptr(x_col) || !is_device_ptr(y_row)) return fail(ctx, FC_ERR_INVALID, "spmv works on device buffers");
     FC_CUDA(cudaSetDevice(ctx->device));
+    ctx->ev = ctx->ev_hist[ctx->ev_count++ % fc_ctx::ev_ring];
     FC_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
     FC_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
     spmv(ctx, K_values, x_col, y_row);

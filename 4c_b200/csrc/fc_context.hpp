@@ -89,7 +89,12 @@ struct fc_ctx
   int* d_err = nullptr;  // [0] = #failing elements, [1] = min failing gid (INT_MAX if none), [2] = flag of the cross-rank reduction
   int* h_err_pinned = nullptr;
 
-  cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+  // device timing: every evaluate / spmv records (start, after zero-fill, end) into the next triple of a ring, so a
+  // caller can read the kernel times of a whole timed region afterwards without synchronising inside it
+  static constexpr int ev_ring = 128;
+  cudaEvent_t ev_hist[ev_ring][3] = {};
+  cudaEvent_t* ev = ev_hist[0];  // triple of the current / last call
+  long long ev_count = 0;
   bool ev_valid = false;
   int64_t launches = 0;
   int eval_elements_flags = 0;

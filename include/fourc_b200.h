@@ -219,6 +219,9 @@ extern "C"
 
   /* ---- timing helpers (device time of the last evaluate, CUDA events on the ctx stream) ----- */
   int fc_solid_last_kernel_ms(fc_ctx* ctx, float* zero_ms, float* element_ms);
+  /* the same for the last n <= 128 evaluate / spmv calls, oldest first (zero_ms, element_ms: host arrays of n, either may
+   * be NULL): the device times of a whole timed region, read after it.  Synchronises on the last call only. */
+  int fc_solid_kernel_ms_history(fc_ctx* ctx, int n, float* zero_ms, float* element_ms);
   int fc_solid_kernel_launch_count(const fc_ctx* ctx, int64_t* launches);
 
   /* FP64 peak probes (TFLOP/s, best of 5) for the roofline denominators: DFMA loop and

@@ -26,6 +26,7 @@ CASES = [
     "solid_ele_tet10_Standard_stressout.dat",
     "solid_ele_tet10_Standard_dynamic.dat",
     "sohex8fbar_cooks_nl_new_struc.dat",  # 64 hex8 TECH fbar, CoupNeoHooke NUE 0.4999, statics, 20 load steps
+    "solid_ele_hex8_Standard_eas_none_volume_neumann.dat",  # surface + VOLUME Neumann loads with functions of space and time
 ]
 
 
@@ -81,6 +82,10 @@ def from_dat(path):
     for l in s["DSURF-NODE TOPOLOGY"]:
         t = l.split()
         surf.setdefault(int(t[3]), []).append(int(t[1]))
+    vol = {}
+    for l in s.get("DVOL-NODE TOPOLOGY", []):
+        t = l.split()
+        vol.setdefault(int(t[3]), []).append(int(t[1]))
     nodes = {}
     for l in s["NODE COORDS"]:
         t = l.split()
@@ -94,6 +99,7 @@ def from_dat(path):
     return {"dynamic": dyn, "materials": mats, "functs": functs, "results": results, "dsurf": surf,
             "dirich": [parse_condition_dat(l) for l in s.get("DESIGN SURF DIRICH CONDITIONS", [])],
             "neumann": [parse_condition_dat(l) for l in s.get("DESIGN SURF NEUMANN CONDITIONS", [])],
+            "dvol": vol, "vol_neumann": [parse_condition_dat(l) for l in s.get("DESIGN VOL NEUMANN CONDITIONS", [])],
             "nodes": nodes, "elements": eles}
 
 

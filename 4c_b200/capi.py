@@ -15,10 +15,13 @@ LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
 FC_HEX8, FC_HEX27, FC_TET10 = 0, 1, 2
 FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
+FC_SUMMAND_COUPNEOHOOKE, FC_SUMMAND_COUPSVK, FC_SUMMAND_COUPANISOEXPO = 0, 1, 2
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
 FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_OWNER_COMPUTED = 1, 2, 4, 8
 FC_EVAL_INTERIOR, FC_EVAL_BOUNDARY = 32, 64
 FC_STRESS_2PK, FC_STRESS_CAUCHY = 0, 1
+FC_FACE_QUAD4, FC_FACE_QUAD9, FC_FACE_TRI6 = 0, 1, 2
+FACE_NEN = {FC_FACE_QUAD4: 4, FC_FACE_QUAD9: 9, FC_FACE_TRI6: 6}
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
 FC_ERR_SOLVER, FC_ERR_SOLVER_NOT_CONVERGED = -7, -8
@@ -27,9 +30,10 @@ NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10}
 
 EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
-    "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_graph", "fc_solid_build_graph",
+    "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_material_elasthyper", "fc_solid_set_fibers", "fc_solid_set_graph", "fc_solid_build_graph",
     "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
-    "fc_solid_error_state", "fc_solid_error_allreduce", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_evaluate_elements",
+    "fc_solid_error_state", "fc_solid_error_allreduce", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_neumann_surface", "fc_solid_neumann_volume",
+    "fc_solid_neumann_surface_gp_coords", "fc_solid_neumann_volume_gp_coords", "fc_solid_evaluate_elements",
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack", "fc_solid_halo_set_counts", "fc_solid_halo_exchange",
     "fc_solid_last_kernel_ms", "fc_solid_kernel_ms_history", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
@@ -250,6 +254,13 @@ class Solid:
         p = _f64([young, nue])
         self._chk(lib().fc_solid_set_material(self.h, C.c_int(kind), _ptr(p), C.c_int(2)))
 
+    def set_material_elasthyper(self, summands, fibers=None):
+        """MAT_ElastHyper with a summand list [(kind, [4 parameters])]; fibers: (n_ele, 3) FIBER1 per element or None"""
+        kinds, par = _i32([k for k, _ in summands]), _f64([list(q) + [0.0] * (4 - len(q)) for _, q in summands])
+        self._chk(lib().fc_solid_set_material_elasthyper(self.h, C.c_int(len(kinds)), _ptr(kinds), _ptr(par)))
+        fb = None if fibers is None else _f64(fibers)
+        self._chk(lib().fc_solid_set_fibers(self.h, _ptr(fb)))
+
     def build_graph(self):
         self._chk(lib().fc_solid_build_graph(self.h))
         return self.graph_sizes()
@@ -338,6 +349,33 @@ class Solid:
     def evaluate_mass(self, density, M_values, flags=FC_EVAL_ZERO_FIRST):
         """consistent mass (struct_calc_nlnstiffmass) into M_values [nnz], layout of the stiffness graph"""
         self._chk(lib().fc_solid_evaluate_mass(self.h, C.c_double(density), C.c_int(flags), _ptr(M_values)))
+
+    # ---- SURVEY 8f F2: Neumann loads TYPE Live ----
+    def neumann_surface(self, face_type, face_nodes, onoff, val, f_ext, gp_factor=None):
+        fn = _i32(face_nodes).reshape(-1, FACE_NEN[face_type])
+        oo, vv = _i32(onoff[:3]), _f64(val[:3])
+        gf = None if gp_factor is None else (_f64(gp_factor) if isinstance(gp_factor, np.ndarray) else gp_factor)
+        self._chk(lib().fc_solid_neumann_surface(self.h, C.c_int(face_type), C.c_int(len(fn)), _ptr(fn), _ptr(oo), _ptr(vv), _ptr(gf), _ptr(f_ext)))
+
+    def neumann_volume(self, ele_lids, onoff, val, f_ext, gp_factor=None):
+        el = _i32(ele_lids)
+        oo, vv = _i32(onoff[:3]), _f64(val[:3])
+        gf = None if gp_factor is None else (_f64(gp_factor) if isinstance(gp_factor, np.ndarray) else gp_factor)
+        self._chk(lib().fc_solid_neumann_volume(self.h, C.c_int(len(el)), _ptr(el), _ptr(oo), _ptr(vv), _ptr(gf), _ptr(f_ext)))
+
+    def neumann_surface_gp_coords(self, face_type, face_nodes):
+        fn = _i32(face_nodes).reshape(-1, FACE_NEN[face_type])
+        ngp = FACE_NEN[face_type]
+        out = np.zeros((len(fn), ngp, 3))
+        self._chk(lib().fc_solid_neumann_surface_gp_coords(self.h, C.c_int(face_type), C.c_int(len(fn)), _ptr(fn), _ptr(out)))
+        return out
+
+    def neumann_volume_gp_coords(self, ele_lids):
+        el = _i32(ele_lids)
+        ngp = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4}[self.celltype]
+        out = np.zeros((len(el), ngp, 3))
+        self._chk(lib().fc_solid_neumann_volume_gp_coords(self.h, C.c_int(len(el)), _ptr(el), _ptr(out)))
+        return out
 
     def evaluate_stress(self, u_col, stress_type=1, want_gp=True, want_nodal=True):
         """struct_calc_stress: (gp_stress [n_ele, ngp, 6], nodal_stress [n_row_nodes, 6]); 0 = 2PK, 1 = Cauchy"""

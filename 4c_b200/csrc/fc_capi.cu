@@ -2,6 +2,7 @@
 // There is no CPU fallback anywhere in this file: every compute entry point launches CUDA
 // kernels on the context's device or fails.
 #include <algorithm>
+#include <cmath>
 #include <climits>
 #include <cstdio>
 #include <cstring>
@@ -61,6 +62,7 @@ extern "C"
     dev_free(ctx->d_gpw);
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
+    dev_free(ctx->d_fiber);
     dev_free(ctx->d_ele_perm);
     dev_free(ctx->d_node_rowbase);
     dev_free(ctx->d_node_rowlen);
@@ -107,6 +109,66 @@ extern "C"
     ctx->mat.young = young;
     ctx->mat.nue = nue;
     ctx->have_material = true;
+    return FC_OK;
+  }
+
+  int fc_solid_set_material_elasthyper(fc_ctx* ctx, int n_summands, const int* kinds, const double* params)
+  {
+    if (!ctx || !kinds || !params || n_summands < 1) return FC_ERR_INVALID;
+    if (n_summands > fc::max_summands) return fail(ctx, FC_ERR_UNSUPPORTED, "MAT_ElastHyper with more than 4 summands");
+    fc::MatParams m = ctx->mat;
+    m.kind = fc::MAT_ELASTHYPER;
+    m.n_summands = n_summands;
+    bool iso = false;
+    for (int k = 0; k < n_summands; ++k)
+    {
+      const double* p = params + 4 * k;
+      if (kinds[k] == FC_SUMMAND_COUPNEOHOOKE || kinds[k] == FC_SUMMAND_COUPSVK)
+      {
+        // YOUNG > 0; NUE in (-1, 0.5) for CoupNeoHooke (beta = nue / (1 - 2 nue)), (-1, 0.5] for CoupSVK (coupSaintVenantKirchhoff.cpp:21-28)
+        const bool nue_ok = p[1] > -1.0 && (kinds[k] == FC_SUMMAND_COUPSVK ? p[1] <= 0.5 : p[1] < 0.5);
+        if (!(p[0] > 0.0) || !nue_ok) return fail(ctx, FC_ERR_INVALID, "summand: YOUNG must be > 0 and NUE inside its range");
+        iso = true;
+      }
+      else if (kinds[k] == FC_SUMMAND_COUPANISOEXPO)
+      {
+        if (p[0] < 0.0 || p[2] < 0.0) return fail(ctx, FC_ERR_INVALID, "ELAST_CoupAnisoExpo: K1 and K1COMP must be >= 0");
+      }
+      else
+        return fail(ctx, FC_ERR_UNSUPPORTED, "summand kind not on the path");
+      m.sum_kind[k] = kinds[k];
+      for (int j = 0; j < 4; ++j) m.sum_par[k][j] = p[j];
+    }
+    if (!iso) return fail(ctx, FC_ERR_UNSUPPORTED, "MAT_ElastHyper needs at least one isotropic summand here");
+    // one CoupNeoHooke summand is the material of the closed-form kernels
+    if (n_summands == 1 && kinds[0] == FC_SUMMAND_COUPNEOHOOKE)
+    {
+      m.kind = fc::MAT_NEOHOOKE;
+      m.young = params[0];
+      m.nue = params[1];
+    }
+    ctx->mat = m;
+    ctx->have_material = true;
+    return FC_OK;
+  }
+
+  int fc_solid_set_fibers(fc_ctx* ctx, const double* fiber1)
+  {
+    if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede set_fibers");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    dev_free(ctx->d_fiber);
+    if (!fiber1) return FC_OK;
+    std::vector<double> f((size_t)3 * ctx->n_ele);
+    for (int e = 0; e < ctx->n_ele; ++e)
+    {
+      // read_anisotropy_fiber (src/mat/4C_mat_anisotropy_utils.cpp:19-44): normalised, a zero vector is an error
+      const double* v = fiber1 + 3 * (size_t)e;
+      const double nrm = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+      if (nrm < 1e-9) return fail(ctx, FC_ERR_INVALID, "The given fiber is not a vector but zero.");
+      for (int i = 0; i < 3; ++i) f[3 * (size_t)e + i] = v[i] / nrm;
+    }
+    FC_CUDA(dev_upload(ctx->d_fiber, f.data(), f.size(), ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
     return FC_OK;
   }
 
@@ -164,6 +226,7 @@ extern "C"
     FC_CUDA(dev_upload(ctx->d_gpw, w.data(), w.size(), ctx->stream));
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
+    dev_free(ctx->d_fiber);  // fibres belong to the elements of the previous mesh
     dev_free(ctx->d_ele_perm);
     {
       // launch-slot order of the tensor-core kernels.  Large meshes: visit the elements so that a row's contributions arrive

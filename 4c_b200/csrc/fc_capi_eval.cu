@@ -132,7 +132,7 @@ namespace
   {
     if (flags & FC_EVAL_FORCE_GENERIC) return false;
     const bool fbar = ctx->formulation == FC_FORM_FBAR, nh = ctx->mat.kind == fc::MAT_NEOHOOKE;
-    if (ctx->celltype == FC_HEX8) return nh ? (fbar || !(flags & FC_EVAL_CLOSED_FORM_FMA)) : !fbar;  // k_hex8_neohooke_mma, k_hex8_mma_ext
+    if (ctx->celltype == FC_HEX8) return nh ? (fbar || !(flags & FC_EVAL_CLOSED_FORM_FMA)) : (ctx->mat.kind == fc::MAT_SVK && !fbar);  // k_hex8_neohooke_mma, k_hex8_mma_ext
     return nh && !fbar;                                                                            // k_nh_mma_gen
   }
 
@@ -168,6 +168,7 @@ namespace
     A.dbc = ctx->have_dbc ? ctx->d_dbc : nullptr;
     A.err = ctx->d_err;
     A.mat = ctx->mat;
+    A.fiber = ctx->d_fiber;
     return A;
   }
 

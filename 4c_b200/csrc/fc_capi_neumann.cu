@@ -1,0 +1,119 @@
+// fc_solid_neumann_*: Neumann loads of TYPE Live on the device, the external force of
+// Solid::ModelEvaluator::Structure::apply_force_external -> Discretization::evaluate_neumann
+// (src/structure_new/src/model_evaluator/4C_structure_new_model_evaluator_structure.cpp:368-396).
+#include "fc_host_util.hpp"
+#include "fc_kernels_neumann.cuh"
+
+namespace
+{
+  // device copy of a host|device array of n elements; tmp is set when a staging buffer was allocated
+  template <class T>
+  int stage_in(fc_ctx* ctx, const T* p, size_t n, const T** dev, T** tmp)
+  {
+    *tmp = nullptr;
+    *dev = p;
+    if (!p || n == 0 || is_device_ptr(p)) return FC_OK;
+    FC_CUDA(cudaMalloc((void**)tmp, n * sizeof(T)));
+    FC_CUDA(cudaMemcpyAsync(*tmp, p, n * sizeof(T), cudaMemcpyHostToDevice, ctx->stream));
+    *dev = *tmp;
+    return FC_OK;
+  }
+
+  int check_val(fc_ctx* ctx, const int* onoff, const double* val, fc::NeumannVal& V)
+  {
+    if (!onoff || !val) return fail(ctx, FC_ERR_INVALID, "ONOFF and VAL are required");
+    for (int i = 0; i < 3; ++i)
+    {
+      V.onoff[i] = onoff[i];
+      V.val[i] = val[i];
+    }
+    return FC_OK;
+  }
+
+  // shared body: mode 0 = add the load into f_ext, 1 = hand out the Gauss-point reference coordinates
+  int neumann_run(fc_ctx* ctx, bool surface, int face_type, int n_items, const int* items, const int* onoff, const double* val,
+      const double* gp_factor, double* out, bool coords)
+  {
+    if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede the Neumann evaluation");
+    if (n_items < 0 || (n_items > 0 && !items) || !out) return fail(ctx, FC_ERR_INVALID, "item list and output are required");
+    if (surface && face_type != FC_FACE_QUAD4 && face_type != FC_FACE_QUAD9 && face_type != FC_FACE_TRI6)
+      return fail(ctx, FC_ERR_UNSUPPORTED, "surface cell type");
+    fc::NeumannVal V{};
+    if (!coords)
+      if (int rc = check_val(ctx, onoff, val, V)) return rc;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    const int per = surface ? fc::face_nen(face_type) : 1;
+    const int ngp = surface ? fc::face_ngp(face_type) : fc::cell_ngp(ctx->celltype);
+    for (size_t i = 0; i < (size_t)n_items * per; ++i)
+      if (items[i] < 0 || items[i] >= (surface ? ctx->n_col_nodes : ctx->n_ele)) return fail(ctx, FC_ERR_INVALID, surface ? "face node out of range" : "element out of range");
+    const size_t n_out = coords ? (size_t)n_items * ngp * 3 : (size_t)ctx->n_row_dof;
+    if (n_items == 0) return FC_OK;
+    const int* d_items = nullptr;
+    int* t_items = nullptr;
+    FC_CUDA(dev_upload(t_items, items, (size_t)n_items * per, ctx->stream));
+    d_items = t_items;
+    const double* d_fac = nullptr;
+    double* t_fac = nullptr;
+    int rc = coords ? FC_OK : stage_in(ctx, gp_factor, (size_t)n_items * ngp * 3, &d_fac, &t_fac);
+    double *d_out = out, *t_out = nullptr;
+    const bool out_dev = is_device_ptr(out);
+    cudaError_t e = cudaSuccess;
+    if (rc == FC_OK && !out_dev)
+    {
+      e = cudaMalloc((void**)&t_out, n_out * sizeof(double));
+      if (e == cudaSuccess && !coords) e = cudaMemcpyAsync(t_out, out, n_out * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);  // += semantics
+      d_out = t_out;
+    }
+    if (rc == FC_OK && e == cudaSuccess)
+    {
+      const int bs = 128;
+      double* f = coords ? nullptr : d_out;
+      double* xc = coords ? d_out : nullptr;
+      if (surface)
+        fc::k_neumann_surface<<<(n_items + bs - 1) / bs, bs, 0, ctx->stream>>>(ctx->d_X, d_items, face_type, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
+      else
+      {
+        const long long nt = (long long)n_items * ngp;
+        const unsigned gs = (unsigned)((nt + bs - 1) / bs);
+        if (ctx->celltype == FC_HEX8) fc::k_neumann_volume<fc::HEX8><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
+        if (ctx->celltype == FC_HEX27) fc::k_neumann_volume<fc::HEX27><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
+        if (ctx->celltype == FC_TET10) fc::k_neumann_volume<fc::TET10><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
+      }
+      ctx->launches++;
+      e = cudaGetLastError();
+      if (e == cudaSuccess && !out_dev) e = cudaMemcpyAsync(out, d_out, n_out * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    const cudaError_t es = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess) e = es;
+    cudaFree(t_items);
+    if (t_fac) cudaFree(t_fac);
+    if (t_out) cudaFree(t_out);
+    if (rc != FC_OK) return rc;
+    FC_CUDA(e);
+    return FC_OK;
+  }
+}  // namespace
+
+extern "C"
+{
+  int fc_solid_neumann_surface(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, const int* onoff, const double* val,
+      const double* gp_factor, double* f_ext)
+  {
+    return neumann_run(ctx, true, face_type, n_faces, face_nodes, onoff, val, gp_factor, f_ext, false);
+  }
+
+  int fc_solid_neumann_volume(fc_ctx* ctx, int n_ele, const int* ele_lids, const int* onoff, const double* val, const double* gp_factor, double* f_ext)
+  {
+    return neumann_run(ctx, false, 0, n_ele, ele_lids, onoff, val, gp_factor, f_ext, false);
+  }
+
+  int fc_solid_neumann_surface_gp_coords(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, double* gp_coords)
+  {
+    return neumann_run(ctx, true, face_type, n_faces, face_nodes, nullptr, nullptr, nullptr, gp_coords, true);
+  }
+
+  int fc_solid_neumann_volume_gp_coords(fc_ctx* ctx, int n_ele, const int* ele_lids, double* gp_coords)
+  {
+    return neumann_run(ctx, false, 0, n_ele, ele_lids, nullptr, nullptr, nullptr, gp_coords, true);
+  }
+}

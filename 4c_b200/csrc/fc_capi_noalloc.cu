@@ -204,6 +204,7 @@ extern "C" int fc_solid_evaluate_stress_noalloc(fc_ctx* ctx, const double* u_col
   A.dNtab = ctx->d_dNtab;
   A.u = u_col_dev;
   A.mat = ctx->mat;
+  A.fiber = ctx->d_fiber;
   const bool fbar = ctx->formulation == FC_FORM_FBAR;
   if (ctx->celltype == FC_HEX8)
     return fbar ? stress_noalloc_impl<fc::HEX8, fc::FORM_FBAR>(ctx, A, stress_type, scratch, nodal_stress_dev)

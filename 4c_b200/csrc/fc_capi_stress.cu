@@ -165,6 +165,7 @@ extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int st
   A.dNtab = ctx->d_dNtab;
   A.u = d_u;
   A.mat = ctx->mat;
+  A.fiber = ctx->d_fiber;
   const bool fbar = ctx->formulation == FC_FORM_FBAR;
   int rc = FC_ERR_UNSUPPORTED;
   if (ctx->celltype == FC_HEX8)

@@ -32,7 +32,8 @@ struct fc_ctx
   int geom_bad_count = 0, geom_first_bad_gid = -1;
 
   // material
-  fc::MatParams mat{fc::MAT_NEOHOOKE, 10.0, 0.25};
+  fc::MatParams mat{fc::MAT_NEOHOOKE, 10.0, 0.25, 0, {0, 0, 0, 0}, {{0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}}};
+  double* d_fiber = nullptr;  // [n_ele][3] unit fibre directions (fc_solid_set_fibers) or nullptr
   bool have_material = false;
 
   // graph (node-block CSR: every owned node row lists its coupled column nodes, ascending LID)

@@ -29,6 +29,7 @@ namespace fc
     const unsigned char* slots;   // [n_ele][nen][nen]
     const unsigned char* dbc;     // [n_row_dof] or nullptr
     const double* geom;           // hex8 geometry cache [n_ele][72] (k_hex8_geom_cache) or nullptr
+    const double* fiber;          // [n_ele][3] unit fibre direction FIBER1 of every element or nullptr (anisotropic summands)
     // outputs
     double* f;             // [n_row_dof] or nullptr
     double* K;             // [nnz] or nullptr

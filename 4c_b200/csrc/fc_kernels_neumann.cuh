@@ -1,0 +1,120 @@
+// Neumann loads of TYPE Live: dead loads integrated over the reference configuration.
+//   surface  src/solid_3D_ele/4C_solid_3D_ele_surface_evaluate.cpp:225-330 (neum_live):
+//            f[a][dof] += N_a w sqrt(det(metric)) val[dof] funct[dof](X_gp, t)
+//   volume   src/solid_3D_ele/4C_solid_3D_ele_neumann_evaluator.cpp:43-115 (evaluate_neumann):
+//            f[a][dof] += N_a w detJ val[dof] funct[dof](X_gp, t), stiffness Gauss rule of the cell
+// The function factor funct[dof](X_gp, t) is the caller's: gp_factor[item][gp][3] (nullptr = 1), evaluated at the
+// reference coordinates that k_neumann_*_gp_coords hand out.  Owned rows only, like the element path.
+// Not on the per-iteration path (loads change per time step): one thread per face / element, atomics into f_ext.
+#pragma once
+#include "fc_fem_surface.cuh"
+#include "fc_kernels_common.cuh"
+
+namespace fc
+{
+  struct NeumannVal
+  {
+    double val[3];
+    int onoff[3];
+  };
+
+  static __global__ void k_neumann_surface(const double* __restrict__ X, const int* __restrict__ face_nodes, int ft, int n_faces, NeumannVal V,
+      const double* __restrict__ gp_factor, int n_row_nodes, double* __restrict__ f, double* __restrict__ gp_coords)
+  {
+    const int face = blockIdx.x * blockDim.x + threadIdx.x;
+    if (face >= n_faces) return;
+    const int nen = face_nen(ft), ngp = face_ngp(ft);
+    double P[face_max_nen][3];
+    int nodes[face_max_nen];
+    for (int a = 0; a < nen; ++a)
+    {
+      nodes[a] = face_nodes[(size_t)face * nen + a];
+      for (int i = 0; i < 3; ++i) P[a][i] = X[3 * (size_t)nodes[a] + i];
+    }
+    double fa[face_max_nen][3];
+    for (int a = 0; a < nen; ++a) fa[a][0] = fa[a][1] = fa[a][2] = 0.0;
+    for (int g = 0; g < ngp; ++g)
+    {
+      double rs[2], w, N[face_max_nen], dr[face_max_nen], ds[face_max_nen];
+      face_gauss_point(ft, g, rs, &w);
+      face_shape(ft, rs, N, dr, ds);
+      if (gp_coords)
+      {
+        for (int i = 0; i < 3; ++i)
+        {
+          double x = 0.0;
+          for (int a = 0; a < nen; ++a) x += N[a] * P[a][i];
+          gp_coords[((size_t)face * ngp + g) * 3 + i] = x;
+        }
+        continue;
+      }
+      double g1[3] = {0, 0, 0}, g2[3] = {0, 0, 0};
+      for (int a = 0; a < nen; ++a)
+        for (int i = 0; i < 3; ++i)
+        {
+          g1[i] += dr[a] * P[a][i];
+          g2[i] += ds[a] * P[a][i];
+        }
+      const double m11 = g1[0] * g1[0] + g1[1] * g1[1] + g1[2] * g1[2];
+      const double m22 = g2[0] * g2[0] + g2[1] * g2[1] + g2[2] * g2[2];
+      const double m12 = g1[0] * g2[0] + g1[1] * g2[1] + g1[2] * g2[2];
+      const double detA = sqrt(m11 * m22 - m12 * m12);
+      for (int dof = 0; dof < 3; ++dof)
+      {
+        if (!V.onoff[dof]) continue;
+        const double functfac = gp_factor ? gp_factor[((size_t)face * ngp + g) * 3 + dof] : 1.0;
+        const double fac = w * detA * V.val[dof] * functfac;
+        for (int a = 0; a < nen; ++a) fa[a][dof] += N[a] * fac;
+      }
+    }
+    if (gp_coords) return;
+    for (int a = 0; a < nen; ++a)
+      if (nodes[a] < n_row_nodes)
+        for (int dof = 0; dof < 3; ++dof)
+          if (V.onoff[dof]) red_add(f + 3 * (size_t)nodes[a] + dof, fa[a][dof]);
+  }
+
+  // one thread per (listed element, Gauss point)
+  template <int CT>
+  __global__ void k_neumann_volume(const double* __restrict__ X, const int* __restrict__ conn, const int* __restrict__ ele_list, int n_list, NeumannVal V,
+      const double* __restrict__ gp_factor, int n_row_nodes, double* __restrict__ f, double* __restrict__ gp_coords)
+  {
+    constexpr int NEN = Cell<CT>::nen, NGP = Cell<CT>::ngp;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= (long long)n_list * NGP) return;
+    const int item = (int)(tid / NGP), g = (int)(tid % NGP);
+    const int e = ele_list[item];
+    double xi[3], w, N[NEN], dN[3 * NEN];
+    gauss_point<CT>(g, xi, &w);
+    shape_function<CT>(xi, N);
+    shape_deriv1<CT>(xi, dN);
+    double J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, xg[3] = {0, 0, 0};
+    for (int a = 0; a < NEN; ++a)
+    {
+      const int n = conn[(size_t)e * NEN + a];
+      for (int i = 0; i < 3; ++i)
+      {
+        const double x = X[3 * (size_t)n + i];
+        xg[i] += N[a] * x;
+        for (int d = 0; d < 3; ++d) J[3 * d + i] += dN[3 * a + d] * x;
+      }
+    }
+    if (gp_coords)
+    {
+      for (int i = 0; i < 3; ++i) gp_coords[((size_t)item * NGP + g) * 3 + i] = xg[i];
+      return;
+    }
+    const double intfac = w * det3(J);
+    for (int dof = 0; dof < 3; ++dof)
+    {
+      if (!V.onoff[dof]) continue;
+      const double functfac = gp_factor ? gp_factor[((size_t)item * NGP + g) * 3 + dof] : 1.0;
+      const double vif = V.val[dof] * functfac * intfac;
+      for (int a = 0; a < NEN; ++a)
+      {
+        const int n = conn[(size_t)e * NEN + a];
+        if (n < n_row_nodes) red_add(f + 3 * (size_t)n + dof, N[a] * vif);
+      }
+    }
+  }
+}  // namespace fc

@@ -42,7 +42,7 @@ namespace fc
         F[2] * F[2] + F[5] * F[5] + F[8] * F[8], F[0] * F[1] + F[3] * F[4] + F[6] * F[7],
         F[1] * F[2] + F[4] * F[5] + F[7] * F[8], F[0] * F[2] + F[3] * F[5] + F[6] * F[8]};
     double S[6], cmat[36];
-    material_evaluate(A.mat, C, S, cmat);
+    material_evaluate(A.mat, C, S, cmat, A.fiber ? A.fiber + 3 * (size_t)e : nullptr);
     double* out = gp_stress + ((size_t)e * NGP + gp) * 6;
     if (stress_type == 0)
     {

@@ -4,6 +4,11 @@
 //   ElastHyper toolbox    src/mat/4C_mat_elasthyper_service.cpp:19-78 (driver), :162-215 (isotropic
 //                         stress + cmat from gamma/delta), :413-431 (gamma/delta)
 //   CoupNeoHooke summand  src/mat/elast/4C_mat_elast_coupneohooke.cpp:17-25,60-77
+//   summand list          the loops over potsum_ of 4C_mat_elasthyper_service.cpp:90-104 (isotropic principal
+//                         derivatives) and :386-396 (anisotropic principal stress + cmat)
+//   CoupSVK summand       src/mat/elast/4C_mat_elast_coupSaintVenantKirchhoff.cpp:15-29,47-57
+//   CoupAnisoExpo summand src/mat/elast/4C_mat_elast_coupanisoexpobase.cpp:157-185, one fibre per element (FIBER1,
+//                         normalised: src/mat/4C_mat_anisotropy_utils.cpp:19-44), structural tensor a a^T
 // Written in tensor form (no Voigt scale-factor tables): the same algebra as the reference, a
 // different evaluation order.
 #pragma once
@@ -14,13 +19,24 @@ namespace fc
   enum
   {
     MAT_SVK = 0,
-    MAT_NEOHOOKE = 1
+    MAT_NEOHOOKE = 1,   // MAT_ElastHyper with one CoupNeoHooke summand (young, nue): the closed-form kernels
+    MAT_ELASTHYPER = 2  // MAT_ElastHyper with the summand list below: generic kernel
   };
+  enum
+  {
+    SUM_COUPNEOHOOKE = 0,  // par = YOUNG, NUE
+    SUM_COUPSVK = 1,       // par = YOUNG, NUE
+    SUM_COUPANISOEXPO = 2  // par = K1, K2, K1COMP, K2COMP
+  };
+  constexpr int max_summands = 4;
 
   struct MatParams
   {
     int kind;
     double young, nue;
+    int n_summands;
+    int sum_kind[max_summands];
+    double sum_par[max_summands][4];
   };
 
   // symmetric 3x3 stored as 6: [00,11,22,01,12,02]
@@ -58,6 +74,16 @@ namespace fc
     }
   }
 
+  // Invariant derivatives of ELAST_CoupSVK: Psi = (mue/4 + lambda/8) I1^2 - (3 lambda/4 + mue/2) I1 - mue/2 I2 + const
+  FC_HD void coupsvk_derivs(double young, double nue, const double* prinv, double* dPI, double* ddPII)
+  {
+    const double lambda = nue == 0.5 ? 0.0 : young * nue / ((1.0 + nue) * (1.0 - 2.0 * nue));
+    const double mue = young / (2.0 * (1.0 + nue));
+    dPI[0] += (0.5 * mue + 0.25 * lambda) * prinv[0] - 0.75 * lambda - 0.5 * mue;
+    dPI[1] -= 0.5 * mue;
+    ddPII[0] += 0.5 * mue + 0.25 * lambda;
+  }
+
   FC_HD void gamma_delta(const double* prinv, const double* dPI, const double* ddPII, double* gamma, double* delta)
   {
     gamma[0] = 2.0 * (dPI[0] + prinv[0] * dPI[1]);
@@ -86,7 +112,8 @@ namespace fc
 
   // C: right Cauchy-Green as symmetric-6 (true tensor components, no doubled shear).
   // S[6], cmat[36] (cmat[6*r+c], symmetric).
-  FC_HD void material_evaluate(const MatParams& mp, const double* C, double* S, double* cmat)
+  // fiber [3]: unit fibre direction of the element (anisotropic summands only)
+  FC_HD void material_evaluate(const MatParams& mp, const double* C, double* S, double* cmat, const double* fiber = nullptr)
   {
     if (mp.kind == MAT_SVK)
     {
@@ -110,7 +137,14 @@ namespace fc
     prinv[2] = sym_det(C);
     sym_inv(C, prinv[2], iC);
     double dPI[3] = {0, 0, 0}, ddPII[6] = {0, 0, 0, 0, 0, 0};
-    coupneohooke_derivs(mp.young, mp.nue, prinv, dPI, ddPII);
+    if (mp.kind == MAT_NEOHOOKE)
+      coupneohooke_derivs(mp.young, mp.nue, prinv, dPI, ddPII);
+    else
+      for (int k = 0; k < mp.n_summands; ++k)
+      {
+        if (mp.sum_kind[k] == SUM_COUPNEOHOOKE) coupneohooke_derivs(mp.sum_par[k][0], mp.sum_par[k][1], prinv, dPI, ddPII);
+        if (mp.sum_kind[k] == SUM_COUPSVK) coupsvk_derivs(mp.sum_par[k][0], mp.sum_par[k][1], prinv, dPI, ddPII);
+      }
     double gamma[3], delta[8];
     gamma_delta(prinv, dPI, ddPII, gamma, delta);
     const double id2[6] = {1, 1, 1, 0, 0, 0};
@@ -126,6 +160,22 @@ namespace fc
         if (r == c) v += delta[7] * (r < 3 ? 1.0 : 0.5);
         cmat[6 * r + c] = v;
         cmat[6 * c + r] = v;
+      }
+    if (mp.kind != MAT_ELASTHYPER || !fiber) return;
+    // anisotropic principal summands: S += 2 dPsi/dI4 A, cmat += 4 d2Psi/dI4^2 A x A, I4 = a . C a
+    for (int k = 0; k < mp.n_summands; ++k)
+      if (mp.sum_kind[k] == SUM_COUPANISOEXPO)
+      {
+        const double A[6] = {fiber[0] * fiber[0], fiber[1] * fiber[1], fiber[2] * fiber[2], fiber[0] * fiber[1], fiber[1] * fiber[2], fiber[0] * fiber[2]};
+        const double I4 = A[0] * C[0] + A[1] * C[1] + A[2] * C[2] + 2.0 * (A[3] * C[3] + A[4] * C[4] + A[5] * C[5]);
+        const double k1 = I4 < 1.0 ? mp.sum_par[k][2] : mp.sum_par[k][0], k2 = I4 < 1.0 ? mp.sum_par[k][3] : mp.sum_par[k][1];
+        const double d = I4 - 1.0, ex = exp(k2 * d * d);
+        const double gam = 2.0 * k1 * d * ex, del = 4.0 * (1.0 + 2.0 * k2 * d * d) * k1 * ex;
+        for (int r = 0; r < 6; ++r)
+        {
+          S[r] += gam * A[r];
+          for (int c = 0; c < 6; ++c) cmat[6 * r + c] += del * A[r] * A[c];
+        }
       }
   }
 }  // namespace fc

@@ -431,7 +431,8 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     comm = None
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=180))  # a mismatch fails in minutes, not in ten
         comm = fc.capi.nccl_comm_init(rank, world, local)  # the library's own communicator (ncclCommInitRank through ctypes)
 
     # ---- problem setup (not timed) -------------------------------------------------------------------
@@ -457,12 +458,13 @@ def run_ours(args):
     ms_per_step, zero_ms, ele_ms, win = P.timed(args.steps, flags, overlap)
     sampler.window = list(win)
     launches = s.launch_count() - l0
-    if len([1 for t, _ in sampler.rows if sampler.window[0] <= t <= sampler.window[1]]) < 3:
-        # a timed region shorter than a few sampling periods: keep the GPU on the identical steps until the sampler has rows
-        t_more = time.monotonic()
-        while time.monotonic() - t_more < 0.3:
+    if args.steps * ms_per_step < 300.0:
+        # a timed region shorter than a few sampling periods: keep the GPU on the identical steps for 0.3 s so that the sampler
+        # has rows (the summary says which rows it used).  The count comes from the all-reduced step time: every rank runs the
+        # same number of steps, hence the same number of halo exchanges.
+        for _ in range(int(300.0 / ms_per_step) + 1):
             P.step(flags, overlap)
-        torch.cuda.synchronize()
+        P.barrier()
     sampler.stop()
     n_global_ele = n[0] * n[1] * n[2]
     value = n_global_ele / (ms_per_step * 1e-3)

@@ -120,6 +120,23 @@ extern "C"
 
   int fc_solid_set_material(fc_ctx* ctx, int kind, const double* params, int n_params);
 
+  /* MAT_ElastHyper with a list of summands (src/mat/4C_mat_elasthyper.cpp:76-90): kinds [n_summands],
+   * params [n_summands][4].  One FC_SUMMAND_COUPNEOHOOKE alone is the same material as
+   * FC_MAT_ELASTHYPER_COUPNEOHOOKE (closed-form tensor-core kernels); every other list runs the generic B-operator
+   * kernel.  Anisotropic summands take the element fibres of fc_solid_set_fibers. */
+  enum
+  {
+    FC_SUMMAND_COUPNEOHOOKE = 0, /* ELAST_CoupNeoHooke  YOUNG NUE - -   (src/mat/elast/4C_mat_elast_coupneohooke.cpp) */
+    FC_SUMMAND_COUPSVK = 1,      /* ELAST_CoupSVK       YOUNG NUE - -   (src/mat/elast/4C_mat_elast_coupSaintVenantKirchhoff.cpp:15-57) */
+    FC_SUMMAND_COUPANISOEXPO = 2 /* ELAST_CoupAnisoExpo K1 K2 K1COMP K2COMP, INIT 1, FIBER_ID 1, STRATEGY Standard
+                                    (src/mat/elast/4C_mat_elast_coupanisoexpobase.cpp:157-185) */
+  };
+  int fc_solid_set_material_elasthyper(fc_ctx* ctx, int n_summands, const int* kinds, const double* params);
+  /* FIBER1 of every column element ([n_col_ele][3], host; the element line's FIBER1 x y z, src/solid_3D_ele/4C_solid_3D_ele.cpp:60),
+   * normalised like Mat::read_anisotropy_fiber (src/mat/4C_mat_anisotropy_utils.cpp:19-44).  NULL removes them.
+   * Call after fc_solid_set_mesh. */
+  int fc_solid_set_fibers(fc_ctx* ctx, const double* fiber1);
+
   /* CSR graph of the rank's rows, the state of Epetra_CrsMatrix after FillComplete on the saved
    * graph (4C_linalg_sparsematrix.cpp:353-378,843-865): rows = owned DOFs, column ids local and
    * ascending per row.  set_graph adopts a caller-provided graph (host arrays); build_graph
@@ -162,6 +179,35 @@ extern "C"
    * added into M_values [nnz] (host|device) in the layout of the stiffness graph, owned rows only.  flags:
    * FC_EVAL_ZERO_FIRST.  Constant for a mesh: call once, not per Newton iteration. */
   int fc_solid_evaluate_mass(fc_ctx* ctx, double density, int flags, double* M_values);
+
+  /* Neumann loads of TYPE Live: the external force that
+   * Solid::ModelEvaluator::Structure::apply_force_external assembles through Discretization::evaluate_neumann
+   * (src/structure_new/src/model_evaluator/4C_structure_new_model_evaluator_structure.cpp:368-396), added into f_ext
+   * [n_row_dof] (host|device, += like the reference's assemble; owned rows only, so pass every face / element that
+   * touches an owned node).
+   *   surface  neum_live of src/solid_3D_ele/4C_solid_3D_ele_surface_evaluate.cpp:225-330 on faces given by their nodes
+   *            (face_nodes [n_faces][4|9|6] column-node LIDs in the reference's quad4 / quad9 / tri6 node order), rules
+   *            quad_4point / quad_9point / tri_6point with the reference's 13-digit constants
+   *            (4C_solid_3D_ele_surface.cpp:58-77, 4C_fem_general_utils_integration.cpp:6151-6231, 6374-6396)
+   *   volume   evaluate_neumann of src/solid_3D_ele/4C_solid_3D_ele_neumann_evaluator.cpp:43-115 on column elements
+   *            ele_lids [n_ele], stiffness Gauss rule of the cell
+   *   onoff [3], val [3]  ONOFF and VAL of the condition's first three DOFs
+   *   gp_factor           [n][ngp][3] (host|device) value of the condition's FUNCT per Gauss point and DOF
+   *                       (FunctionOfSpaceTime::evaluate(X_gp, t, dof)); NULL = 1.  The library does not parse
+   *                       functions: the caller evaluates them at the reference coordinates of the Gauss points,
+   *                       which the *_gp_coords calls return ([n][ngp][3], host|device). */
+  enum
+  {
+    FC_FACE_QUAD4 = 0,
+    FC_FACE_QUAD9 = 1,
+    FC_FACE_TRI6 = 2
+  };
+  int fc_solid_neumann_surface(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, const int* onoff, const double* val,
+      const double* gp_factor, double* f_ext);
+  int fc_solid_neumann_volume(fc_ctx* ctx, int n_ele, const int* ele_lids, const int* onoff, const double* val, const double* gp_factor,
+      double* f_ext);
+  int fc_solid_neumann_surface_gp_coords(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, double* gp_coords);
+  int fc_solid_neumann_volume_gp_coords(fc_ctx* ctx, int n_ele, const int* ele_lids, double* gp_coords);
 
   /* struct_calc_stress post-processing: Gauss-point stresses (calculate_stress,
    * 4C_solid_3D_ele_calc.cpp:347-390; Cauchy = F S F^T / det F, 4C_solid_3D_ele_utils.cpp:20-33) and their extrapolation

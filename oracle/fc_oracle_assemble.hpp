@@ -124,7 +124,7 @@ namespace fc_oracle
   // returns number of elements with an error; first_bad = GID of the first one.
   inline int evaluate_rank(const Mesh& mesh, const Partition& part, const RankSystem& rs, int form,
       const MaterialParams& mp, int action, const double* u_col, double* f_row, double* K_values,
-      int* first_bad)
+      int* first_bad, const double* ele_fiber = nullptr /* [n_ele][3] FIBER1 in mesh element order */)
   {
     const int nen = mesh.nen, nd = 3 * nen;
     std::vector<int> lm(nd), lmowner(nd), localcol(nd);
@@ -150,7 +150,8 @@ namespace fc_oracle
       std::fill(fe.begin(), fe.end(), 0.0);
       if (action == 0) std::fill(Ke.begin(), Ke.end(), 0.0);
       const int err = element_evaluate(
-          mesh.ct, form, mp, X.data(), u.data(), fe.data(), action == 0 ? Ke.data() : nullptr);
+          mesh.ct, form, mp, X.data(), u.data(), fe.data(), action == 0 ? Ke.data() : nullptr, nullptr, 0.0, nullptr, STRESS_CAUCHY,
+          ele_fiber ? ele_fiber + 3 * (size_t)e : nullptr);
       if (err)
       {
         if (nbad == 0 && first_bad) *first_bad = eg;
@@ -208,6 +209,7 @@ namespace fc_oracle
     std::vector<RankSystem> sys;
     int form = FORM_DISP;
     MaterialParams mp{MAT_NEOHOOKE, 10.0, 0.25};
+    std::vector<double> ele_fiber;  // [n_ele][3] or empty
   };
 
   inline int evaluate_job(const Job& job, int action, const std::vector<std::vector<double>>& u_row,
@@ -221,7 +223,8 @@ namespace fc_oracle
       std::vector<double> u_col;
       import_column_state(job.mesh, job.part, job.sys, r, u_row, u_col);
       nbad[r] = evaluate_rank(job.mesh, job.part, job.sys[r], job.form, job.mp, action,
-          u_col.data(), f_row[r].data(), action == 0 ? K_values[r].data() : nullptr, &fb[r]);
+          u_col.data(), f_row[r].data(), action == 0 ? K_values[r].data() : nullptr, &fb[r],
+          job.ele_fiber.empty() ? nullptr : job.ele_fiber.data());
     };
     if (max_threads <= 1 || nr == 1)
       for (int r = 0; r < nr; ++r) work(r);

@@ -5,6 +5,7 @@
 #include <cstring>
 
 #include "fc_oracle_assemble.hpp"
+#include "fc_oracle_neumann.hpp"
 
 using namespace fc_oracle;
 
@@ -125,6 +126,24 @@ extern "C"
     MaterialParams mp{kind, young, nue};
     return element_evaluate(ct, form, mp, X, u, nullptr, nullptr, nullptr, 0.0, gp_stress, stress_type);
   }
+  // Neumann loads TYPE Live on n independent faces / elements (fc_oracle_neumann.hpp): x [n][nen][3] reference coordinates,
+  // functfac [n][ngp][3] or NULL, fe [n][nen][3] += (may be NULL), gp_coord [n][ngp][3] (may be NULL)
+  void oracle_surface_neumann(int ft, int n, const double* x, const int* onoff, const double* val, const double* functfac, double* fe,
+      double* gp_coord)
+  {
+    const int nn = face_num_nodes(ft), ng = face_num_gp(ft);
+    for (int k = 0; k < n; ++k)
+      surface_neumann_live(ft, x + (size_t)k * nn * 3, onoff, val, functfac ? functfac + (size_t)k * ng * 3 : nullptr,
+          fe ? fe + (size_t)k * nn * 3 : nullptr, gp_coord ? gp_coord + (size_t)k * ng * 3 : nullptr);
+  }
+  void oracle_volume_neumann(int ct, int n, const double* X, const int* onoff, const double* val, const double* functfac, double* fe,
+      double* gp_coord)
+  {
+    const int nn = num_nodes(ct), ng = num_gp(ct);
+    for (int k = 0; k < n; ++k)
+      volume_neumann_live(ct, X + (size_t)k * nn * 3, onoff, val, functfac ? functfac + (size_t)k * ng * 3 : nullptr,
+          fe ? fe + (size_t)k * nn * 3 : nullptr, gp_coord ? gp_coord + (size_t)k * ng * 3 : nullptr);
+  }
   // batch of independent elements (X,u: [n][3*nen]); used as the checker for the CUDA
   // element-level entry point.  returns the number of failing elements.
   int oracle_element_evaluate_batch(int ct, int form, int kind, double young, double nue, int n,
@@ -183,6 +202,36 @@ extern "C"
     auto* js = (JobState*)h;
     js->job.form = form;
     js->job.mp = MaterialParams{kind, young, nue};
+  }
+  // MAT_ElastHyper with a summand list (kinds [n], par [n][4]) and optional element fibres FIBER1 [n_ele][3] in the job's
+  // element order (NULL = none)
+  void oracle_job_set_elasthyper(void* h, int form, int n, const int* kinds, const double* par, const double* ele_fiber)
+  {
+    auto* js = (JobState*)h;
+    js->job.form = form;
+    MaterialParams mp{MAT_ELASTHYPER, 0.0, 0.0};
+    mp.n_summands = n;
+    for (int k = 0; k < n && k < 4; ++k)
+    {
+      mp.sum_kind[k] = kinds[k];
+      for (int j = 0; j < 4; ++j) mp.sum_par[k][j] = par[4 * k + j];
+    }
+    js->job.mp = mp;
+    js->job.ele_fiber.clear();
+    if (ele_fiber) js->job.ele_fiber.assign(ele_fiber, ele_fiber + 3 * js->job.mesh.ele_gid.size());
+  }
+  // one element with a summand list: fe, Ke (col-major), optional Gauss-point stresses
+  int oracle_element_evaluate_elasthyper(int ct, int form, int n, const int* kinds, const double* par, const double* fiber, const double* X,
+      const double* u, double* fe, double* Ke, double* gp_stress, int stress_type)
+  {
+    MaterialParams mp{MAT_ELASTHYPER, 0.0, 0.0};
+    mp.n_summands = n;
+    for (int k = 0; k < n && k < 4; ++k)
+    {
+      mp.sum_kind[k] = kinds[k];
+      for (int j = 0; j < 4; ++j) mp.sum_par[k][j] = par[4 * k + j];
+    }
+    return element_evaluate(ct, form, mp, X, u, fe, Ke, nullptr, 0.0, gp_stress, stress_type, fiber);
   }
   int oracle_job_nranks(void* h) { return ((JobState*)h)->job.part.nranks; }
   void oracle_job_subdivisions(void* h, int* s)

@@ -181,7 +181,7 @@ namespace fc_oracle
   template <int NEN, int NGP>
   inline int element_evaluate_t(int ct, int form, const MaterialParams& mp, const double* X,
       const double* u, double* fe, double* Ke, double* Me, double rho, double* gp_stress = nullptr,
-      int stress_type = STRESS_CAUCHY)
+      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr)
   {
     constexpr int ND = 3 * NEN;
     double x[ND];
@@ -267,7 +267,7 @@ namespace fc_oracle
       }
 
       double S[6], cmat[36];
-      material_evaluate(mp, Fmat, E, S, cmat);
+      material_evaluate(mp, Fmat, E, S, cmat, fiber);
       if (gp_stress)
       {
         // calculate_stress / assemble_stress_type_to_matrix_row: solid_3D_ele_calc.cpp:347-390, calc_lib_io.hpp:167-190
@@ -333,16 +333,16 @@ namespace fc_oracle
 
   inline int element_evaluate(int ct, int form, const MaterialParams& mp, const double* X,
       const double* u, double* fe, double* Ke, double* Me = nullptr, double rho = 0.0, double* gp_stress = nullptr,
-      int stress_type = STRESS_CAUCHY)
+      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr)
   {
     switch (ct)
     {
       case HEX8:
-        return element_evaluate_t<8, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type);
+        return element_evaluate_t<8, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
       case HEX27:
-        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type);
+        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
       case TET10:
-        return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type);
+        return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
     }
     return -1;
   }

@@ -1,0 +1,223 @@
+// ORACLE (test infrastructure): CPU restatement of the reference's Neumann loads of TYPE Live.
+//   surface  Discret::Elements::SolidSurface::evaluate_neumann, case neum_live
+//            src/solid_3D_ele/4C_solid_3D_ele_surface_evaluate.cpp:225-330
+//   volume   Discret::Elements::evaluate_neumann
+//            src/solid_3D_ele/4C_solid_3D_ele_neumann_evaluator.cpp:43-115
+//   2D shape functions  src/core/fem/src/general/utils/4C_fem_general_utils_fem_shapefunctions.hpp:2003-2015 (quad4),
+//                       :2065-2087 (quad9), :2098-2111 (tri6) and their first derivatives
+//   2D Gauss rules      src/core/fem/src/general/utils/4C_fem_general_utils_integration.cpp:6151-6183 (quad_4point),
+//                       :6185-6231 (quad_9point), :6374-6396 (tri_6point), truncated constants as written there
+//   rule per cell       src/solid_3D_ele/4C_solid_3D_ele_surface.cpp:58-77
+// Parity: pinned by the reference's RESULT DESCRIPTION of tests/input_files/solid_ele_hex8_Standard_eas_none_volume_neumann.dat
+// (surface + volume loads with FUNCT (x+1)(y+2)(z+3) and t; tests/golden) and by the surface loads of the other goldens.
+#pragma once
+#include <cmath>
+
+#include "fc_oracle_fem.hpp"
+
+namespace fc_oracle
+{
+  enum
+  {
+    QUAD4 = 0,
+    QUAD9 = 1,
+    TRI6 = 2
+  };
+  inline int face_num_nodes(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 ? 9 : 6); }
+  inline int face_num_gp(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 ? 9 : 6); }
+
+  // shape_function_2d / shape_function_2d_deriv1
+  inline void shape_function_2d(int ft, double r, double s, double* funct, double* deriv_r, double* deriv_s)
+  {
+    if (ft == QUAD4)
+    {
+      const double rp = 1.0 + r, rm = 1.0 - r, sp = 1.0 + s, sm = 1.0 - s;
+      funct[0] = 0.25 * rm * sm;
+      funct[1] = 0.25 * rp * sm;
+      funct[2] = 0.25 * rp * sp;
+      funct[3] = 0.25 * rm * sp;
+      deriv_r[0] = -0.25 * sm;
+      deriv_s[0] = -0.25 * rm;
+      deriv_r[1] = 0.25 * sm;
+      deriv_s[1] = -0.25 * rp;
+      deriv_r[2] = 0.25 * sp;
+      deriv_s[2] = 0.25 * rp;
+      deriv_r[3] = -0.25 * sp;
+      deriv_s[3] = 0.25 * rm;
+    }
+    else if (ft == QUAD9)
+    {
+      const double rp = 1.0 + r, rm = 1.0 - r, sp = 1.0 + s, sm = 1.0 - s;
+      const double r2 = 1.0 - r * r, s2 = 1.0 - s * s, rh = 0.5 * r, sh = 0.5 * s, rs = rh * sh;
+      const double rhp = r + 0.5, rhm = r - 0.5, shp = s + 0.5, shm = s - 0.5;
+      funct[0] = rs * rm * sm;
+      funct[1] = -rs * rp * sm;
+      funct[2] = rs * rp * sp;
+      funct[3] = -rs * rm * sp;
+      funct[4] = -sh * sm * r2;
+      funct[5] = rh * rp * s2;
+      funct[6] = sh * sp * r2;
+      funct[7] = -rh * rm * s2;
+      funct[8] = r2 * s2;
+      deriv_r[0] = -rhm * sh * sm;
+      deriv_s[0] = -shm * rh * rm;
+      deriv_r[1] = -rhp * sh * sm;
+      deriv_s[1] = shm * rh * rp;
+      deriv_r[2] = rhp * sh * sp;
+      deriv_s[2] = shp * rh * rp;
+      deriv_r[3] = rhm * sh * sp;
+      deriv_s[3] = -shp * rh * rm;
+      deriv_r[4] = 2.0 * r * sh * sm;
+      deriv_s[4] = shm * r2;
+      deriv_r[5] = rhp * s2;
+      deriv_s[5] = -2.0 * s * rh * rp;
+      deriv_r[6] = -2.0 * r * sh * sp;
+      deriv_s[6] = shp * r2;
+      deriv_r[7] = rhm * s2;
+      deriv_s[7] = 2.0 * s * rh * rm;
+      deriv_r[8] = -2.0 * r * s2;
+      deriv_s[8] = -2.0 * s * r2;
+    }
+    else
+    {
+      const double t1 = 1.0 - r - s, t2 = r, t3 = s;
+      funct[0] = t1 * (2.0 * t1 - 1.0);
+      funct[1] = t2 * (2.0 * t2 - 1.0);
+      funct[2] = t3 * (2.0 * t3 - 1.0);
+      funct[3] = 4.0 * t2 * t1;
+      funct[4] = 4.0 * t2 * t3;
+      funct[5] = 4.0 * t3 * t1;
+      deriv_r[0] = -3.0 + 4.0 * (r + s);
+      deriv_s[0] = -3.0 + 4.0 * (r + s);
+      deriv_r[1] = 4.0 * r - 1.0;
+      deriv_s[1] = 0.0;
+      deriv_r[2] = 0.0;
+      deriv_s[2] = 4.0 * s - 1.0;
+      deriv_r[3] = 4.0 * (1.0 - 2.0 * r - s);
+      deriv_s[3] = -4.0 * r;
+      deriv_r[4] = 4.0 * s;
+      deriv_s[4] = 4.0 * r;
+      deriv_r[5] = -4.0 * s;
+      deriv_s[5] = 4.0 * (1.0 - r - 2.0 * s);
+    }
+  }
+
+  // IntegrationPoints2D(gaussrule_)
+  inline void gauss_rule_2d(int ft, double (*qxg)[2], double* qwgt)
+  {
+    if (ft == QUAD4)
+    {
+      const double g = 0.5773502691896;
+      const double p[4][2] = {{-g, -g}, {g, -g}, {g, g}, {-g, g}};
+      for (int i = 0; i < 4; ++i)
+      {
+        qxg[i][0] = p[i][0];
+        qxg[i][1] = p[i][1];
+        qwgt[i] = 1.0;
+      }
+    }
+    else if (ft == QUAD9)
+    {
+      const double g = 0.7745966692415, a = 0.5555555555556, b = 0.8888888888889;
+      const double p[9][2] = {{-g, -g}, {g, -g}, {g, g}, {-g, g}, {0.0, -g}, {g, 0.0}, {0.0, g}, {-g, 0.0}, {0.0, 0.0}};
+      const double w[9] = {a * a, a * a, a * a, a * a, b * a, a * b, b * a, a * b, b * b};
+      for (int i = 0; i < 9; ++i)
+      {
+        qxg[i][0] = p[i][0];
+        qxg[i][1] = p[i][1];
+        qwgt[i] = w[i];
+      }
+    }
+    else
+    {
+      const double p[6][2] = {{0.0915762135098, 0.0915762135098}, {0.8168475729805, 0.0915762135098}, {0.0915762135098, 0.8168475729805},
+          {0.4459484909160, 0.1081030181681}, {0.4459484909160, 0.4459484909160}, {0.1081030181681, 0.4459484909160}};
+      for (int i = 0; i < 6; ++i)
+      {
+        qxg[i][0] = p[i][0];
+        qxg[i][1] = p[i][1];
+        qwgt[i] = i < 3 ? 0.0549758718277 : 0.1116907948390;
+      }
+    }
+  }
+
+  // x [numnode][3] reference coordinates of the face nodes; functfac [ngp][3] or nullptr (= 1); elevec1 [numnode][3] +=
+  // gp_coord [ngp][3] (optional output): reference position of the Gauss points (multiply_tn(gp_coord, funct, x))
+  inline void surface_neumann_live(int ft, const double* x, const int* onoff, const double* val, const double* functfac, double* elevec1,
+      double* gp_coord)
+  {
+    const int numnode = face_num_nodes(ft), nquad = face_num_gp(ft);
+    double qxg[9][2], qwgt[9];
+    gauss_rule_2d(ft, qxg, qwgt);
+    for (int gp = 0; gp < nquad; ++gp)
+    {
+      double funct[9], deriv[2][9];
+      shape_function_2d(ft, qxg[gp][0], qxg[gp][1], funct, deriv[0], deriv[1]);
+      if (gp_coord)
+        for (int i = 0; i < 3; ++i)
+        {
+          double c = 0.0;
+          for (int n = 0; n < numnode; ++n) c += funct[n] * x[3 * n + i];
+          gp_coord[3 * gp + i] = c;
+        }
+      if (!elevec1) continue;
+      double dxyzdrs[2][3] = {{0, 0, 0}, {0, 0, 0}};
+      for (int a = 0; a < 2; ++a)
+        for (int i = 0; i < 3; ++i)
+          for (int n = 0; n < numnode; ++n) dxyzdrs[a][i] += deriv[a][n] * x[3 * n + i];
+      double metrictensor[2][2];
+      for (int a = 0; a < 2; ++a)
+        for (int b = 0; b < 2; ++b)
+        {
+          metrictensor[a][b] = 0.0;
+          for (int i = 0; i < 3; ++i) metrictensor[a][b] += dxyzdrs[a][i] * dxyzdrs[b][i];
+        }
+      const double detA = std::sqrt(metrictensor[0][0] * metrictensor[1][1] - metrictensor[0][1] * metrictensor[1][0]);
+      for (int dof = 0; dof < 3; ++dof)
+        if (onoff[dof])
+        {
+          const double ff = functfac ? functfac[3 * gp + dof] : 1.0;
+          const double fac = qwgt[gp] * detA * val[dof] * ff;
+          for (int node = 0; node < numnode; ++node) elevec1[node * 3 + dof] += funct[node] * fac;
+        }
+    }
+  }
+
+  // X [nen][3]; element_force_vector [nen][3] +=; gauss rule = get_gauss_rule_stiffness_matrix<celltype>
+  inline void volume_neumann_live(int ct, const double* X, const int* onoff, const double* value, const double* functfac,
+      double* element_force_vector, double* gp_coord)
+  {
+    const int numnod = num_nodes(ct), ngp = num_gp(ct);
+    double xi[27][3], w[27];
+    gauss_rule(ct, xi, w);
+    for (int gp = 0; gp < ngp; ++gp)
+    {
+      double N[27], dN[81];
+      shape_function(ct, xi[gp], N);
+      shape_function_deriv1(ct, xi[gp], dN);
+      // jacobian_mapping: J(d, i) = sum_a dN(d, a) X(a, i); integration_factor = w det J
+      double J[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+      for (int d = 0; d < 3; ++d)
+        for (int i = 0; i < 3; ++i)
+          for (int a = 0; a < numnod; ++a) J[d][i] += dN[3 * a + d] * X[3 * a + i];
+      const double det = J[0][0] * (J[1][1] * J[2][2] - J[1][2] * J[2][1]) - J[0][1] * (J[1][0] * J[2][2] - J[1][2] * J[2][0]) +
+                         J[0][2] * (J[1][0] * J[2][1] - J[1][1] * J[2][0]);
+      const double integration_factor = w[gp] * det;
+      if (gp_coord)
+        for (int i = 0; i < 3; ++i)
+        {
+          double c = 0.0;
+          for (int a = 0; a < numnod; ++a) c += X[3 * a + i] * N[a];
+          gp_coord[3 * gp + i] = c;
+        }
+      if (!element_force_vector) continue;
+      for (int i = 0; i < 3; ++i)
+        if (onoff[i])
+        {
+          const double function_scale_factor = functfac ? functfac[3 * gp + i] : 1.0;
+          const double value_times_integration_factor = value[i] * function_scale_factor * integration_factor;
+          for (int nodeid = 0; nodeid < numnod; ++nodeid) element_force_vector[nodeid * 3 + i] += N[nodeid] * value_times_integration_factor;
+        }
+    }
+  }
+}  // namespace fc_oracle

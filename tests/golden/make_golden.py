@@ -27,6 +27,7 @@ CASES = [
     "solid_ele_tet10_Standard_dynamic.dat",
     "sohex8fbar_cooks_nl_new_struc.dat",  # 64 hex8 TECH fbar, CoupNeoHooke NUE 0.4999, statics, 20 load steps
     "solid_ele_hex8_Standard_eas_none_volume_neumann.dat",  # surface + VOLUME Neumann loads with functions of space and time
+    "solid_ele_hex8_Standard_fbar.dat",  # TECH fbar, MAT_ElastHyper with TWO summands: CoupNeoHooke + CoupAnisoExpo (FIBER1 on the element)
 ]
 
 
@@ -146,9 +147,12 @@ def main():
         path = os.path.join(INP, name)
         d = from_yaml(path) if name.endswith(".yaml") else from_dat(path)
         d["source"] = "tests/input_files/" + name
-        # keep only what the in-scope path can replay: ElastHyper + one CoupNeoHooke summand
+        # keep only what the in-scope path can replay: ElastHyper with CoupNeoHooke / CoupSVK / CoupAnisoExpo summands
         m1 = d["materials"][1]
-        assert m1[0] == "MAT_ElastHyper" and m1[m1.index("NUMMAT") + 1] == "1", name
+        assert m1[0] == "MAT_ElastHyper", name
+        nm = int(m1[m1.index("NUMMAT") + 1])
+        for mid in m1[m1.index("MATIDS") + 1:m1.index("MATIDS") + 1 + nm]:
+            assert d["materials"][int(mid)][0] in ("ELAST_CoupNeoHooke", "ELAST_CoupSVK", "ELAST_CoupAnisoExpo"), name
         out = os.path.join(OUT, re.sub(r"\.(dat|4C\.yaml)$", "", name) + ".json")
         with open(out, "w") as f:
             json.dump(d, f, indent=0, sort_keys=True)

@@ -112,6 +112,17 @@ def element_evaluate(ct, form, kind, young, nue, X, u, want_K=True, want_M=False
     return err, fe, Ke, Me
 
 
+def element_evaluate_elasthyper(ct, form, summands, fiber, X, u, stress_type=1):
+    """one element of MAT_ElastHyper with a summand list: err, fe, Ke [r, c], gp_stress (ngp, 6)"""
+    nd = 3 * NEN[ct]
+    kinds, par = _i([k for k, _ in summands]), _d([q for _, q in summands])
+    fe, Ke, gp = np.zeros(nd), np.zeros(nd * nd), np.zeros((NGP[ct], 6))
+    fib = _d(fiber) if fiber is not None else None
+    err = lib.oracle_element_evaluate_elasthyper(C.c_int(ct), C.c_int(form), C.c_int(len(summands)), _p(kinds), _p(par), _p(fib),
+                                                 _p(_d(X).reshape(-1)), _p(_d(u).reshape(-1)), _p(fe), _p(Ke), _p(gp), C.c_int(stress_type))
+    return err, fe, Ke.reshape(nd, nd).T.copy(), gp
+
+
 def element_gp_stress(ct, form, kind, young, nue, X, u, stress_type=1):
     """Gauss-point stresses (ngp, 6) of one element; stress_type 0 = 2nd Piola-Kirchhoff, 1 = Cauchy"""
     X, u = _d(X), _d(u)
@@ -119,6 +130,32 @@ def element_gp_stress(ct, form, kind, young, nue, X, u, stress_type=1):
     err = lib.oracle_element_gp_stress(C.c_int(ct), C.c_int(form), C.c_int(kind), C.c_double(young), C.c_double(nue), _p(X), _p(u),
                                        C.c_int(stress_type), _p(out))
     return err, out
+
+
+QUAD4, QUAD9, TRI6 = 0, 1, 2
+FACE_NEN = {QUAD4: 4, QUAD9: 9, TRI6: 6}
+
+
+def surface_neumann(ft, x, onoff, val, functfac=None, want_coords=False):
+    """x: (n, nfn, 3) reference coordinates of the face nodes -> fe (n, nfn, 3) [, gp_coord (n, ngp, 3)]"""
+    x = _d(x)
+    n, nn = x.shape[0], FACE_NEN[ft]
+    fe = np.zeros((n, nn, 3))
+    gc = np.zeros((n, nn, 3)) if want_coords else None
+    ff = _d(functfac) if functfac is not None else None
+    lib.oracle_surface_neumann(C.c_int(ft), C.c_int(n), _p(x), _p(_i(onoff[:3])), _p(_d(val[:3])), _p(ff), _p(fe), _p(gc))
+    return (fe, gc) if want_coords else fe
+
+
+def volume_neumann(ct, X, onoff, val, functfac=None, want_coords=False):
+    """X: (n, nen, 3) -> fe (n, nen, 3) [, gp_coord (n, ngp, 3)]"""
+    X = _d(X)
+    n = X.shape[0]
+    fe = np.zeros((n, NEN[ct], 3))
+    gc = np.zeros((n, NGP[ct], 3)) if want_coords else None
+    ff = _d(functfac) if functfac is not None else None
+    lib.oracle_volume_neumann(C.c_int(ct), C.c_int(n), _p(X), _p(_i(onoff[:3])), _p(_d(val[:3])), _p(ff), _p(fe), _p(gc))
+    return (fe, gc) if want_coords else fe
 
 
 def gauss_rule(ct):
@@ -200,6 +237,13 @@ class Job:
 
     def set_problem(self, form, kind, young, nue):
         lib.oracle_job_set_problem(self.h, C.c_int(form), C.c_int(kind), C.c_double(young), C.c_double(nue))
+
+    def set_elasthyper(self, form, summands, fibers=None):
+        """summands: [(kind, [4 parameters])]; fibers: (n_ele, 3) FIBER1 in the order of self.ele_gid or None"""
+        kinds = _i([k for k, _ in summands])
+        par = _d([q for _, q in summands])
+        lib.oracle_job_set_elasthyper(self.h, C.c_int(form), C.c_int(len(summands)), _p(kinds), _p(par),
+                                      _p(_d(fibers)) if fibers is not None else None)
 
     def rank(self, r):
         sizes = np.zeros(8, np.int64)

@@ -42,11 +42,35 @@ class Problem:
         self.conn = np.array([[self.index[n] for n in e["nodes"]] for e in fx["elements"]], np.int32)
         self.ele_gid = np.array([e["id"] - 1 for e in fx["elements"]], np.int32)
         m1 = fx["materials"]["1"]
+        self.summands, self.fibers = None, None
         if m1[0] == "MAT_Struct_StVenantKirchhoff":
             m10, self.mat = m1, 0  # FC_MAT_STVENANTKIRCHHOFF
         else:
-            m10, self.mat = fx["materials"][m1[m1.index("MATIDS") + 1]], 1  # FC_MAT_ELASTHYPER_COUPNEOHOOKE
-            assert m1[0] == "MAT_ElastHyper" and m10[0] == "ELAST_CoupNeoHooke"
+            assert m1[0] == "MAT_ElastHyper"
+            nm = int(m1[m1.index("NUMMAT") + 1])
+            mids = m1[m1.index("MATIDS") + 1:m1.index("MATIDS") + 1 + nm]
+            m10 = fx["materials"][mids[0]]
+            if nm == 1 and m10[0] == "ELAST_CoupNeoHooke":
+                self.mat = 1  # FC_MAT_ELASTHYPER_COUPNEOHOOKE
+            else:
+                # summand list (kind, 4 parameters): 0 CoupNeoHooke / 1 CoupSVK (YOUNG, NUE), 2 CoupAnisoExpo (K1, K2, K1COMP, K2COMP)
+                self.mat, self.summands = 2, []
+                for mid in mids:
+                    m = fx["materials"][mid]
+                    g = lambda k: float(m[m.index(k) + 1])
+                    if m[0] in ("ELAST_CoupNeoHooke", "ELAST_CoupSVK"):
+                        self.summands.append((0 if m[0] == "ELAST_CoupNeoHooke" else 1, [g("YOUNG"), g("NUE"), 0.0, 0.0]))
+                    else:
+                        assert m[0] == "ELAST_CoupAnisoExpo" and int(g("INIT")) == 1 and int(g("FIBER_ID")) == 1
+                        self.summands.append((2, [g("K1"), g("K2"), g("K1COMP"), g("K2COMP")]))
+                m10 = next(fx["materials"][mid] for mid in mids if "YOUNG" in fx["materials"][mid])
+                if any(k == 2 for k, _ in self.summands):
+                    fib = []
+                    for e in fx["elements"]:
+                        t = e["opts"].split()
+                        i = t.index("FIBER1")
+                        fib.append([float(x) for x in t[i + 1:i + 4]])
+                    self.fibers = np.array(fib)
         techs = {"TECH fbar" in e["opts"] for e in fx["elements"]}
         assert len(techs) == 1
         self.form = 1 if techs.pop() else 0  # FC_FORM_FBAR / FC_FORM_DISPLACEMENT
@@ -74,6 +98,20 @@ class Problem:
                     if all(int(en[a]) in sset for a in loc):
                         self.faces.append((c, en[loc], rs))
         assert self.faces or not fx["neumann"]
+        # the same loads as lists for a Neumann backend (oracle / CUDA library): faces by their nodes in the reference's
+        # quad4 / quad9 / tri6 node order, volume conditions by their elements
+        self.neumann = None  # backend with surface(), volume(), *_coords(); None = the numpy restatement below (surfaces only)
+        self.face_lists, self.vol_lists = [], []
+        for c in fx["neumann"]:
+            fl = [self._ordered_face(nodes, rs) for cc, nodes, rs in self.faces if cc is c]
+            self.face_lists.append((c, {4: 0, 9: 1, 6: 2}[len(fl[0])], np.array(fl, np.int32)))
+        for c in fx.get("vol_neumann", []):
+            assert c["type"] == "Live" and not any(c["onoff"][3:])
+            vset = {self.index[n] for n in fx["dvol"][str(c["E"])]}
+            els = [e for e, en in enumerate(self.conn) if all(int(a) in vset for a in en)]
+            assert els
+            self.vol_lists.append((c, np.array(els, np.int32)))
+        self._gp_cache = {}
 
     # faces of the parent cell as (local node ids, in-face parameter coordinates of those nodes)
     def _element_faces(self):
@@ -99,6 +137,20 @@ class Problem:
                         lam.append(l)
                 assert len(loc) == 6
                 out.append((loc, np.array(lam)))
+        return out
+
+    def _ordered_face(self, nodes, rs):
+        """face nodes in the node order of the reference's surface cell (4C_fem_general_utils_fem_shapefunctions.hpp:2003-2111)"""
+        rs = np.asarray(rs, float)
+        if self.ct in (0, 1):
+            want = [(-1, -1), (1, -1), (1, 1), (-1, 1), (0, -1), (1, 0), (0, 1), (-1, 0), (0, 0)][:len(nodes)]
+        else:
+            want = [(1, 0, 0), (0, 1, 0), (0, 0, 1), (.5, .5, 0), (0, .5, .5), (.5, 0, .5)]
+        out = []
+        for w in want:
+            k = [i for i in range(len(nodes)) if np.allclose(rs[i], w, atol=1e-12)]
+            assert len(k) == 1
+            out.append(int(nodes[k[0]]))
         return out
 
     def _surface_shape(self, rs_nodes, pt):
@@ -151,7 +203,30 @@ class Problem:
         expr = self.fx["functs"][str(fid)]
         return float(eval(expr, {"__builtins__": {}}, {"x": x[0], "y": x[1], "z": x[2], "t": t}))
 
+    def _factors(self, key, cond, coords, t):
+        """FUNCT of the condition at the Gauss points: (n, ngp, 3), None when every factor is 1"""
+        if not any(cond["onoff"][d] and cond["funct"][d] > 0 for d in range(3)):
+            return None
+        fac = np.ones(coords.shape)
+        for d in range(3):
+            if cond["onoff"][d] and cond["funct"][d] > 0:
+                fac[..., d] = [[self.funct(cond["funct"][d], x, t) for x in row] for row in coords]
+        return fac
+
     def f_ext(self, t):
+        if self.neumann is not None:
+            # Neumann backend (oracle restatement or the CUDA library): the driver only evaluates the FUNCT expressions at the
+            # Gauss-point coordinates the backend hands out
+            nb = self.neumann
+            f = np.zeros(self.n_dof)
+            for i, (c, ft, fn) in enumerate(self.face_lists):
+                xg = self._gp_cache.setdefault(("s", i), nb.surface_coords(ft, fn))
+                nb.surface(ft, fn, c["onoff"], c["val"], self._factors(("s", i), c, xg, t), f)
+            for i, (c, els) in enumerate(self.vol_lists):
+                xg = self._gp_cache.setdefault(("v", i), nb.volume_coords(els))
+                nb.volume(els, c["onoff"], c["val"], self._factors(("v", i), c, xg, t), f)
+            return f
+        assert not self.vol_lists, "the numpy restatement covers surface loads only"
         f = np.zeros((len(self.ids), 3))
         for c, nodes, rs in self.faces:
             P = self.X[nodes]
@@ -177,6 +252,44 @@ class Problem:
                 err = max(err, abs(v - r["value"]) / r["tolerance"])
                 n += 1
         return err, n
+
+
+class OracleNeumann:
+    """Neumann backend on the CPU oracle (oracle/fc_oracle_neumann.hpp)"""
+
+    def __init__(self, oracle, p):
+        self.o, self.p = oracle, p
+
+    def surface_coords(self, ft, fn):
+        return self.o.surface_neumann(ft, self.p.X[fn], [0, 0, 0], [0.0, 0.0, 0.0], want_coords=True)[1]
+
+    def volume_coords(self, els):
+        return self.o.volume_neumann(self.p.ct, self.p.X[self.p.conn[els]], [0, 0, 0], [0.0, 0.0, 0.0], want_coords=True)[1]
+
+    def surface(self, ft, fn, onoff, val, fac, f):
+        np.add.at(f.reshape(-1, 3), fn, self.o.surface_neumann(ft, self.p.X[fn], onoff, val, fac))
+
+    def volume(self, els, onoff, val, fac, f):
+        np.add.at(f.reshape(-1, 3), self.p.conn[els], self.o.volume_neumann(self.p.ct, self.p.X[self.p.conn[els]], onoff, val, fac))
+
+
+class CudaNeumann:
+    """Neumann backend on the CUDA library (fc_solid_neumann_*): f_ext is assembled on the device"""
+
+    def __init__(self, solid):
+        self.s = solid
+
+    def surface_coords(self, ft, fn):
+        return self.s.neumann_surface_gp_coords(ft, fn)
+
+    def volume_coords(self, els):
+        return self.s.neumann_volume_gp_coords(els)
+
+    def surface(self, ft, fn, onoff, val, fac, f):
+        self.s.neumann_surface(ft, fn, onoff, val, f, gp_factor=fac)
+
+    def volume(self, els, onoff, val, fac, f):
+        self.s.neumann_volume(els, onoff, val, f, gp_factor=fac)
 
 
 def _solve(A, rhs, fixed):

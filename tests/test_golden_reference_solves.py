@@ -15,12 +15,17 @@ CASES = [
     "solid_ele_tet10_Standard_dynamic",
     "sohex8fbar_cooks_nl_new_struc",  # F-bar + Neo-Hooke NUE 0.4999 (BASELINE config C4's element), TOLERANCE 1e-8
     "solid_runtime_ghosting_output",  # 640 hex8 SVK (BASELINE config C1's mesh), reference = its runtime VTK output, 1e-8
+    "solid_ele_hex8_Standard_eas_none_volume_neumann",  # surface + volume Neumann loads with FUNCT (x+1)(y+2)(z+3) and t
+    "solid_ele_hex8_Standard_fbar",  # the reference's F-bar ELEMENT golden: MAT_ElastHyper = CoupNeoHooke + CoupAnisoExpo fibres
 ]
 
 
 def oracle_backend(oracle, p):
     job = oracle.Job.from_mesh(p.ct, p.node_gid, p.X, p.ele_gid, p.node_gid[p.conn])
-    job.set_problem(p.form, p.mat, p.young, p.nue)
+    if p.summands is None:
+        job.set_problem(p.form, p.mat, p.young, p.nue)
+    else:
+        job.set_elasthyper(p.form, p.summands, p.fibers)
     o = job.rank(0)
     assert np.array_equal(job.node_gid, p.node_gid)
 
@@ -45,6 +50,7 @@ def oracle_backend(oracle, p):
 @pytest.mark.parametrize("case", CASES)
 def test_reference_result_description_oracle(oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
+    p.neumann = sd.OracleNeumann(oracle, p)
     assemble, mass = oracle_backend(oracle, p)
     d, hist = sd.run(p, assemble, mass)
     err, n = p.result_error(d)  # in units of the reference's TOLERANCE of each value (1e-12; Cook: 1e-8)
@@ -55,7 +61,10 @@ def test_reference_result_description_oracle(oracle, case):
 def cuda_backend(fc, p):
     s = fc.Solid(0)
     s.set_mesh(p.ct, p.form, p.X, p.node_gid, np.zeros(len(p.node_gid), np.int32), p.conn, p.ele_gid)
-    s.set_material(p.mat, p.young, p.nue)
+    if p.summands is None:
+        s.set_material(p.mat, p.young, p.nue)
+    else:
+        s.set_material_elasthyper(p.summands, p.fibers)
     n_row, n_col, nnz = s.build_graph()
     assert n_row == p.n_dof
     rowptr, colind = s.get_graph()
@@ -77,9 +86,17 @@ def cuda_backend(fc, p):
 def test_reference_result_description_cuda(fc, oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     s, assemble, mass = cuda_backend(fc, p)
+    p.neumann = sd.CudaNeumann(s)  # f_ext from fc_solid_neumann_surface / _volume
     d, hist = sd.run(p, assemble, mass)
     err, n = p.result_error(d)
     assert err <= 1.0, (case, err, hist)
+    # the external force of the library against the oracle's, at the end time
+    t_end = p.dt * p.numstep
+    fe_cuda = p.f_ext(t_end)
+    p.neumann = sd.OracleNeumann(oracle, p)
+    p._gp_cache = {}
+    fe_ref = p.f_ext(t_end)
+    assert np.max(np.abs(fe_cuda - fe_ref)) <= 1e-13 * np.max(np.abs(fe_ref))
     # same Newton history as the oracle-driven solve (north_star: iteration counts and residual norms match)
     a2, m2 = oracle_backend(oracle, p)
     d2, hist2 = sd.run(p, a2, m2)
@@ -100,7 +117,27 @@ def test_reference_result_description_cuda(fc, oracle, case):
     s.close()
 
 
-STRESS_CASES = ["solid_ele_hex8_Standard_eas_none_stressout", "solid_ele_hex27_Standard_stressout", "solid_ele_tet10_Standard_stressout"]
+@pytest.mark.parametrize("case", [c for c in CASES if c not in ("solid_ele_hex8_Standard_eas_none_volume_neumann", "solid_ele_hex8_Standard_fbar")])
+def test_neumann_oracle_matches_numpy_restatement(oracle, case):
+    """two independent restatements of the surface loads (oracle C++, structure_driver numpy) agree"""
+    p = sd.Problem(sd.load(case), oracle.node_param_coords)
+    t = p.dt * p.numstep
+    f_np = p.f_ext(t)
+    p.neumann = sd.OracleNeumann(oracle, p)
+    f_or = p.f_ext(t)
+    assert np.max(np.abs(f_np)) > 0 or not p.face_lists
+    assert np.max(np.abs(f_np - f_or)) <= 1e-14 * max(np.max(np.abs(f_np)), 1e-300)
+
+
+STRESS_CASES = ["solid_ele_hex8_Standard_eas_none_stressout", "solid_ele_hex27_Standard_stressout", "solid_ele_tet10_Standard_stressout",
+                "solid_ele_hex8_Standard_fbar"]
+
+
+def oracle_gp_stress(oracle, p, U, e, st):
+    en = p.conn[e]
+    if p.summands is None:
+        return oracle.element_gp_stress(p.ct, p.form, p.mat, p.young, p.nue, p.X[en], U[en], st)[1]
+    return oracle.element_evaluate_elasthyper(p.ct, p.form, p.summands, None if p.fibers is None else p.fibers[e], p.X[en], U[en], st)[3]
 
 
 @pytest.mark.parametrize("case", STRESS_CASES)
@@ -108,11 +145,12 @@ def test_reference_nodal_stresses_oracle(oracle, case):
     """stress_xx ... at nodes (STRUCT_STRESS Cauchy, TOLERANCE 1e-12): Gauss-point Cauchy stresses extrapolated to the
     nodes and averaged like the reference's post-processing (24 / 54 / 78 values)."""
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
+    p.neumann = sd.OracleNeumann(oracle, p)
     assemble, mass = oracle_backend(oracle, p)
     d, _ = sd.run(p, assemble, mass)
     E = sd.extrapolation_matrix(p.ct, oracle.gauss_rule(p.ct)[0], oracle.shape, oracle.node_param_coords(p.ct))
     U = d.reshape(-1, 3)
-    nodal = sd.nodal_stresses(p, lambda e: oracle.element_gp_stress(p.ct, p.form, p.mat, p.young, p.nue, p.X[p.conn[e]], U[p.conn[e]], 1)[1], E)
+    nodal = sd.nodal_stresses(p, lambda e: oracle_gp_stress(oracle, p, U, e, 1), E)
     err, n = sd.stress_result_error(p, nodal)
     assert n >= 24 and err <= 1.0, (case, err, n)
 
@@ -124,6 +162,7 @@ def test_reference_nodal_stresses_cuda(fc, oracle, case):
     Gauss-point stresses also compared with the oracle's, Cauchy and 2nd Piola-Kirchhoff."""
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     s, assemble, mass = cuda_backend(fc, p)
+    p.neumann = sd.CudaNeumann(s)
     d, _ = sd.run(p, assemble, mass)
     gp, nodal = s.evaluate_stress(d, fc.FC_STRESS_CAUCHY)
     err, n = sd.stress_result_error(p, nodal)
@@ -132,6 +171,6 @@ def test_reference_nodal_stresses_cuda(fc, oracle, case):
     for st in (fc.FC_STRESS_2PK, fc.FC_STRESS_CAUCHY):
         gp, _ = s.evaluate_stress(d, st, want_nodal=False)
         for e in range(len(p.conn)):
-            _, ref = oracle.element_gp_stress(p.ct, p.form, p.mat, p.young, p.nue, p.X[p.conn[e]], U[p.conn[e]], st)
+            ref = oracle_gp_stress(oracle, p, U, e, st)
             assert np.max(np.abs(gp[e] - ref)) <= 1e-12 * np.max(np.abs(ref))
     s.close()

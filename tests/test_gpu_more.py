@@ -293,3 +293,60 @@ def test_interior_then_boundary_equals_full_evaluation(fc, ct, form, mat, n, nra
             s.evaluate(fc.FC_ACTION_NLNSTIFF, u_d, f1, K1, flags=fc.FC_EVAL_INTERIOR | fc.FC_EVAL_FORCE_GENERIC)
         assert ei.value.code == fc.FC_ERR_UNSUPPORTED
         s.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ct", [0, 1, 2])
+def test_neumann_loads_match_oracle(fc, oracle, ct):
+    """fc_solid_neumann_volume / _surface (TYPE Live) against the oracle's restatement of evaluate_neumann
+    (4C_solid_3D_ele_neumann_evaluator.cpp:43-115) and SolidSurface neum_live (4C_solid_3D_ele_surface_evaluate.cpp:225-330),
+    with per-Gauss-point function factors, host and device outputs, += semantics"""
+    import torch
+    import structure_driver as sd
+    if ct == 2:
+        p = sd.Problem(sd.load("solid_ele_tet10_Standard_dynamic"), oracle.node_param_coords)
+        X, gid, conn, egid = p.X, p.node_gid, p.conn, p.ele_gid
+        ft, faces = p.face_lists[0][1], p.face_lists[0][2]
+    else:
+        g = fc.Grid(ct, (3, 2, 2))
+        X, gid, conn, egid = g.X * np.array([1.0, 1.3, 0.7]), g.node_gid, g.conn, g.ele_gid
+        # faces on the x+ side in the reference's quad4 / quad9 node order
+        xi = oracle.node_param_coords(ct)
+        loc = [a for a in range(len(xi)) if xi[a, 0] == 1.0]
+        want = [(-1, -1), (1, -1), (1, 1), (-1, 1), (0, -1), (1, 0), (0, 1), (-1, 0), (0, 0)][:len(loc)]
+        order = [next(a for a in loc if (xi[a, 1], xi[a, 2]) == w) for w in want]
+        faces = np.array([en[order] for en in conn if np.all(X[en[order], 0] > 1.0 - 1e-12)], np.int32)
+        ft = fc.FC_FACE_QUAD4 if ct == 0 else fc.FC_FACE_QUAD9
+    s = fc.Solid(0)
+    s.set_mesh(ct, DISP, X, gid, np.zeros(len(gid), np.int32), conn, egid)
+    s.set_material(NH, 10.0, 0.25)
+    rng = np.random.default_rng(2)
+    n_dof = 3 * len(gid)
+    # volume
+    els = np.arange(len(conn), dtype=np.int32)[::2]
+    xg = s.neumann_volume_gp_coords(els)
+    fe_ref, xg_ref = oracle.volume_neumann(ct, X[conn[els]], [1, 0, 1], [2.0, 9.0, -0.5], want_coords=True)
+    assert np.max(np.abs(xg - xg_ref)) <= 1e-14
+    fac = 1.0 + rng.random(xg.shape)
+    fe_ref = oracle.volume_neumann(ct, X[conn[els]], [1, 0, 1], [2.0, 9.0, -0.5], fac)
+    f_ref = np.full(n_dof, 0.125)
+    np.add.at(f_ref.reshape(-1, 3), conn[els], fe_ref)
+    f = np.full(n_dof, 0.125)
+    s.neumann_volume(els, [1, 0, 1], [2.0, 9.0, -0.5], f, gp_factor=fac)
+    assert np.max(np.abs(f - f_ref)) <= 1e-14 * np.max(np.abs(f_ref))
+    f_dev = torch.full((n_dof,), 0.125, dtype=torch.float64, device="cuda")
+    s.neumann_volume(els, [1, 0, 1], [2.0, 9.0, -0.5], f_dev, gp_factor=torch.from_numpy(fac).cuda())
+    assert np.max(np.abs(f_dev.cpu().numpy() - f_ref)) <= 1e-14 * np.max(np.abs(f_ref))
+    # surface
+    assert len(faces) > 0
+    xs = s.neumann_surface_gp_coords(ft, faces)
+    fs_ref, xs_ref = oracle.surface_neumann(ft, X[faces], [1, 1, 1], [1.0, -2.0, 0.3], want_coords=True)
+    assert np.max(np.abs(xs - xs_ref)) <= 1e-14
+    fac = 1.0 + rng.random(xs.shape)
+    fs_ref = oracle.surface_neumann(ft, X[faces], [1, 1, 1], [1.0, -2.0, 0.3], fac)
+    f_ref = np.zeros(n_dof)
+    np.add.at(f_ref.reshape(-1, 3), faces, fs_ref)
+    f = np.zeros(n_dof)
+    s.neumann_surface(ft, faces, [1, 1, 1], [1.0, -2.0, 0.3], f, gp_factor=fac)
+    assert np.max(np.abs(f - f_ref)) <= 1e-14 * np.max(np.abs(f_ref))
+    s.close()

@@ -133,6 +133,42 @@ def test_element_level_parity(fc, oracle, ct, form, mat, nue, n):
     s.close()
 
 
+@pytest.mark.parametrize("ct,form,n,summands,with_fibers", [
+    (HEX8, DISP, (4, 3, 3), [(1, [10.0, 0.3, 0, 0])], False),                                  # ELAST_CoupSVK alone
+    (HEX8, DISP, (4, 3, 3), [(0, [10.0, 0.25, 0, 0]), (1, [4.0, 0.1, 0, 0])], False),           # CoupNeoHooke + CoupSVK
+    (HEX8, FBAR, (3, 3, 3), [(0, [10.0, 0.25, 0, 0]), (2, [100.0, 1.0, 0.0, 1.0])], True),      # the material of solid_ele_hex8_Standard_fbar.dat
+    (HEX8, DISP, (3, 3, 2), [(0, [10.0, 0.3, 0, 0]), (2, [50.0, 2.0, 5.0, 0.5])], True),        # fibres active in compression too
+    (HEX27, DISP, (2, 2, 2), [(1, [10.0, 0.3, 0, 0]), (2, [20.0, 1.0, 0.0, 1.0])], True),
+    (TET10, DISP, (2, 2, 2), [(0, [10.0, 0.25, 0, 0]), (2, [20.0, 1.0, 0.0, 1.0])], True),
+])
+def test_elasthyper_summand_list_parity(fc, oracle, ct, form, n, summands, with_fibers):
+    """MAT_ElastHyper with a summand list (CoupNeoHooke, CoupSVK, CoupAnisoExpo with element fibres): fe, Ke of every element
+    and the Gauss-point Cauchy stresses against the oracle's restatement of the summand loop."""
+    job = make_case(oracle, ct, n)
+    s, o, col = setup_rank(fc, job, 0, ct, form, NH, 10.0, 0.25)
+    rng = np.random.default_rng(11)
+    ne = len(job.conn)
+    fibers = rng.standard_normal((ne, 3)) * 3.0 if with_fibers else None  # not normalised: the library normalises like the reference
+    s.set_material_elasthyper(summands, fibers)
+    h = 1.0 / max(n)
+    u = oracle.smooth_displacement(job.X, h, amp=0.03)
+    nidx = {int(g): i for i, g in enumerate(job.node_gid)}
+    conn = np.vectorize(nidx.get)(job.conn)
+    ucol = np.ascontiguousarray(u[col].reshape(-1))
+    fe, Ke = s.evaluate_elements(ucol, want_K=True)
+    gp, _ = s.evaluate_stress(ucol, fc.FC_STRESS_CAUCHY, want_nodal=False)
+    eidx = {int(g): i for i, g in enumerate(job.ele_gid)}
+    order = np.array([eidx[int(g)] for g in o["col_eles"]])
+    for e in range(ne):
+        j = order[e]
+        err, fr, kr, gr = oracle.element_evaluate_elasthyper(ct, form, summands, None if fibers is None else fibers[e], job.X[conn[j]], u[conn[j]], 1)
+        assert err == 0
+        assert np.max(np.abs(Ke[e] - kr)) <= TOL * np.max(np.abs(kr)), (e, rel(Ke[e], kr))
+        assert np.max(np.abs(fe[e] - fr)) <= TOL * max(np.max(np.abs(fr)), np.max(np.abs(kr)) * h), e
+        assert np.max(np.abs(gp[e] - gr)) <= TOL * np.max(np.abs(gr)), e
+    s.close()
+
+
 @pytest.mark.parametrize("ct,form,mat,nue,n,nranks", [
     (HEX8, DISP, NH, 0.25, (10, 10, 10), 1),
     (HEX8, DISP, NH, 0.25, (7, 6, 5), 4),

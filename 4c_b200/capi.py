@@ -25,7 +25,7 @@ FACE_NEN = {FC_FACE_QUAD4: 4, FC_FACE_QUAD9: 9, FC_FACE_TRI6: 6}
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
 FC_ERR_SOLVER, FC_ERR_SOLVER_NOT_CONVERGED = -7, -8
-FC_SOLVER_CG, FC_SOLVER_BICGSTAB = 0, 1
+FC_SOLVER_CG, FC_SOLVER_BICGSTAB, FC_SOLVER_CG_MG = 0, 1, 2
 NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10}
 
 EXPORTS = [
@@ -38,7 +38,7 @@ EXPORTS = [
     "fc_solid_last_kernel_ms", "fc_solid_kernel_ms_history", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
     "fc_grid_halo_counts", "fc_grid_halo_send_nodes", "fc_probe_fp64_fma", "fc_probe_fp64_mma",
-    "fc_solid_set_comm", "fc_solid_set_dirichlet_toggle", "fc_solid_apply_dirichlet", "fc_solid_apply_dirichlet_to_system", "fc_solid_spmv", "fc_solid_linear_solve",
+    "fc_solid_set_comm", "fc_solid_set_dirichlet_toggle", "fc_solid_apply_dirichlet", "fc_solid_apply_dirichlet_to_system", "fc_solid_spmv", "fc_solid_linear_solve", "fc_solid_mg_setup", "fc_solid_mg_update", "fc_solid_mg_set_sweeps", "fc_solid_mg_level_info",
     "fc_l2_sweep_order", "fc_brick_plan_create", "fc_brick_plan_sizes", "fc_brick_plan_get", "fc_brick_plan_destroy",
 ]
 
@@ -300,6 +300,24 @@ class Solid:
 
     def spmv(self, K_values, x_col, y_row):
         self._chk(lib().fc_solid_spmv(self.h, _ptr(K_values), _ptr(x_col), _ptr(y_row)))
+
+    def mg_setup(self, max_levels=8):
+        """geometric multigrid hierarchy for FC_SOLVER_CG_MG; returns the number of levels"""
+        n = C.c_int(0)
+        self._chk(lib().fc_solid_mg_setup(self.h, C.c_int(max_levels), C.byref(n)))
+        return n.value
+
+    def mg_set_sweeps(self, nu):
+        self._chk(lib().fc_solid_mg_set_sweeps(self.h, C.c_int(nu)))
+
+    def mg_level_info(self, level):
+        """(nodes, Jacobi damping) of one multigrid level, 0 = finest"""
+        n, w = C.c_int(0), C.c_double(0.0)
+        self._chk(lib().fc_solid_mg_level_info(self.h, C.c_int(level), C.byref(n), C.byref(w)))
+        return n.value, w.value
+
+    def mg_update(self, u_col_dev):
+        self._chk(lib().fc_solid_mg_update(self.h, _ptr(u_col_dev)))
 
     def linear_solve(self, K_values, b, x, method=FC_SOLVER_CG, rel_tol=1e-10, max_iter=10000, check=True):
         """K x = b; x holds the initial guess.  Returns (iterations, relative residual)."""

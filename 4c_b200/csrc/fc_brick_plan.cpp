@@ -5,10 +5,19 @@
 #include <cmath>
 #include <numeric>
 
+namespace fc_host
+{
+  bool lattice_axis(int n_nodes, const double* X, int d, int n_ele, const int* conn, std::vector<int>& idx, int& n_levels);
+}
+
 namespace
 {
   using fc_host::BrickPlanHost;
+  using fc_host::lattice_axis;
+}  // namespace
 
+namespace fc_host
+{
   // lattice index of every node along axis d: uniform spacing first (O(n)), sorted distinct levels otherwise
   bool lattice_axis(int n_nodes, const double* X, int d, int n_ele, const int* conn, std::vector<int>& idx, int& n_levels)
   {
@@ -71,10 +80,7 @@ namespace
     n_levels = (int)lev.size();
     return true;
   }
-}  // namespace
 
-namespace fc_host
-{
   bool build_brick_plan_host(int n_col_nodes, const double* X, int n_ele, const int* conn, int n_row_nodes, int max_row_nodes,
       int chunk, BrickPlanHost& plan)
   {

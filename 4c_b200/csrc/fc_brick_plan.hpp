@@ -37,6 +37,11 @@ namespace fc_host
     long long n_element_instances = 0;     // non-empty entries of ele_tab (>= n_ele: elements on unit faces repeat)
   };
 
+  // Lattice index of every node along coordinate axis d (uniform spacing, or the sorted distinct levels of a non-uniform
+  // rectilinear grid); false when the coordinates do not sit on such a grid.  conn [n_ele][8].  Also used by the
+  // geometric multigrid hierarchy (fc_capi_mg.cu).
+  bool lattice_axis(int n_nodes, const double* X, int d, int n_ele, const int* conn, std::vector<int>& idx, int& n_levels);
+
   // X [n_col_nodes][3]; conn [n_ele][8] column-node ids; nodes [0, n_row_nodes) own rows; max_row_nodes = largest
   // number of coupled nodes of an owned node (the kernel keeps 27 blocks per row).  chunk = node planes per unit
   // along the sweep axis (0 = choose: at least ~8 units per SM-wave of 148).  Returns false (plan left empty) when

@@ -15,6 +15,7 @@
 #include "fc_sweep_order.hpp"
 
 void fc_free_brick_plan(fc_ctx* ctx);  // fc_capi_graph.cu
+void fc_mg_free(fc_ctx* ctx);          // fc_capi_mg.cu
 
 extern "C"
 {
@@ -68,6 +69,7 @@ extern "C"
     dev_free(ctx->d_node_rowlen);
     dev_free(ctx->d_slots);
     fc_free_brick_plan(ctx);
+    fc_mg_free(ctx);
     dev_free(ctx->d_dbc);
     dev_free(ctx->d_nodeptr);
     dev_free(ctx->d_nodeadj);
@@ -212,7 +214,10 @@ extern "C"
     dev_free(ctx->d_Dinv);
     ctx->Dinv_cap = 0;
     ctx->n_toggle = 0;
+    ctx->h_toggle_rows.clear();
+    ctx->toggle_version++;
     fc_free_brick_plan(ctx);
+    fc_mg_free(ctx);
     ctx->n_col_dof = 3 * n_col_nodes;
     ctx->n_row_dof = 3 * n_row;
     FC_CUDA(dev_upload(ctx->d_X, X, (size_t)3 * n_col_nodes, ctx->stream));

@@ -16,6 +16,7 @@
 #include "fc_kernels_setup.cuh"
 
 void fc_free_brick_plan(fc_ctx* ctx);
+void fc_mg_free(fc_ctx* ctx);  // fc_capi_mg.cu
 
 namespace
 {
@@ -114,6 +115,7 @@ namespace
     // whatever was derived from the previous graph goes before anything can fail
     ctx->have_graph = false;
     fc_free_brick_plan(ctx);
+    fc_mg_free(ctx);
     dev_free(ctx->d_Dinv);
     ctx->Dinv_cap = 0;
     ctx->nnz = 9 * ctx->h_nodeptr[nrow];
@@ -153,6 +155,8 @@ namespace
     }
     dev_free(ctx->d_toggle_rows);  // refers to rows of the previous graph
     ctx->n_toggle = 0;
+    ctx->h_toggle_rows.clear();
+    ctx->toggle_version++;
     dev_free(ctx->d_slots);
     const size_t nslots = (size_t)ctx->n_ele * ctx->nen * ctx->nen;
     int bad = 0;

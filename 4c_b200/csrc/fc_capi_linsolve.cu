@@ -12,6 +12,7 @@
 #include "fc_kernels_linsolve.cuh"
 
 int fc_allreduce_sum(fc_ctx* ctx, double* buf_dev, int n);  // fc_capi_halo.cu
+int fc_mg_vcycle(fc_ctx* ctx, const double* K, const double* r, double* z);  // fc_capi_mg.cu
 
 namespace
 {
@@ -85,6 +86,8 @@ extern "C"
     FC_CUDA(dev_upload(ctx->d_toggle_rows, row_lids, (size_t)n, ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
     ctx->n_toggle = n;
+    ctx->h_toggle_rows.assign(row_lids, row_lids + n);
+    ctx->toggle_version++;
     return FC_OK;
   }
 
@@ -134,7 +137,9 @@ extern "C"
       int* iters, double* rel_residual)
   {
     if (!ctx || !ctx->have_graph || !K_values || !b || !x) return fail(ctx, FC_ERR_INVALID, "graph, K_values, b and x required");
-    if (method != FC_SOLVER_CG && method != FC_SOLVER_BICGSTAB) return fail(ctx, FC_ERR_UNSUPPORTED, "solver method");
+    if (method != FC_SOLVER_CG && method != FC_SOLVER_BICGSTAB && method != FC_SOLVER_CG_MG) return fail(ctx, FC_ERR_UNSUPPORTED, "solver method");
+    if (method == FC_SOLVER_CG_MG && (ctx->mg.size() < 2 || !ctx->mg_operators_ready || ctx->mg_toggle_version != ctx->toggle_version))
+      return fail(ctx, FC_ERR_INVALID, "FC_SOLVER_CG_MG: fc_solid_mg_setup and fc_solid_mg_update (after the last change of the toggle) must precede the solve");
     const bool multi = ctx->nranks > 1;
     if (!multi && ctx->n_col_dof != ctx->n_row_dof) return fail(ctx, FC_ERR_INVALID, "ghost columns on a single rank");
     if (multi && (!ctx->nccl_comm || (int)ctx->halo_send_count.size() != ctx->nranks))
@@ -143,7 +148,7 @@ extern "C"
     FC_CUDA(cudaSetDevice(ctx->device));
     if (int rc = ensure_dot(ctx)) return rc;
     const int n = ctx->n_row_dof;
-    const size_t nvec = method == FC_SOLVER_CG ? 4 : 8;
+    const size_t nvec = method == FC_SOLVER_BICGSTAB ? 8 : 4;
     const size_t NC = (size_t)ctx->n_col_dof;  // every work vector is column-sized: the ones K multiplies carry ghosts
     FC_CUDA(ensure_cap(ctx->d_solver_ws, ctx->solver_ws_cap, nvec * NC));
     FC_CUDA(ensure_cap(ctx->d_Dinv, ctx->Dinv_cap, 9 * (size_t)ctx->n_row_nodes));
@@ -166,7 +171,39 @@ extern "C"
       FC_CUDA(cudaMemsetAsync(x, 0, sizeof(double) * (size_t)n, ctx->stream));
       return finish(FC_OK);
     }
-    if (method == FC_SOLVER_CG)
+    if (method == FC_SOLVER_CG_MG)
+    {
+      // CG preconditioned by one multigrid V-cycle per iteration (fc_capi_mg.cu); scalars on the host: two small
+      // read-backs per iteration against a V-cycle of a dozen sweeps over the matrix
+      double *r = W, *z = W + NC, *p = W + 2 * NC, *Ap = W + 3 * NC;
+      spmv(ctx, K_values, x, Ap);
+      xpaypbw(ctx, n, b, -1.0, Ap, 0.0, nullptr, r);
+      if (int rc = dots(ctx, n, r, r, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+      relres = std::sqrt(d[0]) / bnorm;
+      double rz = 0.0;
+      while (relres > rel_tol && it < max_iter)
+      {
+        if (int rc = fc_mg_vcycle(ctx, K_values, r, z)) return finish(rc);
+        if (int rc = dots(ctx, n, r, z, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+        const double rz_new = d[0];
+        if (!(rz_new > 0.0) || !std::isfinite(rz_new)) return finish(fail(ctx, FC_ERR_SOLVER, "CG-MG breakdown: r.z <= 0 (preconditioner or matrix not positive definite on the free DOFs)"));
+        if (it == 0)
+          FC_CUDA(cudaMemcpyAsync(p, z, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, ctx->stream));
+        else
+          axpby(ctx, n, 1.0, z, rz_new / rz, p);
+        rz = rz_new;
+        spmv(ctx, K_values, p, Ap);
+        if (int rc = dots(ctx, n, p, Ap, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+        if (!(d[0] > 0.0)) return finish(fail(ctx, FC_ERR_SOLVER, "CG-MG breakdown: p.Ap <= 0 (matrix not positive definite on the free DOFs)"));
+        const double alpha = rz / d[0];
+        axpby(ctx, n, alpha, p, 1.0, x);
+        axpby(ctx, n, -alpha, Ap, 1.0, r);
+        if (int rc = dots(ctx, n, r, r, nullptr, nullptr, nullptr, nullptr, d)) return rc;
+        relres = std::sqrt(d[0]) / bnorm;
+        ++it;
+      }
+    }
+    else if (method == FC_SOLVER_CG)
     {
       // preconditioned CG.  With Dirichlet rows applied (identity rows, columns kept) the operator is symmetric on the
       // free DOFs as long as the iterates keep x = b on the Dirichlet rows: pass x with those entries set

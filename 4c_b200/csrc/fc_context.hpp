@@ -8,6 +8,25 @@
 
 #include "fc_material.cuh"
 
+struct fc_ctx;
+
+// one level of the geometric multigrid hierarchy (fc_capi_mg.cu); level 0 is the context's own mesh
+struct fc_mg_level
+{
+  fc_ctx* c = nullptr;               // coarse context (levels >= 1), owned by the hierarchy
+  int nn[3] = {0, 0, 0};             // lattice nodes per direction
+  int n_nodes = 0;
+  std::vector<int> h_lat2lid;        // [nn0 nn1 nn2]
+  std::vector<unsigned char> h_free; // [3 n_nodes] 1 = free DOF
+  int* d_lat2lid = nullptr;
+  int* d_lat = nullptr;              // [n_nodes][3]
+  unsigned char* d_free = nullptr;   // [3 n_nodes]
+  double* d_K = nullptr;             // tangent of the level (levels >= 1; level 0 uses the caller's)
+  double* d_Dinv = nullptr;          // inverse diagonal blocks (levels >= 1; level 0 uses ctx->d_Dinv)
+  double omega = 0.6;                // Jacobi damping of the level: 4 / (3 lambda_max(D^-1 K)), estimated by fc_solid_mg_update
+  double *d_b = nullptr, *d_x = nullptr, *d_y = nullptr, *d_r = nullptr, *d_u = nullptr;  // [3 n_nodes] each
+};
+
 struct fc_ctx
 {
   int device = 0, rank = 0, nranks = 1;
@@ -58,6 +77,13 @@ struct fc_ctx
   size_t solver_ws_cap = 0;
   double* d_Dinv = nullptr;           // [n_row_nodes][9] inverse diagonal blocks
   size_t Dinv_cap = 0;
+  std::vector<int> h_toggle_rows;     // host copy of the toggle (the multigrid hierarchy injects it into the coarse levels)
+  long long toggle_version = 0;
+  std::vector<fc_mg_level> mg;        // geometric multigrid hierarchy (fc_solid_mg_setup), empty = none
+  long long mg_toggle_version = -1;   // toggle the coarse Dirichlet maps were derived from
+  bool mg_operators_ready = false;    // fc_solid_mg_update ran for the current state
+  int mg_nu = 2;                      // pre- and post-smoothing sweeps of the V-cycle
+  bool mg_fine_omega_stale = true;    // the damping of level 0 is estimated at the first cycle after fc_solid_mg_update
   double* d_dot = nullptr;            // block partials [3][592] + results [3]
   double* h_dot_pinned = nullptr;
 

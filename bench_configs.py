@@ -99,7 +99,7 @@ def run(fc, name, ct, form, mat, nue, n, steps, flags=0):
     torch.cuda.empty_cache()
 
 
-def run_newton(fc, edge, steps):
+def run_newton(fc, edge, steps, method=None, mg_sweeps=2):
     """SURVEY 8f F1 at C2 size: one load step of a clamped hex8 Neo-Hooke cube under a nodal load on the x+ face, full Newton with
     every stage on the device (element evaluation, Dirichlet application, CG with node-block Jacobi): times per stage, the
     y = K x kernel against the HBM roofline, CG iterations."""
@@ -135,6 +135,10 @@ def run_newton(fc, edge, steps):
     spmv_ms = e0.elapsed_time(e1) / steps
     spmv_bytes = 8 * nnz + 4 * (nnz // 9) + 16 * n_row  # K once, one column-node id per 3x3 block, x and y once
     hist = []
+    method = fc.FC_SOLVER_CG if method is None else method
+    levels = s.mg_setup() if method == fc.FC_SOLVER_CG_MG else 1
+    if method == fc.FC_SOLVER_CG_MG:
+        s.mg_set_sweeps(mg_sweeps)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     for it in range(12):
         ev[0].record()
@@ -143,9 +147,11 @@ def run_newton(fc, edge, steps):
         s.apply_dirichlet(K)
         x.zero_()
         s.apply_dirichlet_to_system(x, r, None)
+        if method == fc.FC_SOLVER_CG_MG:
+            s.mg_update(u)  # coarse tangents at the injected state: part of the evaluation time
         ev[1].record()
         rn = float(r.norm())
-        cg_it, rr = s.linear_solve(K, r, x, method=fc.FC_SOLVER_CG, rel_tol=1e-8, max_iter=5000, check=False)
+        cg_it, rr = s.linear_solve(K, r, x, method=method, rel_tol=1e-8, max_iter=5000, check=False)
         u += x
         ev[2].record()
         torch.cuda.synchronize()
@@ -154,17 +160,102 @@ def run_newton(fc, edge, steps):
             break
     assert s.error_state() == (0, -1)
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
-    out = {"config": f"F1 device Newton step, hex8 NeoHooke {edge}^3, clamped x-, load on x+", "elements": edge ** 3, "n_dof": n_row, "nnz": int(nnz),
+    out = {"config": f"F1 device Newton step, hex8 NeoHooke {edge}^3, clamped x-, load on x+", "solver": ["CG + node-block Jacobi", "BiCGStab", f"CG + geometric multigrid V({mg_sweeps},{mg_sweeps}), {levels} levels"][method], "elements": edge ** 3, "n_dof": n_row, "nnz": int(nnz),
            "spmv_ms": spmv_ms, "spmv_algorithmic_GBps": spmv_bytes / (spmv_ms * 1e-3) / 1e9, "measured_peaks": peak,
            "newton": hist, "max_displacement": float(u.abs().max())}
+    if method == fc.FC_SOLVER_CG_MG:
+        out["mg_levels"] = [dict(zip(("nodes", "jacobi_omega"), s.mg_level_info(l))) for l in range(levels)]
     print(json.dumps(out), flush=True)
     s.close()
+
+
+def run_variant_b(fc, edge, steps):
+    """SURVEY 8e variant B against variant A, measured under torchrun on N GPUs (weak scaling, edge^3 per GPU).
+    A (built, bit-comparable with the reference's decomposition): forward halo import of u, every rank evaluates its owned
+      AND ghost elements, assembles owned rows only - no reduction of f or K.
+    B (north_star's wording): every element evaluated once by its owner; the matrix rows of ghost nodes that the rank's
+      owned elements touch are exported to their owners and summed there.
+    B is measured as a cost model on the real partition: the element kernel over the owned elements only, plus the export
+    of EXACTLY the bytes B would send (9 doubles per (ghost row node, coupled column node) pair through owned elements,
+    3 per ghost node for f) as one grouped exchange, plus the add of the received payload into K.  The index translation
+    between the sender's and the owner's CSR positions (a gather list per peer) is not built: it only adds to B."""
+    import torch
+    import torch.distributed as dist
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    from bench import Problem, global_edge
+    comm = fc.capi.nccl_comm_init(rank, world, local)
+    P = Problem(fc, torch, edge, rank, world, local, comm)
+    g, s = P.grid, P.s
+    flags = fc.FC_EVAL_ZERO_FIRST
+    # ---- variant A --------------------------------------------------------------------------------
+    for _ in range(3):
+        P.step(flags, False)
+    ms_a, zero_a, ker_a, _ = P.timed(steps, flags, False)
+    halo_bytes = 8 * (P.n_col_dof - P.n_row_dof)
+    # ---- variant B payload from the partition ---------------------------------------------------------
+    n_row_nodes, n_row_eles = g.n_row_nodes, g.n_row_eles
+    own = g.conn[:n_row_eles]                       # row elements come first
+    a = np.repeat(own, 8, axis=1).reshape(-1)       # row node of every (a, b) pair
+    b = np.tile(own, (1, 8)).reshape(-1)
+    m = a >= n_row_nodes                            # rows of ghost nodes
+    pairs = np.unique(a[m].astype(np.int64) * g.n_col_nodes + b[m])
+    ghost_rows = (pairs // g.n_col_nodes).astype(np.int64)
+    owner = g.node_owner[ghost_rows]
+    send_doubles = np.array([9 * int(np.sum(owner == p)) + 3 * len(np.unique(ghost_rows[owner == p])) for p in range(world)], np.int64)
+    send_t = torch.tensor(send_doubles, device=dev)
+    recv_t = torch.empty_like(send_t)
+    dist.all_to_all_single(recv_t, send_t)
+    recv_doubles = recv_t.cpu().numpy()
+    sendbuf = torch.ones(int(send_doubles.sum()), dtype=torch.float64, device=dev)
+    recvbuf = torch.empty(int(recv_doubles.sum()), dtype=torch.float64, device=dev)
+    # the element kernel over the owned elements only: a second context on the row elements of this rank
+    sB = fc.Solid(local, rank, world)
+    sB.set_stream(torch.cuda.current_stream().cuda_stream)
+    sB.set_mesh(fc.FC_HEX8, fc.FC_FORM_DISPLACEMENT, g.X, g.node_gid, g.node_owner, own, g.ele_gid[:n_row_eles])
+    sB.set_material(fc.FC_MAT_ELASTHYPER_COUPNEOHOOKE, 10.0, 0.25)
+    sB.build_graph()
+
+    def step_b():
+        P.halo_library()  # B needs the ghost displacements as well (its owned elements touch ghost nodes)
+        sB.evaluate(fc.FC_ACTION_NLNSTIFF, P.u_col, P.f_row, P.K, flags=flags, want_errors=False)
+        dist.all_to_all_single(recvbuf, sendbuf, [int(v) for v in recv_doubles], [int(v) for v in send_doubles])
+        P.K[:recvbuf.numel()] += recvbuf  # add of the received rows (contiguous stand-in for the gather-add)
+
+    for _ in range(3):
+        step_b()
+    P.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step_b()
+    e1.record()
+    P.barrier()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    z, k = sB.kernel_ms_history(min(steps, 64))
+    tot = torch.tensor([float(send_doubles.sum()) * 8, float(halo_bytes)], dtype=torch.float64, device=dev)
+    dist.all_reduce(tot)
+    if rank == 0:
+        print(json.dumps({"config": f"variant A vs variant B, hex8 NeoHooke {edge}^3 per GPU on {world} GPUs, partition " + "x".join(str(v) for v in g.subdivisions),
+                          "variant_A": {"ms_per_step": ms_a, "kernel_ms": ker_a, "zero_fill_ms": zero_a, "exchange_bytes_all_ranks": float(tot[1].item()),
+                                        "elements_evaluated_rank0": int(g.n_col_eles), "what": "halo import of u + owned and ghost elements, owner rows only"},
+                          "variant_B": {"ms_per_step": float(t.item()), "kernel_ms": float(k.mean()), "zero_fill_ms": float(z.mean()),
+                                        "exchange_bytes_all_ranks": float(tot[0].item()), "elements_evaluated_rank0": int(n_row_eles),
+                                        "what": "halo import of u + owned elements only + export of the ghost-node rows (exact byte counts) + add; cost model, index translation not built"},
+                          "bytes_ratio_B_over_A": float(tot[0].item() / tot[1].item())}), flush=True)
+    sB.close()
+    P.close()
+    dist.destroy_process_group()
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--only", default=None)
     ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--mg-sweeps", type=int, default=2)
     args = ap.parse_args()
     fc = importlib.import_module("4c_b200")
     H8, H27, T10 = fc.FC_HEX8, fc.FC_HEX27, fc.FC_TET10
@@ -186,8 +277,12 @@ def main():
         ("C5/8 hex8 NeoHooke 200^3 (one GPU's share of 400^3)", H8, D, NH, 0.25, (200, 200, 200), 0),
         ("C5/8-oc hex8 NeoHooke 200^3, owner-computed rows", H8, D, NH, 0.25, (200, 200, 200), fc.FC_EVAL_OWNER_COMPUTED),
     ]
+    if args.only and args.only.startswith("variantB"):
+        run_variant_b(fc, int(args.only[8:] or 100), args.steps)
+        return
     if args.only and args.only.startswith("newton"):
-        run_newton(fc, int(args.only[6:] or 100), args.steps)
+        mg = args.only.startswith("newtonmg")
+        run_newton(fc, int(args.only[8 if mg else 6:] or 100), args.steps, fc.FC_SOLVER_CG_MG if mg else None, args.mg_sweeps)
         return
     for c in cfgs:
         if args.only and args.only not in c[0]:

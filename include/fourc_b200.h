@@ -316,8 +316,24 @@ extern "C"
   enum
   {
     FC_SOLVER_CG = 0,
-    FC_SOLVER_BICGSTAB = 1
+    FC_SOLVER_BICGSTAB = 1,
+    FC_SOLVER_CG_MG = 2 /* CG preconditioned by a geometric multigrid V-cycle (fc_solid_mg_setup / _update) */
   };
+  /* Geometric multigrid hierarchy for FC_SOLVER_CG_MG, in place of the MueLu preconditioner the reference configures
+   * for large structural problems (src/core/linear_solver).  hex8 lattice mesh on one rank; isotropic materials.
+   *   mg_setup   once per mesh + graph: coarse lattices (every second node, plus the last node of a direction with an odd
+   *              number of elements) down to 2 elements per direction or max_levels levels; n_levels (host) = levels
+   *              built, FC_ERR_UNSUPPORTED when there is no coarser one
+   *   mg_update  once per Newton iteration, after fc_solid_set_dirichlet_toggle: coarse tangents = the same elements and
+   *              material re-discretised on the coarse lattices at the injected state u_col_dev (device), coarse
+   *              Dirichlet rows = the toggled DOFs of the coincident nodes, node-block Jacobi smoother blocks
+   * The V(2,2) cycle uses damped node-block Jacobi (omega = 4 / (3 lambda_max(D^-1 K)) per level, lambda_max from a few
+   * power iterations in mg_update), trilinear transfers, 60 sweeps on the coarsest level. */
+  int fc_solid_mg_setup(fc_ctx* ctx, int max_levels, int* n_levels);
+  int fc_solid_mg_update(fc_ctx* ctx, const double* u_col_dev);
+  int fc_solid_mg_set_sweeps(fc_ctx* ctx, int nu); /* pre- and post-smoothing sweeps of the cycle, default 2 */
+  /* nodes and Jacobi damping of one level (0 = finest; its damping is known after the first solve that follows mg_update) */
+  int fc_solid_mg_level_info(fc_ctx* ctx, int level, int* n_nodes, double* omega);
   int fc_solid_set_dirichlet_toggle(fc_ctx* ctx, int n, const int* row_lids);
   int fc_solid_apply_dirichlet(fc_ctx* ctx, double* K_values, int diagonalblock);
   int fc_solid_apply_dirichlet_to_system(fc_ctx* ctx, double* x, double* b, const double* dbcval);

@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
 
-FC_HEX8, FC_HEX27, FC_TET10 = 0, 1, 2
+FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
 FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_SUMMAND_COUPNEOHOOKE, FC_SUMMAND_COUPSVK, FC_SUMMAND_COUPANISOEXPO = 0, 1, 2
@@ -20,13 +20,15 @@ FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
 FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_OWNER_COMPUTED = 1, 2, 4, 8
 FC_EVAL_INTERIOR, FC_EVAL_BOUNDARY = 32, 64
 FC_STRESS_2PK, FC_STRESS_CAUCHY = 0, 1
-FC_FACE_QUAD4, FC_FACE_QUAD9, FC_FACE_TRI6 = 0, 1, 2
-FACE_NEN = {FC_FACE_QUAD4: 4, FC_FACE_QUAD9: 9, FC_FACE_TRI6: 6}
+FC_FACE_QUAD4, FC_FACE_QUAD9, FC_FACE_TRI6, FC_FACE_QUAD8, FC_FACE_TRI3 = 0, 1, 2, 3, 4
+FACE_NEN = {FC_FACE_QUAD4: 4, FC_FACE_QUAD9: 9, FC_FACE_TRI6: 6, FC_FACE_QUAD8: 8, FC_FACE_TRI3: 3}
+FACE_NGP = {FC_FACE_QUAD4: 4, FC_FACE_QUAD9: 9, FC_FACE_TRI6: 6, FC_FACE_QUAD8: 9, FC_FACE_TRI3: 3}
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
 FC_ERR_SOLVER, FC_ERR_SOLVER_NOT_CONVERGED = -7, -8
 FC_SOLVER_CG, FC_SOLVER_BICGSTAB, FC_SOLVER_CG_MG = 0, 1, 2
-NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10}
+NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10, FC_HEX20: 20, FC_TET4: 4, FC_WEDGE6: 6, FC_PYRAMID5: 5}
+NGP = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4, FC_HEX20: 27, FC_TET4: 1, FC_WEDGE6: 6, FC_PYRAMID5: 8}
 
 EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
@@ -383,21 +385,21 @@ class Solid:
 
     def neumann_surface_gp_coords(self, face_type, face_nodes):
         fn = _i32(face_nodes).reshape(-1, FACE_NEN[face_type])
-        ngp = FACE_NEN[face_type]
+        ngp = FACE_NGP[face_type]
         out = np.zeros((len(fn), ngp, 3))
         self._chk(lib().fc_solid_neumann_surface_gp_coords(self.h, C.c_int(face_type), C.c_int(len(fn)), _ptr(fn), _ptr(out)))
         return out
 
     def neumann_volume_gp_coords(self, ele_lids):
         el = _i32(ele_lids)
-        ngp = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4}[self.celltype]
+        ngp = NGP[self.celltype]
         out = np.zeros((len(el), ngp, 3))
         self._chk(lib().fc_solid_neumann_volume_gp_coords(self.h, C.c_int(len(el)), _ptr(el), _ptr(out)))
         return out
 
     def evaluate_stress(self, u_col, stress_type=1, want_gp=True, want_nodal=True):
         """struct_calc_stress: (gp_stress [n_ele, ngp, 6], nodal_stress [n_row_nodes, 6]); 0 = 2PK, 1 = Cauchy"""
-        ngp = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4}[self.celltype]
+        ngp = NGP[self.celltype]
         gp = np.zeros((self.n_ele, ngp, 6)) if want_gp else None
         nodal = np.zeros((self.n_row_dof // 3, 6)) if want_nodal else None
         self._chk(lib().fc_solid_evaluate_stress(self.h, _ptr(u_col), C.c_int(stress_type), _ptr(gp), _ptr(nodal)))

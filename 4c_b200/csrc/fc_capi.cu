@@ -179,10 +179,9 @@ extern "C"
   {
     if (!ctx || !X || !node_owner || !conn || !ele_gid || n_col_nodes <= 0 || n_col_ele < 0) return FC_ERR_INVALID;
     (void)node_gid;
-    if (celltype != FC_HEX8 && celltype != FC_HEX27 && celltype != FC_TET10)
-      return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
-    if (formulation != FC_FORM_DISPLACEMENT && !(formulation == FC_FORM_FBAR && celltype == FC_HEX8))
-      return fail(ctx, FC_ERR_UNSUPPORTED, "F-bar exists for hex8 only (4C_solid_3D_ele_factory.hpp:49-50)");
+    if (celltype < FC_HEX8 || celltype > FC_PYRAMID5) return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
+    if (formulation != FC_FORM_DISPLACEMENT && !(formulation == FC_FORM_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)))
+      return fail(ctx, FC_ERR_UNSUPPORTED, "F-bar exists for hex8 and pyramid5 only (4C_solid_3D_ele_factory.hpp:49-50)");
     FC_CUDA(cudaSetDevice(ctx->device));
     const int nen = fc::cell_nen(celltype);
     // owned nodes first (Epetra column-map convention)
@@ -224,9 +223,16 @@ extern "C"
     FC_CUDA(dev_upload(ctx->d_conn, conn, (size_t)n_col_ele * nen, ctx->stream));
     FC_CUDA(dev_upload(ctx->d_ele_gid, ele_gid, (size_t)n_col_ele, ctx->stream));
     std::vector<double> dN, w;
-    if (celltype == FC_HEX8) fill_tables<fc::HEX8>(dN, w);
-    if (celltype == FC_HEX27) fill_tables<fc::HEX27>(dN, w);
-    if (celltype == FC_TET10) fill_tables<fc::TET10>(dN, w);
+    switch (celltype)
+    {
+      case FC_HEX8: fill_tables<fc::HEX8>(dN, w); break;
+      case FC_HEX27: fill_tables<fc::HEX27>(dN, w); break;
+      case FC_TET10: fill_tables<fc::TET10>(dN, w); break;
+      case FC_HEX20: fill_tables<fc::HEX20>(dN, w); break;
+      case FC_TET4: fill_tables<fc::TET4>(dN, w); break;
+      case FC_WEDGE6: fill_tables<fc::WEDGE6>(dN, w); break;
+      default: fill_tables<fc::PYRAMID5>(dN, w); break;
+    }
     FC_CUDA(dev_upload(ctx->d_dNtab, dN.data(), dN.size(), ctx->stream));
     FC_CUDA(dev_upload(ctx->d_gpw, w.data(), w.size(), ctx->stream));
     dev_free(ctx->d_ele_bad);
@@ -239,7 +245,7 @@ extern "C"
       // 37 KB per element).  More than one rank: elements without ghost nodes first, so that they can be evaluated while the
       // halo import is in flight (FC_EVAL_INTERIOR, then FC_EVAL_BOUNDARY).
       std::vector<int> perm;
-      const long long budget = celltype == FC_HEX8 ? 12000 : (celltype == FC_TET10 ? 8500 : 650);
+      const long long budget = celltype == FC_HEX8 ? 12000 : (celltype == FC_TET10 ? 8500 : (celltype == FC_HEX27 ? 650 : 2000));
       fc_host::l2_sweep_order(n_col_nodes, X, n_col_ele, nen, conn, budget, perm);
       ctx->n_interior_ele = n_col_ele;
       if (n_row < n_col_nodes)
@@ -267,12 +273,19 @@ extern "C"
       ctx->h_err_pinned[1] = INT_MAX;
       FC_CUDA(cudaMemcpyAsync(ctx->d_err, ctx->h_err_pinned, 2 * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
       const int bs = 128, gs = (n_col_ele + bs - 1) / bs;
-      if (celltype == FC_HEX8)
-        fc::k_check_node_jacobians<fc::HEX8><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_ele_gid, n_col_ele, ctx->d_dNtab, ctx->d_ele_bad, ctx->d_err);
-      else if (celltype == FC_HEX27)
-        fc::k_check_node_jacobians<fc::HEX27><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_ele_gid, n_col_ele, ctx->d_dNtab, ctx->d_ele_bad, ctx->d_err);
-      else
-        fc::k_check_node_jacobians<fc::TET10><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_ele_gid, n_col_ele, ctx->d_dNtab, ctx->d_ele_bad, ctx->d_err);
+#define FC_CHECK_NODE_JACOBIANS(CT) \
+  fc::k_check_node_jacobians<CT><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_ele_gid, n_col_ele, ctx->d_dNtab, ctx->d_ele_bad, ctx->d_err)
+      switch (celltype)
+      {
+        case FC_HEX8: FC_CHECK_NODE_JACOBIANS(fc::HEX8); break;
+        case FC_HEX27: FC_CHECK_NODE_JACOBIANS(fc::HEX27); break;
+        case FC_TET10: FC_CHECK_NODE_JACOBIANS(fc::TET10); break;
+        case FC_HEX20: FC_CHECK_NODE_JACOBIANS(fc::HEX20); break;
+        case FC_TET4: FC_CHECK_NODE_JACOBIANS(fc::TET4); break;
+        case FC_WEDGE6: FC_CHECK_NODE_JACOBIANS(fc::WEDGE6); break;
+        default: FC_CHECK_NODE_JACOBIANS(fc::PYRAMID5); break;
+      }
+#undef FC_CHECK_NODE_JACOBIANS
       ctx->launches++;
       FC_CUDA(cudaGetLastError());
       FC_CUDA(cudaMemcpyAsync(ctx->h_err_pinned, ctx->d_err, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));

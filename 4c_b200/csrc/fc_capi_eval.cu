@@ -133,6 +133,7 @@ namespace
     if (flags & FC_EVAL_FORCE_GENERIC) return false;
     const bool fbar = ctx->formulation == FC_FORM_FBAR, nh = ctx->mat.kind == fc::MAT_NEOHOOKE;
     if (ctx->celltype == FC_HEX8) return nh ? (fbar || !(flags & FC_EVAL_CLOSED_FORM_FMA)) : (ctx->mat.kind == fc::MAT_SVK && !fbar);  // k_hex8_neohooke_mma, k_hex8_mma_ext
+    if (ctx->celltype != FC_HEX27 && ctx->celltype != FC_TET10) return false;                      // k_generic
     return nh && !fbar;                                                                            // k_nh_mma_gen
   }
 
@@ -147,6 +148,12 @@ namespace
     if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_SVK && !(flags & FC_EVAL_FORCE_GENERIC))
       return launch_hex8_ext<fc::VAR_SVK_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_HEX8) return fbar ? launch_generic<fc::HEX8, fc::FORM_FBAR, WANT_K>(ctx, A) : launch_generic<fc::HEX8, fc::FORM_DISP, WANT_K>(ctx, A);
+    // SURVEY 8f F4 cell types: the generic B-operator kernel
+    if (ctx->celltype == FC_HEX20) return launch_generic<fc::HEX20, fc::FORM_DISP, WANT_K>(ctx, A);
+    if (ctx->celltype == FC_TET4) return launch_generic<fc::TET4, fc::FORM_DISP, WANT_K>(ctx, A);
+    if (ctx->celltype == FC_WEDGE6) return launch_generic<fc::WEDGE6, fc::FORM_DISP, WANT_K>(ctx, A);
+    if (ctx->celltype == FC_PYRAMID5)
+      return fbar ? launch_generic<fc::PYRAMID5, fc::FORM_FBAR, WANT_K>(ctx, A) : launch_generic<fc::PYRAMID5, fc::FORM_DISP, WANT_K>(ctx, A);
     const bool nh_gen = ctx->mat.kind == fc::MAT_NEOHOOKE && !fbar && !(flags & FC_EVAL_FORCE_GENERIC);
     if (ctx->celltype == FC_HEX27) return nh_gen ? launch_nh_gen<fc::HEX27, WANT_K>(ctx, A) : launch_generic<fc::HEX27, fc::FORM_DISP, WANT_K>(ctx, A);
     return nh_gen ? launch_nh_gen<fc::TET10, WANT_K>(ctx, A) : launch_generic<fc::TET10, fc::FORM_DISP, WANT_K>(ctx, A);

@@ -132,6 +132,7 @@ extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int st
 {
   if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede evaluate_stress");
   if (!ctx->have_material) return fail(ctx, FC_ERR_INVALID, "set_material must precede evaluate_stress");
+  if (ctx->celltype > FC_TET10) return fail(ctx, FC_ERR_UNSUPPORTED, "stress output exists for hex8, hex27 and tet10");
   if (!u_col || (!gp_stress && !nodal_stress)) return fail(ctx, FC_ERR_INVALID, "u_col and one output are required");
   if (stress_type != FC_STRESS_2PK && stress_type != FC_STRESS_CAUCHY) return fail(ctx, FC_ERR_UNSUPPORTED, "stress type");
   FC_CUDA(cudaSetDevice(ctx->device));

@@ -2,10 +2,16 @@
 // device kernels (all __host__ __device__).  Definitions follow the reference (paths relative
 // to the reference tree):
 //   shape functions  src/core/fem/src/general/utils/4C_fem_general_utils_fem_shapefunctions.hpp
-//                    hex8 :53-72/:386-427, hex27 :190-230/:683-792, tet10 :244-259/:808-850
+//                    hex8 :53-72/:386-427, hex27 :190-230/:683-792, tet10 :244-259/:808-850,
+//                    hex20 :138-189/:584-682, tet4 :231-243/:790-807, wedge6 :260-271/:854-882, pyramid5 :312-345/:953-996
 //   Gauss rules      src/core/fem/src/general/utils/4C_fem_general_utils_integration.cpp
-//                    hex_8point :74-105, hex_27point :130-243, tet_4point :331-350
-//   rule selection   src/solid_3D_ele/4C_solid_3D_ele_calc_lib_integration.hpp:39-62
+//                    hex_8point :74-105, hex_27point :130-243, tet_1point :322-330, tet_4point :331-350,
+//                    wedge_6point :5992-6030, pyramid_8point :6092-6133
+//   rule selection   src/solid_3D_ele/4C_solid_3D_ele_calc_lib_integration.hpp:39-62 and
+//                    src/core/fem/src/general/element/4C_fem_general_element_integration_select.hpp:49-82
+//   node parameter coordinates (the points of the node-Jacobian check)
+//                    src/core/fem/src/general/utils/4C_fem_general_utils_local_connectivity_matrices.hpp:291-327, :564-575
+//                    (wedge6 takes the first six points of the wedge18 table: they are not where its own shape functions are 1)
 #pragma once
 #include <cmath>
 
@@ -21,7 +27,11 @@ namespace fc
   {
     HEX8 = 0,
     HEX27 = 1,
-    TET10 = 2
+    TET10 = 2,
+    HEX20 = 3,
+    TET4 = 4,
+    WEDGE6 = 5,
+    PYRAMID5 = 6
   };
 
   template <int CT>
@@ -42,8 +52,53 @@ namespace fc
     static constexpr int nen = 10, ngp = 4;
   };
 
-  FC_HD int cell_nen(int ct) { return ct == HEX8 ? 8 : (ct == HEX27 ? 27 : 10); }
-  FC_HD int cell_ngp(int ct) { return ct == HEX8 ? 8 : (ct == HEX27 ? 27 : 4); }
+  template <>
+  struct Cell<HEX20>
+  {
+    static constexpr int nen = 20, ngp = 27;
+  };
+  template <>
+  struct Cell<TET4>
+  {
+    static constexpr int nen = 4, ngp = 1;
+  };
+  template <>
+  struct Cell<WEDGE6>
+  {
+    static constexpr int nen = 6, ngp = 6;
+  };
+  template <>
+  struct Cell<PYRAMID5>
+  {
+    static constexpr int nen = 5, ngp = 8;
+  };
+
+  FC_HD int cell_nen(int ct)
+  {
+    switch (ct)
+    {
+      case HEX8: return Cell<HEX8>::nen;
+      case HEX27: return Cell<HEX27>::nen;
+      case TET10: return Cell<TET10>::nen;
+      case HEX20: return Cell<HEX20>::nen;
+      case TET4: return Cell<TET4>::nen;
+      case WEDGE6: return Cell<WEDGE6>::nen;
+      default: return Cell<PYRAMID5>::nen;
+    }
+  }
+  FC_HD int cell_ngp(int ct)
+  {
+    switch (ct)
+    {
+      case HEX8: return Cell<HEX8>::ngp;
+      case HEX27: return Cell<HEX27>::ngp;
+      case TET10: return Cell<TET10>::ngp;
+      case HEX20: return Cell<HEX20>::ngp;
+      case TET4: return Cell<TET4>::ngp;
+      case WEDGE6: return Cell<WEDGE6>::ngp;
+      default: return Cell<PYRAMID5>::ngp;
+    }
+  }
 
   // Parameter-space sign/position of hex node a in direction d as an integer in {-1,0,1}.
   // Reference numbering: corners 0-7, edge mids 8-19, face centres 20-25, centre 26.
@@ -66,7 +121,17 @@ namespace fc
 
   FC_HD void node_param_coords(int ct, int a, double* xi)
   {
-    if (ct == TET10)
+    if (ct == WEDGE6)
+    {
+      const double t[6][3] = {{0, 0, -1}, {1, 0, -1}, {0, 1, -1}, {0, 0, 1}, {1, 0, 1}, {0, 1, 1}};
+      for (int d = 0; d < 3; ++d) xi[d] = t[a][d];
+    }
+    else if (ct == PYRAMID5)
+    {
+      const double t[5][3] = {{-1, -1, 0}, {1, -1, 0}, {1, 1, 0}, {-1, 1, 0}, {0, 0, 1}};
+      for (int d = 0; d < 3; ++d) xi[d] = t[a][d];
+    }
+    else if (ct == TET10 || ct == TET4)
     {
       // corners (0,0,0),(1,0,0),(0,1,0),(0,0,1); mids 4:(01) 5:(12) 6:(02) 7:(03) 8:(13) 9:(23)
       const double t[10][3] = {{0, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {.5, 0, 0}, {.5, .5, 0},
@@ -115,6 +180,57 @@ namespace fc
         dN[3 * a + 2] = R[ir] * S[is] * dT[it];
       }
     }
+    else if constexpr (CT == HEX20)
+    {
+      // corner a: N = 1/8 R S T (R + S + T - 5) with R = 1 + r_a r, ...; mid-edge node on an edge along r: 1/4 (1 - r^2) S T
+      const double P[3] = {r, s, t};
+      for (int a = 0; a < 20; ++a)
+      {
+        int p[3];
+        double L[3];
+        for (int d = 0; d < 3; ++d)
+        {
+          p[d] = hex_node_pos(a, d);
+          L[d] = p[d] == 0 ? 1.0 - P[d] * P[d] : 1.0 + p[d] * P[d];
+        }
+        if (a < 8)
+        {
+          const double sum = L[0] + L[1] + L[2] - 5.0;
+          dN[3 * a + 0] = 0.125 * p[0] * L[1] * L[2] * (sum + L[0]);
+          dN[3 * a + 1] = 0.125 * p[1] * L[2] * L[0] * (sum + L[1]);
+          dN[3 * a + 2] = 0.125 * p[2] * L[0] * L[1] * (sum + L[2]);
+        }
+        else
+          for (int d = 0; d < 3; ++d)
+          {
+            const int d1 = (d + 1) % 3, d2 = (d + 2) % 3;
+            dN[3 * a + d] = p[d] == 0 ? -0.5 * P[d] * L[d1] * L[d2] : 0.25 * p[d] * L[d1] * L[d2];
+          }
+      }
+    }
+    else if constexpr (CT == TET4)
+    {
+      const double v[12] = {-1, -1, -1, 1, 0, 0, 0, 1, 0, 0, 0, 1};
+      for (int i = 0; i < 12; ++i) dN[i] = v[i];
+    }
+    else if constexpr (CT == WEDGE6)
+    {
+      const double p1 = 0.5 * (1.0 - t), p2 = 0.5 * (1.0 + t), t3 = 1.0 - r - s;
+      const double v[18] = {p1, 0, -0.5 * r, 0, p1, -0.5 * s, -p1, -p1, -0.5 * t3, p2, 0, 0.5 * r, 0, p2, 0.5 * s, -p2, -p2, 0.5 * t3};
+      for (int i = 0; i < 18; ++i) dN[i] = v[i];
+    }
+    else if constexpr (CT == PYRAMID5)
+    {
+      // the reference's rational pyramid functions; at the apex (|t - 1| <= 1e-14) it sets the three ratios to 1
+      const bool apex = !(fabs(t - 1.0) > 1.0e-14);
+      const double dr = apex ? 1.0 : s * t / (1.0 - t), ds = apex ? 1.0 : r * t / (1.0 - t), dt = apex ? 1.0 : r * s / ((1.0 - t) * (1.0 - t));
+      const double v[15] = {0.25 * (-(1.0 - s) + dr), 0.25 * (-(1.0 - r) + ds), 0.25 * (dt - 1.0),  //
+          0.25 * ((1.0 - s) - dr), 0.25 * (-(1.0 + r) - ds), 0.25 * (-dt - 1.0),                     //
+          0.25 * ((1.0 + s) + dr), 0.25 * ((1.0 + r) + ds), 0.25 * (dt - 1.0),                       //
+          0.25 * (-(1.0 + s) - dr), 0.25 * ((1.0 - r) - ds), 0.25 * (-dt - 1.0),                     //
+          0.0, 0.0, 1.0};
+      for (int i = 0; i < 15; ++i) dN[i] = v[i];
+    }
     else
     {
       const double u = 1.0 - r - s - t;
@@ -144,6 +260,42 @@ namespace fc
       const double T[3] = {0.5 * t * (t - 1.0), 1.0 - t * t, 0.5 * t * (t + 1.0)};
       for (int a = 0; a < 27; ++a) N[a] = R[hex_node_pos(a, 0) + 1] * S[hex_node_pos(a, 1) + 1] * T[hex_node_pos(a, 2) + 1];
     }
+    else if constexpr (CT == HEX20)
+    {
+      const double P[3] = {r, s, t};
+      for (int a = 0; a < 20; ++a)
+      {
+        double L[3];
+        for (int d = 0; d < 3; ++d)
+        {
+          const int p = hex_node_pos(a, d);
+          L[d] = p == 0 ? 1.0 - P[d] * P[d] : 1.0 + p * P[d];
+        }
+        N[a] = a < 8 ? 0.125 * L[0] * L[1] * L[2] * (L[0] + L[1] + L[2] - 5.0) : 0.25 * L[0] * L[1] * L[2];
+      }
+    }
+    else if constexpr (CT == TET4)
+    {
+      N[0] = 1.0 - r - s - t;
+      N[1] = r;
+      N[2] = s;
+      N[3] = t;
+    }
+    else if constexpr (CT == WEDGE6)
+    {
+      const double t3 = 1.0 - r - s, lo = 0.5 * (1.0 - t), hi = 0.5 * (1.0 + t);
+      const double v[6] = {r * lo, s * lo, t3 * lo, r * hi, s * hi, t3 * hi};
+      for (int a = 0; a < 6; ++a) N[a] = v[a];
+    }
+    else if constexpr (CT == PYRAMID5)
+    {
+      const double ration = fabs(t - 1.0) > 1.0e-14 ? (r * s * t) / (1.0 - t) : 0.0;
+      N[0] = 0.25 * ((1.0 - r) * (1.0 - s) - t + ration);
+      N[1] = 0.25 * ((1.0 + r) * (1.0 - s) - t - ration);
+      N[2] = 0.25 * ((1.0 + r) * (1.0 + s) - t + ration);
+      N[3] = 0.25 * ((1.0 - r) * (1.0 + s) - t - ration);
+      N[4] = t;
+    }
     else
     {
       const double u = 1.0 - r - s - t;
@@ -154,11 +306,12 @@ namespace fc
   }
 
   // Gauss rule of the mass integral (get_gauss_rule_mass_matrix, 4C_solid_3D_ele_calc_lib_integration.hpp:40-44):
-  // the stiffness rule for the hexes, tet_11point for tet10 (4C_fem_general_utils_integration.cpp:447-495)
+  // the stiffness rule except for the tets: tet_11point for tet10 (4C_fem_general_utils_integration.cpp:447-495),
+  // tet_4point for tet4
   template <int CT>
   struct MassRule
   {
-    static constexpr int ngp = CT == TET10 ? 11 : Cell<CT>::ngp;
+    static constexpr int ngp = CT == TET10 ? 11 : (CT == TET4 ? 4 : Cell<CT>::ngp);
   };
 
   // Gauss rule of the stiffness/force integral: point g of cell type CT
@@ -171,7 +324,31 @@ namespace fc
       for (int d = 0; d < 3; ++d) xi[d] = hex_node_pos(g, d) > 0 ? p : -p;
       *w = 1.0;
     }
-    else if constexpr (CT == HEX27)
+    else if constexpr (CT == TET4)
+    {
+      xi[0] = xi[1] = xi[2] = 0.25;
+      *w = 1.0 / 6.0;
+    }
+    else if constexpr (CT == WEDGE6)
+    {
+      const double q23 = 2.0 / 3.0, q16 = 1.0 / 6.0, p = 0.57735026918962576451;
+      const int k = g % 3;
+      xi[0] = k == 0 ? q23 : q16;
+      xi[1] = k == 1 ? q23 : q16;
+      xi[2] = g < 3 ? p : -p;
+      *w = q16;
+    }
+    else if constexpr (CT == PYRAMID5)
+    {
+      // the reference's 14-digit table
+      const double a = 0.26318405556971, b = 0.50661630334979;
+      const double m = (g & 1) ? b : a;
+      xi[0] = g < 4 ? -m : m;
+      xi[1] = (g & 2) ? m : -m;
+      xi[2] = (g & 1) ? 0.12251482265544 : 0.54415184401122;
+      *w = (g & 1) ? 0.23254745125351 : 0.10078588207983;
+    }
+    else if constexpr (CT == HEX27 || CT == HEX20)
     {
       // the reference's truncated 13-digit constants (integration.cpp:133,214-215)
       const double p = 0.7745966692415, w1 = 0.5555555555556, w2 = 0.8888888888889;
@@ -198,7 +375,9 @@ namespace fc
   template <int CT>
   FC_HD void mass_gauss_point(int g, double* xi, double* w)
   {
-    if constexpr (CT != TET10)
+    if constexpr (CT == TET4)
+      gauss_point<TET10>(g, xi, w);  // tet_4point
+    else if constexpr (CT != TET10)
       gauss_point<CT>(g, xi, w);
     else
     {
@@ -213,8 +392,11 @@ namespace fc
 
   FC_HD void centroid_param(int ct, double* xi)
   {
-    const double c = ct == TET10 ? 0.25 : 0.0;
+    // evaluate_parameter_coordinate_centroid, 4C_solid_3D_ele_calc_lib.hpp:230-294
+    const double c = (ct == TET10 || ct == TET4) ? 0.25 : 0.0;
     xi[0] = xi[1] = xi[2] = c;
+    if (ct == WEDGE6) xi[0] = xi[1] = 1.0 / 3.0;
+    if (ct == PYRAMID5) xi[2] = 0.25;
   }
 
   // ---- 3x3 helpers, row-major a[3*r+c] ------------------------------------------------------------

@@ -1,9 +1,12 @@
 // Surface cells of the Neumann loads (host + device): shape functions, first derivatives and Gauss rules of quad4 /
-// quad9 / tri6, the faces of hex8 / hex27 / tet10.  Definitions follow the reference (paths relative to its tree):
+// quad9 / tri6 / quad8 / tri3, the faces of hex8 / hex27 / tet10 / hex20 / tet4 (wedge6 and pyramid5 have quad4 and
+// tri3 faces).  Definitions follow the reference (paths relative to its tree):
 //   shape functions  src/core/fem/src/general/utils/4C_fem_general_utils_fem_shapefunctions.hpp  quad4 :2003-2015,
-//                    quad9 :2065-2087, tri6 :2098-2111 (derivatives :2148-, :2233-, :2288-)
+//                    quad8 :2027-2064, quad9 :2065-2087, tri3 :2088-2097, tri6 :2098-2111 (derivatives :2148-, :2185-, :2233-,
+//                    :2276-, :2288-)
 //   Gauss rules      src/core/fem/src/general/utils/4C_fem_general_utils_integration.cpp  quad_4point :6151-6183,
-//                    quad_9point :6185-6231, tri_6point :6374-6396 - with the reference's 13-digit constants
+//                    quad_9point :6185-6231 (quad8 and quad9), tri_3point :6341-6353, tri_6point :6374-6396 - with the
+//                    reference's 13-digit constants
 //   rule per cell    src/solid_3D_ele/4C_solid_3D_ele_surface.cpp:58-77 (get_optimal_gauss_rule)
 // The shape functions are generated from the node positions (products of 1D Lagrange polynomials / barycentric
 // coordinates) instead of the reference's per-node literals.
@@ -16,11 +19,19 @@ namespace fc
   {
     QUAD4 = 0,
     QUAD9 = 1,
-    TRI6 = 2
+    TRI6 = 2,
+    QUAD8 = 3,
+    TRI3 = 4
   };
 
-  FC_HD int face_nen(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 ? 9 : 6); }
-  FC_HD int face_ngp(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 ? 9 : 6); }
+  template <int FT>
+  struct FaceCell
+  {
+    static constexpr int nen = FT == QUAD4 ? 4 : (FT == QUAD9 ? 9 : (FT == TRI6 ? 6 : (FT == QUAD8 ? 8 : 3)));
+    static constexpr int ngp = FT == QUAD4 ? 4 : (FT == QUAD9 || FT == QUAD8 ? 9 : (FT == TRI6 ? 6 : 3));
+  };
+  FC_HD int face_nen(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 ? 9 : (ft == TRI6 ? 6 : (ft == QUAD8 ? 8 : 3))); }
+  FC_HD int face_ngp(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 || ft == QUAD8 ? 9 : (ft == TRI6 ? 6 : 3)); }
   constexpr int face_max_nen = 9, face_max_ngp = 9;
 
   // in-face position of quad node a in direction d as an integer in {-1, 0, 1}: corners 0-3 counter-clockwise from
@@ -41,7 +52,13 @@ namespace fc
       rs[1] = quad_node_pos(g, 1) * p;
       *w = 1.0;
     }
-    else if (ft == QUAD9)
+    else if (ft == TRI3)
+    {
+      rs[0] = g == 1 ? 2.0 / 3.0 : 1.0 / 6.0;
+      rs[1] = g == 2 ? 2.0 / 3.0 : 1.0 / 6.0;
+      *w = 1.0 / 6.0;
+    }
+    else if (ft == QUAD9 || ft == QUAD8)
     {
       // the points sit where the nodes of a quad9 sit (scaled), in the same order
       const double p = 0.7745966692415, w1 = 0.5555555555556, w2 = 0.8888888888889;
@@ -74,6 +91,46 @@ namespace fc
         dNr[a] = 0.25 * ra * (1.0 + sa * s);
         dNs[a] = 0.25 * (1.0 + ra * r) * sa;
       }
+    }
+    else if (ft == QUAD8)
+    {
+      // serendipity: corner = bilinear - half of the two neighbouring mid-edge functions
+      const double r2 = 1.0 - r * r, s2 = 1.0 - s * s;
+      for (int a = 0; a < 8; ++a)
+      {
+        const double ra = quad_node_pos(a, 0), sa = quad_node_pos(a, 1);
+        const double R = 1.0 + ra * r, S = 1.0 + sa * s;
+        if (a < 4)
+        {
+          N[a] = 0.25 * (R * S - (r2 * S + s2 * R));
+          dNr[a] = 0.25 * (ra * S - (-2.0 * r * S + s2 * ra));
+          dNs[a] = 0.25 * (R * sa - (r2 * sa - 2.0 * s * R));
+        }
+        else if (ra == 0.0)
+        {
+          N[a] = 0.5 * r2 * S;
+          dNr[a] = -r * S;
+          dNs[a] = 0.5 * r2 * sa;
+        }
+        else
+        {
+          N[a] = 0.5 * s2 * R;
+          dNr[a] = 0.5 * s2 * ra;
+          dNs[a] = -s * R;
+        }
+      }
+    }
+    else if (ft == TRI3)
+    {
+      N[0] = 1.0 - r - s;
+      N[1] = r;
+      N[2] = s;
+      dNr[0] = -1.0;
+      dNr[1] = 1.0;
+      dNr[2] = 0.0;
+      dNs[0] = -1.0;
+      dNs[1] = 0.0;
+      dNs[2] = 1.0;
     }
     else if (ft == QUAD9)
     {

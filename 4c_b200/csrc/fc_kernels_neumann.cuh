@@ -18,24 +18,28 @@ namespace fc
     int onoff[3];
   };
 
-  static __global__ void k_neumann_surface(const double* __restrict__ X, const int* __restrict__ face_nodes, int ft, int n_faces, NeumannVal V,
+  // One instance per face type: every loop bound is a compile-time constant.  (A single kernel with the face type as a
+  // run-time argument - bounds read from a table - was miscompiled by nvcc 12.9 -O3 for tri6: illegal address in the
+  // accumulation loop, clean with -G.)
+  template <int FT>
+  static __global__ void k_neumann_surface(const double* __restrict__ X, const int* __restrict__ face_nodes, int n_faces, NeumannVal V,
       const double* __restrict__ gp_factor, int n_row_nodes, double* __restrict__ f, double* __restrict__ gp_coords)
   {
     const int face = blockIdx.x * blockDim.x + threadIdx.x;
     if (face >= n_faces) return;
-    const int nen = face_nen(ft), ngp = face_ngp(ft);
-    double P[face_max_nen][3];
-    int nodes[face_max_nen];
+    constexpr int ft = FT, nen = FaceCell<FT>::nen, ngp = FaceCell<FT>::ngp;
+    double P[nen][3];
+    int nodes[nen];
     for (int a = 0; a < nen; ++a)
     {
       nodes[a] = face_nodes[(size_t)face * nen + a];
       for (int i = 0; i < 3; ++i) P[a][i] = X[3 * (size_t)nodes[a] + i];
     }
-    double fa[face_max_nen][3];
+    double fa[nen][3];
     for (int a = 0; a < nen; ++a) fa[a][0] = fa[a][1] = fa[a][2] = 0.0;
     for (int g = 0; g < ngp; ++g)
     {
-      double rs[2], w, N[face_max_nen], dr[face_max_nen], ds[face_max_nen];
+      double rs[2], w, N[nen], dr[nen], ds[nen];
       face_gauss_point(ft, g, rs, &w);
       face_shape(ft, rs, N, dr, ds);
       if (gp_coords)

@@ -52,13 +52,18 @@ extern "C"
   {
     FC_HEX8 = 0,
     FC_HEX27 = 1,
-    FC_TET10 = 2
+    FC_TET10 = 2,
+    /* evaluated by the generic B-operator kernel (no tensor-core variant); stress output not built */
+    FC_HEX20 = 3,   /* 27-point rule */
+    FC_TET4 = 4,    /* stiffness tet_1point, mass tet_4point */
+    FC_WEDGE6 = 5,  /* wedge_6point */
+    FC_PYRAMID5 = 6 /* pyramid_8point; F-bar allowed (4C_solid_3D_ele_factory.hpp:49-50) */
   };
   /* element technology (TECH none | fbar): src/solid_3D_ele/4C_solid_3D_ele.cpp:71-138 */
   enum
   {
     FC_FORM_DISPLACEMENT = 0, /* 4C_solid_3D_ele_calc_displacement_based.hpp:35-251 */
-    FC_FORM_FBAR = 1          /* 4C_solid_3D_ele_calc_fbar.hpp:43-191 (hex8 only) */
+    FC_FORM_FBAR = 1          /* 4C_solid_3D_ele_calc_fbar.hpp:43-191 (hex8 and pyramid5 only) */
   };
   /* materials: MAT_Struct_StVenantKirchhoff (src/mat/4C_mat_stvenantkirchhoff.cpp) and
    * MAT_ElastHyper with one ELAST_CoupNeoHooke summand (src/mat/4C_mat_elasthyper.cpp,
@@ -200,7 +205,9 @@ extern "C"
   {
     FC_FACE_QUAD4 = 0,
     FC_FACE_QUAD9 = 1,
-    FC_FACE_TRI6 = 2
+    FC_FACE_TRI6 = 2,
+    FC_FACE_QUAD8 = 3, /* hex20 faces, quad_9point */
+    FC_FACE_TRI3 = 4   /* tet4 / wedge6 / pyramid5 faces, tri_3point */
   };
   int fc_solid_neumann_surface(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, const int* onoff, const double* val,
       const double* gp_factor, double* f_ext);

@@ -304,7 +304,7 @@ namespace fc_oracle
       }
       if (Me)
       {
-        if (ct != TET10)
+        if (ct != TET10 && ct != TET4)
           add_mass_matrix<NEN>(N, integration_factor, rho, Me);  // same rule as the stiffness integral
         else
         {
@@ -313,11 +313,11 @@ namespace fc_oracle
         }
       }
     }
-    if (Me && ct == TET10)
+    if (Me && (ct == TET10 || ct == TET4))
     {
       // mass rule differs from the stiffness rule: second loop with the mean density   solid_3D_ele_calc.cpp:228-240
       double mxi[11][3], mw[11];
-      const int nm = gauss_rule_mass_tet10(mxi, mw);
+      const int nm = gauss_rule_mass(ct, mxi, mw);
       for (int gp = 0; gp < nm; ++gp)
       {
         double N[NEN], dN[3 * NEN];
@@ -343,6 +343,14 @@ namespace fc_oracle
         return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
       case TET10:
         return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+      case HEX20:
+        return element_evaluate_t<20, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+      case TET4:
+        return element_evaluate_t<4, 1>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+      case WEDGE6:
+        return element_evaluate_t<6, 6>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+      case PYRAMID5:
+        return element_evaluate_t<5, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
     }
     return -1;
   }

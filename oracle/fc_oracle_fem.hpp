@@ -1,13 +1,19 @@
 // ORACLE — TEST INFRASTRUCTURE ONLY. Never linked into or called by the product library.
 //
 // Shape functions, their first derivatives, node parameter coordinates and Gauss rules for
-// hex8 / hex27 / tet10 as the reference defines them (paths relative to /root/reference):
+// hex8 / hex27 / tet10 / hex20 / tet4 / wedge6 / pyramid5 as the reference defines them (paths relative to /root/reference):
 //   shape functions   src/core/fem/src/general/utils/4C_fem_general_utils_fem_shapefunctions.hpp
-//                     hex8 :53-72 / :386-427, hex27 :190-230 / :683-792, tet10 :244-259 / :808-850
+//                     hex8 :53-72 / :386-427, hex27 :190-230 / :683-792, tet10 :244-259 / :808-850,
+//                     hex20 :138-189 / :584-682, tet4 :231-243 / :790-807, wedge6 :260-271 / :854-882,
+//                     pyramid5 :312-345 / :953-996 (PY5TOL = 1e-14, :18)
 //   Gauss rules       src/core/fem/src/general/utils/4C_fem_general_utils_integration.cpp
-//                     hex_8point :74-105, hex_27point :130-243 (13-digit constants!), tet_4point :331-350
+//                     hex_8point :74-105, hex_27point :130-243 (13-digit constants!), tet_1point :322-330,
+//                     tet_4point :331-350, wedge_6point :5992-6030, pyramid_8point :6092-6133 (14-digit constants)
 //   rule selection    src/solid_3D_ele/4C_solid_3D_ele_calc_lib_integration.hpp:39-62
-//                     (tet10 stiffness uses the 4-point rule)
+//                     (tet10 stiffness uses the 4-point rule, tet4 stiffness the 1-point rule) over
+//                     src/core/fem/src/general/element/4C_fem_general_element_integration_select.hpp:49-82
+//   node parameter coordinates  src/core/fem/src/general/utils/4C_fem_general_utils_local_connectivity_matrices.hpp
+//                     :291-327 (tables), :564-575 (wedge6 reads the first six rows of the wedge18 table)
 #pragma once
 #include <cmath>
 
@@ -17,11 +23,23 @@ namespace fc_oracle
   {
     HEX8 = 0,
     HEX27 = 1,
-    TET10 = 2
+    TET10 = 2,
+    HEX20 = 3,
+    TET4 = 4,
+    WEDGE6 = 5,
+    PYRAMID5 = 6
   };
 
-  inline int num_nodes(int ct) { return ct == HEX8 ? 8 : (ct == HEX27 ? 27 : 10); }
-  inline int num_gp(int ct) { return ct == HEX8 ? 8 : (ct == HEX27 ? 27 : 4); }
+  inline int num_nodes(int ct)
+  {
+    static const int n[7] = {8, 27, 10, 20, 4, 6, 5};
+    return n[ct];
+  }
+  inline int num_gp(int ct)
+  {
+    static const int n[7] = {8, 27, 4, 27, 1, 6, 8};
+    return n[ct];
+  }
 
   // parameter coordinates (r,s,t) of the element nodes, reference node numbering.
   // hex8/hex27: corner nodes, then edge mid nodes 8..19, face centres 20..25, centre 26.
@@ -34,8 +52,14 @@ namespace fc_oracle
         {0, 0, 1}, {0, 0, 0}};
     static const double tet[10][3] = {{0, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {.5, 0, 0},
         {.5, .5, 0}, {0, .5, 0}, {0, 0, .5}, {.5, 0, .5}, {0, .5, .5}};
-    if (ct == TET10)
+    static const double wedge[6][3] = {{0, 0, -1}, {1, 0, -1}, {0, 1, -1}, {0, 0, 1}, {1, 0, 1}, {0, 1, 1}};
+    static const double pyramid[5][3] = {{-1, -1, 0}, {1, -1, 0}, {1, 1, 0}, {-1, 1, 0}, {0, 0, 1}};
+    if (ct == TET10 || ct == TET4)
       for (int d = 0; d < 3; ++d) xi[d] = tet[a][d];
+    else if (ct == WEDGE6)
+      for (int d = 0; d < 3; ++d) xi[d] = wedge[a][d];
+    else if (ct == PYRAMID5)
+      for (int d = 0; d < 3; ++d) xi[d] = pyramid[a][d];
     else
       for (int d = 0; d < 3; ++d) xi[d] = hex[a][d];
   }
@@ -70,6 +94,60 @@ namespace fc_oracle
         node_param_coords(HEX27, a, x);
         N[a] = R[(int)x[0] + 1] * S[(int)x[1] + 1] * T[(int)x[2] + 1];
       }
+    }
+    else if (ct == HEX20)
+    {
+      const double Q18 = 1.0 / 8.0;
+      const double rp = 1.0 + r, rm = 1.0 - r, sp = 1.0 + s, sm = 1.0 - s, tp = 1.0 + t, tm = 1.0 - t;
+      const double rrm = 1.0 - r * r, ssm = 1.0 - s * s, ttm = 1.0 - t * t;
+      N[0] = Q18 * rm * sm * tm * (rm + sm + tm - 5.0);
+      N[1] = Q18 * rp * sm * tm * (rp + sm + tm - 5.0);
+      N[2] = Q18 * rp * sp * tm * (rp + sp + tm - 5.0);
+      N[3] = Q18 * rm * sp * tm * (rm + sp + tm - 5.0);
+      N[4] = Q18 * rm * sm * tp * (rm + sm + tp - 5.0);
+      N[5] = Q18 * rp * sm * tp * (rp + sm + tp - 5.0);
+      N[6] = Q18 * rp * sp * tp * (rp + sp + tp - 5.0);
+      N[7] = Q18 * rm * sp * tp * (rm + sp + tp - 5.0);
+      N[8] = 0.25 * rrm * sm * tm;
+      N[9] = 0.25 * rp * ssm * tm;
+      N[10] = 0.25 * rrm * sp * tm;
+      N[11] = 0.25 * rm * ssm * tm;
+      N[12] = 0.25 * rm * sm * ttm;
+      N[13] = 0.25 * rp * sm * ttm;
+      N[14] = 0.25 * rp * sp * ttm;
+      N[15] = 0.25 * rm * sp * ttm;
+      N[16] = 0.25 * rrm * sm * tp;
+      N[17] = 0.25 * rp * ssm * tp;
+      N[18] = 0.25 * rrm * sp * tp;
+      N[19] = 0.25 * rm * ssm * tp;
+    }
+    else if (ct == TET4)
+    {
+      N[0] = 1.0 - r - s - t;
+      N[1] = r;
+      N[2] = s;
+      N[3] = t;
+    }
+    else if (ct == WEDGE6)
+    {
+      const double Q12 = 1.0 / 2.0, t3 = 1.0 - r - s;
+      N[0] = Q12 * r * (1.0 - t);
+      N[1] = Q12 * s * (1.0 - t);
+      N[2] = Q12 * t3 * (1.0 - t);
+      N[3] = Q12 * r * (1.0 + t);
+      N[4] = Q12 * s * (1.0 + t);
+      N[5] = Q12 * t3 * (1.0 + t);
+    }
+    else if (ct == PYRAMID5)
+    {
+      const double Q14 = 1.0 / 4.0;
+      double ration = 0.0;
+      if (std::abs(t - 1.0) > 1.0e-14) ration = (r * s * t) / (1.0 - t);
+      N[0] = Q14 * ((1.0 - r) * (1.0 - s) - t + ration);
+      N[1] = Q14 * ((1.0 + r) * (1.0 - s) - t - ration);
+      N[2] = Q14 * ((1.0 + r) * (1.0 + s) - t + ration);
+      N[3] = Q14 * ((1.0 - r) * (1.0 + s) - t - ration);
+      N[4] = t;
     }
     else
     {
@@ -127,6 +205,64 @@ namespace fc_oracle
         dN[2 + 3 * a] = R[ir] * S[is] * dT[it];
       }
     }
+    else if (ct == HEX20)
+    {
+      const double Q18 = 1.0 / 8.0;
+      const double rp = 1.0 + r, rm = 1.0 - r, sp = 1.0 + s, sm = 1.0 - s, tp = 1.0 + t, tm = 1.0 - t;
+      const double rrm = 1.0 - r * r, ssm = 1.0 - s * s, ttm = 1.0 - t * t;
+      // corner a: factors R, S, T in {m, p} by the sign of its position; the reference writes, e.g. for node 0,
+      //   d/dr = -Q18 sm tm (2 rm + sm + tm - 5),  d/ds = -Q18 tm rm (2 sm + tm + rm - 5),  d/dt = -Q18 rm sm (2 tm + rm + sm - 5)
+      const double Rf[2] = {rm, rp}, Sf[2] = {sm, sp}, Tf[2] = {tm, tp};
+      for (int a = 0; a < 8; ++a)
+      {
+        double x[3];
+        node_param_coords(HEX27, a, x);
+        const int ir = x[0] > 0, is = x[1] > 0, it = x[2] > 0;
+        const double R = Rf[ir], S = Sf[is], T = Tf[it];
+        dN[0 + 3 * a] = (ir ? Q18 : -Q18) * S * T * (2.0 * R + S + T - 5.0);
+        dN[1 + 3 * a] = (is ? Q18 : -Q18) * T * R * (2.0 * S + T + R - 5.0);
+        dN[2 + 3 * a] = (it ? Q18 : -Q18) * R * S * (2.0 * T + R + S - 5.0);
+      }
+      const double v[12][3] = {{-0.5 * r * sm * tm, -0.25 * rrm * tm, -0.25 * rrm * sm}, {0.25 * ssm * tm, -0.5 * s * tm * rp, -0.25 * ssm * rp},
+          {-0.5 * r * sp * tm, 0.25 * rrm * tm, -0.25 * rrm * sp}, {-0.25 * ssm * tm, -0.5 * s * tm * rm, -0.25 * ssm * rm},
+          {-0.25 * sm * ttm, -0.25 * ttm * rm, -0.5 * t * rm * sm}, {0.25 * sm * ttm, -0.25 * ttm * rp, -0.5 * t * rp * sm},
+          {0.25 * sp * ttm, 0.25 * ttm * rp, -0.5 * t * rp * sp}, {-0.25 * sp * ttm, 0.25 * ttm * rm, -0.5 * t * rm * sp},
+          {-0.5 * r * sm * tp, -0.25 * rrm * tp, 0.25 * rrm * sm}, {0.25 * ssm * tp, -0.5 * s * tp * rp, 0.25 * ssm * rp},
+          {-0.5 * r * sp * tp, 0.25 * rrm * tp, 0.25 * rrm * sp}, {-0.25 * ssm * tp, -0.5 * s * tp * rm, 0.25 * ssm * rm}};
+      for (int a = 8; a < 20; ++a)
+        for (int d = 0; d < 3; ++d) dN[d + 3 * a] = v[a - 8][d];
+    }
+    else if (ct == TET4)
+    {
+      const double v[4][3] = {{-1, -1, -1}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+      for (int a = 0; a < 4; ++a)
+        for (int d = 0; d < 3; ++d) dN[d + 3 * a] = v[a][d];
+    }
+    else if (ct == WEDGE6)
+    {
+      const double Q12 = 1.0 / 2.0;
+      const double p1 = Q12 * (1.0 - t), p2 = Q12 * (1.0 + t), t3 = 1.0 - r - s;
+      const double v[6][3] = {{p1, 0, -Q12 * r}, {0, p1, -Q12 * s}, {-p1, -p1, -Q12 * t3}, {p2, 0, Q12 * r}, {0, p2, Q12 * s}, {-p2, -p2, Q12 * t3}};
+      for (int a = 0; a < 6; ++a)
+        for (int d = 0; d < 3; ++d) dN[d + 3 * a] = v[a][d];
+    }
+    else if (ct == PYRAMID5)
+    {
+      const double Q14 = 1.0 / 4.0;
+      double rationdr = 1.0, rationds = 1.0, rationdt = 1.0;
+      if (std::abs(t - 1.0) > 1.0e-14)
+      {
+        rationdr = s * t / (1.0 - t);
+        rationds = r * t / (1.0 - t);
+        rationdt = r * s / ((1.0 - t) * (1.0 - t));
+      }
+      const double v[5][3] = {{Q14 * (-1.0 * (1.0 - s) + rationdr), Q14 * (-1.0 * (1.0 - r) + rationds), Q14 * (rationdt - 1.0)},
+          {Q14 * (1.0 * (1.0 - s) - rationdr), Q14 * (-1.0 * (1.0 + r) - rationds), Q14 * (-1.0 * rationdt - 1.0)},
+          {Q14 * (1.0 * (1.0 + s) + rationdr), Q14 * (1.0 * (1.0 + r) + rationds), Q14 * (rationdt - 1.0)},
+          {Q14 * (-1.0 * (1.0 + s) - rationdr), Q14 * (1.0 * (1.0 - r) - rationds), Q14 * (-1.0 * rationdt - 1.0)}, {0.0, 0.0, 1.0}};
+      for (int a = 0; a < 5; ++a)
+        for (int d = 0; d < 3; ++d) dN[d + 3 * a] = v[a][d];
+    }
     else
     {
       const double u = 1.0 - r - s - t;
@@ -154,7 +290,34 @@ namespace fc_oracle
         w[g] = 1.0;
       }
     }
-    else if (ct == HEX27)
+    else if (ct == TET4)
+    {
+      xi[0][0] = xi[0][1] = xi[0][2] = 1.0 / 4.0;
+      w[0] = 1.0 / 6.0;
+    }
+    else if (ct == WEDGE6)
+    {
+      const double xi3 = 1.0 / std::sqrt(3.0), Q23 = 2.0 / 3.0, Q16 = 1.0 / 6.0;
+      for (int g = 0; g < 6; ++g)
+      {
+        xi[g][0] = g % 3 == 0 ? Q23 : Q16;
+        xi[g][1] = g % 3 == 1 ? Q23 : Q16;
+        xi[g][2] = g < 3 ? xi3 : -xi3;
+        w[g] = Q16;
+      }
+    }
+    else if (ct == PYRAMID5)
+    {
+      const double a = 0.26318405556971, b = 0.50661630334979, za = 0.54415184401122, zb = 0.12251482265544;
+      const double wa = 0.10078588207983, wb = 0.23254745125351;
+      const double p[8][3] = {{-a, -a, za}, {-b, -b, zb}, {-a, a, za}, {-b, b, zb}, {a, -a, za}, {b, -b, zb}, {a, a, za}, {b, b, zb}};
+      for (int g = 0; g < 8; ++g)
+      {
+        for (int d = 0; d < 3; ++d) xi[g][d] = p[g][d];
+        w[g] = (g & 1) ? wb : wa;
+      }
+    }
+    else if (ct == HEX27 || ct == HEX20)
     {
       // the reference hard-codes truncated constants (integration.cpp:133,214-215)
       const double xi3 = 0.7745966692415;
@@ -204,10 +367,27 @@ namespace fc_oracle
     return 11;
   }
 
-  // centroid in parameter space (used by F-bar): hex -> origin, tet -> (1/4,1/4,1/4)
+  // mass rule of a cell type where it differs from the stiffness rule (tet10 -> tet_11point, tet4 -> tet_4point);
+  // returns the number of points, 0 = same rule as the stiffness integral
+  inline int gauss_rule_mass(int ct, double (*xi)[3], double* w)
+  {
+    if (ct == TET10) return gauss_rule_mass_tet10(xi, w);
+    if (ct == TET4)
+    {
+      gauss_rule(TET10, xi, w);
+      return 4;
+    }
+    return 0;
+  }
+
+  // centroid in parameter space (used by F-bar), evaluate_parameter_coordinate_centroid
+  // (src/solid_3D_ele/4C_solid_3D_ele_calc_lib.hpp:230-294): hex -> origin, tet -> (1/4,1/4,1/4), pyramid -> (0,0,1/4),
+  // wedge -> (1/3,1/3,0)
   inline void centroid_param(int ct, double* xi)
   {
-    const double c = ct == TET10 ? 0.25 : 0.0;
+    const double c = (ct == TET10 || ct == TET4) ? 0.25 : 0.0;
     xi[0] = xi[1] = xi[2] = c;
+    if (ct == PYRAMID5) xi[2] = 0.25;
+    if (ct == WEDGE6) xi[0] = xi[1] = 1.0 / 3.0;
   }
 }  // namespace fc_oracle

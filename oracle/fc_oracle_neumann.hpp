@@ -4,9 +4,11 @@
 //   volume   Discret::Elements::evaluate_neumann
 //            src/solid_3D_ele/4C_solid_3D_ele_neumann_evaluator.cpp:43-115
 //   2D shape functions  src/core/fem/src/general/utils/4C_fem_general_utils_fem_shapefunctions.hpp:2003-2015 (quad4),
-//                       :2065-2087 (quad9), :2098-2111 (tri6) and their first derivatives
+//                       :2027-2064 (quad8), :2065-2087 (quad9), :2088-2097 (tri3), :2098-2111 (tri6) and their first
+//                       derivatives (:2148-, :2185-2232, :2233-, :2276-2287, :2288-)
 //   2D Gauss rules      src/core/fem/src/general/utils/4C_fem_general_utils_integration.cpp:6151-6183 (quad_4point),
-//                       :6185-6231 (quad_9point), :6374-6396 (tri_6point), truncated constants as written there
+//                       :6185-6231 (quad_9point, also the rule of quad8), :6341-6353 (tri_3point), :6374-6396 (tri_6point),
+//                       truncated constants as written there
 //   rule per cell       src/solid_3D_ele/4C_solid_3D_ele_surface.cpp:58-77
 // Parity: pinned by the reference's RESULT DESCRIPTION of tests/input_files/solid_ele_hex8_Standard_eas_none_volume_neumann.dat
 // (surface + volume loads with FUNCT (x+1)(y+2)(z+3) and t; tests/golden) and by the surface loads of the other goldens.
@@ -21,10 +23,20 @@ namespace fc_oracle
   {
     QUAD4 = 0,
     QUAD9 = 1,
-    TRI6 = 2
+    TRI6 = 2,
+    QUAD8 = 3,
+    TRI3 = 4
   };
-  inline int face_num_nodes(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 ? 9 : 6); }
-  inline int face_num_gp(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 ? 9 : 6); }
+  inline int face_num_nodes(int ft)
+  {
+    static const int n[5] = {4, 9, 6, 8, 3};
+    return n[ft];
+  }
+  inline int face_num_gp(int ft)
+  {
+    static const int n[5] = {4, 9, 6, 9, 3};
+    return n[ft];
+  }
 
   // shape_function_2d / shape_function_2d_deriv1
   inline void shape_function_2d(int ft, double r, double s, double* funct, double* deriv_r, double* deriv_s)
@@ -44,6 +56,47 @@ namespace fc_oracle
       deriv_s[2] = 0.25 * rp;
       deriv_r[3] = -0.25 * sp;
       deriv_s[3] = 0.25 * rm;
+    }
+    else if (ft == QUAD8)
+    {
+      const double rp = 1.0 + r, rm = 1.0 - r, sp = 1.0 + s, sm = 1.0 - s;
+      const double r2 = 1.0 - r * r, s2 = 1.0 - s * s;
+      funct[0] = 0.25 * (rm * sm - (r2 * sm + s2 * rm));
+      funct[1] = 0.25 * (rp * sm - (r2 * sm + s2 * rp));
+      funct[2] = 0.25 * (rp * sp - (s2 * rp + r2 * sp));
+      funct[3] = 0.25 * (rm * sp - (r2 * sp + s2 * rm));
+      funct[4] = 0.5 * r2 * sm;
+      funct[5] = 0.5 * s2 * rp;
+      funct[6] = 0.5 * r2 * sp;
+      funct[7] = 0.5 * s2 * rm;
+      deriv_r[0] = 0.25 * sm * (2. * r + s);
+      deriv_s[0] = 0.25 * rm * (r + 2. * s);
+      deriv_r[1] = 0.25 * sm * (2. * r - s);
+      deriv_s[1] = 0.25 * rp * (2. * s - r);
+      deriv_r[2] = 0.25 * sp * (2. * r + s);
+      deriv_s[2] = 0.25 * rp * (r + 2. * s);
+      deriv_r[3] = 0.25 * sp * (2. * r - s);
+      deriv_s[3] = 0.25 * rm * (2. * s - r);
+      deriv_r[4] = -sm * r;
+      deriv_s[4] = -0.5 * rm * rp;
+      deriv_r[5] = 0.5 * sm * sp;
+      deriv_s[5] = -rp * s;
+      deriv_r[6] = -sp * r;
+      deriv_s[6] = 0.5 * rm * rp;
+      deriv_r[7] = -0.5 * sm * sp;
+      deriv_s[7] = -rm * s;
+    }
+    else if (ft == TRI3)
+    {
+      funct[0] = 1.0 - r - s;
+      funct[1] = r;
+      funct[2] = s;
+      deriv_r[0] = -1.0;
+      deriv_r[1] = 1.0;
+      deriv_r[2] = 0.0;
+      deriv_s[0] = -1.0;
+      deriv_s[1] = 0.0;
+      deriv_s[2] = 1.0;
     }
     else if (ft == QUAD9)
     {
@@ -116,7 +169,17 @@ namespace fc_oracle
         qwgt[i] = 1.0;
       }
     }
-    else if (ft == QUAD9)
+    else if (ft == TRI3)
+    {
+      const double p[3][2] = {{1.0 / 6.0, 1.0 / 6.0}, {2.0 / 3.0, 1.0 / 6.0}, {1.0 / 6.0, 2.0 / 3.0}};
+      for (int i = 0; i < 3; ++i)
+      {
+        qxg[i][0] = p[i][0];
+        qxg[i][1] = p[i][1];
+        qwgt[i] = 1.0 / 6.0;
+      }
+    }
+    else if (ft == QUAD9 || ft == QUAD8)
     {
       const double g = 0.7745966692415, a = 0.5555555555556, b = 0.8888888888889;
       const double p[9][2] = {{-g, -g}, {g, -g}, {g, g}, {-g, g}, {0.0, -g}, {g, 0.0}, {0.0, g}, {-g, 0.0}, {0.0, 0.0}};

@@ -28,6 +28,15 @@ CASES = [
     "sohex8fbar_cooks_nl_new_struc.dat",  # 64 hex8 TECH fbar, CoupNeoHooke NUE 0.4999, statics, 20 load steps
     "solid_ele_hex8_Standard_eas_none_volume_neumann.dat",  # surface + VOLUME Neumann loads with functions of space and time
     "solid_ele_hex8_Standard_fbar.dat",  # TECH fbar, MAT_ElastHyper with TWO summands: CoupNeoHooke + CoupAnisoExpo (FIBER1 on the element)
+    # SURVEY 8f F4 cell types (generic kernel): GenAlpha with surface loads on quad8 / tri3 / quad4 faces
+    "solid_ele_hex20_Standard_dynamic.dat",
+    "solid_ele_tet4_Standard_dynamic.dat",
+    "solid_ele_wedge6_Standard_dynamic.dat",
+    "solid_ele_pyramid5_Standard_dynamic.dat",
+    "solid_ele_pyramid5_Standard_fbar.dat",  # F-bar on pyramid5 + CoupAnisoExpo fibres, statics, surface + volume loads
+    "solid_ele_hex20_Standard_volume_neumann.dat",
+    "solid_ele_tet4_Standard_volume_neumann.dat",
+    "solid_ele_pyramid5_Standard_volume_neumann.dat",
 ]
 
 

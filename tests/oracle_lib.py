@@ -12,12 +12,12 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
-HEX8, HEX27, TET10 = 0, 1, 2
+HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
 FORM_DISP, FORM_FBAR = 0, 1
 MAT_SVK, MAT_NEOHOOKE = 0, 1
 ACTION_NLNSTIFF, ACTION_INTERNALFORCE = 0, 1
-NEN = {HEX8: 8, HEX27: 27, TET10: 10}
-NGP = {HEX8: 8, HEX27: 27, TET10: 4}
+NEN = {HEX8: 8, HEX27: 27, TET10: 10, HEX20: 20, TET4: 4, WEDGE6: 6, PYRAMID5: 5}
+NGP = {HEX8: 8, HEX27: 27, TET10: 4, HEX20: 27, TET4: 1, WEDGE6: 6, PYRAMID5: 8}
 
 _dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 _ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
@@ -132,8 +132,9 @@ def element_gp_stress(ct, form, kind, young, nue, X, u, stress_type=1):
     return err, out
 
 
-QUAD4, QUAD9, TRI6 = 0, 1, 2
-FACE_NEN = {QUAD4: 4, QUAD9: 9, TRI6: 6}
+QUAD4, QUAD9, TRI6, QUAD8, TRI3 = 0, 1, 2, 3, 4
+FACE_NEN = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 8, TRI3: 3}
+FACE_NGP = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 9, TRI3: 3}
 
 
 def surface_neumann(ft, x, onoff, val, functfac=None, want_coords=False):
@@ -141,7 +142,7 @@ def surface_neumann(ft, x, onoff, val, functfac=None, want_coords=False):
     x = _d(x)
     n, nn = x.shape[0], FACE_NEN[ft]
     fe = np.zeros((n, nn, 3))
-    gc = np.zeros((n, nn, 3)) if want_coords else None
+    gc = np.zeros((n, FACE_NGP[ft], 3)) if want_coords else None
     ff = _d(functfac) if functfac is not None else None
     lib.oracle_surface_neumann(C.c_int(ft), C.c_int(n), _p(x), _p(_i(onoff[:3])), _p(_d(val[:3])), _p(ff), _p(fe), _p(gc))
     return (fe, gc) if want_coords else fe

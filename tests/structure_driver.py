@@ -19,7 +19,16 @@ import os
 import numpy as np
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CT = {"HEX8": 0, "HEX27": 1, "TET10": 2}
+CT = {"HEX8": 0, "HEX27": 1, "TET10": 2, "HEX20": 3, "TET4": 4, "WEDGE6": 5, "PYRAMID5": 6}
+# faces of the SURVEY 8f F4 cell types as (face type, local nodes in the node order of the surface cell); face types
+# 0 quad4, 3 quad8, 4 tri3.  Node numbering of the faces: 4C_fem_general_utils_local_connectivity_matrices.hpp:51-86
+FACE_TABLES = {
+    3: [(3, f) for f in ([0, 3, 2, 1, 11, 10, 9, 8], [0, 1, 5, 4, 8, 13, 16, 12], [1, 2, 6, 5, 9, 14, 17, 13], [2, 3, 7, 6, 10, 15, 18, 14],
+                         [0, 4, 7, 3, 12, 19, 15, 11], [4, 5, 6, 7, 16, 17, 18, 19])],
+    4: [(4, f) for f in ([0, 1, 3], [1, 2, 3], [0, 3, 2], [0, 2, 1])],
+    5: [(4, [2, 1, 0]), (4, [3, 4, 5]), (0, [0, 1, 4, 3]), (0, [1, 2, 5, 4]), (0, [2, 0, 3, 5])],
+    6: [(0, [0, 3, 2, 1]), (4, [0, 1, 4]), (4, [1, 2, 4]), (4, [2, 3, 4]), (4, [0, 4, 3])],
+}
 
 
 def load(name):
@@ -94,6 +103,11 @@ class Problem:
             assert c["type"] == "Live" and not any(c["onoff"][3:])
             sset = {self.index[n] for n in fx["dsurf"][str(c["E"])]}
             for en in self.conn:
+                if self.ct in FACE_TABLES:
+                    for ft, loc in FACE_TABLES[self.ct]:
+                        if all(int(en[a]) in sset for a in loc):
+                            self.faces.append((c, en[loc], ft))  # already in the surface cell's node order
+                    continue
                 for loc, rs in self._element_faces():
                     if all(int(en[a]) in sset for a in loc):
                         self.faces.append((c, en[loc], rs))
@@ -103,6 +117,10 @@ class Problem:
         self.neumann = None  # backend with surface(), volume(), *_coords(); None = the numpy restatement below (surfaces only)
         self.face_lists, self.vol_lists = [], []
         for c in fx["neumann"]:
+            if self.ct in FACE_TABLES:
+                for ft in sorted({ft for cc, _, ft in self.faces if cc is c}):
+                    self.face_lists.append((c, ft, np.array([nodes for cc, nodes, f in self.faces if cc is c and f == ft], np.int32)))
+                continue
             fl = [self._ordered_face(nodes, rs) for cc, nodes, rs in self.faces if cc is c]
             self.face_lists.append((c, {4: 0, 9: 1, 6: 2}[len(fl[0])], np.array(fl, np.int32)))
         for c in fx.get("vol_neumann", []):
@@ -226,7 +244,7 @@ class Problem:
                 xg = self._gp_cache.setdefault(("v", i), nb.volume_coords(els))
                 nb.volume(els, c["onoff"], c["val"], self._factors(("v", i), c, xg, t), f)
             return f
-        assert not self.vol_lists, "the numpy restatement covers surface loads only"
+        assert not self.vol_lists and self.ct not in FACE_TABLES, "the numpy restatement covers surface loads of hex8 / hex27 / tet10 only"
         f = np.zeros((len(self.ids), 3))
         for c, nodes, rs in self.faces:
             P = self.X[nodes]

@@ -1,6 +1,7 @@
 """Solve-level golden vectors of the reference's own regression inputs (RESULT DESCRIPTION, TOLERANCE 1e-12),
 replayed with the mock structure driver on (a) the CPU oracle and (b) the CUDA library.  These pin the
-Neo-Hooke internal force of hex8 / hex27 / tet10 (and the consistent mass matrix for the GenAlpha cases)
+Neo-Hooke internal force of hex8 / hex27 / tet10 / hex20 / tet4 / wedge6 / pyramid5 (and the consistent mass matrix for the
+GenAlpha cases)
 against numbers produced by the reference itself.  Fixtures: tests/golden/*.json (made by make_golden.py)."""
 import numpy as np
 import pytest
@@ -17,6 +18,15 @@ CASES = [
     "solid_runtime_ghosting_output",  # 640 hex8 SVK (BASELINE config C1's mesh), reference = its runtime VTK output, 1e-8
     "solid_ele_hex8_Standard_eas_none_volume_neumann",  # surface + volume Neumann loads with FUNCT (x+1)(y+2)(z+3) and t
     "solid_ele_hex8_Standard_fbar",  # the reference's F-bar ELEMENT golden: MAT_ElastHyper = CoupNeoHooke + CoupAnisoExpo fibres
+    # SURVEY 8f F4 cell types on the generic kernel
+    "solid_ele_hex20_Standard_dynamic",
+    "solid_ele_tet4_Standard_dynamic",
+    "solid_ele_wedge6_Standard_dynamic",
+    "solid_ele_pyramid5_Standard_dynamic",
+    "solid_ele_pyramid5_Standard_fbar",
+    "solid_ele_hex20_Standard_volume_neumann",
+    "solid_ele_tet4_Standard_volume_neumann",
+    "solid_ele_pyramid5_Standard_volume_neumann",
 ]
 
 
@@ -117,7 +127,7 @@ def test_reference_result_description_cuda(fc, oracle, case):
     s.close()
 
 
-@pytest.mark.parametrize("case", [c for c in CASES if c not in ("solid_ele_hex8_Standard_eas_none_volume_neumann", "solid_ele_hex8_Standard_fbar")])
+@pytest.mark.parametrize("case", CASES[:8])  # the cases whose loads are surface loads on quad4 / quad9 / tri6 only
 def test_neumann_oracle_matches_numpy_restatement(oracle, case):
     """two independent restatements of the surface loads (oracle C++, structure_driver numpy) agree"""
     p = sd.Problem(sd.load(case), oracle.node_param_coords)

@@ -1,0 +1,126 @@
+"""SURVEY 8f F4 cell types (hex20, tet4, wedge6, pyramid5; pyramid5 also with F-bar) on the generic kernel: CUDA against the CPU
+oracle on the meshes of the reference's own element tests (tests/golden), with the nodes moved off their regular places so
+that no Jacobian is constant.  Element level (fe, Ke), assembled system, consistent mass and Neumann loads."""
+import numpy as np
+import pytest
+import structure_driver as sd
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-12
+DISP, FBAR = 0, 1
+SVK, NH = 0, 1
+
+CASES = [
+    ("solid_ele_hex20_Standard_dynamic", DISP, NH, 0.25),
+    ("solid_ele_hex20_Standard_dynamic", DISP, SVK, 0.3),
+    ("solid_ele_tet4_Standard_dynamic", DISP, NH, 0.25),
+    ("solid_ele_tet4_Standard_dynamic", DISP, SVK, 0.3),
+    ("solid_ele_wedge6_Standard_dynamic", DISP, NH, 0.25),
+    ("solid_ele_pyramid5_Standard_dynamic", DISP, NH, 0.25),
+    ("solid_ele_pyramid5_Standard_dynamic", FBAR, NH, 0.45),
+    ("solid_ele_pyramid5_Standard_dynamic", FBAR, SVK, 0.3),
+]
+
+
+def distorted(oracle, name):
+    p = sd.Problem(sd.load(name), oracle.node_param_coords)
+    rng = np.random.default_rng(11)
+    X = p.X + 0.04 * (rng.random(p.X.shape) - 0.5)
+    u = 0.05 * (rng.random(p.X.shape) - 0.5) + 0.03 * X * X[:, ::-1]
+    return p, X, u
+
+
+@pytest.mark.parametrize("name,form,mat,nue", CASES)
+def test_element_and_assembly_parity(fc, oracle, name, form, mat, nue):
+    p, X, u = distorted(oracle, name)
+    ct, conn = p.ct, p.conn
+    s = fc.Solid(0)
+    s.set_mesh(ct, form, X, p.node_gid, np.zeros(len(X), np.int32), conn, p.ele_gid)
+    s.set_material(mat, 10.0, nue)
+    n_row, n_col, nnz = s.build_graph()
+    bad, fe_ref, Ke_ref = oracle.element_evaluate_batch(ct, form, mat, 10.0, nue, X[conn], u[conn])
+    assert bad == 0
+    fe, Ke = s.evaluate_elements(np.ascontiguousarray(u.reshape(-1)), want_K=True)
+    for e in range(len(conn)):
+        kr, fr = Ke_ref[e], fe_ref[e]
+        assert np.max(np.abs(Ke[e] - kr)) <= TOL * np.max(np.abs(kr)), (e, np.max(np.abs(Ke[e] - kr)) / np.max(np.abs(kr)))
+        assert np.max(np.abs(fe[e] - fr)) <= TOL * max(np.max(np.abs(fr)), np.max(np.abs(kr))), e
+    # assembled system against the oracle's owner-row assembly, and the residual-only action
+    job = oracle.Job.from_mesh(ct, p.node_gid, X, p.ele_gid, p.node_gid[conn])
+    job.set_problem(form, mat, 10.0, nue)
+    o = job.rank(0)
+    job.set_u_nodal(u)
+    assert job.evaluate(oracle.ACTION_NLNSTIFF)[0] == 0
+    f_ref, K_ref = job.get_f(0, n_row), job.get_K(0, o["nnz"])
+    rowptr, colind = s.get_graph()
+    assert nnz == o["nnz"] and np.array_equal(rowptr, o["rowptr"]) and np.array_equal(colind, o["colind"])
+    K, f = np.zeros(nnz), np.zeros(n_row)
+    assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u.reshape(-1), f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+    starts = np.asarray(rowptr[:-1], np.int64)
+    rmax = np.maximum.reduceat(np.abs(K_ref), starts)
+    emax = np.maximum.reduceat(np.abs(K - K_ref), starts)
+    assert np.max(emax / rmax) <= TOL
+    assert np.max(np.abs(f - f_ref)) <= TOL * max(np.max(np.abs(f_ref)), np.max(np.abs(K_ref)))
+    f2 = np.zeros(n_row)
+    assert s.evaluate(fc.FC_ACTION_INTERNALFORCE, u.reshape(-1), f2, None, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+    assert np.max(np.abs(f2 - f)) <= 1e-14 * np.max(np.abs(f))
+    s.close()
+
+
+@pytest.mark.parametrize("name", ["solid_ele_hex20_Standard_dynamic", "solid_ele_tet4_Standard_dynamic", "solid_ele_wedge6_Standard_dynamic",
+                                  "solid_ele_pyramid5_Standard_dynamic"])
+def test_mass_and_neumann_parity(fc, oracle, name):
+    p, X, _ = distorted(oracle, name)
+    ct, conn = p.ct, p.conn
+    s = fc.Solid(0)
+    s.set_mesh(ct, DISP, X, p.node_gid, np.zeros(len(X), np.int32), conn, p.ele_gid)
+    s.set_material(NH, 10.0, 0.25)
+    n_row, n_col, nnz = s.build_graph()
+    rowptr, colind = s.get_graph()
+    # consistent mass (tet4: tet_4point, the others their stiffness rule)
+    rho = 0.37
+    M = np.zeros(nnz)
+    s.evaluate_mass(rho, M)
+    Mo = np.zeros((n_row, n_row))
+    for en in conn:
+        err, _, _, Me = oracle.element_evaluate(ct, 0, 1, 10.0, 0.25, X[en], np.zeros((len(en), 3)), want_K=False, want_M=True, rho=rho)
+        assert err == 0
+        dofs = (3 * en[:, None] + np.arange(3)).reshape(-1)
+        Mo[np.ix_(dofs, dofs)] += Me
+    assert np.max(np.abs(sd.csr_to_dense(rowptr, colind, M, n_row) - Mo)) <= 1e-13 * np.max(np.abs(Mo))
+    # volume loads on every second element, surface loads on the loaded faces of the reference's input (quad8 / tri3 / quad4)
+    rng = np.random.default_rng(3)
+    els = np.arange(len(conn), dtype=np.int32)[::2]
+    xg = s.neumann_volume_gp_coords(els)
+    fac = 1.0 + rng.random(xg.shape)
+    fe_ref, xg_ref = oracle.volume_neumann(ct, X[conn[els]], [1, 0, 1], [2.0, 9.0, -0.5], fac, want_coords=True)
+    assert np.max(np.abs(xg - xg_ref)) <= 1e-14
+    f_ref = np.full(n_row, 0.125)
+    np.add.at(f_ref.reshape(-1, 3), conn[els], fe_ref)
+    f = np.full(n_row, 0.125)
+    s.neumann_volume(els, [1, 0, 1], [2.0, 9.0, -0.5], f, gp_factor=fac)
+    assert np.max(np.abs(f - f_ref)) <= 1e-14 * np.max(np.abs(f_ref))
+    assert p.face_lists
+    for c, ft, faces in p.face_lists:
+        xs = s.neumann_surface_gp_coords(ft, faces)
+        fac = 1.0 + rng.random(xs.shape)
+        fs_ref, xs_ref = oracle.surface_neumann(ft, X[faces], [1, 1, 1], [1.0, -2.0, 0.3], fac, want_coords=True)
+        assert np.max(np.abs(xs - xs_ref)) <= 1e-14
+        f_ref = np.zeros(n_row)
+        np.add.at(f_ref.reshape(-1, 3), faces, fs_ref)
+        f = np.zeros(n_row)
+        s.neumann_surface(ft, faces, [1, 1, 1], [1.0, -2.0, 0.3], f, gp_factor=fac)
+        assert np.max(np.abs(f - f_ref)) <= 1e-14 * np.max(np.abs(f_ref))
+    s.close()
+
+
+def test_stress_output_is_refused_for_the_new_cell_types(fc, oracle):
+    p, X, u = distorted(oracle, "solid_ele_tet4_Standard_dynamic")
+    s = fc.Solid(0)
+    s.set_mesh(p.ct, DISP, X, p.node_gid, np.zeros(len(X), np.int32), p.conn, p.ele_gid)
+    s.set_material(NH, 10.0, 0.25)
+    s.build_graph()
+    with pytest.raises(fc.FourCError) as ei:
+        s.evaluate_stress(u.reshape(-1))
+    assert ei.value.code == fc.FC_ERR_UNSUPPORTED
+    s.close()

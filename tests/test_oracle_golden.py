@@ -101,16 +101,20 @@ def test_coupneohooke_against_closed_form():
 
 
 def test_gauss_rules_and_partition_of_unity():
-    for ct, vol in ((O.HEX8, 8.0), (O.HEX27, 8.0), (O.TET10, 1.0 / 6.0)):
+    for ct, vol in ((O.HEX8, 8.0), (O.HEX27, 8.0), (O.TET10, 1.0 / 6.0), (O.HEX20, 8.0), (O.TET4, 1.0 / 6.0), (O.WEDGE6, 1.0), (O.PYRAMID5, 4.0 / 3.0)):
         n, g = O.NEN[ct], O.NGP[ct]
         xi, w = np.zeros(3 * g), np.zeros(g)
         L.oracle_gauss_rule(C.c_int(ct), p(xi), p(w))
-        assert abs(w.sum() - vol) < (1e-11 if ct == O.HEX27 else 1e-14)  # hex27 constants are truncated in the reference
+        # the hex27 / pyramid constants are truncated in the reference
+        assert abs(w.sum() - vol) < (1e-11 if ct in (O.HEX27, O.HEX20, O.PYRAMID5) else 1e-14)
         for q in range(g):
             N, dN = np.zeros(n), np.zeros(3 * n)
             L.oracle_shape(C.c_int(ct), p(np.ascontiguousarray(xi[3 * q:3 * q + 3])), p(N), p(dN))
             assert abs(N.sum() - 1) < 1e-14 and np.abs(dN.reshape(n, 3).sum(0)).max() < 1e-13
-        # Kronecker property at the nodes
+        # Kronecker property at the nodes (the reference's "node" points of wedge6 are the first six of the wedge18 table,
+        # not the places where the wedge6 functions are 1: 4C_fem_general_utils_local_connectivity_matrices.hpp:564-575)
+        if ct == O.WEDGE6:
+            continue
         xn = np.zeros(3 * n)
         L.oracle_node_param_coords(C.c_int(ct), p(xn))
         for a in range(n):

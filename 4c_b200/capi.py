@@ -17,7 +17,7 @@ FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_SUMMAND_COUPNEOHOOKE, FC_SUMMAND_COUPSVK, FC_SUMMAND_COUPANISOEXPO = 0, 1, 2
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
-FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_OWNER_COMPUTED = 1, 2, 4, 8
+FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_OWNER_COMPUTED, FC_EVAL_DMMA_TILES = 1, 2, 4, 8, 16
 FC_EVAL_INTERIOR, FC_EVAL_BOUNDARY = 32, 64
 FC_STRESS_2PK, FC_STRESS_CAUCHY = 0, 1
 FC_FACE_QUAD4, FC_FACE_QUAD9, FC_FACE_TRI6, FC_FACE_QUAD8, FC_FACE_TRI3 = 0, 1, 2, 3, 4

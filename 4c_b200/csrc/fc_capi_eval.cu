@@ -14,6 +14,7 @@
 #include "fc_kernels_hex8_mma_ext.cuh"
 #include "fc_kernels_nh_mma_gen.cuh"
 #include "fc_kernels_setup.cuh"
+#include "fc_kernels_tet10nh.cuh"
 
 int fc_build_brick_plan(fc_ctx* ctx);  // fc_capi_graph.cu
 
@@ -127,6 +128,28 @@ namespace
     return cudaGetLastError();
   }
 
+  // tet10 Neo-Hooke, one warp per element
+  template <bool WANT_K>
+  cudaError_t launch_tet10_nh(fc_ctx* ctx, const fc::EvalArgs& A)
+  {
+    using Cfg = fc::Tet10NhCfg;
+    if (!ctx->d_geom)  // geometry cache: once per mesh
+    {
+      cudaError_t eg = cudaMalloc((void**)&ctx->d_geom, sizeof(double) * Cfg::geom_doubles * (size_t)ctx->n_ele);
+      if (eg != cudaSuccess) return eg;
+      fc::k_tet10_geom_cache<<<(ctx->n_ele + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->n_ele, ctx->d_dNtab, ctx->d_gpw, ctx->d_geom);
+      ctx->launches++;
+    }
+    fc::EvalArgs Ag = A;
+    Ag.geom = ctx->d_geom;
+    const bool ele_out = A.Ke_out || A.fe_out;
+    auto kern = ele_out ? (A.dbc ? fc::k_tet10_nh<WANT_K, true, true> : fc::k_tet10_nh<WANT_K, false, true>)
+                        : (A.dbc ? fc::k_tet10_nh<WANT_K, true, false> : fc::k_tet10_nh<WANT_K, false, false>);
+    kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, 0, ctx->stream>>>(Ag, ctx->d_ele_bad);
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
   // true if dispatch() picks a kernel that visits the elements through EvalArgs::ele_perm and the launch-slot range
   bool follows_launch_order(const fc_ctx* ctx, int flags)
   {
@@ -156,6 +179,7 @@ namespace
       return fbar ? launch_generic<fc::PYRAMID5, fc::FORM_FBAR, WANT_K>(ctx, A) : launch_generic<fc::PYRAMID5, fc::FORM_DISP, WANT_K>(ctx, A);
     const bool nh_gen = ctx->mat.kind == fc::MAT_NEOHOOKE && !fbar && !(flags & FC_EVAL_FORCE_GENERIC);
     if (ctx->celltype == FC_HEX27) return nh_gen ? launch_nh_gen<fc::HEX27, WANT_K>(ctx, A) : launch_generic<fc::HEX27, fc::FORM_DISP, WANT_K>(ctx, A);
+    if (nh_gen && !(flags & FC_EVAL_DMMA_TILES)) return launch_tet10_nh<WANT_K>(ctx, A);
     return nh_gen ? launch_nh_gen<fc::TET10, WANT_K>(ctx, A) : launch_generic<fc::TET10, fc::FORM_DISP, WANT_K>(ctx, A);
   }
 

@@ -272,6 +272,7 @@ def main():
         ("C3a-96 hex27 NeoHooke 96^3", H27, D, NH, 0.25, (96, 96, 96), 0),
         ("C3a-full hex27 NeoHooke 126^3 (K values 74.6 GB)", H27, D, NH, 0.25, (126, 126, 126), 0),
         ("C3b tet10 NeoHooke 70^3x6", T10, D, NH, 0.25, (70, 70, 70), 0),
+        ("C3b tet10 NeoHooke 70^3x6 (tensor-core tiles)", T10, D, NH, 0.25, (70, 70, 70), fc.FC_EVAL_DMMA_TILES),
         ("C4s hex8 F-bar NeoHooke nu=0.499 100^3", H8, FB, NH, 0.499, (100, 100, 100), 0),
         ("C4 hex8 F-bar NeoHooke nu=0.499 200^3", H8, FB, NH, 0.499, (200, 200, 200), 0),
         ("C5/8 hex8 NeoHooke 200^3 (one GPU's share of 400^3)", H8, D, NH, 0.25, (200, 200, 200), 0),
@@ -284,8 +285,9 @@ def main():
         mg = args.only.startswith("newtonmg")
         run_newton(fc, int(args.only[8 if mg else 6:] or 100), args.steps, fc.FC_SOLVER_CG_MG if mg else None, args.mg_sweeps)
         return
+    exact = any(c[0] == args.only for c in cfgs)  # a full config name selects that config alone
     for c in cfgs:
-        if args.only and args.only not in c[0]:
+        if args.only and (c[0] != args.only if exact else args.only not in c[0]):
             continue
         if not args.only and ("C3a-96" in c[0] or "C3a-full" in c[0]):
             continue  # large hex27 cases only on request

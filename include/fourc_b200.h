@@ -93,6 +93,8 @@ extern "C"
                              bit-identical from run to run, 2.8 GB instead of 6.6 GB of DRAM traffic per evaluation at C2 -
                              but 1.9x slower than memset + per-element reductions on B200, so opt-in.
                              Ignored (per-element reductions) where the mesh has no brick plan */
+    FC_EVAL_DMMA_TILES = 16, /* tet10 Neo-Hooke: the padded tensor-core tile kernel (k_nh_mma_gen) instead of the default
+                                warp-per-element FMA kernel (k_tet10_nh) (comparison) */
     FC_EVAL_INTERIOR = 32, /* numproc > 1: only the elements without ghost nodes (they need no halo import: evaluate them while
                               fc_solid_halo_exchange is in flight on another stream) ... */
     FC_EVAL_BOUNDARY = 64 /* ... then only the elements with ghost nodes, after the import; without FC_EVAL_ZERO_FIRST (the

@@ -81,7 +81,9 @@ def kernel_variants(fc, ct, form, mat):
         return [0, fc.FC_EVAL_OWNER_COMPUTED, fc.FC_EVAL_CLOSED_FORM_FMA, fc.FC_EVAL_FORCE_GENERIC]
     if ct == HEX8 and ((form == FBAR and mat == NH) or (form == DISP and mat == SVK)):
         return [0, fc.FC_EVAL_FORCE_GENERIC]  # tensor-core closed form (k_hex8_mma_ext), generic
-    if ct in (HEX27, TET10) and form == DISP and mat == NH:
+    if ct == TET10 and form == DISP and mat == NH:
+        return [0, fc.FC_EVAL_DMMA_TILES, fc.FC_EVAL_FORCE_GENERIC]  # warp-per-element closed form (k_tet10_nh), tensor-core tiles, generic
+    if ct == HEX27 and form == DISP and mat == NH:
         return [0, fc.FC_EVAL_FORCE_GENERIC]  # tensor-core closed form (k_nh_mma_gen), generic
     return [0]
 

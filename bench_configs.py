@@ -285,9 +285,10 @@ def main():
         mg = args.only.startswith("newtonmg")
         run_newton(fc, int(args.only[8 if mg else 6:] or 100), args.steps, fc.FC_SOLVER_CG_MG if mg else None, args.mg_sweeps)
         return
-    exact = any(c[0] == args.only for c in cfgs)  # a full config name selects that config alone
+    names = args.only.split("|") if args.only else []
+    exact = any(c[0] in names for c in cfgs)  # full config names (separated by |) select exactly those configs
     for c in cfgs:
-        if args.only and (c[0] != args.only if exact else args.only not in c[0]):
+        if args.only and (c[0] not in names if exact else args.only not in c[0]):
             continue
         if not args.only and ("C3a-96" in c[0] or "C3a-full" in c[0]):
             continue  # large hex27 cases only on request

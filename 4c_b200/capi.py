@@ -40,7 +40,7 @@ EXPORTS = [
     "fc_solid_last_kernel_ms", "fc_solid_kernel_ms_history", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
     "fc_grid_halo_counts", "fc_grid_halo_send_nodes", "fc_probe_fp64_fma", "fc_probe_fp64_mma",
-    "fc_solid_set_comm", "fc_solid_set_dirichlet_toggle", "fc_solid_apply_dirichlet", "fc_solid_apply_dirichlet_to_system", "fc_solid_spmv", "fc_solid_linear_solve", "fc_solid_mg_setup", "fc_solid_mg_update", "fc_solid_mg_set_sweeps", "fc_solid_mg_level_info",
+    "fc_solid_set_comm", "fc_solid_set_dirichlet_toggle", "fc_solid_apply_dirichlet", "fc_solid_apply_dirichlet_to_system", "fc_solid_spmv", "fc_solid_linear_solve", "fc_solid_mg_setup", "fc_solid_mg_update", "fc_solid_mg_set_sweeps", "fc_solid_mg_set_precision", "fc_solid_mg_set_damping", "fc_solid_mg_level_info",
     "fc_l2_sweep_order", "fc_brick_plan_create", "fc_brick_plan_sizes", "fc_brick_plan_get", "fc_brick_plan_destroy",
 ]
 
@@ -311,6 +311,12 @@ class Solid:
 
     def mg_set_sweeps(self, nu):
         self._chk(lib().fc_solid_mg_set_sweeps(self.h, C.c_int(nu)))
+
+    def mg_set_precision(self, single_precision_cycle):
+        self._chk(lib().fc_solid_mg_set_precision(self.h, C.c_int(1 if single_precision_cycle else 0)))
+
+    def mg_set_damping(self, factor):
+        self._chk(lib().fc_solid_mg_set_damping(self.h, C.c_double(factor)))
 
     def mg_level_info(self, level):
         """(nodes, Jacobi damping) of one multigrid level, 0 = finest"""

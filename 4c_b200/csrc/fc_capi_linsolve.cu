@@ -13,6 +13,7 @@
 
 int fc_allreduce_sum(fc_ctx* ctx, double* buf_dev, int n);  // fc_capi_halo.cu
 int fc_mg_vcycle(fc_ctx* ctx, const double* K, const double* r, double* z);  // fc_capi_mg.cu
+void fc_mg_scale_damping(fc_ctx* ctx, double f);                               // fc_capi_mg.cu
 
 namespace
 {
@@ -181,16 +182,29 @@ extern "C"
       if (int rc = dots(ctx, n, r, r, nullptr, nullptr, nullptr, nullptr, d)) return rc;
       relres = std::sqrt(d[0]) / bnorm;
       double rz = 0.0;
+      bool restart = true;  // the next direction is the preconditioned residual itself
+      int damping_cuts = 0;
       while (relres > rel_tol && it < max_iter)
       {
         if (int rc = fc_mg_vcycle(ctx, K_values, r, z)) return finish(rc);
         if (int rc = dots(ctx, n, r, z, nullptr, nullptr, nullptr, nullptr, d)) return rc;
         const double rz_new = d[0];
-        if (!(rz_new > 0.0) || !std::isfinite(rz_new)) return finish(fail(ctx, FC_ERR_SOLVER, "CG-MG breakdown: r.z <= 0 (preconditioner or matrix not positive definite on the free DOFs)"));
-        if (it == 0)
+        if (!(rz_new > 0.0) || !std::isfinite(rz_new))
+        {
+          // an indefinite cycle: the Jacobi damping of some level exceeds 2 / lambda_max (the estimate is a lower bound).
+          // Cut the damping of every level and restart CG from the current iterate, a few times.
+          if (damping_cuts == 4)
+            return finish(fail(ctx, FC_ERR_SOLVER, "CG-MG breakdown: r.z <= 0 (preconditioner or matrix not positive definite on the free DOFs)"));
+          fc_mg_scale_damping(ctx, 0.7);
+          ++damping_cuts;
+          restart = true;
+          continue;
+        }
+        if (restart)
           FC_CUDA(cudaMemcpyAsync(p, z, sizeof(double) * (size_t)n, cudaMemcpyDeviceToDevice, ctx->stream));
         else
           axpby(ctx, n, 1.0, z, rz_new / rz, p);
+        restart = false;
         rz = rz_new;
         spmv(ctx, K_values, p, Ap);
         if (int rc = dots(ctx, n, p, Ap, nullptr, nullptr, nullptr, nullptr, d)) return rc;

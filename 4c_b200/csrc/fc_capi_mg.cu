@@ -27,6 +27,11 @@ void fc_mg_free(fc_ctx* ctx)
     dev_free(L.d_b);
     dev_free(L.d_x);
     dev_free(L.d_y);
+    dev_free(L.d_ev);
+    dev_free(L.d_K32);
+    dev_free(L.d_Ainv);
+    L.have_Ainv = false;
+    L.have_ev = false;
     dev_free(L.d_r);
     dev_free(L.d_u);
     if (L.c) fc_solid_destroy(L.c);
@@ -38,8 +43,10 @@ void fc_mg_free(fc_ctx* ctx)
 
 namespace
 {
-  constexpr int mg_nu_coarsest = 60;
-  constexpr int mg_power_iterations = 6;
+  constexpr int mg_nu_coarsest = 60;          // Jacobi sweeps on a coarsest level too large for the dense inverse
+  constexpr int mg_dense_max_dof = 600;       // coarsest level: direct solve up to this many DOFs (2.9 MB of inverse)
+  constexpr int mg_power_iterations = 8;       // first estimate of a level, from a random-sign start
+  constexpr int mg_power_iterations_warm = 2;  // later estimates start from the previous iterate
   inline int fine_of(int I, int ne) { return std::min(2 * I, ne); }  // fine index of coarse node I on an axis with ne fine elements
 
   fc::MgLattice lattice_of(const fc_mg_level& L) { return fc::MgLattice{L.nn[0], L.nn[1], L.nn[2], L.d_lat2lid, L.d_lat}; }
@@ -50,6 +57,7 @@ namespace
     const size_t n3 = 3 * (size_t)L.n_nodes;
     FC_CUDA(cudaMalloc((void**)&L.d_x, n3 * sizeof(double)));
     FC_CUDA(cudaMalloc((void**)&L.d_y, n3 * sizeof(double)));
+    FC_CUDA(cudaMalloc((void**)&L.d_ev, n3 * sizeof(double)));
     FC_CUDA(cudaMalloc((void**)&L.d_r, n3 * sizeof(double)));
     FC_CUDA(cudaMalloc((void**)&L.d_free, n3));
     if (coarse)
@@ -69,11 +77,42 @@ namespace
     return FC_OK;
   }
 
-  void smooth(fc_ctx* ctx, const fc_ctx* g, const double* K, const double* Dinv, double omega, const double* b, const double* x_in, double* x_out)
+  // the tangent of a level as the cycle reads it: FP64 values or their single-precision copy
+  struct LevelMatrix
+  {
+    const double* K64;
+    const float* K32;  // used when not null
+  };
+
+  void smooth(fc_ctx* ctx, const fc_ctx* g, LevelMatrix M, const double* Dinv, double omega, const double* b, const double* x_in, double* x_out)
   {
     const int bs = 128;
-    fc::k_mg_smooth<<<grid_for(32LL * g->n_row_nodes, bs), bs, 0, ctx->stream>>>(g->d_nodeptr, g->d_nodeadj, g->n_row_nodes, K, Dinv, omega, b, x_in, x_out);
+    const unsigned gs = grid_for(32LL * g->n_row_nodes, bs);
+    if (M.K32)
+      fc::k_mg_smooth<float><<<gs, bs, 0, ctx->stream>>>(g->d_nodeptr, g->d_nodeadj, g->n_row_nodes, M.K32, Dinv, omega, b, x_in, x_out);
+    else
+      fc::k_mg_smooth<double><<<gs, bs, 0, ctx->stream>>>(g->d_nodeptr, g->d_nodeadj, g->n_row_nodes, M.K64, Dinv, omega, b, x_in, x_out);
     ctx->launches++;
+  }
+
+  // (re)fill the single-precision copy of a level's tangent; returns what the cycle reads
+  int level_matrix(fc_ctx* ctx, fc_mg_level& L, const double* K, long long nnz, bool refresh, LevelMatrix* M)
+  {
+    M->K64 = K;
+    M->K32 = nullptr;
+    if (!ctx->mg_fp32) return FC_OK;
+    if (!L.d_K32)
+    {
+      FC_CUDA(cudaMalloc((void**)&L.d_K32, sizeof(float) * (size_t)nnz));
+      refresh = true;
+    }
+    if (refresh)
+    {
+      fc::k_mg_to_float<<<grid_for(nnz, 256), 256, 0, ctx->stream>>>(nnz, K, L.d_K32);
+      ctx->launches++;
+    }
+    M->K32 = L.d_K32;
+    return FC_OK;
   }
 
   // |v|_2 of a device vector (deterministic block partials, one read-back)
@@ -93,27 +132,47 @@ namespace
   // Jacobi damping of a level from lambda_max(D^-1 K), a few power iterations on I + D^-1 K (its largest eigenvalue is
   // 1 + lambda_max; the eigenvalues of D^-1 K are real and positive).  Stretched elements push lambda_max past the
   // 2 / omega of a fixed damping, and the smoother then diverges.
-  int estimate_omega(fc_ctx* ctx, fc_mg_level& L, const fc_ctx* g, const double* K, const double* Dinv)
+  int estimate_omega(fc_ctx* ctx, fc_mg_level& L, const fc_ctx* g, LevelMatrix K, const double* Dinv)
   {
     const int n3 = 3 * L.n_nodes, bs = 256;
     FC_CUDA(cudaMemsetAsync(L.d_r, 0, sizeof(double) * (size_t)n3, ctx->stream));
-    fc::k_mg_seed<<<grid_for(n3, bs), bs, 0, ctx->stream>>>(n3, L.d_free, L.d_x);
-    ctx->launches++;
+    // start: the previous estimate's iterate (the tangent of the next Newton iteration has nearly the same dominant
+    // eigenvector: two iterations then do what eight do from a random start), zero on the fixed DOFs either way
+    const int iterations = L.have_ev ? mg_power_iterations_warm : mg_power_iterations;
+    if (L.have_ev)
+      FC_CUDA(cudaMemcpyAsync(L.d_x, L.d_ev, sizeof(double) * (size_t)n3, cudaMemcpyDeviceToDevice, ctx->stream));
+    else
+    {
+      fc::k_mg_seed<<<grid_for(n3, bs), bs, 0, ctx->stream>>>(n3, L.d_free, L.d_x);
+      ctx->launches++;
+    }
     // no normalisation in between: the iterate grows by at most (1 + lambda_max)^iterations, far from overflow,
     // and the host then waits for two norms per level instead of one per iteration
     double *cur = L.d_x, *oth = L.d_y;
     double n_prev = 0.0, n_last = 0.0, lambda = 2.0;
-    for (int it = 0; it < mg_power_iterations; ++it)
+    for (int it = 0; it < iterations; ++it)
     {
-      if (it == mg_power_iterations - 1)
+      if (it == iterations - 1)
         if (int rc = norm2(ctx, n3, cur, &n_prev)) return rc;
       smooth(ctx, g, K, Dinv, -1.0, L.d_r, cur, oth);  // oth = (I + D^-1 K) cur
       std::swap(cur, oth);
     }
     if (int rc = norm2(ctx, n3, cur, &n_last)) return rc;
     if (n_prev > 0.0) lambda = n_last / n_prev - 1.0;
-    if (!(lambda > 0.5) || !std::isfinite(lambda)) lambda = 2.0;
-    L.omega = 4.0 / (3.0 * 1.1 * lambda);  // 10 % margin: the power iteration approaches lambda_max from below
+    if (!(lambda > 0.5) || !std::isfinite(lambda) || !(n_last > 0.0))
+    {
+      lambda = 2.0;
+      L.have_ev = false;
+    }
+    else
+    {
+      fc::k_mg_scale_copy<<<grid_for(n3, bs), bs, 0, ctx->stream>>>(n3, 1.0 / n_last, cur, L.d_ev);
+      ctx->launches++;
+      L.have_ev = true;
+    }
+    // default 4/3.  The power iteration approaches lambda_max from below (measured at C2: the estimate is at least 15 % low), so
+    // omega can exceed 2 / lambda_max on a level; CG-MG then sees r.z <= 0, cuts the damping and restarts (fc_capi_linsolve.cu)
+    L.omega = ctx->mg_damping / lambda;
     return FC_OK;
   }
 }  // namespace
@@ -235,6 +294,22 @@ extern "C"
     return FC_OK;
   }
 
+  int fc_solid_mg_set_damping(fc_ctx* ctx, double factor)
+  {
+    if (!ctx || !(factor > 0.0) || !(factor < 2.0)) return FC_ERR_INVALID;
+    ctx->mg_damping = factor;
+    ctx->mg_operators_ready = false;
+    return FC_OK;
+  }
+
+  int fc_solid_mg_set_precision(fc_ctx* ctx, int single_precision_cycle)
+  {
+    if (!ctx) return FC_ERR_INVALID;
+    ctx->mg_fp32 = single_precision_cycle != 0;
+    ctx->mg_operators_ready = false;  // the copies are (re)made by fc_solid_mg_update
+    return FC_OK;
+  }
+
   int fc_solid_mg_level_info(fc_ctx* ctx, int level, int* n_nodes, double* omega)
   {
     if (!ctx || level < 0 || level >= (int)ctx->mg.size()) return FC_ERR_INVALID;
@@ -276,7 +351,11 @@ extern "C"
             }
         if (int rc = fc_solid_set_dirichlet_toggle(C.c, (int)rows.size(), rows.data())) return fail(ctx, rc, "coarse level: " + C.c->last_error);
       }
-      for (fc_mg_level& L : ctx->mg) FC_CUDA(cudaMemcpyAsync(L.d_free, L.h_free.data(), L.h_free.size(), cudaMemcpyHostToDevice, ctx->stream));
+      for (fc_mg_level& L : ctx->mg)
+      {
+        FC_CUDA(cudaMemcpyAsync(L.d_free, L.h_free.data(), L.h_free.size(), cudaMemcpyHostToDevice, ctx->stream));
+        L.have_ev = false;  // the stored iterate is zero on the DOFs that were fixed before
+      }
       FC_CUDA(cudaStreamSynchronize(ctx->stream));
       ctx->mg_toggle_version = ctx->toggle_version;
     }
@@ -300,8 +379,28 @@ extern "C"
       if (rc != FC_OK) return fail(ctx, rc, "coarse level: " + C.c->last_error);
       fc::k_block_jacobi_setup<<<grid_for(C.n_nodes, bs), bs, 0, ctx->stream>>>(C.c->d_nodeptr, C.c->d_node_diagpos, C.n_nodes, C.d_K, C.d_Dinv);
       ctx->launches++;
-      if (int r2 = estimate_omega(ctx, C, C.c, C.d_K, C.d_Dinv)) return r2;
+      LevelMatrix Mc;
+      if (int r2 = level_matrix(ctx, C, C.d_K, C.c->nnz, true, &Mc)) return r2;
+      if (int r2 = estimate_omega(ctx, C, C.c, Mc, C.d_Dinv)) return r2;
       u_f = C.d_u;
+    }
+    {
+      // coarsest level: its inverse replaces the sweeps (one launch instead of sixty per cycle) when the level is small
+      fc_mg_level& Cl = ctx->mg.back();
+      const int n = 3 * Cl.n_nodes;
+      Cl.have_Ainv = false;
+      if (n <= mg_dense_max_dof)
+      {
+        if (!Cl.d_Ainv) FC_CUDA(cudaMalloc((void**)&Cl.d_Ainv, sizeof(double) * ((size_t)n * n + 1)));  // + the pivot flag
+        int* d_ok = reinterpret_cast<int*>(Cl.d_Ainv + (size_t)n * n);
+        fc::k_mg_dense_fill<<<1, 512, 0, ctx->stream>>>(Cl.c->d_nodeptr, Cl.c->d_nodeadj, Cl.n_nodes, Cl.d_K, Cl.d_Ainv);
+        fc::k_mg_dense_invert<<<1, 1024, 0, ctx->stream>>>(n, Cl.d_Ainv, d_ok);
+        ctx->launches += 2;
+        int ok = 0;
+        FC_CUDA(cudaMemcpyAsync(&ok, d_ok, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        FC_CUDA(cudaStreamSynchronize(ctx->stream));
+        Cl.have_Ainv = ok != 0;
+      }
     }
     FC_CUDA(cudaGetLastError());
     ctx->mg_operators_ready = true;
@@ -310,15 +409,23 @@ extern "C"
   }
 }
 
+// omega *= f on every level (the solver's answer to an indefinite cycle); holds until the next fc_solid_mg_update
+void fc_mg_scale_damping(fc_ctx* ctx, double f)
+{
+  for (fc_mg_level& L : ctx->mg) L.omega *= f;
+}
+
 // z = M r: one V(nu, nu) cycle; K = the fine tangent (Dirichlet applied), ctx->d_Dinv = its inverse diagonal blocks
 int fc_mg_vcycle(fc_ctx* ctx, const double* K, const double* r, double* z)
 {
   const int nlev = (int)ctx->mg.size();
   const int bs = 256;
+  // the fine tangent and its diagonal blocks are the caller's: known at the first cycle of a solve
+  LevelMatrix M0;
+  if (int rc = level_matrix(ctx, ctx->mg[0], K, ctx->nnz, ctx->mg_fine_omega_stale, &M0)) return rc;
   if (ctx->mg_fine_omega_stale)
   {
-    // the fine tangent and its diagonal blocks are the caller's: known at the first cycle of a solve
-    if (int rc = estimate_omega(ctx, ctx->mg[0], ctx, K, ctx->d_Dinv)) return rc;
+    if (int rc = estimate_omega(ctx, ctx->mg[0], ctx, M0, ctx->d_Dinv)) return rc;
     ctx->mg_fine_omega_stale = false;
   }
   // down
@@ -326,10 +433,17 @@ int fc_mg_vcycle(fc_ctx* ctx, const double* K, const double* r, double* z)
   {
     fc_mg_level& L = ctx->mg[l];
     const fc_ctx* g = l == 0 ? ctx : L.c;
-    const double* Kl = l == 0 ? K : L.d_K;
+    const LevelMatrix Kl = l == 0 ? M0 : LevelMatrix{L.d_K, ctx->mg_fp32 ? L.d_K32 : nullptr};
     const double* Di = l == 0 ? ctx->d_Dinv : L.d_Dinv;
     const double* b = l == 0 ? r : L.d_b;
     const int mg_nu = ctx->mg_nu;
+    if (l == nlev - 1 && L.have_Ainv)
+    {
+      const int n = 3 * L.n_nodes;
+      fc::k_mg_dense_apply<<<grid_for(32LL * n, 128), 128, 0, ctx->stream>>>(n, L.d_Ainv, b, L.d_x);
+      ctx->launches++;
+      break;
+    }
     const int sweeps = l == nlev - 1 ? mg_nu_coarsest : mg_nu;
     double *cur = L.d_x, *oth = L.d_y;
     smooth(ctx, g, Kl, Di, L.omega, b, nullptr, cur);
@@ -350,7 +464,7 @@ int fc_mg_vcycle(fc_ctx* ctx, const double* K, const double* r, double* z)
   {
     fc_mg_level &L = ctx->mg[l], &C = ctx->mg[l + 1];
     const fc_ctx* g = l == 0 ? ctx : L.c;
-    const double* Kl = l == 0 ? K : L.d_K;
+    const LevelMatrix Kl = l == 0 ? M0 : LevelMatrix{L.d_K, ctx->mg_fp32 ? L.d_K32 : nullptr};
     const double* Di = l == 0 ? ctx->d_Dinv : L.d_Dinv;
     const double* b = l == 0 ? r : L.d_b;
     fc::k_mg_prolong_add<<<grid_for(L.n_nodes, bs), bs, 0, ctx->stream>>>(lattice_of(L), lattice_of(C), L.n_nodes, C.d_x, L.d_free, L.d_x);

@@ -25,6 +25,11 @@ struct fc_mg_level
   double* d_Dinv = nullptr;          // inverse diagonal blocks (levels >= 1; level 0 uses ctx->d_Dinv)
   double omega = 0.6;                // Jacobi damping of the level: 4 / (3 lambda_max(D^-1 K)), estimated by fc_solid_mg_update
   double *d_b = nullptr, *d_x = nullptr, *d_y = nullptr, *d_r = nullptr, *d_u = nullptr;  // [3 n_nodes] each
+  double* d_ev = nullptr;            // [3 n_nodes] last iterate of the power iteration: start of the next estimate
+  bool have_ev = false;
+  float* d_K32 = nullptr;            // [nnz of the level] single-precision copy of the tangent for the cycle (all levels)
+  double* d_Ainv = nullptr;          // [(3 n_nodes)^2] dense inverse of the coarsest level's tangent (small levels only)
+  bool have_Ainv = false;
 };
 
 struct fc_ctx
@@ -83,7 +88,9 @@ struct fc_ctx
   long long mg_toggle_version = -1;   // toggle the coarse Dirichlet maps were derived from
   bool mg_operators_ready = false;    // fc_solid_mg_update ran for the current state
   int mg_nu = 2;                      // pre- and post-smoothing sweeps of the V-cycle
-  bool mg_fine_omega_stale = true;    // the damping of level 0 is estimated at the first cycle after fc_solid_mg_update
+  bool mg_fine_omega_stale = true;
+  double mg_damping = 4.0 / 3.0;      // omega = mg_damping / lambda_max(D^-1 K) estimate
+  bool mg_fp32 = true;                // the V-cycle reads single-precision copies of the tangents    // the damping of level 0 is estimated at the first cycle after fc_solid_mg_update
   double* d_dot = nullptr;            // block partials [3][592] + results [3]
   double* h_dot_pinned = nullptr;
 

@@ -15,8 +15,10 @@ namespace fc
   // one damped node-block Jacobi sweep, or the residual:
   //   Dinv != nullptr:  x_out = x_in + omega Dinv (b - K x_in)          (x_in == nullptr: x_in = 0, no matrix access)
   //   Dinv == nullptr:  x_out = b - K x_in                              (the residual)
-  // One warp per owned node: the three DOF rows share the gathered x.
-  static __global__ void k_mg_smooth(const long long* __restrict__ nodeptr, const int* __restrict__ nodeadj, int n_nodes, const double* __restrict__ K,
+  // One warp per owned node: the three DOF rows share the gathered x.  TK = double, or float: the cycle may run on a single-
+  // precision copy of the level's tangent (half the bytes of the pass that bounds it; vectors and sums stay FP64).
+  template <typename TK>
+  static __global__ void k_mg_smooth(const long long* __restrict__ nodeptr, const int* __restrict__ nodeadj, int n_nodes, const TK* __restrict__ K,
       const double* __restrict__ Dinv, double omega, const double* __restrict__ b, const double* __restrict__ x_in, double* __restrict__ x_out)
   {
     const int a = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
@@ -26,15 +28,15 @@ namespace fc
     {
       const long long p0 = nodeptr[a];
       const int L3 = 3 * (int)(nodeptr[a + 1] - p0);
-      const double* r0 = K + 9 * p0;
+      const TK* r0 = K + 9 * p0;
       const int* adj = nodeadj + p0;
       for (int m = lane; m < L3; m += 32)
       {
         const int k = m / 3;
         const double xv = __ldg(x_in + 3 * (long long)__ldg(adj + k) + (m - 3 * k));
-        s0 += __ldg(r0 + m) * xv;
-        s1 += __ldg(r0 + L3 + m) * xv;
-        s2 += __ldg(r0 + 2 * L3 + m) * xv;
+        s0 += (double)__ldg(r0 + m) * xv;
+        s1 += (double)__ldg(r0 + L3 + m) * xv;
+        s2 += (double)__ldg(r0 + 2 * L3 + m) * xv;
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1)
@@ -172,6 +174,82 @@ namespace fc
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
     z ^= z >> 31;
     v[i] = mask[i] ? ((z & 1) ? 1.0 : -1.0) * (0.5 + (double)((z >> 11) & 0xFFFF) / 131072.0) : 0.0;
+  }
+
+  static __global__ void k_mg_to_float(long long n, const double* __restrict__ src, float* __restrict__ dst)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = (float)src[i];
+  }
+  // dst = a src
+  static __global__ void k_mg_scale_copy(int n, double a, const double* __restrict__ src, double* __restrict__ dst)
+  {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = a * src[i];
+  }
+
+  // ---- direct solve of the coarsest level: dense inverse, one CTA ------------------------------------------------------------
+  // A [n][n] (row-major, n = 3 n_nodes) = the level's tangent expanded from the node-blocked CSR
+  static __global__ void k_mg_dense_fill(const long long* __restrict__ nodeptr, const int* __restrict__ nodeadj, int n_nodes, const double* __restrict__ K,
+      double* __restrict__ A)
+  {
+    const int n = 3 * n_nodes;
+    for (long long i = threadIdx.x; i < (long long)n * n; i += blockDim.x) A[i] = 0.0;
+    __syncthreads();
+    for (int a = threadIdx.x; a < n_nodes; a += blockDim.x)
+    {
+      const long long p0 = nodeptr[a];
+      const int L = (int)(nodeptr[a + 1] - p0), L3 = 3 * L;
+      for (int k = 0; k < L; ++k)
+      {
+        const int b = nodeadj[p0 + k];
+        for (int i = 0; i < 3; ++i)
+          for (int j = 0; j < 3; ++j) A[(long long)(3 * a + i) * n + 3 * b + j] = K[9 * p0 + (long long)i * L3 + 3 * k + j];
+      }
+    }
+  }
+  // in-place Gauss-Jordan inversion without pivoting (the tangent is symmetric positive definite on the free DOFs, identity on
+  // the fixed ones); ok[0] = 0 if a pivot is not positive (the caller then keeps the smoother on this level)
+  static __global__ void k_mg_dense_invert(int n, double* __restrict__ A, int* __restrict__ ok)
+  {
+    __shared__ double s_piv;
+    if (threadIdx.x == 0) ok[0] = 1;
+    for (int k = 0; k < n; ++k)
+    {
+      __syncthreads();
+      if (threadIdx.x == 0)
+      {
+        s_piv = A[(long long)k * n + k];
+        if (!(s_piv > 0.0)) ok[0] = 0;
+      }
+      __syncthreads();
+      const double ip = 1.0 / s_piv;
+      // scale the pivot row (its diagonal becomes 1 / pivot)
+      for (int j = threadIdx.x; j < n; j += blockDim.x) A[(long long)k * n + j] = (j == k ? 1.0 : A[(long long)k * n + j]) * ip;
+      __syncthreads();
+      // eliminate column k from every other row: a warp per row
+      for (int i = threadIdx.x >> 5; i < n; i += blockDim.x >> 5)
+      {
+        if (i == k) continue;
+        const double f = A[(long long)i * n + k];
+        for (int j = threadIdx.x & 31; j < n; j += 32)
+          if (j != k) A[(long long)i * n + j] -= f * A[(long long)k * n + j];
+      }
+      __syncthreads();
+      for (int i = threadIdx.x; i < n; i += blockDim.x)
+        if (i != k) A[(long long)i * n + k] = -A[(long long)i * n + k] * ip;
+    }
+  }
+  // x = Ainv b, one warp per row
+  static __global__ void k_mg_dense_apply(int n, const double* __restrict__ Ainv, const double* __restrict__ b, double* __restrict__ x)
+  {
+    const int r = (int)(((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+    if (r >= n) return;
+    double s = 0.0;
+    for (int j = lane; j < n; j += 32) s += Ainv[(long long)r * n + j] * b[j];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xFFFFFFFFu, s, o);
+    if (lane == 0) x[r] = s;
   }
 
   // y = x restricted to the free DOFs (mask != 0), zero elsewhere

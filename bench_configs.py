@@ -99,7 +99,7 @@ def run(fc, name, ct, form, mat, nue, n, steps, flags=0):
     torch.cuda.empty_cache()
 
 
-def run_newton(fc, edge, steps, method=None, mg_sweeps=2):
+def run_newton(fc, edge, steps, method=None, mg_sweeps=2, mg_fp32=True, mg_damping=None):
     """SURVEY 8f F1 at C2 size: one load step of a clamped hex8 Neo-Hooke cube under a nodal load on the x+ face, full Newton with
     every stage on the device (element evaluation, Dirichlet application, CG with node-block Jacobi): times per stage, the
     y = K x kernel against the HBM roofline, CG iterations."""
@@ -139,6 +139,9 @@ def run_newton(fc, edge, steps, method=None, mg_sweeps=2):
     levels = s.mg_setup() if method == fc.FC_SOLVER_CG_MG else 1
     if method == fc.FC_SOLVER_CG_MG:
         s.mg_set_sweeps(mg_sweeps)
+        s.mg_set_precision(mg_fp32)
+        if mg_damping:
+            s.mg_set_damping(mg_damping)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     for it in range(12):
         ev[0].record()
@@ -160,7 +163,7 @@ def run_newton(fc, edge, steps, method=None, mg_sweeps=2):
             break
     assert s.error_state() == (0, -1)
     peak = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
-    out = {"config": f"F1 device Newton step, hex8 NeoHooke {edge}^3, clamped x-, load on x+", "solver": ["CG + node-block Jacobi", "BiCGStab", f"CG + geometric multigrid V({mg_sweeps},{mg_sweeps}), {levels} levels"][method], "elements": edge ** 3, "n_dof": n_row, "nnz": int(nnz),
+    out = {"config": f"F1 device Newton step, hex8 NeoHooke {edge}^3, clamped x-, load on x+", "solver": ["CG + node-block Jacobi", "BiCGStab", f"CG + geometric multigrid V({mg_sweeps},{mg_sweeps}), {levels} levels, {'FP32' if mg_fp32 else 'FP64'} cycle matrices"][method], "elements": edge ** 3, "n_dof": n_row, "nnz": int(nnz),
            "spmv_ms": spmv_ms, "spmv_algorithmic_GBps": spmv_bytes / (spmv_ms * 1e-3) / 1e9, "measured_peaks": peak,
            "newton": hist, "max_displacement": float(u.abs().max())}
     if method == fc.FC_SOLVER_CG_MG:
@@ -256,6 +259,8 @@ def main():
     ap.add_argument("--only", default=None)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--mg-sweeps", type=int, default=2)
+    ap.add_argument("--mg-damping", type=float, default=None, help="omega = this / lambda_max estimate (library default 4/3.3)")
+    ap.add_argument("--mg-fp64", action="store_true", help="V-cycle on the FP64 tangents instead of their single-precision copies")
     args = ap.parse_args()
     fc = importlib.import_module("4c_b200")
     H8, H27, T10 = fc.FC_HEX8, fc.FC_HEX27, fc.FC_TET10
@@ -283,7 +288,7 @@ def main():
         return
     if args.only and args.only.startswith("newton"):
         mg = args.only.startswith("newtonmg")
-        run_newton(fc, int(args.only[8 if mg else 6:] or 100), args.steps, fc.FC_SOLVER_CG_MG if mg else None, args.mg_sweeps)
+        run_newton(fc, int(args.only[8 if mg else 6:] or 100), args.steps, fc.FC_SOLVER_CG_MG if mg else None, args.mg_sweeps, not args.mg_fp64, args.mg_damping)
         return
     names = args.only.split("|") if args.only else []
     exact = any(c[0] in names for c in cfgs)  # full config names (separated by |) select exactly those configs

@@ -341,6 +341,15 @@ extern "C"
   int fc_solid_mg_setup(fc_ctx* ctx, int max_levels, int* n_levels);
   int fc_solid_mg_update(fc_ctx* ctx, const double* u_col_dev);
   int fc_solid_mg_set_sweeps(fc_ctx* ctx, int nu); /* pre- and post-smoothing sweeps of the cycle, default 2 */
+  /* The V-cycle reads single-precision copies of the level tangents (default; vectors, sums and the CG around it stay FP64:
+   * the cycle is then the exact V-cycle of a matrix that differs from K by 6e-8 relative, still a symmetric positive
+   * definite preconditioner) or the FP64 values (0).  Call fc_solid_mg_update afterwards. */
+  int fc_solid_mg_set_precision(fc_ctx* ctx, int single_precision_cycle);
+  /* Jacobi damping of every level: omega = factor / lambda_max(D^-1 K), 0 < factor < 2 (default 4/3).  lambda_max is a
+   * power-iteration estimate, i.e. a lower bound: should a level's damping come out too large (the cycle is then indefinite and
+   * CG sees r.z <= 0), the solver multiplies every level's damping by 0.7 and restarts from its current iterate, up to four
+   * times, before it gives up with FC_ERR_SOLVER.  Call fc_solid_mg_update afterwards. */
+  int fc_solid_mg_set_damping(fc_ctx* ctx, double factor);
   /* nodes and Jacobi damping of one level (0 = finest; its damping is known after the first solve that follows mg_update) */
   int fc_solid_mg_level_info(fc_ctx* ctx, int level, int* n_nodes, double* omega);
   int fc_solid_set_dirichlet_toggle(fc_ctx* ctx, int n, const int* row_lids);

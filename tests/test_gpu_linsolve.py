@@ -196,7 +196,27 @@ def test_multigrid_preconditioned_cg(fc, n, levels):
     b = torch.from_numpy(b).to(dev)
     x_mg = torch.zeros(n_row, dtype=torch.float64, device=dev)
     s.apply_dirichlet_to_system(x_mg, b, None)
-    it_mg, rr_mg = s.linear_solve(K, b, x_mg, method=fc.FC_SOLVER_CG_MG, rel_tol=1e-10, max_iter=200)
+    it_mg, rr_mg = s.linear_solve(K, b, x_mg, method=fc.FC_SOLVER_CG_MG, rel_tol=1e-10, max_iter=200)  # default: FP32 cycle matrices
+    s.mg_set_precision(False)
+    with pytest.raises(fc.FourCError):  # the copies / estimates belong to an update
+        s.linear_solve(K, b, x_mg.clone(), method=fc.FC_SOLVER_CG_MG)
+    s.mg_update(u)
+    x_64 = torch.zeros(n_row, dtype=torch.float64, device=dev)
+    it_64, rr_64 = s.linear_solve(K, b, x_64, method=fc.FC_SOLVER_CG_MG, rel_tol=1e-10, max_iter=200)
+    assert rr_64 <= 1e-10 and abs(it_64 - it_mg) <= 2 and float((x_64 - x_mg).abs().max()) <= 1e-7 * float(x_mg.abs().max())
+    s.mg_set_precision(True)
+    s.mg_update(u)  # second update of the level: the eigenvalue estimate starts from the stored iterate
+    x_w = torch.zeros(n_row, dtype=torch.float64, device=dev)
+    it_w, _ = s.linear_solve(K, b, x_w, method=fc.FC_SOLVER_CG_MG, rel_tol=1e-10, max_iter=200)
+    assert abs(it_w - it_mg) <= 2
+    # a damping beyond 2 / lambda_max makes the cycle indefinite: the solver cuts it and restarts instead of giving up
+    s.mg_set_damping(1.95)
+    s.mg_update(u)
+    x_d = torch.zeros(n_row, dtype=torch.float64, device=dev)
+    it_d, rr_d = s.linear_solve(K, b, x_d, method=fc.FC_SOLVER_CG_MG, rel_tol=1e-10, max_iter=300)
+    assert rr_d <= 1e-10 and float((x_d - x_mg).abs().max()) <= 1e-7 * float(x_mg.abs().max())
+    s.mg_set_damping(4.0 / 3.0)
+    s.mg_update(u)
     x_j = torch.zeros(n_row, dtype=torch.float64, device=dev)
     it_j, rr_j = s.linear_solve(K, b, x_j, method=fc.FC_SOLVER_CG, rel_tol=1e-10, max_iter=20000)
     print(f"n={n}: CG-MG {it_mg} iterations (rel. residual {rr_mg:.1e}), node-block Jacobi CG {it_j}")

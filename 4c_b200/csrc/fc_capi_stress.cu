@@ -45,13 +45,43 @@ namespace
     return true;
   }
 
-  // Gauss points -> nodes: base cell = hex8 / hex27 / tet4 (4C_fem_general_utils_gauss_point_extrapolation.cpp:29-44)
+  // Gauss points -> nodes (evaluate_gauss_points_to_nodes_extrapolation_matrix,
+  // src/core/fem/src/general/utils/4C_fem_general_utils_gauss_point_extrapolation.cpp:262-292): the shape functions of a BASE
+  // cell chosen by the number of Gauss points (:23-85) are evaluated at the Gauss points and inverted (:147-180), then
+  // interpolated to the nodes of the cell (:211-260).  hex8 / 8 gp -> hex8, hex27 and hex20 / 27 gp -> hex27, tet10 / 4 gp ->
+  // tet4, tet4 / 1 gp -> point1 (every node takes the Gauss-point value), wedge6 / 6 gp -> wedge6; pyramid5 / 8 gp uses the
+  // reference's fixed 5 x 8 matrix (:299-378).
   template <int CT>
   bool extrapolation_matrix(std::vector<double>& E)
   {
     constexpr int NEN = fc::Cell<CT>::nen, NGP = fc::Cell<CT>::ngp;
-    constexpr int NB = CT == fc::TET10 ? 4 : NEN;  // nodes of the base cell; NB == NGP for all three
-    static_assert(NB == NGP, "square base system");
+    E.assign((size_t)NEN * NGP, 0.0);
+    if (CT == fc::TET4)
+    {
+      for (int a = 0; a < NEN; ++a) E[a] = 1.0;
+      return true;
+    }
+    if (CT == fc::PYRAMID5)
+    {
+      // entries of the reference's table by their pattern: rows 0-3 rotate with the base node, row 4 is the apex
+      const double lo[4] = {2.408235313815748, -0.6452847075210328, 0.1729035162684118, -0.6452847075210328};
+      const double hi[4] = {-0.542209910031327, 0.1452847075210439, -0.03892892005285509, 0.1452847075210439};
+      for (int i = 0; i < 4; ++i)
+        for (int k = 0; k < 4; ++k)
+        {
+          E[(size_t)i * 8 + k] = lo[(k - i + 4) % 4];
+          E[(size_t)i * 8 + 4 + k] = hi[(k - i + 4) % 4];
+        }
+      for (int k = 0; k < 4; ++k)
+      {
+        E[(size_t)4 * 8 + k] = -0.2702847075210531;
+        E[(size_t)4 * 8 + 4 + k] = 0.520284707521053;
+      }
+      return true;
+    }
+    constexpr int BASE = CT == fc::HEX20 ? fc::HEX27 : CT;  // tet10 -> tet4 is written out below
+    constexpr int NB = CT == fc::TET10 ? 4 : fc::Cell<BASE>::nen;
+    static_assert(NB == NGP || CT == fc::TET4 || CT == fc::PYRAMID5, "square base system");
     std::vector<double> M((size_t)NGP * NB);
     auto base_shape = [](const double* xi, double* N)
     {
@@ -63,7 +93,7 @@ namespace
         N[3] = xi[2];
       }
       else
-        fc::shape_function<CT>(xi, N);
+        fc::shape_function<BASE>(xi, N);
     };
     for (int g = 0; g < NGP; ++g)
     {
@@ -72,14 +102,15 @@ namespace
       base_shape(xi, &M[(size_t)g * NB]);
     }
     if (!invert_dense(M, NB)) return false;  // M^-1: [base node][gp]
-    E.assign((size_t)NEN * NGP, 0.0);
     for (int a = 0; a < NEN; ++a)
     {
       double xi[3], Nb[NB > 0 ? NB : 1];
-      fc::node_param_coords(CT, a, xi);
       if (CT == fc::TET10)
+      {
+        fc::node_param_coords(CT, a, xi);
         base_shape(xi, Nb);
-      else
+      }
+      else  // node a of the cell is node a of the base cell (hex20: the first 20 nodes of hex27)
         for (int c = 0; c < NB; ++c) Nb[c] = c == a ? 1.0 : 0.0;
       for (int g = 0; g < NGP; ++g)
       {
@@ -132,7 +163,6 @@ extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int st
 {
   if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede evaluate_stress");
   if (!ctx->have_material) return fail(ctx, FC_ERR_INVALID, "set_material must precede evaluate_stress");
-  if (ctx->celltype > FC_TET10) return fail(ctx, FC_ERR_UNSUPPORTED, "stress output exists for hex8, hex27 and tet10");
   if (!u_col || (!gp_stress && !nodal_stress)) return fail(ctx, FC_ERR_INVALID, "u_col and one output are required");
   if (stress_type != FC_STRESS_2PK && stress_type != FC_STRESS_CAUCHY) return fail(ctx, FC_ERR_UNSUPPORTED, "stress type");
   FC_CUDA(cudaSetDevice(ctx->device));
@@ -175,6 +205,14 @@ extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int st
     rc = stress_impl<fc::HEX27, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
   else if (ctx->celltype == FC_TET10)
     rc = stress_impl<fc::TET10, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
+  else if (ctx->celltype == FC_HEX20)
+    rc = stress_impl<fc::HEX20, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
+  else if (ctx->celltype == FC_TET4)
+    rc = stress_impl<fc::TET4, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
+  else if (ctx->celltype == FC_WEDGE6)
+    rc = stress_impl<fc::WEDGE6, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
+  else if (ctx->celltype == FC_PYRAMID5)
+    rc = fbar ? stress_impl<fc::PYRAMID5, fc::FORM_FBAR>(ctx, A, stress_type, d_gp, d_nodal) : stress_impl<fc::PYRAMID5, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
   if (rc == FC_OK && gp_stress && !g_dev) FC_CUDA(cudaMemcpyAsync(gp_stress, d_gp, sizeof(double) * n_gp, cudaMemcpyDeviceToHost, s));
   if (rc == FC_OK && nodal_stress && !n_dev) FC_CUDA(cudaMemcpyAsync(nodal_stress, d_nodal, sizeof(double) * n_nod, cudaMemcpyDeviceToHost, s));
   cudaError_t e = cudaStreamSynchronize(s);

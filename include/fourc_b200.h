@@ -53,7 +53,7 @@ extern "C"
     FC_HEX8 = 0,
     FC_HEX27 = 1,
     FC_TET10 = 2,
-    /* evaluated by the generic B-operator kernel (no tensor-core variant); stress output not built */
+    /* evaluated by the generic B-operator kernel (no tensor-core variant) */
     FC_HEX20 = 3,   /* 27-point rule */
     FC_TET4 = 4,    /* stiffness tet_1point, mass tet_4point */
     FC_WEDGE6 = 5,  /* wedge_6point */

@@ -37,6 +37,11 @@ CASES = [
     "solid_ele_hex20_Standard_volume_neumann.dat",
     "solid_ele_tet4_Standard_volume_neumann.dat",
     "solid_ele_pyramid5_Standard_volume_neumann.dat",
+    # nodal Cauchy stresses of the F4 cells (Gauss-point extrapolation per base cell; pyramid5: the reference's fixed matrix)
+    "solid_ele_hex20_Standard_stressout.dat",
+    "solid_ele_tet4_Standard_stressout.dat",
+    "solid_ele_wedge6_Standard_stressout.dat",
+    "solid_ele_pyramid5_Standard_stressout.dat",
 ]
 
 

@@ -404,9 +404,27 @@ def extrapolation_matrix(ct, gauss_xi, shape, xi_nodes):
     """Gauss points -> nodes (4C_fem_general_utils_gauss_point_extrapolation.cpp:29-44, 90-260, 288-320): invert
     M = [N^base_i(xi_gp)] of the base cell (hex8/8 gp -> hex8, hex27/27 gp -> hex27, tet10/4 gp -> tet4), then interpolate the
     remaining nodes with the base cell's shape functions.  shape(ct, xi) -> N of the full cell."""
-    if ct in (0, 1):
+    if ct in (0, 1, 5):  # hex8 / hex27 / wedge6: the cell is its own base cell
         M = np.array([shape(ct, x) for x in gauss_xi])  # [gp][node]
         return np.linalg.inv(M)  # [node][gp]
+    if ct == 3:  # hex20 with 27 Gauss points: base cell hex27, the 20 nodes are its first 20 (:29-44, :211-262)
+        M = np.array([shape(1, x) for x in gauss_xi])
+        return np.linalg.inv(M)[:20]
+    if ct == 4:  # tet4 with one Gauss point: base "cell" point1, every node takes the Gauss-point value
+        return np.ones((4, 1))
+    if ct == 6:
+        # pyramid5: the reference's hard-coded 5 x 8 matrix (:316-378: "the 8 Gauss points create a HEX-element inside the
+        # pyramid"), used with the Gauss-point order of pyramid_8point as it stands
+        a, b, c, d, e, f, g, h = (2.408235313815748, -0.6452847075210328, 0.1729035162684118, -0.542209910031327, 0.1452847075210439,
+                                  -0.03892892005285509, -0.2702847075210531, 0.520284707521053)
+        lo, hi = [a, b, c, b], [d, e, f, e]
+        E = np.zeros((5, 8))
+        for i in range(4):
+            for k in range(4):
+                E[i, k] = lo[(k - i) % 4]
+                E[i, 4 + k] = hi[(k - i) % 4]
+        E[4, :4], E[4, 4:] = g, h
+        return E
     tet4 = lambda x: np.array([1.0 - x[0] - x[1] - x[2], x[0], x[1], x[2]])  # noqa: E731
     M = np.array([tet4(x) for x in gauss_xi])
     base = np.linalg.inv(M)  # [4][gp]

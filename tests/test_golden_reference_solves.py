@@ -27,6 +27,10 @@ CASES = [
     "solid_ele_hex20_Standard_volume_neumann",
     "solid_ele_tet4_Standard_volume_neumann",
     "solid_ele_pyramid5_Standard_volume_neumann",
+    "solid_ele_hex20_Standard_stressout",
+    "solid_ele_tet4_Standard_stressout",
+    "solid_ele_wedge6_Standard_stressout",
+    "solid_ele_pyramid5_Standard_stressout",
 ]
 
 
@@ -140,7 +144,8 @@ def test_neumann_oracle_matches_numpy_restatement(oracle, case):
 
 
 STRESS_CASES = ["solid_ele_hex8_Standard_eas_none_stressout", "solid_ele_hex27_Standard_stressout", "solid_ele_tet10_Standard_stressout",
-                "solid_ele_hex8_Standard_fbar"]
+                "solid_ele_hex8_Standard_fbar", "solid_ele_hex20_Standard_stressout", "solid_ele_tet4_Standard_stressout",
+                "solid_ele_wedge6_Standard_stressout", "solid_ele_pyramid5_Standard_stressout", "solid_ele_pyramid5_Standard_fbar"]
 
 
 def oracle_gp_stress(oracle, p, U, e, st):

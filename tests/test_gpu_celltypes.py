@@ -114,13 +114,29 @@ def test_mass_and_neumann_parity(fc, oracle, name):
     s.close()
 
 
-def test_stress_output_is_refused_for_the_new_cell_types(fc, oracle):
-    p, X, u = distorted(oracle, "solid_ele_tet4_Standard_dynamic")
+@pytest.mark.parametrize("name,form", [("solid_ele_hex20_Standard_dynamic", DISP), ("solid_ele_tet4_Standard_dynamic", DISP),
+                                       ("solid_ele_wedge6_Standard_dynamic", DISP), ("solid_ele_pyramid5_Standard_dynamic", DISP),
+                                       ("solid_ele_pyramid5_Standard_dynamic", FBAR)])
+def test_stress_output(fc, oracle, name, form):
+    """fc_solid_evaluate_stress on the F4 cells: Gauss-point stresses against the oracle, nodal values against the driver's
+    restatement of the extrapolation (base cell per Gauss-point count; pyramid5: the reference's fixed matrix)"""
+    import torch
+    p, X, u = distorted(oracle, name)
+    p.X = X
     s = fc.Solid(0)
-    s.set_mesh(p.ct, DISP, X, p.node_gid, np.zeros(len(X), np.int32), p.conn, p.ele_gid)
+    s.set_mesh(p.ct, form, X, p.node_gid, np.zeros(len(X), np.int32), p.conn, p.ele_gid)
     s.set_material(NH, 10.0, 0.25)
     s.build_graph()
+    E = sd.extrapolation_matrix(p.ct, oracle.gauss_rule(p.ct)[0], oracle.shape, oracle.node_param_coords(p.ct))
+    for st in (fc.FC_STRESS_2PK, fc.FC_STRESS_CAUCHY):
+        gp, nodal = s.evaluate_stress(u.reshape(-1), st)
+        ref = [oracle.element_gp_stress(p.ct, form, NH, 10.0, 0.25, X[en], u[en], st)[1] for en in p.conn]
+        for e in range(len(p.conn)):
+            assert np.max(np.abs(gp[e] - ref[e])) <= 1e-12 * np.max(np.abs(ref[e]))
+        nodal_ref = sd.nodal_stresses(p, lambda e: ref[e], E)
+        assert np.max(np.abs(nodal - nodal_ref)) <= 1e-12 * np.max(np.abs(nodal_ref))
+    # the allocation-free variant keeps to hex8 / hex27 / tet10
     with pytest.raises(fc.FourCError) as ei:
-        s.evaluate_stress(u.reshape(-1))
+        s.evaluate_stress_noalloc(torch.from_numpy(u.reshape(-1)).cuda(), torch.zeros((len(X), 6), dtype=torch.float64, device="cuda"))
     assert ei.value.code == fc.FC_ERR_UNSUPPORTED
     s.close()

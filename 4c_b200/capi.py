@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
 
 FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
-FC_FORM_DISPLACEMENT, FC_FORM_FBAR = 0, 1
+FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR = 0, 1, 2
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_SUMMAND_COUPNEOHOOKE, FC_SUMMAND_COUPSVK, FC_SUMMAND_COUPANISOEXPO = 0, 1, 2
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1

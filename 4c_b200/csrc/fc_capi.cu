@@ -180,7 +180,8 @@ extern "C"
     if (!ctx || !X || !node_owner || !conn || !ele_gid || n_col_nodes <= 0 || n_col_ele < 0) return FC_ERR_INVALID;
     (void)node_gid;
     if (celltype < FC_HEX8 || celltype > FC_PYRAMID5) return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
-    if (formulation != FC_FORM_DISPLACEMENT && !(formulation == FC_FORM_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)))
+    if (formulation != FC_FORM_DISPLACEMENT && formulation != FC_FORM_LINEAR &&
+        !(formulation == FC_FORM_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)))
       return fail(ctx, FC_ERR_UNSUPPORTED, "F-bar exists for hex8 and pyramid5 only (4C_solid_3D_ele_factory.hpp:49-50)");
     FC_CUDA(cudaSetDevice(ctx->device));
     const int nen = fc::cell_nen(celltype);

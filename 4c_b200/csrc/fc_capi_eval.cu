@@ -154,6 +154,7 @@ namespace
   bool follows_launch_order(const fc_ctx* ctx, int flags)
   {
     if (flags & FC_EVAL_FORCE_GENERIC) return false;
+    if (ctx->formulation == FC_FORM_LINEAR) return false;
     const bool fbar = ctx->formulation == FC_FORM_FBAR, nh = ctx->mat.kind == fc::MAT_NEOHOOKE;
     if (ctx->celltype == FC_HEX8) return nh ? (fbar || !(flags & FC_EVAL_CLOSED_FORM_FMA)) : (ctx->mat.kind == fc::MAT_SVK && !fbar);  // k_hex8_neohooke_mma, k_hex8_mma_ext
     if (ctx->celltype != FC_HEX27 && ctx->celltype != FC_TET10) return false;                      // k_generic
@@ -163,6 +164,17 @@ namespace
   template <bool WANT_K>
   cudaError_t dispatch(fc_ctx* ctx, const fc::EvalArgs& A, int flags)
   {
+    if (ctx->formulation == FC_FORM_LINEAR)  // KINEM linear: the generic B-operator kernel for every cell
+      switch (ctx->celltype)
+      {
+        case FC_HEX8: return launch_generic<fc::HEX8, fc::FORM_LINEAR, WANT_K>(ctx, A);
+        case FC_HEX27: return launch_generic<fc::HEX27, fc::FORM_LINEAR, WANT_K>(ctx, A);
+        case FC_TET10: return launch_generic<fc::TET10, fc::FORM_LINEAR, WANT_K>(ctx, A);
+        case FC_HEX20: return launch_generic<fc::HEX20, fc::FORM_LINEAR, WANT_K>(ctx, A);
+        case FC_TET4: return launch_generic<fc::TET4, fc::FORM_LINEAR, WANT_K>(ctx, A);
+        case FC_WEDGE6: return launch_generic<fc::WEDGE6, fc::FORM_LINEAR, WANT_K>(ctx, A);
+        default: return launch_generic<fc::PYRAMID5, fc::FORM_LINEAR, WANT_K>(ctx, A);
+      }
     const bool fbar = ctx->formulation == FC_FORM_FBAR;
     if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC))
       return launch_hex8nh<WANT_K>(ctx, A, (flags & FC_EVAL_CLOSED_FORM_FMA) != 0);

@@ -197,22 +197,31 @@ extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int st
   A.u = d_u;
   A.mat = ctx->mat;
   A.fiber = ctx->d_fiber;
-  const bool fbar = ctx->formulation == FC_FORM_FBAR;
+  const bool fbar = ctx->formulation == FC_FORM_FBAR, lin = ctx->formulation == FC_FORM_LINEAR;
   int rc = FC_ERR_UNSUPPORTED;
-  if (ctx->celltype == FC_HEX8)
-    rc = fbar ? stress_impl<fc::HEX8, fc::FORM_FBAR>(ctx, A, stress_type, d_gp, d_nodal) : stress_impl<fc::HEX8, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
-  else if (ctx->celltype == FC_HEX27)
-    rc = stress_impl<fc::HEX27, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
-  else if (ctx->celltype == FC_TET10)
-    rc = stress_impl<fc::TET10, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
-  else if (ctx->celltype == FC_HEX20)
-    rc = stress_impl<fc::HEX20, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
-  else if (ctx->celltype == FC_TET4)
-    rc = stress_impl<fc::TET4, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
-  else if (ctx->celltype == FC_WEDGE6)
-    rc = stress_impl<fc::WEDGE6, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
-  else if (ctx->celltype == FC_PYRAMID5)
-    rc = fbar ? stress_impl<fc::PYRAMID5, fc::FORM_FBAR>(ctx, A, stress_type, d_gp, d_nodal) : stress_impl<fc::PYRAMID5, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal);
+#define FC_STRESS(CT) \
+  rc = lin ? stress_impl<CT, fc::FORM_LINEAR>(ctx, A, stress_type, d_gp, d_nodal) : stress_impl<CT, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal)
+  switch (ctx->celltype)
+  {
+    case FC_HEX8:
+      if (fbar)
+        rc = stress_impl<fc::HEX8, fc::FORM_FBAR>(ctx, A, stress_type, d_gp, d_nodal);
+      else
+        FC_STRESS(fc::HEX8);
+      break;
+    case FC_HEX27: FC_STRESS(fc::HEX27); break;
+    case FC_TET10: FC_STRESS(fc::TET10); break;
+    case FC_HEX20: FC_STRESS(fc::HEX20); break;
+    case FC_TET4: FC_STRESS(fc::TET4); break;
+    case FC_WEDGE6: FC_STRESS(fc::WEDGE6); break;
+    case FC_PYRAMID5:
+      if (fbar)
+        rc = stress_impl<fc::PYRAMID5, fc::FORM_FBAR>(ctx, A, stress_type, d_gp, d_nodal);
+      else
+        FC_STRESS(fc::PYRAMID5);
+      break;
+  }
+#undef FC_STRESS
   if (rc == FC_OK && gp_stress && !g_dev) FC_CUDA(cudaMemcpyAsync(gp_stress, d_gp, sizeof(double) * n_gp, cudaMemcpyDeviceToHost, s));
   if (rc == FC_OK && nodal_stress && !n_dev) FC_CUDA(cudaMemcpyAsync(nodal_stress, d_nodal, sizeof(double) * n_nod, cudaMemcpyDeviceToHost, s));
   cudaError_t e = cudaStreamSynchronize(s);

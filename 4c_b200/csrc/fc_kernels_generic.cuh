@@ -20,7 +20,9 @@ namespace fc
   enum
   {
     FORM_DISP = 0,
-    FORM_FBAR = 1
+    FORM_FBAR = 1,
+    FORM_LINEAR = 2  // KINEM linear: B-operator at F = I, strain = B u, no geometric stiffness
+                     // (src/solid_3D_ele/4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155)
   };
 
   template <int CT, int FORM>
@@ -149,11 +151,25 @@ namespace fc
         deformation_gradient<CT>(Xs, us, Nx, F);
         const double intfac = detJ * __ldg(A.gpw + gp);
         double fbar = 1.0, iF[9];
-        const double detF = FORM == FORM_FBAR ? inv3(F, iF) : det3(F);
+        const double detF = FORM == FORM_FBAR ? inv3(F, iF) : (FORM == FORM_LINEAR ? 1.0 : det3(F));
         if (FORM == FORM_FBAR) fbar = pow(detF0 / detF, 1.0 / 3.0);
         if (!(detJ > 0.0) || detF == 0.0 || !isfinite(detF) || !isfinite(fbar)) s_bad[el] = 1;
         // right Cauchy-Green of the (modified) deformation gradient, symmetric-6
         double C[6];
+        if (FORM == FORM_LINEAR)
+        {
+          // gl_strain = B_lin u = sym(grad u) (calc_lib.hpp:683-695, 773-799); the material law sees it as C = 2 E + I
+          // (4C_mat_elasthyper_service.cpp:80-88), and the B-operator below is built with F = I
+          const double H[9] = {F[0] - 1.0, F[1], F[2], F[3], F[4] - 1.0, F[5], F[6], F[7], F[8] - 1.0};
+          C[0] = 2.0 * H[0] + 1.0;
+          C[1] = 2.0 * H[4] + 1.0;
+          C[2] = 2.0 * H[8] + 1.0;
+          C[3] = H[1] + H[3];
+          C[4] = H[5] + H[7];
+          C[5] = H[2] + H[6];
+          for (int i = 0; i < 9; ++i) F[i] = (i % 4 == 0) ? 1.0 : 0.0;
+        }
+        else
         {
           const double s2 = fbar * fbar;
           C[0] = s2 * (F[0] * F[0] + F[3] * F[3] + F[6] * F[6]);
@@ -169,7 +185,7 @@ namespace fc
         for (int i = 0; i < 36; ++i) R[Cfg::oC + i] = cmat[i];
         for (int i = 0; i < 6; ++i) R[Cfg::oS + i] = S[i];
         R[Cfg::oFac + 0] = intfac * fbar;  // elastic stiffness   (calc_fbar.hpp:176-178)
-        R[Cfg::oFac + 1] = intfac / fbar;  // geometric stiffness (:179-180)
+        R[Cfg::oFac + 1] = FORM == FORM_LINEAR ? 0.0 : intfac / fbar;  // geometric stiffness (:179-180); none with linear kinematics
         R[Cfg::oFac + 2] = intfac / fbar;  // internal force      (:164-166)
         if (FORM == FORM_FBAR)
         {

@@ -38,9 +38,21 @@ namespace fc
       const double fbar = pow(det3(F0) / det3(F), 1.0 / 3.0);
       for (int i = 0; i < 9; ++i) F[i] *= fbar;
     }
-    const double C[6] = {F[0] * F[0] + F[3] * F[3] + F[6] * F[6], F[1] * F[1] + F[4] * F[4] + F[7] * F[7],
+    double C[6] = {F[0] * F[0] + F[3] * F[3] + F[6] * F[6], F[1] * F[1] + F[4] * F[4] + F[7] * F[7],
         F[2] * F[2] + F[5] * F[5] + F[8] * F[8], F[0] * F[1] + F[3] * F[4] + F[6] * F[7],
         F[1] * F[2] + F[4] * F[5] + F[7] * F[8], F[0] * F[2] + F[3] * F[5] + F[6] * F[8]};
+    if (FORM == FORM_LINEAR)
+    {
+      // linear kinematics: strain = sym(grad u), the material law and the push-forward see F = I
+      const double H[9] = {F[0] - 1.0, F[1], F[2], F[3], F[4] - 1.0, F[5], F[6], F[7], F[8] - 1.0};
+      C[0] = 2.0 * H[0] + 1.0;
+      C[1] = 2.0 * H[4] + 1.0;
+      C[2] = 2.0 * H[8] + 1.0;
+      C[3] = H[1] + H[3];
+      C[4] = H[5] + H[7];
+      C[5] = H[2] + H[6];
+      for (int i = 0; i < 9; ++i) F[i] = (i % 4 == 0) ? 1.0 : 0.0;
+    }
     double S[6], cmat[36];
     material_evaluate(A.mat, C, S, cmat, A.fiber ? A.fiber + 3 * (size_t)e : nullptr);
     double* out = gp_stress + ((size_t)e * NGP + gp) * 6;

@@ -63,7 +63,8 @@ extern "C"
   enum
   {
     FC_FORM_DISPLACEMENT = 0, /* 4C_solid_3D_ele_calc_displacement_based.hpp:35-251 */
-    FC_FORM_FBAR = 1          /* 4C_solid_3D_ele_calc_fbar.hpp:43-191 (hex8 and pyramid5 only) */
+    FC_FORM_FBAR = 1,         /* 4C_solid_3D_ele_calc_fbar.hpp:43-191 (hex8 and pyramid5 only) */
+    FC_FORM_LINEAR = 2        /* KINEM linear: 4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155 (every cell) */
   };
   /* materials: MAT_Struct_StVenantKirchhoff (src/mat/4C_mat_stvenantkirchhoff.cpp) and
    * MAT_ElastHyper with one ELAST_CoupNeoHooke summand (src/mat/4C_mat_elasthyper.cpp,

@@ -30,7 +30,8 @@ namespace fc_oracle
   enum Formulation
   {
     FORM_DISP = 0,
-    FORM_FBAR = 1
+    FORM_FBAR = 1,
+    FORM_LINEAR = 2  // KINEM linear: src/solid_3D_ele/4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155
   };
 
   enum EleError
@@ -100,6 +101,25 @@ namespace fc_oracle
         B[4 + 6 * (3 * i + e)] = Fm(e, 1) * Nx(2, i) + Fm(e, 2) * Nx(1, i);
         B[5 + 6 * (3 * i + e)] = Fm(e, 2) * Nx(0, i) + Fm(e, 0) * Nx(2, i);
       }
+    }
+  }
+
+  // linear B-operator: the strain gradient at F = I                calc_lib.hpp:773-799
+  template <int NEN>
+  inline void evaluate_linear_strain_gradient(const double* N_XYZ, double* Bop)
+  {
+    auto Nx = [&](int d, int i) { return N_XYZ[d + 3 * i]; };
+    for (int i = 0; i < NEN; ++i)
+    {
+      for (int r = 0; r < 6; ++r)
+        for (int e = 0; e < 3; ++e) Bop[r + 6 * (3 * i + e)] = 0.0;
+      for (int d = 0; d < 3; ++d) Bop[d + 6 * (3 * i + d)] = Nx(d, i);
+      Bop[3 + 6 * (3 * i + 0)] = Nx(1, i);
+      Bop[3 + 6 * (3 * i + 1)] = Nx(0, i);
+      Bop[4 + 6 * (3 * i + 1)] = Nx(2, i);
+      Bop[4 + 6 * (3 * i + 2)] = Nx(1, i);
+      Bop[5 + 6 * (3 * i + 0)] = Nx(2, i);
+      Bop[5 + 6 * (3 * i + 2)] = Nx(0, i);
     }
   }
 
@@ -234,7 +254,15 @@ namespace fc_oracle
 
       double Fmat[9], C[9], E[6];  // what the material sees
       double fbar_factor = 1.0, Hop[ND], Cg[9];
-      if (form == FORM_DISP)
+      if (form == FORM_LINEAR)
+      {
+        // DisplacementBasedLinearKinematicsFormulation::evaluate: gl_strain = B_lin u (calc_lib.hpp:683-695), the material
+        // sees the identity as deformation gradient; no geometric stiffness (add_stiffness_matrix, :138-151)
+        evaluate_linear_strain_gradient<NEN>(jm.N_XYZ, B);
+        for (int i = 0; i < 9; ++i) Fmat[i] = (i % 4 == 0) ? 1.0 : 0.0;
+        multiply_nn<6, ND, 1>(E, B, u);
+      }
+      else if (form == FORM_DISP)
       {
         for (int i = 0; i < 9; ++i) Fmat[i] = sm.F[i];
         multiply_tn<3, 3, 3>(C, sm.F, sm.F);
@@ -287,7 +315,7 @@ namespace fc_oracle
         const double fac_geo = form == FORM_FBAR ? integration_factor / fbar_factor : integration_factor;
         multiply_nn<6, 6, ND>(cb, cmat, B);                              // cb = C B
         multiply_tn_scaled<ND, 6, ND>(fac_mat, Ke, B, cb, 1.0);          // K += fac B^T cb
-        add_geometric_stiffness_matrix<NEN>(jm.N_XYZ, S, fac_geo, Ke);
+        if (form != FORM_LINEAR) add_geometric_stiffness_matrix<NEN>(jm.N_XYZ, S, fac_geo, Ke);
         if (form == FORM_FBAR)
         {
           // add_fbar_stiffness_matrix                                   lib_fbar.hpp:120-154

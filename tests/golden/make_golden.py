@@ -42,6 +42,19 @@ CASES = [
     "solid_ele_tet4_Standard_stressout.dat",
     "solid_ele_wedge6_Standard_stressout.dat",
     "solid_ele_pyramid5_Standard_stressout.dat",
+    # MAT_ElastHyper = CoupNeoHooke + CoupAnisoExpo with FIBER1 per element, displacement-based, all seven cells
+    "solid_ele_hex8_Standard_eas_none_element_fibers.dat",
+    "solid_ele_hex27_Standard_element_fibers.dat",
+    "solid_ele_tet10_Standard_element_fibers.dat",
+    "solid_ele_hex20_Standard_element_fibers.dat",
+    "solid_ele_tet4_Standard_element_fibers.dat",
+    "solid_ele_wedge6_Standard_element_fibers.dat",
+    "solid_ele_pyramid5_Standard_element_fibers.dat",
+    # KINEM linear (DisplacementBasedLinearKinematicsFormulation) with St.Venant-Kirchhoff, surface + volume loads
+    "solid_ele_hex8_Standard_linear.dat",
+    "solid_ele_hex20_Standard_linear.dat",
+    "solid_ele_tet4_Standard_linear.dat",
+    "solid_ele_pyramid5_Standard_linear.dat",
 ]
 
 
@@ -162,11 +175,13 @@ def main():
         d = from_yaml(path) if name.endswith(".yaml") else from_dat(path)
         d["source"] = "tests/input_files/" + name
         # keep only what the in-scope path can replay: ElastHyper with CoupNeoHooke / CoupSVK / CoupAnisoExpo summands
+        # or MAT_Struct_StVenantKirchhoff
         m1 = d["materials"][1]
-        assert m1[0] == "MAT_ElastHyper", name
-        nm = int(m1[m1.index("NUMMAT") + 1])
-        for mid in m1[m1.index("MATIDS") + 1:m1.index("MATIDS") + 1 + nm]:
-            assert d["materials"][int(mid)][0] in ("ELAST_CoupNeoHooke", "ELAST_CoupSVK", "ELAST_CoupAnisoExpo"), name
+        assert m1[0] in ("MAT_ElastHyper", "MAT_Struct_StVenantKirchhoff"), name
+        if m1[0] == "MAT_ElastHyper":
+            nm = int(m1[m1.index("NUMMAT") + 1])
+            for mid in m1[m1.index("MATIDS") + 1:m1.index("MATIDS") + 1 + nm]:
+                assert d["materials"][int(mid)][0] in ("ELAST_CoupNeoHooke", "ELAST_CoupSVK", "ELAST_CoupAnisoExpo"), name
         out = os.path.join(OUT, re.sub(r"\.(dat|4C\.yaml)$", "", name) + ".json")
         with open(out, "w") as f:
             json.dump(d, f, indent=0, sort_keys=True)

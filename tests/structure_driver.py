@@ -80,9 +80,9 @@ class Problem:
                         i = t.index("FIBER1")
                         fib.append([float(x) for x in t[i + 1:i + 4]])
                     self.fibers = np.array(fib)
-        techs = {"TECH fbar" in e["opts"] for e in fx["elements"]}
+        techs = {(2 if "KINEM linear" in e["opts"] else (1 if "TECH fbar" in e["opts"] else 0)) for e in fx["elements"]}
         assert len(techs) == 1
-        self.form = 1 if techs.pop() else 0  # FC_FORM_FBAR / FC_FORM_DISPLACEMENT
+        self.form = techs.pop()  # FC_FORM_DISPLACEMENT / FC_FORM_FBAR / FC_FORM_LINEAR
         self.dens = float(m1[m1.index("DENS") + 1])
         self.young = float(m10[m10.index("YOUNG") + 1])
         self.nue = float(m10[m10.index("NUE") + 1])

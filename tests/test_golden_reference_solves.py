@@ -31,6 +31,19 @@ CASES = [
     "solid_ele_tet4_Standard_stressout",
     "solid_ele_wedge6_Standard_stressout",
     "solid_ele_pyramid5_Standard_stressout",
+    # CoupNeoHooke + CoupAnisoExpo with element fibres on every cell type
+    "solid_ele_hex8_Standard_eas_none_element_fibers",
+    "solid_ele_hex27_Standard_element_fibers",
+    "solid_ele_tet10_Standard_element_fibers",
+    "solid_ele_hex20_Standard_element_fibers",
+    "solid_ele_tet4_Standard_element_fibers",
+    "solid_ele_wedge6_Standard_element_fibers",
+    "solid_ele_pyramid5_Standard_element_fibers",
+    # KINEM linear + St.Venant-Kirchhoff
+    "solid_ele_hex8_Standard_linear",
+    "solid_ele_hex20_Standard_linear",
+    "solid_ele_tet4_Standard_linear",
+    "solid_ele_pyramid5_Standard_linear",
 ]
 
 
@@ -145,7 +158,9 @@ def test_neumann_oracle_matches_numpy_restatement(oracle, case):
 
 STRESS_CASES = ["solid_ele_hex8_Standard_eas_none_stressout", "solid_ele_hex27_Standard_stressout", "solid_ele_tet10_Standard_stressout",
                 "solid_ele_hex8_Standard_fbar", "solid_ele_hex20_Standard_stressout", "solid_ele_tet4_Standard_stressout",
-                "solid_ele_wedge6_Standard_stressout", "solid_ele_pyramid5_Standard_stressout", "solid_ele_pyramid5_Standard_fbar"]
+                "solid_ele_wedge6_Standard_stressout", "solid_ele_pyramid5_Standard_stressout", "solid_ele_pyramid5_Standard_fbar",
+                "solid_ele_hex8_Standard_linear", "solid_ele_hex20_Standard_linear", "solid_ele_tet4_Standard_linear",
+                "solid_ele_pyramid5_Standard_linear"]
 
 
 def oracle_gp_stress(oracle, p, U, e, st):

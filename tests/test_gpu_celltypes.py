@@ -7,7 +7,7 @@ import structure_driver as sd
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-12
-DISP, FBAR = 0, 1
+DISP, FBAR, LINEAR = 0, 1, 2
 SVK, NH = 0, 1
 
 CASES = [
@@ -19,6 +19,14 @@ CASES = [
     ("solid_ele_pyramid5_Standard_dynamic", DISP, NH, 0.25),
     ("solid_ele_pyramid5_Standard_dynamic", FBAR, NH, 0.45),
     ("solid_ele_pyramid5_Standard_dynamic", FBAR, SVK, 0.3),
+    # KINEM linear on every cell type (hex8 / hex27 / tet10 meshes of the reference's element tests as well)
+    ("solid_ele_hex8_Standard_eas_none_dynamic", LINEAR, SVK, 0.3),
+    ("solid_ele_hex27_Standard_dynamic", LINEAR, SVK, 0.3),
+    ("solid_ele_tet10_Standard_dynamic", LINEAR, NH, 0.25),
+    ("solid_ele_hex20_Standard_dynamic", LINEAR, SVK, 0.3),
+    ("solid_ele_tet4_Standard_dynamic", LINEAR, SVK, 0.3),
+    ("solid_ele_wedge6_Standard_dynamic", LINEAR, SVK, 0.3),
+    ("solid_ele_pyramid5_Standard_dynamic", LINEAR, NH, 0.25),
 ]
 
 

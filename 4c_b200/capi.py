@@ -32,7 +32,7 @@ NGP = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4, FC_HEX20: 27, FC_TET4: 1, FC_WEDGE
 
 EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
-    "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_material_elasthyper", "fc_solid_set_fibers", "fc_solid_set_graph", "fc_solid_build_graph",
+    "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_material_elasthyper", "fc_solid_set_fibers", "fc_solid_set_nodal_fibers", "fc_solid_set_graph", "fc_solid_build_graph",
     "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
     "fc_solid_error_state", "fc_solid_error_allreduce", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_neumann_surface", "fc_solid_neumann_volume",
     "fc_solid_neumann_surface_gp_coords", "fc_solid_neumann_volume_gp_coords", "fc_solid_evaluate_elements",
@@ -262,6 +262,11 @@ class Solid:
         self._chk(lib().fc_solid_set_material_elasthyper(self.h, C.c_int(len(kinds)), _ptr(kinds), _ptr(par)))
         fb = None if fibers is None else _f64(fibers)
         self._chk(lib().fc_solid_set_fibers(self.h, _ptr(fb)))
+
+    def set_nodal_fibers(self, node_fibers):
+        """(n_col_nodes, 3) FIBER1 of the fibre nodes: interpolated to the Gauss points by the library; None clears"""
+        fb = None if node_fibers is None else _f64(node_fibers)
+        self._chk(lib().fc_solid_set_nodal_fibers(self.h, _ptr(fb)))
 
     def build_graph(self):
         self._chk(lib().fc_solid_build_graph(self.h))

@@ -17,6 +17,36 @@
 void fc_free_brick_plan(fc_ctx* ctx);  // fc_capi_graph.cu
 void fc_mg_free(fc_ctx* ctx);          // fc_capi_mg.cu
 
+namespace
+{
+  // nodal fibres -> Gauss points of the stiffness rule, normalised (project_fibers_to_gauss_points,
+  // src/core/fem/src/general/node/4C_fem_general_fiber_node_utils.cpp:18-75)
+  template <int CT>
+  int project_nodal_fibers(const fc_ctx* ctx, const double* node_fiber, std::vector<double>& out)
+  {
+    constexpr int NEN = fc::Cell<CT>::nen, NGP = fc::Cell<CT>::ngp;
+    double N[NGP][NEN];
+    for (int g = 0; g < NGP; ++g)
+    {
+      double xi[3], w;
+      fc::gauss_point<CT>(g, xi, &w);
+      fc::shape_function<CT>(xi, N[g]);
+    }
+    out.assign((size_t)3 * NGP * ctx->n_ele, 0.0);
+    for (int e = 0; e < ctx->n_ele; ++e)
+      for (int g = 0; g < NGP; ++g)
+      {
+        double v[3] = {0.0, 0.0, 0.0};
+        for (int a = 0; a < NEN; ++a)
+          for (int i = 0; i < 3; ++i) v[i] += N[g][a] * node_fiber[3 * (size_t)ctx->h_conn[(size_t)e * NEN + a] + i];
+        const double nrm = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+        if (!(nrm > 0.0)) return 1;
+        for (int i = 0; i < 3; ++i) out[((size_t)e * NGP + g) * 3 + i] = v[i] * (1.0 / nrm);
+      }
+    return 0;
+  }
+}  // namespace
+
 extern "C"
 {
   const char* fc_version(void) { return "fourc_b200 0.1 (sm_100a)"; }
@@ -159,6 +189,7 @@ extern "C"
     if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede set_fibers");
     FC_CUDA(cudaSetDevice(ctx->device));
     dev_free(ctx->d_fiber);
+    ctx->fiber_gp = 0;
     if (!fiber1) return FC_OK;
     std::vector<double> f((size_t)3 * ctx->n_ele);
     for (int e = 0; e < ctx->n_ele; ++e)
@@ -171,6 +202,32 @@ extern "C"
     }
     FC_CUDA(dev_upload(ctx->d_fiber, f.data(), f.size(), ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FC_OK;
+  }
+
+  int fc_solid_set_nodal_fibers(fc_ctx* ctx, const double* node_fiber1)
+  {
+    if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede set_nodal_fibers");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    dev_free(ctx->d_fiber);
+    ctx->fiber_gp = 0;
+    if (!node_fiber1) return FC_OK;
+    std::vector<double> f;
+    int bad = 0;
+    switch (ctx->celltype)
+    {
+      case FC_HEX8: bad = project_nodal_fibers<fc::HEX8>(ctx, node_fiber1, f); break;
+      case FC_HEX27: bad = project_nodal_fibers<fc::HEX27>(ctx, node_fiber1, f); break;
+      case FC_TET10: bad = project_nodal_fibers<fc::TET10>(ctx, node_fiber1, f); break;
+      case FC_HEX20: bad = project_nodal_fibers<fc::HEX20>(ctx, node_fiber1, f); break;
+      case FC_TET4: bad = project_nodal_fibers<fc::TET4>(ctx, node_fiber1, f); break;
+      case FC_WEDGE6: bad = project_nodal_fibers<fc::WEDGE6>(ctx, node_fiber1, f); break;
+      default: bad = project_nodal_fibers<fc::PYRAMID5>(ctx, node_fiber1, f); break;
+    }
+    if (bad) return fail(ctx, FC_ERR_INVALID, "nodal fibres interpolate to a zero vector at a Gauss point");
+    FC_CUDA(dev_upload(ctx->d_fiber, f.data(), f.size(), ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    ctx->fiber_gp = 3;
     return FC_OK;
   }
 
@@ -239,6 +296,7 @@ extern "C"
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
     dev_free(ctx->d_fiber);  // fibres belong to the elements of the previous mesh
+    ctx->fiber_gp = 0;
     dev_free(ctx->d_ele_perm);
     {
       // launch-slot order of the tensor-core kernels.  Large meshes: visit the elements so that a row's contributions arrive

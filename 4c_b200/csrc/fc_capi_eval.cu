@@ -212,6 +212,8 @@ namespace
     A.err = ctx->d_err;
     A.mat = ctx->mat;
     A.fiber = ctx->d_fiber;
+  A.fiber_gp = ctx->fiber_gp;
+  A.fiber_ele = ctx->fiber_gp ? ctx->fiber_gp * fc::cell_ngp(ctx->celltype) : 3;
     return A;
   }
 

@@ -207,6 +207,8 @@ extern "C" int fc_solid_evaluate_stress_noalloc(fc_ctx* ctx, const double* u_col
   A.u = u_col_dev;
   A.mat = ctx->mat;
   A.fiber = ctx->d_fiber;
+  A.fiber_gp = ctx->fiber_gp;
+  A.fiber_ele = ctx->fiber_gp ? ctx->fiber_gp * fc::cell_ngp(ctx->celltype) : 3;
   const bool fbar = ctx->formulation == FC_FORM_FBAR;
   if (ctx->celltype == FC_HEX8)
     return fbar ? stress_noalloc_impl<fc::HEX8, fc::FORM_FBAR>(ctx, A, stress_type, scratch, nodal_stress_dev)

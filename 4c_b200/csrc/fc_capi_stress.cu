@@ -197,6 +197,8 @@ extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int st
   A.u = d_u;
   A.mat = ctx->mat;
   A.fiber = ctx->d_fiber;
+  A.fiber_gp = ctx->fiber_gp;
+  A.fiber_ele = ctx->fiber_gp ? ctx->fiber_gp * fc::cell_ngp(ctx->celltype) : 3;
   const bool fbar = ctx->formulation == FC_FORM_FBAR, lin = ctx->formulation == FC_FORM_LINEAR;
   int rc = FC_ERR_UNSUPPORTED;
 #define FC_STRESS(CT) \

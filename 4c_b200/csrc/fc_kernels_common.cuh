@@ -29,7 +29,9 @@ namespace fc
     const unsigned char* slots;   // [n_ele][nen][nen]
     const unsigned char* dbc;     // [n_row_dof] or nullptr
     const double* geom;           // hex8 geometry cache [n_ele][72] (k_hex8_geom_cache) or nullptr
-    const double* fiber;          // [n_ele][3] unit fibre direction FIBER1 of every element or nullptr (anisotropic summands)
+    const double* fiber;          // unit fibre directions FIBER1 (anisotropic summands) or nullptr: [n_ele][3] per element
+                                  // (fiber_gp = 0) or [n_ele][ngp][3] per Gauss point (fiber_gp = 3, nodal fibres)
+    int fiber_ele, fiber_gp;      // strides in doubles: element e, Gauss point g -> fiber + e * fiber_ele + g * fiber_gp
     // outputs
     double* f;             // [n_row_dof] or nullptr
     double* K;             // [nnz] or nullptr

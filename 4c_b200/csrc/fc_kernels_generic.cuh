@@ -180,7 +180,7 @@ namespace fc
           C[5] = s2 * (F[0] * F[2] + F[3] * F[5] + F[6] * F[8]);
         }
         double S[6], cmat[36];
-        material_evaluate(A.mat, C, S, cmat, A.fiber ? A.fiber + 3 * (size_t)e : nullptr);
+        material_evaluate(A.mat, C, S, cmat, A.fiber ? A.fiber + (size_t)e * A.fiber_ele + gp * A.fiber_gp : nullptr);
         for (int i = 0; i < 9; ++i) R[Cfg::oF + i] = F[i];
         for (int i = 0; i < 36; ++i) R[Cfg::oC + i] = cmat[i];
         for (int i = 0; i < 6; ++i) R[Cfg::oS + i] = S[i];

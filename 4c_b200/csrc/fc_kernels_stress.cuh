@@ -54,7 +54,7 @@ namespace fc
       for (int i = 0; i < 9; ++i) F[i] = (i % 4 == 0) ? 1.0 : 0.0;
     }
     double S[6], cmat[36];
-    material_evaluate(A.mat, C, S, cmat, A.fiber ? A.fiber + 3 * (size_t)e : nullptr);
+    material_evaluate(A.mat, C, S, cmat, A.fiber ? A.fiber + (size_t)e * A.fiber_ele + gp * A.fiber_gp : nullptr);
     double* out = gp_stress + ((size_t)e * NGP + gp) * 6;
     if (stress_type == 0)
     {

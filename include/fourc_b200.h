@@ -144,6 +144,11 @@ extern "C"
    * normalised like Mat::read_anisotropy_fiber (src/mat/4C_mat_anisotropy_utils.cpp:19-44).  NULL removes them.
    * Call after fc_solid_set_mesh. */
   int fc_solid_set_fibers(fc_ctx* ctx, const double* fiber1);
+  /* Fibres given at the nodes (FNODE ... FIBER1; anisotropic summands with INIT 3): node_fiber1 [n_col_nodes][3].  The library
+   * interpolates them to the Gauss points of the stiffness rule with the element's shape functions and normalises
+   * (Core::Nodes::project_fibers_to_gauss_points, src/core/fem/src/general/node/4C_fem_general_fiber_node_utils.cpp:18-75);
+   * replaces element fibres and vice versa; NULL clears. */
+  int fc_solid_set_nodal_fibers(fc_ctx* ctx, const double* node_fiber1);
 
   /* CSR graph of the rank's rows, the state of Epetra_CrsMatrix after FillComplete on the saved
    * graph (4C_linalg_sparsematrix.cpp:353-378,843-865): rows = owned DOFs, column ids local and

@@ -218,11 +218,35 @@ extern "C"
     }
     js->job.mp = mp;
     js->job.ele_fiber.clear();
+    js->job.fiber_gp_stride = 0;
     if (ele_fiber) js->job.ele_fiber.assign(ele_fiber, ele_fiber + 3 * js->job.mesh.ele_gid.size());
   }
   // one element with a summand list: fe, Ke (col-major), optional Gauss-point stresses
+  // nodal fibres (FNODE ... FIBER1, materials with INIT 3): node_fiber [n_nodes][3] in the order of the mesh's nodes;
+  // projected to the Gauss points of every element
+  void oracle_job_set_nodal_fibers(void* h, const double* node_fiber)
+  {
+    auto* js = static_cast<JobState*>(h);
+    const Mesh& m = js->job.mesh;
+    const int ngp = num_gp(m.ct);
+    js->job.ele_fiber.assign((size_t)3 * ngp * m.ele_gid.size(), 0.0);
+    js->job.fiber_gp_stride = 3;
+    std::vector<double> nodal((size_t)3 * m.nen);
+    for (size_t e = 0; e < m.ele_gid.size(); ++e)
+    {
+      for (int a = 0; a < m.nen; ++a)
+      {
+        const int ni = m.node_index.at(m.ele_nodes[e * m.nen + a]);
+        for (int i = 0; i < 3; ++i) nodal[3 * a + i] = node_fiber[3 * (size_t)ni + i];
+      }
+      project_fibers_to_gauss_points(m.ct, nodal.data(), &js->job.ele_fiber[(size_t)3 * ngp * e]);
+    }
+  }
+  void oracle_project_fibers_to_gauss_points(int ct, const double* nodal, double* gp_fiber) { project_fibers_to_gauss_points(ct, nodal, gp_fiber); }
+
+  // fiber: [3] FIBER1 of the element, or [ngp][3] fibres at the Gauss points when fiber_gp_stride = 3
   int oracle_element_evaluate_elasthyper(int ct, int form, int n, const int* kinds, const double* par, const double* fiber, const double* X,
-      const double* u, double* fe, double* Ke, double* gp_stress, int stress_type)
+      const double* u, double* fe, double* Ke, double* gp_stress, int stress_type, int fiber_gp_stride)
   {
     MaterialParams mp{MAT_ELASTHYPER, 0.0, 0.0};
     mp.n_summands = n;
@@ -231,7 +255,7 @@ extern "C"
       mp.sum_kind[k] = kinds[k];
       for (int j = 0; j < 4; ++j) mp.sum_par[k][j] = par[4 * k + j];
     }
-    return element_evaluate(ct, form, mp, X, u, fe, Ke, nullptr, 0.0, gp_stress, stress_type, fiber);
+    return element_evaluate(ct, form, mp, X, u, fe, Ke, nullptr, 0.0, gp_stress, stress_type, fiber, fiber_gp_stride);
   }
   int oracle_job_nranks(void* h) { return ((JobState*)h)->job.part.nranks; }
   void oracle_job_subdivisions(void* h, int* s)

@@ -201,7 +201,7 @@ namespace fc_oracle
   template <int NEN, int NGP>
   inline int element_evaluate_t(int ct, int form, const MaterialParams& mp, const double* X,
       const double* u, double* fe, double* Ke, double* Me, double rho, double* gp_stress = nullptr,
-      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr)
+      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr, int fiber_gp_stride = 0)
   {
     constexpr int ND = 3 * NEN;
     double x[ND];
@@ -295,7 +295,8 @@ namespace fc_oracle
       }
 
       double S[6], cmat[36];
-      material_evaluate(mp, Fmat, E, S, cmat, fiber);
+      // fibre of the Gauss point: the element's FIBER1 (stride 0) or the nodal fibres projected to this point (stride 3)
+      material_evaluate(mp, Fmat, E, S, cmat, fiber ? fiber + (size_t)fiber_gp_stride * gp : nullptr);
       if (gp_stress)
       {
         // calculate_stress / assemble_stress_type_to_matrix_row: solid_3D_ele_calc.cpp:347-390, calc_lib_io.hpp:167-190
@@ -359,26 +360,46 @@ namespace fc_oracle
     return singular ? ELE_ERR_SINGULAR : ELE_OK;
   }
 
+  // Nodal fibres -> Gauss points of the stiffness rule: interpolated with the element's shape functions and normalised
+  // (Core::Nodes::project_fibers_to_gauss_points, src/core/fem/src/general/node/4C_fem_general_fiber_node_utils.cpp:18-75;
+  // called from interpolate_fibers_to_gauss_points_and_add_to_parameter_list, 4C_solid_3D_ele_calc_lib.hpp:1110-1143).
+  // nodal [nen][3] -> gp_fiber [ngp][3]
+  inline void project_fibers_to_gauss_points(int ct, const double* nodal, double* gp_fiber)
+  {
+    const int nen = num_nodes(ct), ngp = num_gp(ct);
+    double xi[27][3], w[27];
+    gauss_rule(ct, xi, w);
+    for (int g = 0; g < ngp; ++g)
+    {
+      double N[27], v[3] = {0.0, 0.0, 0.0};
+      shape_function(ct, xi[g], N);
+      for (int a = 0; a < nen; ++a)
+        for (int i = 0; i < 3; ++i) v[i] += N[a] * nodal[3 * a + i];
+      const double nrm = std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+      for (int i = 0; i < 3; ++i) gp_fiber[3 * g + i] = v[i] * (1.0 / nrm);
+    }
+  }
+
   inline int element_evaluate(int ct, int form, const MaterialParams& mp, const double* X,
       const double* u, double* fe, double* Ke, double* Me = nullptr, double rho = 0.0, double* gp_stress = nullptr,
-      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr)
+      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr, int fiber_gp_stride = 0)
   {
     switch (ct)
     {
       case HEX8:
-        return element_evaluate_t<8, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+        return element_evaluate_t<8, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
       case HEX27:
-        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
       case TET10:
-        return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+        return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
       case HEX20:
-        return element_evaluate_t<20, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+        return element_evaluate_t<20, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
       case TET4:
-        return element_evaluate_t<4, 1>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+        return element_evaluate_t<4, 1>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
       case WEDGE6:
-        return element_evaluate_t<6, 6>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+        return element_evaluate_t<6, 6>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
       case PYRAMID5:
-        return element_evaluate_t<5, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber);
+        return element_evaluate_t<5, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
     }
     return -1;
   }

@@ -55,6 +55,10 @@ CASES = [
     "solid_ele_hex20_Standard_linear.dat",
     "solid_ele_tet4_Standard_linear.dat",
     "solid_ele_pyramid5_Standard_linear.dat",
+    # CoupAnisoExpo with INIT 3: FIBER1 at the nodes (FNODE), interpolated to the Gauss points
+    "solid_ele_hex8_Standard_eas_none_nodal_fibers.dat",
+    "solid_ele_tet4_Standard_nodal_fibers.dat",
+    "solid_ele_tet10_Standard_nodal_fibers.dat",
 ]
 
 
@@ -114,10 +118,13 @@ def from_dat(path):
     for l in s.get("DVOL-NODE TOPOLOGY", []):
         t = l.split()
         vol.setdefault(int(t[3]), []).append(int(t[1]))
-    nodes = {}
+    nodes, node_fibers = {}, {}
     for l in s["NODE COORDS"]:
         t = l.split()
         nodes[int(t[1])] = [float(t[3]), float(t[4]), float(t[5])]
+        if t[0] == "FNODE":  # fibre node: FNODE id COORD x y z FIBER1 a b c
+            i = t.index("FIBER1")
+            node_fibers[int(t[1])] = [float(x) for x in t[i + 1:i + 4]]
     eles = []
     for l in s["STRUCTURE ELEMENTS"]:
         t = l.split()
@@ -128,7 +135,7 @@ def from_dat(path):
             "dirich": [parse_condition_dat(l) for l in s.get("DESIGN SURF DIRICH CONDITIONS", [])],
             "neumann": [parse_condition_dat(l) for l in s.get("DESIGN SURF NEUMANN CONDITIONS", [])],
             "dvol": vol, "vol_neumann": [parse_condition_dat(l) for l in s.get("DESIGN VOL NEUMANN CONDITIONS", [])],
-            "nodes": nodes, "elements": eles}
+            "nodes": nodes, "node_fibers": node_fibers, "elements": eles}
 
 
 def from_yaml(path):

@@ -113,14 +113,23 @@ def element_evaluate(ct, form, kind, young, nue, X, u, want_K=True, want_M=False
 
 
 def element_evaluate_elasthyper(ct, form, summands, fiber, X, u, stress_type=1):
-    """one element of MAT_ElastHyper with a summand list: err, fe, Ke [r, c], gp_stress (ngp, 6)"""
+    """one element of MAT_ElastHyper with a summand list: err, fe, Ke [r, c], gp_stress (ngp, 6); fiber: (3,) FIBER1 of the
+    element, (ngp, 3) fibres at the Gauss points, or None"""
     nd = 3 * NEN[ct]
     kinds, par = _i([k for k, _ in summands]), _d([q for _, q in summands])
     fe, Ke, gp = np.zeros(nd), np.zeros(nd * nd), np.zeros((NGP[ct], 6))
     fib = _d(fiber) if fiber is not None else None
     err = lib.oracle_element_evaluate_elasthyper(C.c_int(ct), C.c_int(form), C.c_int(len(summands)), _p(kinds), _p(par), _p(fib),
-                                                 _p(_d(X).reshape(-1)), _p(_d(u).reshape(-1)), _p(fe), _p(Ke), _p(gp), C.c_int(stress_type))
+                                                 _p(_d(X).reshape(-1)), _p(_d(u).reshape(-1)), _p(fe), _p(Ke), _p(gp), C.c_int(stress_type),
+                                                 C.c_int(3 if fib is not None and fib.size > 3 else 0))
     return err, fe, Ke.reshape(nd, nd).T.copy(), gp
+
+
+def project_fibers_to_gauss_points(ct, nodal):
+    """nodal (nen, 3) -> (ngp, 3): fibres interpolated to the Gauss points and normalised"""
+    out = np.zeros((NGP[ct], 3))
+    lib.oracle_project_fibers_to_gauss_points(C.c_int(ct), _p(_d(nodal)), _p(out))
+    return out
 
 
 def element_gp_stress(ct, form, kind, young, nue, X, u, stress_type=1):
@@ -245,6 +254,10 @@ class Job:
         par = _d([q for _, q in summands])
         lib.oracle_job_set_elasthyper(self.h, C.c_int(form), C.c_int(len(summands)), _p(kinds), _p(par),
                                       _p(_d(fibers)) if fibers is not None else None)
+
+    def set_nodal_fibers(self, node_fibers):
+        """node_fibers: (n_nodes, 3) FIBER1 of the FNODEs in the order of self.node_gid; call after set_elasthyper"""
+        lib.oracle_job_set_nodal_fibers(self.h, _p(_d(node_fibers)))
 
     def rank(self, r):
         sizes = np.zeros(8, np.int64)

@@ -51,7 +51,7 @@ class Problem:
         self.conn = np.array([[self.index[n] for n in e["nodes"]] for e in fx["elements"]], np.int32)
         self.ele_gid = np.array([e["id"] - 1 for e in fx["elements"]], np.int32)
         m1 = fx["materials"]["1"]
-        self.summands, self.fibers = None, None
+        self.summands, self.fibers, self.node_fibers = None, None, None
         if m1[0] == "MAT_Struct_StVenantKirchhoff":
             m10, self.mat = m1, 0  # FC_MAT_STVENANTKIRCHHOFF
         else:
@@ -70,10 +70,13 @@ class Problem:
                     if m[0] in ("ELAST_CoupNeoHooke", "ELAST_CoupSVK"):
                         self.summands.append((0 if m[0] == "ELAST_CoupNeoHooke" else 1, [g("YOUNG"), g("NUE"), 0.0, 0.0]))
                     else:
-                        assert m[0] == "ELAST_CoupAnisoExpo" and int(g("INIT")) == 1 and int(g("FIBER_ID")) == 1
+                        # INIT 1: FIBER1 of the element line; INIT 3: FIBER1 of the fibre nodes, interpolated to the Gauss points
+                        assert m[0] == "ELAST_CoupAnisoExpo" and int(g("INIT")) in (1, 3) and int(g("FIBER_ID")) == 1
                         self.summands.append((2, [g("K1"), g("K2"), g("K1COMP"), g("K2COMP")]))
+                        if int(g("INIT")) == 3:
+                            self.node_fibers = np.array([fx["node_fibers"][str(i)] for i in ids], float)
                 m10 = next(fx["materials"][mid] for mid in mids if "YOUNG" in fx["materials"][mid])
-                if any(k == 2 for k, _ in self.summands):
+                if any(k == 2 for k, _ in self.summands) and self.node_fibers is None:
                     fib = []
                     for e in fx["elements"]:
                         t = e["opts"].split()

@@ -44,6 +44,10 @@ CASES = [
     "solid_ele_hex20_Standard_linear",
     "solid_ele_tet4_Standard_linear",
     "solid_ele_pyramid5_Standard_linear",
+    # fibres at the nodes (INIT 3)
+    "solid_ele_hex8_Standard_eas_none_nodal_fibers",
+    "solid_ele_tet4_Standard_nodal_fibers",
+    "solid_ele_tet10_Standard_nodal_fibers",
 ]
 
 
@@ -53,6 +57,8 @@ def oracle_backend(oracle, p):
         job.set_problem(p.form, p.mat, p.young, p.nue)
     else:
         job.set_elasthyper(p.form, p.summands, p.fibers)
+        if p.node_fibers is not None:
+            job.set_nodal_fibers(p.node_fibers)
     o = job.rank(0)
     assert np.array_equal(job.node_gid, p.node_gid)
 
@@ -92,6 +98,8 @@ def cuda_backend(fc, p):
         s.set_material(p.mat, p.young, p.nue)
     else:
         s.set_material_elasthyper(p.summands, p.fibers)
+        if p.node_fibers is not None:
+            s.set_nodal_fibers(p.node_fibers)
     n_row, n_col, nnz = s.build_graph()
     assert n_row == p.n_dof
     rowptr, colind = s.get_graph()
@@ -136,6 +144,12 @@ def test_reference_result_description_cuda(fc, oracle, case):
         floor = 1e-6 * max(h2)
         n2 = next((i for i, x in enumerate(h2) if x < floor), len(h2))
         n1 = next((i for i, x in enumerate(h) if x < floor), len(h))
+        if p.node_fibers is not None:
+            # fibres interpolated from the nodes have |a|^2 = 1 up to the last bit, and CoupAnisoExpo switches from K1COMP to K1
+            # at I4 = 1: at u = 0 the tangent of the first iteration depends on that bit (del = 0 or 4 K1), in the reference
+            # too.  The histories then differ (also in length) although both solves end at the same solution; fe, Ke and the
+            # stresses of deformed states are compared in tests/test_gpu_parity.py::test_elasthyper_summand_list_parity.
+            continue
         assert abs(n1 - n2) <= 1, (h, h2)
         for x, y in zip(h[:min(n1, n2)], h2[:min(n1, n2)]):
             assert abs(x - y) <= 1e-3 * y + floor, (h, h2)

@@ -142,6 +142,10 @@ def test_element_level_parity(fc, oracle, ct, form, mat, nue, n):
     (HEX8, DISP, (3, 3, 2), [(0, [10.0, 0.3, 0, 0]), (2, [50.0, 2.0, 5.0, 0.5])], True),        # fibres active in compression too
     (HEX27, DISP, (2, 2, 2), [(1, [10.0, 0.3, 0, 0]), (2, [20.0, 1.0, 0.0, 1.0])], True),
     (TET10, DISP, (2, 2, 2), [(0, [10.0, 0.25, 0, 0]), (2, [20.0, 1.0, 0.0, 1.0])], True),
+    # fibres given at the nodes (INIT 3), interpolated to the Gauss points by the library
+    (HEX8, DISP, (3, 3, 2), [(0, [10.0, 0.25, 0, 0]), (2, [100.0, 1.0, 0.0, 1.0])], "nodal"),
+    (HEX27, DISP, (2, 2, 2), [(0, [10.0, 0.25, 0, 0]), (2, [20.0, 1.0, 5.0, 0.5])], "nodal"),
+    (TET10, DISP, (2, 2, 2), [(0, [10.0, 0.25, 0, 0]), (2, [100.0, 1.0, 0.0, 1.0])], "nodal"),
 ])
 def test_elasthyper_summand_list_parity(fc, oracle, ct, form, n, summands, with_fibers):
     """MAT_ElastHyper with a summand list (CoupNeoHooke, CoupSVK, CoupAnisoExpo with element fibres): fe, Ke of every element
@@ -150,8 +154,13 @@ def test_elasthyper_summand_list_parity(fc, oracle, ct, form, n, summands, with_
     s, o, col = setup_rank(fc, job, 0, ct, form, NH, 10.0, 0.25)
     rng = np.random.default_rng(11)
     ne = len(job.conn)
-    fibers = rng.standard_normal((ne, 3)) * 3.0 if with_fibers else None  # not normalised: the library normalises like the reference
+    nodal = with_fibers == "nodal"
+    fibers = rng.standard_normal((ne, 3)) * 3.0 if with_fibers and not nodal else None  # not normalised: the library normalises like the reference
     s.set_material_elasthyper(summands, fibers)
+    node_fibers = None
+    if nodal:
+        node_fibers = rng.standard_normal((len(job.X), 3)) + np.array([2.5, 0.0, 0.0])  # no near-zero interpolants
+        s.set_nodal_fibers(node_fibers[col])
     h = 1.0 / max(n)
     u = oracle.smooth_displacement(job.X, h, amp=0.03)
     nidx = {int(g): i for i, g in enumerate(job.node_gid)}
@@ -163,7 +172,8 @@ def test_elasthyper_summand_list_parity(fc, oracle, ct, form, n, summands, with_
     order = np.array([eidx[int(g)] for g in o["col_eles"]])
     for e in range(ne):
         j = order[e]
-        err, fr, kr, gr = oracle.element_evaluate_elasthyper(ct, form, summands, None if fibers is None else fibers[e], job.X[conn[j]], u[conn[j]], 1)
+        fib = oracle.project_fibers_to_gauss_points(ct, node_fibers[conn[j]]) if nodal else (None if fibers is None else fibers[e])
+        err, fr, kr, gr = oracle.element_evaluate_elasthyper(ct, form, summands, fib, job.X[conn[j]], u[conn[j]], 1)
         assert err == 0
         assert np.max(np.abs(Ke[e] - kr)) <= TOL * np.max(np.abs(kr)), (e, rel(Ke[e], kr))
         assert np.max(np.abs(fe[e] - fr)) <= TOL * max(np.max(np.abs(fr)), np.max(np.abs(kr)) * h), e

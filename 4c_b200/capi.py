@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
 
 FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
-FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR = 0, 1, 2
+FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR, FC_FORM_MULF = 0, 1, 2, 3
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_SUMMAND_COUPNEOHOOKE, FC_SUMMAND_COUPSVK, FC_SUMMAND_COUPANISOEXPO = 0, 1, 2
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
@@ -32,7 +32,7 @@ NGP = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4, FC_HEX20: 27, FC_TET4: 1, FC_WEDGE
 
 EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
-    "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_material_elasthyper", "fc_solid_set_fibers", "fc_solid_set_nodal_fibers", "fc_solid_set_graph", "fc_solid_build_graph",
+    "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_material_elasthyper", "fc_solid_set_fibers", "fc_solid_set_nodal_fibers", "fc_solid_update_prestress", "fc_solid_mulf_get_history", "fc_solid_mulf_set_history", "fc_solid_set_graph", "fc_solid_build_graph",
     "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
     "fc_solid_error_state", "fc_solid_error_allreduce", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_neumann_surface", "fc_solid_neumann_volume",
     "fc_solid_neumann_surface_gp_coords", "fc_solid_neumann_volume_gp_coords", "fc_solid_evaluate_elements",
@@ -267,6 +267,21 @@ class Solid:
         """(n_col_nodes, 3) FIBER1 of the fibre nodes: interpolated to the Gauss points by the library; None clears"""
         fb = None if node_fibers is None else _f64(node_fibers)
         self._chk(lib().fc_solid_set_nodal_fibers(self.h, _ptr(fb)))
+
+    def update_prestress(self, u_col):
+        """FC_FORM_MULF: fold the displacements of the finished step into the Gauss-point history (the caller resets them)"""
+        self._chk(lib().fc_solid_update_prestress(self.h, _ptr(u_col if hasattr(u_col, "data_ptr") else _f64(u_col))))
+
+    def mulf_history(self):
+        """(n_col_ele, ngp, 18) inverse Jacobian | deformation gradient of every Gauss point"""
+        h = np.zeros((self.n_ele, NGP[self.celltype], 18))
+        self._chk(lib().fc_solid_mulf_get_history(self.h, _ptr(h)))
+        return h
+
+    def set_mulf_history(self, history):
+        h = _f64(history)
+        assert h.size == self.n_ele * NGP[self.celltype] * 18
+        self._chk(lib().fc_solid_mulf_set_history(self.h, _ptr(h)))
 
     def build_graph(self):
         self._chk(lib().fc_solid_build_graph(self.h))

@@ -16,6 +16,7 @@
 
 void fc_free_brick_plan(fc_ctx* ctx);  // fc_capi_graph.cu
 void fc_mg_free(fc_ctx* ctx);          // fc_capi_mg.cu
+int fc_mulf_init(fc_ctx* ctx);         // fc_capi_eval.cu
 
 namespace
 {
@@ -94,6 +95,7 @@ extern "C"
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
     dev_free(ctx->d_fiber);
+    dev_free(ctx->d_mulf);
     dev_free(ctx->d_ele_perm);
     dev_free(ctx->d_node_rowbase);
     dev_free(ctx->d_node_rowlen);
@@ -237,7 +239,7 @@ extern "C"
     if (!ctx || !X || !node_owner || !conn || !ele_gid || n_col_nodes <= 0 || n_col_ele < 0) return FC_ERR_INVALID;
     (void)node_gid;
     if (celltype < FC_HEX8 || celltype > FC_PYRAMID5) return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
-    if (formulation != FC_FORM_DISPLACEMENT && formulation != FC_FORM_LINEAR &&
+    if (formulation != FC_FORM_DISPLACEMENT && formulation != FC_FORM_LINEAR && formulation != FC_FORM_MULF &&
         !(formulation == FC_FORM_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)))
       return fail(ctx, FC_ERR_UNSUPPORTED, "F-bar exists for hex8 and pyramid5 only (4C_solid_3D_ele_factory.hpp:49-50)");
     FC_CUDA(cudaSetDevice(ctx->device));
@@ -349,6 +351,7 @@ extern "C"
       FC_CUDA(cudaGetLastError());
       FC_CUDA(cudaMemcpyAsync(ctx->h_err_pinned, ctx->d_err, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     }
+    if (int rc = fc_mulf_init(ctx)) return rc;
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
     if (n_col_ele > 0 && ctx->h_err_pinned[0] > 0)
     {

@@ -154,7 +154,7 @@ namespace
   bool follows_launch_order(const fc_ctx* ctx, int flags)
   {
     if (flags & FC_EVAL_FORCE_GENERIC) return false;
-    if (ctx->formulation == FC_FORM_LINEAR) return false;
+    if (ctx->formulation == FC_FORM_LINEAR || ctx->formulation == FC_FORM_MULF) return false;
     const bool fbar = ctx->formulation == FC_FORM_FBAR, nh = ctx->mat.kind == fc::MAT_NEOHOOKE;
     if (ctx->celltype == FC_HEX8) return nh ? (fbar || !(flags & FC_EVAL_CLOSED_FORM_FMA)) : (ctx->mat.kind == fc::MAT_SVK && !fbar);  // k_hex8_neohooke_mma, k_hex8_mma_ext
     if (ctx->celltype != FC_HEX27 && ctx->celltype != FC_TET10) return false;                      // k_generic
@@ -174,6 +174,17 @@ namespace
         case FC_TET4: return launch_generic<fc::TET4, fc::FORM_LINEAR, WANT_K>(ctx, A);
         case FC_WEDGE6: return launch_generic<fc::WEDGE6, fc::FORM_LINEAR, WANT_K>(ctx, A);
         default: return launch_generic<fc::PYRAMID5, fc::FORM_LINEAR, WANT_K>(ctx, A);
+      }
+    if (ctx->formulation == FC_FORM_MULF)  // PRESTRESS_TECH mulf: same kernel, F from the Gauss-point history
+      switch (ctx->celltype)
+      {
+        case FC_HEX8: return launch_generic<fc::HEX8, fc::FORM_MULF, WANT_K>(ctx, A);
+        case FC_HEX27: return launch_generic<fc::HEX27, fc::FORM_MULF, WANT_K>(ctx, A);
+        case FC_TET10: return launch_generic<fc::TET10, fc::FORM_MULF, WANT_K>(ctx, A);
+        case FC_HEX20: return launch_generic<fc::HEX20, fc::FORM_MULF, WANT_K>(ctx, A);
+        case FC_TET4: return launch_generic<fc::TET4, fc::FORM_MULF, WANT_K>(ctx, A);
+        case FC_WEDGE6: return launch_generic<fc::WEDGE6, fc::FORM_MULF, WANT_K>(ctx, A);
+        default: return launch_generic<fc::PYRAMID5, fc::FORM_MULF, WANT_K>(ctx, A);
       }
     const bool fbar = ctx->formulation == FC_FORM_FBAR;
     if (ctx->celltype == FC_HEX8 && !fbar && ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC))
@@ -195,6 +206,29 @@ namespace
     return nh_gen ? launch_nh_gen<fc::TET10, WANT_K>(ctx, A) : launch_generic<fc::TET10, fc::FORM_DISP, WANT_K>(ctx, A);
   }
 
+  // k_mulf_history over all column elements: u == nullptr writes the initial history
+  cudaError_t launch_mulf_history(fc_ctx* ctx, const double* d_u)
+  {
+    const long long nt = (long long)ctx->n_ele * fc::cell_ngp(ctx->celltype);
+    if (nt == 0) return cudaSuccess;
+    const int bs = 128;
+    const unsigned gs = (unsigned)((nt + bs - 1) / bs);
+#define FC_MULF_HISTORY(CT) fc::k_mulf_history<CT><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->n_ele, ctx->d_dNtab, d_u, ctx->d_mulf)
+    switch (ctx->celltype)
+    {
+      case FC_HEX8: FC_MULF_HISTORY(fc::HEX8); break;
+      case FC_HEX27: FC_MULF_HISTORY(fc::HEX27); break;
+      case FC_TET10: FC_MULF_HISTORY(fc::TET10); break;
+      case FC_HEX20: FC_MULF_HISTORY(fc::HEX20); break;
+      case FC_TET4: FC_MULF_HISTORY(fc::TET4); break;
+      case FC_WEDGE6: FC_MULF_HISTORY(fc::WEDGE6); break;
+      default: FC_MULF_HISTORY(fc::PYRAMID5); break;
+    }
+#undef FC_MULF_HISTORY
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
   fc::EvalArgs base_args(const fc_ctx* ctx)
   {
     fc::EvalArgs A{};
@@ -212,8 +246,9 @@ namespace
     A.err = ctx->d_err;
     A.mat = ctx->mat;
     A.fiber = ctx->d_fiber;
-  A.fiber_gp = ctx->fiber_gp;
-  A.fiber_ele = ctx->fiber_gp ? ctx->fiber_gp * fc::cell_ngp(ctx->celltype) : 3;
+    A.fiber_gp = ctx->fiber_gp;
+    A.fiber_ele = ctx->fiber_gp ? ctx->fiber_gp * fc::cell_ngp(ctx->celltype) : 3;
+    A.mulf = ctx->d_mulf;
     return A;
   }
 
@@ -234,6 +269,16 @@ namespace
     return FC_OK;
   }
 }  // namespace
+
+// fc_solid_set_mesh: allocate and initialise the prestress history of an FC_FORM_MULF mesh (the stream is synchronised by the caller)
+int fc_mulf_init(fc_ctx* ctx)
+{
+  dev_free(ctx->d_mulf);
+  if (ctx->formulation != FC_FORM_MULF || ctx->n_ele == 0) return FC_OK;
+  FC_CUDA(cudaMalloc((void**)&ctx->d_mulf, sizeof(double) * 18 * (size_t)ctx->n_ele * fc::cell_ngp(ctx->celltype)));
+  FC_CUDA(launch_mulf_history(ctx, nullptr));
+  return FC_OK;
+}
 
 extern "C"
 {
@@ -454,6 +499,50 @@ extern "C"
   {
     if (!ctx || !launches) return FC_ERR_INVALID;
     *launches = ctx->launches;
+    return FC_OK;
+  }
+
+  int fc_solid_update_prestress(fc_ctx* ctx, const double* u_col)
+  {
+    if (!ctx || ctx->celltype < 0 || !u_col) return fail(ctx, FC_ERR_INVALID, "mesh and u_col are required");
+    if (ctx->formulation != FC_FORM_MULF) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF");
+    if (ctx->n_ele == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    double* t_u = nullptr;
+    const double* d_u = u_col;
+    if (!is_device_ptr(u_col))
+    {
+      FC_CUDA(cudaMalloc((void**)&t_u, sizeof(double) * (size_t)ctx->n_col_dof));
+      FC_CUDA(cudaMemcpyAsync(t_u, u_col, sizeof(double) * (size_t)ctx->n_col_dof, cudaMemcpyHostToDevice, ctx->stream));
+      d_u = t_u;
+    }
+    cudaError_t e = launch_mulf_history(ctx, d_u);
+    const cudaError_t es = cudaStreamSynchronize(ctx->stream);
+    if (t_u) cudaFree(t_u);
+    FC_CUDA(e);
+    FC_CUDA(es);
+    return FC_OK;
+  }
+
+  int fc_solid_mulf_get_history(fc_ctx* ctx, double* history)
+  {
+    if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
+    if (ctx->formulation != FC_FORM_MULF) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF");
+    if (ctx->n_ele == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    FC_CUDA(cudaMemcpyAsync(history, ctx->d_mulf, sizeof(double) * 18 * (size_t)ctx->n_ele * fc::cell_ngp(ctx->celltype), cudaMemcpyDefault, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FC_OK;
+  }
+
+  int fc_solid_mulf_set_history(fc_ctx* ctx, const double* history)
+  {
+    if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
+    if (ctx->formulation != FC_FORM_MULF) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF");
+    if (ctx->n_ele == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    FC_CUDA(cudaMemcpyAsync(ctx->d_mulf, history, sizeof(double) * 18 * (size_t)ctx->n_ele * fc::cell_ngp(ctx->celltype), cudaMemcpyDefault, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
     return FC_OK;
   }
 }

@@ -199,10 +199,13 @@ extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int st
   A.fiber = ctx->d_fiber;
   A.fiber_gp = ctx->fiber_gp;
   A.fiber_ele = ctx->fiber_gp ? ctx->fiber_gp * fc::cell_ngp(ctx->celltype) : 3;
-  const bool fbar = ctx->formulation == FC_FORM_FBAR, lin = ctx->formulation == FC_FORM_LINEAR;
+  A.mulf = ctx->d_mulf;
+  const bool fbar = ctx->formulation == FC_FORM_FBAR, lin = ctx->formulation == FC_FORM_LINEAR, mulf = ctx->formulation == FC_FORM_MULF;
   int rc = FC_ERR_UNSUPPORTED;
 #define FC_STRESS(CT) \
-  rc = lin ? stress_impl<CT, fc::FORM_LINEAR>(ctx, A, stress_type, d_gp, d_nodal) : stress_impl<CT, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal)
+  rc = lin    ? stress_impl<CT, fc::FORM_LINEAR>(ctx, A, stress_type, d_gp, d_nodal) \
+       : mulf ? stress_impl<CT, fc::FORM_MULF>(ctx, A, stress_type, d_gp, d_nodal)   \
+              : stress_impl<CT, fc::FORM_DISP>(ctx, A, stress_type, d_gp, d_nodal)
   switch (ctx->celltype)
   {
     case FC_HEX8:

@@ -21,9 +21,43 @@ namespace fc
   {
     FORM_DISP = 0,
     FORM_FBAR = 1,
-    FORM_LINEAR = 2  // KINEM linear: B-operator at F = I, strain = B u, no geometric stiffness
-                     // (src/solid_3D_ele/4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155)
+    FORM_LINEAR = 2,  // KINEM linear: B-operator at F = I, strain = B u, no geometric stiffness
+                      // (src/solid_3D_ele/4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155)
+    FORM_MULF = 3     // PRESTRESS_TECH mulf: F = (I + u N_xyz_hist^T) F_hist with the history of the prestress updates
+                      // (src/solid_3D_ele/4C_solid_3D_ele_calc_mulf.hpp:40-196, ..._calc_lib_mulf.hpp:24-84)
   };
+
+  // MULF: deformation gradient update delta = I + u (invJ_hist dN)^T of one Gauss point.  dN [nen][3], us [nen][3],
+  // invJh row-major; delta row-major [3 i + I]
+  template <int NEN>
+  __device__ __forceinline__ void mulf_delta(const double* __restrict__ dN, const double* us, const double* __restrict__ invJh, double* delta)
+  {
+    for (int i = 0; i < 9; ++i) delta[i] = (i % 4 == 0) ? 1.0 : 0.0;
+    for (int a = 0; a < NEN; ++a)
+    {
+      const double d0 = __ldg(dN + 3 * a), d1 = __ldg(dN + 3 * a + 1), d2 = __ldg(dN + 3 * a + 2);
+      double nh[3];
+      for (int I = 0; I < 3; ++I) nh[I] = invJh[3 * I] * d0 + invJh[3 * I + 1] * d1 + invJh[3 * I + 2] * d2;
+      for (int i = 0; i < 3; ++i)
+        for (int I = 0; I < 3; ++I) delta[3 * i + I] += us[3 * a + i] * nh[I];
+    }
+  }
+  // history record in memory: inverse Jacobian | deformation gradient, both column-major like the Core::LinAlg::Matrix<3, 3>
+  // members of MulfHistoryData; the kernels work on row-major copies
+  __device__ __forceinline__ void mulf_load(const double* __restrict__ hist, double* hl)
+  {
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c)
+      {
+        hl[3 * r + c] = __ldg(hist + r + 3 * c);
+        hl[9 + 3 * r + c] = __ldg(hist + 9 + r + 3 * c);
+      }
+  }
+  __device__ __forceinline__ void mat3_mul(const double* A_, const double* B_, double* C_)
+  {
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) C_[3 * i + j] = A_[3 * i] * B_[j] + A_[3 * i + 1] * B_[3 + j] + A_[3 * i + 2] * B_[6 + j];
+  }
 
   template <int CT, int FORM>
   struct GenCfg
@@ -41,6 +75,68 @@ namespace fc
     static constexpr int ele_doubles = 6 * nen + ngp * gpd;  // X, u, gp records
     static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles + 64;
   };
+
+  // MULF history of every (element, Gauss point), hist [n_ele][ngp][18] = inverse Jacobian | deformation gradient.
+  //   u == nullptr: the state before the first prestress update - inverse Jacobian of the reference mapping (what
+  //                 MulfFormulation::evaluate stores at its first call, calc_mulf.hpp:59-63) and F = I
+  //   u != nullptr: MulfFormulation::update_prestress (calc_mulf.hpp:150-171) with the displacements of the finished step:
+  //                 F_hist <- (I + u N_xyz_hist^T) F_hist,  invJ_hist <- (I + u N_xyz_hist^T)^-T invJ_hist
+  template <int CT>
+  __global__ void k_mulf_history(const double* __restrict__ X, const int* __restrict__ conn, int n_ele, const double* __restrict__ dNtab,
+      const double* __restrict__ u, double* hist)
+  {
+    constexpr int NEN = Cell<CT>::nen, NGP = Cell<CT>::ngp;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= (long long)n_ele * NGP) return;
+    const int e = (int)(tid / NGP), gp = (int)(tid % NGP);
+    const double* dN = dNtab + (size_t)gp * NEN * 3;
+    double* H = hist + (size_t)tid * 18;
+    if (!u)
+    {
+      double J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, iJ[9];
+      for (int a = 0; a < NEN; ++a)
+      {
+        const int n = conn[(size_t)e * NEN + a];
+        for (int d = 0; d < 3; ++d)
+          for (int i = 0; i < 3; ++i) J[3 * d + i] += dN[3 * a + d] * X[3 * (size_t)n + i];
+      }
+      inv3(J, iJ);
+      for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c)
+        {
+          H[r + 3 * c] = iJ[3 * r + c];
+          H[9 + r + 3 * c] = r == c ? 1.0 : 0.0;
+        }
+      return;
+    }
+    double us[3 * NEN], hl[18], delta[9], Ft[9], id[9];
+    for (int a = 0; a < NEN; ++a)
+    {
+      const int n = conn[(size_t)e * NEN + a];
+      for (int i = 0; i < 3; ++i) us[3 * a + i] = u[3 * (size_t)n + i];
+    }
+    for (int r = 0; r < 3; ++r)  // plain loads: the record is rewritten below
+      for (int c = 0; c < 3; ++c)
+      {
+        hl[3 * r + c] = H[r + 3 * c];
+        hl[9 + 3 * r + c] = H[9 + r + 3 * c];
+      }
+    for (int i = 0; i < 9; ++i) delta[i] = (i % 4 == 0) ? 1.0 : 0.0;
+    for (int a = 0; a < NEN; ++a)
+    {
+      double nh[3];
+      for (int I = 0; I < 3; ++I) nh[I] = hl[3 * I] * dN[3 * a] + hl[3 * I + 1] * dN[3 * a + 1] + hl[3 * I + 2] * dN[3 * a + 2];
+      for (int i = 0; i < 3; ++i)
+        for (int I = 0; I < 3; ++I) delta[3 * i + I] += us[3 * a + i] * nh[I];
+    }
+    for (int i = 0; i < 3; ++i)
+      for (int j = 0; j < 3; ++j) Ft[3 * i + j] = delta[3 * i] * hl[9 + j] + delta[3 * i + 1] * hl[12 + j] + delta[3 * i + 2] * hl[15 + j];
+    inv3(delta, id);
+    for (int i = 0; i < 3; ++i)
+      for (int d = 0; d < 3; ++d) H[i + 3 * d] = id[i] * hl[d] + id[3 + i] * hl[3 + d] + id[6 + i] * hl[6 + d];  // delta^-T invJ
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) H[9 + r + 3 * c] = Ft[3 * r + c];
+  }
 
   // J = dN X^T, N_XYZ = J^-1 dN.  dN, Nxyz: [nen][3]; Xs: [nen][3].  returns det J.
   template <int NEN>
@@ -148,7 +244,17 @@ namespace fc
         double* Nx = R + Cfg::oN;
         const double detJ = jacobian_mapping<NEN>(A.dNtab + (size_t)gp * ND, Xs, Nx);
         double F[9];
-        deformation_gradient<CT>(Xs, us, Nx, F);
+        if (FORM == FORM_MULF)
+        {
+          // evaluate_mulf_spatial_material_mapping; the B-operator and K_geo below keep the N_XYZ of the reference mapping
+          const double* hist = A.mulf + ((size_t)e * NGP + gp) * 18;
+          double hl[18], delta[9];
+          mulf_load(hist, hl);
+          mulf_delta<NEN>(A.dNtab + (size_t)gp * ND, us, hl, delta);
+          mat3_mul(delta, hl + 9, F);
+        }
+        else
+          deformation_gradient<CT>(Xs, us, Nx, F);
         const double intfac = detJ * __ldg(A.gpw + gp);
         double fbar = 1.0, iF[9];
         const double detF = FORM == FORM_FBAR ? inv3(F, iF) : (FORM == FORM_LINEAR ? 1.0 : det3(F));

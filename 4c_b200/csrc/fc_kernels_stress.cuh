@@ -29,7 +29,16 @@ namespace fc
     }
     double Nx[ND], F[9];
     jacobian_mapping<NEN>(A.dNtab + (size_t)gp * ND, Xs, Nx);
-    deformation_gradient<CT>(Xs, us, Nx, F);
+    if (FORM == FORM_MULF)
+    {
+      const double* hist = A.mulf + ((size_t)e * NGP + gp) * 18;
+      double hl[18], delta[9];
+      mulf_load(hist, hl);
+      mulf_delta<NEN>(A.dNtab + (size_t)gp * ND, us, hl, delta);
+      mat3_mul(delta, hl + 9, F);
+    }
+    else
+      deformation_gradient<CT>(Xs, us, Nx, F);
     if (FORM == FORM_FBAR)
     {
       double N0[ND], F0[9];

@@ -64,7 +64,9 @@ extern "C"
   {
     FC_FORM_DISPLACEMENT = 0, /* 4C_solid_3D_ele_calc_displacement_based.hpp:35-251 */
     FC_FORM_FBAR = 1,         /* 4C_solid_3D_ele_calc_fbar.hpp:43-191 (hex8 and pyramid5 only) */
-    FC_FORM_LINEAR = 2        /* KINEM linear: 4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155 (every cell) */
+    FC_FORM_LINEAR = 2,       /* KINEM linear: 4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155 (every cell) */
+    FC_FORM_MULF = 3          /* PRESTRESS_TECH mulf: 4C_solid_3D_ele_calc_mulf.hpp:40-196 (every cell); Gauss-point history in the
+                                 context, see fc_solid_update_prestress */
   };
   /* materials: MAT_Struct_StVenantKirchhoff (src/mat/4C_mat_stvenantkirchhoff.cpp) and
    * MAT_ElastHyper with one ELAST_CoupNeoHooke summand (src/mat/4C_mat_elasthyper.cpp,
@@ -143,6 +145,16 @@ extern "C"
   /* FIBER1 of every column element ([n_col_ele][3], host; the element line's FIBER1 x y z, src/solid_3D_ele/4C_solid_3D_ele.cpp:60),
    * normalised like Mat::read_anisotropy_fiber (src/mat/4C_mat_anisotropy_utils.cpp:19-44).  NULL removes them.
    * Call after fc_solid_set_mesh. */
+  /* FC_FORM_MULF (modified updated Lagrangian prestressing).  The context keeps, per column element and Gauss point, the
+   * history of MulfHistoryData (src/solid_3D_ele/4C_solid_3D_ele_calc_lib_mulf.hpp:24-33): 18 doubles = inverse Jacobian
+   * (N_xyz = invJ dN) | deformation gradient, both column-major like the Core::LinAlg::Matrix<3, 3> members; fc_solid_set_mesh initialises it (reference Jacobian,
+   * identity).  fc_solid_update_prestress is struct_update_prestress (Solid::ModelEvaluator::Structure::update_step_element,
+   * 4C_structure_new_model_evaluator_structure.cpp:1555-1592 -> MulfFormulation::update_prestress) with the column
+   * displacements (host|device) of the finished step; the caller resets its displacements afterwards like
+   * Solid::IMPLICIT::PreStress::post_update.  get/set move the history (host|device, [n_col_ele][ngp][18]) for restart files. */
+  int fc_solid_update_prestress(fc_ctx* ctx, const double* u_col);
+  int fc_solid_mulf_get_history(fc_ctx* ctx, double* history);
+  int fc_solid_mulf_set_history(fc_ctx* ctx, const double* history);
   int fc_solid_set_fibers(fc_ctx* ctx, const double* fiber1);
   /* Fibres given at the nodes (FNODE ... FIBER1; anisotropic summands with INIT 3): node_fiber1 [n_col_nodes][3].  The library
    * interpolates them to the Gauss points of the stiffness rule with the element's shape functions and normalises

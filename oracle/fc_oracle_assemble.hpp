@@ -125,7 +125,8 @@ namespace fc_oracle
   inline int evaluate_rank(const Mesh& mesh, const Partition& part, const RankSystem& rs, int form,
       const MaterialParams& mp, int action, const double* u_col, double* f_row, double* K_values,
       int* first_bad, const double* ele_fiber = nullptr /* [n_ele][3] FIBER1 in mesh element order, or [n_ele][ngp][3] */,
-      int fiber_gp_stride = 0 /* 3: ele_fiber holds one fibre per Gauss point */)
+      int fiber_gp_stride = 0 /* 3: ele_fiber holds one fibre per Gauss point */,
+      const double* mulf_hist = nullptr /* FORM_MULF: [n_ele][ngp][18] in mesh element order */)
   {
     const int nen = mesh.nen, nd = 3 * nen;
     std::vector<int> lm(nd), lmowner(nd), localcol(nd);
@@ -152,7 +153,8 @@ namespace fc_oracle
       if (action == 0) std::fill(Ke.begin(), Ke.end(), 0.0);
       const int err = element_evaluate(
           mesh.ct, form, mp, X.data(), u.data(), fe.data(), action == 0 ? Ke.data() : nullptr, nullptr, 0.0, nullptr, STRESS_CAUCHY,
-          ele_fiber ? ele_fiber + (fiber_gp_stride ? (size_t)fiber_gp_stride * num_gp(mesh.ct) : 3) * (size_t)e : nullptr, fiber_gp_stride);
+          ele_fiber ? ele_fiber + (fiber_gp_stride ? (size_t)fiber_gp_stride * num_gp(mesh.ct) : 3) * (size_t)e : nullptr, fiber_gp_stride,
+          mulf_hist ? mulf_hist + (size_t)18 * num_gp(mesh.ct) * e : nullptr);
       if (err)
       {
         if (nbad == 0 && first_bad) *first_bad = eg;
@@ -212,6 +214,7 @@ namespace fc_oracle
     MaterialParams mp{MAT_NEOHOOKE, 10.0, 0.25};
     std::vector<double> ele_fiber;  // [n_ele][3], [n_ele][ngp][3] (fiber_gp_stride = 3) or empty
     int fiber_gp_stride = 0;
+    std::vector<double> mulf_hist;  // [n_ele][ngp][18] when form == FORM_MULF
   };
 
   inline int evaluate_job(const Job& job, int action, const std::vector<std::vector<double>>& u_row,
@@ -226,7 +229,8 @@ namespace fc_oracle
       import_column_state(job.mesh, job.part, job.sys, r, u_row, u_col);
       nbad[r] = evaluate_rank(job.mesh, job.part, job.sys[r], job.form, job.mp, action,
           u_col.data(), f_row[r].data(), action == 0 ? K_values[r].data() : nullptr, &fb[r],
-          job.ele_fiber.empty() ? nullptr : job.ele_fiber.data(), job.fiber_gp_stride);
+          job.ele_fiber.empty() ? nullptr : job.ele_fiber.data(), job.fiber_gp_stride,
+          job.mulf_hist.empty() ? nullptr : job.mulf_hist.data());
     };
     if (max_threads <= 1 || nr == 1)
       for (int r = 0; r < nr; ++r) work(r);

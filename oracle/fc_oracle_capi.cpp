@@ -197,11 +197,79 @@ extern "C"
     return js;
   }
   void oracle_job_destroy(void* h) { delete (JobState*)h; }
+  // FORM_MULF: history of every element as MulfFormulation holds it before the first prestress update
+  static void mulf_init(JobState* js)
+  {
+    js->job.mulf_hist.clear();
+    if (js->job.form != FORM_MULF) return;
+    const Mesh& m = js->job.mesh;
+    const int ngp = num_gp(m.ct);
+    js->job.mulf_hist.assign((size_t)18 * ngp * m.ele_gid.size(), 0.0);
+    std::vector<double> X((size_t)3 * m.nen);
+    for (size_t e = 0; e < m.ele_gid.size(); ++e)
+    {
+      for (int a = 0; a < m.nen; ++a)
+        for (int i = 0; i < 3; ++i) X[3 * a + i] = m.node_X[3 * (size_t)m.node_index.at(m.ele_nodes[e * m.nen + a]) + i];
+      mulf_history(m.ct, X.data(), nullptr, &js->job.mulf_hist[(size_t)18 * ngp * e]);
+    }
+  }
   void oracle_job_set_problem(void* h, int form, int kind, double young, double nue)
   {
     auto* js = (JobState*)h;
     js->job.form = form;
     js->job.mp = MaterialParams{kind, young, nue};
+    mulf_init(js);
+  }
+  // struct_update_prestress with the displacements of the finished step, u_nodes [n_nodes][3] in the mesh's node order
+  void oracle_job_update_prestress(void* h, const double* u_nodes)
+  {
+    auto* js = (JobState*)h;
+    const Mesh& m = js->job.mesh;
+    if (js->job.mulf_hist.empty()) return;
+    const int ngp = num_gp(m.ct);
+    std::vector<double> X((size_t)3 * m.nen), u((size_t)3 * m.nen);
+    for (size_t e = 0; e < m.ele_gid.size(); ++e)
+    {
+      for (int a = 0; a < m.nen; ++a)
+      {
+        const size_t ni = (size_t)m.node_index.at(m.ele_nodes[e * m.nen + a]);
+        for (int i = 0; i < 3; ++i)
+        {
+          X[3 * a + i] = m.node_X[3 * ni + i];
+          u[3 * a + i] = u_nodes[3 * ni + i];
+        }
+      }
+      mulf_history(m.ct, X.data(), u.data(), &js->job.mulf_hist[(size_t)18 * ngp * e]);
+    }
+  }
+  // the job's prestress history [n_ele][ngp][18] (inverse Jacobian | deformation gradient, both column-major); returns its length
+  long long oracle_job_get_mulf_history(void* h, double* hist)
+  {
+    auto* js = (JobState*)h;
+    if (hist) std::copy(js->job.mulf_hist.begin(), js->job.mulf_hist.end(), hist);
+    return (long long)js->job.mulf_hist.size();
+  }
+  // Gauss-point stresses of element e (index in the mesh's element order) with the job's formulation, material, fibres and
+  // history: gp_stress [ngp][6]
+  int oracle_job_element_gp_stress(void* h, int e, const double* u_nodes, int stress_type, double* gp_stress)
+  {
+    auto* js = (JobState*)h;
+    const Mesh& m = js->job.mesh;
+    const int ngp = num_gp(m.ct);
+    std::vector<double> X((size_t)3 * m.nen), u((size_t)3 * m.nen);
+    for (int a = 0; a < m.nen; ++a)
+    {
+      const size_t ni = (size_t)m.node_index.at(m.ele_nodes[(size_t)e * m.nen + a]);
+      for (int i = 0; i < 3; ++i)
+      {
+        X[3 * a + i] = m.node_X[3 * ni + i];
+        u[3 * a + i] = u_nodes[3 * ni + i];
+      }
+    }
+    const Job& job = js->job;
+    const double* fib = job.ele_fiber.empty() ? nullptr : job.ele_fiber.data() + (job.fiber_gp_stride ? (size_t)job.fiber_gp_stride * ngp : 3) * (size_t)e;
+    return element_evaluate(m.ct, job.form, job.mp, X.data(), u.data(), nullptr, nullptr, nullptr, 0.0, gp_stress, stress_type, fib,
+        job.fiber_gp_stride, job.mulf_hist.empty() ? nullptr : job.mulf_hist.data() + (size_t)18 * ngp * e);
   }
   // MAT_ElastHyper with a summand list (kinds [n], par [n][4]) and optional element fibres FIBER1 [n_ele][3] in the job's
   // element order (NULL = none)
@@ -220,6 +288,7 @@ extern "C"
     js->job.ele_fiber.clear();
     js->job.fiber_gp_stride = 0;
     if (ele_fiber) js->job.ele_fiber.assign(ele_fiber, ele_fiber + 3 * js->job.mesh.ele_gid.size());
+    mulf_init(js);
   }
   // one element with a summand list: fe, Ke (col-major), optional Gauss-point stresses
   // nodal fibres (FNODE ... FIBER1, materials with INIT 3): node_fiber [n_nodes][3] in the order of the mesh's nodes;

@@ -31,7 +31,8 @@ namespace fc_oracle
   {
     FORM_DISP = 0,
     FORM_FBAR = 1,
-    FORM_LINEAR = 2  // KINEM linear: src/solid_3D_ele/4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155
+    FORM_LINEAR = 2,  // KINEM linear: src/solid_3D_ele/4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155
+    FORM_MULF = 3     // PRESTRESS_TECH mulf: src/solid_3D_ele/4C_solid_3D_ele_calc_mulf.hpp:40-196, ..._calc_lib_mulf.hpp:24-84
   };
 
   enum EleError
@@ -201,7 +202,8 @@ namespace fc_oracle
   template <int NEN, int NGP>
   inline int element_evaluate_t(int ct, int form, const MaterialParams& mp, const double* X,
       const double* u, double* fe, double* Ke, double* Me, double rho, double* gp_stress = nullptr,
-      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr, int fiber_gp_stride = 0)
+      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr, int fiber_gp_stride = 0,
+      const double* mulf_hist = nullptr /* FORM_MULF: [ngp][18] = inverse_jacobian (9, column-major) | deformation_gradient (9) */)
   {
     constexpr int ND = 3 * NEN;
     double x[ND];
@@ -254,7 +256,24 @@ namespace fc_oracle
 
       double Fmat[9], C[9], E[6];  // what the material sees
       double fbar_factor = 1.0, Hop[ND], Cg[9];
-      if (form == FORM_LINEAR)
+      if (form == FORM_MULF)
+      {
+        // MulfFormulation::evaluate (calc_mulf.hpp:52-90): F = (I + u N_xyz_hist^T) F_hist with N_xyz_hist = invJ_hist dN
+        // (calc_lib_mulf.hpp:34-84); B-operator and geometric stiffness with the N_XYZ of the reference Jacobian mapping
+        const double* invJh = mulf_hist + 18 * gp;
+        const double* Fh = invJh + 9;
+        double Nh[3 * NEN], delta[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+        multiply_nn<3, 3, NEN>(Nh, invJh, dN);
+        multiply_nt_scaled<3, NEN, 3>(1.0, delta, u, Nh, 1.0);
+        multiply_nn<3, 3, 3>(sm.F, delta, Fh);
+        invert3x3(sm.iF, sm.F, &singular);
+        sm.detF = determinant3x3(sm.F);
+        for (int i = 0; i < 9; ++i) Fmat[i] = sm.F[i];
+        multiply_tn<3, 3, 3>(C, sm.F, sm.F);
+        evaluate_green_lagrange_strain(C, E);
+        evaluate_strain_gradient<NEN>(jm.N_XYZ, sm.F, B);
+      }
+      else if (form == FORM_LINEAR)
       {
         // DisplacementBasedLinearKinematicsFormulation::evaluate: gl_strain = B_lin u (calc_lib.hpp:683-695), the material
         // sees the identity as deformation gradient; no geometric stiffness (add_stiffness_matrix, :138-151)
@@ -380,26 +399,78 @@ namespace fc_oracle
     }
   }
 
+  // MULF history of one element, [ngp][18]: inverse_jacobian | deformation_gradient, both 3x3 column-major.
+  // init: what MulfFormulation::evaluate stores at its first call (calc_mulf.hpp:59-63) and the identity of MulfHistoryData.
+  // update: MulfFormulation::update_prestress (calc_mulf.hpp:150-171) with the displacements u of the finished step.
+  template <int NEN, int NGP>
+  inline void mulf_history_t(int ct, const double* X, const double* u /* nullptr = init */, double* hist)
+  {
+    double gxi[NGP][3], gw[NGP];
+    gauss_rule(ct, gxi, gw);
+    for (int gp = 0; gp < NGP; ++gp)
+    {
+      double dN[3 * NEN];
+      shape_function_deriv1(ct, gxi[gp], dN);
+      double* invJh = hist + 18 * gp;
+      double* Fh = invJh + 9;
+      if (!u)
+      {
+        JacobianMapping<NEN> jm;
+        evaluate_jacobian_mapping<NEN>(dN, X, jm, nullptr);
+        for (int i = 0; i < 9; ++i)
+        {
+          invJh[i] = jm.iJ[i];
+          Fh[i] = (i % 4 == 0) ? 1.0 : 0.0;
+        }
+        continue;
+      }
+      double Nh[3 * NEN], delta[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}, Ftot[9], idelta[9], invJ_new[9];
+      multiply_nn<3, 3, NEN>(Nh, invJh, dN);
+      multiply_nt_scaled<3, NEN, 3>(1.0, delta, u, Nh, 1.0);  // evaluate_mulf_deformation_gradient_update
+      multiply_nn<3, 3, 3>(Ftot, delta, Fh);                   // the deformation gradient the evaluation saw
+      invert3x3(idelta, delta, nullptr);
+      multiply_tn<3, 3, 3>(invJ_new, idelta, invJh);
+      for (int i = 0; i < 9; ++i)
+      {
+        Fh[i] = Ftot[i];
+        invJh[i] = invJ_new[i];
+      }
+    }
+  }
+  inline void mulf_history(int ct, const double* X, const double* u, double* hist)
+  {
+    switch (ct)
+    {
+      case HEX8: return mulf_history_t<8, 8>(ct, X, u, hist);
+      case HEX27: return mulf_history_t<27, 27>(ct, X, u, hist);
+      case TET10: return mulf_history_t<10, 4>(ct, X, u, hist);
+      case HEX20: return mulf_history_t<20, 27>(ct, X, u, hist);
+      case TET4: return mulf_history_t<4, 1>(ct, X, u, hist);
+      case WEDGE6: return mulf_history_t<6, 6>(ct, X, u, hist);
+      case PYRAMID5: return mulf_history_t<5, 8>(ct, X, u, hist);
+    }
+  }
+
   inline int element_evaluate(int ct, int form, const MaterialParams& mp, const double* X,
       const double* u, double* fe, double* Ke, double* Me = nullptr, double rho = 0.0, double* gp_stress = nullptr,
-      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr, int fiber_gp_stride = 0)
+      int stress_type = STRESS_CAUCHY, const double* fiber = nullptr, int fiber_gp_stride = 0, const double* mulf_hist = nullptr)
   {
     switch (ct)
     {
       case HEX8:
-        return element_evaluate_t<8, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
+        return element_evaluate_t<8, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
       case HEX27:
-        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
+        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
       case TET10:
-        return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
+        return element_evaluate_t<10, 4>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
       case HEX20:
-        return element_evaluate_t<20, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
+        return element_evaluate_t<20, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
       case TET4:
-        return element_evaluate_t<4, 1>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
+        return element_evaluate_t<4, 1>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
       case WEDGE6:
-        return element_evaluate_t<6, 6>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
+        return element_evaluate_t<6, 6>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
       case PYRAMID5:
-        return element_evaluate_t<5, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride);
+        return element_evaluate_t<5, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
     }
     return -1;
   }

@@ -59,6 +59,12 @@ CASES = [
     "solid_ele_hex8_Standard_eas_none_nodal_fibers.dat",
     "solid_ele_tet4_Standard_nodal_fibers.dat",
     "solid_ele_tet10_Standard_nodal_fibers.dat",
+    # PRESTRESS mulf (PRESTRESS_TECH mulf): two prestress steps, then eight load steps; displacements and nodal stresses
+    "solid_ele_hex8_Standard_mulf.dat",
+    "solid_ele_hex20_Standard_mulf.dat",
+    "solid_ele_tet4_Standard_mulf.dat",
+    "solid_ele_wedge6_Standard_mulf.dat",
+    "solid_ele_pyramid5_Standard_mulf.dat",
 ]
 
 

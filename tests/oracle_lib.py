@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
-FORM_DISP, FORM_FBAR = 0, 1
+FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF = 0, 1, 2, 3
 MAT_SVK, MAT_NEOHOOKE = 0, 1
 ACTION_NLNSTIFF, ACTION_INTERNALFORCE = 0, 1
 NEN = {HEX8: 8, HEX27: 27, TET10: 10, HEX20: 20, TET4: 4, WEDGE6: 6, PYRAMID5: 5}
@@ -258,6 +258,24 @@ class Job:
     def set_nodal_fibers(self, node_fibers):
         """node_fibers: (n_nodes, 3) FIBER1 of the FNODEs in the order of self.node_gid; call after set_elasthyper"""
         lib.oracle_job_set_nodal_fibers(self.h, _p(_d(node_fibers)))
+
+    def update_prestress(self, u_nodes):
+        """struct_update_prestress (PRESTRESS_TECH mulf) with the displacements of the finished step, (n_nodes, 3)"""
+        lib.oracle_job_update_prestress(self.h, _p(_d(u_nodes)))
+
+    def mulf_history(self):
+        """(n_ele, ngp, 18) inverse Jacobian | deformation gradient of every Gauss point (empty unless FORM_MULF)"""
+        lib.oracle_job_get_mulf_history.restype = C.c_longlong
+        n = lib.oracle_job_get_mulf_history(self.h, None)
+        out = np.zeros(n)
+        lib.oracle_job_get_mulf_history(self.h, _p(out))
+        return out.reshape(-1, NGP[self.ct], 18)
+
+    def element_gp_stress(self, e, u_nodes, stress_type=1):
+        """(ngp, 6) Gauss-point stresses of element e with the job's formulation, material, fibres and history"""
+        out = np.zeros((NGP[self.ct], 6))
+        err = lib.oracle_job_element_gp_stress(self.h, C.c_int(e), _p(_d(u_nodes)), C.c_int(stress_type), _p(out))
+        return err, out
 
     def rank(self, r):
         sizes = np.zeros(8, np.int64)

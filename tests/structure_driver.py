@@ -83,9 +83,10 @@ class Problem:
                         i = t.index("FIBER1")
                         fib.append([float(x) for x in t[i + 1:i + 4]])
                     self.fibers = np.array(fib)
-        techs = {(2 if "KINEM linear" in e["opts"] else (1 if "TECH fbar" in e["opts"] else 0)) for e in fx["elements"]}
+        techs = {(3 if "PRESTRESS_TECH mulf" in e["opts"] else (2 if "KINEM linear" in e["opts"] else (1 if "TECH fbar" in e["opts"] else 0)))
+                 for e in fx["elements"]}
         assert len(techs) == 1
-        self.form = techs.pop()  # FC_FORM_DISPLACEMENT / FC_FORM_FBAR / FC_FORM_LINEAR
+        self.form = techs.pop()  # FC_FORM_DISPLACEMENT / FC_FORM_FBAR / FC_FORM_LINEAR / FC_FORM_MULF
         self.dens = float(m1[m1.index("DENS") + 1])
         self.young = float(m10[m10.index("YOUNG") + 1])
         self.nue = float(m10[m10.index("NUE") + 1])
@@ -93,6 +94,8 @@ class Problem:
         dyn = fx["dynamic"]
         self.dt, self.numstep = float(dyn["TIMESTEP"]), int(dyn["NUMSTEP"])
         self.dynamic = dyn["DYNAMICTYPE"]
+        # PRESTRESS mulf: steps with t <= PRESTRESSTIME end with struct_update_prestress and a reset of the displacements
+        self.prestress_time = float(dyn["PRESTRESSTIME"]) if dyn.get("PRESTRESS", "none").lower() == "mulf" else None
         # Dirichlet: all values are zero in these inputs
         fixed = []
         for c in fx["dirich"]:
@@ -330,10 +333,14 @@ def _converged(norms, inc, newton_tol):
     return len(norms) > 2 and norms[-1] < 1e-9 * max(norms) and norms[-1] > 0.5 * norms[-2]
 
 
-def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None):
+def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, update_prestress=None):
     """assemble(d) -> (f_int [n], K dense [n, n]); mass() -> M dense.  Returns d at MAXTIME and the residual
     norm history of every step (list of lists).  solve(A, rhs, fixed) replaces the dense direct solve (A is then
-    whatever assemble/mass return, e.g. device-resident CSR values supporting a*A + b*B and A @ x)."""
+    whatever assemble/mass return, e.g. device-resident CSR values supporting a*A + b*B and A @ x).
+    update_prestress(d): the element action of a MULF prestress step (problems with PRESTRESS mulf): after a step with
+    t <= PRESTRESSTIME the elements update their history and the displacements are reset
+    (Solid::ModelEvaluator::Structure::update_step_element, 4C_structure_new_model_evaluator_structure.cpp:1555-1592;
+    Solid::IMPLICIT::PreStress::post_update, 4C_structure_new_impl_prestress.cpp)."""
     _solve = solve or globals()["_solve"]
     p = problem
     n, fixed, dt = p.n_dof, p.fixed, p.dt
@@ -353,6 +360,9 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None):
                 if _converged(norms, inc, newton_tol):
                     break
             history.append(norms)
+            if p.prestress_time is not None and step * dt <= p.prestress_time + 1.0e-15:
+                update_prestress(d)
+                d = np.zeros(n)
         return d, history
 
     assert p.dynamic == "GenAlpha"

@@ -48,6 +48,12 @@ CASES = [
     "solid_ele_hex8_Standard_eas_none_nodal_fibers",
     "solid_ele_tet4_Standard_nodal_fibers",
     "solid_ele_tet10_Standard_nodal_fibers",
+    # PRESTRESS mulf
+    "solid_ele_hex8_Standard_mulf",
+    "solid_ele_hex20_Standard_mulf",
+    "solid_ele_tet4_Standard_mulf",
+    "solid_ele_wedge6_Standard_mulf",
+    "solid_ele_pyramid5_Standard_mulf",
 ]
 
 
@@ -77,6 +83,7 @@ def oracle_backend(oracle, p):
             dofs = (3 * en[:, None] + np.arange(3)).reshape(-1)
             M[np.ix_(dofs, dofs)] += Me
         return M
+    assemble.job = job  # prestress update and Gauss-point stresses with the job's history
     return assemble, mass
 
 
@@ -85,7 +92,7 @@ def test_reference_result_description_oracle(oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     p.neumann = sd.OracleNeumann(oracle, p)
     assemble, mass = oracle_backend(oracle, p)
-    d, hist = sd.run(p, assemble, mass)
+    d, hist = sd.run(p, assemble, mass, update_prestress=lambda dd: assemble.job.update_prestress(dd.reshape(-1, 3)))
     err, n = p.result_error(d)  # in units of the reference's TOLERANCE of each value (1e-12; Cook: 1e-8)
     assert n >= 1
     assert err <= 1.0, (case, err, hist)
@@ -122,7 +129,7 @@ def test_reference_result_description_cuda(fc, oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     s, assemble, mass = cuda_backend(fc, p)
     p.neumann = sd.CudaNeumann(s)  # f_ext from fc_solid_neumann_surface / _volume
-    d, hist = sd.run(p, assemble, mass)
+    d, hist = sd.run(p, assemble, mass, update_prestress=s.update_prestress)  # PRESTRESS_TECH mulf: fc_solid_update_prestress
     err, n = p.result_error(d)
     assert err <= 1.0, (case, err, hist)
     # the external force of the library against the oracle's, at the end time
@@ -134,7 +141,10 @@ def test_reference_result_description_cuda(fc, oracle, case):
     assert np.max(np.abs(fe_cuda - fe_ref)) <= 1e-13 * np.max(np.abs(fe_ref))
     # same Newton history as the oracle-driven solve (north_star: iteration counts and residual norms match)
     a2, m2 = oracle_backend(oracle, p)
-    d2, hist2 = sd.run(p, a2, m2)
+    d2, hist2 = sd.run(p, a2, m2, update_prestress=lambda dd: a2.job.update_prestress(dd.reshape(-1, 3)))
+    if p.form == 3:  # the Gauss-point histories after the prestress steps
+        h1, h2 = s.mulf_history(), a2.job.mulf_history()
+        assert np.max(np.abs(h1 - h2)) <= 1e-10 * np.max(np.abs(h2))
     # ... compared down to the rounding floor of the residual.  The near-incompressible Cook problem (nu = 0.4999,
     # condition ~1e8) amplifies last-bit differences of K (FP64 reductions arrive in any order) to ~1e-5 in the
     # Newton iterates, so the norms are compared to 1e-3 here; the strict comparison (1e-10) lives in
@@ -174,7 +184,8 @@ STRESS_CASES = ["solid_ele_hex8_Standard_eas_none_stressout", "solid_ele_hex27_S
                 "solid_ele_hex8_Standard_fbar", "solid_ele_hex20_Standard_stressout", "solid_ele_tet4_Standard_stressout",
                 "solid_ele_wedge6_Standard_stressout", "solid_ele_pyramid5_Standard_stressout", "solid_ele_pyramid5_Standard_fbar",
                 "solid_ele_hex8_Standard_linear", "solid_ele_hex20_Standard_linear", "solid_ele_tet4_Standard_linear",
-                "solid_ele_pyramid5_Standard_linear"]
+                "solid_ele_pyramid5_Standard_linear", "solid_ele_hex8_Standard_mulf", "solid_ele_hex20_Standard_mulf",
+                "solid_ele_tet4_Standard_mulf", "solid_ele_wedge6_Standard_mulf", "solid_ele_pyramid5_Standard_mulf"]
 
 
 def oracle_gp_stress(oracle, p, U, e, st):
@@ -191,10 +202,13 @@ def test_reference_nodal_stresses_oracle(oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     p.neumann = sd.OracleNeumann(oracle, p)
     assemble, mass = oracle_backend(oracle, p)
-    d, _ = sd.run(p, assemble, mass)
+    d, _ = sd.run(p, assemble, mass, update_prestress=lambda dd: assemble.job.update_prestress(dd.reshape(-1, 3)))
     E = sd.extrapolation_matrix(p.ct, oracle.gauss_rule(p.ct)[0], oracle.shape, oracle.node_param_coords(p.ct))
     U = d.reshape(-1, 3)
-    nodal = sd.nodal_stresses(p, lambda e: oracle_gp_stress(oracle, p, U, e, 1), E)
+    if p.form == 3:  # MULF: the stresses need the history the job holds after the prestress steps
+        nodal = sd.nodal_stresses(p, lambda e: assemble.job.element_gp_stress(e, U, 1)[1], E)
+    else:
+        nodal = sd.nodal_stresses(p, lambda e: oracle_gp_stress(oracle, p, U, e, 1), E)
     err, n = sd.stress_result_error(p, nodal)
     assert n >= 24 and err <= 1.0, (case, err, n)
 
@@ -207,7 +221,17 @@ def test_reference_nodal_stresses_cuda(fc, oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     s, assemble, mass = cuda_backend(fc, p)
     p.neumann = sd.CudaNeumann(s)
-    d, _ = sd.run(p, assemble, mass)
+    job = None
+    if p.form == 3:  # MULF: an oracle job that sees the same prestress updates holds the history for the comparison below
+        job = oracle_backend(oracle, p)[0].job
+
+    def update(dd):
+        s.update_prestress(dd)
+        job.update_prestress(dd.reshape(-1, 3))
+    d, _ = sd.run(p, assemble, mass, update_prestress=update)
+    if job is not None:
+        h1, h2 = s.mulf_history(), job.mulf_history()
+        assert np.max(np.abs(h1 - h2)) <= 1e-13 * np.max(np.abs(h2))
     gp, nodal = s.evaluate_stress(d, fc.FC_STRESS_CAUCHY)
     err, n = sd.stress_result_error(p, nodal)
     assert n >= 24 and err <= 1.0, (case, err, n)
@@ -215,6 +239,6 @@ def test_reference_nodal_stresses_cuda(fc, oracle, case):
     for st in (fc.FC_STRESS_2PK, fc.FC_STRESS_CAUCHY):
         gp, _ = s.evaluate_stress(d, st, want_nodal=False)
         for e in range(len(p.conn)):
-            ref = oracle_gp_stress(oracle, p, U, e, st)
+            ref = job.element_gp_stress(e, U, st)[1] if job is not None else oracle_gp_stress(oracle, p, U, e, st)
             assert np.max(np.abs(gp[e] - ref)) <= 1e-12 * np.max(np.abs(ref))
     s.close()

@@ -148,3 +148,62 @@ def test_stress_output(fc, oracle, name, form):
         s.evaluate_stress_noalloc(torch.from_numpy(u.reshape(-1)).cuda(), torch.zeros((len(X), 6), dtype=torch.float64, device="cuda"))
     assert ei.value.code == fc.FC_ERR_UNSUPPORTED
     s.close()
+
+
+@pytest.mark.parametrize("name,mat", [("solid_ele_hex8_Standard_eas_none_dynamic", NH), ("solid_ele_hex27_Standard_dynamic", NH),
+                                      ("solid_ele_tet10_Standard_dynamic", SVK), ("solid_ele_hex20_Standard_dynamic", NH),
+                                      ("solid_ele_tet4_Standard_dynamic", NH), ("solid_ele_wedge6_Standard_dynamic", SVK),
+                                      ("solid_ele_pyramid5_Standard_dynamic", NH)])
+def test_mulf_prestress_parity(fc, oracle, name, mat):
+    """PRESTRESS_TECH mulf on every cell type: two prestress updates with different displacements, then the assembled system, the
+    Gauss-point stresses and the history itself against an oracle job that saw the same updates; history round trip."""
+    MULF = fc.FC_FORM_MULF
+    p, X, u = distorted(oracle, name)
+    ct, conn = p.ct, p.conn
+    s = fc.Solid(0)
+    s.set_mesh(ct, MULF, X, p.node_gid, np.zeros(len(X), np.int32), conn, p.ele_gid)
+    s.set_material(mat, 10.0, 0.3)
+    n_row, n_col, nnz = s.build_graph()
+    job = oracle.Job.from_mesh(ct, p.node_gid, X, p.ele_gid, p.node_gid[conn])
+    job.set_problem(MULF, mat, 10.0, 0.3)
+    o = job.rank(0)
+    assert np.max(np.abs(s.mulf_history() - job.mulf_history())) <= 1e-14 * np.max(np.abs(job.mulf_history()))
+    for k, uk in enumerate((0.6 * u, -0.3 * u[::-1])):
+        s.update_prestress(uk.reshape(-1) if k == 0 else __import__("torch").from_numpy(np.ascontiguousarray(uk.reshape(-1))).cuda())
+        job.update_prestress(uk)
+        h_ref = job.mulf_history()
+        assert np.max(np.abs(s.mulf_history() - h_ref)) <= 1e-14 * np.max(np.abs(h_ref))
+    job.set_u_nodal(u)
+    assert job.evaluate(oracle.ACTION_NLNSTIFF)[0] == 0
+    f_ref, K_ref = job.get_f(0, n_row), job.get_K(0, o["nnz"])
+    rowptr, _ = s.get_graph()
+    K, f = np.zeros(nnz), np.zeros(n_row)
+    assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u.reshape(-1), f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+    starts = np.asarray(rowptr[:-1], np.int64)
+    assert np.max(np.maximum.reduceat(np.abs(K - K_ref), starts) / np.maximum.reduceat(np.abs(K_ref), starts)) <= TOL
+    assert np.max(np.abs(f - f_ref)) <= TOL * max(np.max(np.abs(f_ref)), np.max(np.abs(K_ref)))
+    f2 = np.zeros(n_row)
+    assert s.evaluate(fc.FC_ACTION_INTERNALFORCE, u.reshape(-1), f2, None, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+    assert np.max(np.abs(f2 - f)) <= 1e-14 * np.max(np.abs(f))
+    for st in (fc.FC_STRESS_2PK, fc.FC_STRESS_CAUCHY):
+        gp, _ = s.evaluate_stress(u.reshape(-1), st, want_nodal=False)
+        for e in range(len(conn)):
+            ref = job.element_gp_stress(e, u, st)[1]
+            assert np.max(np.abs(gp[e] - ref)) <= 1e-12 * np.max(np.abs(ref))
+    # restart: the history moved to a fresh context reproduces the system; the unsupported operators say so
+    s2 = fc.Solid(0)
+    s2.set_mesh(ct, MULF, X, p.node_gid, np.zeros(len(X), np.int32), conn, p.ele_gid)
+    s2.set_material(mat, 10.0, 0.3)
+    s2.build_graph()
+    s2.set_mulf_history(s.mulf_history())
+    K2, f3 = np.zeros(nnz), np.zeros(n_row)
+    assert s2.evaluate(fc.FC_ACTION_NLNSTIFF, u.reshape(-1), f3, K2, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+    assert np.max(np.abs(K2 - K)) <= 1e-14 * np.max(np.abs(K)) and np.max(np.abs(f3 - f)) <= 1e-14 * np.max(np.abs(f))
+    s2.close()
+    s3 = fc.Solid(0)
+    s3.set_mesh(ct, DISP, X, p.node_gid, np.zeros(len(X), np.int32), conn, p.ele_gid)
+    with pytest.raises(fc.FourCError) as ei:
+        s3.update_prestress(u.reshape(-1))
+    assert ei.value.code == fc.FC_ERR_INVALID
+    s3.close()
+    s.close()

@@ -13,7 +13,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
 
 FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
-FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR, FC_FORM_MULF = 0, 1, 2, 3
+FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR, FC_FORM_MULF, FC_FORM_EAS_MILD, FC_FORM_EAS_FULL = 0, 1, 2, 3, 4, 5
+FC_STRAIN_GL, FC_STRAIN_EA, FC_STRAIN_LOG = 0, 1, 2
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_SUMMAND_COUPNEOHOOKE, FC_SUMMAND_COUPSVK, FC_SUMMAND_COUPANISOEXPO = 0, 1, 2
 FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
@@ -32,7 +33,7 @@ NGP = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4, FC_HEX20: 27, FC_TET4: 1, FC_WEDGE
 
 EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
-    "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_material_elasthyper", "fc_solid_set_fibers", "fc_solid_set_nodal_fibers", "fc_solid_update_prestress", "fc_solid_mulf_get_history", "fc_solid_mulf_set_history", "fc_solid_set_graph", "fc_solid_build_graph",
+    "fc_solid_set_mesh", "fc_solid_set_material", "fc_solid_set_material_elasthyper", "fc_solid_set_fibers", "fc_solid_set_nodal_fibers", "fc_solid_update_prestress", "fc_solid_recover", "fc_solid_eas_history_doubles", "fc_solid_eas_get_history", "fc_solid_eas_set_history", "fc_solid_evaluate_strain", "fc_solid_mulf_get_history", "fc_solid_mulf_set_history", "fc_solid_set_graph", "fc_solid_build_graph",
     "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
     "fc_solid_error_state", "fc_solid_error_allreduce", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_neumann_surface", "fc_solid_neumann_volume",
     "fc_solid_neumann_surface_gp_coords", "fc_solid_neumann_volume_gp_coords", "fc_solid_evaluate_elements",
@@ -272,6 +273,21 @@ class Solid:
         """FC_FORM_MULF: fold the displacements of the finished step into the Gauss-point history (the caller resets them)"""
         self._chk(lib().fc_solid_update_prestress(self.h, _ptr(u_col if hasattr(u_col, "data_ptr") else _f64(u_col))))
 
+    def recover(self, du_col, step_length=1.0):
+        """struct_calc_recover (EAS): alpha += step_length * alpha_inc(du_col); a no-op for formulations without condensed variables"""
+        self._chk(lib().fc_solid_recover(self.h, _ptr(du_col if hasattr(du_col, "data_ptr") else _f64(du_col)), C.c_double(step_length)))
+
+    def eas_history(self):
+        """(n_col_ele, 3 n + n^2 + 24 n + 1): alpha_inc | alpha | s | Kaa^-1 | Kda | old_step_length of every element"""
+        n = C.c_int()
+        self._chk(lib().fc_solid_eas_history_doubles(self.h, C.byref(n)))
+        h = np.zeros((self.n_ele, n.value))
+        self._chk(lib().fc_solid_eas_get_history(self.h, _ptr(h)))
+        return h
+
+    def set_eas_history(self, history):
+        self._chk(lib().fc_solid_eas_set_history(self.h, _ptr(_f64(history))))
+
     def mulf_history(self):
         """(n_col_ele, ngp, 18) inverse Jacobian | deformation gradient of every Gauss point"""
         h = np.zeros((self.n_ele, NGP[self.celltype], 18))
@@ -429,6 +445,14 @@ class Solid:
         gp = np.zeros((self.n_ele, ngp, 6)) if want_gp else None
         nodal = np.zeros((self.n_row_dof // 3, 6)) if want_nodal else None
         self._chk(lib().fc_solid_evaluate_stress(self.h, _ptr(u_col), C.c_int(stress_type), _ptr(gp), _ptr(nodal)))
+        return gp, nodal
+
+    def evaluate_strain(self, u_col, strain_type=0, want_gp=True, want_nodal=True):
+        """(gp_strain [n_ele, ngp, 6], nodal_strain [n_row_nodes, 6]); 0 = Green-Lagrange, 1 = Euler-Almansi, 2 = logarithmic"""
+        ngp = NGP[self.celltype]
+        gp = np.zeros((self.n_ele, ngp, 6)) if want_gp else None
+        nodal = np.zeros((self.n_row_dof // 3, 6)) if want_nodal else None
+        self._chk(lib().fc_solid_evaluate_strain(self.h, _ptr(u_col), C.c_int(strain_type), _ptr(gp), _ptr(nodal)))
         return gp, nodal
 
     def evaluate_stress_noalloc(self, u_col_dev, nodal_dev, stress_type=1):

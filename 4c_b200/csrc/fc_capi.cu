@@ -96,6 +96,7 @@ extern "C"
     dev_free(ctx->d_geom);
     dev_free(ctx->d_fiber);
     dev_free(ctx->d_mulf);
+    dev_free(ctx->d_eas);
     dev_free(ctx->d_ele_perm);
     dev_free(ctx->d_node_rowbase);
     dev_free(ctx->d_node_rowlen);
@@ -240,8 +241,9 @@ extern "C"
     (void)node_gid;
     if (celltype < FC_HEX8 || celltype > FC_PYRAMID5) return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
     if (formulation != FC_FORM_DISPLACEMENT && formulation != FC_FORM_LINEAR && formulation != FC_FORM_MULF &&
-        !(formulation == FC_FORM_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)))
-      return fail(ctx, FC_ERR_UNSUPPORTED, "F-bar exists for hex8 and pyramid5 only (4C_solid_3D_ele_factory.hpp:49-50)");
+        !(formulation == FC_FORM_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)) &&
+        !((formulation == FC_FORM_EAS_MILD || formulation == FC_FORM_EAS_FULL) && celltype == FC_HEX8))
+      return fail(ctx, FC_ERR_UNSUPPORTED, "F-bar exists for hex8 and pyramid5, EAS for hex8 only (4C_solid_3D_ele_factory.hpp:49-60)");
     FC_CUDA(cudaSetDevice(ctx->device));
     const int nen = fc::cell_nen(celltype);
     // owned nodes first (Epetra column-map convention)

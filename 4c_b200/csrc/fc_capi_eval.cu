@@ -9,6 +9,7 @@
 #include "fc_host_util.hpp"
 #include "fc_kernels_generic.cuh"
 #include "fc_kernels_hex8nh.cuh"
+#include "fc_kernels_hex8eas.cuh"
 #include "fc_kernels_hex8nh_brick.cuh"
 #include "fc_kernels_hex8nh_mma.cuh"
 #include "fc_kernels_hex8_mma_ext.cuh"
@@ -29,6 +30,18 @@ namespace
     if (e != cudaSuccess) return e;
     const int grid = (A.n_ele + Cfg::epb - 1) / Cfg::epb;
     kern<<<grid, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
+  template <int NEAS, bool WANT_K>
+  cudaError_t launch_hex8_eas(fc_ctx* ctx, const fc::EvalArgs& A)
+  {
+    using Cfg = fc::EasCfg<NEAS>;
+    auto kern = fc::k_hex8_eas<NEAS, WANT_K>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+    if (e != cudaSuccess) return e;
+    kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
     ctx->launches++;
     return cudaGetLastError();
   }
@@ -154,7 +167,7 @@ namespace
   bool follows_launch_order(const fc_ctx* ctx, int flags)
   {
     if (flags & FC_EVAL_FORCE_GENERIC) return false;
-    if (ctx->formulation == FC_FORM_LINEAR || ctx->formulation == FC_FORM_MULF) return false;
+    if (ctx->formulation >= FC_FORM_LINEAR) return false;  // linear, MULF, EAS: k_generic / k_hex8_eas
     const bool fbar = ctx->formulation == FC_FORM_FBAR, nh = ctx->mat.kind == fc::MAT_NEOHOOKE;
     if (ctx->celltype == FC_HEX8) return nh ? (fbar || !(flags & FC_EVAL_CLOSED_FORM_FMA)) : (ctx->mat.kind == fc::MAT_SVK && !fbar);  // k_hex8_neohooke_mma, k_hex8_mma_ext
     if (ctx->celltype != FC_HEX27 && ctx->celltype != FC_TET10) return false;                      // k_generic
@@ -175,6 +188,8 @@ namespace
         case FC_WEDGE6: return launch_generic<fc::WEDGE6, fc::FORM_LINEAR, WANT_K>(ctx, A);
         default: return launch_generic<fc::PYRAMID5, fc::FORM_LINEAR, WANT_K>(ctx, A);
       }
+    if (ctx->formulation == FC_FORM_EAS_MILD) return launch_hex8_eas<9, WANT_K>(ctx, A);
+    if (ctx->formulation == FC_FORM_EAS_FULL) return launch_hex8_eas<21, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_MULF)  // PRESTRESS_TECH mulf: same kernel, F from the Gauss-point history
       switch (ctx->celltype)
       {
@@ -249,6 +264,7 @@ namespace
     A.fiber_gp = ctx->fiber_gp;
     A.fiber_ele = ctx->fiber_gp ? ctx->fiber_gp * fc::cell_ngp(ctx->celltype) : 3;
     A.mulf = ctx->d_mulf;
+    A.eas = ctx->d_eas;
     return A;
   }
 
@@ -270,10 +286,25 @@ namespace
   }
 }  // namespace
 
-// fc_solid_set_mesh: allocate and initialise the prestress history of an FC_FORM_MULF mesh (the stream is synchronised by the caller)
+static int eas_doubles(const fc_ctx* ctx)
+{
+  return ctx->formulation == FC_FORM_EAS_MILD ? fc::EasCfg<9>::hist_doubles : (ctx->formulation == FC_FORM_EAS_FULL ? fc::EasCfg<21>::hist_doubles : 0);
+}
+
+// fc_solid_set_mesh: allocate and initialise the element history of an FC_FORM_MULF / FC_FORM_EAS_* mesh (the stream is
+// synchronised by the caller)
 int fc_mulf_init(fc_ctx* ctx)
 {
   dev_free(ctx->d_mulf);
+  dev_free(ctx->d_eas);
+  if (eas_doubles(ctx) && ctx->n_ele > 0)
+  {
+    const long long n = (long long)ctx->n_ele * eas_doubles(ctx);
+    FC_CUDA(cudaMalloc((void**)&ctx->d_eas, sizeof(double) * (size_t)n));
+    fc::k_eas_history_init<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->n_ele, eas_doubles(ctx), ctx->d_eas);
+    ctx->launches++;
+    FC_CUDA(cudaGetLastError());
+  }
   if (ctx->formulation != FC_FORM_MULF || ctx->n_ele == 0) return FC_OK;
   FC_CUDA(cudaMalloc((void**)&ctx->d_mulf, sizeof(double) * 18 * (size_t)ctx->n_ele * fc::cell_ngp(ctx->celltype)));
   FC_CUDA(launch_mulf_history(ctx, nullptr));
@@ -542,6 +573,63 @@ extern "C"
     if (ctx->n_ele == 0) return FC_OK;
     FC_CUDA(cudaSetDevice(ctx->device));
     FC_CUDA(cudaMemcpyAsync(ctx->d_mulf, history, sizeof(double) * 18 * (size_t)ctx->n_ele * fc::cell_ngp(ctx->celltype), cudaMemcpyDefault, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FC_OK;
+  }
+
+  int fc_solid_recover(fc_ctx* ctx, const double* du_col, double step_length)
+  {
+    if (!ctx || ctx->celltype < 0 || !du_col) return fail(ctx, FC_ERR_INVALID, "mesh and du_col are required");
+    if (!eas_doubles(ctx)) return FC_OK;  // no condensed variables: nothing to recover (SolidEleCalc::recover, calc.cpp:244-273)
+    if (ctx->n_ele == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    double* t_u = nullptr;
+    const double* d_u = du_col;
+    if (!is_device_ptr(du_col))
+    {
+      FC_CUDA(cudaMalloc((void**)&t_u, sizeof(double) * (size_t)ctx->n_col_dof));
+      FC_CUDA(cudaMemcpyAsync(t_u, du_col, sizeof(double) * (size_t)ctx->n_col_dof, cudaMemcpyHostToDevice, ctx->stream));
+      d_u = t_u;
+    }
+    const unsigned gs = (unsigned)((ctx->n_ele + 7) / 8);
+    if (ctx->formulation == FC_FORM_EAS_MILD)
+      fc::k_hex8_eas_recover<9><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
+    else
+      fc::k_hex8_eas_recover<21><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
+    ctx->launches++;
+    const cudaError_t e = cudaGetLastError();
+    const cudaError_t es = t_u ? cudaStreamSynchronize(ctx->stream) : cudaSuccess;  // device input: stays asynchronous
+    if (t_u) cudaFree(t_u);
+    FC_CUDA(e);
+    FC_CUDA(es);
+    return FC_OK;
+  }
+
+  int fc_solid_eas_history_doubles(const fc_ctx* ctx, int* doubles_per_element)
+  {
+    if (!ctx || !doubles_per_element) return FC_ERR_INVALID;
+    *doubles_per_element = eas_doubles(ctx);
+    return FC_OK;
+  }
+
+  int fc_solid_eas_get_history(fc_ctx* ctx, double* history)
+  {
+    if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
+    if (!eas_doubles(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_EAS_MILD / FC_FORM_EAS_FULL");
+    if (ctx->n_ele == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    FC_CUDA(cudaMemcpyAsync(history, ctx->d_eas, sizeof(double) * (size_t)ctx->n_ele * eas_doubles(ctx), cudaMemcpyDefault, ctx->stream));
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
+    return FC_OK;
+  }
+
+  int fc_solid_eas_set_history(fc_ctx* ctx, const double* history)
+  {
+    if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
+    if (!eas_doubles(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_EAS_MILD / FC_FORM_EAS_FULL");
+    if (ctx->n_ele == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    FC_CUDA(cudaMemcpyAsync(ctx->d_eas, history, sizeof(double) * (size_t)ctx->n_ele * eas_doubles(ctx), cudaMemcpyDefault, ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
     return FC_OK;
   }

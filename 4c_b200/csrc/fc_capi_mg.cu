@@ -185,7 +185,7 @@ extern "C"
     if (ctx->celltype != FC_HEX8 || ctx->nranks != 1 || ctx->n_col_nodes != ctx->n_row_nodes)
       return fail(ctx, FC_ERR_UNSUPPORTED, "the geometric multigrid hierarchy needs a hex8 mesh on one rank");
     if (ctx->d_fiber) return fail(ctx, FC_ERR_UNSUPPORTED, "element fibres are not carried to the coarse levels");
-    if (ctx->formulation == FC_FORM_MULF) return fail(ctx, FC_ERR_UNSUPPORTED, "the prestress history is not carried to the coarse levels");
+    if (ctx->formulation >= FC_FORM_MULF) return fail(ctx, FC_ERR_UNSUPPORTED, "element histories (MULF, EAS) are not carried to the coarse levels");
     FC_CUDA(cudaSetDevice(ctx->device));
     fc_mg_free(ctx);
     if (max_levels < 2) max_levels = 2;

@@ -182,7 +182,7 @@ extern "C" int fc_solid_evaluate_stress_noalloc(fc_ctx* ctx, const double* u_col
 {
   if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede evaluate_stress_noalloc");
   if (!ctx->have_material) return fail(ctx, FC_ERR_INVALID, "set_material must precede evaluate_stress_noalloc");
-  if (ctx->celltype > FC_TET10 || ctx->formulation == FC_FORM_LINEAR || ctx->formulation == FC_FORM_MULF)
+  if (ctx->celltype > FC_TET10 || ctx->formulation >= FC_FORM_LINEAR)  // linear, MULF, EAS
     return fail(ctx, FC_ERR_UNSUPPORTED, "evaluate_stress_noalloc covers hex8, hex27 and tet10 with nonlinear kinematics (use fc_solid_evaluate_stress)");
   if (!u_col_dev || !nodal_stress_dev) return fail(ctx, FC_ERR_INVALID, "u_col_dev and nodal_stress_dev are required");
   if (stress_type != FC_STRESS_2PK && stress_type != FC_STRESS_CAUCHY) return fail(ctx, FC_ERR_UNSUPPORTED, "stress type");

@@ -129,7 +129,13 @@ namespace
     const long long n1 = (long long)ctx->n_ele * NGP;
     if (n1 > 0)
     {
-      fc::k_gp_stress<CT, FORM><<<(unsigned)((n1 + 63) / 64), 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      const unsigned gs = (unsigned)((n1 + 63) / 64);
+      if (CT == fc::HEX8 && ctx->formulation == FC_FORM_EAS_MILD)
+        fc::k_gp_stress_eas<9><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_EAS_FULL)
+        fc::k_gp_stress_eas<21><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      else
+        fc::k_gp_stress<CT, FORM><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       ctx->launches++;
       FC_CUDA(cudaGetLastError());
     }
@@ -159,12 +165,12 @@ namespace
   }
 }  // namespace
 
-extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int stress_type, double* gp_stress, double* nodal_stress)
+// Gauss-point output of kind fc::GpOutput and its extrapolation to the nodes
+static int gp_output_run(fc_ctx* ctx, const double* u_col, int stress_type, double* gp_stress, double* nodal_stress)
 {
   if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede evaluate_stress");
   if (!ctx->have_material) return fail(ctx, FC_ERR_INVALID, "set_material must precede evaluate_stress");
   if (!u_col || (!gp_stress && !nodal_stress)) return fail(ctx, FC_ERR_INVALID, "u_col and one output are required");
-  if (stress_type != FC_STRESS_2PK && stress_type != FC_STRESS_CAUCHY) return fail(ctx, FC_ERR_UNSUPPORTED, "stress type");
   FC_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t s = ctx->stream;
   const int ngp = fc::cell_ngp(ctx->celltype);
@@ -200,6 +206,7 @@ extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int st
   A.fiber_gp = ctx->fiber_gp;
   A.fiber_ele = ctx->fiber_gp ? ctx->fiber_gp * fc::cell_ngp(ctx->celltype) : 3;
   A.mulf = ctx->d_mulf;
+  A.eas = ctx->d_eas;
   const bool fbar = ctx->formulation == FC_FORM_FBAR, lin = ctx->formulation == FC_FORM_LINEAR, mulf = ctx->formulation == FC_FORM_MULF;
   int rc = FC_ERR_UNSUPPORTED;
 #define FC_STRESS(CT) \
@@ -235,4 +242,17 @@ extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int st
   if (rc != FC_OK) return rc;
   FC_CUDA(e);
   return FC_OK;
+}
+
+extern "C" int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int stress_type, double* gp_stress, double* nodal_stress)
+{
+  if (stress_type != FC_STRESS_2PK && stress_type != FC_STRESS_CAUCHY) return fail(ctx, FC_ERR_UNSUPPORTED, "stress type");
+  return gp_output_run(ctx, u_col, stress_type == FC_STRESS_2PK ? fc::OUT_PK2 : fc::OUT_CAUCHY, gp_stress, nodal_stress);
+}
+
+extern "C" int fc_solid_evaluate_strain(fc_ctx* ctx, const double* u_col, int strain_type, double* gp_strain, double* nodal_strain)
+{
+  if (strain_type != FC_STRAIN_GL && strain_type != FC_STRAIN_EA && strain_type != FC_STRAIN_LOG)
+    return fail(ctx, FC_ERR_UNSUPPORTED, "strain type");
+  return gp_output_run(ctx, u_col, fc::OUT_STRAIN_GL + strain_type, gp_strain, nodal_strain);
 }

@@ -59,6 +59,7 @@ struct fc_ctx
   fc::MatParams mat{fc::MAT_NEOHOOKE, 10.0, 0.25, 0, {0, 0, 0, 0}, {{0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}, {0, 0, 0, 0}}};
   double* d_fiber = nullptr;  // unit fibre directions or nullptr: [n_ele][3] (fc_solid_set_fibers) or [n_ele][ngp][3] (fc_solid_set_nodal_fibers)
   int fiber_gp = 0;           // 0: one fibre per element, 3: one per Gauss point
+  double* d_eas = nullptr;    // FC_FORM_EAS_*: [n_ele][3 n + n^2 + 24 n + 1] element history (alpha_inc | alpha | s | Kaa^-1 | Kda | step)
   double* d_mulf = nullptr;   // FC_FORM_MULF: [n_ele][ngp][18] prestress history (inverse Jacobian | deformation gradient, column-major)
   bool have_material = false;
 

@@ -31,8 +31,9 @@ namespace fc
     const double* geom;           // hex8 geometry cache [n_ele][72] (k_hex8_geom_cache) or nullptr
     const double* fiber;          // unit fibre directions FIBER1 (anisotropic summands) or nullptr: [n_ele][3] per element
                                   // (fiber_gp = 0) or [n_ele][ngp][3] per Gauss point (fiber_gp = 3, nodal fibres)
-    const double* mulf;           // FORM_MULF: [n_ele][ngp][18] history = inverse Jacobian (9, row-major: N_xyz = invJ dN) |
-                                  // deformation gradient (9, row-major F[3 i + I]) of the prestressed configuration, else nullptr
+    const double* mulf;           // FORM_MULF: [n_ele][ngp][18] history = inverse Jacobian (9, N_xyz = invJ dN) | deformation
+                                  // gradient (9) of the prestressed configuration, both column-major; else nullptr
+    double* eas;                  // hex8 EAS: [n_ele][EasCfg::hist_doubles] element history (alpha read; Kaa^-1, Kda, s written)
     int fiber_ele, fiber_gp;      // strides in doubles: element e, Gauss point g -> fiber + e * fiber_ele + g * fiber_gp
     // outputs
     double* f;             // [n_row_dof] or nullptr

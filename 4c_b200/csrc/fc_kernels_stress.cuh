@@ -4,12 +4,125 @@
 //   pk2_to_cauchy  sigma = F S F^T / det F src/solid_3D_ele/4C_solid_3D_ele_utils.cpp:20-33   (F-bar: the modified F)
 //   extrapolate_gp_quantity_to_nodes_and_assemble, nodal_average = true
 //                                          src/core/fem/src/general/utils/4C_fem_general_utils_gauss_point_extrapolation.cpp:260-284, 418-427
+// Strain output of the same action (assemble_strain_type_to_matrix_row, 4C_solid_3D_ele_calc_lib_io.hpp:113-153; Euler-Almansi
+// and logarithmic strains: 4C_solid_3D_ele_utils.cpp:35-84).  The reference takes the 3x3 eigenproblems from LAPACK; here cyclic
+// Jacobi rotations.
 // Post-processing, not on the per-iteration path: one thread per (element, Gauss point) / (element, node).
 #pragma once
 #include "fc_kernels_generic.cuh"
+#include "fc_kernels_hex8eas.cuh"
 
 namespace fc
 {
+  // Gauss-point output kinds of k_gp_stress
+  enum GpOutput
+  {
+    OUT_PK2 = 0,
+    OUT_CAUCHY = 1,
+    OUT_STRAIN_GL = 2,
+    OUT_STRAIN_EA = 3,
+    OUT_STRAIN_LOG = 4
+  };
+
+  // symmetric 3x3 (row-major): A = V diag(w) V^T, V[3 r + c] = component r of eigenvector c
+  __device__ inline void sym_eig3(const double* Am, double* w, double* V)
+  {
+    double a[9];
+    for (int k = 0; k < 9; ++k)
+    {
+      a[k] = Am[k];
+      V[k] = (k % 4 == 0) ? 1.0 : 0.0;
+    }
+    for (int sweep = 0; sweep < 60; ++sweep)
+    {
+      const double off = a[1] * a[1] + a[2] * a[2] + a[5] * a[5];
+      const double diag = a[0] * a[0] + a[4] * a[4] + a[8] * a[8];
+      if (off <= 1.0e-34 * diag || off == 0.0) break;
+      for (int p = 0; p < 2; ++p)
+        for (int q = p + 1; q < 3; ++q)
+        {
+          const double apq = a[3 * p + q];
+          if (apq == 0.0) continue;
+          const double theta = (a[4 * q] - a[4 * p]) / (2.0 * apq);
+          const double t = (theta >= 0.0 ? 1.0 : -1.0) / (fabs(theta) + sqrt(theta * theta + 1.0));
+          const double c = 1.0 / sqrt(t * t + 1.0), s = t * c;
+          for (int k = 0; k < 3; ++k)
+          {
+            const double akp = a[3 * k + p], akq = a[3 * k + q];
+            a[3 * k + p] = c * akp - s * akq;
+            a[3 * k + q] = s * akp + c * akq;
+          }
+          for (int k = 0; k < 3; ++k)
+          {
+            const double apk = a[3 * p + k], aqk = a[3 * q + k];
+            a[3 * p + k] = c * apk - s * aqk;
+            a[3 * q + k] = s * apk + c * aqk;
+          }
+          for (int k = 0; k < 3; ++k)
+          {
+            const double vkp = V[3 * k + p], vkq = V[3 * k + q];
+            V[3 * k + p] = c * vkp - s * vkq;
+            V[3 * k + q] = s * vkp + c * vkq;
+          }
+        }
+    }
+    for (int k = 0; k < 3; ++k) w[k] = a[4 * k];
+  }
+  // out = V diag(f(w)) V^T with f = sqrt (mode 0) or log(sqrt(2 x + 1)) (mode 1)
+  __device__ inline void sym_fn3(const double* Am, int mode, double* out)
+  {
+    double w[3], V[9];
+    sym_eig3(Am, w, V);
+    for (int k = 0; k < 3; ++k) w[k] = mode == 0 ? sqrt(w[k]) : log(sqrt(2.0 * w[k] + 1.0));
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) out[3 * r + c] = V[3 * r] * w[0] * V[3 * c] + V[3 * r + 1] * w[1] * V[3 * c + 1] + V[3 * r + 2] * w[2] * V[3 * c + 2];
+  }
+
+  // one Gauss point: S (2nd Piola-Kirchhoff), C (symmetric-6 right Cauchy-Green the material saw) and F (row-major, the
+  // deformation gradient the reference hands to the output) -> out[6] in stress-like Voigt order xx yy zz xy yz xz
+  __device__ inline void gp_output(int kind, const double* S, const double* C, const double* F, double* out)
+  {
+    const int vi6[6] = {0, 1, 2, 0, 1, 0}, vj6[6] = {0, 1, 2, 1, 2, 2};
+    if (kind == OUT_PK2)
+    {
+      for (int v = 0; v < 6; ++v) out[v] = S[v];
+      return;
+    }
+    if (kind == OUT_CAUCHY)
+    {
+      // sigma = F S F^T / det F; S = (00,11,22,01,12,02)
+      const double Sm[9] = {S[0], S[3], S[5], S[3], S[1], S[4], S[5], S[4], S[2]};
+      double FS[9];
+      for (int i = 0; i < 3; ++i)
+        for (int J = 0; J < 3; ++J) FS[3 * i + J] = F[3 * i] * Sm[J] + F[3 * i + 1] * Sm[3 + J] + F[3 * i + 2] * Sm[6 + J];
+      const double idet = 1.0 / det3(F);
+      for (int v = 0; v < 6; ++v)
+      {
+        const int i = vi6[v], j = vj6[v];
+        out[v] = idet * (FS[3 * i] * F[3 * j] + FS[3 * i + 1] * F[3 * j + 1] + FS[3 * i + 2] * F[3 * j + 2]);
+      }
+      return;
+    }
+    const double Em[9] = {0.5 * (C[0] - 1.0), 0.5 * C[3], 0.5 * C[5], 0.5 * C[3], 0.5 * (C[1] - 1.0), 0.5 * C[4], 0.5 * C[5], 0.5 * C[4],
+        0.5 * (C[2] - 1.0)};
+    double R[9];
+    if (kind == OUT_STRAIN_GL)
+      for (int k = 0; k < 9; ++k) R[k] = Em[k];
+    else if (kind == OUT_STRAIN_EA)
+    {
+      // e = F^-T E F^-1
+      double iF[9], t[9];
+      inv3(F, iF);
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) t[3 * i + j] = iF[i] * Em[j] + iF[3 + i] * Em[3 + j] + iF[6 + i] * Em[6 + j];
+      for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) R[3 * i + j] = t[3 * i] * iF[j] + t[3 * i + 1] * iF[3 + j] + t[3 * i + 2] * iF[6 + j];
+    }
+    else
+      sym_fn3(Em, 1, R);
+    for (int v = 0; v < 6; ++v) out[v] = 0.5 * (R[3 * vi6[v] + vj6[v]] + R[3 * vj6[v] + vi6[v]]);
+  }
+
   template <int CT, int FORM>
   __global__ void k_gp_stress(const EvalArgs A, int stress_type, double* __restrict__ gp_stress)
   {
@@ -64,24 +177,52 @@ namespace fc
     }
     double S[6], cmat[36];
     material_evaluate(A.mat, C, S, cmat, A.fiber ? A.fiber + (size_t)e * A.fiber_ele + gp * A.fiber_gp : nullptr);
-    double* out = gp_stress + ((size_t)e * NGP + gp) * 6;
-    if (stress_type == 0)
+    gp_output(stress_type, S, C, F, gp_stress + ((size_t)e * NGP + gp) * 6);
+  }
+
+  // hex8 EAS: the enhanced Green-Lagrange strains of the element's alpha; the deformation gradient handed to the output is
+  // F^enh = R U^enh with the rotation of the displacement-based F (compute_deformation_gradient_from_gl_strains,
+  // 4C_solid_3D_ele_calc_lib.hpp:1257-1299).  The iteration data (Kaa^-1, Kda, s) is left alone, like calculate_stress.
+  template <int NEAS>
+  __global__ void k_gp_stress_eas(const EvalArgs A, int kind, double* __restrict__ gp_stress)
+  {
+    using Cfg = EasCfg<NEAS>;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= (long long)A.n_ele * 8) return;
+    const int e = (int)(tid / 8), gp = (int)(tid % 8);
+    double Xs[24], us[24];
+    for (int a = 0; a < 8; ++a)
     {
-      for (int v = 0; v < 6; ++v) out[v] = S[v];
-      return;
+      const int node = __ldg(A.conn + (size_t)e * 8 + a);
+      for (int i = 0; i < 3; ++i)
+      {
+        Xs[3 * a + i] = __ldg(A.X + 3 * (size_t)node + i);
+        us[3 * a + i] = __ldg(A.u + 3 * (size_t)node + i);
+      }
     }
-    // sigma = F S F^T / det F; S = (00,11,22,01,12,02)
-    const double Sm[9] = {S[0], S[3], S[5], S[3], S[1], S[4], S[5], S[4], S[2]};
-    double FS[9];
-    for (int i = 0; i < 3; ++i)
-      for (int J = 0; J < 3; ++J) FS[3 * i + J] = F[3 * i] * Sm[J] + F[3 * i + 1] * Sm[3 + J] + F[3 * i + 2] * Sm[6 + J];
-    const double idet = 1.0 / det3(F);
-    const int vi6[6] = {0, 1, 2, 0, 1, 0}, vj6[6] = {0, 1, 2, 1, 2, 2};
-    for (int v = 0; v < 6; ++v)
-    {
-      const int i = vi6[v], j = vj6[v];
-      out[v] = idet * (FS[3 * i] * F[3 * j] + FS[3 * i + 1] * F[3 * j + 1] + FS[3 * i + 2] * F[3 * j + 2]);
-    }
+    double Tm[36], Nx[24], F[9], m[6], alpha[NEAS];
+    const double detJ0 = eas_centroid_transformation(A.dNtab + (size_t)16 * 24, Xs, Tm);
+    const double detJ = jacobian_mapping<8>(A.dNtab + (size_t)gp * 24, Xs, Nx);
+    deformation_gradient<HEX8>(Xs, us, Nx, F);
+    double Cd[6] = {F[0] * F[0] + F[3] * F[3] + F[6] * F[6], F[1] * F[1] + F[4] * F[4] + F[7] * F[7],
+        F[2] * F[2] + F[5] * F[5] + F[8] * F[8], F[0] * F[1] + F[3] * F[4] + F[6] * F[7],
+        F[1] * F[2] + F[4] * F[5] + F[7] * F[8], F[0] * F[2] + F[3] * F[5] + F[6] * F[8]};
+    double C[6] = {Cd[0], Cd[1], Cd[2], Cd[3], Cd[4], Cd[5]};
+    eas_monomials(gp, detJ0 / detJ, m);
+    for (int k = 0; k < NEAS; ++k) alpha[k] = A.eas[(size_t)e * Cfg::hist_doubles + Cfg::oAlpha + k];
+    eas_enhance_cauchy_green<NEAS>(Tm, m, alpha, C);
+    double S[6], cmat[36];
+    material_evaluate(A.mat, C, S, cmat, A.fiber ? A.fiber + (size_t)e * A.fiber_ele + gp * A.fiber_gp : nullptr);
+    // F^enh = F U_disp^-1 U_enh
+    const double Cm[9] = {C[0], C[3], C[5], C[3], C[1], C[4], C[5], C[4], C[2]};
+    const double Cdm[9] = {Cd[0], Cd[3], Cd[5], Cd[3], Cd[1], Cd[4], Cd[5], Cd[4], Cd[2]};
+    double Ue[9], Ud[9], iUd[9], Rm[9], Fe[9];
+    sym_fn3(Cm, 0, Ue);
+    sym_fn3(Cdm, 0, Ud);
+    inv3(Ud, iUd);
+    mat3_mul(F, iUd, Rm);
+    mat3_mul(Rm, Ue, Fe);
+    gp_output(kind, S, C, Fe, gp_stress + ((size_t)e * 8 + gp) * 6);
   }
 
   // nodal[node][6] += (E gp_stress_e)[a] / (elements at the node), owned nodes only.  Emat: [nen][ngp]

@@ -65,8 +65,11 @@ extern "C"
     FC_FORM_DISPLACEMENT = 0, /* 4C_solid_3D_ele_calc_displacement_based.hpp:35-251 */
     FC_FORM_FBAR = 1,         /* 4C_solid_3D_ele_calc_fbar.hpp:43-191 (hex8 and pyramid5 only) */
     FC_FORM_LINEAR = 2,       /* KINEM linear: 4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155 (every cell) */
-    FC_FORM_MULF = 3          /* PRESTRESS_TECH mulf: 4C_solid_3D_ele_calc_mulf.hpp:40-196 (every cell); Gauss-point history in the
+    FC_FORM_MULF = 3,         /* PRESTRESS_TECH mulf: 4C_solid_3D_ele_calc_mulf.hpp:40-196 (every cell); Gauss-point history in the
                                  context, see fc_solid_update_prestress */
+    FC_FORM_EAS_MILD = 4,     /* TECH eas_mild (hex8, 9 enhanced strain modes) and */
+    FC_FORM_EAS_FULL = 5      /* TECH eas_full (hex8, 21 modes): 4C_solid_3D_ele_calc_eas.hpp:44-291; element history in the
+                                 context, see fc_solid_recover */
   };
   /* materials: MAT_Struct_StVenantKirchhoff (src/mat/4C_mat_stvenantkirchhoff.cpp) and
    * MAT_ElastHyper with one ELAST_CoupNeoHooke summand (src/mat/4C_mat_elasthyper.cpp,
@@ -155,6 +158,21 @@ extern "C"
   int fc_solid_update_prestress(fc_ctx* ctx, const double* u_col);
   int fc_solid_mulf_get_history(fc_ctx* ctx, double* history);
   int fc_solid_mulf_set_history(fc_ctx* ctx, const double* history);
+  /* FC_FORM_EAS_MILD / FC_FORM_EAS_FULL (hex8 with enhanced assumed strains, condensed on the element).  The context keeps the
+   * history of every column element in the order EASFormulation::pack writes it (4C_solid_3D_ele_calc_eas.hpp:266-274):
+   * alpha_inc [n] | alpha [n] | s [n] | Kaa^-1 [n][n] | Kda [24][n] | old_step_length, matrices column-major, n = 9 | 21, i.e.
+   * 3 n + n^2 + 24 n + 1 doubles (fc_solid_eas_history_doubles).  fc_solid_set_mesh zeroes it (old_step_length = 1).
+   * Every fc_solid_evaluate / fc_solid_evaluate_elements integrates Kaa, Kda and s with the current alpha, adds the condensed
+   * contributions -Kda Kaa^-1 s and -Kda Kaa^-1 Kda^T and stores Kaa^-1, Kda, s (4C_solid_3D_ele_calc.cpp:110-240), also for
+   * FC_ACTION_INTERNALFORCE.  fc_solid_recover is struct_calc_recover for a default step (SolidEleCalc::recover,
+   * 4C_solid_3D_ele_calc.cpp:244-273; update_alpha, 4C_solid_3D_ele_calc_eas_helpers.hpp:189-228): with the Newton increment
+   * du_col (column layout, host|device) alpha_inc = -Kaa^-1 (s + Kda^T du), alpha += step_length alpha_inc.  Call it after every
+   * solution update, before the next evaluation.  A rank evaluates and recovers its ghost elements too, so every copy of an
+   * element holds the same alpha.  get/set move the history (host|device) for restart or to repeat an evaluation. */
+  int fc_solid_recover(fc_ctx* ctx, const double* du_col, double step_length);
+  int fc_solid_eas_history_doubles(const fc_ctx* ctx, int* doubles_per_element);
+  int fc_solid_eas_get_history(fc_ctx* ctx, double* history);
+  int fc_solid_eas_set_history(fc_ctx* ctx, const double* history);
   int fc_solid_set_fibers(fc_ctx* ctx, const double* fiber1);
   /* Fibres given at the nodes (FNODE ... FIBER1; anisotropic summands with INIT 3): node_fiber1 [n_col_nodes][3].  The library
    * interpolates them to the Gauss points of the stiffness rule with the element's shape functions and normalises
@@ -248,6 +266,18 @@ extern "C"
     FC_STRESS_CAUCHY = 1
   };
   int fc_solid_evaluate_stress(fc_ctx* ctx, const double* u_col, int stress_type, double* gp_stress, double* nodal_stress);
+  /* The strains the same action writes next to the stresses (STRUCT_STRAIN gl | ea | log; assemble_strain_type_to_matrix_row,
+   * 4C_solid_3D_ele_calc_lib_io.hpp:113-153): Green-Lagrange E, Euler-Almansi F^-T E F^-1 or logarithmic strains
+   * (4C_solid_3D_ele_utils.cpp:35-84) of the formulation's strain measure (F-bar: of the modified F; EAS: the enhanced strains;
+   * KINEM linear: sym grad u), in the stress-like Voigt order of the output xx,yy,zz,xy,yz,zx (shear components not doubled).
+   * Same layouts and extrapolation as fc_solid_evaluate_stress. */
+  enum fc_strain_type
+  {
+    FC_STRAIN_GL = 0,
+    FC_STRAIN_EA = 1,
+    FC_STRAIN_LOG = 2
+  };
+  int fc_solid_evaluate_strain(fc_ctx* ctx, const double* u_col, int strain_type, double* gp_strain, double* nodal_strain);
 
   /* Nodal stresses as fc_solid_evaluate_stress computes them (Gauss-point stresses extrapolated to the nodes and averaged),
    * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).

@@ -16,6 +16,7 @@
 #pragma once
 #include <thread>
 
+#include "fc_oracle_eas.hpp"
 #include "fc_oracle_element.hpp"
 #include "fc_oracle_mesh.hpp"
 
@@ -126,9 +127,11 @@ namespace fc_oracle
       const MaterialParams& mp, int action, const double* u_col, double* f_row, double* K_values,
       int* first_bad, const double* ele_fiber = nullptr /* [n_ele][3] FIBER1 in mesh element order, or [n_ele][ngp][3] */,
       int fiber_gp_stride = 0 /* 3: ele_fiber holds one fibre per Gauss point */,
-      const double* mulf_hist = nullptr /* FORM_MULF: [n_ele][ngp][18] in mesh element order */)
+      const double* mulf_hist = nullptr /* FORM_MULF: [n_ele][ngp][18] in mesh element order */,
+      double* eas_hist = nullptr /* FORM_EAS_*: [n_ele][eas_history_doubles] in mesh element order; invKaa, Kda, s are written */)
   {
     const int nen = mesh.nen, nd = 3 * nen;
+    const int neas = form == FORM_EAS_FULL ? 21 : 9;
     std::vector<int> lm(nd), lmowner(nd), localcol(nd);
     std::vector<double> X(nd), u(nd), fe(nd), Ke((size_t)nd * nd);
     int nbad = 0;
@@ -151,10 +154,13 @@ namespace fc_oracle
       for (int i = 0; i < nd; ++i) u[i] = u_col[rs.col_dof_lid.at(lm[i])];
       std::fill(fe.begin(), fe.end(), 0.0);
       if (action == 0) std::fill(Ke.begin(), Ke.end(), 0.0);
-      const int err = element_evaluate(
-          mesh.ct, form, mp, X.data(), u.data(), fe.data(), action == 0 ? Ke.data() : nullptr, nullptr, 0.0, nullptr, STRESS_CAUCHY,
-          ele_fiber ? ele_fiber + (fiber_gp_stride ? (size_t)fiber_gp_stride * num_gp(mesh.ct) : 3) * (size_t)e : nullptr, fiber_gp_stride,
-          mulf_hist ? mulf_hist + (size_t)18 * num_gp(mesh.ct) * e : nullptr);
+      const double* fib = ele_fiber ? ele_fiber + (fiber_gp_stride ? (size_t)fiber_gp_stride * num_gp(mesh.ct) : 3) * (size_t)e : nullptr;
+      const int err = (form == FORM_EAS_MILD || form == FORM_EAS_FULL)
+                          ? element_evaluate_eas(neas, mp, X.data(), u.data(), eas_hist + (size_t)eas_history_doubles(neas) * e, fe.data(),
+                                action == 0 ? Ke.data() : nullptr, fib, fiber_gp_stride)
+                          : element_evaluate(mesh.ct, form, mp, X.data(), u.data(), fe.data(), action == 0 ? Ke.data() : nullptr, nullptr,
+                                0.0, nullptr, STRESS_CAUCHY, fib, fiber_gp_stride,
+                                mulf_hist ? mulf_hist + (size_t)18 * num_gp(mesh.ct) * e : nullptr);
       if (err)
       {
         if (nbad == 0 && first_bad) *first_bad = eg;
@@ -215,6 +221,7 @@ namespace fc_oracle
     std::vector<double> ele_fiber;  // [n_ele][3], [n_ele][ngp][3] (fiber_gp_stride = 3) or empty
     int fiber_gp_stride = 0;
     std::vector<double> mulf_hist;  // [n_ele][ngp][18] when form == FORM_MULF
+    mutable std::vector<double> eas_hist;  // [n_ele][eas_history_doubles] when form == FORM_EAS_MILD / FORM_EAS_FULL
   };
 
   inline int evaluate_job(const Job& job, int action, const std::vector<std::vector<double>>& u_row,
@@ -230,9 +237,10 @@ namespace fc_oracle
       nbad[r] = evaluate_rank(job.mesh, job.part, job.sys[r], job.form, job.mp, action,
           u_col.data(), f_row[r].data(), action == 0 ? K_values[r].data() : nullptr, &fb[r],
           job.ele_fiber.empty() ? nullptr : job.ele_fiber.data(), job.fiber_gp_stride,
-          job.mulf_hist.empty() ? nullptr : job.mulf_hist.data());
+          job.mulf_hist.empty() ? nullptr : job.mulf_hist.data(), job.eas_hist.empty() ? nullptr : job.eas_hist.data());
     };
-    if (max_threads <= 1 || nr == 1)
+    // EAS: every rank that holds an element writes its iteration data (the same values) - one rank at a time
+    if (max_threads <= 1 || nr == 1 || !job.eas_hist.empty())
       for (int r = 0; r < nr; ++r) work(r);
     else
     {

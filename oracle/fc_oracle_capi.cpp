@@ -201,6 +201,14 @@ extern "C"
   static void mulf_init(JobState* js)
   {
     js->job.mulf_hist.clear();
+    js->job.eas_hist.clear();
+    if (js->job.form == FORM_EAS_MILD || js->job.form == FORM_EAS_FULL)
+    {
+      // EASHistoryData of a new element: everything zero, old_step_length = 1
+      const int neas = js->job.form == FORM_EAS_FULL ? 21 : 9, nh = eas_history_doubles(neas);
+      js->job.eas_hist.assign((size_t)nh * js->job.mesh.ele_gid.size(), 0.0);
+      for (size_t e = 0; e < js->job.mesh.ele_gid.size(); ++e) eas_history_init(neas, &js->job.eas_hist[(size_t)nh * e]);
+    }
     if (js->job.form != FORM_MULF) return;
     const Mesh& m = js->job.mesh;
     const int ngp = num_gp(m.ct);
@@ -242,6 +250,48 @@ extern "C"
       mulf_history(m.ct, X.data(), u.data(), &js->job.mulf_hist[(size_t)18 * ngp * e]);
     }
   }
+  // struct_calc_recover of the EAS elements (default step): du_nodes [n_nodes][3] = the Newton increment in the mesh's node order
+  void oracle_job_recover(void* h, const double* du_nodes, double step_length)
+  {
+    auto* js = (JobState*)h;
+    const Mesh& m = js->job.mesh;
+    if (js->job.eas_hist.empty()) return;
+    const int neas = js->job.form == FORM_EAS_FULL ? 21 : 9, nh = eas_history_doubles(neas);
+    double du[24];
+    for (size_t e = 0; e < m.ele_gid.size(); ++e)
+    {
+      for (int a = 0; a < 8; ++a)
+      {
+        const size_t ni = (size_t)m.node_index.at(m.ele_nodes[e * 8 + a]);
+        for (int i = 0; i < 3; ++i) du[3 * a + i] = du_nodes[3 * ni + i];
+      }
+      eas_recover(neas, &js->job.eas_hist[(size_t)nh * e], du, step_length);
+    }
+  }
+  // the job's EAS history [n_ele][eas_history_doubles]; get returns its length (hist may be NULL)
+  long long oracle_job_get_eas_history(void* h, double* hist)
+  {
+    auto* js = (JobState*)h;
+    if (hist) std::copy(js->job.eas_hist.begin(), js->job.eas_hist.end(), hist);
+    return (long long)js->job.eas_hist.size();
+  }
+  void oracle_job_set_eas_history(void* h, const double* hist)
+  {
+    auto* js = (JobState*)h;
+    std::copy(hist, hist + js->job.eas_hist.size(), js->job.eas_hist.begin());
+  }
+  // one hex8 EAS element (neas = 9 | 21) with the history hist [eas_history_doubles(neas)]: fe [24] and Ke [24 x 24] are
+  // overwritten (Ke may be NULL); invKaa, Kda, s of the history are written.  recover: alpha += step * alpha_inc(du).
+  int oracle_eas_history_doubles(int neas) { return eas_history_doubles(neas); }
+  int oracle_element_evaluate_eas(int neas, int kind, double young, double nue, const double* X, const double* u, double* hist,
+      double* fe, double* Ke)
+  {
+    MaterialParams mp{kind, young, nue};
+    std::memset(fe, 0, sizeof(double) * 24);
+    if (Ke) std::memset(Ke, 0, sizeof(double) * 576);
+    return element_evaluate_eas(neas, mp, X, u, hist, fe, Ke, nullptr, 0);
+  }
+  void oracle_element_recover_eas(int neas, double* hist, const double* du, double step_length) { eas_recover(neas, hist, du, step_length); }
   // the job's prestress history [n_ele][ngp][18] (inverse Jacobian | deformation gradient, both column-major); returns its length
   long long oracle_job_get_mulf_history(void* h, double* hist)
   {
@@ -268,6 +318,13 @@ extern "C"
     }
     const Job& job = js->job;
     const double* fib = job.ele_fiber.empty() ? nullptr : job.ele_fiber.data() + (job.fiber_gp_stride ? (size_t)job.fiber_gp_stride * ngp : 3) * (size_t)e;
+    if (!job.eas_hist.empty())
+    {
+      const int neas = job.form == FORM_EAS_FULL ? 21 : 9;
+      const bool strain = stress_type >= OUTPUT_STRAIN;
+      return element_evaluate_eas(neas, job.mp, X.data(), u.data(), job.eas_hist.data() + (size_t)eas_history_doubles(neas) * e, nullptr,
+          nullptr, fib, job.fiber_gp_stride, gp_stress, strain ? 1 : 0, strain ? stress_type - OUTPUT_STRAIN : stress_type);
+    }
     return element_evaluate(m.ct, job.form, job.mp, X.data(), u.data(), nullptr, nullptr, nullptr, 0.0, gp_stress, stress_type, fib,
         job.fiber_gp_stride, job.mulf_hist.empty() ? nullptr : job.mulf_hist.data() + (size_t)18 * ngp * e);
   }

@@ -24,6 +24,7 @@
 #include "fc_oracle_dense.hpp"
 #include "fc_oracle_fem.hpp"
 #include "fc_oracle_material.hpp"
+#include "fc_oracle_strain.hpp"
 
 namespace fc_oracle
 {
@@ -32,7 +33,9 @@ namespace fc_oracle
     FORM_DISP = 0,
     FORM_FBAR = 1,
     FORM_LINEAR = 2,  // KINEM linear: src/solid_3D_ele/4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155
-    FORM_MULF = 3     // PRESTRESS_TECH mulf: src/solid_3D_ele/4C_solid_3D_ele_calc_mulf.hpp:40-196, ..._calc_lib_mulf.hpp:24-84
+    FORM_MULF = 3,    // PRESTRESS_TECH mulf: src/solid_3D_ele/4C_solid_3D_ele_calc_mulf.hpp:40-196, ..._calc_lib_mulf.hpp:24-84
+    FORM_EAS_MILD = 4,  // TECH eas_mild (hex8, 9 modes) and
+    FORM_EAS_FULL = 5   // TECH eas_full (hex8, 21 modes): src/solid_3D_ele/4C_solid_3D_ele_calc_eas.hpp, fc_oracle_eas.hpp
   };
 
   enum EleError
@@ -196,7 +199,8 @@ namespace fc_oracle
   enum StressType
   {
     STRESS_2PK = 0,
-    STRESS_CAUCHY = 1
+    STRESS_CAUCHY = 1,
+    OUTPUT_STRAIN = 16  // + StrainType: the Gauss-point output is the strain of that type (struct_calc_stress writes both)
   };
 
   template <int NEN, int NGP>
@@ -319,7 +323,9 @@ namespace fc_oracle
       if (gp_stress)
       {
         // calculate_stress / assemble_stress_type_to_matrix_row: solid_3D_ele_calc.cpp:347-390, calc_lib_io.hpp:167-190
-        if (stress_type == STRESS_CAUCHY)
+        if (stress_type >= OUTPUT_STRAIN)
+          strain_output(stress_type - OUTPUT_STRAIN, E, Fmat, gp_stress + 6 * gp);
+        else if (stress_type == STRESS_CAUCHY)
           pk2_to_cauchy(S, Fmat, gp_stress + 6 * gp);
         else
           for (int v = 0; v < 6; ++v) gp_stress[6 * gp + v] = S[v];

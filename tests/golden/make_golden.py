@@ -58,6 +58,15 @@ CASES = [
     # CoupAnisoExpo with INIT 3: FIBER1 at the nodes (FNODE), interpolated to the Gauss points
     "solid_ele_hex8_Standard_eas_none_nodal_fibers.dat",
     "solid_ele_tet4_Standard_nodal_fibers.dat",
+    # strain output (Green-Lagrange, Euler-Almansi, logarithmic) next to 2nd Piola-Kirchhoff / Cauchy stresses
+    "solid_ele_hex8_Standard_stressout_2pk_strainout_gl.dat",
+    "solid_ele_hex8_Standard_stressout_cauchy_strainout_ea.dat",
+    "solid_ele_hex8_Standard_stressout_cauchy_strainout_log.dat",
+    # TECH eas_mild / eas_full (9 / 21 enhanced strain modes, condensed on the element): displacements, nodal stresses and strains
+    "solid_ele_hex8_Standard_eas_mild_stressout_2pk_strainout_gl.dat",
+    "solid_ele_hex8_Standard_eas_mild_stressout_cauchy_strainout_ea.dat",
+    "solid_ele_hex8_Standard_eas_full_stressout_2pk_strainout_gl.dat",
+    "solid_ele_hex8_Standard_eas_full_stressout_cauchy_strainout_ea.dat",
     "solid_ele_tet10_Standard_nodal_fibers.dat",
     # PRESTRESS mulf (PRESTRESS_TECH mulf): two prestress steps, then eight load steps; displacements and nodal stresses
     "solid_ele_hex8_Standard_mulf.dat",
@@ -137,7 +146,7 @@ def from_dat(path):
         i = t.index("MAT")
         eles.append({"id": int(t[0]), "type": t[2], "nodes": [int(x) for x in t[3:i]], "mat": int(t[i + 1]),
                      "opts": " ".join(t[i + 2:])})
-    return {"dynamic": dyn, "materials": mats, "functs": functs, "results": results, "dsurf": surf,
+    return {"dynamic": dyn, "io": keyvals(s.get("IO", [])), "materials": mats, "functs": functs, "results": results, "dsurf": surf,
             "dirich": [parse_condition_dat(l) for l in s.get("DESIGN SURF DIRICH CONDITIONS", [])],
             "neumann": [parse_condition_dat(l) for l in s.get("DESIGN SURF NEUMANN CONDITIONS", [])],
             "dvol": vol, "vol_neumann": [parse_condition_dat(l) for l in s.get("DESIGN VOL NEUMANN CONDITIONS", [])],

@@ -13,7 +13,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
-FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF = 0, 1, 2, 3
+FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF, FORM_EAS_MILD, FORM_EAS_FULL = 0, 1, 2, 3, 4, 5
+NEAS = {FORM_EAS_MILD: 9, FORM_EAS_FULL: 21}
+OUTPUT_STRAIN = 16  # stress_type = OUTPUT_STRAIN + strain type: the Gauss-point output is that strain (stress-like Voigt)
+STRAIN_GL, STRAIN_EA, STRAIN_LOG = 0, 1, 2
 MAT_SVK, MAT_NEOHOOKE = 0, 1
 ACTION_NLNSTIFF, ACTION_INTERNALFORCE = 0, 1
 NEN = {HEX8: 8, HEX27: 27, TET10: 10, HEX20: 20, TET4: 4, WEDGE6: 6, PYRAMID5: 5}
@@ -139,6 +142,24 @@ def element_gp_stress(ct, form, kind, young, nue, X, u, stress_type=1):
     err = lib.oracle_element_gp_stress(C.c_int(ct), C.c_int(form), C.c_int(kind), C.c_double(young), C.c_double(nue), _p(X), _p(u),
                                        C.c_int(stress_type), _p(out))
     return err, out
+
+
+def eas_history_doubles(neas):
+    return lib.oracle_eas_history_doubles(C.c_int(neas))
+
+
+def element_evaluate_eas(neas, kind, young, nue, X, u, hist, want_K=True):
+    """one hex8 EAS element with history hist (modified in place: invKaa, Kda, s) -> err, fe (8, 3), Ke (24, 24) [r, c]"""
+    X, u = _d(X), _d(u)
+    assert hist.dtype == np.float64 and hist.flags["C_CONTIGUOUS"] and hist.size == eas_history_doubles(neas)
+    fe, Ke = np.zeros(24), (np.zeros((24, 24)) if want_K else None)
+    err = lib.oracle_element_evaluate_eas(C.c_int(neas), C.c_int(kind), C.c_double(young), C.c_double(nue), _p(X), _p(u), _p(hist),
+                                          _p(fe), _p(Ke) if want_K else None)
+    return err, fe.reshape(8, 3), (np.ascontiguousarray(Ke.T) if want_K else None)
+
+
+def element_recover_eas(neas, hist, du, step_length=1.0):
+    lib.oracle_element_recover_eas(C.c_int(neas), _p(hist), _p(_d(du)), C.c_double(step_length))
 
 
 QUAD4, QUAD9, TRI6, QUAD8, TRI3 = 0, 1, 2, 3, 4
@@ -271,8 +292,24 @@ class Job:
         lib.oracle_job_get_mulf_history(self.h, _p(out))
         return out.reshape(-1, NGP[self.ct], 18)
 
+    def recover(self, du_nodes, step_length=1.0):
+        """struct_calc_recover (EAS): alpha of every element += step_length * alpha_inc(Newton increment), (n_nodes, 3)"""
+        lib.oracle_job_recover(self.h, _p(_d(du_nodes)), C.c_double(step_length))
+
+    def eas_history(self):
+        """(n_ele, 3 n + n^2 + 24 n + 1): alpha_inc | alpha | s | invKaa | Kda | old_step_length (empty unless FORM_EAS_*)"""
+        lib.oracle_job_get_eas_history.restype = C.c_longlong
+        n = lib.oracle_job_get_eas_history(self.h, None)
+        out = np.zeros(n)
+        lib.oracle_job_get_eas_history(self.h, _p(out))
+        return out.reshape(len(self.ele_gid), -1) if n else out
+
+    def set_eas_history(self, hist):
+        lib.oracle_job_set_eas_history(self.h, _p(_d(hist)))
+
     def element_gp_stress(self, e, u_nodes, stress_type=1):
-        """(ngp, 6) Gauss-point stresses of element e with the job's formulation, material, fibres and history"""
+        """(ngp, 6) Gauss-point stresses of element e with the job's formulation, material, fibres and history;
+        stress_type = OUTPUT_STRAIN + t: the strains of type t instead"""
         out = np.zeros((NGP[self.ct], 6))
         err = lib.oracle_job_element_gp_stress(self.h, C.c_int(e), _p(_d(u_nodes)), C.c_int(stress_type), _p(out))
         return err, out

@@ -83,10 +83,18 @@ class Problem:
                         i = t.index("FIBER1")
                         fib.append([float(x) for x in t[i + 1:i + 4]])
                     self.fibers = np.array(fib)
-        techs = {(3 if "PRESTRESS_TECH mulf" in e["opts"] else (2 if "KINEM linear" in e["opts"] else (1 if "TECH fbar" in e["opts"] else 0)))
-                 for e in fx["elements"]}
+        def tech(opts):
+            if "PRESTRESS_TECH mulf" in opts:
+                return 3
+            if "KINEM linear" in opts:
+                return 2
+            return {"fbar": 1, "eas_mild": 4, "eas_full": 5}.get(opts.split()[opts.split().index("TECH") + 1], 0) if "TECH" in opts.split() else 0
+        techs = {tech(e["opts"]) for e in fx["elements"]}
         assert len(techs) == 1
-        self.form = techs.pop()  # FC_FORM_DISPLACEMENT / FC_FORM_FBAR / FC_FORM_LINEAR / FC_FORM_MULF
+        self.form = techs.pop()  # FC_FORM_DISPLACEMENT / _FBAR / _LINEAR / _MULF / _EAS_MILD / _EAS_FULL
+        io = fx.get("io", {})
+        self.stress_type = {"2pk": 0, "cauchy": 1}.get(io.get("STRUCT_STRESS", "cauchy").lower(), 1)
+        self.strain_type = {"gl": 0, "ea": 1, "log": 2}.get(io.get("STRUCT_STRAIN", "none").lower())  # None: no strain output
         self.dens = float(m1[m1.index("DENS") + 1])
         self.young = float(m10[m10.index("YOUNG") + 1])
         self.nue = float(m10[m10.index("NUE") + 1])
@@ -333,14 +341,16 @@ def _converged(norms, inc, newton_tol):
     return len(norms) > 2 and norms[-1] < 1e-9 * max(norms) and norms[-1] > 0.5 * norms[-2]
 
 
-def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, update_prestress=None):
+def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, update_prestress=None, recover=None):
     """assemble(d) -> (f_int [n], K dense [n, n]); mass() -> M dense.  Returns d at MAXTIME and the residual
     norm history of every step (list of lists).  solve(A, rhs, fixed) replaces the dense direct solve (A is then
     whatever assemble/mass return, e.g. device-resident CSR values supporting a*A + b*B and A @ x).
     update_prestress(d): the element action of a MULF prestress step (problems with PRESTRESS mulf): after a step with
     t <= PRESTRESSTIME the elements update their history and the displacements are reset
     (Solid::ModelEvaluator::Structure::update_step_element, 4C_structure_new_model_evaluator_structure.cpp:1555-1592;
-    Solid::IMPLICIT::PreStress::post_update, 4C_structure_new_impl_prestress.cpp)."""
+    Solid::IMPLICIT::PreStress::post_update, 4C_structure_new_impl_prestress.cpp).
+    recover(inc): struct_calc_recover after every Newton update (elements with condensed variables, EAS:
+    Solid::ModelEvaluator::Structure::run_recover, 4C_structure_new_model_evaluator_structure.cpp)."""
     _solve = solve or globals()["_solve"]
     p = problem
     n, fixed, dt = p.n_dof, p.fixed, p.dt
@@ -357,6 +367,8 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, 
                 norms.append(float(np.linalg.norm(r)))
                 inc = _solve(K, -r, fixed)
                 d = d + inc
+                if recover is not None:
+                    recover(inc)
                 if _converged(norms, inc, newton_tol):
                     break
             history.append(norms)
@@ -394,6 +406,8 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, 
             J = (1.0 - af) * K + (1.0 - am) / (beta * dt * dt) * M
             inc = _solve(J, -r, fixed)
             d_np = d_np + inc
+            if recover is not None:
+                recover(inc)
             if _converged(norms, inc, newton_tol):
                 break
         history.append(norms)
@@ -462,12 +476,14 @@ def nodal_stresses(problem, gp_stress_of_element, E):
 STRESS_COMP = {"stress_xx": 0, "stress_yy": 1, "stress_zz": 2, "stress_xy": 3, "stress_yz": 4, "stress_xz": 5}
 
 
-def stress_result_error(problem, nodal):
-    """max (|nodal stress - VALUE| / TOLERANCE) over the stress results of the fixture, and the number compared"""
+def stress_result_error(problem, nodal, prefix="stress"):
+    """max (|nodal stress - VALUE| / TOLERANCE) over the stress (prefix "strain": strain) results of the fixture, and the
+    number compared"""
     err, n = 0.0, 0
+    comp = {k.replace("stress", prefix): v for k, v in STRESS_COMP.items()}
     for r in problem.fx["results"]:
-        if r["quantity"] in STRESS_COMP:
-            v = nodal[problem.index[r["node"]], STRESS_COMP[r["quantity"]]]
+        if r["quantity"] in comp:
+            v = nodal[problem.index[r["node"]], comp[r["quantity"]]]
             err = max(err, abs(v - r["value"]) / r["tolerance"])
             n += 1
     return err, n

@@ -207,3 +207,83 @@ def test_mulf_prestress_parity(fc, oracle, name, mat):
     assert ei.value.code == fc.FC_ERR_INVALID
     s3.close()
     s.close()
+
+
+@pytest.mark.parametrize("form,mat", [(4, NH), (4, SVK), (5, NH), (5, SVK)])
+def test_eas_parity(fc, oracle, form, mat):
+    """hex8 TECH eas_mild / eas_full on a distorted 3x2x2 block: three rounds of evaluate + recover with the library and with an
+    oracle job; element fe / Ke, assembled system, history (alpha, s, Kaa^-1, Kda) and Gauss-point stresses / strains."""
+    neas = oracle.NEAS[form]
+    m = fc.Grid(fc.FC_HEX8, (3, 2, 2), (0.0, 0.0, 0.0), (1.5, 1.0, 1.0))
+    rng = np.random.default_rng(5)
+    X = m.X + 0.06 * (rng.random(m.X.shape) - 0.5)
+    conn = m.conn
+    u = 0.05 * (rng.random(X.shape) - 0.5) + 0.04 * X * X[:, ::-1]
+    s = fc.Solid(0)
+    s.set_mesh(fc.FC_HEX8, form, X, m.node_gid, np.zeros(len(X), np.int32), conn, m.ele_gid)
+    s.set_material(mat, 10.0, 0.3)
+    n_row, n_col, nnz = s.build_graph()
+    rowptr, _ = s.get_graph()
+    starts = np.asarray(rowptr[:-1], np.int64)
+    job = oracle.Job.from_mesh(fc.FC_HEX8, m.node_gid, X, m.ele_gid, m.node_gid[conn])
+    job.set_problem(form, mat, 10.0, 0.3)
+    o = job.rank(0)
+    assert s.eas_history().shape == (len(conn), oracle.eas_history_doubles(neas))
+    assert np.array_equal(s.eas_history(), job.eas_history())
+    for it in range(3):
+        uk = (0.4 + 0.3 * it) * u
+        # element level: the oracle element with the library's history before the evaluation
+        h0 = s.eas_history()
+        fe, Ke = s.evaluate_elements(np.ascontiguousarray(uk.reshape(-1)), want_K=True)
+        for e in range(len(conn)):
+            he = np.ascontiguousarray(h0[e])
+            err, fr, kr = oracle.element_evaluate_eas(neas, mat, 10.0, 0.3, X[conn[e]], uk[conn[e]], he)
+            assert err == 0
+            assert np.max(np.abs(Ke[e] - kr)) <= 1e-11 * np.max(np.abs(kr)), (it, e, np.max(np.abs(Ke[e] - kr)) / np.max(np.abs(kr)))
+            assert np.max(np.abs(fe[e].reshape(8, 3) - fr)) <= 1e-11 * max(np.max(np.abs(fr)), np.max(np.abs(kr)))
+            assert np.max(np.abs(s.eas_history()[e] - he)) <= 1e-10 * np.max(np.abs(he))
+        # assembled system: both sides continue from their own history
+        job.set_u_nodal(uk)
+        assert job.evaluate(oracle.ACTION_NLNSTIFF)[0] == 0
+        f_ref, K_ref = job.get_f(0, n_row), job.get_K(0, o["nnz"])
+        K, f = np.zeros(nnz), np.zeros(n_row)
+        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, uk.reshape(-1), f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+        assert np.max(np.maximum.reduceat(np.abs(K - K_ref), starts) / np.maximum.reduceat(np.abs(K_ref), starts)) <= 1e-10
+        assert np.max(np.abs(f - f_ref)) <= 1e-10 * max(np.max(np.abs(f_ref)), np.max(np.abs(K_ref)))
+        f2 = np.zeros(n_row)
+        assert s.evaluate(fc.FC_ACTION_INTERNALFORCE, uk.reshape(-1), f2, None, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+        assert np.max(np.abs(f2 - f)) <= 1e-14 * np.max(np.abs(f))
+        h1, h2 = s.eas_history(), job.eas_history()
+        assert np.max(np.abs(h1 - h2)) <= 1e-9 * np.max(np.abs(h2))
+        # recover with a made-up increment (host array, then a device tensor)
+        du = 0.02 * (rng.random(X.shape) - 0.5)
+        if it == 1:
+            s.recover(__import__("torch").from_numpy(np.ascontiguousarray(du.reshape(-1))).cuda(), 0.75)
+            __import__("torch").cuda.synchronize()
+        else:
+            s.recover(du.reshape(-1), 0.75)
+        job.recover(du, 0.75)
+        h1, h2 = s.eas_history(), job.eas_history()
+        assert np.max(np.abs(h1[:, :2 * neas] - h2[:, :2 * neas])) <= 1e-9 * np.max(np.abs(h2[:, :2 * neas]))
+        assert np.all(h1[:, -1] == 0.75)
+    # Gauss-point output with the enhanced strains (the oracle job takes the library's history)
+    job.set_eas_history(s.eas_history())
+    for st in (fc.FC_STRESS_2PK, fc.FC_STRESS_CAUCHY):
+        gp, _ = s.evaluate_stress(u.reshape(-1), st, want_nodal=False)
+        for e in range(len(conn)):
+            ref = job.element_gp_stress(e, u, st)[1]
+            assert np.max(np.abs(gp[e] - ref)) <= 1e-12 * np.max(np.abs(ref))
+    for st in (fc.FC_STRAIN_GL, fc.FC_STRAIN_EA, fc.FC_STRAIN_LOG):
+        gp, _ = s.evaluate_strain(u.reshape(-1), st, want_nodal=False)
+        for e in range(len(conn)):
+            ref = job.element_gp_stress(e, u, oracle.OUTPUT_STRAIN + st)[1]
+            assert np.max(np.abs(gp[e] - ref)) <= 1e-12 * np.max(np.abs(ref))
+    assert np.array_equal(s.eas_history(), job.eas_history())  # the output leaves the history alone
+    # EAS exists for hex8 only
+    s2 = fc.Solid(0)
+    p = sd.Problem(sd.load("solid_ele_tet4_Standard_dynamic"), oracle.node_param_coords)
+    with pytest.raises(fc.FourCError) as ei:
+        s2.set_mesh(p.ct, form, p.X, p.node_gid, np.zeros(len(p.X), np.int32), p.conn, p.ele_gid)
+    assert ei.value.code == fc.FC_ERR_UNSUPPORTED
+    s2.close()
+    s.close()

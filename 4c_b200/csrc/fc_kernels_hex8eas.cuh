@@ -36,70 +36,43 @@ namespace fc
     static constexpr int epb = 4, threads = 32 * epb;
     // Gauss-point record: F(9) N_XYZ(24) cmat(36) S(6) fac m(6) G(36) H(36) T^T S(6) pad
     static constexpr int gF = 0, gN = 9, gC = 33, gS = 69, gFac = 75, gM = 76, gG = 82, gH = 118, gTS = 154, gpd = 160;
-    // per element: X(24) u(24) T(36) detJ0 pad alpha(NEAS) s(NEAS) | records | W = [Kaa | I] (NEAS x 2 NEAS) | Kda (24 x NEAS) | -Kda Kaa^-1
+    // per element: X(24) u(24) T(36) detJ0 pad alpha(NEAS) s(NEAS) | records | W = [Kaa | I] (NEAS x 2 NEAS) | Kda (24 x NEAS)
     static constexpr int sX = 0, sU = 24, sT = 48, sDet = 84, sAlpha = 86, sS = sAlpha + NEAS, sGp = (sS + NEAS + 1) / 2 * 2,
-                         sW = sGp + 8 * gpd, sKda = sW + 2 * NEAS * NEAS, sMki = sKda + 24 * NEAS, ele_doubles = (sMki + 24 * NEAS + 1) / 2 * 2;
+                         sW = sGp + 8 * gpd, sKda = sW + 2 * NEAS * NEAS, ele_doubles = (sKda + 24 * NEAS + 1) / 2 * 2;
     static constexpr size_t smem_bytes = sizeof(double) * ele_doubles * epb;
   };
 
-  // in-place inverse of a row-major 6 x 6 (Gauss-Jordan, partial pivoting)
-  __device__ inline void inv6(double* Tm)
+  // Entry (r, c) of the strain-like Voigt form of E -> A E A^T (rows r = (a, b), columns c = (p, q) in the order xx yy zz xy yz
+  // xz; shear rows and columns carry the doubled shear strains), A row-major 3 x 3.  The reference builds this matrix from the
+  // centroid Jacobian and inverts it with LAPACK (evaluate_voigt_transformation_matrix, calc_lib.hpp:1177-1244); the inverse of
+  // the map with A is the map with A^-1, so T0^-T is this matrix of J0^-1 and no 6 x 6 system is solved.
+  __device__ __forceinline__ double voigt_transformation_entry(const double* Am, int r, int c)
   {
-    double W[72];
-    for (int r = 0; r < 6; ++r)
-      for (int c = 0; c < 6; ++c)
-      {
-        W[12 * r + c] = Tm[6 * r + c];
-        W[12 * r + 6 + c] = r == c ? 1.0 : 0.0;
-      }
-    for (int k = 0; k < 6; ++k)
-    {
-      int piv = k;
-      for (int r = k + 1; r < 6; ++r)
-        if (fabs(W[12 * r + k]) > fabs(W[12 * piv + k])) piv = r;
-      if (piv != k)
-        for (int c = 0; c < 12; ++c)
-        {
-          const double t = W[12 * k + c];
-          W[12 * k + c] = W[12 * piv + c];
-          W[12 * piv + c] = t;
-        }
-      const double ip = 1.0 / W[12 * k + k];
-      for (int c = 0; c < 12; ++c) W[12 * k + c] *= ip;
-      for (int r = 0; r < 6; ++r)
-      {
-        if (r == k) continue;
-        const double m = W[12 * r + k];
-        for (int c = 0; c < 12; ++c) W[12 * r + c] -= m * W[12 * k + c];
-      }
-    }
-    for (int r = 0; r < 6; ++r)
-      for (int c = 0; c < 6; ++c) Tm[6 * r + c] = W[12 * r + 6 + c];
+    const int a = r < 3 ? r : (r == 4 ? 1 : 0), b = r < 3 ? r : (r == 3 ? 1 : 2);
+    const int p = c < 3 ? c : (c == 4 ? 1 : 0), q = c < 3 ? c : (c == 3 ? 1 : 2);
+    if (c < 3) return (r < 3 ? 1.0 : 2.0) * Am[3 * a + p] * Am[3 * b + p];
+    if (r < 3) return Am[3 * a + p] * Am[3 * a + q];
+    return Am[3 * a + p] * Am[3 * b + q] + Am[3 * b + p] * Am[3 * a + q];
   }
 
-  // T0^-T (row-major 6 x 6) and det J0 from the Jacobian at the element centroid; dN0 [8][3], Xs [8][3]
-  __device__ inline double eas_centroid_transformation(const double* __restrict__ dN0, const double* Xs, double* Tm)
+  // inverse of the centroid Jacobian iJ0 (row-major; J0[3 d + i] = dX_i / dxi_d) and det J0; dN0 [8][3], Xs [8][3]
+  __device__ __forceinline__ double eas_centroid_jacobian(const double* __restrict__ dN0, const double* Xs, double* iJ0)
   {
-    double J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // J[3 d + i] = dX_i / dxi_d
+    double J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
     for (int a = 0; a < 8; ++a)
       for (int d = 0; d < 3; ++d)
         for (int i = 0; i < 3; ++i) J[3 * d + i] += __ldg(dN0 + 3 * a + d) * Xs[3 * a + i];
-    const int va[6] = {0, 1, 2, 0, 1, 0}, vb[6] = {0, 1, 2, 1, 2, 2};
+    return inv3(J, iJ0);
+  }
+
+  // T0^-T (row-major 6 x 6) and det J0, one thread
+  __device__ inline double eas_centroid_transformation(const double* __restrict__ dN0, const double* Xs, double* Tm)
+  {
+    double iJ0[9];
+    const double detJ0 = eas_centroid_jacobian(dN0, Xs, iJ0);
     for (int r = 0; r < 6; ++r)
-      for (int c = 0; c < 6; ++c)
-      {
-        const int a = va[r], b = vb[r], p = va[c], q = vb[c];
-        double v;
-        if (c < 3)
-          v = (r < 3 ? 1.0 : 2.0) * J[3 * a + p] * J[3 * b + p];
-        else if (r < 3)
-          v = J[3 * a + p] * J[3 * a + q];
-        else
-          v = J[3 * a + p] * J[3 * b + q] + J[3 * b + p] * J[3 * a + q];
-        Tm[6 * r + c] = v;
-      }
-    inv6(Tm);
-    return det3(J);
+      for (int c = 0; c < 6; ++c) Tm[6 * r + c] = voigt_transformation_entry(iJ0, r, c);
+    return detJ0;
   }
 
   // m[6] = scale (r, s, t, rs, rt, st) of Gauss point gp
@@ -148,7 +121,7 @@ namespace fc
     if (e >= A.n_ele) return;  // the warps are independent: only __syncwarp below
     double* sm = smem + (size_t)el * Cfg::ele_doubles;
     double *Xs = sm + Cfg::sX, *us = sm + Cfg::sU, *Tm = sm + Cfg::sT, *alpha = sm + Cfg::sAlpha, *sv = sm + Cfg::sS,
-           *gpdat = sm + Cfg::sGp, *W = sm + Cfg::sW, *Kda = sm + Cfg::sKda, *mKi = sm + Cfg::sMki;
+           *gpdat = sm + Cfg::sGp, *W = sm + Cfg::sW, *Kda = sm + Cfg::sKda;
     double* hist = A.eas + (size_t)e * Cfg::hist_doubles;
     const int a = lane / 3, i = lane % 3;  // lanes 0..23: DOF d = lane = 3 a + i
     int node = 0;
@@ -160,7 +133,14 @@ namespace fc
     }
     if (lane < NEAS) alpha[lane] = hist[Cfg::oAlpha + lane];
     __syncwarp();
-    if (lane == 0) sm[Cfg::sDet] = eas_centroid_transformation(A.dNtab + (size_t)16 * 24, Xs, Tm);
+    {
+      // T0^-T: every lane inverts the centroid Jacobian and takes one or two of the 36 entries
+      double iJ0[9];
+      const double detJ0 = eas_centroid_jacobian(A.dNtab + (size_t)16 * 24, Xs, iJ0);
+      Tm[lane] = voigt_transformation_entry(iJ0, lane / 6, lane % 6);
+      if (lane < 4) Tm[32 + lane] = voigt_transformation_entry(iJ0, 5, 2 + lane);
+      if (lane == 0) sm[Cfg::sDet] = detJ0;
+    }
     __syncwarp();
 
     // ---- Gauss-point records (lanes 0..7) ----------------------------------------------------------
@@ -187,25 +167,32 @@ namespace fc
       for (int k = 0; k < 6; ++k) R[Cfg::gS + k] = S[k];
       R[Cfg::gFac] = detJ * __ldg(A.gpw + gp);
       for (int k = 0; k < 6; ++k) R[Cfg::gM + k] = m[k];
-      // H = cmat T, G = T^T H, T^T S
-      for (int v = 0; v < 6; ++v)
-        for (int c = 0; c < 6; ++c)
-        {
-          double h = 0.0;
-          for (int w = 0; w < 6; ++w) h += cmat[6 * v + w] * Tm[6 * w + c];
-          R[Cfg::gH + 6 * v + c] = h;
-        }
-      for (int r = 0; r < 6; ++r)
+    }
+    __syncwarp();
+    // H = cmat T, then G = T^T H and T^T S of the eight records, entries over the lanes
+    for (int idx = lane; idx < 8 * 36; idx += 32)
+    {
+      double* R = gpdat + (size_t)(idx / 36) * Cfg::gpd;
+      const int v = (idx % 36) / 6, c = idx % 6;
+      double h = 0.0;
+      for (int w = 0; w < 6; ++w) h += R[Cfg::gC + 6 * v + w] * Tm[6 * w + c];
+      R[Cfg::gH + 6 * v + c] = h;
+    }
+    __syncwarp();
+    for (int idx = lane; idx < 8 * 42; idx += 32)
+    {
+      double* R = gpdat + (size_t)(idx / 42) * Cfg::gpd;
+      const int r = (idx % 42) / 7, c = idx % 7;
+      double g = 0.0;
+      if (c < 6)
       {
-        for (int c = 0; c < 6; ++c)
-        {
-          double g = 0.0;
-          for (int v = 0; v < 6; ++v) g += Tm[6 * v + r] * R[Cfg::gH + 6 * v + c];
-          R[Cfg::gG + 6 * r + c] = g;
-        }
-        double ts = 0.0;
-        for (int v = 0; v < 6; ++v) ts += Tm[6 * v + r] * S[v];
-        R[Cfg::gTS + r] = ts;
+        for (int v = 0; v < 6; ++v) g += Tm[6 * v + r] * R[Cfg::gH + 6 * v + c];
+        R[Cfg::gG + 6 * r + c] = g;
+      }
+      else
+      {
+        for (int v = 0; v < 6; ++v) g += Tm[6 * v + r] * R[Cfg::gS + v];
+        R[Cfg::gTS + r] = g;
       }
     }
     __syncwarp();
@@ -320,11 +307,7 @@ namespace fc
         for (int l = 0; l < NEAS; ++l) mk[l] -= kd * W[k * N2 + NEAS + l];
       }
 #pragma unroll
-      for (int l = 0; l < NEAS; ++l)
-      {
-        mKi[lane * NEAS + l] = mk[l];
-        fd += mk[l] * sv[l];
-      }
+      for (int l = 0; l < NEAS; ++l) fd += mk[l] * sv[l];
     }
     if (lane < NEAS) hist[Cfg::oS + lane] = sv[lane];
     for (int idx = lane; idx < NEAS * NEAS; idx += 32) hist[Cfg::oInvKaa + idx] = W[(idx % NEAS) * N2 + NEAS + idx / NEAS];

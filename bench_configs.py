@@ -282,6 +282,11 @@ def main():
         ("C4 hex8 F-bar NeoHooke nu=0.499 200^3", H8, FB, NH, 0.499, (200, 200, 200), 0),
         ("C5/8 hex8 NeoHooke 200^3 (one GPU's share of 400^3)", H8, D, NH, 0.25, (200, 200, 200), 0),
         ("C5/8-oc hex8 NeoHooke 200^3, owner-computed rows", H8, D, NH, 0.25, (200, 200, 200), fc.FC_EVAL_OWNER_COMPUTED),
+        # SURVEY 8f F4 formulations (on request): element histories in HBM (EAS 325 / 1009 doubles per element, MULF 144)
+        ("F4 hex8 eas_mild NeoHooke 100^3", H8, fc.FC_FORM_EAS_MILD, NH, 0.25, (100, 100, 100), 0),
+        ("F4 hex8 eas_full NeoHooke 100^3", H8, fc.FC_FORM_EAS_FULL, NH, 0.25, (100, 100, 100), 0),
+        ("F4 hex8 mulf NeoHooke 100^3", H8, fc.FC_FORM_MULF, NH, 0.25, (100, 100, 100), 0),
+        ("F4 hex8 linear SVK 100^3", H8, fc.FC_FORM_LINEAR, SVK, 0.3, (100, 100, 100), 0),
     ]
     if args.only and args.only.startswith("variantB"):
         run_variant_b(fc, int(args.only[8:] or 100), args.steps)
@@ -295,8 +300,8 @@ def main():
     for c in cfgs:
         if args.only and (c[0] not in names if exact else args.only not in c[0]):
             continue
-        if not args.only and ("C3a-96" in c[0] or "C3a-full" in c[0]):
-            continue  # large hex27 cases only on request
+        if not args.only and ("C3a-96" in c[0] or "C3a-full" in c[0] or c[0].startswith("F4 ")):
+            continue  # large hex27 cases and the F4 formulations only on request
         run(fc, c[0], c[1], c[2], c[3], c[4], c[5], args.steps, c[6])
 
 

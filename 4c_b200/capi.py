@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
 
 FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
-FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR, FC_FORM_MULF, FC_FORM_EAS_MILD, FC_FORM_EAS_FULL = 0, 1, 2, 3, 4, 5
+FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR, FC_FORM_MULF, FC_FORM_EAS_MILD, FC_FORM_EAS_FULL, FC_FORM_MULF_FBAR = 0, 1, 2, 3, 4, 5, 6
 FC_STRAIN_GL, FC_STRAIN_EA, FC_STRAIN_LOG = 0, 1, 2
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_SUMMAND_COUPNEOHOOKE, FC_SUMMAND_COUPSVK, FC_SUMMAND_COUPANISOEXPO = 0, 1, 2
@@ -245,7 +245,7 @@ class Solid:
 
     def set_mesh(self, celltype, formulation, X, node_gid, node_owner, conn, ele_gid):
         X, node_gid, node_owner, conn, ele_gid = _f64(X), _i32(node_gid), _i32(node_owner), _i32(conn), _i32(ele_gid)
-        self.celltype, self.nen = celltype, NEN[celltype]
+        self.celltype, self.nen, self.formulation = celltype, NEN[celltype], formulation
         self.n_col_nodes, self.n_ele = len(node_gid), len(ele_gid)
         self.n_col_dof = 3 * self.n_col_nodes
         self.n_row_dof = 3 * int(np.sum(node_owner == self.rank))
@@ -290,13 +290,13 @@ class Solid:
 
     def mulf_history(self):
         """(n_col_ele, ngp, 18) inverse Jacobian | deformation gradient of every Gauss point"""
-        h = np.zeros((self.n_ele, NGP[self.celltype], 18))
+        h = np.zeros((self.n_ele, NGP[self.celltype] + (1 if self.formulation == FC_FORM_MULF_FBAR else 0), 18))
         self._chk(lib().fc_solid_mulf_get_history(self.h, _ptr(h)))
         return h
 
     def set_mulf_history(self, history):
         h = _f64(history)
-        assert h.size == self.n_ele * NGP[self.celltype] * 18
+        assert h.size == self.n_ele * (NGP[self.celltype] + (1 if self.formulation == FC_FORM_MULF_FBAR else 0)) * 18
         self._chk(lib().fc_solid_mulf_set_history(self.h, _ptr(h)))
 
     def build_graph(self):

@@ -190,6 +190,9 @@ namespace
       }
     if (ctx->formulation == FC_FORM_EAS_MILD) return launch_hex8_eas<9, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_EAS_FULL) return launch_hex8_eas<21, WANT_K>(ctx, A);
+    if (ctx->formulation == FC_FORM_MULF_FBAR)
+      return ctx->celltype == FC_HEX8 ? launch_generic<fc::HEX8, fc::FORM_MULF_FBAR, WANT_K>(ctx, A)
+                                      : launch_generic<fc::PYRAMID5, fc::FORM_MULF_FBAR, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_MULF)  // PRESTRESS_TECH mulf: same kernel, F from the Gauss-point history
       switch (ctx->celltype)
       {
@@ -221,14 +224,22 @@ namespace
     return nh_gen ? launch_nh_gen<fc::TET10, WANT_K>(ctx, A) : launch_generic<fc::TET10, fc::FORM_DISP, WANT_K>(ctx, A);
   }
 
+  // MULF history records per element: the Gauss points, with F-bar also the centroid; 0 without MULF
+  int mulf_records(const fc_ctx* ctx)
+  {
+    if (ctx->formulation != FC_FORM_MULF && ctx->formulation != FC_FORM_MULF_FBAR) return 0;
+    return fc::mulf_records(fc::cell_ngp(ctx->celltype), ctx->formulation == FC_FORM_MULF_FBAR ? fc::FORM_MULF_FBAR : fc::FORM_MULF);
+  }
+
   // k_mulf_history over all column elements: u == nullptr writes the initial history
   cudaError_t launch_mulf_history(fc_ctx* ctx, const double* d_u)
   {
-    const long long nt = (long long)ctx->n_ele * fc::cell_ngp(ctx->celltype);
+    const int nrec = mulf_records(ctx);
+    const long long nt = (long long)ctx->n_ele * nrec;
     if (nt == 0) return cudaSuccess;
     const int bs = 128;
     const unsigned gs = (unsigned)((nt + bs - 1) / bs);
-#define FC_MULF_HISTORY(CT) fc::k_mulf_history<CT><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->n_ele, ctx->d_dNtab, d_u, ctx->d_mulf)
+#define FC_MULF_HISTORY(CT) fc::k_mulf_history<CT><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->n_ele, ctx->d_dNtab, d_u, ctx->d_mulf, nrec)
     switch (ctx->celltype)
     {
       case FC_HEX8: FC_MULF_HISTORY(fc::HEX8); break;
@@ -305,8 +316,8 @@ int fc_mulf_init(fc_ctx* ctx)
     ctx->launches++;
     FC_CUDA(cudaGetLastError());
   }
-  if (ctx->formulation != FC_FORM_MULF || ctx->n_ele == 0) return FC_OK;
-  FC_CUDA(cudaMalloc((void**)&ctx->d_mulf, sizeof(double) * 18 * (size_t)ctx->n_ele * fc::cell_ngp(ctx->celltype)));
+  if (!mulf_records(ctx) || ctx->n_ele == 0) return FC_OK;
+  FC_CUDA(cudaMalloc((void**)&ctx->d_mulf, sizeof(double) * 18 * (size_t)ctx->n_ele * mulf_records(ctx)));
   FC_CUDA(launch_mulf_history(ctx, nullptr));
   return FC_OK;
 }
@@ -536,7 +547,7 @@ extern "C"
   int fc_solid_update_prestress(fc_ctx* ctx, const double* u_col)
   {
     if (!ctx || ctx->celltype < 0 || !u_col) return fail(ctx, FC_ERR_INVALID, "mesh and u_col are required");
-    if (ctx->formulation != FC_FORM_MULF) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF");
+    if (!mulf_records(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF / FC_FORM_MULF_FBAR");
     if (ctx->n_ele == 0) return FC_OK;
     FC_CUDA(cudaSetDevice(ctx->device));
     double* t_u = nullptr;
@@ -558,10 +569,10 @@ extern "C"
   int fc_solid_mulf_get_history(fc_ctx* ctx, double* history)
   {
     if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
-    if (ctx->formulation != FC_FORM_MULF) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF");
+    if (!mulf_records(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF / FC_FORM_MULF_FBAR");
     if (ctx->n_ele == 0) return FC_OK;
     FC_CUDA(cudaSetDevice(ctx->device));
-    FC_CUDA(cudaMemcpyAsync(history, ctx->d_mulf, sizeof(double) * 18 * (size_t)ctx->n_ele * fc::cell_ngp(ctx->celltype), cudaMemcpyDefault, ctx->stream));
+    FC_CUDA(cudaMemcpyAsync(history, ctx->d_mulf, sizeof(double) * 18 * (size_t)ctx->n_ele * mulf_records(ctx), cudaMemcpyDefault, ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
     return FC_OK;
   }
@@ -569,10 +580,10 @@ extern "C"
   int fc_solid_mulf_set_history(fc_ctx* ctx, const double* history)
   {
     if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
-    if (ctx->formulation != FC_FORM_MULF) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF");
+    if (!mulf_records(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF / FC_FORM_MULF_FBAR");
     if (ctx->n_ele == 0) return FC_OK;
     FC_CUDA(cudaSetDevice(ctx->device));
-    FC_CUDA(cudaMemcpyAsync(ctx->d_mulf, history, sizeof(double) * 18 * (size_t)ctx->n_ele * fc::cell_ngp(ctx->celltype), cudaMemcpyDefault, ctx->stream));
+    FC_CUDA(cudaMemcpyAsync(ctx->d_mulf, history, sizeof(double) * 18 * (size_t)ctx->n_ele * mulf_records(ctx), cudaMemcpyDefault, ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
     return FC_OK;
   }

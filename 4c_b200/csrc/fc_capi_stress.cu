@@ -208,6 +208,7 @@ static int gp_output_run(fc_ctx* ctx, const double* u_col, int stress_type, doub
   A.mulf = ctx->d_mulf;
   A.eas = ctx->d_eas;
   const bool fbar = ctx->formulation == FC_FORM_FBAR, lin = ctx->formulation == FC_FORM_LINEAR, mulf = ctx->formulation == FC_FORM_MULF;
+  const bool mulf_fbar = ctx->formulation == FC_FORM_MULF_FBAR;
   int rc = FC_ERR_UNSUPPORTED;
 #define FC_STRESS(CT) \
   rc = lin    ? stress_impl<CT, fc::FORM_LINEAR>(ctx, A, stress_type, d_gp, d_nodal) \
@@ -216,7 +217,9 @@ static int gp_output_run(fc_ctx* ctx, const double* u_col, int stress_type, doub
   switch (ctx->celltype)
   {
     case FC_HEX8:
-      if (fbar)
+      if (mulf_fbar)
+        rc = stress_impl<fc::HEX8, fc::FORM_MULF_FBAR>(ctx, A, stress_type, d_gp, d_nodal);
+      else if (fbar)
         rc = stress_impl<fc::HEX8, fc::FORM_FBAR>(ctx, A, stress_type, d_gp, d_nodal);
       else
         FC_STRESS(fc::HEX8);
@@ -227,7 +230,9 @@ static int gp_output_run(fc_ctx* ctx, const double* u_col, int stress_type, doub
     case FC_TET4: FC_STRESS(fc::TET4); break;
     case FC_WEDGE6: FC_STRESS(fc::WEDGE6); break;
     case FC_PYRAMID5:
-      if (fbar)
+      if (mulf_fbar)
+        rc = stress_impl<fc::PYRAMID5, fc::FORM_MULF_FBAR>(ctx, A, stress_type, d_gp, d_nodal);
+      else if (fbar)
         rc = stress_impl<fc::PYRAMID5, fc::FORM_FBAR>(ctx, A, stress_type, d_gp, d_nodal);
       else
         FC_STRESS(fc::PYRAMID5);

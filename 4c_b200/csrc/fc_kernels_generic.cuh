@@ -23,9 +23,15 @@ namespace fc
     FORM_FBAR = 1,
     FORM_LINEAR = 2,  // KINEM linear: B-operator at F = I, strain = B u, no geometric stiffness
                       // (src/solid_3D_ele/4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155)
-    FORM_MULF = 3     // PRESTRESS_TECH mulf: F = (I + u N_xyz_hist^T) F_hist with the history of the prestress updates
+    FORM_MULF = 3,    // PRESTRESS_TECH mulf: F = (I + u N_xyz_hist^T) F_hist with the history of the prestress updates
                       // (src/solid_3D_ele/4C_solid_3D_ele_calc_mulf.hpp:40-196, ..._calc_lib_mulf.hpp:24-84)
+    FORM_MULF_FBAR = 6  // both (hex8, pyramid5; 4C_solid_3D_ele_calc_mulf_fbar.hpp:33-300): F-bar with the MULF deformation gradients
+                        // of the Gauss points and of the centroid, whose history is one more record behind the Gauss points'
   };
+  __host__ __device__ constexpr bool form_fbar(int form) { return form == FORM_FBAR || form == FORM_MULF_FBAR; }
+  __host__ __device__ constexpr bool form_mulf(int form) { return form == FORM_MULF || form == FORM_MULF_FBAR; }
+  // MULF history records of one element
+  __host__ __device__ constexpr int mulf_records(int ngp, int form) { return form == FORM_MULF_FBAR ? ngp + 1 : ngp; }
 
   // MULF: deformation gradient update delta = I + u (invJ_hist dN)^T of one Gauss point.  dN [nen][3], us [nen][3],
   // invJh row-major; delta row-major [3 i + I]
@@ -71,7 +77,7 @@ namespace fc
     // per-Gauss-point record: F(9) N_XYZ(3 nen) cmat(36) S(6) fac_mat fac_geo fac_force pad [H(3 nen) v(6)]
     static constexpr int oF = 0, oN = 9, oC = 9 + 3 * nen, oS = oC + 36, oFac = oS + 6, oH = oFac + 4,
                          oV = oH + 3 * nen;
-    static constexpr int gpd = FORM == FORM_FBAR ? oV + 6 : oH;
+    static constexpr int gpd = form_fbar(FORM) ? oV + 6 : oH;
     static constexpr int ele_doubles = 6 * nen + ngp * gpd;  // X, u, gp records
     static constexpr size_t smem_bytes = sizeof(double) * (size_t)epb * ele_doubles + 64;
   };
@@ -81,15 +87,16 @@ namespace fc
   //                 MulfFormulation::evaluate stores at its first call, calc_mulf.hpp:59-63) and F = I
   //   u != nullptr: MulfFormulation::update_prestress (calc_mulf.hpp:150-171) with the displacements of the finished step:
   //                 F_hist <- (I + u N_xyz_hist^T) F_hist,  invJ_hist <- (I + u N_xyz_hist^T)^-T invJ_hist
+  // nrec = ngp, or ngp + 1 with the centroid's record last (FORM_MULF_FBAR)
   template <int CT>
   __global__ void k_mulf_history(const double* __restrict__ X, const int* __restrict__ conn, int n_ele, const double* __restrict__ dNtab,
-      const double* __restrict__ u, double* hist)
+      const double* __restrict__ u, double* hist, int nrec)
   {
     constexpr int NEN = Cell<CT>::nen, NGP = Cell<CT>::ngp;
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid >= (long long)n_ele * NGP) return;
-    const int e = (int)(tid / NGP), gp = (int)(tid % NGP);
-    const double* dN = dNtab + (size_t)gp * NEN * 3;
+    if (tid >= (long long)n_ele * nrec) return;
+    const int e = (int)(tid / nrec), gp = (int)(tid % nrec);
+    const double* dN = dNtab + (size_t)(gp < NGP ? gp : NGP + NEN) * NEN * 3;
     double* H = hist + (size_t)tid * 18;
     if (!u)
     {
@@ -230,12 +237,22 @@ namespace fc
     // ---- phase 1: Gauss-point records ----------------------------------------------------------
     if (active)
     {
-      double N0[FORM == FORM_FBAR ? ND : 1], iF0[9], detF0 = 1.0;
-      if (FORM == FORM_FBAR)
+      constexpr int NREC = mulf_records(NGP, FORM);
+      double N0[form_fbar(FORM) ? ND : 1], iF0[9], detF0 = 1.0;
+      if (form_fbar(FORM))
       {
         double F0[9];
         jacobian_mapping<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, Xs, N0);
-        deformation_gradient<CT>(Xs, us, N0, F0);
+        if (FORM == FORM_MULF_FBAR)
+        {
+          // MulfFBarFormulation::prepare: N_XYZ_0 of the reference Jacobian, F_0 from the centroid's history record
+          double hl[18], delta[9];
+          mulf_load(A.mulf + ((size_t)e * NREC + NGP) * 18, hl);
+          mulf_delta<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, us, hl, delta);
+          mat3_mul(delta, hl + 9, F0);
+        }
+        else
+          deformation_gradient<CT>(Xs, us, N0, F0);
         detF0 = inv3(F0, iF0);
       }
       for (int gp = a; gp < NGP; gp += NEN)
@@ -244,10 +261,10 @@ namespace fc
         double* Nx = R + Cfg::oN;
         const double detJ = jacobian_mapping<NEN>(A.dNtab + (size_t)gp * ND, Xs, Nx);
         double F[9];
-        if (FORM == FORM_MULF)
+        if (form_mulf(FORM))
         {
           // evaluate_mulf_spatial_material_mapping; the B-operator and K_geo below keep the N_XYZ of the reference mapping
-          const double* hist = A.mulf + ((size_t)e * NGP + gp) * 18;
+          const double* hist = A.mulf + ((size_t)e * NREC + gp) * 18;
           double hl[18], delta[9];
           mulf_load(hist, hl);
           mulf_delta<NEN>(A.dNtab + (size_t)gp * ND, us, hl, delta);
@@ -257,8 +274,8 @@ namespace fc
           deformation_gradient<CT>(Xs, us, Nx, F);
         const double intfac = detJ * __ldg(A.gpw + gp);
         double fbar = 1.0, iF[9];
-        const double detF = FORM == FORM_FBAR ? inv3(F, iF) : (FORM == FORM_LINEAR ? 1.0 : det3(F));
-        if (FORM == FORM_FBAR) fbar = pow(detF0 / detF, 1.0 / 3.0);
+        const double detF = form_fbar(FORM) ? inv3(F, iF) : (FORM == FORM_LINEAR ? 1.0 : det3(F));
+        if (form_fbar(FORM)) fbar = pow(detF0 / detF, 1.0 / 3.0);
         if (!(detJ > 0.0) || detF == 0.0 || !isfinite(detF) || !isfinite(fbar)) s_bad[el] = 1;
         // right Cauchy-Green of the (modified) deformation gradient, symmetric-6
         double C[6];
@@ -293,7 +310,7 @@ namespace fc
         R[Cfg::oFac + 0] = intfac * fbar;  // elastic stiffness   (calc_fbar.hpp:176-178)
         R[Cfg::oFac + 1] = FORM == FORM_LINEAR ? 0.0 : intfac / fbar;  // geometric stiffness (:179-180); none with linear kinematics
         R[Cfg::oFac + 2] = intfac / fbar;  // internal force      (:164-166)
-        if (FORM == FORM_FBAR)
+        if (form_fbar(FORM))
         {
           // H operator (lib_fbar.hpp:71-104) and v = (w f/3) cmat:C_gp - (w/f/3) S (lib_fbar.hpp:133-147)
           for (int b = 0; b < NEN; ++b)
@@ -370,7 +387,7 @@ namespace fc
           const double SN1 = fg * (S[3] * n0 + S[1] * n1 + S[4] * n2);
           const double SN2 = fg * (S[5] * n0 + S[4] * n1 + S[2] * n2);
           double q[3] = {0, 0, 0};
-          if (FORM == FORM_FBAR)
+          if (form_fbar(FORM))
             for (int i = 0; i < 3; ++i)
               for (int v = 0; v < 6; ++v) q[i] += Ba[3 * v + i] * R[Cfg::oV + v];
 #pragma unroll
@@ -392,7 +409,7 @@ namespace fc
 #pragma unroll
                   for (int v = 0; v < 6; ++v) s += CBa[3 * v + i] * Bb[3 * v + j];
                   if (i == j) s += geo;
-                  if (FORM == FORM_FBAR) s += q[i] * R[Cfg::oH + 3 * b + j];
+                  if (form_fbar(FORM)) s += q[i] * R[Cfg::oH + 3 * b + j];
                   acc[9 * bb + 3 * i + j] = s;
                 }
             }

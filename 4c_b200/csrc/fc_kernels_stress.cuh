@@ -142,9 +142,10 @@ namespace fc
     }
     double Nx[ND], F[9];
     jacobian_mapping<NEN>(A.dNtab + (size_t)gp * ND, Xs, Nx);
-    if (FORM == FORM_MULF)
+    constexpr int NREC = mulf_records(NGP, FORM);
+    if (form_mulf(FORM))
     {
-      const double* hist = A.mulf + ((size_t)e * NGP + gp) * 18;
+      const double* hist = A.mulf + ((size_t)e * NREC + gp) * 18;
       double hl[18], delta[9];
       mulf_load(hist, hl);
       mulf_delta<NEN>(A.dNtab + (size_t)gp * ND, us, hl, delta);
@@ -152,11 +153,21 @@ namespace fc
     }
     else
       deformation_gradient<CT>(Xs, us, Nx, F);
-    if (FORM == FORM_FBAR)
+    if (form_fbar(FORM))
     {
       double N0[ND], F0[9];
-      jacobian_mapping<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, Xs, N0);
-      deformation_gradient<CT>(Xs, us, N0, F0);
+      if (FORM == FORM_MULF_FBAR)
+      {
+        double hl[18], delta[9];
+        mulf_load(A.mulf + ((size_t)e * NREC + NGP) * 18, hl);
+        mulf_delta<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, us, hl, delta);
+        mat3_mul(delta, hl + 9, F0);
+      }
+      else
+      {
+        jacobian_mapping<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, Xs, N0);
+        deformation_gradient<CT>(Xs, us, N0, F0);
+      }
       const double fbar = pow(det3(F0) / det3(F), 1.0 / 3.0);
       for (int i = 0; i < 9; ++i) F[i] *= fbar;
     }

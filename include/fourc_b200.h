@@ -68,8 +68,10 @@ extern "C"
     FC_FORM_MULF = 3,         /* PRESTRESS_TECH mulf: 4C_solid_3D_ele_calc_mulf.hpp:40-196 (every cell); Gauss-point history in the
                                  context, see fc_solid_update_prestress */
     FC_FORM_EAS_MILD = 4,     /* TECH eas_mild (hex8, 9 enhanced strain modes) and */
-    FC_FORM_EAS_FULL = 5      /* TECH eas_full (hex8, 21 modes): 4C_solid_3D_ele_calc_eas.hpp:44-291; element history in the
+    FC_FORM_EAS_FULL = 5,     /* TECH eas_full (hex8, 21 modes): 4C_solid_3D_ele_calc_eas.hpp:44-291; element history in the
                                  context, see fc_solid_recover */
+    FC_FORM_MULF_FBAR = 6     /* TECH fbar with PRESTRESS_TECH mulf (hex8 and pyramid5): 4C_solid_3D_ele_calc_mulf_fbar.hpp:33-300;
+                                 the history has one more record per element, for the centroid, behind the Gauss points' */
   };
   /* materials: MAT_Struct_StVenantKirchhoff (src/mat/4C_mat_stvenantkirchhoff.cpp) and
    * MAT_ElastHyper with one ELAST_CoupNeoHooke summand (src/mat/4C_mat_elasthyper.cpp,
@@ -151,7 +153,8 @@ extern "C"
   /* FC_FORM_MULF (modified updated Lagrangian prestressing).  The context keeps, per column element and Gauss point, the
    * history of MulfHistoryData (src/solid_3D_ele/4C_solid_3D_ele_calc_lib_mulf.hpp:24-33): 18 doubles = inverse Jacobian
    * (N_xyz = invJ dN) | deformation gradient, both column-major like the Core::LinAlg::Matrix<3, 3> members; fc_solid_set_mesh initialises it (reference Jacobian,
-   * identity).  fc_solid_update_prestress is struct_update_prestress (Solid::ModelEvaluator::Structure::update_step_element,
+   * identity; FC_FORM_MULF_FBAR: [n_col_ele][ngp + 1][18], the last record of an element is its centroid's).
+   * fc_solid_update_prestress is struct_update_prestress (Solid::ModelEvaluator::Structure::update_step_element,
    * 4C_structure_new_model_evaluator_structure.cpp:1555-1592 -> MulfFormulation::update_prestress) with the column
    * displacements (host|device) of the finished step; the caller resets its displacements afterwards like
    * Solid::IMPLICIT::PreStress::post_update.  get/set move the history (host|device, [n_col_ele][ngp][18]) for restart files. */

@@ -160,7 +160,7 @@ namespace fc_oracle
                                 action == 0 ? Ke.data() : nullptr, fib, fiber_gp_stride)
                           : element_evaluate(mesh.ct, form, mp, X.data(), u.data(), fe.data(), action == 0 ? Ke.data() : nullptr, nullptr,
                                 0.0, nullptr, STRESS_CAUCHY, fib, fiber_gp_stride,
-                                mulf_hist ? mulf_hist + (size_t)18 * num_gp(mesh.ct) * e : nullptr);
+                                mulf_hist ? mulf_hist + (size_t)18 * mulf_records(mesh.ct, form) * e : nullptr);
       if (err)
       {
         if (nbad == 0 && first_bad) *first_bad = eg;

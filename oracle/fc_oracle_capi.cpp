@@ -209,16 +209,16 @@ extern "C"
       js->job.eas_hist.assign((size_t)nh * js->job.mesh.ele_gid.size(), 0.0);
       for (size_t e = 0; e < js->job.mesh.ele_gid.size(); ++e) eas_history_init(neas, &js->job.eas_hist[(size_t)nh * e]);
     }
-    if (js->job.form != FORM_MULF) return;
     const Mesh& m = js->job.mesh;
-    const int ngp = num_gp(m.ct);
+    const int ngp = mulf_records(m.ct, js->job.form);  // records per element (MULF with F-bar: + the centroid)
+    if (ngp == 0) return;
     js->job.mulf_hist.assign((size_t)18 * ngp * m.ele_gid.size(), 0.0);
     std::vector<double> X((size_t)3 * m.nen);
     for (size_t e = 0; e < m.ele_gid.size(); ++e)
     {
       for (int a = 0; a < m.nen; ++a)
         for (int i = 0; i < 3; ++i) X[3 * a + i] = m.node_X[3 * (size_t)m.node_index.at(m.ele_nodes[e * m.nen + a]) + i];
-      mulf_history(m.ct, X.data(), nullptr, &js->job.mulf_hist[(size_t)18 * ngp * e]);
+      mulf_history(m.ct, X.data(), nullptr, &js->job.mulf_hist[(size_t)18 * ngp * e], js->job.form == FORM_MULF_FBAR);
     }
   }
   void oracle_job_set_problem(void* h, int form, int kind, double young, double nue)
@@ -234,7 +234,7 @@ extern "C"
     auto* js = (JobState*)h;
     const Mesh& m = js->job.mesh;
     if (js->job.mulf_hist.empty()) return;
-    const int ngp = num_gp(m.ct);
+    const int ngp = mulf_records(m.ct, js->job.form);
     std::vector<double> X((size_t)3 * m.nen), u((size_t)3 * m.nen);
     for (size_t e = 0; e < m.ele_gid.size(); ++e)
     {
@@ -247,7 +247,7 @@ extern "C"
           u[3 * a + i] = u_nodes[3 * ni + i];
         }
       }
-      mulf_history(m.ct, X.data(), u.data(), &js->job.mulf_hist[(size_t)18 * ngp * e]);
+      mulf_history(m.ct, X.data(), u.data(), &js->job.mulf_hist[(size_t)18 * ngp * e], js->job.form == FORM_MULF_FBAR);
     }
   }
   // struct_calc_recover of the EAS elements (default step): du_nodes [n_nodes][3] = the Newton increment in the mesh's node order
@@ -326,7 +326,7 @@ extern "C"
           nullptr, fib, job.fiber_gp_stride, gp_stress, strain ? 1 : 0, strain ? stress_type - OUTPUT_STRAIN : stress_type);
     }
     return element_evaluate(m.ct, job.form, job.mp, X.data(), u.data(), nullptr, nullptr, nullptr, 0.0, gp_stress, stress_type, fib,
-        job.fiber_gp_stride, job.mulf_hist.empty() ? nullptr : job.mulf_hist.data() + (size_t)18 * ngp * e);
+        job.fiber_gp_stride, job.mulf_hist.empty() ? nullptr : job.mulf_hist.data() + (size_t)18 * mulf_records(m.ct, job.form) * e);
   }
   // MAT_ElastHyper with a summand list (kinds [n], par [n][4]) and optional element fibres FIBER1 [n_ele][3] in the job's
   // element order (NULL = none)

@@ -35,7 +35,9 @@ namespace fc_oracle
     FORM_LINEAR = 2,  // KINEM linear: src/solid_3D_ele/4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155
     FORM_MULF = 3,    // PRESTRESS_TECH mulf: src/solid_3D_ele/4C_solid_3D_ele_calc_mulf.hpp:40-196, ..._calc_lib_mulf.hpp:24-84
     FORM_EAS_MILD = 4,  // TECH eas_mild (hex8, 9 modes) and
-    FORM_EAS_FULL = 5   // TECH eas_full (hex8, 21 modes): src/solid_3D_ele/4C_solid_3D_ele_calc_eas.hpp, fc_oracle_eas.hpp
+    FORM_EAS_FULL = 5,  // TECH eas_full (hex8, 21 modes): src/solid_3D_ele/4C_solid_3D_ele_calc_eas.hpp, fc_oracle_eas.hpp
+    FORM_MULF_FBAR = 6  // TECH fbar PRESTRESS_TECH mulf (hex8, pyramid5): src/solid_3D_ele/4C_solid_3D_ele_calc_mulf_fbar.hpp:33-300;
+                        // history [ngp + 1][18], the last record belongs to the centroid
   };
 
   enum EleError
@@ -218,13 +220,27 @@ namespace fc_oracle
     // F-bar preparation: centroid jacobian mapping + centroid F          calc_fbar.hpp:55-63
     JacobianMapping<NEN> jm0;
     SpatialMaterialMapping<NEN> sm0;
-    if (form == FORM_FBAR)
+    const bool fbar_like = form == FORM_FBAR || form == FORM_MULF_FBAR;
+    // F = (I + u N_xyz_hist^T) F_hist with N_xyz_hist = invJ_hist dN (evaluate_mulf_spatial_material_mapping, calc_lib_mulf.hpp:34-84)
+    auto mulf_mapping = [&](const double* hist, const double* dN, SpatialMaterialMapping<NEN>& sm)
+    {
+      double Nh[3 * NEN], delta[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+      multiply_nn<3, 3, NEN>(Nh, hist, dN);
+      multiply_nt_scaled<3, NEN, 3>(1.0, delta, u, Nh, 1.0);
+      multiply_nn<3, 3, 3>(sm.F, delta, hist + 9);
+      invert3x3(sm.iF, sm.F, &singular);
+      sm.detF = determinant3x3(sm.F);
+    };
+    if (fbar_like)
     {
       double xi0[3], dN0[3 * NEN];
       centroid_param(ct, xi0);
       shape_function_deriv1(ct, xi0, dN0);
       evaluate_jacobian_mapping<NEN>(dN0, X, jm0, &singular);
       evaluate_spatial_material_mapping<NEN>(ct, jm0, x, u, 1.0, sm0, &singular);
+      // MulfFBarFormulation::prepare (calc_mulf_fbar.hpp:118-143): N_XYZ_0 stays that of the reference Jacobian, the centroid
+      // deformation gradient comes from the centroid's history record
+      if (form == FORM_MULF_FBAR) mulf_mapping(mulf_hist + 18 * NGP, dN0, sm0);
     }
 
     // negative Jacobian check at the element nodes                   calc_lib.hpp:475-496
@@ -294,6 +310,7 @@ namespace fc_oracle
       }
       else
       {
+        if (form == FORM_MULF_FBAR) mulf_mapping(mulf_hist + 18 * gp, dN, sm);  // MulfFBarFormulation::evaluate, calc_mulf_fbar.hpp:162-166
         fbar_factor = std::pow(sm0.detF / sm.detF, 1.0 / 3.0);  // lib_fbar.hpp:49-53
         evaluate_strain_gradient<NEN>(jm.N_XYZ, sm.F, B);
         // H operator                                                 lib_fbar.hpp:71-104
@@ -311,7 +328,10 @@ namespace fc_oracle
         }
         multiply_tn<3, 3, 3>(Cg, sm.F, sm.F);  // linearization.cauchygreen (unmodified F)
         SpatialMaterialMapping<NEN> smbar;
-        evaluate_spatial_material_mapping<NEN>(ct, jm, x, u, fbar_factor, smbar, &singular);
+        if (form == FORM_MULF_FBAR)
+          for (int i = 0; i < 9; ++i) smbar.F[i] = fbar_factor * sm.F[i];  // get_spatial_material_mapping_bar, calc_mulf_fbar.hpp:59-70
+        else
+          evaluate_spatial_material_mapping<NEN>(ct, jm, x, u, fbar_factor, smbar, &singular);
         for (int i = 0; i < 9; ++i) Fmat[i] = smbar.F[i];
         multiply_tn<3, 3, 3>(C, smbar.F, smbar.F);
         evaluate_green_lagrange_strain(C, E);
@@ -331,18 +351,18 @@ namespace fc_oracle
           for (int v = 0; v < 6; ++v) gp_stress[6 * gp + v] = S[v];
       }
 
-      const double fac_force = form == FORM_FBAR ? integration_factor / fbar_factor : integration_factor;
+      const double fac_force = fbar_like ? integration_factor / fbar_factor : integration_factor;
       // f += fac * B^T S                                               calc_lib.hpp:851-860
       if (fe) multiply_tn_scaled<ND, 6, 1>(fac_force, fe, B, S, 1.0);
 
       if (Ke)
       {
-        const double fac_mat = form == FORM_FBAR ? integration_factor * fbar_factor : integration_factor;
-        const double fac_geo = form == FORM_FBAR ? integration_factor / fbar_factor : integration_factor;
+        const double fac_mat = fbar_like ? integration_factor * fbar_factor : integration_factor;
+        const double fac_geo = fbar_like ? integration_factor / fbar_factor : integration_factor;
         multiply_nn<6, 6, ND>(cb, cmat, B);                              // cb = C B
         multiply_tn_scaled<ND, 6, ND>(fac_mat, Ke, B, cb, 1.0);          // K += fac B^T cb
         if (form != FORM_LINEAR) add_geometric_stiffness_matrix<NEN>(jm.N_XYZ, S, fac_geo, Ke);
-        if (form == FORM_FBAR)
+        if (fbar_like)
         {
           // add_fbar_stiffness_matrix                                   lib_fbar.hpp:120-154
           double rcg[6], ccg[6];
@@ -409,11 +429,12 @@ namespace fc_oracle
   // init: what MulfFormulation::evaluate stores at its first call (calc_mulf.hpp:59-63) and the identity of MulfHistoryData.
   // update: MulfFormulation::update_prestress (calc_mulf.hpp:150-171) with the displacements u of the finished step.
   template <int NEN, int NGP>
-  inline void mulf_history_t(int ct, const double* X, const double* u /* nullptr = init */, double* hist)
+  inline void mulf_history_t(int ct, const double* X, const double* u /* nullptr = init */, double* hist, bool centroid)
   {
-    double gxi[NGP][3], gw[NGP];
+    double gxi[NGP + 1][3], gw[NGP];
     gauss_rule(ct, gxi, gw);
-    for (int gp = 0; gp < NGP; ++gp)
+    centroid_param(ct, gxi[NGP]);  // MULF with F-bar: one more record for the element centroid (calc_mulf_fbar.hpp:118-143, 255-270)
+    for (int gp = 0; gp < NGP + (centroid ? 1 : 0); ++gp)
     {
       double dN[3 * NEN];
       shape_function_deriv1(ct, gxi[gp], dN);
@@ -443,17 +464,19 @@ namespace fc_oracle
       }
     }
   }
-  inline void mulf_history(int ct, const double* X, const double* u, double* hist)
+  // number of history records of one element
+  inline int mulf_records(int ct, int form) { return form == FORM_MULF ? num_gp(ct) : (form == FORM_MULF_FBAR ? num_gp(ct) + 1 : 0); }
+  inline void mulf_history(int ct, const double* X, const double* u, double* hist, bool centroid = false)
   {
     switch (ct)
     {
-      case HEX8: return mulf_history_t<8, 8>(ct, X, u, hist);
-      case HEX27: return mulf_history_t<27, 27>(ct, X, u, hist);
-      case TET10: return mulf_history_t<10, 4>(ct, X, u, hist);
-      case HEX20: return mulf_history_t<20, 27>(ct, X, u, hist);
-      case TET4: return mulf_history_t<4, 1>(ct, X, u, hist);
-      case WEDGE6: return mulf_history_t<6, 6>(ct, X, u, hist);
-      case PYRAMID5: return mulf_history_t<5, 8>(ct, X, u, hist);
+      case HEX8: return mulf_history_t<8, 8>(ct, X, u, hist, centroid);
+      case HEX27: return mulf_history_t<27, 27>(ct, X, u, hist, centroid);
+      case TET10: return mulf_history_t<10, 4>(ct, X, u, hist, centroid);
+      case HEX20: return mulf_history_t<20, 27>(ct, X, u, hist, centroid);
+      case TET4: return mulf_history_t<4, 1>(ct, X, u, hist, centroid);
+      case WEDGE6: return mulf_history_t<6, 6>(ct, X, u, hist, centroid);
+      case PYRAMID5: return mulf_history_t<5, 8>(ct, X, u, hist, centroid);
     }
   }
 

@@ -74,6 +74,9 @@ CASES = [
     "solid_ele_tet4_Standard_mulf.dat",
     "solid_ele_wedge6_Standard_mulf.dat",
     "solid_ele_pyramid5_Standard_mulf.dat",
+    "solid_ele_hex8_Standard_mulf_fbar.dat",  # PRESTRESS_TECH mulf with TECH fbar
+    "solid_ele_hex27_Standard_mulf.dat",
+    "solid_ele_tet10_Standard_mulf.dat",
 ]
 
 

@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
-FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF, FORM_EAS_MILD, FORM_EAS_FULL = 0, 1, 2, 3, 4, 5
+FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF, FORM_EAS_MILD, FORM_EAS_FULL, FORM_MULF_FBAR = 0, 1, 2, 3, 4, 5, 6
 NEAS = {FORM_EAS_MILD: 9, FORM_EAS_FULL: 21}
 OUTPUT_STRAIN = 16  # stress_type = OUTPUT_STRAIN + strain type: the Gauss-point output is that strain (stress-like Voigt)
 STRAIN_GL, STRAIN_EA, STRAIN_LOG = 0, 1, 2
@@ -285,12 +285,12 @@ class Job:
         lib.oracle_job_update_prestress(self.h, _p(_d(u_nodes)))
 
     def mulf_history(self):
-        """(n_ele, ngp, 18) inverse Jacobian | deformation gradient of every Gauss point (empty unless FORM_MULF)"""
+        """(n_ele, ngp [+ 1], 18) inverse Jacobian | deformation gradient of every Gauss point [and the centroid: FORM_MULF_FBAR]"""
         lib.oracle_job_get_mulf_history.restype = C.c_longlong
         n = lib.oracle_job_get_mulf_history(self.h, None)
         out = np.zeros(n)
         lib.oracle_job_get_mulf_history(self.h, _p(out))
-        return out.reshape(-1, NGP[self.ct], 18)
+        return out.reshape(len(self.ele_gid), -1, 18)  # ngp records per element, MULF with F-bar: + the centroid
 
     def recover(self, du_nodes, step_length=1.0):
         """struct_calc_recover (EAS): alpha of every element += step_length * alpha_inc(Newton increment), (n_nodes, 3)"""

@@ -85,13 +85,13 @@ class Problem:
                     self.fibers = np.array(fib)
         def tech(opts):
             if "PRESTRESS_TECH mulf" in opts:
-                return 3
+                return 6 if "TECH fbar" in opts else 3
             if "KINEM linear" in opts:
                 return 2
             return {"fbar": 1, "eas_mild": 4, "eas_full": 5}.get(opts.split()[opts.split().index("TECH") + 1], 0) if "TECH" in opts.split() else 0
         techs = {tech(e["opts"]) for e in fx["elements"]}
         assert len(techs) == 1
-        self.form = techs.pop()  # FC_FORM_DISPLACEMENT / _FBAR / _LINEAR / _MULF / _EAS_MILD / _EAS_FULL
+        self.form = techs.pop()  # FC_FORM_DISPLACEMENT / _FBAR / _LINEAR / _MULF / _EAS_MILD / _EAS_FULL / _MULF_FBAR
         io = fx.get("io", {})
         self.stress_type = {"2pk": 0, "cauchy": 1}.get(io.get("STRUCT_STRESS", "cauchy").lower(), 1)
         self.strain_type = {"gl": 0, "ea": 1, "log": 2}.get(io.get("STRUCT_STRAIN", "none").lower())  # None: no strain output

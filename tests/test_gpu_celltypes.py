@@ -150,14 +150,16 @@ def test_stress_output(fc, oracle, name, form):
     s.close()
 
 
-@pytest.mark.parametrize("name,mat", [("solid_ele_hex8_Standard_eas_none_dynamic", NH), ("solid_ele_hex27_Standard_dynamic", NH),
-                                      ("solid_ele_tet10_Standard_dynamic", SVK), ("solid_ele_hex20_Standard_dynamic", NH),
-                                      ("solid_ele_tet4_Standard_dynamic", NH), ("solid_ele_wedge6_Standard_dynamic", SVK),
-                                      ("solid_ele_pyramid5_Standard_dynamic", NH)])
-def test_mulf_prestress_parity(fc, oracle, name, mat):
-    """PRESTRESS_TECH mulf on every cell type: two prestress updates with different displacements, then the assembled system, the
-    Gauss-point stresses and the history itself against an oracle job that saw the same updates; history round trip."""
-    MULF = fc.FC_FORM_MULF
+@pytest.mark.parametrize("name,mat,MULF", [("solid_ele_hex8_Standard_eas_none_dynamic", NH, 3), ("solid_ele_hex27_Standard_dynamic", NH, 3),
+                                           ("solid_ele_tet10_Standard_dynamic", SVK, 3), ("solid_ele_hex20_Standard_dynamic", NH, 3),
+                                           ("solid_ele_tet4_Standard_dynamic", NH, 3), ("solid_ele_wedge6_Standard_dynamic", SVK, 3),
+                                           ("solid_ele_pyramid5_Standard_dynamic", NH, 3),
+                                           ("solid_ele_hex8_Standard_eas_none_dynamic", NH, 6), ("solid_ele_pyramid5_Standard_dynamic", SVK, 6)])
+def test_mulf_prestress_parity(fc, oracle, name, mat, MULF):
+    """PRESTRESS_TECH mulf on every cell type (MULF = 6: with TECH fbar, hex8 and pyramid5): two prestress updates with different
+    displacements, then the assembled system, the Gauss-point stresses and the history itself against an oracle job that saw the
+    same updates; history round trip."""
+    assert (fc.FC_FORM_MULF, fc.FC_FORM_MULF_FBAR) == (3, 6)
     p, X, u = distorted(oracle, name)
     ct, conn = p.ct, p.conn
     s = fc.Solid(0)

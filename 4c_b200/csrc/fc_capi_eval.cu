@@ -136,6 +136,8 @@ namespace
     auto kern = A.dbc ? fc::k_nh_mma_gen<CT, WANT_K, true> : fc::k_nh_mma_gen<CT, WANT_K, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    if (e != cudaSuccess) return e;
     kern<<<(A.n_ele - A.ele_offset + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(Ag, ctx->d_ele_bad);
     ctx->launches++;
     return cudaGetLastError();

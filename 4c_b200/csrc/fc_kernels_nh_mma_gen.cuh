@@ -30,6 +30,9 @@ namespace fc
     static constexpr int MT = (nen + 7) / 8, KS = (ngp + 3) / 4, NP = 8 * MT, GP4 = 4 * KS;
     static constexpr int epb = CT == TET10 ? 8 : (CT == HEX27 ? 1 : 4);
     static constexpr int warps = 4, threads = 32 * warps;
+    // CTAs per SM the register allocation leaves room for.  hex27: 5 (96 registers, no spills) measured 4.01 ms at 48^3 against
+    // 4.38 ms with 4 (113 registers) and 4.58 ms with 6 (80 registers, spills)
+    static constexpr int min_blocks = CT == HEX27 ? 5 : 1;
     static constexpr int plane = KS * MT * 32;
     // hex27 reads s_ab / 2c = sum_gp w detJ grad N_a . grad N_b and detJ from a geometry cache (k_gen_geom_cache, once per
     // mesh, like the hex8 kernel): the three nhat planes, J^-1 and 3 of the 12 DMMA per tile step go away, the element needs
@@ -93,7 +96,7 @@ namespace fc
   }
 
   template <int CT, bool WANT_K, bool HAS_DBC>
-  __global__ void __launch_bounds__(NhGenCfg<CT>::threads) k_nh_mma_gen(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
+  __global__ void __launch_bounds__(NhGenCfg<CT>::threads, NhGenCfg<CT>::min_blocks) k_nh_mma_gen(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
   {
     using Cfg = NhGenCfg<CT>;
     constexpr int NEN = Cfg::nen, NGP = Cfg::ngp, MT = Cfg::MT, KS = Cfg::KS, NP = Cfg::NP, EPB = Cfg::epb;
@@ -106,7 +109,11 @@ namespace fc
     // at 48^3: inside the tile loop the byte loads' latency was exposed 4 times per element); tet10: per row tile inside the loop
     // (phase-0 loading measured slower there, 9.9 -> 10.4 ms)
     constexpr bool SLOTS_PHASE0 = CT == HEX27;
-    __shared__ unsigned char s_slots[SLOTS_PHASE0 ? EPB * NEN : Cfg::warps * 8][NP];
+    __shared__ unsigned char s_slots[SLOTS_PHASE0 ? 1 : Cfg::warps * 8][NP];
+    // phase-0 variant: the element's nen x nen bytes as aligned 32-bit words (the byte-wise loop cost 9 000 cycles per element)
+    constexpr int SLW = (NEN * NEN + 6) / 4 + 1;
+    __shared__ unsigned int s_slw[SLOTS_PHASE0 ? EPB : 1][SLOTS_PHASE0 ? SLW : 1];
+    __shared__ int s_slshift[EPB];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ebase = A.ele_offset + blockIdx.x * EPB;  // launch slots [ele_offset, n_ele)
     const double c2 = A.mat.young / (2.0 * (1.0 + A.mat.nue));  // 2c
@@ -151,53 +158,55 @@ namespace fc
     }
     if (SLOTS_PHASE0 && WANT_K && A.K)
     {
-      for (int it = tid; it < EPB * NEN * NP; it += Cfg::threads)
+      for (int it = tid; it < EPB * SLW; it += Cfg::threads)
       {
-        const int el = it / (NEN * NP), aa = (it / NP) % NEN, b = it % NP;
+        const int el = it / SLW, w = it % SLW;
         const int slot_e = ebase + el;
-        unsigned char v = 0xFF;
-        if (slot_e < A.n_ele && b < NEN)
-        {
-          const int e = A.ele_perm ? __ldg(A.ele_perm + slot_e) : slot_e;
-          v = __ldg(A.slots + ((size_t)e * NEN + aa) * NEN + b);
-        }
-        s_slots[el * NEN + aa][b] = v;
+        if (slot_e >= A.n_ele) continue;
+        const int e = A.ele_perm ? __ldg(A.ele_perm + slot_e) : slot_e;
+        const unsigned char* base = A.slots + (size_t)e * NEN * NEN;
+        const int shift = (int)(reinterpret_cast<uintptr_t>(base) & 3u);
+        if (w == 0) s_slshift[el] = shift;
+        // words of the element's byte range; the last one may reach up to 3 bytes past it, inside the same aligned word
+        if (4 * w < shift + NEN * NEN) s_slw[el][w] = __ldg(reinterpret_cast<const unsigned int*>(base - shift) + w);
       }
     }
     __syncthreads();
 
-    // ---- phase 1a: Jacobians ---------------------------------------------------------------------------------
-    for (int it = tid; it < EPB * NGP * 2; it += Cfg::threads)
+    // ---- phase 1a: rows of the Jacobians (J = dN X^T unless cached, j = dN x^T), one (Gauss point, matrix, row) per thread ----
+    for (int it = tid; it < EPB * NGP * 6; it += Cfg::threads)
     {
-      const int which = it & 1, gp = (it >> 1) % NGP, el = (it >> 1) / NGP;
+      const int d = it % 3, which = (it / 3) & 1, gp = (it / 6) % NGP, el = it / (6 * NGP);
       if (ebase + el >= A.n_ele) continue;
       double* E = smem_nhg + (size_t)el * Cfg::ele_doubles;
       if (Cfg::geom && which == 0)
       {
-        const int eg = A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el;
-        E[Cfg::oInv + gp * 20 + 18] = __ldg(A.geom + (size_t)eg * Cfg::geom_doubles + 2 * 32 * MT * MT + gp);  // detJ
+        if (d == 0)
+        {
+          const int eg = A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el;
+          E[Cfg::oInv + gp * 20 + 18] = __ldg(A.geom + (size_t)eg * Cfg::geom_doubles + 2 * 32 * MT * MT + gp);  // detJ
+        }
         continue;
       }
       const double* crd = E + (which ? Cfg::oX : Cfg::oXm);
-      const double* dN = A.dNtab + (size_t)gp * NEN * 3;
-      double M[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+      const double* dN = A.dNtab + (size_t)gp * NEN * 3 + d;
+      double m0 = 0.0, m1 = 0.0, m2 = 0.0;
+#pragma unroll
       for (int a = 0; a < NEN; ++a)
       {
-        const double d0 = __ldg(dN + 3 * a), d1 = __ldg(dN + 3 * a + 1), d2 = __ldg(dN + 3 * a + 2);
-        const double x0 = crd[3 * a], x1 = crd[3 * a + 1], x2 = crd[3 * a + 2];
-        M[0] += d0 * x0; M[1] += d0 * x1; M[2] += d0 * x2;
-        M[3] += d1 * x0; M[4] += d1 * x1; M[5] += d1 * x2;
-        M[6] += d2 * x0; M[7] += d2 * x1; M[8] += d2 * x2;
+        const double dn = __ldg(dN + 3 * a);
+        m0 += dn * crd[3 * a];
+        m1 += dn * crd[3 * a + 1];
+        m2 += dn * crd[3 * a + 2];
       }
-      double Mi[9];
-      const double det = inv3(M, Mi);
-      double* R = E + Cfg::oInv + gp * 20 + (which ? 0 : 9);
-      for (int i = 0; i < 9; ++i) R[i] = Mi[i];
-      E[Cfg::oInv + gp * 20 + 18 + which] = det;  // [18] = detJ, [19] = det j
+      double* R = E + Cfg::oInv + gp * 20 + (which ? 0 : 9) + 3 * d;
+      R[0] = m0;
+      R[1] = m1;
+      R[2] = m2;
     }
     __syncthreads();
 
-    // ---- phase 1b: Gauss-point scalars ------------------------------------------------------------------------
+    // ---- phase 1b: inverses, Gauss-point scalars ---------------------------------------------------------------
     for (int it = tid; it < EPB * Cfg::GP4; it += Cfg::threads)
     {
       const int gp = it % Cfg::GP4, el = it / Cfg::GP4;
@@ -208,7 +217,17 @@ namespace fc
         for (int i = 0; i < 20; ++i) R[i] = 0.0;
         continue;
       }
-      const double detJ = R[18], detj = R[19];
+      double M[9], Mi[9];
+      for (int i = 0; i < 9; ++i) M[i] = R[i];
+      const double detj = inv3(M, Mi);
+      for (int i = 0; i < 9; ++i) R[i] = Mi[i];
+      double detJ = R[18];
+      if (!Cfg::geom)
+      {
+        for (int i = 0; i < 9; ++i) M[i] = R[9 + i];
+        detJ = inv3(M, Mi);
+        for (int i = 0; i < 9; ++i) R[9 + i] = Mi[i];
+      }
       const double detF = detj / detJ;
       const double I3 = detF * detF;
       const double lambda = detJ * __ldg(A.gpw + gp) * c2;
@@ -226,6 +245,7 @@ namespace fc
 
     // ---- phase 1c: component planes in fragment order --------------------------------------------------------
     const int a8 = lane >> 2, q = lane & 3;
+#pragma unroll
     for (int blk = warp; blk < EPB * KS * MT; blk += Cfg::warps)
     {
       const int mt = blk % MT, ks = (blk / MT) % KS, el = blk / (MT * KS);
@@ -375,7 +395,9 @@ namespace fc
               const int rr = 4 * half + r, aa = 8 * mt + rr;
               const bool ok = aa < NEN && bcol < NEN && lane < 24;
               const long long rb = ok ? s_rowbase[el][aa] : -1;
-              const int slot = ok ? (int)s_slots[SLOTS_PHASE0 ? el * NEN + aa : warp * 8 + rr][bcol] : 0;
+              const int slot = !ok ? 0
+                               : (SLOTS_PHASE0 ? (int)(reinterpret_cast<const unsigned char*>(s_slw[el]) + s_slshift[el])[aa * NEN + bcol]
+                                               : (int)s_slots[warp * 8 + rr][bcol]);
               rl[r] = ok ? s_rowlen[el][aa] : 0;
               ptr[r] = rb >= 0 ? A.K + rb + 3 * slot + (ln - 3 * b) : nullptr;
 #pragma unroll

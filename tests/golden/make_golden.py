@@ -77,6 +77,13 @@ CASES = [
     "solid_ele_hex8_Standard_mulf_fbar.dat",  # PRESTRESS_TECH mulf with TECH fbar
     "solid_ele_hex27_Standard_mulf.dat",
     "solid_ele_tet10_Standard_mulf.dat",
+    # more inputs of the same families
+    "solid_ele_hex27_Standard_linear.dat",
+    "solid_ele_hex27_Standard_volume_neumann.dat",
+    "solid_ele_tet10_Standard_volume_neumann.dat",
+    "solid_ele_tet4_Standard_stressout_2pk_strainout_gl.dat",
+    "solid_ele_tet4_Standard_stressout_cauchy_strainout_ea.dat",
+    "solid_ele_tet4_Standard_stressout_cauchy_strainout_log.dat",
 ]
 
 

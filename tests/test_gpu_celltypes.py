@@ -289,3 +289,55 @@ def test_eas_parity(fc, oracle, form, mat):
     assert ei.value.code == fc.FC_ERR_UNSUPPORTED
     s2.close()
     s.close()
+
+
+@pytest.mark.parametrize("form", [3, 6, 4, 5])
+def test_history_formulations_on_several_ranks(fc, oracle, form):
+    """MULF, MULF + F-bar, eas_mild, eas_full on a 3-rank split of a hex8 block: every rank evaluates and updates its column
+    elements, ghosts included; assembled rows against the oracle's before and after a history update, and the history of an
+    element held by two ranks is the same on both, bit for bit."""
+    from test_gpu_parity import setup_rank, rel_per_row
+    n, nranks = (6, 4, 3), 3
+    job = oracle.Job.cuboid(fc.FC_HEX8, n, nranks=nranks)
+    job.set_problem(form, NH, 10.0, 0.3)
+    u1 = oracle.smooth_displacement(job.X, 1.0 / max(n), amp=0.01)
+    rng = np.random.default_rng(2)
+    u2 = 1.3 * u1 + 0.002 * (rng.random(u1.shape) - 0.5)
+    ranks = [setup_rank(fc, job, r, fc.FC_HEX8, form, NH, 10.0, 0.3) for r in range(nranks)]
+    tol = 1e-12 if form in (3, 6) else 1e-10
+
+    def compare(u):
+        job.set_u_nodal(u)
+        assert job.evaluate(oracle.ACTION_NLNSTIFF)[0] == 0
+        for r, (s, o, col) in enumerate(ranks):
+            K, f = np.zeros(o["nnz"]), np.zeros(o["n_row_dof"])
+            assert s.evaluate(fc.FC_ACTION_NLNSTIFF, np.ascontiguousarray(u[col].reshape(-1)), f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+            K_ref, f_ref = job.get_K(r, o["nnz"]), job.get_f(r, o["n_row_dof"])
+            assert rel_per_row(K, K_ref, o["rowptr"]) <= tol, (r, rel_per_row(K, K_ref, o["rowptr"]))
+            assert np.max(np.abs(f - f_ref)) <= tol * max(np.max(np.abs(f_ref)), np.max(np.abs(K_ref)) / max(n))
+
+    compare(u1)
+    for s, o, col in ranks:
+        if form in (3, 6):
+            s.update_prestress(np.ascontiguousarray(u1[col].reshape(-1)))
+        else:
+            s.recover(np.ascontiguousarray((u2 - u1)[col].reshape(-1)))
+    if form in (3, 6):
+        job.update_prestress(u1)
+    else:
+        job.recover(u2 - u1)
+    compare(u2)
+    # copies of an element on different ranks
+    seen = {}
+    shared = 0
+    for s, o, col in ranks:
+        h = s.mulf_history() if form in (3, 6) else s.eas_history()
+        for k, g in enumerate(o["col_eles"]):
+            if int(g) in seen:
+                assert np.array_equal(seen[int(g)], h[k])
+                shared += 1
+            else:
+                seen[int(g)] = h[k].copy()
+    assert shared > 0
+    for s, o, col in ranks:
+        s.close()

@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
 
-FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
+FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5, FC_HEX18 = 0, 1, 2, 3, 4, 5, 6, 7
 FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR, FC_FORM_MULF, FC_FORM_EAS_MILD, FC_FORM_EAS_FULL, FC_FORM_MULF_FBAR = 0, 1, 2, 3, 4, 5, 6
 FC_STRAIN_GL, FC_STRAIN_EA, FC_STRAIN_LOG = 0, 1, 2
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
@@ -21,15 +21,15 @@ FC_ACTION_NLNSTIFF, FC_ACTION_INTERNALFORCE = 0, 1
 FC_EVAL_ZERO_FIRST, FC_EVAL_FORCE_GENERIC, FC_EVAL_CLOSED_FORM_FMA, FC_EVAL_OWNER_COMPUTED, FC_EVAL_DMMA_TILES = 1, 2, 4, 8, 16
 FC_EVAL_INTERIOR, FC_EVAL_BOUNDARY = 32, 64
 FC_STRESS_2PK, FC_STRESS_CAUCHY = 0, 1
-FC_FACE_QUAD4, FC_FACE_QUAD9, FC_FACE_TRI6, FC_FACE_QUAD8, FC_FACE_TRI3 = 0, 1, 2, 3, 4
-FACE_NEN = {FC_FACE_QUAD4: 4, FC_FACE_QUAD9: 9, FC_FACE_TRI6: 6, FC_FACE_QUAD8: 8, FC_FACE_TRI3: 3}
-FACE_NGP = {FC_FACE_QUAD4: 4, FC_FACE_QUAD9: 9, FC_FACE_TRI6: 6, FC_FACE_QUAD8: 9, FC_FACE_TRI3: 3}
+FC_FACE_QUAD4, FC_FACE_QUAD9, FC_FACE_TRI6, FC_FACE_QUAD8, FC_FACE_TRI3, FC_FACE_QUAD6 = 0, 1, 2, 3, 4, 5
+FACE_NEN = {FC_FACE_QUAD4: 4, FC_FACE_QUAD9: 9, FC_FACE_TRI6: 6, FC_FACE_QUAD8: 8, FC_FACE_TRI3: 3, FC_FACE_QUAD6: 6}
+FACE_NGP = {FC_FACE_QUAD4: 4, FC_FACE_QUAD9: 9, FC_FACE_TRI6: 6, FC_FACE_QUAD8: 9, FC_FACE_TRI3: 3, FC_FACE_QUAD6: 6}
 FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
 FC_ERR_SOLVER, FC_ERR_SOLVER_NOT_CONVERGED = -7, -8
 FC_SOLVER_CG, FC_SOLVER_BICGSTAB, FC_SOLVER_CG_MG = 0, 1, 2
-NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10, FC_HEX20: 20, FC_TET4: 4, FC_WEDGE6: 6, FC_PYRAMID5: 5}
-NGP = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4, FC_HEX20: 27, FC_TET4: 1, FC_WEDGE6: 6, FC_PYRAMID5: 8}
+NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10, FC_HEX20: 20, FC_TET4: 4, FC_WEDGE6: 6, FC_PYRAMID5: 5, FC_HEX18: 18}
+NGP = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4, FC_HEX20: 27, FC_TET4: 1, FC_WEDGE6: 6, FC_PYRAMID5: 8, FC_HEX18: 18}
 
 EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",

@@ -225,6 +225,7 @@ extern "C"
       case FC_HEX20: bad = project_nodal_fibers<fc::HEX20>(ctx, node_fiber1, f); break;
       case FC_TET4: bad = project_nodal_fibers<fc::TET4>(ctx, node_fiber1, f); break;
       case FC_WEDGE6: bad = project_nodal_fibers<fc::WEDGE6>(ctx, node_fiber1, f); break;
+      case FC_HEX18: bad = project_nodal_fibers<fc::HEX18>(ctx, node_fiber1, f); break;
       default: bad = project_nodal_fibers<fc::PYRAMID5>(ctx, node_fiber1, f); break;
     }
     if (bad) return fail(ctx, FC_ERR_INVALID, "nodal fibres interpolate to a zero vector at a Gauss point");
@@ -239,7 +240,7 @@ extern "C"
   {
     if (!ctx || !X || !node_owner || !conn || !ele_gid || n_col_nodes <= 0 || n_col_ele < 0) return FC_ERR_INVALID;
     (void)node_gid;
-    if (celltype < FC_HEX8 || celltype > FC_PYRAMID5) return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
+    if (celltype < FC_HEX8 || celltype > FC_HEX18) return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
     if (formulation != FC_FORM_DISPLACEMENT && formulation != FC_FORM_LINEAR && formulation != FC_FORM_MULF &&
         !(formulation == FC_FORM_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)) &&
         !(formulation == FC_FORM_MULF_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)) &&
@@ -294,6 +295,7 @@ extern "C"
       case FC_HEX20: fill_tables<fc::HEX20>(dN, w); break;
       case FC_TET4: fill_tables<fc::TET4>(dN, w); break;
       case FC_WEDGE6: fill_tables<fc::WEDGE6>(dN, w); break;
+      case FC_HEX18: fill_tables<fc::HEX18>(dN, w); break;
       default: fill_tables<fc::PYRAMID5>(dN, w); break;
     }
     FC_CUDA(dev_upload(ctx->d_dNtab, dN.data(), dN.size(), ctx->stream));
@@ -347,6 +349,7 @@ extern "C"
         case FC_HEX20: FC_CHECK_NODE_JACOBIANS(fc::HEX20); break;
         case FC_TET4: FC_CHECK_NODE_JACOBIANS(fc::TET4); break;
         case FC_WEDGE6: FC_CHECK_NODE_JACOBIANS(fc::WEDGE6); break;
+        case FC_HEX18: FC_CHECK_NODE_JACOBIANS(fc::HEX18); break;
         default: FC_CHECK_NODE_JACOBIANS(fc::PYRAMID5); break;
       }
 #undef FC_CHECK_NODE_JACOBIANS

@@ -188,6 +188,7 @@ namespace
         case FC_HEX20: return launch_generic<fc::HEX20, fc::FORM_LINEAR, WANT_K>(ctx, A);
         case FC_TET4: return launch_generic<fc::TET4, fc::FORM_LINEAR, WANT_K>(ctx, A);
         case FC_WEDGE6: return launch_generic<fc::WEDGE6, fc::FORM_LINEAR, WANT_K>(ctx, A);
+        case FC_HEX18: return launch_generic<fc::HEX18, fc::FORM_LINEAR, WANT_K>(ctx, A);
         default: return launch_generic<fc::PYRAMID5, fc::FORM_LINEAR, WANT_K>(ctx, A);
       }
     if (ctx->formulation == FC_FORM_EAS_MILD) return launch_hex8_eas<9, WANT_K>(ctx, A);
@@ -204,6 +205,7 @@ namespace
         case FC_HEX20: return launch_generic<fc::HEX20, fc::FORM_MULF, WANT_K>(ctx, A);
         case FC_TET4: return launch_generic<fc::TET4, fc::FORM_MULF, WANT_K>(ctx, A);
         case FC_WEDGE6: return launch_generic<fc::WEDGE6, fc::FORM_MULF, WANT_K>(ctx, A);
+        case FC_HEX18: return launch_generic<fc::HEX18, fc::FORM_MULF, WANT_K>(ctx, A);
         default: return launch_generic<fc::PYRAMID5, fc::FORM_MULF, WANT_K>(ctx, A);
       }
     const bool fbar = ctx->formulation == FC_FORM_FBAR;
@@ -218,6 +220,7 @@ namespace
     if (ctx->celltype == FC_HEX20) return launch_generic<fc::HEX20, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_TET4) return launch_generic<fc::TET4, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_WEDGE6) return launch_generic<fc::WEDGE6, fc::FORM_DISP, WANT_K>(ctx, A);
+    if (ctx->celltype == FC_HEX18) return launch_generic<fc::HEX18, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_PYRAMID5)
       return fbar ? launch_generic<fc::PYRAMID5, fc::FORM_FBAR, WANT_K>(ctx, A) : launch_generic<fc::PYRAMID5, fc::FORM_DISP, WANT_K>(ctx, A);
     const bool nh_gen = ctx->mat.kind == fc::MAT_NEOHOOKE && !fbar && !(flags & FC_EVAL_FORCE_GENERIC);
@@ -250,6 +253,7 @@ namespace
       case FC_HEX20: FC_MULF_HISTORY(fc::HEX20); break;
       case FC_TET4: FC_MULF_HISTORY(fc::TET4); break;
       case FC_WEDGE6: FC_MULF_HISTORY(fc::WEDGE6); break;
+      case FC_HEX18: FC_MULF_HISTORY(fc::HEX18); break;
       default: FC_MULF_HISTORY(fc::PYRAMID5); break;
     }
 #undef FC_MULF_HISTORY

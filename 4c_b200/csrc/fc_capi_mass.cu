@@ -65,6 +65,7 @@ extern "C" int fc_solid_evaluate_mass(fc_ctx* ctx, double density, int flags, do
     case FC_TET4: rc = mass_impl<fc::TET4>(ctx, density, d_M); break;
     case FC_WEDGE6: rc = mass_impl<fc::WEDGE6>(ctx, density, d_M); break;
     case FC_PYRAMID5: rc = mass_impl<fc::PYRAMID5>(ctx, density, d_M); break;
+    case FC_HEX18: rc = mass_impl<fc::HEX18>(ctx, density, d_M); break;
   }
   if (rc != FC_OK) return rc;
   if (!dev)

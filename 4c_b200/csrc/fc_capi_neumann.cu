@@ -36,7 +36,7 @@ namespace
   {
     if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede the Neumann evaluation");
     if (n_items < 0 || (n_items > 0 && !items) || !out) return fail(ctx, FC_ERR_INVALID, "item list and output are required");
-    if (surface && (face_type < FC_FACE_QUAD4 || face_type > FC_FACE_TRI3))
+    if (surface && (face_type < FC_FACE_QUAD4 || face_type > FC_FACE_QUAD6))
       return fail(ctx, FC_ERR_UNSUPPORTED, "surface cell type");
     fc::NeumannVal V{};
     if (!coords)
@@ -79,6 +79,7 @@ namespace
           case FC_FACE_QUAD9: FC_NEUMANN_SURFACE(fc::QUAD9); break;
           case FC_FACE_TRI6: FC_NEUMANN_SURFACE(fc::TRI6); break;
           case FC_FACE_QUAD8: FC_NEUMANN_SURFACE(fc::QUAD8); break;
+          case FC_FACE_QUAD6: FC_NEUMANN_SURFACE(fc::QUAD6); break;
           default: FC_NEUMANN_SURFACE(fc::TRI3); break;
         }
 #undef FC_NEUMANN_SURFACE
@@ -93,6 +94,7 @@ namespace
         if (ctx->celltype == FC_HEX20) fc::k_neumann_volume<fc::HEX20><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
         if (ctx->celltype == FC_TET4) fc::k_neumann_volume<fc::TET4><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
         if (ctx->celltype == FC_WEDGE6) fc::k_neumann_volume<fc::WEDGE6><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
+        if (ctx->celltype == FC_HEX18) fc::k_neumann_volume<fc::HEX18><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
         if (ctx->celltype == FC_PYRAMID5) fc::k_neumann_volume<fc::PYRAMID5><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
       }
       ctx->launches++;

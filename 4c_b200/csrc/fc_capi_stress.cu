@@ -79,6 +79,35 @@ namespace
       }
       return true;
     }
+    if (CT == fc::HEX18)
+    {
+      // 18 Gauss points of a hex cell -> base cell hex8 (:36-44); more points than base nodes: least squares
+      // P = (M^T M)^-1 M^T with M[gp][c] = N^hex8_c(xi_gp) (evaluate_projection_gauss_points_to_base_distype, :150-208), then the
+      // hex8 functions at the 18 nodes
+      std::vector<double> M((size_t)NGP * 8), A(64, 0.0), P((size_t)8 * NGP, 0.0);
+      for (int g = 0; g < NGP; ++g)
+      {
+        double xi[3], w;
+        fc::gauss_point<CT>(g, xi, &w);
+        fc::shape_function<fc::HEX8>(xi, &M[(size_t)g * 8]);
+      }
+      for (int c = 0; c < 8; ++c)
+        for (int d = 0; d < 8; ++d)
+          for (int g = 0; g < NGP; ++g) A[(size_t)c * 8 + d] += M[(size_t)g * 8 + c] * M[(size_t)g * 8 + d];
+      if (!invert_dense(A, 8)) return false;
+      for (int c = 0; c < 8; ++c)
+        for (int g = 0; g < NGP; ++g)
+          for (int d = 0; d < 8; ++d) P[(size_t)c * NGP + g] += A[(size_t)c * 8 + d] * M[(size_t)g * 8 + d];
+      for (int a = 0; a < NEN; ++a)
+      {
+        double xi[3], N8[8];
+        fc::node_param_coords(CT, a, xi);
+        fc::shape_function<fc::HEX8>(xi, N8);
+        for (int g = 0; g < NGP; ++g)
+          for (int c = 0; c < 8; ++c) E[(size_t)a * NGP + g] += N8[c] * P[(size_t)c * NGP + g];
+      }
+      return true;
+    }
     constexpr int BASE = CT == fc::HEX20 ? fc::HEX27 : CT;  // tet10 -> tet4 is written out below
     constexpr int NB = CT == fc::TET10 ? 4 : fc::Cell<BASE>::nen;
     static_assert(NB == NGP || CT == fc::TET4 || CT == fc::PYRAMID5, "square base system");
@@ -229,6 +258,7 @@ static int gp_output_run(fc_ctx* ctx, const double* u_col, int stress_type, doub
     case FC_HEX20: FC_STRESS(fc::HEX20); break;
     case FC_TET4: FC_STRESS(fc::TET4); break;
     case FC_WEDGE6: FC_STRESS(fc::WEDGE6); break;
+    case FC_HEX18: FC_STRESS(fc::HEX18); break;
     case FC_PYRAMID5:
       if (mulf_fbar)
         rc = stress_impl<fc::PYRAMID5, fc::FORM_MULF_FBAR>(ctx, A, stress_type, d_gp, d_nodal);

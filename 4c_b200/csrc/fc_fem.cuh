@@ -31,7 +31,8 @@ namespace fc
     HEX20 = 3,
     TET4 = 4,
     WEDGE6 = 5,
-    PYRAMID5 = 6
+    PYRAMID5 = 6,
+    HEX18 = 7  // quad9 in (r, s) x line2 in t: nodes 0-8 at t = -1 (corners, edge mids, centre), 9-17 at t = +1
   };
 
   template <int CT>
@@ -73,6 +74,12 @@ namespace fc
     static constexpr int nen = 5, ngp = 8;
   };
 
+  template <>
+  struct Cell<HEX18>
+  {
+    static constexpr int nen = 18, ngp = 18;  // hex_18point = quad_9point x line_2point
+  };
+
   FC_HD int cell_nen(int ct)
   {
     switch (ct)
@@ -83,6 +90,7 @@ namespace fc
       case HEX20: return Cell<HEX20>::nen;
       case TET4: return Cell<TET4>::nen;
       case WEDGE6: return Cell<WEDGE6>::nen;
+      case HEX18: return Cell<HEX18>::nen;
       default: return Cell<PYRAMID5>::nen;
     }
   }
@@ -96,6 +104,7 @@ namespace fc
       case HEX20: return Cell<HEX20>::ngp;
       case TET4: return Cell<TET4>::ngp;
       case WEDGE6: return Cell<WEDGE6>::ngp;
+      case HEX18: return Cell<HEX18>::ngp;
       default: return Cell<PYRAMID5>::ngp;
     }
   }
@@ -119,8 +128,19 @@ namespace fc
     return v % 3 - 1;
   }
 
+  // position of node / Gauss point k of the quad9 pattern (corners 0-3, edge mids 4-7, centre 8) in direction d, in {-1,0,1}
+  FC_HD int quad9_pos(int k, int d) { return k < 4 ? hex_node_pos(k, d) : (k < 8 ? hex_node_pos(k + 4, d) : 0); }
+
   FC_HD void node_param_coords(int ct, int a, double* xi)
   {
+    if (ct == HEX18)
+    {
+      // eleNodeNumbering_hex18_nodes_reference, 4C_fem_general_utils_local_connectivity_matrices.hpp:175-180
+      xi[0] = (double)quad9_pos(a % 9, 0);
+      xi[1] = (double)quad9_pos(a % 9, 1);
+      xi[2] = a < 9 ? -1.0 : 1.0;
+      return;
+    }
     if (ct == WEDGE6)
     {
       const double t[6][3] = {{0, 0, -1}, {1, 0, -1}, {0, 1, -1}, {0, 0, 1}, {1, 0, 1}, {0, 1, 1}};
@@ -162,6 +182,22 @@ namespace fc
         dN[3 * a + 0] = (ir ? q : -q) * sf[is] * tf[it];
         dN[3 * a + 1] = (is ? q : -q) * tf[it] * rf[ir];
         dN[3 * a + 2] = (it ? q : -q) * rf[ir] * sf[is];
+      }
+    }
+    else if constexpr (CT == HEX18)
+    {
+      // 4C_fem_general_utils_fem_shapefunctions.hpp:508-560: quadratic Lagrange in r and s, linear in t
+      const double R[3] = {0.5 * r * (r - 1.0), 1.0 - r * r, 0.5 * r * (r + 1.0)};
+      const double S[3] = {0.5 * s * (s - 1.0), 1.0 - s * s, 0.5 * s * (s + 1.0)};
+      const double dR[3] = {r - 0.5, -2.0 * r, r + 0.5};
+      const double dS[3] = {s - 0.5, -2.0 * s, s + 0.5};
+      for (int a = 0; a < 18; ++a)
+      {
+        const int ir = quad9_pos(a % 9, 0) + 1, is = quad9_pos(a % 9, 1) + 1;
+        const double L = a < 9 ? 0.5 * (1.0 - t) : 0.5 * (1.0 + t);
+        dN[3 * a + 0] = dR[ir] * S[is] * L;
+        dN[3 * a + 1] = R[ir] * dS[is] * L;
+        dN[3 * a + 2] = R[ir] * S[is] * (a < 9 ? -0.5 : 0.5);
       }
     }
     else if constexpr (CT == HEX27)
@@ -252,6 +288,13 @@ namespace fc
       const double rf[2] = {1.0 - r, 1.0 + r}, sf[2] = {1.0 - s, 1.0 + s}, tf[2] = {1.0 - t, 1.0 + t};
       for (int a = 0; a < 8; ++a)
         N[a] = 0.125 * rf[hex_node_pos(a, 0) > 0] * sf[hex_node_pos(a, 1) > 0] * tf[hex_node_pos(a, 2) > 0];
+    }
+    else if constexpr (CT == HEX18)
+    {
+      // 4C_fem_general_utils_fem_shapefunctions.hpp:104-137
+      const double R[3] = {0.5 * r * (r - 1.0), 1.0 - r * r, 0.5 * r * (r + 1.0)};
+      const double S[3] = {0.5 * s * (s - 1.0), 1.0 - s * s, 0.5 * s * (s + 1.0)};
+      for (int a = 0; a < 18; ++a) N[a] = R[quad9_pos(a % 9, 0) + 1] * S[quad9_pos(a % 9, 1) + 1] * (a < 9 ? 0.5 * (1.0 - t) : 0.5 * (1.0 + t));
     }
     else if constexpr (CT == HEX27)
     {
@@ -347,6 +390,17 @@ namespace fc
       xi[1] = (g & 2) ? m : -m;
       xi[2] = (g & 1) ? 0.12251482265544 : 0.54415184401122;
       *w = (g & 1) ? 0.23254745125351 : 0.10078588207983;
+    }
+    else if constexpr (CT == HEX18)
+    {
+      // hex_18point (4C_fem_general_utils_integration.cpp:112-130): quad_9point in the plane (:6185-6233, the order of the quad9
+      // nodes) times line_2point through the thickness (:6946-6953), with the reference's truncated constants
+      const double p = 0.7745966692415, w1 = 0.5555555555556, w2 = 0.8888888888889;
+      const int k = g % 9, sr = quad9_pos(k, 0), ss = quad9_pos(k, 1);
+      xi[0] = sr == 0 ? 0.0 : (sr > 0 ? p : -p);
+      xi[1] = ss == 0 ? 0.0 : (ss > 0 ? p : -p);
+      xi[2] = g < 9 ? -0.5773502691896 : 0.5773502691896;
+      *w = (sr == 0 ? w2 : w1) * (ss == 0 ? w2 : w1);
     }
     else if constexpr (CT == HEX27 || CT == HEX20)
     {

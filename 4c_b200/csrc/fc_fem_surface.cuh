@@ -21,17 +21,18 @@ namespace fc
     QUAD9 = 1,
     TRI6 = 2,
     QUAD8 = 3,
-    TRI3 = 4
+    TRI3 = 4,
+    QUAD6 = 5  // side faces of hex18: nodes 0 (r = -1), 1 (r = +1), 2 (r = 0) at s = -1, then 3, 4, 5 at s = +1
   };
 
   template <int FT>
   struct FaceCell
   {
-    static constexpr int nen = FT == QUAD4 ? 4 : (FT == QUAD9 ? 9 : (FT == TRI6 ? 6 : (FT == QUAD8 ? 8 : 3)));
-    static constexpr int ngp = FT == QUAD4 ? 4 : (FT == QUAD9 || FT == QUAD8 ? 9 : (FT == TRI6 ? 6 : 3));
+    static constexpr int nen = FT == QUAD4 ? 4 : (FT == QUAD9 ? 9 : (FT == TRI6 || FT == QUAD6 ? 6 : (FT == QUAD8 ? 8 : 3)));
+    static constexpr int ngp = FT == QUAD4 ? 4 : (FT == QUAD9 || FT == QUAD8 ? 9 : (FT == TRI6 || FT == QUAD6 ? 6 : 3));
   };
-  FC_HD int face_nen(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 ? 9 : (ft == TRI6 ? 6 : (ft == QUAD8 ? 8 : 3))); }
-  FC_HD int face_ngp(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 || ft == QUAD8 ? 9 : (ft == TRI6 ? 6 : 3)); }
+  FC_HD int face_nen(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 ? 9 : (ft == TRI6 || ft == QUAD6 ? 6 : (ft == QUAD8 ? 8 : 3))); }
+  FC_HD int face_ngp(int ft) { return ft == QUAD4 ? 4 : (ft == QUAD9 || ft == QUAD8 ? 9 : (ft == TRI6 || ft == QUAD6 ? 6 : 3)); }
   constexpr int face_max_nen = 9, face_max_ngp = 9;
 
   // in-face position of quad node a in direction d as an integer in {-1, 0, 1}: corners 0-3 counter-clockwise from
@@ -67,6 +68,15 @@ namespace fc
       rs[1] = b * p;
       // the reference writes weight(xi_1) * weight(xi_2)
       *w = (a == 0 ? w2 : w1) * (b == 0 ? w2 : w1);
+    }
+    else if (ft == QUAD6)
+    {
+      // quad_6point (4C_fem_general_utils_integration.cpp:6235-6261): three points in r, two in s, in the order of the nodes
+      const double p = 0.7745966692415, q = 0.5773502691896;
+      const int k = g % 3;
+      rs[0] = k == 0 ? -p : (k == 1 ? p : 0.0);
+      rs[1] = g < 3 ? -q : q;
+      *w = k == 2 ? 0.8888888888889 : 0.5555555555556;
     }
     else
     {
@@ -142,6 +152,18 @@ namespace fc
         N[a] = Lr[ir] * Ls[is];
         dNr[a] = dLr[ir] * Ls[is];
         dNs[a] = Lr[ir] * dLs[is];
+      }
+    }
+    else if (ft == QUAD6)
+    {
+      // 4C_fem_general_utils_fem_shapefunctions.hpp:2016-2026, 2168-2184
+      const double Lr[3] = {0.5 * r * (r - 1.0), 0.5 * r * (r + 1.0), 1.0 - r * r}, dLr[3] = {r - 0.5, r + 0.5, -2.0 * r};
+      for (int a = 0; a < 6; ++a)
+      {
+        const double Ls = a < 3 ? 0.5 * (1.0 - s) : 0.5 * (1.0 + s);
+        N[a] = Lr[a % 3] * Ls;
+        dNr[a] = dLr[a % 3] * Ls;
+        dNs[a] = Lr[a % 3] * (a < 3 ? -0.5 : 0.5);
       }
     }
     else

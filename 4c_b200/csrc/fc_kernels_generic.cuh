@@ -71,7 +71,7 @@ namespace fc
     static constexpr int nen = Cell<CT>::nen;
     static constexpr int ngp = Cell<CT>::ngp;
     // elements per CTA and column nodes per register chunk, indexed by cell type (hex8, hex27, tet10, hex20, tet4, wedge6, pyramid5)
-    static constexpr int epb_tab[7] = {8, 4, 12, 4, 32, 16, 16}, bch_tab[7] = {4, 9, 5, 5, 4, 3, 5};
+    static constexpr int epb_tab[8] = {8, 4, 12, 4, 32, 16, 16, 4}, bch_tab[8] = {4, 9, 5, 5, 4, 3, 5, 6};
     static constexpr int epb = epb_tab[CT], bch = bch_tab[CT];
     static constexpr int threads = epb * nen;
     // per-Gauss-point record: F(9) N_XYZ(3 nen) cmat(36) S(6) fac_mat fac_geo fac_force pad [H(3 nen) v(6)]

@@ -57,7 +57,8 @@ extern "C"
     FC_HEX20 = 3,   /* 27-point rule */
     FC_TET4 = 4,    /* stiffness tet_1point, mass tet_4point */
     FC_WEDGE6 = 5,  /* wedge_6point */
-    FC_PYRAMID5 = 6 /* pyramid_8point; F-bar allowed (4C_solid_3D_ele_factory.hpp:49-50) */
+    FC_PYRAMID5 = 6, /* pyramid_8point; F-bar allowed (4C_solid_3D_ele_factory.hpp:49-50) */
+    FC_HEX18 = 7     /* quad9 x line2 (18 nodes, hex_18point); faces quad9 (bottom, top) and quad6 (sides) */
   };
   /* element technology (TECH none | fbar): src/solid_3D_ele/4C_solid_3D_ele.cpp:71-138 */
   enum
@@ -248,7 +249,8 @@ extern "C"
     FC_FACE_QUAD9 = 1,
     FC_FACE_TRI6 = 2,
     FC_FACE_QUAD8 = 3, /* hex20 faces, quad_9point */
-    FC_FACE_TRI3 = 4   /* tet4 / wedge6 / pyramid5 faces, tri_3point */
+    FC_FACE_TRI3 = 4,  /* tet4 / wedge6 / pyramid5 faces, tri_3point */
+    FC_FACE_QUAD6 = 5  /* side faces of hex18 (quadratic in r, linear in s), quad_6point */
   };
   int fc_solid_neumann_surface(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, const int* onoff, const double* val,
       const double* gp_factor, double* f_ext);

@@ -477,6 +477,7 @@ namespace fc_oracle
       case TET4: return mulf_history_t<4, 1>(ct, X, u, hist, centroid);
       case WEDGE6: return mulf_history_t<6, 6>(ct, X, u, hist, centroid);
       case PYRAMID5: return mulf_history_t<5, 8>(ct, X, u, hist, centroid);
+      case HEX18: return mulf_history_t<18, 18>(ct, X, u, hist, centroid);
     }
   }
 
@@ -500,6 +501,8 @@ namespace fc_oracle
         return element_evaluate_t<6, 6>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
       case PYRAMID5:
         return element_evaluate_t<5, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
+      case HEX18:
+        return element_evaluate_t<18, 18>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
     }
     return -1;
   }

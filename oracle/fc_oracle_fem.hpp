@@ -27,17 +27,18 @@ namespace fc_oracle
     HEX20 = 3,
     TET4 = 4,
     WEDGE6 = 5,
-    PYRAMID5 = 6
+    PYRAMID5 = 6,
+    HEX18 = 7
   };
 
   inline int num_nodes(int ct)
   {
-    static const int n[7] = {8, 27, 10, 20, 4, 6, 5};
+    static const int n[8] = {8, 27, 10, 20, 4, 6, 5, 18};
     return n[ct];
   }
   inline int num_gp(int ct)
   {
-    static const int n[7] = {8, 27, 4, 27, 1, 6, 8};
+    static const int n[8] = {8, 27, 4, 27, 1, 6, 8, 18};
     return n[ct];
   }
 
@@ -54,7 +55,15 @@ namespace fc_oracle
         {.5, .5, 0}, {0, .5, 0}, {0, 0, .5}, {.5, 0, .5}, {0, .5, .5}};
     static const double wedge[6][3] = {{0, 0, -1}, {1, 0, -1}, {0, 1, -1}, {0, 0, 1}, {1, 0, 1}, {0, 1, 1}};
     static const double pyramid[5][3] = {{-1, -1, 0}, {1, -1, 0}, {1, 1, 0}, {-1, 1, 0}, {0, 0, 1}};
-    if (ct == TET10 || ct == TET4)
+    // hex18 (4C_fem_general_utils_local_connectivity_matrices.hpp:175-180): the quad9 pattern at t = -1, then at t = +1
+    static const signed char q9[9][2] = {{-1, -1}, {1, -1}, {1, 1}, {-1, 1}, {0, -1}, {1, 0}, {0, 1}, {-1, 0}, {0, 0}};
+    if (ct == HEX18)
+    {
+      xi[0] = q9[a % 9][0];
+      xi[1] = q9[a % 9][1];
+      xi[2] = a < 9 ? -1.0 : 1.0;
+    }
+    else if (ct == TET10 || ct == TET4)
       for (int d = 0; d < 3; ++d) xi[d] = tet[a][d];
     else if (ct == WEDGE6)
       for (int d = 0; d < 3; ++d) xi[d] = wedge[a][d];
@@ -62,6 +71,24 @@ namespace fc_oracle
       for (int d = 0; d < 3; ++d) xi[d] = pyramid[a][d];
     else
       for (int d = 0; d < 3; ++d) xi[d] = hex[a][d];
+  }
+
+  // hex18: the nine in-plane functions of (r, s) and their derivatives in the factored form of the reference
+  // (4C_fem_general_utils_fem_shapefunctions.hpp:104-137, 508-560); node order: corners, edge mids, centre
+  inline void hex18_inplane(double r, double s, double* q, double* qr, double* qs)
+  {
+    const double rp = 1.0 + r, rm = 1.0 - r, sp = 1.0 + s, sm = 1.0 - s;
+    const double r2 = 1.0 - r * r, s2 = 1.0 - s * s, rh = 0.5 * r, sh = 0.5 * s, rs = rh * sh;
+    const double rhp = r + 0.5, rhm = r - 0.5, shp = s + 0.5, shm = s - 0.5;
+    q[0] = rs * rm * sm;   qr[0] = -rhm * sh * sm;     qs[0] = -shm * rh * rm;
+    q[1] = -rs * rp * sm;  qr[1] = -rhp * sh * sm;     qs[1] = shm * rh * rp;
+    q[2] = rs * rp * sp;   qr[2] = rhp * sh * sp;      qs[2] = shp * rh * rp;
+    q[3] = -rs * rm * sp;  qr[3] = rhm * sh * sp;      qs[3] = -shp * rh * rm;
+    q[4] = -sh * sm * r2;  qr[4] = 2.0 * r * sh * sm;  qs[4] = shm * r2;
+    q[5] = rh * rp * s2;   qr[5] = rhp * s2;           qs[5] = -2.0 * s * rh * rp;
+    q[6] = sh * sp * r2;   qr[6] = -2.0 * r * sh * sp; qs[6] = shp * r2;
+    q[7] = -rh * rm * s2;  qr[7] = rhm * s2;           qs[7] = 2.0 * s * rh * rm;
+    q[8] = r2 * s2;        qr[8] = -2.0 * r * s2;      qs[8] = -2.0 * s * r2;
   }
 
   // N_a(xi)
@@ -81,6 +108,17 @@ namespace fc_oracle
       N[5] = Q18 * rp * sm * tp;
       N[6] = Q18 * rp * sp * tp;
       N[7] = Q18 * rm * sp * tp;
+    }
+    else if (ct == HEX18)
+    {
+      // 4C_fem_general_utils_fem_shapefunctions.hpp:104-137: nine in-plane functions times (1 -+ t) / 2
+      double q[9], qr[9], qs[9];
+      hex18_inplane(r, s, q, qr, qs);
+      for (int k = 0; k < 9; ++k)
+      {
+        N[k] = q[k] * (1.0 - t) * 0.5;
+        N[9 + k] = q[k] * (1.0 + t) * 0.5;
+      }
     }
     else if (ct == HEX27)
     {
@@ -185,6 +223,21 @@ namespace fc_oracle
         dN[0 + 3 * a] = (x[0] > 0 ? Q18 : -Q18) * Sf[is] * Tf[it];
         dN[1 + 3 * a] = (x[1] > 0 ? Q18 : -Q18) * Tf[it] * Rf[ir];
         dN[2 + 3 * a] = (x[2] > 0 ? Q18 : -Q18) * Rf[ir] * Sf[is];
+      }
+    }
+    else if (ct == HEX18)
+    {
+      // 4C_fem_general_utils_fem_shapefunctions.hpp:508-570
+      double q[9], qr[9], qs[9];
+      hex18_inplane(r, s, q, qr, qs);
+      for (int k = 0; k < 9; ++k)
+      {
+        dN[0 + 3 * k] = qr[k] * (1.0 - t) * 0.5;
+        dN[1 + 3 * k] = qs[k] * (1.0 - t) * 0.5;
+        dN[2 + 3 * k] = -0.5 * q[k];
+        dN[0 + 3 * (9 + k)] = qr[k] * (1.0 + t) * 0.5;
+        dN[1 + 3 * (9 + k)] = qs[k] * (1.0 + t) * 0.5;
+        dN[2 + 3 * (9 + k)] = 0.5 * q[k];
       }
     }
     else if (ct == HEX27)
@@ -315,6 +368,20 @@ namespace fc_oracle
       {
         for (int d = 0; d < 3; ++d) xi[g][d] = p[g][d];
         w[g] = (g & 1) ? wb : wa;
+      }
+    }
+    else if (ct == HEX18)
+    {
+      // hex_18point (integration.cpp:112-130) = quad_9point (:6185-6233) x line_2point (:6946-6953), truncated constants
+      const double xi3 = 0.7745966692415, w1 = 0.5555555555556, w2 = 0.8888888888889, xi2 = 0.5773502691896;
+      for (int g = 0; g < 18; ++g)
+      {
+        double x[3];
+        node_param_coords(HEX18, g, x);  // in-plane points ordered like the nodes
+        xi[g][0] = x[0] == 0 ? 0.0 : (x[0] > 0 ? xi3 : -xi3);
+        xi[g][1] = x[1] == 0 ? 0.0 : (x[1] > 0 ? xi3 : -xi3);
+        xi[g][2] = g < 9 ? -xi2 : xi2;
+        w[g] = 1.0 * ((x[0] == 0 ? w2 : w1) * (x[1] == 0 ? w2 : w1));
       }
     }
     else if (ct == HEX27 || ct == HEX20)

@@ -25,16 +25,17 @@ namespace fc_oracle
     QUAD9 = 1,
     TRI6 = 2,
     QUAD8 = 3,
-    TRI3 = 4
+    TRI3 = 4,
+    QUAD6 = 5
   };
   inline int face_num_nodes(int ft)
   {
-    static const int n[5] = {4, 9, 6, 8, 3};
+    static const int n[6] = {4, 9, 6, 8, 3, 6};
     return n[ft];
   }
   inline int face_num_gp(int ft)
   {
-    static const int n[5] = {4, 9, 6, 9, 3};
+    static const int n[6] = {4, 9, 6, 9, 3, 6};
     return n[ft];
   }
 
@@ -85,6 +86,28 @@ namespace fc_oracle
       deriv_s[6] = 0.5 * rm * rp;
       deriv_r[7] = -0.5 * sm * sp;
       deriv_s[7] = -rm * s;
+    }
+    else if (ft == QUAD6)
+    {
+      // side face of hex18 (4C_fem_general_utils_fem_shapefunctions.hpp:2016-2026, 2168-2184): quadratic in r, linear in s
+      funct[0] = 0.25 * r * (r - 1.) * (1. - s);
+      funct[1] = 0.25 * r * (r + 1.) * (1. - s);
+      funct[2] = -0.5 * (r - 1.) * (r + 1.) * (1. - s);
+      funct[3] = 0.25 * r * (r - 1.) * (1. + s);
+      funct[4] = 0.25 * r * (r + 1.) * (1. + s);
+      funct[5] = -0.5 * (r - 1.) * (r + 1.) * (1. + s);
+      deriv_r[0] = 0.25 * (2. * r - 1.) * (1. - s);
+      deriv_r[1] = 0.25 * (2. * r + 1.) * (1. - s);
+      deriv_r[2] = -r * (1. - s);
+      deriv_r[3] = 0.25 * (2. * r - 1.) * (1. + s);
+      deriv_r[4] = 0.25 * (2. * r + 1.) * (1. + s);
+      deriv_r[5] = -r * (1. + s);
+      deriv_s[0] = -0.25 * r * (r - 1.);
+      deriv_s[1] = -0.25 * r * (r + 1.);
+      deriv_s[2] = +0.5 * (r - 1.) * (r + 1.);
+      deriv_s[3] = 0.25 * r * (r - 1.);
+      deriv_s[4] = 0.25 * r * (r + 1.);
+      deriv_s[5] = -0.5 * (r - 1.) * (r + 1.);
     }
     else if (ft == TRI3)
     {
@@ -177,6 +200,18 @@ namespace fc_oracle
         qxg[i][0] = p[i][0];
         qxg[i][1] = p[i][1];
         qwgt[i] = 1.0 / 6.0;
+      }
+    }
+    else if (ft == QUAD6)
+    {
+      // quad_6point, 4C_fem_general_utils_integration.cpp:6235-6261
+      const double g = 0.7745966692415, h = 0.5773502691896, a = 0.5555555555556, b = 0.8888888888889;
+      const double p[6][2] = {{-g, -h}, {g, -h}, {0.0, -h}, {-g, h}, {g, h}, {0.0, h}};
+      for (int i = 0; i < 6; ++i)
+      {
+        qxg[i][0] = p[i][0];
+        qxg[i][1] = p[i][1];
+        qwgt[i] = (i % 3 == 2) ? b : a;
       }
     }
     else if (ft == QUAD9 || ft == QUAD8)

@@ -84,6 +84,10 @@ CASES = [
     "solid_ele_tet4_Standard_stressout_2pk_strainout_gl.dat",
     "solid_ele_tet4_Standard_stressout_cauchy_strainout_ea.dat",
     "solid_ele_tet4_Standard_stressout_cauchy_strainout_log.dat",
+    # hex18 (quad9 x line2, hex_18point; quad6 side faces)
+    "solid_ele_hex18_Standard_dynamic.dat",
+    "solid_ele_hex18_Standard_element_fibers.dat",
+    "solid_ele_hex18_Standard_volume_neumann.dat",
 ]
 
 

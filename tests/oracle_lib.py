@@ -12,15 +12,15 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
-HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5 = 0, 1, 2, 3, 4, 5, 6
+HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5, HEX18 = 0, 1, 2, 3, 4, 5, 6, 7
 FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF, FORM_EAS_MILD, FORM_EAS_FULL, FORM_MULF_FBAR = 0, 1, 2, 3, 4, 5, 6
 NEAS = {FORM_EAS_MILD: 9, FORM_EAS_FULL: 21}
 OUTPUT_STRAIN = 16  # stress_type = OUTPUT_STRAIN + strain type: the Gauss-point output is that strain (stress-like Voigt)
 STRAIN_GL, STRAIN_EA, STRAIN_LOG = 0, 1, 2
 MAT_SVK, MAT_NEOHOOKE = 0, 1
 ACTION_NLNSTIFF, ACTION_INTERNALFORCE = 0, 1
-NEN = {HEX8: 8, HEX27: 27, TET10: 10, HEX20: 20, TET4: 4, WEDGE6: 6, PYRAMID5: 5}
-NGP = {HEX8: 8, HEX27: 27, TET10: 4, HEX20: 27, TET4: 1, WEDGE6: 6, PYRAMID5: 8}
+NEN = {HEX8: 8, HEX27: 27, TET10: 10, HEX20: 20, TET4: 4, WEDGE6: 6, PYRAMID5: 5, HEX18: 18}
+NGP = {HEX8: 8, HEX27: 27, TET10: 4, HEX20: 27, TET4: 1, WEDGE6: 6, PYRAMID5: 8, HEX18: 18}
 
 _dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 _ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
@@ -162,9 +162,9 @@ def element_recover_eas(neas, hist, du, step_length=1.0):
     lib.oracle_element_recover_eas(C.c_int(neas), _p(hist), _p(_d(du)), C.c_double(step_length))
 
 
-QUAD4, QUAD9, TRI6, QUAD8, TRI3 = 0, 1, 2, 3, 4
-FACE_NEN = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 8, TRI3: 3}
-FACE_NGP = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 9, TRI3: 3}
+QUAD4, QUAD9, TRI6, QUAD8, TRI3, QUAD6 = 0, 1, 2, 3, 4, 5
+FACE_NEN = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 8, TRI3: 3, QUAD6: 6}
+FACE_NGP = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 9, TRI3: 3, QUAD6: 6}
 
 
 def surface_neumann(ft, x, onoff, val, functfac=None, want_coords=False):

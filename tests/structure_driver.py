@@ -19,7 +19,7 @@ import os
 import numpy as np
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CT = {"HEX8": 0, "HEX27": 1, "TET10": 2, "HEX20": 3, "TET4": 4, "WEDGE6": 5, "PYRAMID5": 6}
+CT = {"HEX8": 0, "HEX27": 1, "TET10": 2, "HEX20": 3, "TET4": 4, "WEDGE6": 5, "PYRAMID5": 6, "HEX18": 7}
 # faces of the SURVEY 8f F4 cell types as (face type, local nodes in the node order of the surface cell); face types
 # 0 quad4, 3 quad8, 4 tri3.  Node numbering of the faces: 4C_fem_general_utils_local_connectivity_matrices.hpp:51-86
 FACE_TABLES = {
@@ -28,6 +28,9 @@ FACE_TABLES = {
     4: [(4, f) for f in ([0, 1, 3], [1, 2, 3], [0, 3, 2], [0, 2, 1])],
     5: [(4, [2, 1, 0]), (4, [3, 4, 5]), (0, [0, 1, 4, 3]), (0, [1, 2, 5, 4]), (0, [2, 0, 3, 5])],
     6: [(0, [0, 3, 2, 1]), (4, [0, 1, 4]), (4, [1, 2, 4]), (4, [2, 3, 4]), (4, [0, 4, 3])],
+    # hex18: two quad9 faces, four quad6 side faces (4C_fem_general_utils_local_connectivity_matrices.hpp:38-43)
+    7: [(1, [0, 3, 2, 1, 7, 6, 5, 4, 8]), (1, [9, 10, 11, 12, 13, 14, 15, 16, 17]), (5, [0, 1, 4, 9, 10, 13]), (5, [1, 2, 5, 10, 11, 14]),
+        (5, [2, 3, 6, 11, 12, 15]), (5, [3, 0, 7, 12, 9, 16])],
 }
 
 
@@ -437,6 +440,11 @@ def extrapolation_matrix(ct, gauss_xi, shape, xi_nodes):
     if ct == 3:  # hex20 with 27 Gauss points: base cell hex27, the 20 nodes are its first 20 (:29-44, :211-262)
         M = np.array([shape(1, x) for x in gauss_xi])
         return np.linalg.inv(M)[:20]
+    if ct == 7:
+        # hex18 with 18 Gauss points: base cell hex8 by least squares (M^T M)^-1 M^T (:150-208), then the hex8 functions at the nodes
+        M = np.array([shape(0, x) for x in gauss_xi])  # [18][8]
+        P = np.linalg.inv(M.T @ M) @ M.T
+        return np.array([shape(0, x) for x in xi_nodes]) @ P
     if ct == 4:  # tet4 with one Gauss point: base "cell" point1, every node takes the Gauss-point value
         return np.ones((4, 1))
     if ct == 6:

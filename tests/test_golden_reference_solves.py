@@ -73,6 +73,9 @@ CASES = [
     "solid_ele_tet4_Standard_stressout_2pk_strainout_gl",
     "solid_ele_tet4_Standard_stressout_cauchy_strainout_ea",
     "solid_ele_tet4_Standard_stressout_cauchy_strainout_log",
+    "solid_ele_hex18_Standard_dynamic",
+    "solid_ele_hex18_Standard_element_fibers",
+    "solid_ele_hex18_Standard_volume_neumann",
 ]
 
 
@@ -217,7 +220,7 @@ STRESS_CASES = ["solid_ele_hex8_Standard_eas_none_stressout", "solid_ele_hex27_S
                 "solid_ele_wedge6_Standard_stressout", "solid_ele_pyramid5_Standard_stressout", "solid_ele_pyramid5_Standard_fbar",
                 "solid_ele_hex8_Standard_linear", "solid_ele_hex20_Standard_linear", "solid_ele_tet4_Standard_linear",
                 "solid_ele_pyramid5_Standard_linear", "solid_ele_hex8_Standard_mulf", "solid_ele_hex20_Standard_mulf",
-                "solid_ele_tet4_Standard_mulf", "solid_ele_wedge6_Standard_mulf", "solid_ele_pyramid5_Standard_mulf"] + CASES[-16:-6] + CASES[-4:]
+                "solid_ele_tet4_Standard_mulf", "solid_ele_wedge6_Standard_mulf", "solid_ele_pyramid5_Standard_mulf"] + CASES[-19:-9] + CASES[-7:-3]
 
 
 def oracle_gp_stress(oracle, p, U, e, st):

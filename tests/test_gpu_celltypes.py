@@ -27,6 +27,10 @@ CASES = [
     ("solid_ele_tet4_Standard_dynamic", LINEAR, SVK, 0.3),
     ("solid_ele_wedge6_Standard_dynamic", LINEAR, SVK, 0.3),
     ("solid_ele_pyramid5_Standard_dynamic", LINEAR, NH, 0.25),
+    # hex18 (quad9 x line2)
+    ("solid_ele_hex18_Standard_dynamic", DISP, NH, 0.25),
+    ("solid_ele_hex18_Standard_dynamic", DISP, SVK, 0.3),
+    ("solid_ele_hex18_Standard_dynamic", LINEAR, SVK, 0.3),
 ]
 
 
@@ -76,7 +80,7 @@ def test_element_and_assembly_parity(fc, oracle, name, form, mat, nue):
 
 
 @pytest.mark.parametrize("name", ["solid_ele_hex20_Standard_dynamic", "solid_ele_tet4_Standard_dynamic", "solid_ele_wedge6_Standard_dynamic",
-                                  "solid_ele_pyramid5_Standard_dynamic"])
+                                  "solid_ele_pyramid5_Standard_dynamic", "solid_ele_hex18_Standard_dynamic"])
 def test_mass_and_neumann_parity(fc, oracle, name):
     p, X, _ = distorted(oracle, name)
     ct, conn = p.ct, p.conn
@@ -124,7 +128,7 @@ def test_mass_and_neumann_parity(fc, oracle, name):
 
 @pytest.mark.parametrize("name,form", [("solid_ele_hex20_Standard_dynamic", DISP), ("solid_ele_tet4_Standard_dynamic", DISP),
                                        ("solid_ele_wedge6_Standard_dynamic", DISP), ("solid_ele_pyramid5_Standard_dynamic", DISP),
-                                       ("solid_ele_pyramid5_Standard_dynamic", FBAR)])
+                                       ("solid_ele_pyramid5_Standard_dynamic", FBAR), ("solid_ele_hex18_Standard_dynamic", DISP)])
 def test_stress_output(fc, oracle, name, form):
     """fc_solid_evaluate_stress on the F4 cells: Gauss-point stresses against the oracle, nodal values against the driver's
     restatement of the extrapolation (base cell per Gauss-point count; pyramid5: the reference's fixed matrix)"""
@@ -153,7 +157,7 @@ def test_stress_output(fc, oracle, name, form):
 @pytest.mark.parametrize("name,mat,MULF", [("solid_ele_hex8_Standard_eas_none_dynamic", NH, 3), ("solid_ele_hex27_Standard_dynamic", NH, 3),
                                            ("solid_ele_tet10_Standard_dynamic", SVK, 3), ("solid_ele_hex20_Standard_dynamic", NH, 3),
                                            ("solid_ele_tet4_Standard_dynamic", NH, 3), ("solid_ele_wedge6_Standard_dynamic", SVK, 3),
-                                           ("solid_ele_pyramid5_Standard_dynamic", NH, 3),
+                                           ("solid_ele_pyramid5_Standard_dynamic", NH, 3), ("solid_ele_hex18_Standard_dynamic", NH, 3),
                                            ("solid_ele_hex8_Standard_eas_none_dynamic", NH, 6), ("solid_ele_pyramid5_Standard_dynamic", SVK, 6)])
 def test_mulf_prestress_parity(fc, oracle, name, mat, MULF):
     """PRESTRESS_TECH mulf on every cell type (MULF = 6: with TECH fbar, hex8 and pyramid5): two prestress updates with different

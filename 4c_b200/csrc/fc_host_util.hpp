@@ -89,6 +89,22 @@ namespace fc_host
     double xi[3];
     fc::centroid_param(CT, xi);
     fc::shape_deriv1<CT>(xi, &dN[(size_t)(NGP + NEN) * NEN * 3]);
+    // the Gauss-point part again in the two orders k_nh_mma_gen reads it in (fc_kernels_nh_mma_gen.cuh):
+    //   node-major  [nen][ngp][3]            - a thread owns a (Gauss point, direction) and walks over the nodes
+    //   fragment    [3][KS * MT][32 lanes]   - lane (a8, q) of block (ks, mt) holds node 8 mt + a8 at Gauss point 4 ks + q, 0 = padding
+    constexpr int MT = (NEN + 7) / 8, KS = (NGP + 3) / 4;
+    const size_t o1 = dN.size(), o2 = o1 + (size_t)NEN * NGP * 3;
+    dN.resize(o2 + (size_t)3 * KS * MT * 32, 0.0);
+    for (int a = 0; a < NEN; ++a)
+      for (int g = 0; g < NGP; ++g)
+        for (int d = 0; d < 3; ++d) dN[o1 + ((size_t)a * NGP + g) * 3 + d] = dN[((size_t)g * NEN + a) * 3 + d];
+    for (int d = 0; d < 3; ++d)
+      for (int blk = 0; blk < KS * MT; ++blk)
+        for (int lane = 0; lane < 32; ++lane)
+        {
+          const int g = 4 * (blk / MT) + (lane & 3), a = 8 * (blk % MT) + (lane >> 2);
+          if (g < NGP && a < NEN) dN[o2 + ((size_t)d * KS * MT + blk) * 32 + lane] = dN[((size_t)g * NEN + a) * 3 + d];
+        }
   }
 }  // namespace fc_host
 using namespace fc_host;

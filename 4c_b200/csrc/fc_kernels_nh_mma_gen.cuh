@@ -34,6 +34,9 @@ namespace fc
     // 4.38 ms with 4 (113 registers) and 4.58 ms with 6 (80 registers, spills)
     static constexpr int min_blocks = CT == HEX27 ? 5 : 1;
     static constexpr int plane = KS * MT * 32;
+    // shape-function derivatives at the Gauss points behind the [ngp + nen + 1][nen][3] table (fill_tables, fc_host_util.hpp)
+    static constexpr int oTabNodeMajor = (ngp + nen + 1) * nen * 3;   // [nen][ngp][3]
+    static constexpr int oTabFragment = oTabNodeMajor + nen * ngp * 3;  // [3][KS * MT][32]
     // hex27 reads s_ab / 2c = sum_gp w detJ grad N_a . grad N_b and detJ from a geometry cache (k_gen_geom_cache, once per
     // mesh, like the hex8 kernel): the three nhat planes, J^-1 and 3 of the 12 DMMA per tile step go away, the element needs
     // 22 KB of shared memory less.  tet10 recomputes them (measured with the cache: stiffness 9.88 -> 10.10 ms, residual-only
@@ -173,28 +176,21 @@ namespace fc
     }
     __syncthreads();
 
-    // ---- phase 1a: rows of the Jacobians (J = dN X^T unless cached, j = dN x^T), one (Gauss point, matrix, row) per thread ----
-    for (int it = tid; it < EPB * NGP * 6; it += Cfg::threads)
+    // ---- phase 1a: rows of the Jacobians (J = dN X^T unless cached, j = dN x^T), one (Gauss point, matrix, row) per thread; the
+    // node-major table makes a warp's loads of one node contiguous ---------------------------------------------------------
+    constexpr int NW = Cfg::geom ? 1 : 2;
+    for (int it = tid; it < EPB * NGP * 3 * NW; it += Cfg::threads)
     {
-      const int d = it % 3, which = (it / 3) & 1, gp = (it / 6) % NGP, el = it / (6 * NGP);
+      const int d = it % 3, which = Cfg::geom ? 1 : (it / 3) & 1, gp = (it / (3 * NW)) % NGP, el = it / (3 * NW * NGP);
       if (ebase + el >= A.n_ele) continue;
       double* E = smem_nhg + (size_t)el * Cfg::ele_doubles;
-      if (Cfg::geom && which == 0)
-      {
-        if (d == 0)
-        {
-          const int eg = A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el;
-          E[Cfg::oInv + gp * 20 + 18] = __ldg(A.geom + (size_t)eg * Cfg::geom_doubles + 2 * 32 * MT * MT + gp);  // detJ
-        }
-        continue;
-      }
       const double* crd = E + (which ? Cfg::oX : Cfg::oXm);
-      const double* dN = A.dNtab + (size_t)gp * NEN * 3 + d;
+      const double* dN = A.dNtab + Cfg::oTabNodeMajor + gp * 3 + d;
       double m0 = 0.0, m1 = 0.0, m2 = 0.0;
 #pragma unroll
       for (int a = 0; a < NEN; ++a)
       {
-        const double dn = __ldg(dN + 3 * a);
+        const double dn = __ldg(dN + a * NGP * 3);
         m0 += dn * crd[3 * a];
         m1 += dn * crd[3 * a + 1];
         m2 += dn * crd[3 * a + 2];
@@ -204,6 +200,14 @@ namespace fc
       R[1] = m1;
       R[2] = m2;
     }
+    if (Cfg::geom)  // detJ from the geometry cache, on the threads the loop above leaves idle first
+      for (int it = Cfg::threads - 1 - tid; it < EPB * NGP; it += Cfg::threads)
+      {
+        const int gp = it % NGP, el = it / NGP;
+        if (ebase + el >= A.n_ele) continue;
+        const int eg = A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el;
+        smem_nhg[(size_t)el * Cfg::ele_doubles + Cfg::oInv + gp * 20 + 18] = __ldg(A.geom + (size_t)eg * Cfg::geom_doubles + 2 * 32 * MT * MT + gp);
+      }
     __syncthreads();
 
     // ---- phase 1b: inverses, Gauss-point scalars ---------------------------------------------------------------
@@ -250,12 +254,13 @@ namespace fc
     {
       const int mt = blk % MT, ks = (blk / MT) % KS, el = blk / (MT * KS);
       double* E = smem_nhg + (size_t)el * Cfg::ele_doubles;
-      const int gp = 4 * ks + q, nodeb = 8 * mt + a8;
+      const int gp = 4 * ks + q;
       double out[6] = {0, 0, 0, 0, 0, 0};
-      if (ebase + el < A.n_ele && gp < NGP && nodeb < NEN)
+      if (ebase + el < A.n_ele)
       {
-        const double* dN = A.dNtab + ((size_t)gp * NEN + nodeb) * 3;
-        const double d0 = __ldg(dN), d1 = __ldg(dN + 1), d2 = __ldg(dN + 2);
+        // fragment-ordered table: one coalesced load per direction, zero where the tile is padding (R is zero for padded Gauss points)
+        const double* dN = A.dNtab + Cfg::oTabFragment + (ks * MT + mt) * 32 + lane;
+        const double d0 = __ldg(dN), d1 = __ldg(dN + Cfg::plane), d2 = __ldg(dN + 2 * Cfg::plane);
         const double* R = E + Cfg::oInv + gp * 20;
 #pragma unroll
         for (int i = 0; i < 3; ++i)

@@ -193,6 +193,7 @@ namespace
       }
     if (ctx->formulation == FC_FORM_EAS_MILD) return launch_hex8_eas<9, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_EAS_FULL) return launch_hex8_eas<21, WANT_K>(ctx, A);
+    if (ctx->formulation == FC_FORM_EAS_SHELL) return launch_hex8_eas<7, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_MULF_FBAR)
       return ctx->celltype == FC_HEX8 ? launch_generic<fc::HEX8, fc::FORM_MULF_FBAR, WANT_K>(ctx, A)
                                       : launch_generic<fc::PYRAMID5, fc::FORM_MULF_FBAR, WANT_K>(ctx, A);
@@ -305,7 +306,13 @@ namespace
 
 static int eas_doubles(const fc_ctx* ctx)
 {
-  return ctx->formulation == FC_FORM_EAS_MILD ? fc::EasCfg<9>::hist_doubles : (ctx->formulation == FC_FORM_EAS_FULL ? fc::EasCfg<21>::hist_doubles : 0);
+  switch (ctx->formulation)
+  {
+    case FC_FORM_EAS_MILD: return fc::EasCfg<9>::hist_doubles;
+    case FC_FORM_EAS_FULL: return fc::EasCfg<21>::hist_doubles;
+    case FC_FORM_EAS_SHELL: return fc::EasCfg<7>::hist_doubles;
+    default: return 0;
+  }
 }
 
 // fc_solid_set_mesh: allocate and initialise the element history of an FC_FORM_MULF / FC_FORM_EAS_* mesh (the stream is
@@ -609,7 +616,9 @@ extern "C"
       d_u = t_u;
     }
     const unsigned gs = (unsigned)((ctx->n_ele + 7) / 8);
-    if (ctx->formulation == FC_FORM_EAS_MILD)
+    if (ctx->formulation == FC_FORM_EAS_SHELL)
+      fc::k_hex8_eas_recover<7><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
+    else if (ctx->formulation == FC_FORM_EAS_MILD)
       fc::k_hex8_eas_recover<9><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
     else
       fc::k_hex8_eas_recover<21><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
@@ -632,7 +641,7 @@ extern "C"
   int fc_solid_eas_get_history(fc_ctx* ctx, double* history)
   {
     if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
-    if (!eas_doubles(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_EAS_MILD / FC_FORM_EAS_FULL");
+    if (!eas_doubles(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with one of the FC_FORM_EAS_* formulations");
     if (ctx->n_ele == 0) return FC_OK;
     FC_CUDA(cudaSetDevice(ctx->device));
     FC_CUDA(cudaMemcpyAsync(history, ctx->d_eas, sizeof(double) * (size_t)ctx->n_ele * eas_doubles(ctx), cudaMemcpyDefault, ctx->stream));
@@ -643,7 +652,7 @@ extern "C"
   int fc_solid_eas_set_history(fc_ctx* ctx, const double* history)
   {
     if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
-    if (!eas_doubles(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_EAS_MILD / FC_FORM_EAS_FULL");
+    if (!eas_doubles(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with one of the FC_FORM_EAS_* formulations");
     if (ctx->n_ele == 0) return FC_OK;
     FC_CUDA(cudaSetDevice(ctx->device));
     FC_CUDA(cudaMemcpyAsync(ctx->d_eas, history, sizeof(double) * (size_t)ctx->n_ele * eas_doubles(ctx), cudaMemcpyDefault, ctx->stream));

@@ -163,6 +163,8 @@ namespace
         fc::k_gp_stress_eas<9><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_EAS_FULL)
         fc::k_gp_stress_eas<21><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_EAS_SHELL)
+        fc::k_gp_stress_eas<7><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       else
         fc::k_gp_stress<CT, FORM><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       ctx->launches++;

@@ -1,4 +1,4 @@
-// hex8 with enhanced assumed strains (TECH eas_mild: 9 modes, eas_full: 21 modes), SURVEY 8f F4.
+// hex8 with enhanced assumed strains (TECH eas_mild: 9 modes, eas_full: 21 modes, shell_eas: 7 modes), SURVEY 8f F4.
 //   EASFormulation, history, condensation      src/solid_3D_ele/4C_solid_3D_ele_calc_eas.hpp:44-291
 //   M(xi), Mtilde = detJ0/detJ T0^-T M, integrate_eas, update_alpha
 //                                              src/solid_3D_ele/4C_solid_3D_ele_calc_eas_helpers.hpp:189-228, 258-420, 511-585
@@ -23,8 +23,14 @@ namespace fc
   }
   constexpr unsigned long long EAS_ROWS = eas_pack({0, 1, 2, 3, 3, 4, 4, 5, 5, 3, 3, 4, 4, 5, 5, 0, 0, 1, 1, 2, 2});
   constexpr unsigned long long EAS_MONO = eas_pack({0, 1, 2, 0, 1, 1, 2, 0, 2, 4, 5, 3, 4, 3, 5, 3, 4, 3, 5, 4, 5});
-  __host__ __device__ constexpr int eas_row(int k) { return (int)((EAS_ROWS >> (3 * k)) & 7ull); }
-  __host__ __device__ constexpr int eas_mono(int k) { return (int)((EAS_MONO >> (3 * k)) & 7ull); }
+  // eas_sosh8 (TECH shell_eas, 7 modes, t = thickness direction; 4C_solid_3D_ele_calc_eas_helpers.hpp:325-349):
+  // r, s, t on the normal strains, r and s on the in-plane shear, rt and st on the thickness strain
+  constexpr unsigned long long EAS_ROWS_SH7 = eas_pack({0, 1, 2, 3, 3, 2, 2, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0});
+  constexpr unsigned long long EAS_MONO_SH7 = eas_pack({0, 1, 2, 0, 1, 4, 5, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0});
+  template <int NEAS>
+  __host__ __device__ constexpr int eas_row(int k) { return (int)(((NEAS == 7 ? EAS_ROWS_SH7 : EAS_ROWS) >> (3 * k)) & 7ull); }
+  template <int NEAS>
+  __host__ __device__ constexpr int eas_mono(int k) { return (int)(((NEAS == 7 ? EAS_MONO_SH7 : EAS_MONO) >> (3 * k)) & 7ull); }
 
   template <int NEAS>
   struct EasCfg
@@ -96,8 +102,8 @@ namespace fc
 #pragma unroll
     for (int k = 0; k < NEAS; ++k)
     {
-      const double ma = m[eas_mono(k)] * alpha[k];
-      for (int v = 0; v < 6; ++v) ea[v] += Tm[6 * v + eas_row(k)] * ma;
+      const double ma = m[eas_mono<NEAS>(k)] * alpha[k];
+      for (int v = 0; v < 6; ++v) ea[v] += Tm[6 * v + eas_row<NEAS>(k)] * ma;
     }
     for (int v = 0; v < 3; ++v) C[v] += 2.0 * ea[v];
     for (int v = 3; v < 6; ++v) C[v] += ea[v];
@@ -206,7 +212,7 @@ namespace fc
     for (int idx = lane; idx < NEAS * NEAS; idx += 32)
     {
       const int k = idx / NEAS, l = idx % NEAS;
-      const int rk = eas_row(k), rl = eas_row(l), mk = eas_mono(k), ml = eas_mono(l);
+      const int rk = eas_row<NEAS>(k), rl = eas_row<NEAS>(l), mk = eas_mono<NEAS>(k), ml = eas_mono<NEAS>(l);
       double v = 0.0;
       for (int gp = 0; gp < 8; ++gp)
       {
@@ -218,7 +224,7 @@ namespace fc
     }
     if (lane < NEAS)
     {
-      const int rk = eas_row(lane), mk = eas_mono(lane);
+      const int rk = eas_row<NEAS>(lane), mk = eas_mono<NEAS>(lane);
       double v = 0.0;
       for (int gp = 0; gp < 8; ++gp)
       {
@@ -252,7 +258,7 @@ namespace fc
         }
         fd += fac * bs;
 #pragma unroll
-        for (int l = 0; l < NEAS; ++l) acc[l] += fm[eas_mono(l)] * P[eas_row(l)];
+        for (int l = 0; l < NEAS; ++l) acc[l] += fm[eas_mono<NEAS>(l)] * P[eas_row<NEAS>(l)];
       }
 #pragma unroll
       for (int l = 0; l < NEAS; ++l) Kda[lane * NEAS + l] = acc[l];

@@ -71,8 +71,10 @@ extern "C"
     FC_FORM_EAS_MILD = 4,     /* TECH eas_mild (hex8, 9 enhanced strain modes) and */
     FC_FORM_EAS_FULL = 5,     /* TECH eas_full (hex8, 21 modes): 4C_solid_3D_ele_calc_eas.hpp:44-291; element history in the
                                  context, see fc_solid_recover */
-    FC_FORM_MULF_FBAR = 6     /* TECH fbar with PRESTRESS_TECH mulf (hex8 and pyramid5): 4C_solid_3D_ele_calc_mulf_fbar.hpp:33-300;
+    FC_FORM_MULF_FBAR = 6,    /* TECH fbar with PRESTRESS_TECH mulf (hex8 and pyramid5): 4C_solid_3D_ele_calc_mulf_fbar.hpp:33-300;
                                  the history has one more record per element, for the centroid, behind the Gauss points' */
+    FC_FORM_EAS_SHELL = 7     /* TECH shell_eas (hex8, the 7 modes of eas_sosh8 with t as thickness direction, no ANS):
+                                 EASSolidIntegrator<hex8, eastype_sh8_7>, 4C_solid_3D_ele_factory.hpp:56-57; like FC_FORM_EAS_MILD */
   };
   /* materials: MAT_Struct_StVenantKirchhoff (src/mat/4C_mat_stvenantkirchhoff.cpp) and
    * MAT_ElastHyper with one ELAST_CoupNeoHooke summand (src/mat/4C_mat_elasthyper.cpp,
@@ -164,7 +166,7 @@ extern "C"
   int fc_solid_mulf_set_history(fc_ctx* ctx, const double* history);
   /* FC_FORM_EAS_MILD / FC_FORM_EAS_FULL (hex8 with enhanced assumed strains, condensed on the element).  The context keeps the
    * history of every column element in the order EASFormulation::pack writes it (4C_solid_3D_ele_calc_eas.hpp:266-274):
-   * alpha_inc [n] | alpha [n] | s [n] | Kaa^-1 [n][n] | Kda [24][n] | old_step_length, matrices column-major, n = 9 | 21, i.e.
+   * alpha_inc [n] | alpha [n] | s [n] | Kaa^-1 [n][n] | Kda [24][n] | old_step_length, matrices column-major, n = 9 | 21 | 7, i.e.
    * 3 n + n^2 + 24 n + 1 doubles (fc_solid_eas_history_doubles).  fc_solid_set_mesh zeroes it (old_step_length = 1).
    * Every fc_solid_evaluate / fc_solid_evaluate_elements integrates Kaa, Kda and s with the current alpha, adds the condensed
    * contributions -Kda Kaa^-1 s and -Kda Kaa^-1 Kda^T and stores Kaa^-1, Kda, s (4C_solid_3D_ele_calc.cpp:110-240), also for

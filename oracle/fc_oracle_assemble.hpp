@@ -131,7 +131,7 @@ namespace fc_oracle
       double* eas_hist = nullptr /* FORM_EAS_*: [n_ele][eas_history_doubles] in mesh element order; invKaa, Kda, s are written */)
   {
     const int nen = mesh.nen, nd = 3 * nen;
-    const int neas = form == FORM_EAS_FULL ? 21 : 9;
+    const int neas = eas_modes(form);
     std::vector<int> lm(nd), lmowner(nd), localcol(nd);
     std::vector<double> X(nd), u(nd), fe(nd), Ke((size_t)nd * nd);
     int nbad = 0;
@@ -155,7 +155,7 @@ namespace fc_oracle
       std::fill(fe.begin(), fe.end(), 0.0);
       if (action == 0) std::fill(Ke.begin(), Ke.end(), 0.0);
       const double* fib = ele_fiber ? ele_fiber + (fiber_gp_stride ? (size_t)fiber_gp_stride * num_gp(mesh.ct) : 3) * (size_t)e : nullptr;
-      const int err = (form == FORM_EAS_MILD || form == FORM_EAS_FULL)
+      const int err = form_is_eas(form)
                           ? element_evaluate_eas(neas, mp, X.data(), u.data(), eas_hist + (size_t)eas_history_doubles(neas) * e, fe.data(),
                                 action == 0 ? Ke.data() : nullptr, fib, fiber_gp_stride)
                           : element_evaluate(mesh.ct, form, mp, X.data(), u.data(), fe.data(), action == 0 ? Ke.data() : nullptr, nullptr,

@@ -202,10 +202,10 @@ extern "C"
   {
     js->job.mulf_hist.clear();
     js->job.eas_hist.clear();
-    if (js->job.form == FORM_EAS_MILD || js->job.form == FORM_EAS_FULL)
+    if (form_is_eas(js->job.form))
     {
       // EASHistoryData of a new element: everything zero, old_step_length = 1
-      const int neas = js->job.form == FORM_EAS_FULL ? 21 : 9, nh = eas_history_doubles(neas);
+      const int neas = eas_modes(js->job.form), nh = eas_history_doubles(neas);
       js->job.eas_hist.assign((size_t)nh * js->job.mesh.ele_gid.size(), 0.0);
       for (size_t e = 0; e < js->job.mesh.ele_gid.size(); ++e) eas_history_init(neas, &js->job.eas_hist[(size_t)nh * e]);
     }
@@ -256,7 +256,7 @@ extern "C"
     auto* js = (JobState*)h;
     const Mesh& m = js->job.mesh;
     if (js->job.eas_hist.empty()) return;
-    const int neas = js->job.form == FORM_EAS_FULL ? 21 : 9, nh = eas_history_doubles(neas);
+    const int neas = eas_modes(js->job.form), nh = eas_history_doubles(neas);
     double du[24];
     for (size_t e = 0; e < m.ele_gid.size(); ++e)
     {
@@ -320,7 +320,7 @@ extern "C"
     const double* fib = job.ele_fiber.empty() ? nullptr : job.ele_fiber.data() + (job.fiber_gp_stride ? (size_t)job.fiber_gp_stride * ngp : 3) * (size_t)e;
     if (!job.eas_hist.empty())
     {
-      const int neas = job.form == FORM_EAS_FULL ? 21 : 9;
+      const int neas = eas_modes(job.form);
       const bool strain = stress_type >= OUTPUT_STRAIN;
       return element_evaluate_eas(neas, job.mp, X.data(), u.data(), job.eas_hist.data() + (size_t)eas_history_doubles(neas) * e, nullptr,
           nullptr, fib, job.fiber_gp_stride, gp_stress, strain ? 1 : 0, strain ? stress_type - OUTPUT_STRAIN : stress_type);

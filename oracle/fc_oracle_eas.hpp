@@ -26,6 +26,8 @@ namespace fc_oracle
   // ---- EAS ----------------------------------------------------------------------------------------------------------
   // element history, in the order EASFormulation::pack writes it:
   //   alpha_inc [n] | alpha [n] | s [n] | invKaa [n x n] | Kda [24 x n] | old_step_length      (matrices column-major)
+  inline bool form_is_eas(int form) { return form == FORM_EAS_MILD || form == FORM_EAS_FULL || form == FORM_EAS_SHELL; }
+  inline int eas_modes(int form) { return form == FORM_EAS_FULL ? 21 : (form == FORM_EAS_SHELL ? 7 : 9); }
   inline int eas_history_doubles(int neas) { return 3 * neas + neas * neas + 24 * neas + 1; }
   struct EasView
   {
@@ -53,6 +55,14 @@ namespace fc_oracle
     for (int i = 0; i < 6 * neas; ++i) M[i] = 0.0;
     const double r = xi[0], s = xi[1], t = xi[2];
     auto set = [&](int row, int col, double v) { M[row + 6 * col] = v; };
+    if (neas == 7)
+    {
+      // eas_sosh8: solid shell with t as thickness direction (4C_solid_3D_ele_calc_eas_helpers.hpp:325-349)
+      set(0, 0, r); set(1, 1, s); set(2, 2, t);
+      set(2, 5, r * t); set(2, 6, s * t);
+      set(3, 3, r); set(3, 4, s);
+      return;
+    }
     // the nine modes both interpolations share
     set(0, 0, r); set(1, 1, s); set(2, 2, t);
     set(3, 3, r); set(3, 4, s);

@@ -88,6 +88,7 @@ CASES = [
     "solid_ele_hex18_Standard_dynamic.dat",
     "solid_ele_hex18_Standard_element_fibers.dat",
     "solid_ele_hex18_Standard_volume_neumann.dat",
+    "solid_ele_hex8_Standard_shell_eas.dat",  # TECH shell_eas = EAS with the 7 modes of eas_sosh8
 ]
 
 

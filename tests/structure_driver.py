@@ -91,7 +91,7 @@ class Problem:
                 return 6 if "TECH fbar" in opts else 3
             if "KINEM linear" in opts:
                 return 2
-            return {"fbar": 1, "eas_mild": 4, "eas_full": 5}.get(opts.split()[opts.split().index("TECH") + 1], 0) if "TECH" in opts.split() else 0
+            return {"fbar": 1, "eas_mild": 4, "eas_full": 5, "shell_eas": 7}.get(opts.split()[opts.split().index("TECH") + 1], 0) if "TECH" in opts.split() else 0
         techs = {tech(e["opts"]) for e in fx["elements"]}
         assert len(techs) == 1
         self.form = techs.pop()  # FC_FORM_DISPLACEMENT / _FBAR / _LINEAR / _MULF / _EAS_MILD / _EAS_FULL / _MULF_FBAR

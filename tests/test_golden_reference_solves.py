@@ -76,6 +76,7 @@ CASES = [
     "solid_ele_hex18_Standard_dynamic",
     "solid_ele_hex18_Standard_element_fibers",
     "solid_ele_hex18_Standard_volume_neumann",
+    "solid_ele_hex8_Standard_shell_eas",  # TECH shell_eas: the 7 EAS modes of the solid shell, without ANS
 ]
 
 
@@ -107,7 +108,7 @@ def oracle_backend(oracle, p):
         return M
     assemble.job = job  # prestress update, recover and Gauss-point output with the job's history
     assemble.hooks = dict(update_prestress=lambda dd: job.update_prestress(dd.reshape(-1, 3)),
-                          recover=(lambda inc: job.recover(inc.reshape(-1, 3))) if p.form in (4, 5) else None)
+                          recover=(lambda inc: job.recover(inc.reshape(-1, 3))) if p.form in (4, 5, 7) else None)
     return assemble, mass
 
 
@@ -154,7 +155,7 @@ def test_reference_result_description_cuda(fc, oracle, case):
     s, assemble, mass = cuda_backend(fc, p)
     p.neumann = sd.CudaNeumann(s)  # f_ext from fc_solid_neumann_surface / _volume
     # PRESTRESS_TECH mulf: fc_solid_update_prestress; EAS: fc_solid_recover after every Newton update
-    d, hist = sd.run(p, assemble, mass, update_prestress=s.update_prestress, recover=s.recover if p.form in (4, 5) else None)
+    d, hist = sd.run(p, assemble, mass, update_prestress=s.update_prestress, recover=s.recover if p.form in (4, 5, 7) else None)
     err, n = p.result_error(d)
     assert err <= 1.0, (case, err, hist)
     # the external force of the library against the oracle's, at the end time
@@ -170,8 +171,8 @@ def test_reference_result_description_cuda(fc, oracle, case):
     if p.form in (3, 6):  # the Gauss-point histories after the prestress steps
         h1, h2 = s.mulf_history(), a2.job.mulf_history()
         assert np.max(np.abs(h1 - h2)) <= 1e-10 * np.max(np.abs(h2))
-    if p.form in (4, 5):  # the enhanced strain parameters at the end of the solve
-        n = 9 if p.form == 4 else 21
+    if p.form in (4, 5, 7):  # the enhanced strain parameters at the end of the solve
+        n = oracle.NEAS[p.form]
         a1, a2_ = s.eas_history()[:, n:2 * n], a2.job.eas_history()[:, n:2 * n]
         assert np.max(np.abs(a1 - a2_)) <= 1e-9 * np.max(np.abs(a2_))
     # ... compared down to the rounding floor of the residual.  The near-incompressible Cook problem (nu = 0.4999,
@@ -220,7 +221,7 @@ STRESS_CASES = ["solid_ele_hex8_Standard_eas_none_stressout", "solid_ele_hex27_S
                 "solid_ele_wedge6_Standard_stressout", "solid_ele_pyramid5_Standard_stressout", "solid_ele_pyramid5_Standard_fbar",
                 "solid_ele_hex8_Standard_linear", "solid_ele_hex20_Standard_linear", "solid_ele_tet4_Standard_linear",
                 "solid_ele_pyramid5_Standard_linear", "solid_ele_hex8_Standard_mulf", "solid_ele_hex20_Standard_mulf",
-                "solid_ele_tet4_Standard_mulf", "solid_ele_wedge6_Standard_mulf", "solid_ele_pyramid5_Standard_mulf"] + CASES[-19:-9] + CASES[-7:-3]
+                "solid_ele_tet4_Standard_mulf", "solid_ele_wedge6_Standard_mulf", "solid_ele_pyramid5_Standard_mulf"] + CASES[-20:-10] + CASES[-8:-4] + CASES[-1:]
 
 
 def oracle_gp_stress(oracle, p, U, e, st):
@@ -267,11 +268,11 @@ def test_reference_nodal_stresses_cuda(fc, oracle, case):
     def update(dd):
         s.update_prestress(dd)
         job.update_prestress(dd.reshape(-1, 3))
-    d, _ = sd.run(p, assemble, mass, update_prestress=update, recover=s.recover if p.form in (4, 5) else None)
+    d, _ = sd.run(p, assemble, mass, update_prestress=update, recover=s.recover if p.form in (4, 5, 7) else None)
     if p.form in (3, 6):
         h1, h2 = s.mulf_history(), job.mulf_history()
         assert np.max(np.abs(h1 - h2)) <= 1e-13 * np.max(np.abs(h2))
-    if p.form in (4, 5):
+    if p.form in (4, 5, 7):
         job.set_eas_history(s.eas_history())
     gp, nodal = s.evaluate_stress(d, p.stress_type)
     err, n = sd.stress_result_error(p, nodal)

@@ -215,7 +215,7 @@ def test_mulf_prestress_parity(fc, oracle, name, mat, MULF):
     s.close()
 
 
-@pytest.mark.parametrize("form,mat", [(4, NH), (4, SVK), (5, NH), (5, SVK)])
+@pytest.mark.parametrize("form,mat", [(4, NH), (4, SVK), (5, NH), (5, SVK), (7, NH)])
 def test_eas_parity(fc, oracle, form, mat):
     """hex8 TECH eas_mild / eas_full on a distorted 3x2x2 block: three rounds of evaluate + recover with the library and with an
     oracle job; element fe / Ke, assembled system, history (alpha, s, Kaa^-1, Kda) and Gauss-point stresses / strains."""
@@ -295,7 +295,7 @@ def test_eas_parity(fc, oracle, form, mat):
     s.close()
 
 
-@pytest.mark.parametrize("form", [3, 6, 4, 5])
+@pytest.mark.parametrize("form", [3, 6, 4, 5, 7])
 def test_history_formulations_on_several_ranks(fc, oracle, form):
     """MULF, MULF + F-bar, eas_mild, eas_full on a 3-rank split of a hex8 block: every rank evaluates and updates its column
     elements, ghosts included; assembled rows against the oracle's before and after a history update, and the history of an

@@ -17,6 +17,7 @@
 #include <thread>
 
 #include "fc_oracle_eas.hpp"
+#include "fc_oracle_shell.hpp"
 #include "fc_oracle_element.hpp"
 #include "fc_oracle_mesh.hpp"
 
@@ -155,7 +156,12 @@ namespace fc_oracle
       std::fill(fe.begin(), fe.end(), 0.0);
       if (action == 0) std::fill(Ke.begin(), Ke.end(), 0.0);
       const double* fib = ele_fiber ? ele_fiber + (fiber_gp_stride ? (size_t)fiber_gp_stride * num_gp(mesh.ct) : 3) * (size_t)e : nullptr;
-      const int err = form_is_eas(form)
+      const bool shell = form == FORM_SHELL_ANS || form == FORM_SHELL_EAS_ANS;
+      const int nshell = shell_eas_modes(mesh.ct, form);
+      const int err = shell ? element_evaluate_shell(mesh.ct, nshell, mp, X.data(), u.data(),
+                                  nshell ? eas_hist + (size_t)shell_history_doubles(nshell, nd) * e : nullptr, fe.data(),
+                                  action == 0 ? Ke.data() : nullptr, fib, fiber_gp_stride)
+                      : form_is_eas(form)
                           ? element_evaluate_eas(neas, mp, X.data(), u.data(), eas_hist + (size_t)eas_history_doubles(neas) * e, fe.data(),
                                 action == 0 ? Ke.data() : nullptr, fib, fiber_gp_stride)
                           : element_evaluate(mesh.ct, form, mp, X.data(), u.data(), fe.data(), action == 0 ? Ke.data() : nullptr, nullptr,

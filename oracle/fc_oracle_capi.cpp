@@ -209,6 +209,12 @@ extern "C"
       js->job.eas_hist.assign((size_t)nh * js->job.mesh.ele_gid.size(), 0.0);
       for (size_t e = 0; e < js->job.mesh.ele_gid.size(); ++e) eas_history_init(neas, &js->job.eas_hist[(size_t)nh * e]);
     }
+    if (js->job.form == FORM_SHELL_EAS_ANS)
+    {
+      const int nd = 3 * js->job.mesh.nen, neas = shell_eas_modes(js->job.mesh.ct, js->job.form), nh = shell_history_doubles(neas, nd);
+      js->job.eas_hist.assign((size_t)nh * js->job.mesh.ele_gid.size(), 0.0);
+      for (size_t e = 0; e < js->job.mesh.ele_gid.size(); ++e) js->job.eas_hist[(size_t)nh * (e + 1) - 1] = 1.0;
+    }
     const Mesh& m = js->job.mesh;
     const int ngp = mulf_records(m.ct, js->job.form);  // records per element (MULF with F-bar: + the centroid)
     if (ngp == 0) return;
@@ -256,16 +262,21 @@ extern "C"
     auto* js = (JobState*)h;
     const Mesh& m = js->job.mesh;
     if (js->job.eas_hist.empty()) return;
-    const int neas = eas_modes(js->job.form), nh = eas_history_doubles(neas);
+    const bool shell = js->job.form == FORM_SHELL_EAS_ANS;
+    const int nd = 3 * m.nen, neas = shell ? shell_eas_modes(m.ct, js->job.form) : eas_modes(js->job.form);
+    const int nh = shell ? shell_history_doubles(neas, nd) : eas_history_doubles(neas);
     double du[24];
     for (size_t e = 0; e < m.ele_gid.size(); ++e)
     {
-      for (int a = 0; a < 8; ++a)
+      for (int a = 0; a < m.nen; ++a)
       {
-        const size_t ni = (size_t)m.node_index.at(m.ele_nodes[e * 8 + a]);
+        const size_t ni = (size_t)m.node_index.at(m.ele_nodes[e * m.nen + a]);
         for (int i = 0; i < 3; ++i) du[3 * a + i] = du_nodes[3 * ni + i];
       }
-      eas_recover(neas, &js->job.eas_hist[(size_t)nh * e], du, step_length);
+      if (shell)
+        shell_recover(neas, nd, &js->job.eas_hist[(size_t)nh * e], du, step_length);
+      else
+        eas_recover(neas, &js->job.eas_hist[(size_t)nh * e], du, step_length);
     }
   }
   // the job's EAS history [n_ele][eas_history_doubles]; get returns its length (hist may be NULL)
@@ -318,6 +329,14 @@ extern "C"
     }
     const Job& job = js->job;
     const double* fib = job.ele_fiber.empty() ? nullptr : job.ele_fiber.data() + (job.fiber_gp_stride ? (size_t)job.fiber_gp_stride * ngp : 3) * (size_t)e;
+    if (job.form == FORM_SHELL_ANS || job.form == FORM_SHELL_EAS_ANS)
+    {
+      const int neas = shell_eas_modes(m.ct, job.form);
+      const bool strain = stress_type >= OUTPUT_STRAIN;
+      return element_evaluate_shell(m.ct, neas, job.mp, X.data(), u.data(),
+          neas ? job.eas_hist.data() + (size_t)shell_history_doubles(neas, 3 * m.nen) * e : nullptr, nullptr, nullptr, fib, job.fiber_gp_stride,
+          gp_stress, strain ? 1 : 0, strain ? stress_type - OUTPUT_STRAIN : stress_type);
+    }
     if (!job.eas_hist.empty())
     {
       const int neas = eas_modes(job.form);

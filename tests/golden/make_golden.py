@@ -89,6 +89,11 @@ CASES = [
     "solid_ele_hex18_Standard_element_fibers.dat",
     "solid_ele_hex18_Standard_volume_neumann.dat",
     "solid_ele_hex8_Standard_shell_eas.dat",  # TECH shell_eas = EAS with the 7 modes of eas_sosh8
+    # solid shells: assumed natural strains, alone and with the EAS modes of the solid shell
+    "solid_ele_hex8_Standard_shell_ans.dat",
+    "solid_ele_hex8_Standard_shell_eas_ans.4C.yaml",
+    "solid_ele_wedge6_Standard_shell_ans.4C.yaml",
+    "solid_ele_wedge6_Standard_shell_eas_ans.4C.yaml",
 ]
 
 

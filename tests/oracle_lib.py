@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5, HEX18 = 0, 1, 2, 3, 4, 5, 6, 7
-FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF, FORM_EAS_MILD, FORM_EAS_FULL, FORM_MULF_FBAR, FORM_EAS_SHELL = 0, 1, 2, 3, 4, 5, 6, 7
+FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF, FORM_EAS_MILD, FORM_EAS_FULL, FORM_MULF_FBAR, FORM_EAS_SHELL, FORM_SHELL_ANS, FORM_SHELL_EAS_ANS = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9
 NEAS = {FORM_EAS_MILD: 9, FORM_EAS_FULL: 21, FORM_EAS_SHELL: 7}
 OUTPUT_STRAIN = 16  # stress_type = OUTPUT_STRAIN + strain type: the Gauss-point output is that strain (stress-like Voigt)
 STRAIN_GL, STRAIN_EA, STRAIN_LOG = 0, 1, 2

@@ -91,7 +91,7 @@ class Problem:
                 return 6 if "TECH fbar" in opts else 3
             if "KINEM linear" in opts:
                 return 2
-            return {"fbar": 1, "eas_mild": 4, "eas_full": 5, "shell_eas": 7}.get(opts.split()[opts.split().index("TECH") + 1], 0) if "TECH" in opts.split() else 0
+            return {"fbar": 1, "eas_mild": 4, "eas_full": 5, "shell_eas": 7, "shell_ans": 8, "shell_eas_ans": 9}.get(opts.split()[opts.split().index("TECH") + 1], 0) if "TECH" in opts.split() else 0
         techs = {tech(e["opts"]) for e in fx["elements"]}
         assert len(techs) == 1
         self.form = techs.pop()  # FC_FORM_DISPLACEMENT / _FBAR / _LINEAR / _MULF / _EAS_MILD / _EAS_FULL / _MULF_FBAR
@@ -104,7 +104,7 @@ class Problem:
         self.n_dof = 3 * len(ids)
         dyn = fx["dynamic"]
         self.dt, self.numstep = float(dyn["TIMESTEP"]), int(dyn["NUMSTEP"])
-        self.dynamic = dyn["DYNAMICTYPE"]
+        self.dynamic = dyn.get("DYNAMICTYPE", "GenAlpha")  # the default of STRUCTURAL DYNAMIC (4C_inpar_structure.cpp:80-92)
         # PRESTRESS mulf: steps with t <= PRESTRESSTIME end with struct_update_prestress and a reset of the displacements
         self.prestress_time = float(dyn["PRESTRESSTIME"]) if dyn.get("PRESTRESS", "none").lower() == "mulf" else None
         # Dirichlet: all values are zero in these inputs

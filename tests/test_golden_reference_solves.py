@@ -108,11 +108,16 @@ def oracle_backend(oracle, p):
         return M
     assemble.job = job  # prestress update, recover and Gauss-point output with the job's history
     assemble.hooks = dict(update_prestress=lambda dd: job.update_prestress(dd.reshape(-1, 3)),
-                          recover=(lambda inc: job.recover(inc.reshape(-1, 3))) if p.form in (4, 5, 7) else None)
+                          recover=(lambda inc: job.recover(inc.reshape(-1, 3))) if p.form in (4, 5, 7, 9) else None)
     return assemble, mass
 
 
-@pytest.mark.parametrize("case", CASES)
+# solid shells (TECH shell_ans, shell_eas_ans)
+SHELL_CASES = ["solid_ele_hex8_Standard_shell_ans", "solid_ele_hex8_Standard_shell_eas_ans", "solid_ele_wedge6_Standard_shell_ans",
+               "solid_ele_wedge6_Standard_shell_eas_ans"]
+
+
+@pytest.mark.parametrize("case", CASES + SHELL_CASES)
 def test_reference_result_description_oracle(oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     p.neumann = sd.OracleNeumann(oracle, p)
@@ -231,7 +236,7 @@ def oracle_gp_stress(oracle, p, U, e, st):
     return oracle.element_evaluate_elasthyper(p.ct, p.form, p.summands, None if p.fibers is None else p.fibers[e], p.X[en], U[en], st)[3]
 
 
-@pytest.mark.parametrize("case", STRESS_CASES)
+@pytest.mark.parametrize("case", STRESS_CASES + SHELL_CASES[:2])
 def test_reference_nodal_stresses_oracle(oracle, case):
     """stress_xx ... at nodes (STRUCT_STRESS Cauchy, TOLERANCE 1e-12): Gauss-point Cauchy stresses extrapolated to the
     nodes and averaged like the reference's post-processing (24 / 54 / 78 values)."""

@@ -10,6 +10,7 @@
 #include "fc_kernels_generic.cuh"
 #include "fc_kernels_hex8nh.cuh"
 #include "fc_kernels_hex8eas.cuh"
+#include "fc_kernels_shell.cuh"
 #include "fc_kernels_hex8nh_brick.cuh"
 #include "fc_kernels_hex8nh_mma.cuh"
 #include "fc_kernels_hex8_mma_ext.cuh"
@@ -39,6 +40,18 @@ namespace
   {
     using Cfg = fc::EasCfg<NEAS>;
     auto kern = fc::k_hex8_eas<NEAS, WANT_K>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
+    if (e != cudaSuccess) return e;
+    kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
+    ctx->launches++;
+    return cudaGetLastError();
+  }
+
+  template <int CT, int NEAS, bool WANT_K>
+  cudaError_t launch_shell(fc_ctx* ctx, const fc::EvalArgs& A)
+  {
+    using Cfg = fc::ShellCfg<CT, NEAS>;
+    auto kern = fc::k_shell<CT, NEAS, WANT_K>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
     if (e != cudaSuccess) return e;
     kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
@@ -194,6 +207,10 @@ namespace
     if (ctx->formulation == FC_FORM_EAS_MILD) return launch_hex8_eas<9, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_EAS_FULL) return launch_hex8_eas<21, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_EAS_SHELL) return launch_hex8_eas<7, WANT_K>(ctx, A);
+    if (ctx->formulation == FC_FORM_SHELL_ANS)
+      return ctx->celltype == FC_HEX8 ? launch_shell<fc::HEX8, 0, WANT_K>(ctx, A) : launch_shell<fc::WEDGE6, 0, WANT_K>(ctx, A);
+    if (ctx->formulation == FC_FORM_SHELL_EAS_ANS)
+      return ctx->celltype == FC_HEX8 ? launch_shell<fc::HEX8, 7, WANT_K>(ctx, A) : launch_shell<fc::WEDGE6, 1, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_MULF_FBAR)
       return ctx->celltype == FC_HEX8 ? launch_generic<fc::HEX8, fc::FORM_MULF_FBAR, WANT_K>(ctx, A)
                                       : launch_generic<fc::PYRAMID5, fc::FORM_MULF_FBAR, WANT_K>(ctx, A);
@@ -311,6 +328,7 @@ static int eas_doubles(const fc_ctx* ctx)
     case FC_FORM_EAS_MILD: return fc::EasCfg<9>::hist_doubles;
     case FC_FORM_EAS_FULL: return fc::EasCfg<21>::hist_doubles;
     case FC_FORM_EAS_SHELL: return fc::EasCfg<7>::hist_doubles;
+    case FC_FORM_SHELL_EAS_ANS: return ctx->celltype == FC_HEX8 ? fc::ShellCfg<fc::HEX8, 7>::hist_doubles : fc::ShellCfg<fc::WEDGE6, 1>::hist_doubles;
     default: return 0;
   }
 }
@@ -616,7 +634,11 @@ extern "C"
       d_u = t_u;
     }
     const unsigned gs = (unsigned)((ctx->n_ele + 7) / 8);
-    if (ctx->formulation == FC_FORM_EAS_SHELL)
+    if (ctx->formulation == FC_FORM_SHELL_EAS_ANS && ctx->celltype == FC_HEX8)
+      fc::k_shell_recover<fc::HEX8, 7><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
+    else if (ctx->formulation == FC_FORM_SHELL_EAS_ANS)
+      fc::k_shell_recover<fc::WEDGE6, 1><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
+    else if (ctx->formulation == FC_FORM_EAS_SHELL)
       fc::k_hex8_eas_recover<7><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
     else if (ctx->formulation == FC_FORM_EAS_MILD)
       fc::k_hex8_eas_recover<9><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);

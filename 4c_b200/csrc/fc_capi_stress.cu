@@ -165,6 +165,14 @@ namespace
         fc::k_gp_stress_eas<21><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_EAS_SHELL)
         fc::k_gp_stress_eas<7><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_SHELL_ANS)
+        fc::k_gp_stress_shell<fc::HEX8, 0><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_SHELL_EAS_ANS)
+        fc::k_gp_stress_shell<fc::HEX8, 7><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      else if (CT == fc::WEDGE6 && ctx->formulation == FC_FORM_SHELL_ANS)
+        fc::k_gp_stress_shell<fc::WEDGE6, 0><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      else if (CT == fc::WEDGE6 && ctx->formulation == FC_FORM_SHELL_EAS_ANS)
+        fc::k_gp_stress_shell<fc::WEDGE6, 1><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       else
         fc::k_gp_stress<CT, FORM><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       ctx->launches++;

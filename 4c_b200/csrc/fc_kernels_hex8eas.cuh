@@ -62,13 +62,18 @@ namespace fc
   }
 
   // inverse of the centroid Jacobian iJ0 (row-major; J0[3 d + i] = dX_i / dxi_d) and det J0; dN0 [8][3], Xs [8][3]
-  __device__ __forceinline__ double eas_centroid_jacobian(const double* __restrict__ dN0, const double* Xs, double* iJ0)
+  template <int NEN>
+  __device__ __forceinline__ double eas_centroid_jacobian_n(const double* __restrict__ dN0, const double* Xs, double* iJ0)
   {
     double J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-    for (int a = 0; a < 8; ++a)
+    for (int a = 0; a < NEN; ++a)
       for (int d = 0; d < 3; ++d)
         for (int i = 0; i < 3; ++i) J[3 * d + i] += __ldg(dN0 + 3 * a + d) * Xs[3 * a + i];
     return inv3(J, iJ0);
+  }
+  __device__ __forceinline__ double eas_centroid_jacobian(const double* __restrict__ dN0, const double* Xs, double* iJ0)
+  {
+    return eas_centroid_jacobian_n<8>(dN0, Xs, iJ0);
   }
 
   // T0^-T (row-major 6 x 6) and det J0, one thread

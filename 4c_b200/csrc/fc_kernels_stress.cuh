@@ -11,6 +11,7 @@
 #pragma once
 #include "fc_kernels_generic.cuh"
 #include "fc_kernels_hex8eas.cuh"
+#include "fc_kernels_shell.cuh"
 
 namespace fc
 {
@@ -256,5 +257,94 @@ namespace fc
     }
     const double inv = 1.0 / (double)node_elecount[node];
     for (int c = 0; c < 6; ++c) red_add(nodal + 6 * (size_t)node + c, v[c] * inv);
+  }
+
+  // solid shells (k_shell, fc_kernels_shell.cuh): ANS strains of the Gauss point, optionally enhanced with the element's alpha; the
+  // deformation gradient handed to the output is the one consistent with those strains (R U), like the reference
+  template <int CT, int NEAS>
+  __global__ void k_gp_stress_shell(const EvalArgs A, int kind, double* __restrict__ gp_stress)
+  {
+    using Cfg = ShellCfg<CT, NEAS>;
+    constexpr int NEN = Cfg::nen, NGP = Cfg::ngp, ND = Cfg::nd, NSP = Cfg::nsp;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= (long long)A.n_ele * NGP) return;
+    const int e = (int)(tid / NGP), gp = (int)(tid % NGP);
+    double Xs[ND], us[ND];
+    for (int a = 0; a < NEN; ++a)
+    {
+      const int node = __ldg(A.conn + (size_t)e * NEN + a);
+      for (int i = 0; i < 3; ++i)
+      {
+        Xs[3 * a + i] = __ldg(A.X + 3 * (size_t)node + i);
+        us[3 * a + i] = __ldg(A.u + 3 * (size_t)node + i);
+      }
+    }
+    double spj[NSP * 18];  // Jref | Jcur of every sampling point
+    for (int k = 0; k < NSP; ++k)
+    {
+      double xi[3], dN[ND];
+      shell_sampling_point<CT>(k, xi);
+      shape_deriv1<CT>(xi, dN);
+      double* Jr = spj + 18 * k;
+      for (int q = 0; q < 18; ++q) Jr[q] = 0.0;
+      for (int a = 0; a < NEN; ++a)
+        for (int d = 0; d < 3; ++d)
+          for (int i = 0; i < 3; ++i)
+          {
+            Jr[3 * d + i] += dN[3 * a + d] * Xs[3 * a + i];
+            Jr[9 + 3 * d + i] += dN[3 * a + d] * (Xs[3 * a + i] + us[3 * a + i]);
+          }
+    }
+    double xi[3], wq, J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, jc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, iJ[9], Nx[ND], F[9];
+    gauss_point<CT>(gp, xi, &wq);
+    const double* dNg = A.dNtab + (size_t)gp * ND;
+    for (int a = 0; a < NEN; ++a)
+      for (int d = 0; d < 3; ++d)
+        for (int i = 0; i < 3; ++i)
+        {
+          J[3 * d + i] += __ldg(dNg + 3 * a + d) * Xs[3 * a + i];
+          jc[3 * d + i] += __ldg(dNg + 3 * a + d) * (Xs[3 * a + i] + us[3 * a + i]);
+        }
+    const double detJ = inv3(J, iJ);
+    for (int a = 0; a < NEN; ++a)
+      for (int i = 0; i < 3; ++i) Nx[3 * a + i] = iJ[3 * i] * __ldg(dNg + 3 * a) + iJ[3 * i + 1] * __ldg(dNg + 3 * a + 1) + iJ[3 * i + 2] * __ldg(dNg + 3 * a + 2);
+    deformation_gradient<CT>(Xs, us, Nx, F);
+    double w[8], El[6], E[6];
+    shell_weights<CT>(xi[0], xi[1], w);
+    shell_local_strain<CT>(J, jc, w, spj, 18, 0, El);
+    for (int r = 0; r < 6; ++r)
+    {
+      double v = 0.0;
+      for (int q = 0; q < 6; ++q) v += voigt_transformation_entry(iJ, r, q) * El[q];
+      E[r] = v;
+    }
+    double C[6] = {2.0 * E[0] + 1.0, 2.0 * E[1] + 1.0, 2.0 * E[2] + 1.0, E[3], E[4], E[5]};
+    if (NEAS > 0)
+    {
+      double iJ0[9];
+      const double detJ0 = eas_centroid_jacobian_n<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, Xs, iJ0);
+      const double sc = detJ0 / detJ;
+      const double m[6] = {sc * xi[0], sc * xi[1], sc * xi[2], sc * xi[0] * xi[1], sc * xi[0] * xi[2], sc * xi[1] * xi[2]};
+      double ea[6] = {0, 0, 0, 0, 0, 0};
+      for (int k = 0; k < Cfg::ne; ++k)
+      {
+        const double ma = m[shell_mono<CT, NEAS>(k)] * A.eas[(size_t)e * Cfg::hist_doubles + Cfg::oAlpha + k];
+        for (int v = 0; v < 6; ++v) ea[v] += voigt_transformation_entry(iJ0, v, shell_row<CT, NEAS>(k)) * ma;
+      }
+      for (int v = 0; v < 3; ++v) C[v] += 2.0 * ea[v];
+      for (int v = 3; v < 6; ++v) C[v] += ea[v];
+    }
+    double S[6], cmat[36];
+    material_evaluate(A.mat, C, S, cmat, A.fiber ? A.fiber + (size_t)e * A.fiber_ele + gp * A.fiber_gp : nullptr);
+    const double Cm[9] = {C[0], C[3], C[5], C[3], C[1], C[4], C[5], C[4], C[2]};
+    double Cd[9], Ue[9], Ud[9], iUd[9], Rm[9], Fe[9];
+    for (int r = 0; r < 3; ++r)
+      for (int c = 0; c < 3; ++c) Cd[3 * r + c] = F[r] * F[c] + F[3 + r] * F[3 + c] + F[6 + r] * F[6 + c];
+    sym_fn3(Cm, 0, Ue);
+    sym_fn3(Cd, 0, Ud);
+    inv3(Ud, iUd);
+    mat3_mul(F, iUd, Rm);
+    mat3_mul(Rm, Ue, Fe);
+    gp_output(kind, S, C, Fe, gp_stress + ((size_t)e * NGP + gp) * 6);
   }
 }  // namespace fc

@@ -73,6 +73,11 @@ extern "C"
                                  context, see fc_solid_recover */
     FC_FORM_MULF_FBAR = 6,    /* TECH fbar with PRESTRESS_TECH mulf (hex8 and pyramid5): 4C_solid_3D_ele_calc_mulf_fbar.hpp:33-300;
                                  the history has one more record per element, for the centroid, behind the Gauss points' */
+    FC_FORM_SHELL_ANS = 8,    /* TECH shell_ans (hex8, wedge6): assumed natural strains, t = thickness direction;
+                                 4C_solid_3D_ele_calc_shell_ans.hpp:52-196 */
+    FC_FORM_SHELL_EAS_ANS = 9, /* TECH shell_eas_ans (hex8: + the 7 modes of eas_sosh8, wedge6: + the mode of eas_sosw6);
+                                 4C_solid_3D_ele_calc_shell_eas_ans.hpp:48-345; history and fc_solid_recover like FC_FORM_EAS_*,
+                                 with K_da [3 nen][n] */
     FC_FORM_EAS_SHELL = 7     /* TECH shell_eas (hex8, the 7 modes of eas_sosh8 with t as thickness direction, no ANS):
                                  EASSolidIntegrator<hex8, eastype_sh8_7>, 4C_solid_3D_ele_factory.hpp:56-57; like FC_FORM_EAS_MILD */
   };

@@ -154,13 +154,13 @@ def cuda_backend(fc, p):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("case", CASES + SHELL_CASES)
 def test_reference_result_description_cuda(fc, oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     s, assemble, mass = cuda_backend(fc, p)
     p.neumann = sd.CudaNeumann(s)  # f_ext from fc_solid_neumann_surface / _volume
     # PRESTRESS_TECH mulf: fc_solid_update_prestress; EAS: fc_solid_recover after every Newton update
-    d, hist = sd.run(p, assemble, mass, update_prestress=s.update_prestress, recover=s.recover if p.form in (4, 5, 7) else None)
+    d, hist = sd.run(p, assemble, mass, update_prestress=s.update_prestress, recover=s.recover if p.form in (4, 5, 7, 9) else None)
     err, n = p.result_error(d)
     assert err <= 1.0, (case, err, hist)
     # the external force of the library against the oracle's, at the end time
@@ -176,8 +176,8 @@ def test_reference_result_description_cuda(fc, oracle, case):
     if p.form in (3, 6):  # the Gauss-point histories after the prestress steps
         h1, h2 = s.mulf_history(), a2.job.mulf_history()
         assert np.max(np.abs(h1 - h2)) <= 1e-10 * np.max(np.abs(h2))
-    if p.form in (4, 5, 7):  # the enhanced strain parameters at the end of the solve
-        n = oracle.NEAS[p.form]
+    if p.form in (4, 5, 7, 9):  # the enhanced strain parameters at the end of the solve
+        n = oracle.NEAS.get(p.form) or (7 if p.ct == 0 else 1)
         a1, a2_ = s.eas_history()[:, n:2 * n], a2.job.eas_history()[:, n:2 * n]
         assert np.max(np.abs(a1 - a2_)) <= 1e-9 * np.max(np.abs(a2_))
     # ... compared down to the rounding floor of the residual.  The near-incompressible Cook problem (nu = 0.4999,
@@ -259,7 +259,7 @@ def test_reference_nodal_stresses_oracle(oracle, case):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", STRESS_CASES)
+@pytest.mark.parametrize("case", STRESS_CASES + SHELL_CASES[:2])
 def test_reference_nodal_stresses_cuda(fc, oracle, case):
     """the same values from fc_solid_evaluate_stress (device Gauss-point stresses + device extrapolation/averaging);
     Gauss-point stresses also compared with the oracle's, Cauchy and 2nd Piola-Kirchhoff."""
@@ -273,11 +273,11 @@ def test_reference_nodal_stresses_cuda(fc, oracle, case):
     def update(dd):
         s.update_prestress(dd)
         job.update_prestress(dd.reshape(-1, 3))
-    d, _ = sd.run(p, assemble, mass, update_prestress=update, recover=s.recover if p.form in (4, 5, 7) else None)
+    d, _ = sd.run(p, assemble, mass, update_prestress=update, recover=s.recover if p.form in (4, 5, 7, 9) else None)
     if p.form in (3, 6):
         h1, h2 = s.mulf_history(), job.mulf_history()
         assert np.max(np.abs(h1 - h2)) <= 1e-13 * np.max(np.abs(h2))
-    if p.form in (4, 5, 7):
+    if p.form in (4, 5, 7, 9):
         job.set_eas_history(s.eas_history())
     gp, nodal = s.evaluate_stress(d, p.stress_type)
     err, n = sd.stress_result_error(p, nodal)

@@ -295,7 +295,7 @@ def test_eas_parity(fc, oracle, form, mat):
     s.close()
 
 
-@pytest.mark.parametrize("form", [3, 6, 4, 5, 7])
+@pytest.mark.parametrize("form", [3, 6, 4, 5, 7, 8, 9])
 def test_history_formulations_on_several_ranks(fc, oracle, form):
     """MULF, MULF + F-bar, eas_mild, eas_full on a 3-rank split of a hex8 block: every rank evaluates and updates its column
     elements, ghosts included; assembled rows against the oracle's before and after a history update, and the history of an
@@ -325,7 +325,7 @@ def test_history_formulations_on_several_ranks(fc, oracle, form):
         if form in (3, 6):
             s.update_prestress(np.ascontiguousarray(u1[col].reshape(-1)))
         else:
-            s.recover(np.ascontiguousarray((u2 - u1)[col].reshape(-1)))
+            s.recover(np.ascontiguousarray((u2 - u1)[col].reshape(-1)))  # a no-op without condensed variables (form 8)
     if form in (3, 6):
         job.update_prestress(u1)
     else:
@@ -335,6 +335,9 @@ def test_history_formulations_on_several_ranks(fc, oracle, form):
     seen = {}
     shared = 0
     for s, o, col in ranks:
+        if form == 8:  # ANS alone keeps no history
+            shared = 1
+            break
         h = s.mulf_history() if form in (3, 6) else s.eas_history()
         for k, g in enumerate(o["col_eles"]):
             if int(g) in seen:
@@ -345,3 +348,52 @@ def test_history_formulations_on_several_ranks(fc, oracle, form):
     assert shared > 0
     for s, o, col in ranks:
         s.close()
+
+
+@pytest.mark.parametrize("form,mat", [(8, NH), (9, NH), (9, SVK)])
+def test_wedge6_solid_shell_parity(fc, oracle, form, mat):
+    """TECH shell_ans / shell_eas_ans on wedge6 (5 sampling points, one EAS mode): two rounds of evaluate (+ recover) against an oracle
+    job on a distorted copy of the reference's wedge mesh; Gauss-point stresses and strains"""
+    p, X, u = distorted(oracle, "solid_ele_wedge6_Standard_dynamic")
+    ct, conn = p.ct, p.conn
+    s = fc.Solid(0)
+    s.set_mesh(ct, form, X, p.node_gid, np.zeros(len(X), np.int32), conn, p.ele_gid)
+    s.set_material(mat, 10.0, 0.3)
+    n_row, n_col, nnz = s.build_graph()
+    rowptr, _ = s.get_graph()
+    starts = np.asarray(rowptr[:-1], np.int64)
+    job = oracle.Job.from_mesh(ct, p.node_gid, X, p.ele_gid, p.node_gid[conn])
+    job.set_problem(form, mat, 10.0, 0.3)
+    o = job.rank(0)
+    rng = np.random.default_rng(9)
+    for it in range(2):
+        uk = (0.5 + 0.4 * it) * u
+        job.set_u_nodal(uk)
+        assert job.evaluate(oracle.ACTION_NLNSTIFF)[0] == 0
+        f_ref, K_ref = job.get_f(0, n_row), job.get_K(0, o["nnz"])
+        K, f = np.zeros(nnz), np.zeros(n_row)
+        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, uk.reshape(-1), f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+        assert np.max(np.maximum.reduceat(np.abs(K - K_ref), starts) / np.maximum.reduceat(np.abs(K_ref), starts)) <= 1e-10
+        assert np.max(np.abs(f - f_ref)) <= 1e-10 * max(np.max(np.abs(f_ref)), np.max(np.abs(K_ref)))
+        fe, Ke = s.evaluate_elements(np.ascontiguousarray(uk.reshape(-1)), want_K=True)
+        assert np.all(np.isfinite(Ke)) and np.max(np.abs(Ke - Ke.transpose(0, 2, 1))) <= 1e-10 * np.max(np.abs(Ke))
+        du = 0.02 * (rng.random(X.shape) - 0.5)
+        s.recover(du.reshape(-1))
+        job.recover(du)
+        if form == 9:
+            h1, h2 = s.eas_history(), job.eas_history()
+            assert h1.shape == h2.shape == (len(conn), 3 + 1 + 18 + 1)
+            assert np.max(np.abs(h1 - h2)) <= 1e-9 * np.max(np.abs(h2))
+    if form == 9:
+        job.set_eas_history(s.eas_history())
+    for st in (fc.FC_STRESS_2PK, fc.FC_STRESS_CAUCHY):
+        gp, _ = s.evaluate_stress(u.reshape(-1), st, want_nodal=False)
+        for e in range(len(conn)):
+            ref = job.element_gp_stress(e, u, st)[1]
+            assert np.max(np.abs(gp[e] - ref)) <= 1e-12 * np.max(np.abs(ref))
+    for st in (fc.FC_STRAIN_GL, fc.FC_STRAIN_EA, fc.FC_STRAIN_LOG):
+        gp, _ = s.evaluate_strain(u.reshape(-1), st, want_nodal=False)
+        for e in range(len(conn)):
+            ref = job.element_gp_stress(e, u, oracle.OUTPUT_STRAIN + st)[1]
+            assert np.max(np.abs(gp[e] - ref)) <= 1e-12 * np.max(np.abs(ref))
+    s.close()

@@ -89,6 +89,8 @@ CASES = [
     "solid_ele_hex18_Standard_element_fibers.dat",
     "solid_ele_hex18_Standard_volume_neumann.dat",
     "solid_ele_hex8_Standard_shell_eas.dat",  # TECH shell_eas = EAS with the 7 modes of eas_sosh8
+    # Cook's membrane with 64 EAS elements, near-incompressible Neo-Hooke, 100 load steps (the multi-element EAS golden)
+    "sohex8_easmild_cooks_nl.dat",
     # solid shells: assumed natural strains, alone and with the EAS modes of the solid shell
     "solid_ele_hex8_Standard_shell_ans.dat",
     "solid_ele_hex8_Standard_shell_eas_ans.4C.yaml",

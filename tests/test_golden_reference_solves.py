@@ -112,6 +112,14 @@ def oracle_backend(oracle, p):
     return assemble, mass
 
 
+# Cook's membrane with 64 eas_mild elements, Neo-Hooke nu = 0.4999, 100 load steps: the reference stops each step at TOLRES /
+# TOLDISP 1e-7 ("Or") and lists dispy = 6.669329703176632762 with TOLERANCE 1e-12.  The replay applies the same stopping rule
+# (structure_driver.Problem.ref_stop); what is left is the rounding of a tangent with condition number ~1e8: 6e-12 on the oracle,
+# 0.3e-10 ... 1e-10 through the CUDA library, different from run to run because the FP64 reductions of the scatter arrive in any
+# order.  Accepted within 1e-9 (1.5e-10 relative).
+CASES.append("sohex8_easmild_cooks_nl")
+RESULT_TOLERANCE_FACTOR = {"sohex8_easmild_cooks_nl": 1000.0}
+
 # solid shells (TECH shell_ans, shell_eas_ans)
 SHELL_CASES = ["solid_ele_hex8_Standard_shell_ans", "solid_ele_hex8_Standard_shell_eas_ans", "solid_ele_wedge6_Standard_shell_ans",
                "solid_ele_wedge6_Standard_shell_eas_ans"]
@@ -125,7 +133,7 @@ def test_reference_result_description_oracle(oracle, case):
     d, hist = sd.run(p, assemble, mass, **assemble.hooks)
     err, n = p.result_error(d)  # in units of the reference's TOLERANCE of each value (1e-12; Cook: 1e-8)
     assert n >= 1
-    assert err <= 1.0, (case, err, hist)
+    assert err <= RESULT_TOLERANCE_FACTOR.get(case, 1.0), (case, err, hist)
 
 
 def cuda_backend(fc, p):
@@ -162,7 +170,7 @@ def test_reference_result_description_cuda(fc, oracle, case):
     # PRESTRESS_TECH mulf: fc_solid_update_prestress; EAS: fc_solid_recover after every Newton update
     d, hist = sd.run(p, assemble, mass, update_prestress=s.update_prestress, recover=s.recover if p.form in (4, 5, 7, 9) else None)
     err, n = p.result_error(d)
-    assert err <= 1.0, (case, err, hist)
+    assert err <= RESULT_TOLERANCE_FACTOR.get(case, 1.0), (case, err, hist)
     # the external force of the library against the oracle's, at the end time
     t_end = p.dt * p.numstep
     fe_cuda = p.f_ext(t_end)
@@ -179,7 +187,8 @@ def test_reference_result_description_cuda(fc, oracle, case):
     if p.form in (4, 5, 7, 9):  # the enhanced strain parameters at the end of the solve
         n = oracle.NEAS.get(p.form) or (7 if p.ct == 0 else 1)
         a1, a2_ = s.eas_history()[:, n:2 * n], a2.job.eas_history()[:, n:2 * n]
-        assert np.max(np.abs(a1 - a2_)) <= 1e-9 * np.max(np.abs(a2_))
+        # near-incompressible Cook problem: condition ~1e8, see below
+        assert np.max(np.abs(a1 - a2_)) <= (1e-9 if p.nue < 0.49 else 1e-5) * np.max(np.abs(a2_))
     # ... compared down to the rounding floor of the residual.  The near-incompressible Cook problem (nu = 0.4999,
     # condition ~1e8) amplifies last-bit differences of K (FP64 reductions arrive in any order) to ~1e-5 in the
     # Newton iterates, so the norms are compared to 1e-3 here; the strict comparison (1e-10) lives in
@@ -221,12 +230,8 @@ def test_neumann_oracle_matches_numpy_restatement(oracle, case):
     assert np.max(np.abs(f_np - f_or)) <= 1e-14 * max(np.max(np.abs(f_np)), 1e-300)
 
 
-STRESS_CASES = ["solid_ele_hex8_Standard_eas_none_stressout", "solid_ele_hex27_Standard_stressout", "solid_ele_tet10_Standard_stressout",
-                "solid_ele_hex8_Standard_fbar", "solid_ele_hex20_Standard_stressout", "solid_ele_tet4_Standard_stressout",
-                "solid_ele_wedge6_Standard_stressout", "solid_ele_pyramid5_Standard_stressout", "solid_ele_pyramid5_Standard_fbar",
-                "solid_ele_hex8_Standard_linear", "solid_ele_hex20_Standard_linear", "solid_ele_tet4_Standard_linear",
-                "solid_ele_pyramid5_Standard_linear", "solid_ele_hex8_Standard_mulf", "solid_ele_hex20_Standard_mulf",
-                "solid_ele_tet4_Standard_mulf", "solid_ele_wedge6_Standard_mulf", "solid_ele_pyramid5_Standard_mulf"] + CASES[-20:-10] + CASES[-8:-4] + CASES[-1:]
+# every input that lists nodal stresses (all but the *_dynamic, *_volume_neumann, *_fibers, Cook and ghosting cases)
+STRESS_CASES = [c for c in CASES if any(k in c for k in ("stressout", "strainout", "_linear", "_mulf", "_fbar", "shell_eas")) and not c.startswith("sohex8")]
 
 
 def oracle_gp_stress(oracle, p, U, e, st):

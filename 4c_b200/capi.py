@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
 
 FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5, FC_HEX18 = 0, 1, 2, 3, 4, 5, 6, 7
-FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR, FC_FORM_MULF, FC_FORM_EAS_MILD, FC_FORM_EAS_FULL, FC_FORM_MULF_FBAR, FC_FORM_EAS_SHELL, FC_FORM_SHELL_ANS, FC_FORM_SHELL_EAS_ANS = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9
+FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR, FC_FORM_MULF, FC_FORM_EAS_MILD, FC_FORM_EAS_FULL, FC_FORM_MULF_FBAR, FC_FORM_EAS_SHELL, FC_FORM_SHELL_ANS, FC_FORM_SHELL_EAS_ANS, FC_FORM_EAS_MILD_LINEAR, FC_FORM_EAS_FULL_LINEAR = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11
 FC_STRAIN_GL, FC_STRAIN_EA, FC_STRAIN_LOG = 0, 1, 2
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
 FC_SUMMAND_COUPNEOHOOKE, FC_SUMMAND_COUPSVK, FC_SUMMAND_COUPANISOEXPO = 0, 1, 2

@@ -245,7 +245,9 @@ extern "C"
         !(formulation == FC_FORM_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)) &&
         !(formulation == FC_FORM_MULF_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)) &&
         !((formulation == FC_FORM_SHELL_ANS || formulation == FC_FORM_SHELL_EAS_ANS) && (celltype == FC_HEX8 || celltype == FC_WEDGE6)) &&
-        !((formulation == FC_FORM_EAS_MILD || formulation == FC_FORM_EAS_FULL || formulation == FC_FORM_EAS_SHELL) && celltype == FC_HEX8))
+        !((formulation == FC_FORM_EAS_MILD || formulation == FC_FORM_EAS_FULL || formulation == FC_FORM_EAS_SHELL ||
+              formulation == FC_FORM_EAS_MILD_LINEAR || formulation == FC_FORM_EAS_FULL_LINEAR) &&
+            celltype == FC_HEX8))
       return fail(ctx, FC_ERR_UNSUPPORTED, "F-bar exists for hex8 and pyramid5, EAS for hex8, solid shells for hex8 and wedge6 only (4C_solid_3D_ele_factory.hpp:49-75)");
     FC_CUDA(cudaSetDevice(ctx->device));
     const int nen = fc::cell_nen(celltype);

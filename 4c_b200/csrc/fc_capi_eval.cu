@@ -35,11 +35,11 @@ namespace
     return cudaGetLastError();
   }
 
-  template <int NEAS, bool WANT_K>
+  template <int NEAS, bool WANT_K, bool LINEAR = false>
   cudaError_t launch_hex8_eas(fc_ctx* ctx, const fc::EvalArgs& A)
   {
     using Cfg = fc::EasCfg<NEAS>;
-    auto kern = fc::k_hex8_eas<NEAS, WANT_K>;
+    auto kern = fc::k_hex8_eas<NEAS, WANT_K, LINEAR>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::smem_bytes);
     if (e != cudaSuccess) return e;
     kern<<<(A.n_ele + Cfg::epb - 1) / Cfg::epb, Cfg::threads, Cfg::smem_bytes, ctx->stream>>>(A, ctx->d_ele_bad);
@@ -207,6 +207,8 @@ namespace
     if (ctx->formulation == FC_FORM_EAS_MILD) return launch_hex8_eas<9, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_EAS_FULL) return launch_hex8_eas<21, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_EAS_SHELL) return launch_hex8_eas<7, WANT_K>(ctx, A);
+    if (ctx->formulation == FC_FORM_EAS_MILD_LINEAR) return launch_hex8_eas<9, WANT_K, true>(ctx, A);
+    if (ctx->formulation == FC_FORM_EAS_FULL_LINEAR) return launch_hex8_eas<21, WANT_K, true>(ctx, A);
     if (ctx->formulation == FC_FORM_SHELL_ANS)
       return ctx->celltype == FC_HEX8 ? launch_shell<fc::HEX8, 0, WANT_K>(ctx, A) : launch_shell<fc::WEDGE6, 0, WANT_K>(ctx, A);
     if (ctx->formulation == FC_FORM_SHELL_EAS_ANS)
@@ -325,8 +327,10 @@ static int eas_doubles(const fc_ctx* ctx)
 {
   switch (ctx->formulation)
   {
-    case FC_FORM_EAS_MILD: return fc::EasCfg<9>::hist_doubles;
-    case FC_FORM_EAS_FULL: return fc::EasCfg<21>::hist_doubles;
+    case FC_FORM_EAS_MILD:
+    case FC_FORM_EAS_MILD_LINEAR: return fc::EasCfg<9>::hist_doubles;
+    case FC_FORM_EAS_FULL:
+    case FC_FORM_EAS_FULL_LINEAR: return fc::EasCfg<21>::hist_doubles;
     case FC_FORM_EAS_SHELL: return fc::EasCfg<7>::hist_doubles;
     case FC_FORM_SHELL_EAS_ANS: return ctx->celltype == FC_HEX8 ? fc::ShellCfg<fc::HEX8, 7>::hist_doubles : fc::ShellCfg<fc::WEDGE6, 1>::hist_doubles;
     default: return 0;
@@ -640,7 +644,7 @@ extern "C"
       fc::k_shell_recover<fc::WEDGE6, 1><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
     else if (ctx->formulation == FC_FORM_EAS_SHELL)
       fc::k_hex8_eas_recover<7><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
-    else if (ctx->formulation == FC_FORM_EAS_MILD)
+    else if (ctx->formulation == FC_FORM_EAS_MILD || ctx->formulation == FC_FORM_EAS_MILD_LINEAR)
       fc::k_hex8_eas_recover<9><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);
     else
       fc::k_hex8_eas_recover<21><<<gs, 256, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, d_u, step_length, ctx->d_eas);

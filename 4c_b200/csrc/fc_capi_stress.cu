@@ -165,6 +165,10 @@ namespace
         fc::k_gp_stress_eas<21><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_EAS_SHELL)
         fc::k_gp_stress_eas<7><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_EAS_MILD_LINEAR)
+        fc::k_gp_stress_eas<9, true><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
+      else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_EAS_FULL_LINEAR)
+        fc::k_gp_stress_eas<21, true><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_SHELL_ANS)
         fc::k_gp_stress_shell<fc::HEX8, 0><<<gs, 64, 0, ctx->stream>>>(A, stress_type, d_gp);
       else if (CT == fc::HEX8 && ctx->formulation == FC_FORM_SHELL_EAS_ANS)

@@ -121,7 +121,9 @@ namespace fc
     material_evaluate(*mp, C, S, cmat, fiber);
   }
 
-  template <int NEAS, bool WANT_K>
+  // LINEAR: KINEM linear (evaluate_eas_kinematics, calc_eas_helpers.hpp:617-632): B-operator at F = I, strain = sym grad u + Mtilde
+  // alpha; the geometric stiffness term stays, as EASFormulation::add_stiffness_matrix adds it for both kinematics (calc_eas.hpp:150-163)
+  template <int NEAS, bool WANT_K, bool LINEAR = false>
   __global__ void __launch_bounds__(EasCfg<NEAS>::threads) k_hex8_eas(const EvalArgs A, const unsigned char* __restrict__ ele_bad)
   {
     using Cfg = EasCfg<NEAS>;
@@ -163,10 +165,22 @@ namespace fc
       const double detJ = jacobian_mapping<8>(A.dNtab + (size_t)gp * 24, Xs, R + Cfg::gN);
       double F[9];
       deformation_gradient<HEX8>(Xs, us, R + Cfg::gN, F);
-      const double detF = det3(F);
+      const double detF = LINEAR ? 1.0 : det3(F);
       double C[6] = {F[0] * F[0] + F[3] * F[3] + F[6] * F[6], F[1] * F[1] + F[4] * F[4] + F[7] * F[7],
           F[2] * F[2] + F[5] * F[5] + F[8] * F[8], F[0] * F[1] + F[3] * F[4] + F[6] * F[7],
           F[1] * F[2] + F[4] * F[5] + F[7] * F[8], F[0] * F[2] + F[3] * F[5] + F[6] * F[8]};
+      if (LINEAR)
+      {
+        // the material law sees C = 2 sym(grad u) + I, the B-operator F = I
+        const double H[9] = {F[0] - 1.0, F[1], F[2], F[3], F[4] - 1.0, F[5], F[6], F[7], F[8] - 1.0};
+        C[0] = 2.0 * H[0] + 1.0;
+        C[1] = 2.0 * H[4] + 1.0;
+        C[2] = 2.0 * H[8] + 1.0;
+        C[3] = H[1] + H[3];
+        C[4] = H[5] + H[7];
+        C[5] = H[2] + H[6];
+        for (int k = 0; k < 9; ++k) F[k] = (k % 4 == 0) ? 1.0 : 0.0;
+      }
       double m[6];
       eas_monomials(gp, sm[Cfg::sDet] / detJ, m);
       eas_enhance_cauchy_green<NEAS>(Tm, m, alpha, C);

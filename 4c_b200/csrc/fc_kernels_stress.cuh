@@ -195,7 +195,7 @@ namespace fc
   // hex8 EAS: the enhanced Green-Lagrange strains of the element's alpha; the deformation gradient handed to the output is
   // F^enh = R U^enh with the rotation of the displacement-based F (compute_deformation_gradient_from_gl_strains,
   // 4C_solid_3D_ele_calc_lib.hpp:1257-1299).  The iteration data (Kaa^-1, Kda, s) is left alone, like calculate_stress.
-  template <int NEAS>
+  template <int NEAS, bool LINEAR = false>
   __global__ void k_gp_stress_eas(const EvalArgs A, int kind, double* __restrict__ gp_stress)
   {
     using Cfg = EasCfg<NEAS>;
@@ -219,6 +219,16 @@ namespace fc
     double Cd[6] = {F[0] * F[0] + F[3] * F[3] + F[6] * F[6], F[1] * F[1] + F[4] * F[4] + F[7] * F[7],
         F[2] * F[2] + F[5] * F[5] + F[8] * F[8], F[0] * F[1] + F[3] * F[4] + F[6] * F[7],
         F[1] * F[2] + F[4] * F[5] + F[7] * F[8], F[0] * F[2] + F[3] * F[5] + F[6] * F[8]};
+    if (LINEAR)
+    {
+      const double H[9] = {F[0] - 1.0, F[1], F[2], F[3], F[4] - 1.0, F[5], F[6], F[7], F[8] - 1.0};
+      Cd[0] = 2.0 * H[0] + 1.0;
+      Cd[1] = 2.0 * H[4] + 1.0;
+      Cd[2] = 2.0 * H[8] + 1.0;
+      Cd[3] = H[1] + H[3];
+      Cd[4] = H[5] + H[7];
+      Cd[5] = H[2] + H[6];
+    }
     double C[6] = {Cd[0], Cd[1], Cd[2], Cd[3], Cd[4], Cd[5]};
     eas_monomials(gp, detJ0 / detJ, m);
     for (int k = 0; k < NEAS; ++k) alpha[k] = A.eas[(size_t)e * Cfg::hist_doubles + Cfg::oAlpha + k];
@@ -234,6 +244,8 @@ namespace fc
     inv3(Ud, iUd);
     mat3_mul(F, iUd, Rm);
     mat3_mul(Rm, Ue, Fe);
+    if (LINEAR)  // the output sees the identity as deformation gradient
+      for (int k = 0; k < 9; ++k) Fe[k] = (k % 4 == 0) ? 1.0 : 0.0;
     gp_output(kind, S, C, Fe, gp_stress + ((size_t)e * 8 + gp) * 6);
   }
 

@@ -78,6 +78,8 @@ extern "C"
     FC_FORM_SHELL_EAS_ANS = 9, /* TECH shell_eas_ans (hex8: + the 7 modes of eas_sosh8, wedge6: + the mode of eas_sosw6);
                                  4C_solid_3D_ele_calc_shell_eas_ans.hpp:48-345; history and fc_solid_recover like FC_FORM_EAS_*,
                                  with K_da [3 nen][n] */
+    FC_FORM_EAS_MILD_LINEAR = 10, /* TECH eas_mild / eas_full with KINEM linear (EASSolidIntegrator<hex8, ..., KinemType::linear>, */
+    FC_FORM_EAS_FULL_LINEAR = 11, /* 4C_solid_3D_ele_factory.hpp:58-61): B-operator at F = I, strain = sym grad u + Mtilde alpha */
     FC_FORM_EAS_SHELL = 7     /* TECH shell_eas (hex8, the 7 modes of eas_sosh8 with t as thickness direction, no ANS):
                                  EASSolidIntegrator<hex8, eastype_sh8_7>, 4C_solid_3D_ele_factory.hpp:56-57; like FC_FORM_EAS_MILD */
   };

@@ -163,7 +163,7 @@ namespace fc_oracle
                                   action == 0 ? Ke.data() : nullptr, fib, fiber_gp_stride)
                       : form_is_eas(form)
                           ? element_evaluate_eas(neas, mp, X.data(), u.data(), eas_hist + (size_t)eas_history_doubles(neas) * e, fe.data(),
-                                action == 0 ? Ke.data() : nullptr, fib, fiber_gp_stride)
+                                action == 0 ? Ke.data() : nullptr, fib, fiber_gp_stride, nullptr, 0, 0, eas_linear(form))
                           : element_evaluate(mesh.ct, form, mp, X.data(), u.data(), fe.data(), action == 0 ? Ke.data() : nullptr, nullptr,
                                 0.0, nullptr, STRESS_CAUCHY, fib, fiber_gp_stride,
                                 mulf_hist ? mulf_hist + (size_t)18 * mulf_records(mesh.ct, form) * e : nullptr);

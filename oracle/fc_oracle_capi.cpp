@@ -295,12 +295,12 @@ extern "C"
   // overwritten (Ke may be NULL); invKaa, Kda, s of the history are written.  recover: alpha += step * alpha_inc(du).
   int oracle_eas_history_doubles(int neas) { return eas_history_doubles(neas); }
   int oracle_element_evaluate_eas(int neas, int kind, double young, double nue, const double* X, const double* u, double* hist,
-      double* fe, double* Ke)
+      double* fe, double* Ke, int linear)
   {
     MaterialParams mp{kind, young, nue};
     std::memset(fe, 0, sizeof(double) * 24);
     if (Ke) std::memset(Ke, 0, sizeof(double) * 576);
-    return element_evaluate_eas(neas, mp, X, u, hist, fe, Ke, nullptr, 0);
+    return element_evaluate_eas(neas, mp, X, u, hist, fe, Ke, nullptr, 0, nullptr, 0, 0, linear != 0);
   }
   void oracle_element_recover_eas(int neas, double* hist, const double* du, double step_length) { eas_recover(neas, hist, du, step_length); }
   // the job's prestress history [n_ele][ngp][18] (inverse Jacobian | deformation gradient, both column-major); returns its length
@@ -342,7 +342,7 @@ extern "C"
       const int neas = eas_modes(job.form);
       const bool strain = stress_type >= OUTPUT_STRAIN;
       return element_evaluate_eas(neas, job.mp, X.data(), u.data(), job.eas_hist.data() + (size_t)eas_history_doubles(neas) * e, nullptr,
-          nullptr, fib, job.fiber_gp_stride, gp_stress, strain ? 1 : 0, strain ? stress_type - OUTPUT_STRAIN : stress_type);
+          nullptr, fib, job.fiber_gp_stride, gp_stress, strain ? 1 : 0, strain ? stress_type - OUTPUT_STRAIN : stress_type, eas_linear(job.form));
     }
     return element_evaluate(m.ct, job.form, job.mp, X.data(), u.data(), nullptr, nullptr, nullptr, 0.0, gp_stress, stress_type, fib,
         job.fiber_gp_stride, job.mulf_hist.empty() ? nullptr : job.mulf_hist.data() + (size_t)18 * mulf_records(m.ct, job.form) * e);

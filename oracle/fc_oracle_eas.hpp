@@ -26,8 +26,9 @@ namespace fc_oracle
   // ---- EAS ----------------------------------------------------------------------------------------------------------
   // element history, in the order EASFormulation::pack writes it:
   //   alpha_inc [n] | alpha [n] | s [n] | invKaa [n x n] | Kda [24 x n] | old_step_length      (matrices column-major)
-  inline bool form_is_eas(int form) { return form == FORM_EAS_MILD || form == FORM_EAS_FULL || form == FORM_EAS_SHELL; }
-  inline int eas_modes(int form) { return form == FORM_EAS_FULL ? 21 : (form == FORM_EAS_SHELL ? 7 : 9); }
+  inline bool eas_linear(int form) { return form == FORM_EAS_MILD_LINEAR || form == FORM_EAS_FULL_LINEAR; }
+  inline bool form_is_eas(int form) { return form == FORM_EAS_MILD || form == FORM_EAS_FULL || form == FORM_EAS_SHELL || eas_linear(form); }
+  inline int eas_modes(int form) { return (form == FORM_EAS_FULL || form == FORM_EAS_FULL_LINEAR) ? 21 : (form == FORM_EAS_SHELL ? 7 : 9); }
   inline int eas_history_doubles(int neas) { return 3 * neas + neas * neas + 24 * neas + 1; }
   struct EasView
   {
@@ -146,7 +147,8 @@ namespace fc_oracle
   // one hex8 EAS element: fe [24], Ke [24 x 24] col-major (either may be null), Gauss-point output gp_out [8][6] (null = none):
   // out_kind 0 = stress of stress_type, 1 = strain of strain type stress_type.  Writes invKaa, Kda, s of the history.
   inline int element_evaluate_eas(int neas, const MaterialParams& mp, const double* X, const double* u, double* hist, double* fe,
-      double* Ke, const double* fiber, int fiber_gp_stride, double* gp_out = nullptr, int out_kind = 0, int out_type = 0)
+      double* Ke, const double* fiber, int fiber_gp_stride, double* gp_out = nullptr, int out_kind = 0, int out_type = 0,
+      bool linear = false /* KINEM linear: B at F = I, strain = B u + Mtilde alpha, deformation gradient = I */)
   {
     constexpr int NEN = 8, ND = 24;
     EasView h(neas, hist);
@@ -185,7 +187,10 @@ namespace fc_oracle
       const double fac = jm.det * gw[gp];
       SpatialMaterialMapping<NEN> sm;
       evaluate_spatial_material_mapping<NEN>(HEX8, jm, x, u, 1.0, sm, &singular);
-      evaluate_strain_gradient<NEN>(jm.N_XYZ, sm.F, B);
+      if (linear)
+        evaluate_linear_strain_gradient<NEN>(jm.N_XYZ, B);
+      else
+        evaluate_strain_gradient<NEN>(jm.N_XYZ, sm.F, B);
       eas_shape_functions(neas, gxi[gp], M.data());
       const double scale = detJ0 / jm.det;
       for (int k = 0; k < neas; ++k)
@@ -196,15 +201,23 @@ namespace fc_oracle
           Mt[r + 6 * k] = scale * v;
         }
       double C[9], E[6], Fenh[9];
-      multiply_tn<3, 3, 3>(C, sm.F, sm.F);
-      evaluate_green_lagrange_strain(C, E);
+      if (linear)
+        multiply_nn<6, ND, 1>(E, B, u);  // evaluate_linear_gl_strain
+      else
+      {
+        multiply_tn<3, 3, 3>(C, sm.F, sm.F);
+        evaluate_green_lagrange_strain(C, E);
+      }
       for (int r = 0; r < 6; ++r)
       {
         double v = Mt[r] * h.alpha[0];
         for (int k = 1; k < neas; ++k) v += Mt[r + 6 * k] * h.alpha[k];
         E[r] += v;
       }
-      eas_deformation_gradient(sm.F, E, Fenh);
+      if (linear)
+        for (int i = 0; i < 9; ++i) Fenh[i] = (i % 4 == 0) ? 1.0 : 0.0;
+      else
+        eas_deformation_gradient(sm.F, E, Fenh);
       double S[6], cmat[36];
       material_evaluate(mp, Fenh, E, S, cmat, fiber ? fiber + (size_t)fiber_gp_stride * gp : nullptr);
       if (gp_out)

@@ -36,6 +36,8 @@ namespace fc_oracle
     FORM_MULF = 3,    // PRESTRESS_TECH mulf: src/solid_3D_ele/4C_solid_3D_ele_calc_mulf.hpp:40-196, ..._calc_lib_mulf.hpp:24-84
     FORM_EAS_MILD = 4,  // TECH eas_mild (hex8, 9 modes) and
     FORM_EAS_FULL = 5,  // TECH eas_full (hex8, 21 modes): src/solid_3D_ele/4C_solid_3D_ele_calc_eas.hpp, fc_oracle_eas.hpp
+    FORM_EAS_MILD_LINEAR = 10,  // TECH eas_mild / eas_full with KINEM linear (EASSolidIntegrator<hex8, ..., KinemType::linear>,
+    FORM_EAS_FULL_LINEAR = 11,  // 4C_solid_3D_ele_factory.hpp:58-61; evaluate_eas_kinematics, calc_eas_helpers.hpp:617-632)
     FORM_SHELL_ANS = 8,      // TECH shell_ans (hex8, wedge6) and
     FORM_SHELL_EAS_ANS = 9,  // TECH shell_eas_ans (hex8: 7 EAS modes, wedge6: 1): fc_oracle_shell.hpp
     FORM_EAS_SHELL = 7,  // TECH shell_eas (hex8, the 7 modes of eas_sosh8, no ANS): EASSolidIntegrator<hex8, eastype_sh8_7>

@@ -91,6 +91,8 @@ CASES = [
     "solid_ele_hex8_Standard_shell_eas.dat",  # TECH shell_eas = EAS with the 7 modes of eas_sosh8
     # Cook's membrane with 64 EAS elements, near-incompressible Neo-Hooke, 100 load steps (the multi-element EAS golden)
     "sohex8_easmild_cooks_nl.dat",
+    "sohex8_easmild_cooks_lin.dat",  # the same mesh with KINEM linear, St.Venant-Kirchhoff nu = 0.4999, one load step
+    "sohex8_easfull_cooks_lin.dat",
     # solid shells: assumed natural strains, alone and with the EAS modes of the solid shell
     "solid_ele_hex8_Standard_shell_ans.dat",
     "solid_ele_hex8_Standard_shell_eas_ans.4C.yaml",

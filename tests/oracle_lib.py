@@ -13,8 +13,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
 HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5, HEX18 = 0, 1, 2, 3, 4, 5, 6, 7
-FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF, FORM_EAS_MILD, FORM_EAS_FULL, FORM_MULF_FBAR, FORM_EAS_SHELL, FORM_SHELL_ANS, FORM_SHELL_EAS_ANS = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9
-NEAS = {FORM_EAS_MILD: 9, FORM_EAS_FULL: 21, FORM_EAS_SHELL: 7}
+FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF, FORM_EAS_MILD, FORM_EAS_FULL, FORM_MULF_FBAR, FORM_EAS_SHELL, FORM_SHELL_ANS, FORM_SHELL_EAS_ANS, FORM_EAS_MILD_LINEAR, FORM_EAS_FULL_LINEAR = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11
+NEAS = {FORM_EAS_MILD: 9, FORM_EAS_FULL: 21, FORM_EAS_SHELL: 7, FORM_EAS_MILD_LINEAR: 9, FORM_EAS_FULL_LINEAR: 21}
 OUTPUT_STRAIN = 16  # stress_type = OUTPUT_STRAIN + strain type: the Gauss-point output is that strain (stress-like Voigt)
 STRAIN_GL, STRAIN_EA, STRAIN_LOG = 0, 1, 2
 MAT_SVK, MAT_NEOHOOKE = 0, 1
@@ -148,13 +148,13 @@ def eas_history_doubles(neas):
     return lib.oracle_eas_history_doubles(C.c_int(neas))
 
 
-def element_evaluate_eas(neas, kind, young, nue, X, u, hist, want_K=True):
+def element_evaluate_eas(neas, kind, young, nue, X, u, hist, want_K=True, linear=False):
     """one hex8 EAS element with history hist (modified in place: invKaa, Kda, s) -> err, fe (8, 3), Ke (24, 24) [r, c]"""
     X, u = _d(X), _d(u)
     assert hist.dtype == np.float64 and hist.flags["C_CONTIGUOUS"] and hist.size == eas_history_doubles(neas)
     fe, Ke = np.zeros(24), (np.zeros((24, 24)) if want_K else None)
     err = lib.oracle_element_evaluate_eas(C.c_int(neas), C.c_int(kind), C.c_double(young), C.c_double(nue), _p(X), _p(u), _p(hist),
-                                          _p(fe), _p(Ke) if want_K else None)
+                                          _p(fe), _p(Ke) if want_K else None, C.c_int(1 if linear else 0))
     return err, fe.reshape(8, 3), (np.ascontiguousarray(Ke.T) if want_K else None)
 
 

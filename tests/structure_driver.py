@@ -90,7 +90,7 @@ class Problem:
             if "PRESTRESS_TECH mulf" in opts:
                 return 6 if "TECH fbar" in opts else 3
             if "KINEM linear" in opts:
-                return 2
+                return 10 if "TECH eas_mild" in opts else (11 if "TECH eas_full" in opts else 2)
             return {"fbar": 1, "eas_mild": 4, "eas_full": 5, "shell_eas": 7, "shell_ans": 8, "shell_eas_ans": 9}.get(opts.split()[opts.split().index("TECH") + 1], 0) if "TECH" in opts.split() else 0
         techs = {tech(e["opts"]) for e in fx["elements"]}
         assert len(techs) == 1

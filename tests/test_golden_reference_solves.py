@@ -108,7 +108,7 @@ def oracle_backend(oracle, p):
         return M
     assemble.job = job  # prestress update, recover and Gauss-point output with the job's history
     assemble.hooks = dict(update_prestress=lambda dd: job.update_prestress(dd.reshape(-1, 3)),
-                          recover=(lambda inc: job.recover(inc.reshape(-1, 3))) if p.form in (4, 5, 7, 9) else None)
+                          recover=(lambda inc: job.recover(inc.reshape(-1, 3))) if p.form in (4, 5, 7, 9, 10, 11) else None)
     return assemble, mass
 
 
@@ -118,7 +118,11 @@ def oracle_backend(oracle, p):
 # 0.3e-10 ... 1e-10 through the CUDA library, different from run to run because the FP64 reductions of the scatter arrive in any
 # order.  Accepted within 1e-9 (1.5e-10 relative).
 CASES.append("sohex8_easmild_cooks_nl")
-RESULT_TOLERANCE_FACTOR = {"sohex8_easmild_cooks_nl": 1000.0}
+CASES += ["sohex8_easmild_cooks_lin", "sohex8_easfull_cooks_lin"]  # KINEM linear with EAS, St.Venant-Kirchhoff nu = 0.4999
+# The linear Cook inputs (St.Venant-Kirchhoff, nu = 0.4999, condition ~1e8): the residual of the first solve sits at 3e-8, above
+# TOLRES 1e-12, so the listed value is the reference's own rounding path; its easfull twin lists 1e-8 and carries, commented out, a
+# 1e-12 line whose value differs in the ninth digit.  The replay is 1.5e-9 away; accepted within 1e-8 like the twin.
+RESULT_TOLERANCE_FACTOR = {"sohex8_easmild_cooks_nl": 1000.0, "sohex8_easmild_cooks_lin": 1.0e4}
 
 # solid shells (TECH shell_ans, shell_eas_ans)
 SHELL_CASES = ["solid_ele_hex8_Standard_shell_ans", "solid_ele_hex8_Standard_shell_eas_ans", "solid_ele_wedge6_Standard_shell_ans",
@@ -168,7 +172,7 @@ def test_reference_result_description_cuda(fc, oracle, case):
     s, assemble, mass = cuda_backend(fc, p)
     p.neumann = sd.CudaNeumann(s)  # f_ext from fc_solid_neumann_surface / _volume
     # PRESTRESS_TECH mulf: fc_solid_update_prestress; EAS: fc_solid_recover after every Newton update
-    d, hist = sd.run(p, assemble, mass, update_prestress=s.update_prestress, recover=s.recover if p.form in (4, 5, 7, 9) else None)
+    d, hist = sd.run(p, assemble, mass, update_prestress=s.update_prestress, recover=s.recover if p.form in (4, 5, 7, 9, 10, 11) else None)
     err, n = p.result_error(d)
     assert err <= RESULT_TOLERANCE_FACTOR.get(case, 1.0), (case, err, hist)
     # the external force of the library against the oracle's, at the end time
@@ -184,7 +188,7 @@ def test_reference_result_description_cuda(fc, oracle, case):
     if p.form in (3, 6):  # the Gauss-point histories after the prestress steps
         h1, h2 = s.mulf_history(), a2.job.mulf_history()
         assert np.max(np.abs(h1 - h2)) <= 1e-10 * np.max(np.abs(h2))
-    if p.form in (4, 5, 7, 9):  # the enhanced strain parameters at the end of the solve
+    if p.form in (4, 5, 7, 9, 10, 11):  # the enhanced strain parameters at the end of the solve
         n = oracle.NEAS.get(p.form) or (7 if p.ct == 0 else 1)
         a1, a2_ = s.eas_history()[:, n:2 * n], a2.job.eas_history()[:, n:2 * n]
         # near-incompressible Cook problem: condition ~1e8, see below
@@ -214,7 +218,8 @@ def test_reference_result_description_cuda(fc, oracle, case):
         for x, y in zip(h[:min(n1, n2)], h2[:min(n1, n2)]):
             assert abs(x - y) <= 1e-3 * y + floor, (h, h2)
     tol = min(r["tolerance"] for r in p.fx["results"] if r["quantity"].startswith("disp"))
-    assert np.max(np.abs(d - d2)) <= max(1e-10 * np.max(np.abs(d2)), tol)  # CUDA-driven vs oracle-driven solution
+    # CUDA-driven vs oracle-driven solution (near-incompressible inputs: condition ~1e8 times rounding)
+    assert np.max(np.abs(d - d2)) <= max((1e-10 if p.nue < 0.49 else 1e-8) * np.max(np.abs(d2)), tol)
     s.close()
 
 
@@ -278,11 +283,11 @@ def test_reference_nodal_stresses_cuda(fc, oracle, case):
     def update(dd):
         s.update_prestress(dd)
         job.update_prestress(dd.reshape(-1, 3))
-    d, _ = sd.run(p, assemble, mass, update_prestress=update, recover=s.recover if p.form in (4, 5, 7, 9) else None)
+    d, _ = sd.run(p, assemble, mass, update_prestress=update, recover=s.recover if p.form in (4, 5, 7, 9, 10, 11) else None)
     if p.form in (3, 6):
         h1, h2 = s.mulf_history(), job.mulf_history()
         assert np.max(np.abs(h1 - h2)) <= 1e-13 * np.max(np.abs(h2))
-    if p.form in (4, 5, 7, 9):
+    if p.form in (4, 5, 7, 9, 10, 11):
         job.set_eas_history(s.eas_history())
     gp, nodal = s.evaluate_stress(d, p.stress_type)
     err, n = sd.stress_result_error(p, nodal)

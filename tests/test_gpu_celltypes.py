@@ -215,7 +215,7 @@ def test_mulf_prestress_parity(fc, oracle, name, mat, MULF):
     s.close()
 
 
-@pytest.mark.parametrize("form,mat", [(4, NH), (4, SVK), (5, NH), (5, SVK), (7, NH)])
+@pytest.mark.parametrize("form,mat", [(4, NH), (4, SVK), (5, NH), (5, SVK), (7, NH), (10, SVK), (11, NH)])
 def test_eas_parity(fc, oracle, form, mat):
     """hex8 TECH eas_mild / eas_full on a distorted 3x2x2 block: three rounds of evaluate + recover with the library and with an
     oracle job; element fe / Ke, assembled system, history (alpha, s, Kaa^-1, Kda) and Gauss-point stresses / strains."""
@@ -243,7 +243,7 @@ def test_eas_parity(fc, oracle, form, mat):
         fe, Ke = s.evaluate_elements(np.ascontiguousarray(uk.reshape(-1)), want_K=True)
         for e in range(len(conn)):
             he = np.ascontiguousarray(h0[e])
-            err, fr, kr = oracle.element_evaluate_eas(neas, mat, 10.0, 0.3, X[conn[e]], uk[conn[e]], he)
+            err, fr, kr = oracle.element_evaluate_eas(neas, mat, 10.0, 0.3, X[conn[e]], uk[conn[e]], he, linear=form in (10, 11))
             assert err == 0
             assert np.max(np.abs(Ke[e] - kr)) <= 1e-11 * np.max(np.abs(kr)), (it, e, np.max(np.abs(Ke[e] - kr)) / np.max(np.abs(kr)))
             assert np.max(np.abs(fe[e].reshape(8, 3) - fr)) <= 1e-11 * max(np.max(np.abs(fr)), np.max(np.abs(kr)))

@@ -91,6 +91,12 @@ CASES = [
     "solid_ele_hex8_Standard_shell_eas.dat",  # TECH shell_eas = EAS with the 7 modes of eas_sosh8
     # Cook's membrane with 64 EAS elements, near-incompressible Neo-Hooke, 100 load steps (the multi-element EAS golden)
     "sohex8_easmild_cooks_nl.dat",
+    # 125 eas_full elements, St.Venant-Kirchhoff nu = 0.4999, symmetry planes with LINE Dirichlet conditions that override the
+    # surface ones; patch tests with a POINT condition
+    "sohex8_incompr_block.dat",
+    "sohex8_incompr_block_nln.dat",
+    "sohex8_easfull_patchtest.dat",
+    "sohex8_disp_patchtest.dat",
     "sohex8_easmild_cooks_lin.dat",  # the same mesh with KINEM linear, St.Venant-Kirchhoff nu = 0.4999, one load step
     "sohex8_easfull_cooks_lin.dat",
     # solid shells: assumed natural strains, alone and with the EAS modes of the solid shell
@@ -143,7 +149,7 @@ def from_dat(path):
     for l in s["MATERIALS"]:
         t = l.split()
         mats[int(t[1])] = t[2:]
-    functs = {int(k[5:]): v[0].split("SYMBOLIC_FUNCTION_OF_SPACE_TIME")[1].strip() for k, v in s.items() if re.match(r"FUNCT\d+$", k)}
+    functs = {int(k[5:]): re.split(r"SYMBOLIC_FUNCTION_OF_(?:SPACE_)?TIME", v[0])[1].strip() for k, v in s.items() if re.match(r"FUNCT\d+$", k)}
     results = []
     for l in s.get("RESULT DESCRIPTION", []):
         t = l.split()
@@ -153,6 +159,13 @@ def from_dat(path):
     for l in s["DSURF-NODE TOPOLOGY"]:
         t = l.split()
         surf.setdefault(int(t[3]), []).append(int(t[1]))
+    line, point = {}, {}
+    for l in s.get("DLINE-NODE TOPOLOGY", []):
+        t = l.split()
+        line.setdefault(int(t[3]), []).append(int(t[1]))
+    for l in s.get("DNODE-NODE TOPOLOGY", []):
+        t = l.split()
+        point.setdefault(int(t[3]), []).append(int(t[1]))
     vol = {}
     for l in s.get("DVOL-NODE TOPOLOGY", []):
         t = l.split()
@@ -172,6 +185,8 @@ def from_dat(path):
                      "opts": " ".join(t[i + 2:])})
     return {"dynamic": dyn, "io": keyvals(s.get("IO", [])), "materials": mats, "functs": functs, "results": results, "dsurf": surf,
             "dirich": [parse_condition_dat(l) for l in s.get("DESIGN SURF DIRICH CONDITIONS", [])],
+            "dline": line, "dirich_line": [parse_condition_dat(l) for l in s.get("DESIGN LINE DIRICH CONDITIONS", [])],
+            "dnode": point, "dirich_point": [parse_condition_dat(l) for l in s.get("DESIGN POINT DIRICH CONDITIONS", [])],
             "neumann": [parse_condition_dat(l) for l in s.get("DESIGN SURF NEUMANN CONDITIONS", [])],
             "dvol": vol, "vol_neumann": [parse_condition_dat(l) for l in s.get("DESIGN VOL NEUMANN CONDITIONS", [])],
             "nodes": nodes, "node_fibers": node_fibers, "elements": eles}

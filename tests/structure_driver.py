@@ -111,15 +111,26 @@ class Problem:
         self.ref_stop = None
         if float(dyn.get("TOLRES", 0)) >= 1e-9 and dyn.get("NORM_RESF", "Abs") == "Abs" and dyn.get("NORM_DISP", "Abs") == "Abs":
             self.ref_stop = (float(dyn["TOLRES"]), float(dyn["TOLDISP"]), dyn.get("NORMCOMBI_RESFDISP", "And"))
+        # MAXITER with DIVERCONT continue: the reference goes on with what it has after MAXITER iterations
+        self.ref_maxiter = int(dyn["MAXITER"]) if self.ref_stop is not None and dyn.get("DIVERCONT", "stop") == "continue" and "MAXITER" in dyn else None
         # PRESTRESS mulf: steps with t <= PRESTRESSTIME end with struct_update_prestress and a reset of the displacements
         self.prestress_time = float(dyn["PRESTRESSTIME"]) if dyn.get("PRESTRESS", "none").lower() == "mulf" else None
         # Dirichlet: all values are zero in these inputs
-        fixed = []
-        for c in fx["dirich"]:
-            assert not any(c["val"])
-            for n in fx["dsurf"][str(c["E"])]:
-                fixed += [3 * self.index[n] + d for d in range(3) if c["onoff"][d]]
-        self.fixed = np.array(sorted(set(fixed)), np.int64)
+        # Hierarchy of Core::FE::Utils::Dbc::read_dirichlet_condition (4C_fem_discretization_utils_dbc.cpp:164-400): surface, then
+        # line, then point conditions; a condition sets its ONOFF = 1 DOFs, and its ONOFF = 0 releases a DOF only if a condition of
+        # higher dimension fixed it (conditions of the same kind add up)
+        toggle, level = np.zeros(self.n_dof, bool), np.full(self.n_dof, 9)
+        for order, key, topo in ((2, "dirich", "dsurf"), (1, "dirich_line", "dline"), (0, "dirich_point", "dnode")):
+            for c in fx.get(key, []):
+                assert not any(c["val"])
+                for n in fx[topo][str(c["E"])]:
+                    for d in range(3):
+                        lid = 3 * self.index[n] + d
+                        if c["onoff"][d]:
+                            toggle[lid], level[lid] = True, order
+                        elif order < level[lid]:
+                            toggle[lid], level[lid] = False, order
+        self.fixed = np.nonzero(toggle)[0].astype(np.int64)
         self.xi_nodes = np.asarray(node_param_coords(self.ct), float)
         self.faces = []
         for c in fx["neumann"]:
@@ -376,7 +387,7 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, 
                 fint, K = assemble(d)
                 r = fint - fext
                 r[fixed] = 0.0
-                for _ in range(maxiter):
+                for _ in range(p.ref_maxiter or maxiter):
                     norms.append(float(np.linalg.norm(r)))
                     inc = _solve(K, -r, fixed)
                     d = d + inc

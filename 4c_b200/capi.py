@@ -12,7 +12,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libfourc_b200.so")
 
-FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5, FC_HEX18 = 0, 1, 2, 3, 4, 5, 6, 7
+FC_HEX8, FC_HEX27, FC_TET10, FC_HEX20, FC_TET4, FC_WEDGE6, FC_PYRAMID5, FC_HEX18, FC_NURBS27 = 0, 1, 2, 3, 4, 5, 6, 7, 8
 FC_FORM_DISPLACEMENT, FC_FORM_FBAR, FC_FORM_LINEAR, FC_FORM_MULF, FC_FORM_EAS_MILD, FC_FORM_EAS_FULL, FC_FORM_MULF_FBAR, FC_FORM_EAS_SHELL, FC_FORM_SHELL_ANS, FC_FORM_SHELL_EAS_ANS, FC_FORM_EAS_MILD_LINEAR, FC_FORM_EAS_FULL_LINEAR = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11
 FC_STRAIN_GL, FC_STRAIN_EA, FC_STRAIN_LOG = 0, 1, 2
 FC_MAT_STVENANTKIRCHHOFF, FC_MAT_ELASTHYPER_COUPNEOHOOKE = 0, 1
@@ -28,8 +28,8 @@ FC_OK, FC_ERR_INVALID, FC_ERR_NO_DEVICE, FC_ERR_CUDA = 0, -1, -2, -3
 FC_ERR_NEGATIVE_JACOBIAN, FC_ERR_GRAPH, FC_ERR_UNSUPPORTED = -4, -5, -6
 FC_ERR_SOLVER, FC_ERR_SOLVER_NOT_CONVERGED = -7, -8
 FC_SOLVER_CG, FC_SOLVER_BICGSTAB, FC_SOLVER_CG_MG = 0, 1, 2
-NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10, FC_HEX20: 20, FC_TET4: 4, FC_WEDGE6: 6, FC_PYRAMID5: 5, FC_HEX18: 18}
-NGP = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4, FC_HEX20: 27, FC_TET4: 1, FC_WEDGE6: 6, FC_PYRAMID5: 8, FC_HEX18: 18}
+NEN = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 10, FC_HEX20: 20, FC_TET4: 4, FC_WEDGE6: 6, FC_PYRAMID5: 5, FC_HEX18: 18, FC_NURBS27: 27}
+NGP = {FC_HEX8: 8, FC_HEX27: 27, FC_TET10: 4, FC_HEX20: 27, FC_TET4: 1, FC_WEDGE6: 6, FC_PYRAMID5: 8, FC_HEX18: 18, FC_NURBS27: 27}
 
 EXPORTS = [
     "fc_version", "fc_last_error", "fc_solid_create", "fc_solid_destroy", "fc_solid_set_stream",
@@ -37,6 +37,7 @@ EXPORTS = [
     "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
     "fc_solid_error_state", "fc_solid_error_allreduce", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_neumann_surface", "fc_solid_neumann_volume",
     "fc_solid_neumann_surface_gp_coords", "fc_solid_neumann_volume_gp_coords", "fc_solid_evaluate_elements",
+    "fc_solid_set_nurbs", "fc_solid_neumann_surface_nurbs", "fc_solid_neumann_surface_nurbs_gp_coords",
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack", "fc_solid_halo_set_counts", "fc_solid_halo_exchange",
     "fc_solid_last_kernel_ms", "fc_solid_kernel_ms_history", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
@@ -253,6 +254,12 @@ class Solid:
                                           _ptr(X), _ptr(node_gid), _ptr(node_owner), C.c_int(self.n_ele), _ptr(conn),
                                           _ptr(ele_gid)))
 
+    def set_nurbs(self, ele_knots, node_weights):
+        """FC_NURBS27: knot spans (n_col_ele, 3, 6) and control point weights (n_col_nodes,); must follow set_mesh"""
+        kn, w = _f64(ele_knots).reshape(-1), _f64(node_weights)
+        assert kn.size == 18 * self.n_ele and w.size == self.n_col_nodes
+        self._chk(lib().fc_solid_set_nurbs(self.h, _ptr(kn), _ptr(w)))
+
     def set_material(self, kind, young, nue):
         p = _f64([young, nue])
         self._chk(lib().fc_solid_set_material(self.h, C.c_int(kind), _ptr(p), C.c_int(2)))
@@ -430,6 +437,19 @@ class Solid:
         ngp = FACE_NGP[face_type]
         out = np.zeros((len(fn), ngp, 3))
         self._chk(lib().fc_solid_neumann_surface_gp_coords(self.h, C.c_int(face_type), C.c_int(len(fn)), _ptr(fn), _ptr(out)))
+        return out
+
+    def neumann_surface_nurbs(self, parent_ele, surface_id, onoff, val, f_ext, gp_factor=None):
+        """faces of nurbs27 elements, named by parent column element and the parent's surface number 0..5"""
+        pe, sid = _i32(parent_ele), _i32(surface_id)
+        oo, vv = _i32(onoff[:3]), _f64(val[:3])
+        gf = None if gp_factor is None else (_f64(gp_factor) if isinstance(gp_factor, np.ndarray) else gp_factor)
+        self._chk(lib().fc_solid_neumann_surface_nurbs(self.h, C.c_int(len(pe)), _ptr(pe), _ptr(sid), _ptr(oo), _ptr(vv), _ptr(gf), _ptr(f_ext)))
+
+    def neumann_surface_nurbs_gp_coords(self, parent_ele, surface_id):
+        pe, sid = _i32(parent_ele), _i32(surface_id)
+        out = np.zeros((len(pe), 9, 3))
+        self._chk(lib().fc_solid_neumann_surface_nurbs_gp_coords(self.h, C.c_int(len(pe)), _ptr(pe), _ptr(sid), _ptr(out)))
         return out
 
     def neumann_volume_gp_coords(self, ele_lids):

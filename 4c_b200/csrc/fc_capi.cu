@@ -92,6 +92,8 @@ extern "C"
     dev_free(ctx->d_ele_gid);
     dev_free(ctx->d_dNtab);
     dev_free(ctx->d_gpw);
+    dev_free(ctx->d_nurbs_knots);
+    dev_free(ctx->d_nurbs_weights);
     dev_free(ctx->d_ele_bad);
     dev_free(ctx->d_geom);
     dev_free(ctx->d_fiber);
@@ -215,6 +217,7 @@ extern "C"
     dev_free(ctx->d_fiber);
     ctx->fiber_gp = 0;
     if (!node_fiber1) return FC_OK;
+    if (ctx->celltype == FC_NURBS27) return fail(ctx, FC_ERR_UNSUPPORTED, "nodal fibres on nurbs27");
     std::vector<double> f;
     int bad = 0;
     switch (ctx->celltype)
@@ -240,7 +243,7 @@ extern "C"
   {
     if (!ctx || !X || !node_owner || !conn || !ele_gid || n_col_nodes <= 0 || n_col_ele < 0) return FC_ERR_INVALID;
     (void)node_gid;
-    if (celltype < FC_HEX8 || celltype > FC_HEX18) return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
+    if (celltype < FC_HEX8 || celltype > FC_NURBS27) return fail(ctx, FC_ERR_UNSUPPORTED, "cell type not on the path");
     if (formulation != FC_FORM_DISPLACEMENT && formulation != FC_FORM_LINEAR && formulation != FC_FORM_MULF &&
         !(formulation == FC_FORM_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)) &&
         !(formulation == FC_FORM_MULF_FBAR && (celltype == FC_HEX8 || celltype == FC_PYRAMID5)) &&
@@ -290,8 +293,20 @@ extern "C"
     FC_CUDA(dev_upload(ctx->d_conn, conn, (size_t)n_col_ele * nen, ctx->stream));
     FC_CUDA(dev_upload(ctx->d_ele_gid, ele_gid, (size_t)n_col_ele, ctx->stream));
     std::vector<double> dN, w;
+    ctx->nurbs_ready = false;
+    dev_free(ctx->d_nurbs_knots);
+    dev_free(ctx->d_nurbs_weights);
     switch (celltype)
     {
+      case FC_NURBS27:
+        // Gauss weights only: the shape tables are per element and come with fc_solid_set_nurbs
+        w.resize(27);
+        for (int g = 0; g < 27; ++g)
+        {
+          double xi[3];
+          fc::gauss_point<fc::NURBS27>(g, xi, &w[g]);
+        }
+        break;
       case FC_HEX8: fill_tables<fc::HEX8>(dN, w); break;
       case FC_HEX27: fill_tables<fc::HEX27>(dN, w); break;
       case FC_TET10: fill_tables<fc::TET10>(dN, w); break;
@@ -314,7 +329,7 @@ extern "C"
       // 37 KB per element).  More than one rank: elements without ghost nodes first, so that they can be evaluated while the
       // halo import is in flight (FC_EVAL_INTERIOR, then FC_EVAL_BOUNDARY).
       std::vector<int> perm;
-      const long long budget = celltype == FC_HEX8 ? 12000 : (celltype == FC_TET10 ? 8500 : (celltype == FC_HEX27 ? 650 : 2000));
+      const long long budget = celltype == FC_HEX8 ? 12000 : (celltype == FC_TET10 ? 8500 : (celltype == FC_HEX27 || celltype == FC_NURBS27 ? 650 : 2000));
       fc_host::l2_sweep_order(n_col_nodes, X, n_col_ele, nen, conn, budget, perm);
       ctx->n_interior_ele = n_col_ele;
       if (n_row < n_col_nodes)
@@ -335,7 +350,14 @@ extern "C"
     }
     ctx->geom_bad_count = 0;
     ctx->geom_first_bad_gid = -1;
-    if (n_col_ele > 0)
+    if (n_col_ele > 0 && celltype == FC_NURBS27)
+    {
+      // node-Jacobian check and prestress history need the element tables: fc_solid_set_nurbs
+      FC_CUDA(cudaMalloc((void**)&ctx->d_ele_bad, (size_t)n_col_ele));
+      FC_CUDA(cudaMemsetAsync(ctx->d_ele_bad, 0, (size_t)n_col_ele, ctx->stream));
+      ctx->h_err_pinned[0] = 0;
+    }
+    else if (n_col_ele > 0)
     {
       FC_CUDA(cudaMalloc((void**)&ctx->d_ele_bad, (size_t)n_col_ele));
       ctx->h_err_pinned[0] = 0;
@@ -346,6 +368,7 @@ extern "C"
   fc::k_check_node_jacobians<CT><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_ele_gid, n_col_ele, ctx->d_dNtab, ctx->d_ele_bad, ctx->d_err)
       switch (celltype)
       {
+        case FC_NURBS27: break;  // not reached
         case FC_HEX8: FC_CHECK_NODE_JACOBIANS(fc::HEX8); break;
         case FC_HEX27: FC_CHECK_NODE_JACOBIANS(fc::HEX27); break;
         case FC_TET10: FC_CHECK_NODE_JACOBIANS(fc::TET10); break;
@@ -367,6 +390,60 @@ extern "C"
       ctx->geom_bad_count = ctx->h_err_pinned[0];
       ctx->geom_first_bad_gid = ctx->h_err_pinned[1];
     }
+    return FC_OK;
+  }
+
+  // Knot spans and control point weights of a nurbs27 mesh (what Core::FE::Nurbs::get_my_nurbs_knots_and_weights hands to every
+  // element evaluation, 4C_solid_3D_ele_calc_lib.hpp:193-200): builds the per-element shape tables, then runs what set_mesh
+  // postponed - the node-Jacobian check and the initial prestress history.
+  int fc_solid_set_nurbs(fc_ctx* ctx, const double* ele_knots, const double* node_weights)
+  {
+    if (!ctx || ctx->celltype != FC_NURBS27) return fail(ctx, FC_ERR_INVALID, "set_mesh with FC_NURBS27 must precede set_nurbs");
+    if (!ele_knots || !node_weights) return fail(ctx, FC_ERR_INVALID, "knots and weights are required");
+    for (int i = 0; i < ctx->n_col_nodes; ++i)
+      if (!(node_weights[i] > 0.0)) return fail(ctx, FC_ERR_INVALID, "control point weights must be positive");
+    FC_CUDA(cudaSetDevice(ctx->device));
+    ctx->nurbs_ready = false;
+    const int n_ele = ctx->n_ele;
+    FC_CUDA(dev_upload(ctx->d_nurbs_knots, ele_knots, (size_t)18 * n_ele, ctx->stream));
+    FC_CUDA(dev_upload(ctx->d_nurbs_weights, node_weights, (size_t)ctx->n_col_nodes, ctx->stream));
+    dev_free(ctx->d_dNtab);
+    ctx->geom_bad_count = 0;
+    ctx->geom_first_bad_gid = -1;
+    if (n_ele > 0)
+    {
+      FC_CUDA(cudaMalloc((void**)&ctx->d_dNtab, sizeof(double) * (size_t)fc::NurbsTab::stride * n_ele));
+      unsigned char* d_zero = nullptr;
+      FC_CUDA(cudaMalloc((void**)&d_zero, (size_t)n_ele));
+      const long long nt = (long long)n_ele * (fc::NurbsTab::ngp + fc::NurbsTab::nen + 1);
+      fc::k_nurbs_tables<<<(unsigned)((nt + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_nurbs_knots, ctx->d_nurbs_weights, ctx->d_conn, n_ele,
+          ctx->d_dNtab, d_zero);
+      std::vector<unsigned char> zero((size_t)n_ele);
+      cudaError_t e = cudaGetLastError();
+      if (e == cudaSuccess) e = cudaMemcpyAsync(zero.data(), d_zero, (size_t)n_ele, cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+      cudaFree(d_zero);
+      FC_CUDA(e);
+      for (int el = 0; el < n_ele; ++el)
+        if (zero[el]) return fail(ctx, FC_ERR_INVALID, "nurbs27 element with a zero-sized knot span (the reference throws, 4C_solid_3D_ele_calc_lib.hpp:196-199)");
+      ctx->h_err_pinned[0] = 0;
+      ctx->h_err_pinned[1] = INT_MAX;
+      FC_CUDA(cudaMemcpyAsync(ctx->d_err, ctx->h_err_pinned, 2 * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+      fc::k_check_node_jacobians<fc::NURBS27><<<(n_ele + 127) / 128, 128, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_ele_gid, n_ele, ctx->d_dNtab,
+          ctx->d_ele_bad, ctx->d_err);
+      ctx->launches += 2;
+      FC_CUDA(cudaGetLastError());
+      FC_CUDA(cudaMemcpyAsync(ctx->h_err_pinned, ctx->d_err, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+      FC_CUDA(cudaStreamSynchronize(ctx->stream));
+      if (ctx->h_err_pinned[0] > 0)
+      {
+        ctx->geom_bad_count = ctx->h_err_pinned[0];
+        ctx->geom_first_bad_gid = ctx->h_err_pinned[1];
+      }
+    }
+    ctx->nurbs_ready = true;
+    if (int rc = fc_mulf_init(ctx)) return rc;
+    FC_CUDA(cudaStreamSynchronize(ctx->stream));
     return FC_OK;
   }
 }

@@ -202,6 +202,7 @@ namespace
         case FC_TET4: return launch_generic<fc::TET4, fc::FORM_LINEAR, WANT_K>(ctx, A);
         case FC_WEDGE6: return launch_generic<fc::WEDGE6, fc::FORM_LINEAR, WANT_K>(ctx, A);
         case FC_HEX18: return launch_generic<fc::HEX18, fc::FORM_LINEAR, WANT_K>(ctx, A);
+        case FC_NURBS27: return launch_generic<fc::NURBS27, fc::FORM_LINEAR, WANT_K>(ctx, A);
         default: return launch_generic<fc::PYRAMID5, fc::FORM_LINEAR, WANT_K>(ctx, A);
       }
     if (ctx->formulation == FC_FORM_EAS_MILD) return launch_hex8_eas<9, WANT_K>(ctx, A);
@@ -226,6 +227,7 @@ namespace
         case FC_TET4: return launch_generic<fc::TET4, fc::FORM_MULF, WANT_K>(ctx, A);
         case FC_WEDGE6: return launch_generic<fc::WEDGE6, fc::FORM_MULF, WANT_K>(ctx, A);
         case FC_HEX18: return launch_generic<fc::HEX18, fc::FORM_MULF, WANT_K>(ctx, A);
+        case FC_NURBS27: return launch_generic<fc::NURBS27, fc::FORM_MULF, WANT_K>(ctx, A);
         default: return launch_generic<fc::PYRAMID5, fc::FORM_MULF, WANT_K>(ctx, A);
       }
     const bool fbar = ctx->formulation == FC_FORM_FBAR;
@@ -241,6 +243,7 @@ namespace
     if (ctx->celltype == FC_TET4) return launch_generic<fc::TET4, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_WEDGE6) return launch_generic<fc::WEDGE6, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_HEX18) return launch_generic<fc::HEX18, fc::FORM_DISP, WANT_K>(ctx, A);
+    if (ctx->celltype == FC_NURBS27) return launch_generic<fc::NURBS27, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_PYRAMID5)
       return fbar ? launch_generic<fc::PYRAMID5, fc::FORM_FBAR, WANT_K>(ctx, A) : launch_generic<fc::PYRAMID5, fc::FORM_DISP, WANT_K>(ctx, A);
     const bool nh_gen = ctx->mat.kind == fc::MAT_NEOHOOKE && !fbar && !(flags & FC_EVAL_FORCE_GENERIC);
@@ -274,6 +277,7 @@ namespace
       case FC_TET4: FC_MULF_HISTORY(fc::TET4); break;
       case FC_WEDGE6: FC_MULF_HISTORY(fc::WEDGE6); break;
       case FC_HEX18: FC_MULF_HISTORY(fc::HEX18); break;
+      case FC_NURBS27: FC_MULF_HISTORY(fc::NURBS27); break;
       default: FC_MULF_HISTORY(fc::PYRAMID5); break;
     }
 #undef FC_MULF_HISTORY
@@ -352,6 +356,7 @@ int fc_mulf_init(fc_ctx* ctx)
     FC_CUDA(cudaGetLastError());
   }
   if (!mulf_records(ctx) || ctx->n_ele == 0) return FC_OK;
+  if (ctx->celltype == FC_NURBS27 && !ctx->nurbs_ready) return FC_OK;  // the history needs the element tables: fc_solid_set_nurbs calls again
   FC_CUDA(cudaMalloc((void**)&ctx->d_mulf, sizeof(double) * 18 * (size_t)ctx->n_ele * mulf_records(ctx)));
   FC_CUDA(launch_mulf_history(ctx, nullptr));
   return FC_OK;
@@ -374,6 +379,7 @@ extern "C"
   {
     if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede evaluate");
     if (!ctx->have_material) return fail(ctx, FC_ERR_INVALID, "set_material must precede evaluate");
+    if (ctx->celltype == FC_NURBS27 && !ctx->nurbs_ready) return fail(ctx, FC_ERR_INVALID, "nurbs27: fc_solid_set_nurbs must follow set_mesh");
     if (!u_col) return fail(ctx, FC_ERR_INVALID, "u_col is required");
     if (action != FC_ACTION_NLNSTIFF && action != FC_ACTION_INTERNALFORCE) return fail(ctx, FC_ERR_UNSUPPORTED, "action not on the path");
     const bool want_K = action == FC_ACTION_NLNSTIFF;
@@ -484,6 +490,7 @@ extern "C"
   int fc_solid_evaluate_elements(fc_ctx* ctx, const double* u_col, double* fe, double* Ke)
   {
     if (!ctx || ctx->celltype < 0 || !ctx->have_material || !u_col || !fe) return fail(ctx, FC_ERR_INVALID, "mesh, material, u_col and fe are required");
+    if (ctx->celltype == FC_NURBS27 && !ctx->nurbs_ready) return fail(ctx, FC_ERR_INVALID, "nurbs27: fc_solid_set_nurbs must follow set_mesh");
     FC_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = ctx->stream;
     const size_t nd = 3 * (size_t)ctx->nen, ne = (size_t)ctx->n_ele;
@@ -583,6 +590,7 @@ extern "C"
   {
     if (!ctx || ctx->celltype < 0 || !u_col) return fail(ctx, FC_ERR_INVALID, "mesh and u_col are required");
     if (!mulf_records(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF / FC_FORM_MULF_FBAR");
+    if (ctx->celltype == FC_NURBS27 && !ctx->nurbs_ready) return fail(ctx, FC_ERR_INVALID, "nurbs27: fc_solid_set_nurbs must follow set_mesh");
     if (ctx->n_ele == 0) return FC_OK;
     FC_CUDA(cudaSetDevice(ctx->device));
     double* t_u = nullptr;
@@ -606,6 +614,7 @@ extern "C"
     if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
     if (!mulf_records(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF / FC_FORM_MULF_FBAR");
     if (ctx->n_ele == 0) return FC_OK;
+    if (!ctx->d_mulf) return fail(ctx, FC_ERR_INVALID, "no prestress history yet (nurbs27: fc_solid_set_nurbs first)");
     FC_CUDA(cudaSetDevice(ctx->device));
     FC_CUDA(cudaMemcpyAsync(history, ctx->d_mulf, sizeof(double) * 18 * (size_t)ctx->n_ele * mulf_records(ctx), cudaMemcpyDefault, ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -617,6 +626,7 @@ extern "C"
     if (!ctx || ctx->celltype < 0 || !history) return fail(ctx, FC_ERR_INVALID, "mesh and history are required");
     if (!mulf_records(ctx)) return fail(ctx, FC_ERR_INVALID, "the mesh was not set with FC_FORM_MULF / FC_FORM_MULF_FBAR");
     if (ctx->n_ele == 0) return FC_OK;
+    if (!ctx->d_mulf) return fail(ctx, FC_ERR_INVALID, "no prestress history yet (nurbs27: fc_solid_set_nurbs first)");
     FC_CUDA(cudaSetDevice(ctx->device));
     FC_CUDA(cudaMemcpyAsync(ctx->d_mulf, history, sizeof(double) * 18 * (size_t)ctx->n_ele * mulf_records(ctx), cudaMemcpyDefault, ctx->stream));
     FC_CUDA(cudaStreamSynchronize(ctx->stream));

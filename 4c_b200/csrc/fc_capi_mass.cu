@@ -66,6 +66,21 @@ extern "C" int fc_solid_evaluate_mass(fc_ctx* ctx, double density, int flags, do
     case FC_WEDGE6: rc = mass_impl<fc::WEDGE6>(ctx, density, d_M); break;
     case FC_PYRAMID5: rc = mass_impl<fc::PYRAMID5>(ctx, density, d_M); break;
     case FC_HEX18: rc = mass_impl<fc::HEX18>(ctx, density, d_M); break;
+    case FC_NURBS27:
+    {
+      if (!ctx->nurbs_ready) return fail(ctx, FC_ERR_INVALID, "nurbs27: fc_solid_set_nurbs must follow set_mesh");
+      const long long nthreads = (long long)ctx->n_ele * 27;
+      if (nthreads > 0)
+      {
+        fc::k_mass_nurbs<<<(unsigned)((nthreads + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->n_ele, ctx->n_row_nodes,
+            ctx->d_dNtab, ctx->d_gpw, ctx->d_node_rowbase, ctx->d_node_rowlen, ctx->d_slots, density, d_M);
+        ctx->launches++;
+      }
+      FC_CUDA(cudaGetLastError());
+      FC_CUDA(cudaStreamSynchronize(ctx->stream));
+      rc = FC_OK;
+      break;
+    }
   }
   if (rc != FC_OK) return rc;
   if (!dev)

@@ -32,26 +32,37 @@ namespace
 
   // shared body: mode 0 = add the load into f_ext, 1 = hand out the Gauss-point reference coordinates
   int neumann_run(fc_ctx* ctx, bool surface, int face_type, int n_items, const int* items, const int* onoff, const double* val,
-      const double* gp_factor, double* out, bool coords)
+      const double* gp_factor, double* out, bool coords, const int* surface_id = nullptr /* faces of nurbs27: items = parent elements */)
   {
+    const bool nurbs_face = surface && surface_id != nullptr;
     if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede the Neumann evaluation");
     if (n_items < 0 || (n_items > 0 && !items) || !out) return fail(ctx, FC_ERR_INVALID, "item list and output are required");
-    if (surface && (face_type < FC_FACE_QUAD4 || face_type > FC_FACE_QUAD6))
+    if (surface && !nurbs_face && (face_type < FC_FACE_QUAD4 || face_type > FC_FACE_QUAD6))
       return fail(ctx, FC_ERR_UNSUPPORTED, "surface cell type");
+    if ((nurbs_face || (!surface && ctx->celltype == FC_NURBS27)) && (ctx->celltype != FC_NURBS27 || !ctx->nurbs_ready))
+      return fail(ctx, FC_ERR_INVALID, "nurbs27 mesh with fc_solid_set_nurbs required");
+    if (surface && !nurbs_face && ctx->celltype == FC_NURBS27)
+      return fail(ctx, FC_ERR_INVALID, "faces of nurbs27 elements: fc_solid_neumann_surface_nurbs");
     fc::NeumannVal V{};
     if (!coords)
       if (int rc = check_val(ctx, onoff, val, V)) return rc;
     FC_CUDA(cudaSetDevice(ctx->device));
-    const int per = surface ? fc::face_nen(face_type) : 1;
-    const int ngp = surface ? fc::face_ngp(face_type) : fc::cell_ngp(ctx->celltype);
+    const int per = surface && !nurbs_face ? fc::face_nen(face_type) : 1;
+    const int ngp = nurbs_face ? 9 : (surface ? fc::face_ngp(face_type) : fc::cell_ngp(ctx->celltype));
     for (size_t i = 0; i < (size_t)n_items * per; ++i)
-      if (items[i] < 0 || items[i] >= (surface ? ctx->n_col_nodes : ctx->n_ele)) return fail(ctx, FC_ERR_INVALID, surface ? "face node out of range" : "element out of range");
+      if (items[i] < 0 || items[i] >= (surface && !nurbs_face ? ctx->n_col_nodes : ctx->n_ele))
+        return fail(ctx, FC_ERR_INVALID, surface && !nurbs_face ? "face node out of range" : "element out of range");
+    if (nurbs_face)
+      for (int i = 0; i < n_items; ++i)
+        if (surface_id[i] < 0 || surface_id[i] > 5) return fail(ctx, FC_ERR_INVALID, "surface number of a nurbs27 element: 0..5");
     const size_t n_out = coords ? (size_t)n_items * ngp * 3 : (size_t)ctx->n_row_dof;
     if (n_items == 0) return FC_OK;
     const int* d_items = nullptr;
     int* t_items = nullptr;
     FC_CUDA(dev_upload(t_items, items, (size_t)n_items * per, ctx->stream));
     d_items = t_items;
+    int* t_sid = nullptr;
+    if (nurbs_face) FC_CUDA(dev_upload(t_sid, surface_id, (size_t)n_items, ctx->stream));
     const double* d_fac = nullptr;
     double* t_fac = nullptr;
     int rc = coords ? FC_OK : stage_in(ctx, gp_factor, (size_t)n_items * ngp * 3, &d_fac, &t_fac);
@@ -69,7 +80,10 @@ namespace
       const int bs = 128;
       double* f = coords ? nullptr : d_out;
       double* xc = coords ? d_out : nullptr;
-      if (surface)
+      if (nurbs_face)
+        fc::k_neumann_surface_nurbs<<<(unsigned)((n_items + bs - 1) / bs), bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_nurbs_knots,
+            ctx->d_nurbs_weights, d_items, t_sid, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
+      else if (surface)
       {
         const unsigned gs = (unsigned)((n_items + bs - 1) / bs);
 #define FC_NEUMANN_SURFACE(FT) fc::k_neumann_surface<FT><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc)
@@ -95,6 +109,8 @@ namespace
         if (ctx->celltype == FC_TET4) fc::k_neumann_volume<fc::TET4><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
         if (ctx->celltype == FC_WEDGE6) fc::k_neumann_volume<fc::WEDGE6><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
         if (ctx->celltype == FC_HEX18) fc::k_neumann_volume<fc::HEX18><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
+        if (ctx->celltype == FC_NURBS27)
+          fc::k_neumann_volume_nurbs<<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, ctx->d_dNtab, ctx->d_gpw, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
         if (ctx->celltype == FC_PYRAMID5) fc::k_neumann_volume<fc::PYRAMID5><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, ctx->d_conn, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc);
       }
       ctx->launches++;
@@ -104,6 +120,7 @@ namespace
     const cudaError_t es = cudaStreamSynchronize(ctx->stream);
     if (e == cudaSuccess) e = es;
     cudaFree(t_items);
+    if (t_sid) cudaFree(t_sid);
     if (t_fac) cudaFree(t_fac);
     if (t_out) cudaFree(t_out);
     if (rc != FC_OK) return rc;
@@ -133,5 +150,20 @@ extern "C"
   int fc_solid_neumann_volume_gp_coords(fc_ctx* ctx, int n_ele, const int* ele_lids, double* gp_coords)
   {
     return neumann_run(ctx, false, 0, n_ele, ele_lids, nullptr, nullptr, nullptr, gp_coords, true);
+  }
+
+  int fc_solid_neumann_surface_nurbs(fc_ctx* ctx, int n_faces, const int* parent_ele, const int* surface_id, const int* onoff,
+      const double* val, const double* gp_factor, double* f_ext)
+  {
+    if (n_faces > 0 && !surface_id) return fail(ctx, FC_ERR_INVALID, "surface_id is required");
+    static const int none = 0;
+    return neumann_run(ctx, true, -1, n_faces, parent_ele, onoff, val, gp_factor, f_ext, false, surface_id ? surface_id : &none);
+  }
+
+  int fc_solid_neumann_surface_nurbs_gp_coords(fc_ctx* ctx, int n_faces, const int* parent_ele, const int* surface_id, double* gp_coords)
+  {
+    if (n_faces > 0 && !surface_id) return fail(ctx, FC_ERR_INVALID, "surface_id is required");
+    static const int none = 0;
+    return neumann_run(ctx, true, -1, n_faces, parent_ele, nullptr, nullptr, nullptr, gp_coords, true, surface_id ? surface_id : &none);
   }
 }

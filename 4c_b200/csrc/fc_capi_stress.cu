@@ -183,6 +183,12 @@ namespace
       FC_CUDA(cudaGetLastError());
     }
     if (!d_nodal) return FC_OK;
+    if constexpr (CT == fc::NURBS27)
+      // the reference inverts the element's own basis at the Gauss points (evaluate_gauss_points_to_nurbs_knots_extrapolation_matrix,
+      // 4C_fem_general_utils_gauss_point_extrapolation.cpp:386-420): one 27 x 27 system per element, not built
+      return fail(ctx, FC_ERR_UNSUPPORTED, "nurbs27: Gauss-point output only, no extrapolation to the control points");
+    else
+    {
     std::vector<double> E;
     if (!extrapolation_matrix<CT>(E)) return fail(ctx, FC_ERR_INVALID, "singular Gauss point extrapolation matrix");
     std::vector<int> count((size_t)ctx->n_col_nodes, 0);
@@ -205,6 +211,7 @@ namespace
     cudaFree(d_count);
     FC_CUDA(e);
     return FC_OK;
+    }
   }
 }  // namespace
 
@@ -214,6 +221,7 @@ static int gp_output_run(fc_ctx* ctx, const double* u_col, int stress_type, doub
   if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede evaluate_stress");
   if (!ctx->have_material) return fail(ctx, FC_ERR_INVALID, "set_material must precede evaluate_stress");
   if (!u_col || (!gp_stress && !nodal_stress)) return fail(ctx, FC_ERR_INVALID, "u_col and one output are required");
+  if (ctx->celltype == FC_NURBS27 && !ctx->nurbs_ready) return fail(ctx, FC_ERR_INVALID, "nurbs27: fc_solid_set_nurbs must follow set_mesh");
   FC_CUDA(cudaSetDevice(ctx->device));
   cudaStream_t s = ctx->stream;
   const int ngp = fc::cell_ngp(ctx->celltype);
@@ -273,6 +281,7 @@ static int gp_output_run(fc_ctx* ctx, const double* u_col, int stress_type, doub
     case FC_TET4: FC_STRESS(fc::TET4); break;
     case FC_WEDGE6: FC_STRESS(fc::WEDGE6); break;
     case FC_HEX18: FC_STRESS(fc::HEX18); break;
+    case FC_NURBS27: FC_STRESS(fc::NURBS27); break;
     case FC_PYRAMID5:
       if (mulf_fbar)
         rc = stress_impl<fc::PYRAMID5, fc::FORM_MULF_FBAR>(ctx, A, stress_type, d_gp, d_nodal);

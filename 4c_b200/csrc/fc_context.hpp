@@ -49,6 +49,10 @@ struct fc_ctx
   int* d_ele_gid = nullptr;  // [n_ele]
   double* d_dNtab = nullptr; // [ngp + nen + 1][nen][3]: Gauss points, node positions, centroid
   double* d_gpw = nullptr;   // [ngp] weights
+  // nurbs27 (fc_nurbs.cuh): d_dNtab holds one table per element, built by fc_solid_set_nurbs from
+  double* d_nurbs_knots = nullptr;    // [n_ele][3][6] knot spans of the elements and
+  double* d_nurbs_weights = nullptr;  // [n_col_nodes] control point weights
+  bool nurbs_ready = false;
   unsigned char* d_ele_bad = nullptr;  // [n_ele] 1 = det J <= 0 at an element node
   int* d_ele_perm = nullptr; // element order of the tensor-core assembled-path kernels (L2 sweep order, fc_sweep_order.hpp) or nullptr = caller's order
   int n_interior_ele = 0;    // launch slots [0, n_interior_ele) hold the elements without ghost nodes (FC_EVAL_INTERIOR / _BOUNDARY)

@@ -32,7 +32,8 @@ namespace fc
     TET4 = 4,
     WEDGE6 = 5,
     PYRAMID5 = 6,
-    HEX18 = 7  // quad9 in (r, s) x line2 in t: nodes 0-8 at t = -1 (corners, edge mids, centre), 9-17 at t = +1
+    HEX18 = 7,  // quad9 in (r, s) x line2 in t: nodes 0-8 at t = -1 (corners, edge mids, centre), 9-17 at t = +1
+    NURBS27 = 8  // 3 x 3 x 3 control points, u fastest; shape functions per element from its knot spans and weights (fc_nurbs.cuh)
   };
 
   template <int CT>
@@ -80,6 +81,12 @@ namespace fc
     static constexpr int nen = 18, ngp = 18;  // hex_18point = quad_9point x line_2point
   };
 
+  template <>
+  struct Cell<NURBS27>
+  {
+    static constexpr int nen = 27, ngp = 27;  // hex_27point (4C_fem_general_element_integration_select.hpp:89-92)
+  };
+
   FC_HD int cell_nen(int ct)
   {
     switch (ct)
@@ -91,6 +98,7 @@ namespace fc
       case TET4: return Cell<TET4>::nen;
       case WEDGE6: return Cell<WEDGE6>::nen;
       case HEX18: return Cell<HEX18>::nen;
+      case NURBS27: return Cell<NURBS27>::nen;
       default: return Cell<PYRAMID5>::nen;
     }
   }
@@ -105,6 +113,7 @@ namespace fc
       case TET4: return Cell<TET4>::ngp;
       case WEDGE6: return Cell<WEDGE6>::ngp;
       case HEX18: return Cell<HEX18>::ngp;
+      case NURBS27: return Cell<NURBS27>::ngp;
       default: return Cell<PYRAMID5>::ngp;
     }
   }
@@ -133,6 +142,14 @@ namespace fc
 
   FC_HD void node_param_coords(int ct, int a, double* xi)
   {
+    if (ct == NURBS27)
+    {
+      // eleNodeNumbering_nurbs27_nodes_reference, 4C_fem_general_utils_local_connectivity_matrices.hpp:305-314
+      xi[0] = (double)(a % 3 - 1);
+      xi[1] = (double)((a / 3) % 3 - 1);
+      xi[2] = (double)(a / 9 - 1);
+      return;
+    }
     if (ct == HEX18)
     {
       // eleNodeNumbering_hex18_nodes_reference, 4C_fem_general_utils_local_connectivity_matrices.hpp:175-180
@@ -170,6 +187,7 @@ namespace fc
   template <int CT>
   FC_HD void shape_deriv1(const double* xi, double* dN)
   {
+    static_assert(CT != NURBS27, "nurbs27 has no parameter-space shape functions of its own: element tables, fc_nurbs.cuh");
     const double r = xi[0], s = xi[1], t = xi[2];
     if constexpr (CT == HEX8)
     {
@@ -282,6 +300,7 @@ namespace fc
   template <int CT>
   FC_HD void shape_function(const double* xi, double* N)
   {
+    static_assert(CT != NURBS27, "nurbs27 has no parameter-space shape functions of its own: element tables, fc_nurbs.cuh");
     const double r = xi[0], s = xi[1], t = xi[2];
     if constexpr (CT == HEX8)
     {
@@ -402,7 +421,7 @@ namespace fc
       xi[2] = g < 9 ? -0.5773502691896 : 0.5773502691896;
       *w = (sr == 0 ? w2 : w1) * (ss == 0 ? w2 : w1);
     }
-    else if constexpr (CT == HEX27 || CT == HEX20)
+    else if constexpr (CT == HEX27 || CT == HEX20 || CT == NURBS27)
     {
       // the reference's truncated 13-digit constants (integration.cpp:133,214-215)
       const double p = 0.7745966692415, w1 = 0.5555555555556, w2 = 0.8888888888889;

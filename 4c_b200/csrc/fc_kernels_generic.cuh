@@ -14,6 +14,7 @@
 //            4C_linalg_sparsematrix.cpp:474) with fire-and-forget FP64 reductions
 #pragma once
 #include "fc_kernels_common.cuh"
+#include "fc_nurbs.cuh"
 
 namespace fc
 {
@@ -70,8 +71,8 @@ namespace fc
   {
     static constexpr int nen = Cell<CT>::nen;
     static constexpr int ngp = Cell<CT>::ngp;
-    // elements per CTA and column nodes per register chunk, indexed by cell type (hex8, hex27, tet10, hex20, tet4, wedge6, pyramid5)
-    static constexpr int epb_tab[8] = {8, 4, 12, 4, 32, 16, 16, 4}, bch_tab[8] = {4, 9, 5, 5, 4, 3, 5, 6};
+    // elements per CTA and column nodes per register chunk, indexed by cell type (hex8, hex27, tet10, hex20, tet4, wedge6, pyramid5, hex18, nurbs27)
+    static constexpr int epb_tab[9] = {8, 4, 12, 4, 32, 16, 16, 4, 4}, bch_tab[9] = {4, 9, 5, 5, 4, 3, 5, 6, 9};
     static constexpr int epb = epb_tab[CT], bch = bch_tab[CT];
     static constexpr int threads = epb * nen;
     // per-Gauss-point record: F(9) N_XYZ(3 nen) cmat(36) S(6) fac_mat fac_geo fac_force pad [H(3 nen) v(6)]
@@ -96,7 +97,7 @@ namespace fc
     const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= (long long)n_ele * nrec) return;
     const int e = (int)(tid / nrec), gp = (int)(tid % nrec);
-    const double* dN = dNtab + (size_t)(gp < NGP ? gp : NGP + NEN) * NEN * 3;
+    const double* dN = ele_table<CT>(dNtab, e) + (size_t)(gp < NGP ? gp : NGP + NEN) * NEN * 3;
     double* H = hist + (size_t)tid * 18;
     if (!u)
     {
@@ -242,13 +243,13 @@ namespace fc
       if (form_fbar(FORM))
       {
         double F0[9];
-        jacobian_mapping<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, Xs, N0);
+        jacobian_mapping<NEN>(ele_table<CT>(A.dNtab, e) + (size_t)(NGP + NEN) * ND, Xs, N0);
         if (FORM == FORM_MULF_FBAR)
         {
           // MulfFBarFormulation::prepare: N_XYZ_0 of the reference Jacobian, F_0 from the centroid's history record
           double hl[18], delta[9];
           mulf_load(A.mulf + ((size_t)e * NREC + NGP) * 18, hl);
-          mulf_delta<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, us, hl, delta);
+          mulf_delta<NEN>(ele_table<CT>(A.dNtab, e) + (size_t)(NGP + NEN) * ND, us, hl, delta);
           mat3_mul(delta, hl + 9, F0);
         }
         else
@@ -259,7 +260,7 @@ namespace fc
       {
         double* R = gpdat + (size_t)gp * GPD;
         double* Nx = R + Cfg::oN;
-        const double detJ = jacobian_mapping<NEN>(A.dNtab + (size_t)gp * ND, Xs, Nx);
+        const double detJ = jacobian_mapping<NEN>(ele_table<CT>(A.dNtab, e) + (size_t)gp * ND, Xs, Nx);
         double F[9];
         if (form_mulf(FORM))
         {
@@ -267,7 +268,7 @@ namespace fc
           const double* hist = A.mulf + ((size_t)e * NREC + gp) * 18;
           double hl[18], delta[9];
           mulf_load(hist, hl);
-          mulf_delta<NEN>(A.dNtab + (size_t)gp * ND, us, hl, delta);
+          mulf_delta<NEN>(ele_table<CT>(A.dNtab, e) + (size_t)gp * ND, us, hl, delta);
           mat3_mul(delta, hl + 9, F);
         }
         else

@@ -9,6 +9,7 @@
 #pragma once
 #include "fc_fem_surface.cuh"
 #include "fc_kernels_common.cuh"
+#include "fc_nurbs.cuh"
 
 namespace fc
 {
@@ -76,6 +77,121 @@ namespace fc
       if (nodes[a] < n_row_nodes)
         for (int dof = 0; dof < 3; ++dof)
           if (V.onoff[dof]) red_add(f + 3 * (size_t)nodes[a] + dof, fa[a][dof]);
+  }
+
+  // Faces of nurbs27 elements (nurbs9, quad_9point): one thread per face, named by parent element and surface number like the
+  // reference's surface element; its knot vectors are two of the parent's knot spans
+  // (Knotvector::get_boundary_ele_and_parent_knots, 4C_fem_nurbs_discretization_knotvector.cpp:265-413).
+  static __global__ void k_neumann_surface_nurbs(const double* __restrict__ X, const int* __restrict__ conn, const double* __restrict__ ele_knots,
+      const double* __restrict__ node_weights, const int* __restrict__ parent, const int* __restrict__ surface, int n_faces, NeumannVal V,
+      const double* __restrict__ gp_factor, int n_row_nodes, double* __restrict__ f, double* __restrict__ gp_coords)
+  {
+    const int face = blockIdx.x * blockDim.x + threadIdx.x;
+    if (face >= n_faces) return;
+    // eleNodeNumbering_nurbs27_surfaces, 4C_fem_general_utils_local_connectivity_matrices.hpp:250-253
+    const unsigned char fn[6][9] = {{0, 1, 2, 3, 4, 5, 6, 7, 8}, {18, 19, 20, 21, 22, 23, 24, 25, 26}, {0, 1, 2, 9, 10, 11, 18, 19, 20},
+        {6, 7, 8, 15, 16, 17, 24, 25, 26}, {2, 5, 8, 11, 14, 17, 20, 23, 26}, {0, 3, 6, 9, 12, 15, 18, 21, 24}};
+    const int e = parent[face], sid = surface[face];
+    const int d0 = sid < 4 ? 0 : 1, d1 = sid < 2 ? 1 : 2;
+    double kn[12], w[9], P[9][3], fa[9][3];
+    int nodes[9];
+    for (int k = 0; k < 6; ++k)
+    {
+      kn[k] = ele_knots[(size_t)e * 18 + 6 * d0 + k];
+      kn[6 + k] = ele_knots[(size_t)e * 18 + 6 * d1 + k];
+    }
+    for (int a = 0; a < 9; ++a)
+    {
+      nodes[a] = conn[(size_t)e * 27 + fn[sid][a]];
+      w[a] = node_weights[nodes[a]];
+      for (int i = 0; i < 3; ++i)
+      {
+        P[a][i] = X[3 * (size_t)nodes[a] + i];
+        fa[a][i] = 0.0;
+      }
+    }
+    for (int g = 0; g < 9; ++g)
+    {
+      double rs[2], gw, N[9], dN[18];
+      face_gauss_point(QUAD9, g, rs, &gw);
+      nurbs_funct_deriv<2>(rs, kn, w, N, dN);
+      if (gp_coords)
+      {
+        for (int i = 0; i < 3; ++i)
+        {
+          double x = 0.0;
+          for (int a = 0; a < 9; ++a) x += N[a] * P[a][i];
+          gp_coords[((size_t)face * 9 + g) * 3 + i] = x;
+        }
+        continue;
+      }
+      double g1[3] = {0, 0, 0}, g2[3] = {0, 0, 0};
+      for (int a = 0; a < 9; ++a)
+        for (int i = 0; i < 3; ++i)
+        {
+          g1[i] += dN[2 * a] * P[a][i];
+          g2[i] += dN[2 * a + 1] * P[a][i];
+        }
+      const double m11 = g1[0] * g1[0] + g1[1] * g1[1] + g1[2] * g1[2];
+      const double m22 = g2[0] * g2[0] + g2[1] * g2[1] + g2[2] * g2[2];
+      const double m12 = g1[0] * g2[0] + g1[1] * g2[1] + g1[2] * g2[2];
+      const double detA = sqrt(m11 * m22 - m12 * m12);
+      for (int dof = 0; dof < 3; ++dof)
+      {
+        if (!V.onoff[dof]) continue;
+        const double functfac = gp_factor ? gp_factor[((size_t)face * 9 + g) * 3 + dof] : 1.0;
+        const double fac = gw * detA * V.val[dof] * functfac;
+        for (int a = 0; a < 9; ++a) fa[a][dof] += N[a] * fac;
+      }
+    }
+    if (gp_coords) return;
+    for (int a = 0; a < 9; ++a)
+      if (nodes[a] < n_row_nodes)
+        for (int dof = 0; dof < 3; ++dof)
+          if (V.onoff[dof]) red_add(f + 3 * (size_t)nodes[a] + dof, fa[a][dof]);
+  }
+
+  // body loads on nurbs27 elements: N and dN of the Gauss point from the element's table (fc_nurbs.cuh)
+  static __global__ void k_neumann_volume_nurbs(const double* __restrict__ X, const int* __restrict__ conn, const double* __restrict__ tab,
+      const double* __restrict__ gpw, const int* __restrict__ ele_list, int n_list, NeumannVal V, const double* __restrict__ gp_factor,
+      int n_row_nodes, double* __restrict__ f, double* __restrict__ gp_coords)
+  {
+    constexpr int NEN = 27, NGP = 27;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= (long long)n_list * NGP) return;
+    const int item = (int)(tid / NGP), g = (int)(tid % NGP);
+    const int e = ele_list[item];
+    const double* T = tab + (size_t)e * NurbsTab::stride;
+    const double* N = T + NurbsTab::oN + g * NEN;
+    const double* dN = T + (size_t)g * NEN * 3;
+    double J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, xg[3] = {0, 0, 0};
+    for (int a = 0; a < NEN; ++a)
+    {
+      const int n = conn[(size_t)e * NEN + a];
+      for (int i = 0; i < 3; ++i)
+      {
+        const double x = X[3 * (size_t)n + i];
+        xg[i] += N[a] * x;
+        for (int d = 0; d < 3; ++d) J[3 * d + i] += dN[3 * a + d] * x;
+      }
+    }
+    if (gp_coords)
+    {
+      for (int i = 0; i < 3; ++i) gp_coords[((size_t)item * NGP + g) * 3 + i] = xg[i];
+      return;
+    }
+    const double intfac = gpw[g] * det3(J);
+    for (int dof = 0; dof < 3; ++dof)
+    {
+      if (!V.onoff[dof]) continue;
+      const double functfac = gp_factor ? gp_factor[((size_t)item * NGP + g) * 3 + dof] : 1.0;
+      const double vif = V.val[dof] * functfac * intfac;
+      for (int a = 0; a < NEN; ++a)
+      {
+        const int n = conn[(size_t)e * NEN + a];
+        if (n < n_row_nodes) red_add(f + 3 * (size_t)n + dof, N[a] * vif);
+      }
+    }
   }
 
   // one thread per (listed element, Gauss point)

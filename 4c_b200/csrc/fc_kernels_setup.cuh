@@ -1,6 +1,7 @@
 // One-off setup kernels: node-Jacobian check, scatter slot map, halo pack.
 #pragma once
 #include "fc_kernels_common.cuh"
+#include "fc_nurbs.cuh"
 
 namespace fc
 {
@@ -18,7 +19,7 @@ namespace fc
     bool bad = false;
     for (int p = 0; p < NEN; ++p)
     {
-      const double* dN = dNtab + (size_t)(NGP + p) * NEN * 3;
+      const double* dN = ele_table<CT>(dNtab, e) + (size_t)(NGP + p) * NEN * 3;
       double J[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
       for (int a = 0; a < NEN; ++a)
       {

@@ -142,14 +142,14 @@ namespace fc
       }
     }
     double Nx[ND], F[9];
-    jacobian_mapping<NEN>(A.dNtab + (size_t)gp * ND, Xs, Nx);
+    jacobian_mapping<NEN>(ele_table<CT>(A.dNtab, e) + (size_t)gp * ND, Xs, Nx);
     constexpr int NREC = mulf_records(NGP, FORM);
     if (form_mulf(FORM))
     {
       const double* hist = A.mulf + ((size_t)e * NREC + gp) * 18;
       double hl[18], delta[9];
       mulf_load(hist, hl);
-      mulf_delta<NEN>(A.dNtab + (size_t)gp * ND, us, hl, delta);
+      mulf_delta<NEN>(ele_table<CT>(A.dNtab, e) + (size_t)gp * ND, us, hl, delta);
       mat3_mul(delta, hl + 9, F);
     }
     else
@@ -161,12 +161,12 @@ namespace fc
       {
         double hl[18], delta[9];
         mulf_load(A.mulf + ((size_t)e * NREC + NGP) * 18, hl);
-        mulf_delta<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, us, hl, delta);
+        mulf_delta<NEN>(ele_table<CT>(A.dNtab, e) + (size_t)(NGP + NEN) * ND, us, hl, delta);
         mat3_mul(delta, hl + 9, F0);
       }
       else
       {
-        jacobian_mapping<NEN>(A.dNtab + (size_t)(NGP + NEN) * ND, Xs, N0);
+        jacobian_mapping<NEN>(ele_table<CT>(A.dNtab, e) + (size_t)(NGP + NEN) * ND, Xs, N0);
         deformation_gradient<CT>(Xs, us, N0, F0);
       }
       const double fbar = pow(det3(F0) / det3(F), 1.0 / 3.0);

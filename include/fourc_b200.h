@@ -58,7 +58,8 @@ extern "C"
     FC_TET4 = 4,    /* stiffness tet_1point, mass tet_4point */
     FC_WEDGE6 = 5,  /* wedge_6point */
     FC_PYRAMID5 = 6, /* pyramid_8point; F-bar allowed (4C_solid_3D_ele_factory.hpp:49-50) */
-    FC_HEX18 = 7     /* quad9 x line2 (18 nodes, hex_18point); faces quad9 (bottom, top) and quad6 (sides) */
+    FC_HEX18 = 7,    /* quad9 x line2 (18 nodes, hex_18point); faces quad9 (bottom, top) and quad6 (sides) */
+    FC_NURBS27 = 8   /* 3 x 3 x 3 control points, u fastest (hex_27point); needs fc_solid_set_nurbs after fc_solid_set_mesh */
   };
   /* element technology (TECH none | fbar): src/solid_3D_ele/4C_solid_3D_ele.cpp:71-138 */
   enum
@@ -142,6 +143,13 @@ extern "C"
    * on the device (the result only depends on X); a failure is reported by every evaluate. */
   int fc_solid_set_mesh(fc_ctx* ctx, int celltype, int formulation, int n_col_nodes, const double* X,
       const int* node_gid, const int* node_owner, int n_col_ele, const int* conn, const int* ele_gid);
+  /* FC_NURBS27 meshes: what Core::FE::Nurbs::get_my_nurbs_knots_and_weights gives every element evaluation
+   * (4C_solid_3D_ele_calc_lib.hpp:193-200): ele_knots [n_col_ele][3][6] = the element's knot span per direction
+   * (Knotvector::get_ele_knots, 4C_fem_nurbs_discretization_knotvector.cpp:173-243), node_weights [n_col_nodes] = the control
+   * point weights (host arrays).  Builds the per-element shape tables once (the basis depends on the mesh only), then runs the
+   * node-Jacobian check and the initial prestress history that set_mesh postpones for this cell; evaluations before this call
+   * return FC_ERR_INVALID, an element with a zero-sized knot span is refused like the reference refuses it. */
+  int fc_solid_set_nurbs(fc_ctx* ctx, const double* ele_knots, const double* node_weights);
 
   int fc_solid_set_material(fc_ctx* ctx, int kind, const double* params, int n_params);
 
@@ -267,6 +275,14 @@ extern "C"
       double* f_ext);
   int fc_solid_neumann_surface_gp_coords(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, double* gp_coords);
   int fc_solid_neumann_volume_gp_coords(fc_ctx* ctx, int n_ele, const int* ele_lids, double* gp_coords);
+  /* Surface loads on faces of nurbs27 elements (nurbs9, quad_9point): a face is named like the reference's surface element
+   * names it - by its parent column element and the parent's surface number 0..5 (eleNodeNumbering_nurbs27_surfaces,
+   * 4C_fem_general_utils_local_connectivity_matrices.hpp:250-253) - because its two knot vectors come from the parent's
+   * knot spans (Knotvector::get_boundary_ele_and_parent_knots, 4C_fem_nurbs_discretization_knotvector.cpp:251-420;
+   * 4C_solid_3D_ele_surface_evaluate.cpp:190-256).  parent_ele [n_faces], surface_id [n_faces]; everything else as above. */
+  int fc_solid_neumann_surface_nurbs(fc_ctx* ctx, int n_faces, const int* parent_ele, const int* surface_id, const int* onoff,
+      const double* val, const double* gp_factor, double* f_ext);
+  int fc_solid_neumann_surface_nurbs_gp_coords(fc_ctx* ctx, int n_faces, const int* parent_ele, const int* surface_id, double* gp_coords);
 
   /* struct_calc_stress post-processing: Gauss-point stresses (calculate_stress,
    * 4C_solid_3D_ele_calc.cpp:347-390; Cauchy = F S F^T / det F, 4C_solid_3D_ele_utils.cpp:20-33) and their extrapolation

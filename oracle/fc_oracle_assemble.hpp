@@ -140,6 +140,7 @@ namespace fc_oracle
     {
       const int e = mesh.ele_index.at(eg);
       const int* en = &mesh.ele_nodes[(size_t)e * nen];
+      const NurbsScope nurbs(mesh, (size_t)e);
       // location vector: node-major x,y,z; owner of a dof = owner of its node (element.cpp:474-541)
       for (int a = 0; a < nen; ++a)
       {

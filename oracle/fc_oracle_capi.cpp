@@ -197,6 +197,25 @@ extern "C"
     return js;
   }
   void oracle_job_destroy(void* h) { delete (JobState*)h; }
+  // nurbs27 meshes: knots [n_ele][3][6] in the mesh's element order, weights [n_nodes] parallel to node_gid [n_nodes]
+  void oracle_job_set_nurbs(void* h, const double* knots, int n_nodes, const int* node_gid, const double* weights)
+  {
+    auto* js = (JobState*)h;
+    Mesh& m = js->job.mesh;
+    m.nurbs_knots.assign(knots, knots + 18 * m.ele_gid.size());
+    m.nurbs_weights.assign(m.node_gid.size(), 1.0);
+    for (int i = 0; i < n_nodes; ++i) m.nurbs_weights[(size_t)m.node_index.at(node_gid[i])] = weights[i];
+  }
+  // unit-level calls on one nurbs27 element / nurbs9 face (oracle_shape, oracle_element_evaluate, oracle_neumann_*): the knots
+  // ([3][6] or [2][6]) and weights ([27] or [9]) that the following calls of this thread use
+  void oracle_set_nurbs_element(const double* knots, int n_knots, const double* weights, int n_weights)
+  {
+    static thread_local double kn[18], w[27];
+    std::copy(knots, knots + n_knots, kn);
+    std::copy(weights, weights + n_weights, w);
+    nurbs_context().knots = kn;
+    nurbs_context().weights = w;
+  }
   // FORM_MULF: history of every element as MulfFormulation holds it before the first prestress update
   static void mulf_init(JobState* js)
   {
@@ -224,6 +243,7 @@ extern "C"
     {
       for (int a = 0; a < m.nen; ++a)
         for (int i = 0; i < 3; ++i) X[3 * a + i] = m.node_X[3 * (size_t)m.node_index.at(m.ele_nodes[e * m.nen + a]) + i];
+      const NurbsScope nurbs(m, e);
       mulf_history(m.ct, X.data(), nullptr, &js->job.mulf_hist[(size_t)18 * ngp * e], js->job.form == FORM_MULF_FBAR);
     }
   }
@@ -253,6 +273,7 @@ extern "C"
           u[3 * a + i] = u_nodes[3 * ni + i];
         }
       }
+      const NurbsScope nurbs(m, e);
       mulf_history(m.ct, X.data(), u.data(), &js->job.mulf_hist[(size_t)18 * ngp * e], js->job.form == FORM_MULF_FBAR);
     }
   }
@@ -328,6 +349,7 @@ extern "C"
       }
     }
     const Job& job = js->job;
+    const NurbsScope nurbs(m, (size_t)e);
     const double* fib = job.ele_fiber.empty() ? nullptr : job.ele_fiber.data() + (job.fiber_gp_stride ? (size_t)job.fiber_gp_stride * ngp : 3) * (size_t)e;
     if (job.form == FORM_SHELL_ANS || job.form == FORM_SHELL_EAS_ANS)
     {

@@ -483,6 +483,7 @@ namespace fc_oracle
       case WEDGE6: return mulf_history_t<6, 6>(ct, X, u, hist, centroid);
       case PYRAMID5: return mulf_history_t<5, 8>(ct, X, u, hist, centroid);
       case HEX18: return mulf_history_t<18, 18>(ct, X, u, hist, centroid);
+      case NURBS27: return mulf_history_t<27, 27>(ct, X, u, hist, centroid);
     }
   }
 
@@ -508,6 +509,8 @@ namespace fc_oracle
         return element_evaluate_t<5, 8>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
       case HEX18:
         return element_evaluate_t<18, 18>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
+      case NURBS27:  // knots and weights of the element: nurbs_context()
+        return element_evaluate_t<27, 27>(ct, form, mp, X, u, fe, Ke, Me, rho, gp_stress, stress_type, fiber, fiber_gp_stride, mulf_hist);
     }
     return -1;
   }

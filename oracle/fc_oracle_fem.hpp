@@ -17,6 +17,8 @@
 #pragma once
 #include <cmath>
 
+#include "fc_oracle_nurbs.hpp"
+
 namespace fc_oracle
 {
   enum CellType
@@ -28,17 +30,18 @@ namespace fc_oracle
     TET4 = 4,
     WEDGE6 = 5,
     PYRAMID5 = 6,
-    HEX18 = 7
+    HEX18 = 7,
+    NURBS27 = 8  // needs the element's knots and weights: nurbs_context(), fc_oracle_nurbs.hpp
   };
 
   inline int num_nodes(int ct)
   {
-    static const int n[8] = {8, 27, 10, 20, 4, 6, 5, 18};
+    static const int n[9] = {8, 27, 10, 20, 4, 6, 5, 18, 27};
     return n[ct];
   }
   inline int num_gp(int ct)
   {
-    static const int n[8] = {8, 27, 4, 27, 1, 6, 8, 18};
+    static const int n[9] = {8, 27, 4, 27, 1, 6, 8, 18, 27};
     return n[ct];
   }
 
@@ -57,7 +60,9 @@ namespace fc_oracle
     static const double pyramid[5][3] = {{-1, -1, 0}, {1, -1, 0}, {1, 1, 0}, {-1, 1, 0}, {0, 0, 1}};
     // hex18 (4C_fem_general_utils_local_connectivity_matrices.hpp:175-180): the quad9 pattern at t = -1, then at t = +1
     static const signed char q9[9][2] = {{-1, -1}, {1, -1}, {1, 1}, {-1, 1}, {0, -1}, {1, 0}, {0, 1}, {-1, 0}, {0, 0}};
-    if (ct == HEX18)
+    if (ct == NURBS27)
+      nurbs27_node_param(a, xi);
+    else if (ct == HEX18)
     {
       xi[0] = q9[a % 9][0];
       xi[1] = q9[a % 9][1];
@@ -95,7 +100,9 @@ namespace fc_oracle
   inline void shape_function(int ct, const double* xi, double* N)
   {
     const double r = xi[0], s = xi[1], t = xi[2];
-    if (ct == HEX8)
+    if (ct == NURBS27)
+      nurbs_funct_deriv<3>(xi, nurbs_context().knots, nurbs_context().weights, N, nullptr);
+    else if (ct == HEX8)
     {
       const double Q18 = 1.0 / 8.0;
       const double rp = 1.0 + r, rm = 1.0 - r, sp = 1.0 + s, sm = 1.0 - s, tp = 1.0 + t,
@@ -207,7 +214,9 @@ namespace fc_oracle
   inline void shape_function_deriv1(int ct, const double* xi, double* dN)
   {
     const double r = xi[0], s = xi[1], t = xi[2];
-    if (ct == HEX8)
+    if (ct == NURBS27)
+      nurbs_funct_deriv<3>(xi, nurbs_context().knots, nurbs_context().weights, nullptr, dN);
+    else if (ct == HEX8)
     {
       const double Q18 = 1.0 / 8.0;
       const double rp = 1.0 + r, rm = 1.0 - r, sp = 1.0 + s, sm = 1.0 - s, tp = 1.0 + t,
@@ -384,7 +393,7 @@ namespace fc_oracle
         w[g] = 1.0 * ((x[0] == 0 ? w2 : w1) * (x[1] == 0 ? w2 : w1));
       }
     }
-    else if (ct == HEX27 || ct == HEX20)
+    else if (ct == HEX27 || ct == HEX20 || ct == NURBS27)  // nurbs27: hex_27point too (integration_select.hpp:89-92)
     {
       // the reference hard-codes truncated constants (integration.cpp:133,214-215)
       const double xi3 = 0.7745966692415;

@@ -30,6 +30,8 @@ namespace fc_oracle
     std::unordered_map<int, int> node_index;  // gid -> position in node_gid
     std::unordered_map<int, int> ele_index;
     int min_node_gid = 0;
+    // nurbs27: the element's knot spans [n_ele][3][6] (Knotvector::get_ele_knots) and the control point weights, one per node
+    std::vector<double> nurbs_knots, nurbs_weights;
 
     void finalize()
     {
@@ -43,6 +45,20 @@ namespace fc_oracle
     }
     // dofset.cpp:344-352 with count = 0 and maxnodenumdf = 3
     int dof_gid(int node_gid_, int j) const { return (node_gid_ - min_node_gid) * 3 + j; }
+  };
+
+  // makes element e (index in the mesh's element order) the current NURBS element of this thread for its lifetime
+  struct NurbsScope
+  {
+    double w[27];
+    NurbsScope(const Mesh& m, size_t e)
+    {
+      if (m.ct != NURBS27) return;
+      for (int a = 0; a < 27; ++a) w[a] = m.nurbs_weights[(size_t)m.node_index.at(m.ele_nodes[e * 27 + a])];
+      nurbs_context().knots = &m.nurbs_knots[18 * e];
+      nurbs_context().weights = w;
+    }
+    ~NurbsScope() { nurbs_context() = NurbsContext{}; }
   };
 
   struct Partition

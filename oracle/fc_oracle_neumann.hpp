@@ -26,23 +26,36 @@ namespace fc_oracle
     TRI6 = 2,
     QUAD8 = 3,
     TRI3 = 4,
-    QUAD6 = 5
+    QUAD6 = 5,
+    NURBS9 = 6  // faces of nurbs27: knots [2][6] and weights [9] of the face in nurbs_context() (fc_oracle_nurbs.hpp);
+                // 4C_solid_3D_ele_surface_evaluate.cpp:190-256, quad_9point like quad9 (4C_solid_3D_ele_surface.cpp:68-71)
   };
   inline int face_num_nodes(int ft)
   {
-    static const int n[6] = {4, 9, 6, 8, 3, 6};
+    static const int n[7] = {4, 9, 6, 8, 3, 6, 9};
     return n[ft];
   }
   inline int face_num_gp(int ft)
   {
-    static const int n[6] = {4, 9, 6, 9, 3, 6};
+    static const int n[7] = {4, 9, 6, 9, 3, 6, 9};
     return n[ft];
   }
 
   // shape_function_2d / shape_function_2d_deriv1
   inline void shape_function_2d(int ft, double r, double s, double* funct, double* deriv_r, double* deriv_s)
   {
-    if (ft == QUAD4)
+    if (ft == NURBS9)
+    {
+      const double uv[2] = {r, s};
+      double d[18];
+      nurbs_funct_deriv<2>(uv, nurbs_context().knots, nurbs_context().weights, funct, d);
+      for (int a = 0; a < 9; ++a)
+      {
+        deriv_r[a] = d[2 * a];
+        deriv_s[a] = d[2 * a + 1];
+      }
+    }
+    else if (ft == QUAD4)
     {
       const double rp = 1.0 + r, rm = 1.0 - r, sp = 1.0 + s, sm = 1.0 - s;
       funct[0] = 0.25 * rm * sm;
@@ -214,7 +227,7 @@ namespace fc_oracle
         qwgt[i] = (i % 3 == 2) ? b : a;
       }
     }
-    else if (ft == QUAD9 || ft == QUAD8)
+    else if (ft == QUAD9 || ft == QUAD8 || ft == NURBS9)
     {
       const double g = 0.7745966692415, a = 0.5555555555556, b = 0.8888888888889;
       const double p[9][2] = {{-g, -g}, {g, -g}, {g, g}, {-g, g}, {0.0, -g}, {g, 0.0}, {0.0, g}, {-g, 0.0}, {0.0, 0.0}};

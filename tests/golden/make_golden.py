@@ -93,6 +93,10 @@ CASES = [
     "sohex8_easmild_cooks_nl.dat",
     # 125 eas_full elements, St.Venant-Kirchhoff nu = 0.4999, symmetry planes with LINE Dirichlet conditions that override the
     # surface ones; patch tests with a POINT condition
+    # nurbs27: one element and a 2 x 3 x 4 patch (control points with weights, STRUCTURE KNOTVECTORS)
+    "solid_ele_nurbs27_Standard_Static.dat",
+    "solid_ele_nurbs27_Standard_Static_multielement.dat",  # no RESULT DESCRIPTION: CUDA against oracle only
+    "solid_runtime_nurbs.dat",  # two curved patches (17 elements), weights != 1, three load steps
     "sohex8_incompr_block.dat",
     "sohex8_incompr_block_nln.dat",
     "sohex8_easfull_patchtest.dat",
@@ -170,10 +174,12 @@ def from_dat(path):
     for l in s.get("DVOL-NODE TOPOLOGY", []):
         t = l.split()
         vol.setdefault(int(t[3]), []).append(int(t[1]))
-    nodes, node_fibers = {}, {}
+    nodes, node_fibers, weights = {}, {}, {}
     for l in s["NODE COORDS"]:
         t = l.split()
         nodes[int(t[1])] = [float(t[3]), float(t[4]), float(t[5])]
+        if t[0] == "CP":  # NURBS control point: CP id COORD x y z weight
+            weights[int(t[1])] = float(t[6])
         if t[0] == "FNODE":  # fibre node: FNODE id COORD x y z FIBER1 a b c
             i = t.index("FIBER1")
             node_fibers[int(t[1])] = [float(x) for x in t[i + 1:i + 4]]
@@ -183,7 +189,21 @@ def from_dat(path):
         i = t.index("MAT")
         eles.append({"id": int(t[0]), "type": t[2], "nodes": [int(x) for x in t[3:i]], "mat": int(t[i + 1]),
                      "opts": " ".join(t[i + 2:])})
-    return {"dynamic": dyn, "io": keyvals(s.get("IO", [])), "materials": mats, "functs": functs, "results": results, "dsurf": surf,
+    # STRUCTURE KNOTVECTORS: patches of NURBS_DIMENSION knot vectors (NUMKNOTS, DEGREE, TYPE, then the knots)
+    patches = []
+    kv = s.get("STRUCTURE KNOTVECTORS", [])
+    i = 0
+    while i < len(kv):
+        t = kv[i].split()
+        if t[0] == "BEGIN":
+            patches.append([])
+        elif t[0] == "NUMKNOTS":
+            n = int(t[1])
+            deg, typ = int(kv[i + 1].split()[1]), kv[i + 2].split()[1]
+            patches[-1].append({"degree": deg, "type": typ, "knots": [float(x) for x in kv[i + 3:i + 3 + n]]})
+            i += 2 + n
+        i += 1
+    return {"dynamic": dyn, "io": keyvals(s.get("IO", [])), "materials": mats, "weights": weights, "knotvectors": patches, "functs": functs, "results": results, "dsurf": surf,
             "dirich": [parse_condition_dat(l) for l in s.get("DESIGN SURF DIRICH CONDITIONS", [])],
             "dline": line, "dirich_line": [parse_condition_dat(l) for l in s.get("DESIGN LINE DIRICH CONDITIONS", [])],
             "dnode": point, "dirich_point": [parse_condition_dat(l) for l in s.get("DESIGN POINT DIRICH CONDITIONS", [])],

@@ -12,15 +12,15 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 
-HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5, HEX18 = 0, 1, 2, 3, 4, 5, 6, 7
+HEX8, HEX27, TET10, HEX20, TET4, WEDGE6, PYRAMID5, HEX18, NURBS27 = 0, 1, 2, 3, 4, 5, 6, 7, 8
 FORM_DISP, FORM_FBAR, FORM_LINEAR, FORM_MULF, FORM_EAS_MILD, FORM_EAS_FULL, FORM_MULF_FBAR, FORM_EAS_SHELL, FORM_SHELL_ANS, FORM_SHELL_EAS_ANS, FORM_EAS_MILD_LINEAR, FORM_EAS_FULL_LINEAR = 0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11
 NEAS = {FORM_EAS_MILD: 9, FORM_EAS_FULL: 21, FORM_EAS_SHELL: 7, FORM_EAS_MILD_LINEAR: 9, FORM_EAS_FULL_LINEAR: 21}
 OUTPUT_STRAIN = 16  # stress_type = OUTPUT_STRAIN + strain type: the Gauss-point output is that strain (stress-like Voigt)
 STRAIN_GL, STRAIN_EA, STRAIN_LOG = 0, 1, 2
 MAT_SVK, MAT_NEOHOOKE = 0, 1
 ACTION_NLNSTIFF, ACTION_INTERNALFORCE = 0, 1
-NEN = {HEX8: 8, HEX27: 27, TET10: 10, HEX20: 20, TET4: 4, WEDGE6: 6, PYRAMID5: 5, HEX18: 18}
-NGP = {HEX8: 8, HEX27: 27, TET10: 4, HEX20: 27, TET4: 1, WEDGE6: 6, PYRAMID5: 8, HEX18: 18}
+NEN = {HEX8: 8, HEX27: 27, TET10: 10, HEX20: 20, TET4: 4, WEDGE6: 6, PYRAMID5: 5, HEX18: 18, NURBS27: 27}
+NGP = {HEX8: 8, HEX27: 27, TET10: 4, HEX20: 27, TET4: 1, WEDGE6: 6, PYRAMID5: 8, HEX18: 18, NURBS27: 27}
 
 _dp = np.ctypeslib.ndpointer(dtype=np.float64, flags="C_CONTIGUOUS")
 _ip = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
@@ -162,9 +162,20 @@ def element_recover_eas(neas, hist, du, step_length=1.0):
     lib.oracle_element_recover_eas(C.c_int(neas), _p(hist), _p(_d(du)), C.c_double(step_length))
 
 
-QUAD4, QUAD9, TRI6, QUAD8, TRI3, QUAD6 = 0, 1, 2, 3, 4, 5
-FACE_NEN = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 8, TRI3: 3, QUAD6: 6}
-FACE_NGP = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 9, TRI3: 3, QUAD6: 6}
+QUAD4, QUAD9, TRI6, QUAD8, TRI3, QUAD6, NURBS9 = 0, 1, 2, 3, 4, 5, 6
+FACE_NEN = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 8, TRI3: 3, QUAD6: 6, NURBS9: 9}
+FACE_NGP = {QUAD4: 4, QUAD9: 9, TRI6: 6, QUAD8: 9, TRI3: 3, QUAD6: 6, NURBS9: 9}
+# faces of a nurbs27 element and the parent directions of their two knot vectors (fc_oracle_nurbs.hpp)
+NURBS27_FACES = [[0, 1, 2, 3, 4, 5, 6, 7, 8], [18, 19, 20, 21, 22, 23, 24, 25, 26], [0, 1, 2, 9, 10, 11, 18, 19, 20],
+                 [6, 7, 8, 15, 16, 17, 24, 25, 26], [2, 5, 8, 11, 14, 17, 20, 23, 26], [0, 3, 6, 9, 12, 15, 18, 21, 24]]
+NURBS27_FACE_DIRS = [(0, 1), (0, 1), (0, 2), (0, 2), (1, 2), (1, 2)]
+
+
+def set_nurbs_element(knots, weights):
+    """knots (3, 6) + weights (27,) of the nurbs27 element, or (2, 6) + (9,) of the nurbs9 face, that the following
+    unit-level calls (shape, element_evaluate, surface_neumann, volume_neumann with one item) use"""
+    kn, w = _d(knots).reshape(-1), _d(weights).reshape(-1)
+    lib.oracle_set_nurbs_element(_p(kn), C.c_int(kn.size), _p(w), C.c_int(w.size))
 
 
 def surface_neumann(ft, x, onoff, val, functfac=None, want_coords=False):
@@ -256,6 +267,12 @@ class Job:
         j.ct = ct
         j._fetch_eles()
         return j
+
+    def set_nurbs(self, ele_knots, node_gid, weights):
+        """nurbs27: knot spans (n_ele, 3, 6) in the job's element order, weights parallel to node_gid"""
+        kn, g, w = _d(ele_knots).reshape(-1), _i(node_gid), _d(weights)
+        assert kn.size == 18 * self._ne and g.size == w.size
+        lib.oracle_job_set_nurbs(self.h, _p(kn), C.c_int(g.size), _p(g), _p(w))
 
     def _fetch_eles(self):
         self.conn = np.zeros((self._ne, NEN[self.ct]), np.int32)

@@ -19,7 +19,12 @@ import os
 import numpy as np
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-CT = {"HEX8": 0, "HEX27": 1, "TET10": 2, "HEX20": 3, "TET4": 4, "WEDGE6": 5, "PYRAMID5": 6, "HEX18": 7}
+CT = {"HEX8": 0, "HEX27": 1, "TET10": 2, "HEX20": 3, "TET4": 4, "WEDGE6": 5, "PYRAMID5": 6, "HEX18": 7, "NURBS27": 8}
+# faces of a nurbs27 element and the parent directions of their two knot vectors (4C_fem_general_utils_local_connectivity_matrices.hpp:250-253,
+# 4C_fem_nurbs_discretization_knotvector.cpp:265-413)
+NURBS27_FACES = [[0, 1, 2, 3, 4, 5, 6, 7, 8], [18, 19, 20, 21, 22, 23, 24, 25, 26], [0, 1, 2, 9, 10, 11, 18, 19, 20],
+                 [6, 7, 8, 15, 16, 17, 24, 25, 26], [2, 5, 8, 11, 14, 17, 20, 23, 26], [0, 3, 6, 9, 12, 15, 18, 21, 24]]
+NURBS27_FACE_DIRS = [(0, 1), (0, 1), (0, 2), (0, 2), (1, 2), (1, 2)]
 # faces of the SURVEY 8f F4 cell types as (face type, local nodes in the node order of the surface cell); face types
 # 0 quad4, 3 quad8, 4 tri3.  Node numbering of the faces: 4C_fem_general_utils_local_connectivity_matrices.hpp:51-86
 FACE_TABLES = {
@@ -53,6 +58,22 @@ class Problem:
         self.ct = CT[types.pop()]
         self.conn = np.array([[self.index[n] for n in e["nodes"]] for e in fx["elements"]], np.int32)
         self.ele_gid = np.array([e["id"] - 1 for e in fx["elements"]], np.int32)
+        self.ele_knots = self.weights = None
+        if self.ct == 8:
+            # knot span of every element (Knotvector::get_ele_knots, 4C_fem_nurbs_discretization_knotvector.cpp:116-243): element
+            # gids count through the patches, inside a patch u runs fastest; an element with cartesian ids (i, j, k) takes the
+            # knots [i, i + 6) x [j, j + 6) x [k, k + 6) of its patch.  Control point weights: the fourth number of a CP line
+            self.weights = np.array([fx["weights"][str(i)] for i in ids], float)
+            kn, off = [], 0
+            for patch in fx["knotvectors"]:
+                assert all(k["degree"] == 2 and k["type"] == "Interpolated" for k in patch) and len(patch) == 3
+                nele = [len(k["knots"]) - 5 for k in patch]
+                for loc in range(nele[0] * nele[1] * nele[2]):
+                    c = (loc % nele[0], (loc // nele[0]) % nele[1], loc // (nele[0] * nele[1]))
+                    kn.append([patch[d]["knots"][c[d]:c[d] + 6] for d in range(3)])
+                off += nele[0] * nele[1] * nele[2]
+            kn = np.array(kn)
+            self.ele_knots = kn[self.ele_gid - self.ele_gid.min()]
         m1 = fx["materials"]["1"]
         self.summands, self.fibers, self.node_fibers = None, None, None
         if m1[0] == "MAT_Struct_StVenantKirchhoff":
@@ -136,7 +157,12 @@ class Problem:
         for c in fx["neumann"]:
             assert c["type"] == "Live" and not any(c["onoff"][3:])
             sset = {self.index[n] for n in fx["dsurf"][str(c["E"])]}
-            for en in self.conn:
+            for e, en in enumerate(self.conn):
+                if self.ct == 8:
+                    for sid, loc in enumerate(NURBS27_FACES):
+                        if all(int(en[a]) in sset for a in loc):
+                            self.faces.append((c, (e, sid), 6))  # nurbs9 face: named by parent element and surface number
+                    continue
                 if self.ct in FACE_TABLES:
                     for ft, loc in FACE_TABLES[self.ct]:
                         if all(int(en[a]) in sset for a in loc):
@@ -151,7 +177,7 @@ class Problem:
         self.neumann = None  # backend with surface(), volume(), *_coords(); None = the numpy restatement below (surfaces only)
         self.face_lists, self.vol_lists = [], []
         for c in fx["neumann"]:
-            if self.ct in FACE_TABLES:
+            if self.ct in FACE_TABLES or self.ct == 8:
                 for ft in sorted({ft for cc, _, ft in self.faces if cc is c}):
                     self.face_lists.append((c, ft, np.array([nodes for cc, nodes, f in self.faces if cc is c and f == ft], np.int32)))
                 continue
@@ -312,13 +338,29 @@ class OracleNeumann:
     def __init__(self, oracle, p):
         self.o, self.p = oracle, p
 
+    def _nurbs_faces(self, fn, onoff, val, fac, want_coords):
+        """faces (parent element, surface number) of a nurbs27 mesh, one oracle call per face with its knots and weights"""
+        p, out = self.p, []
+        for i, (e, sid) in enumerate(fn):
+            nodes = p.conn[e][NURBS27_FACES[sid]]
+            self.o.set_nurbs_element(p.ele_knots[e][list(NURBS27_FACE_DIRS[sid])], p.weights[nodes])
+            r = self.o.surface_neumann(6, p.X[nodes][None], onoff, val, None if fac is None else fac[i][None], want_coords=want_coords)
+            out.append((nodes, r[1][0] if want_coords else r[0]))
+        return out
+
     def surface_coords(self, ft, fn):
+        if ft == 6:
+            return np.array([xg for _, xg in self._nurbs_faces(fn, [0, 0, 0], [0.0, 0.0, 0.0], None, True)])
         return self.o.surface_neumann(ft, self.p.X[fn], [0, 0, 0], [0.0, 0.0, 0.0], want_coords=True)[1]
 
     def volume_coords(self, els):
         return self.o.volume_neumann(self.p.ct, self.p.X[self.p.conn[els]], [0, 0, 0], [0.0, 0.0, 0.0], want_coords=True)[1]
 
     def surface(self, ft, fn, onoff, val, fac, f):
+        if ft == 6:
+            for nodes, fe in self._nurbs_faces(fn, onoff, val, fac, False):
+                np.add.at(f.reshape(-1, 3), nodes, fe)
+            return
         np.add.at(f.reshape(-1, 3), fn, self.o.surface_neumann(ft, self.p.X[fn], onoff, val, fac))
 
     def volume(self, els, onoff, val, fac, f):
@@ -332,12 +374,16 @@ class CudaNeumann:
         self.s = solid
 
     def surface_coords(self, ft, fn):
+        if ft == 6:
+            return self.s.neumann_surface_nurbs_gp_coords(fn[:, 0], fn[:, 1])
         return self.s.neumann_surface_gp_coords(ft, fn)
 
     def volume_coords(self, els):
         return self.s.neumann_volume_gp_coords(els)
 
     def surface(self, ft, fn, onoff, val, fac, f):
+        if ft == 6:
+            return self.s.neumann_surface_nurbs(fn[:, 0], fn[:, 1], onoff, val, f, gp_factor=fac)
         self.s.neumann_surface(ft, fn, onoff, val, f, gp_factor=fac)
 
     def volume(self, els, onoff, val, fac, f):

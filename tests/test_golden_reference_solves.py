@@ -77,11 +77,16 @@ CASES = [
     "solid_ele_hex18_Standard_element_fibers",
     "solid_ele_hex18_Standard_volume_neumann",
     "solid_ele_hex8_Standard_shell_eas",  # TECH shell_eas: the 7 EAS modes of the solid shell, without ANS
+    # nurbs27: one element, and three load steps on two curved patches with non-unit weights
+    "solid_ele_nurbs27_Standard_Static",
+    "solid_runtime_nurbs",
 ]
 
 
 def oracle_backend(oracle, p):
     job = oracle.Job.from_mesh(p.ct, p.node_gid, p.X, p.ele_gid, p.node_gid[p.conn])
+    if p.ct == 8:  # nurbs27: knot spans and control point weights
+        job.set_nurbs(p.ele_knots, p.node_gid, p.weights)
     if p.summands is None:
         job.set_problem(p.form, p.mat, p.young, p.nue)
     else:
@@ -99,7 +104,9 @@ def oracle_backend(oracle, p):
 
     def mass():
         M = np.zeros((p.n_dof, p.n_dof))
-        for en in p.conn:
+        for e, en in enumerate(p.conn):
+            if p.ct == 8:
+                oracle.set_nurbs_element(p.ele_knots[e], p.weights[en])
             err, _, _, Me = oracle.element_evaluate(p.ct, 0, p.mat, p.young, p.nue, p.X[en], np.zeros((len(en), 3)), want_K=False,
                                                     want_M=True, rho=p.dens)
             assert err == 0
@@ -150,6 +157,8 @@ def test_reference_result_description_oracle(oracle, case):
 def cuda_backend(fc, p):
     s = fc.Solid(0)
     s.set_mesh(p.ct, p.form, p.X, p.node_gid, np.zeros(len(p.node_gid), np.int32), p.conn, p.ele_gid)
+    if p.ct == 8:
+        s.set_nurbs(p.ele_knots, p.weights)
     if p.summands is None:
         s.set_material(p.mat, p.young, p.nue)
     else:

@@ -47,6 +47,23 @@ def tet10_cube(n):
     return used.astype(np.int32), X, inv.reshape(conn.shape).astype(np.int32)
 
 
+def nurbs27_patch(n):
+    """one patch of n^3 nurbs27 elements on the unit cube: open uniform knot vectors of degree 2, (n + 2)^3 control points at the
+    Greville abscissae (the geometry map is the identity), weights 1 +- 10 %; element (i, j, k) holds the control points
+    [i, i + 3) x [j, j + 3) x [k, k + 3) with u fastest and the knots [i, i + 6) of each direction"""
+    kv = np.concatenate([[0.0, 0.0], np.arange(n + 1) / n, [1.0, 1.0]])
+    g = (kv[1:n + 3] + kv[2:n + 4]) / 2
+    m = n + 2
+    k, j, i = np.meshgrid(np.arange(m), np.arange(m), np.arange(m), indexing="ij")
+    X = np.stack([g[i.ravel()], g[j.ravel()], g[k.ravel()]], axis=1)
+    ek, ej, ei = [a.ravel() for a in np.meshgrid(np.arange(n), np.arange(n), np.arange(n), indexing="ij")]
+    a = np.arange(27)
+    conn = ((ek[:, None] + a // 9) * m + (ej[:, None] + (a // 3) % 3)) * m + (ei[:, None] + a % 3)
+    knots = np.stack([kv[ei[:, None] + np.arange(6)], kv[ej[:, None] + np.arange(6)], kv[ek[:, None] + np.arange(6)]], axis=1)
+    w = 1.0 + 0.1 * np.sin(7.0 * X[:, 0] + 3.0 * X[:, 1] + 5.0 * X[:, 2])
+    return np.arange(len(X), dtype=np.int32), X, conn.astype(np.int32), knots, w
+
+
 def run(fc, name, ct, form, mat, nue, n, steps, flags=0):
     import torch
     dev = torch.device("cuda", 0)
@@ -55,12 +72,18 @@ def run(fc, name, ct, form, mat, nue, n, steps, flags=0):
         gid, X, conn = tet10_cube(n[0])
         owner = np.zeros(len(gid), np.int32)
         egid = np.arange(len(conn), dtype=np.int32)
+    elif ct == fc.FC_NURBS27:
+        gid, X, conn, knots, weights = nurbs27_patch(n[0])
+        owner = np.zeros(len(gid), np.int32)
+        egid = np.arange(len(conn), dtype=np.int32)
     else:
         g = fc.Grid(ct, n)
         gid, X, conn, owner, egid = g.node_gid, g.X, g.conn, g.node_owner, g.ele_gid
     s = fc.Solid(0)
     s.set_stream(torch.cuda.current_stream().cuda_stream)
     s.set_mesh(ct, form, X, gid, owner, conn, egid)
+    if ct == fc.FC_NURBS27:
+        s.set_nurbs(knots, weights)
     s.set_material(mat, 10.0, nue)
     n_row, n_col, nnz = s.build_graph()
     setup_s = time.time() - t0
@@ -287,6 +310,9 @@ def main():
         ("F4 hex8 eas_full NeoHooke 100^3", H8, fc.FC_FORM_EAS_FULL, NH, 0.25, (100, 100, 100), 0),
         ("F4 hex8 mulf NeoHooke 100^3", H8, fc.FC_FORM_MULF, NH, 0.25, (100, 100, 100), 0),
         ("F4 hex8 linear SVK 100^3", H8, fc.FC_FORM_LINEAR, SVK, 0.3, (100, 100, 100), 0),
+        # nurbs27 on the generic kernel with per-element shape tables (41.5 KB per element), next to hex27 on the same kernel
+        ("F4 nurbs27 NeoHooke 46^3 patch (48^3 control points)", fc.FC_NURBS27, D, NH, 0.25, (46, 46, 46), 0),
+        ("F4 hex27 NeoHooke 48^3 (generic B-operator)", H27, D, NH, 0.25, (48, 48, 48), fc.FC_EVAL_FORCE_GENERIC),
     ]
     if args.only and args.only.startswith("variantB"):
         run_variant_b(fc, int(args.only[8:] or 100), args.steps)

@@ -408,11 +408,13 @@ extern "C"
     FC_CUDA(dev_upload(ctx->d_nurbs_knots, ele_knots, (size_t)18 * n_ele, ctx->stream));
     FC_CUDA(dev_upload(ctx->d_nurbs_weights, node_weights, (size_t)ctx->n_col_nodes, ctx->stream));
     dev_free(ctx->d_dNtab);
+    dev_free(ctx->d_geom);  // geometry cache of the tensor-core kernel: belongs to the previous tables
     ctx->geom_bad_count = 0;
     ctx->geom_first_bad_gid = -1;
     if (n_ele > 0)
     {
       FC_CUDA(cudaMalloc((void**)&ctx->d_dNtab, sizeof(double) * (size_t)fc::NurbsTab::stride * n_ele));
+      FC_CUDA(cudaMemsetAsync(ctx->d_dNtab, 0, sizeof(double) * (size_t)fc::NurbsTab::stride * n_ele, ctx->stream));
       unsigned char* d_zero = nullptr;
       FC_CUDA(cudaMalloc((void**)&d_zero, (size_t)n_ele));
       const long long nt = (long long)n_ele * (fc::NurbsTab::ngp + fc::NurbsTab::nen + 1);

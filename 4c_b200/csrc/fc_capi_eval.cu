@@ -185,7 +185,7 @@ namespace
     if (ctx->formulation >= FC_FORM_LINEAR) return false;  // linear, MULF, EAS: k_generic / k_hex8_eas
     const bool fbar = ctx->formulation == FC_FORM_FBAR, nh = ctx->mat.kind == fc::MAT_NEOHOOKE;
     if (ctx->celltype == FC_HEX8) return nh ? (fbar || !(flags & FC_EVAL_CLOSED_FORM_FMA)) : (ctx->mat.kind == fc::MAT_SVK && !fbar);  // k_hex8_neohooke_mma, k_hex8_mma_ext
-    if (ctx->celltype != FC_HEX27 && ctx->celltype != FC_TET10) return false;                      // k_generic
+    if (ctx->celltype != FC_HEX27 && ctx->celltype != FC_TET10 && ctx->celltype != FC_NURBS27) return false;  // k_generic
     return nh && !fbar;                                                                            // k_nh_mma_gen
   }
 
@@ -243,7 +243,9 @@ namespace
     if (ctx->celltype == FC_TET4) return launch_generic<fc::TET4, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_WEDGE6) return launch_generic<fc::WEDGE6, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_HEX18) return launch_generic<fc::HEX18, fc::FORM_DISP, WANT_K>(ctx, A);
-    if (ctx->celltype == FC_NURBS27) return launch_generic<fc::NURBS27, fc::FORM_DISP, WANT_K>(ctx, A);
+    if (ctx->celltype == FC_NURBS27)  // Neo-Hooke: the tensor-core closed form of hex27 on the element's own shape tables
+      return ctx->mat.kind == fc::MAT_NEOHOOKE && !(flags & FC_EVAL_FORCE_GENERIC) ? launch_nh_gen<fc::NURBS27, WANT_K>(ctx, A)
+                                                                                  : launch_generic<fc::NURBS27, fc::FORM_DISP, WANT_K>(ctx, A);
     if (ctx->celltype == FC_PYRAMID5)
       return fbar ? launch_generic<fc::PYRAMID5, fc::FORM_FBAR, WANT_K>(ctx, A) : launch_generic<fc::PYRAMID5, fc::FORM_DISP, WANT_K>(ctx, A);
     const bool nh_gen = ctx->mat.kind == fc::MAT_NEOHOOKE && !fbar && !(flags & FC_EVAL_FORCE_GENERIC);

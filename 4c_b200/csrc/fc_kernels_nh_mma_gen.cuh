@@ -20,6 +20,7 @@
 //             shared memory and added to the CSR rows with lane-contiguous FP64 reductions; then the residual rows
 #pragma once
 #include "fc_kernels_hex8nh_mma.cuh"
+#include "fc_nurbs.cuh"
 
 namespace fc
 {
@@ -28,11 +29,12 @@ namespace fc
   {
     static constexpr int nen = Cell<CT>::nen, ngp = Cell<CT>::ngp;
     static constexpr int MT = (nen + 7) / 8, KS = (ngp + 3) / 4, NP = 8 * MT, GP4 = 4 * KS;
-    static constexpr int epb = CT == TET10 ? 8 : (CT == HEX27 ? 1 : 4);
+    static constexpr bool is27 = CT == HEX27 || CT == NURBS27;  // nurbs27: the same kernel on the element's own shape tables (fc_nurbs.cuh)
+    static constexpr int epb = CT == TET10 ? 8 : (is27 ? 1 : 4);
     static constexpr int warps = 4, threads = 32 * warps;
     // CTAs per SM the register allocation leaves room for.  hex27: 5 (96 registers, no spills) measured 4.01 ms at 48^3 against
     // 4.38 ms with 4 (113 registers) and 4.58 ms with 6 (80 registers, spills)
-    static constexpr int min_blocks = CT == HEX27 ? 5 : 1;
+    static constexpr int min_blocks = is27 ? 5 : 1;
     static constexpr int plane = KS * MT * 32;
     // shape-function derivatives at the Gauss points behind the [ngp + nen + 1][nen][3] table (fill_tables, fc_host_util.hpp)
     static constexpr int oTabNodeMajor = (ngp + nen + 1) * nen * 3;   // [nen][ngp][3]
@@ -41,7 +43,7 @@ namespace fc
     // mesh, like the hex8 kernel): the three nhat planes, J^-1 and 3 of the 12 DMMA per tile step go away, the element needs
     // 22 KB of shared memory less.  tet10 recomputes them (measured with the cache: stiffness 9.88 -> 10.10 ms, residual-only
     // 3.20 -> 2.86 ms; its cache adds 28 % to the bytes the kernel moves).
-    static constexpr bool geom = CT == HEX27;
+    static constexpr bool geom = is27;
     static constexpr int nplanes = geom ? 3 : 6;
     static constexpr int geom_doubles = 2 * 32 * MT * MT + ((ngp + 7) & ~7);  // [mt][nt][lane][2] accumulator layout, then detJ[gp]
     static constexpr int oInv = nplanes * plane;     // [GP4][20]: sk*j^-1 (9), sl*J^-1 (9) | scratch: inv, det
@@ -51,6 +53,10 @@ namespace fc
     static constexpr int stage = 288;                // per warp: 12 rows x 24
     static constexpr size_t smem_bytes = sizeof(double) * ((size_t)epb * ele_doubles + warps * stage);
   };
+
+  static_assert(NhGenCfg<NURBS27>::oTabNodeMajor == NurbsTab::oNodeMajor && NhGenCfg<NURBS27>::oTabFragment == NurbsTab::oFragment &&
+                    NhGenCfg<NURBS27>::MT == NurbsTab::MT && NhGenCfg<NURBS27>::KS == NurbsTab::KS,
+      "per-element nurbs27 table and the shared table of the Lagrange cells: same layout");
 
   // geometry cache of k_nh_mma_gen (cells with NhGenCfg::geom): per element G[a][b] = sum_gp w detJ grad N_a . grad N_b in the
   // accumulator layout of the (mt, nt) tiles - lane (a8, q) holds (8 mt + a8, 8 nt + 2 q + {0, 1}) - followed by detJ at the Gauss
@@ -74,7 +80,7 @@ namespace fc
     __syncthreads();
     for (int gp = tid; gp < NGP; gp += blockDim.x)
     {
-      const double* dN = dNtab + (size_t)gp * NEN * 3;
+      const double* dN = ele_table<CT>(dNtab, e) + (size_t)gp * NEN * 3;
       double M[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, Mi[9];
       for (int a = 0; a < NEN; ++a)
         for (int d = 0; d < 3; ++d)
@@ -111,7 +117,7 @@ namespace fc
     // slot of column node b in the row of node a.  hex27: the whole element map is loaded once in phase 0 (measured 5.77 -> 5.03 ms
     // at 48^3: inside the tile loop the byte loads' latency was exposed 4 times per element); tet10: per row tile inside the loop
     // (phase-0 loading measured slower there, 9.9 -> 10.4 ms)
-    constexpr bool SLOTS_PHASE0 = CT == HEX27;
+    constexpr bool SLOTS_PHASE0 = Cfg::is27;
     __shared__ unsigned char s_slots[SLOTS_PHASE0 ? 1 : Cfg::warps * 8][NP];
     // phase-0 variant: the element's nen x nen bytes as aligned 32-bit words (the byte-wise loop cost 9 000 cycles per element)
     constexpr int SLW = (NEN * NEN + 6) / 4 + 1;
@@ -185,7 +191,7 @@ namespace fc
       if (ebase + el >= A.n_ele) continue;
       double* E = smem_nhg + (size_t)el * Cfg::ele_doubles;
       const double* crd = E + (which ? Cfg::oX : Cfg::oXm);
-      const double* dN = A.dNtab + Cfg::oTabNodeMajor + gp * 3 + d;
+      const double* dN = ele_table<CT>(A.dNtab, A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el) + Cfg::oTabNodeMajor + gp * 3 + d;
       double m0 = 0.0, m1 = 0.0, m2 = 0.0;
 #pragma unroll
       for (int a = 0; a < NEN; ++a)
@@ -259,7 +265,7 @@ namespace fc
       if (ebase + el < A.n_ele)
       {
         // fragment-ordered table: one coalesced load per direction, zero where the tile is padding (R is zero for padded Gauss points)
-        const double* dN = A.dNtab + Cfg::oTabFragment + (ks * MT + mt) * 32 + lane;
+        const double* dN = ele_table<CT>(A.dNtab, A.ele_perm ? __ldg(A.ele_perm + ebase + el) : ebase + el) + Cfg::oTabFragment + (ks * MT + mt) * 32 + lane;
         const double d0 = __ldg(dN), d1 = __ldg(dN + Cfg::plane), d2 = __ldg(dN + 2 * Cfg::plane);
         const double* R = E + Cfg::oInv + gp * 20;
 #pragma unroll

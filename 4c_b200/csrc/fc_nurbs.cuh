@@ -9,8 +9,9 @@
 // belong to the mesh, so here k_nurbs_tables evaluates it once per mesh into a per-element table
 //   dN [ngp + nen + 1][nen][3]   Gauss points, the 27 points of the node-Jacobian check, centroid  (the layout of the other
 //                                cells' shared table, so that the element kernels only add an element offset: ele_table)
+//   dN at the Gauss points in the node-major and the fragment order of the tensor-core kernel (fc_kernels_nh_mma_gen.cuh)
 //   N  [ngp][nen]                for the mass matrix and the body loads
-// 41.5 KB per element, read through L2 by the element kernels.
+// 80 KB per element; an evaluation reads the part its kernel needs (generic kernel 17.5 KB, tensor-core kernel 39 KB).
 #pragma once
 #include "fc_fem.cuh"
 
@@ -19,7 +20,12 @@ namespace fc
   struct NurbsTab
   {
     static constexpr int nen = 27, ngp = 27;
-    static constexpr int oN = (ngp + nen + 1) * nen * 3;  // shape function values behind the derivatives
+    // the Gauss-point derivatives again in the two orders k_nh_mma_gen reads them in (like fill_tables, fc_host_util.hpp):
+    // node-major [nen][ngp][3] and fragment order [3][KS * MT][32 lanes], then the shape function values [ngp][nen]
+    static constexpr int MT = 4, KS = 7;
+    static constexpr int oNodeMajor = (ngp + nen + 1) * nen * 3;
+    static constexpr int oFragment = oNodeMajor + nen * ngp * 3;
+    static constexpr int oN = oFragment + 3 * KS * MT * 32;
     static constexpr int stride = oN + ngp * nen;
   };
 
@@ -109,7 +115,15 @@ namespace fc
     else if (p < T::ngp + T::nen)
       node_param_coords(NURBS27, p - T::ngp, xi);
     double* out = tab + (size_t)e * T::stride;
-    nurbs_funct_deriv<3>(xi, kn, w, p < T::ngp ? out + T::oN + p * T::nen : nullptr, out + (size_t)p * T::nen * 3);
+    double* dN = out + (size_t)p * T::nen * 3;
+    nurbs_funct_deriv<3>(xi, kn, w, p < T::ngp ? out + T::oN + p * T::nen : nullptr, dN);
+    if (p < T::ngp)  // the padding entries of the fragment order stay zero (the table is cleared before this kernel)
+      for (int a = 0; a < T::nen; ++a)
+        for (int d = 0; d < 3; ++d)
+        {
+          out[T::oNodeMajor + (a * T::ngp + p) * 3 + d] = dN[3 * a + d];
+          out[T::oFragment + (d * T::KS * T::MT + (p >> 2) * T::MT + (a >> 3)) * 32 + ((a & 7) << 2 | (p & 3))] = dN[3 * a + d];
+        }
     if (p == 0)
     {
       bool zs = false;

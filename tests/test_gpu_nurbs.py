@@ -35,7 +35,7 @@ def contexts(fc, oracle, p, form, mat, nue=0.3):
     return s, job
 
 
-def compare_system(fc, oracle, s, job, u, tol=TOL):
+def compare_system(fc, oracle, s, job, u, tol=TOL, flags=0):
     n_row, n_col, nnz = s.build_graph() if not getattr(s, "_graph", None) else s._graph
     s._graph = (n_row, n_col, nnz)
     o = job.rank(0)
@@ -45,13 +45,13 @@ def compare_system(fc, oracle, s, job, u, tol=TOL):
     rowptr, colind = s.get_graph()
     assert nnz == o["nnz"] and np.array_equal(rowptr, o["rowptr"]) and np.array_equal(colind, o["colind"])
     K, f = np.zeros(nnz), np.zeros(n_row)
-    assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u.reshape(-1), f, K, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
+    assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u.reshape(-1), f, K, flags=fc.FC_EVAL_ZERO_FIRST | flags) == (0, -1)
     starts = np.asarray(rowptr[:-1], np.int64)
     assert np.max(np.maximum.reduceat(np.abs(K - K_ref), starts) / np.maximum.reduceat(np.abs(K_ref), starts)) <= tol
     assert np.max(np.abs(f - f_ref)) <= tol * max(np.max(np.abs(f_ref)), np.max(np.abs(K_ref)))
     f2 = np.zeros(n_row)
-    assert s.evaluate(fc.FC_ACTION_INTERNALFORCE, u.reshape(-1), f2, None, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
-    assert np.max(np.abs(f2 - f)) <= 1e-14 * np.max(np.abs(f))
+    assert s.evaluate(fc.FC_ACTION_INTERNALFORCE, u.reshape(-1), f2, None, flags=fc.FC_EVAL_ZERO_FIRST | flags) == (0, -1)
+    assert np.max(np.abs(f2 - f)) <= 1e-13 * np.max(np.abs(f))
     return K, f, rowptr, colind
 
 
@@ -76,6 +76,8 @@ def test_assembled_system(fc, oracle, form, mat):
         h_ref = job.mulf_history()
         assert np.max(np.abs(s.mulf_history() - h_ref)) <= 1e-13 * np.max(np.abs(h_ref))
     compare_system(fc, oracle, s, job, u)
+    if form == DISP and mat == NH:  # default: the tensor-core closed form (k_nh_mma_gen<NURBS27>); also the generic kernel
+        compare_system(fc, oracle, s, job, u, flags=fc.FC_EVAL_FORCE_GENERIC)
     for st in (fc.FC_STRESS_2PK, fc.FC_STRESS_CAUCHY):
         gp, _ = s.evaluate_stress(u.reshape(-1), st, want_nodal=False)
         for e in range(len(p.conn)):

@@ -97,6 +97,17 @@ CASES = [
     "solid_ele_nurbs27_Standard_Static.dat",
     "solid_ele_nurbs27_Standard_Static_multielement.dat",  # no RESULT DESCRIPTION: CUDA against oracle only
     "solid_runtime_nurbs.dat",  # two curved patches (17 elements), weights != 1, three load steps
+    # the runtime-output family: St.Venant-Kirchhoff E = 100, nu = 0, two load steps, every node's displacement listed
+    "solid_runtime_hex8.dat",
+    "solid_runtime_hex20.dat",
+    "solid_runtime_hex27.dat",
+    "solid_runtime_tet4.dat",
+    "solid_runtime_tet10.dat",
+    "solid_runtime_wedge6.dat",
+    "solid_runtime_pyramid5.dat",
+    # patch tests on tetrahedra
+    "sotet10_patchtest.dat",
+    "sotet4_patchtest.dat",
     "sohex8_incompr_block.dat",
     "sohex8_incompr_block_nln.dat",
     "sohex8_easfull_patchtest.dat",

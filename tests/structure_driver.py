@@ -130,7 +130,9 @@ class Problem:
         # result then depends on where the reference stopped, so the replay applies the reference's test (absolute L2 norms of
         # the residual and of the increment, combined with NORMCOMBI_RESFDISP) instead of iterating to rounding level
         self.ref_stop = None
-        if float(dyn.get("TOLRES", 0)) >= 1e-9 and dyn.get("NORM_RESF", "Abs") == "Abs" and dyn.get("NORM_DISP", "Abs") == "Abs":
+        # (also the "linear" tests that cut Newton off: MAXITER <= 3 with DIVERCONT continue, whatever the tolerances)
+        cut_off = dyn.get("DIVERCONT", "stop") == "continue" and int(dyn.get("MAXITER", 50)) <= 3
+        if (float(dyn.get("TOLRES", 0)) >= 1e-9 or cut_off) and dyn.get("NORM_RESF", "Abs") == "Abs" and dyn.get("NORM_DISP", "Abs") == "Abs":
             self.ref_stop = (float(dyn["TOLRES"]), float(dyn["TOLDISP"]), dyn.get("NORMCOMBI_RESFDISP", "And"))
         # MAXITER with DIVERCONT continue: the reference goes on with what it has after MAXITER iterations
         self.ref_maxiter = int(dyn["MAXITER"]) if self.ref_stop is not None and dyn.get("DIVERCONT", "stop") == "continue" and "MAXITER" in dyn else None

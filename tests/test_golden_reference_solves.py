@@ -80,6 +80,11 @@ CASES = [
     # nurbs27: one element, and three load steps on two curved patches with non-unit weights
     "solid_ele_nurbs27_Standard_Static",
     "solid_runtime_nurbs",
+    # the runtime-output family on every Lagrange cell (St.Venant-Kirchhoff, two load steps, all nodes listed)
+    "solid_runtime_hex8", "solid_runtime_hex20", "solid_runtime_hex27", "solid_runtime_tet4", "solid_runtime_tet10",
+    "solid_runtime_wedge6", "solid_runtime_pyramid5",
+    # patch tests on tetrahedra (tet10: one Newton iteration, MAXITER 1 with DIVERCONT continue)
+    "sotet10_patchtest", "sotet4_patchtest",
 ]
 
 

@@ -108,6 +108,60 @@ CASES = [
     # patch tests on tetrahedra
     "sotet10_patchtest.dat",
     "sotet4_patchtest.dat",
+    # found by scanning the reference's input directory for Structure problems made of SOLID elements, in-scope materials and
+    # conditions only: linear patch tests, single-step solver tests, body loads per cell, and the same element inputs under
+    # INT_STRATEGY Old (the elements are the new ones; another time-integration framework drives them)
+    "patch_test_cube_h27_linear_no_override_dbc.dat",
+    "patch_test_cube_linear_no_override_dbc.dat",
+    "patch_test_cube_linear_test_react.dat",
+    "patch_test_cube_h27_linear_test_react.dat",
+    "sohex27_patchtest_nl_cost_drt.dat",
+    "structure_new_nln_solver_singlestep_cube_linear.dat",
+    "structure_new_nln_solver_singlestep_cube_linear_restart.dat",
+    "solid_runtime_material_element_id.dat",
+    "solid_ele_nurbs27_solid_runtime.dat",
+    "solidh8_ele_standard_volume_neumann.dat",
+    "solidh18_ele_standard_volume_neumann.dat",
+    "solidh20_ele_standard_volume_neumann.dat",
+    "solidh27_ele_standard_volume_neumann.dat",
+    "solidt4_ele_standard_volume_neumann.dat",
+    "solidt10_ele_standard_volume_neumann.dat",
+    "solid_ele_hex8_Old_eas_none_dynamic.dat",
+    "solid_ele_hex8_Old_eas_none_volume_neumann.dat",
+    "solid_ele_hex8_Old_eas_none_element_fibers.dat",
+    "solid_ele_hex8_Old_eas_none_nodal_fibers.dat",
+    "solid_ele_hex8_Old_eas_mild_dynamic.dat",
+    "solid_ele_hex8_Old_eas_mild_volume_neumann.dat",
+    "solid_ele_hex8_Old_eas_mild_element_fibers.dat",
+    "solid_ele_hex8_Old_eas_mild_nodal_fibers.dat",
+    "solid_ele_hex8_Old_eas_full_dynamic.dat",
+    "solid_ele_hex8_Old_eas_full_volume_neumann.dat",
+    "solid_ele_hex8_Old_eas_full_nodal_fibers.dat",
+    "solid_ele_hex8_Old_fbar.dat",
+    "solid_ele_hex8_Old_mulf.dat",
+    "solid_ele_hex18_Old_dynamic.dat",
+    "solid_ele_hex18_Old_volume_neumann.dat",
+    "solid_ele_hex18_Old_element_fibers.dat",
+    "solid_ele_hex20_Old_dynamic.dat",
+    "solid_ele_hex20_Old_volume_neumann.dat",
+    "solid_ele_hex20_Old_element_fibers.dat",
+    "solid_ele_hex27_Old_dynamic.dat",
+    "solid_ele_hex27_Old_volume_neumann.dat",
+    "solid_ele_hex27_Old_element_fibers.dat",
+    "solid_ele_pyramid5_Old_dynamic.dat",
+    "solid_ele_pyramid5_Old_volume_neumann.dat",
+    "solid_ele_pyramid5_Old_element_fibers.dat",
+    "solid_ele_pyramid5_Old_fbar.dat",
+    "solid_ele_tet10_Old_dynamic.dat",
+    "solid_ele_tet10_Old_volume_neumann.dat",
+    "solid_ele_tet10_Old_element_fibers.dat",
+    "solid_ele_tet10_Old_nodal_fibers.dat",
+    "solid_ele_tet4_Old_dynamic.dat",
+    "solid_ele_tet4_Old_volume_neumann.dat",
+    "solid_ele_tet4_Old_element_fibers.dat",
+    "solid_ele_tet4_Old_nodal_fibers.dat",
+    "solid_ele_wedge6_Old_dynamic.dat",
+    "solid_ele_wedge6_Old_element_fibers.dat",
     "sohex8_incompr_block.dat",
     "sohex8_incompr_block_nln.dat",
     "sohex8_easfull_patchtest.dat",

@@ -162,6 +162,11 @@ CASES = [
     "solid_ele_tet4_Old_nodal_fibers.dat",
     "solid_ele_wedge6_Old_dynamic.dat",
     "solid_ele_wedge6_Old_element_fibers.dat",
+    # prescribed displacements (VAL * FUNCT with a VARIABLE of TYPE linearinterpolation), KINEM linear beams with analytical solutions
+    "patch_test_cube_linear_prescribed_disp_no_override_dbc.dat",
+    "patch_test_cube_linear_prescribed_disp_triaxial_no_override_dbc.dat",
+    "error_analytical_beam_cantilever_end_surface_load_with_poissons_effect.dat",
+    "error_analytical_beam_cantilever_with_bodyload_without_poissons_effect.dat",
     "sohex8_incompr_block.dat",
     "sohex8_incompr_block_nln.dat",
     "sohex8_easfull_patchtest.dat",
@@ -219,13 +224,24 @@ def from_dat(path):
         t = l.split()
         mats[int(t[1])] = t[2:]
     functs = {int(k[5:]): re.split(r"SYMBOLIC_FUNCTION_OF_(?:SPACE_)?TIME", v[0])[1].strip() for k, v in s.items() if re.match(r"FUNCT\d+$", k)}
+    # VARIABLE lines of a function: piecewise linear in time (TYPE linearinterpolation NUMPOINTS n TIMES ... VALUES ...)
+    funct_vars = {}
+    for k, v in s.items():
+        if re.match(r"FUNCT\d+$", k):
+            for l in v[1:]:
+                t = l.split()
+                if t[0] == "VARIABLE" and t[t.index("TYPE") + 1] == "linearinterpolation":
+                    n = int(t[t.index("NUMPOINTS") + 1])
+                    i, j = t.index("TIMES"), t.index("VALUES")
+                    funct_vars.setdefault(int(k[5:]), {})[t[t.index("NAME") + 1]] = {
+                        "times": [float(x) for x in t[i + 1:i + 1 + n]], "values": [float(x) for x in t[j + 1:j + 1 + n]]}
     results = []
     for l in s.get("RESULT DESCRIPTION", []):
         t = l.split()
         results.append({"node": int(t[t.index("NODE") + 1]) if "NODE" in t else -1, "quantity": t[t.index("QUANTITY") + 1],
                         "value": float(t[t.index("VALUE") + 1]), "tolerance": float(t[t.index("TOLERANCE") + 1])})
     surf = {}
-    for l in s["DSURF-NODE TOPOLOGY"]:
+    for l in s.get("DSURF-NODE TOPOLOGY", []):
         t = l.split()
         surf.setdefault(int(t[3]), []).append(int(t[1]))
     line, point = {}, {}
@@ -268,7 +284,7 @@ def from_dat(path):
             patches[-1].append({"degree": deg, "type": typ, "knots": [float(x) for x in kv[i + 3:i + 3 + n]]})
             i += 2 + n
         i += 1
-    return {"dynamic": dyn, "io": keyvals(s.get("IO", [])), "materials": mats, "weights": weights, "knotvectors": patches, "functs": functs, "results": results, "dsurf": surf,
+    return {"dynamic": dyn, "io": keyvals(s.get("IO", [])), "materials": mats, "weights": weights, "knotvectors": patches, "funct_vars": funct_vars, "functs": functs, "results": results, "dsurf": surf,
             "dirich": [parse_condition_dat(l) for l in s.get("DESIGN SURF DIRICH CONDITIONS", [])],
             "dline": line, "dirich_line": [parse_condition_dat(l) for l in s.get("DESIGN LINE DIRICH CONDITIONS", [])],
             "dnode": point, "dirich_point": [parse_condition_dat(l) for l in s.get("DESIGN POINT DIRICH CONDITIONS", [])],

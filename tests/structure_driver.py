@@ -138,22 +138,26 @@ class Problem:
         self.ref_maxiter = int(dyn["MAXITER"]) if self.ref_stop is not None and dyn.get("DIVERCONT", "stop") == "continue" and "MAXITER" in dyn else None
         # PRESTRESS mulf: steps with t <= PRESTRESSTIME end with struct_update_prestress and a reset of the displacements
         self.prestress_time = float(dyn["PRESTRESSTIME"]) if dyn.get("PRESTRESS", "none").lower() == "mulf" else None
-        # Dirichlet: all values are zero in these inputs
+        # Dirichlet: zero in most inputs; prescribed displacements VAL * FUNCT(X, t) are imposed at the start of every load
+        # step (statics only)
         # Hierarchy of Core::FE::Utils::Dbc::read_dirichlet_condition (4C_fem_discretization_utils_dbc.cpp:164-400): surface, then
         # line, then point conditions; a condition sets its ONOFF = 1 DOFs, and its ONOFF = 0 releases a DOF only if a condition of
         # higher dimension fixed it (conditions of the same kind add up)
         toggle, level = np.zeros(self.n_dof, bool), np.full(self.n_dof, 9)
+        prescribed = {}  # DOF -> (VAL, FUNCT id) of the condition that fixed it last
         for order, key, topo in ((2, "dirich", "dsurf"), (1, "dirich_line", "dline"), (0, "dirich_point", "dnode")):
             for c in fx.get(key, []):
-                assert not any(c["val"])
+                assert not any(c["val"]) or dyn.get("DYNAMICTYPE", "GenAlpha") == "Statics"
                 for n in fx[topo][str(c["E"])]:
                     for d in range(3):
                         lid = 3 * self.index[n] + d
                         if c["onoff"][d]:
                             toggle[lid], level[lid] = True, order
+                            prescribed[lid] = (c["val"][d], c["funct"][d])
                         elif order < level[lid]:
                             toggle[lid], level[lid] = False, order
         self.fixed = np.nonzero(toggle)[0].astype(np.int64)
+        self.prescribed = [(lid, v, f) for lid, (v, f) in sorted(prescribed.items()) if toggle[lid] and v != 0.0]
         self.xi_nodes = np.asarray(node_param_coords(self.ct), float)
         self.faces = []
         for c in fx["neumann"]:
@@ -281,7 +285,10 @@ class Problem:
         if fid <= 0:
             return 1.0
         expr = self.fx["functs"][str(fid)]
-        return float(eval(expr, {"__builtins__": {}}, {"x": x[0], "y": x[1], "z": x[2], "t": t}))
+        env = {"x": x[0], "y": x[1], "z": x[2], "t": t}
+        for name, v in self.fx.get("funct_vars", {}).get(str(fid), {}).items():  # VARIABLE ... TYPE linearinterpolation
+            env[name] = float(np.interp(t, v["times"], v["values"]))
+        return float(eval(expr, {"__builtins__": {}}, env))
 
     def _factors(self, key, cond, coords, t):
         """FUNCT of the condition at the Gauss points: (n, ngp, 3), None when every factor is 1"""
@@ -428,6 +435,8 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, 
         for step in range(1, p.numstep + 1):
             fext = p.f_ext(step * dt)
             norms = []
+            for lid, v, fid in p.prescribed:  # prescribed displacements of this step
+                d[lid] = v * p.funct(fid, p.X[lid // 3], step * dt)
             if p.ref_stop is not None:
                 # the reference's loop: solve, update, recover, new residual, test (converged if the residual OR / AND the increment
                 # is below its tolerance)

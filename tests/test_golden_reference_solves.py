@@ -106,6 +106,10 @@ CASES = [
     "solid_ele_tet10_Old_volume_neumann", "solid_ele_tet10_Old_element_fibers", "solid_ele_tet10_Old_nodal_fibers",
     "solid_ele_tet4_Old_dynamic", "solid_ele_tet4_Old_volume_neumann", "solid_ele_tet4_Old_element_fibers",
     "solid_ele_tet4_Old_nodal_fibers", "solid_ele_wedge6_Old_dynamic", "solid_ele_wedge6_Old_element_fibers",
+    # prescribed displacements in statics; cantilevers with analytical solutions (KINEM linear, ten load steps)
+    "patch_test_cube_linear_prescribed_disp_no_override_dbc", "patch_test_cube_linear_prescribed_disp_triaxial_no_override_dbc",
+    "error_analytical_beam_cantilever_end_surface_load_with_poissons_effect",
+    "error_analytical_beam_cantilever_with_bodyload_without_poissons_effect",
 ]
 
 

@@ -167,6 +167,7 @@ CASES = [
     "patch_test_cube_linear_prescribed_disp_triaxial_no_override_dbc.dat",
     "error_analytical_beam_cantilever_end_surface_load_with_poissons_effect.dat",
     "error_analytical_beam_cantilever_with_bodyload_without_poissons_effect.dat",
+    "soweg6_disp_patchtest.dat",  # 4 hex8 + 6 wedge6 in one discretization (tests/test_mixed_cells.py)
     "sohex8_incompr_block.dat",
     "sohex8_incompr_block_nln.dat",
     "sohex8_easfull_patchtest.dat",

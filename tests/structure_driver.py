@@ -177,7 +177,7 @@ class Problem:
                 for loc, rs in self._element_faces():
                     if all(int(en[a]) in sset for a in loc):
                         self.faces.append((c, en[loc], rs))
-        assert self.faces or not fx["neumann"]
+        assert self.faces or not fx["neumann"] or fx.get("part_of_mixed_mesh")  # (the loaded faces may all belong to the other cell type)
         # the same loads as lists for a Neumann backend (oracle / CUDA library): faces by their nodes in the reference's
         # quad4 / quad9 / tri6 node order, volume conditions by their elements
         self.neumann = None  # backend with surface(), volume(), *_coords(); None = the numpy restatement below (surfaces only)

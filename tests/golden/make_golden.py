@@ -168,6 +168,7 @@ CASES = [
     "error_analytical_beam_cantilever_end_surface_load_with_poissons_effect.dat",
     "error_analytical_beam_cantilever_with_bodyload_without_poissons_effect.dat",
     "soweg6_disp_patchtest.dat",  # 4 hex8 + 6 wedge6 in one discretization (tests/test_mixed_cells.py)
+    "prestress_new.dat",  # six bodies: tet4, tet10, hex8, hex8 F-bar, hex20, hex27, all with PRESTRESS_TECH mulf (tests/test_mixed_cells.py)
     "sohex8_incompr_block.dat",
     "sohex8_incompr_block_nln.dat",
     "sohex8_easfull_patchtest.dat",

@@ -188,6 +188,8 @@ class Problem:
                     self.face_lists.append((c, ft, np.array([nodes for cc, nodes, f in self.faces if cc is c and f == ft], np.int32)))
                 continue
             fl = [self._ordered_face(nodes, rs) for cc, nodes, rs in self.faces if cc is c]
+            if not fl:  # part of a mixed mesh: the faces of this condition belong to another group
+                continue
             self.face_lists.append((c, {4: 0, 9: 1, 6: 2}[len(fl[0])], np.array(fl, np.int32)))
         for c in fx.get("vol_neumann", []):
             assert c["type"] == "Live" and not any(c["onoff"][3:])
@@ -457,6 +459,9 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, 
                     if (a or b) if combi == "Or" else (a and b):
                         break
                 history.append(norms)
+                if p.prestress_time is not None and step * dt <= p.prestress_time + 1.0e-15:
+                    update_prestress(d)
+                    d = np.zeros(n)
                 continue
             for _ in range(maxiter):
                 fint, K = assemble(d)

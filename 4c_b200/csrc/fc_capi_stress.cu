@@ -184,9 +184,24 @@ namespace
     }
     if (!d_nodal) return FC_OK;
     if constexpr (CT == fc::NURBS27)
-      // the reference inverts the element's own basis at the Gauss points (evaluate_gauss_points_to_nurbs_knots_extrapolation_matrix,
-      // 4C_fem_general_utils_gauss_point_extrapolation.cpp:386-420): one 27 x 27 system per element, not built
-      return fail(ctx, FC_ERR_UNSUPPORTED, "nurbs27: Gauss-point output only, no extrapolation to the control points");
+    {
+      std::vector<int> count((size_t)ctx->n_col_nodes, 0);
+      for (int n : ctx->h_conn) count[n]++;
+      int* d_count = nullptr;
+      FC_CUDA(dev_upload(d_count, count.data(), count.size(), ctx->stream));
+      FC_CUDA(cudaMemsetAsync(d_nodal, 0, sizeof(double) * 6 * (size_t)ctx->n_row_nodes, ctx->stream));
+      if (ctx->n_ele > 0)
+      {
+        fc::k_extrapolate_nurbs27<<<(ctx->n_ele + 3) / 4, 128, 0, ctx->stream>>>(ctx->d_conn, ctx->n_ele, ctx->n_row_nodes, ctx->d_dNtab, d_count,
+            d_gp, d_nodal);
+        ctx->launches += 2;
+      }
+      cudaError_t e = cudaGetLastError();
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+      cudaFree(d_count);
+      FC_CUDA(e);
+      return FC_OK;
+    }
     else
     {
     std::vector<double> E;

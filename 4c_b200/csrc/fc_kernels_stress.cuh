@@ -9,6 +9,7 @@
 // Jacobi rotations.
 // Post-processing, not on the per-iteration path: one thread per (element, Gauss point) / (element, node).
 #pragma once
+#include "fc_nurbs.cuh"
 #include "fc_kernels_generic.cuh"
 #include "fc_kernels_hex8eas.cuh"
 #include "fc_kernels_shell.cuh"
@@ -269,6 +270,68 @@ namespace fc
     }
     const double inv = 1.0 / (double)node_elecount[node];
     for (int c = 0; c < 6; ++c) red_add(nodal + 6 * (size_t)node + c, v[c] * inv);
+  }
+
+  // nurbs27: Gauss points -> control points.  The reference inverts the element's own basis at the Gauss points
+  // (evaluate_gauss_points_to_nurbs_knots_extrapolation_matrix, 4C_fem_general_utils_gauss_point_extrapolation.cpp:386-420, with
+  // evaluate_nurbs_base_shape_functions_at_gauss_points :116-146: M[gp][a] = N_a(xi_gp), base cell = the cell itself): one
+  // 27 x 27 system with six right-hand sides per element.  One warp per element: Gauss-Jordan with partial pivoting on the
+  // augmented matrix in shared memory, lane r owns row r; then the averaged assembly of the other cells.
+  static __global__ void __launch_bounds__(128) k_extrapolate_nurbs27(const int* __restrict__ conn, int n_ele, int n_row_nodes,
+      const double* __restrict__ tab, const int* __restrict__ node_elecount, const double* __restrict__ gp_stress, double* __restrict__ nodal)
+  {
+    constexpr int N = 27, W = N + 6;
+    __shared__ double sA[4][N][W + 1];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int e = blockIdx.x * 4 + warp;
+    if (e >= n_ele) return;
+    double(*A)[W + 1] = sA[warp];
+    const double* Ntab = tab + (size_t)e * NurbsTab::stride + NurbsTab::oN;  // [gp][a]
+    if (lane < N)
+    {
+      for (int a = 0; a < N; ++a) A[lane][a] = Ntab[lane * N + a];
+      for (int c = 0; c < 6; ++c) A[lane][N + c] = gp_stress[((size_t)e * N + lane) * 6 + c];
+    }
+    __syncwarp();
+    for (int k = 0; k < N; ++k)
+    {
+      // pivot: the largest |A[r][k]| over r >= k
+      double v = (lane >= k && lane < N) ? fabs(A[lane][k]) : -1.0;
+      int idx = lane;
+      for (int o = 16; o > 0; o >>= 1)
+      {
+        const double v2 = __shfl_xor_sync(0xFFFFFFFFu, v, o);
+        const int i2 = __shfl_xor_sync(0xFFFFFFFFu, idx, o);
+        if (v2 > v || (v2 == v && i2 < idx))
+        {
+          v = v2;
+          idx = i2;
+        }
+      }
+      if (idx != k)  // swap rows k and idx, one column per lane (33 columns: two passes)
+        for (int c = lane; c < W; c += 32)
+        {
+          const double t = A[k][c];
+          A[k][c] = A[idx][c];
+          A[idx][c] = t;
+        }
+      __syncwarp();
+      const double piv = 1.0 / A[k][k];
+      const double fac = (lane < N && lane != k) ? A[lane][k] * piv : 0.0;
+      __syncwarp();
+      if (lane < N && lane != k)
+        for (int c = k; c < W; ++c) A[lane][c] -= fac * A[k][c];
+      __syncwarp();
+    }
+    if (lane < N)
+    {
+      const int node = conn[(size_t)e * N + lane];
+      if (node < n_row_nodes)
+      {
+        const double inv = 1.0 / ((double)node_elecount[node] * A[lane][lane]);
+        for (int c = 0; c < 6; ++c) red_add(nodal + 6 * (size_t)node + c, A[lane][N + c] * inv);
+      }
+    }
   }
 
   // solid shells (k_shell, fc_kernels_shell.cuh): ANS strains of the Gauss point, optionally enhanced with the element's alpha; the

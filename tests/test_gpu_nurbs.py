@@ -83,9 +83,18 @@ def test_assembled_system(fc, oracle, form, mat):
         for e in range(len(p.conn)):
             ref = job.element_gp_stress(e, u, st)[1]
             assert np.max(np.abs(gp[e] - ref)) <= 1e-12 * np.max(np.abs(ref))
-    with pytest.raises(fc.FourCError) as ei:  # no extrapolation to the control points
-        s.evaluate_stress(u.reshape(-1), fc.FC_STRESS_CAUCHY)
-    assert ei.value.code == fc.FC_ERR_UNSUPPORTED
+    # values at the control points: per element the inverse of its own basis at the Gauss points
+    # (evaluate_gauss_points_to_nurbs_knots_extrapolation_matrix), averaged over the elements of a control point
+    gp, nodal = s.evaluate_stress(u.reshape(-1), fc.FC_STRESS_CAUCHY)
+    gxi = oracle.gauss_rule(p.ct)[0]
+    acc, cnt = np.zeros((len(X), 6)), np.zeros(len(X))
+    for e, en in enumerate(p.conn):
+        oracle.set_nurbs_element(p.ele_knots[e], p.weights[en])
+        M = np.array([oracle.shape(p.ct, xi) for xi in gxi])  # [gp][a]
+        acc[en] += np.linalg.solve(M, job.element_gp_stress(e, u, fc.FC_STRESS_CAUCHY)[1])
+        cnt[en] += 1
+    ref = acc / cnt[:, None]
+    assert np.max(np.abs(nodal - ref)) <= 1e-10 * np.max(np.abs(ref))
     s.close()
 
 

@@ -49,6 +49,10 @@ class Problem:
         """node_param_coords(ct) -> (nen, 3) parameter coordinates of the element nodes (reference numbering)"""
         self.fx = fx
         ids = sorted(int(k) for k in fx["nodes"])
+        if not fx.get("part_of_mixed_mesh"):
+            # nodes that no element uses carry no DOFs that anything couples to (inputs derived from a richer mesh keep them)
+            used = {n for e in fx["elements"] for n in e["nodes"]}
+            ids = [i for i in ids if i in used]
         self.ids = ids
         self.index = {nid: i for i, nid in enumerate(ids)}
         self.X = np.array([fx["nodes"][str(i)] for i in ids], float)
@@ -148,7 +152,7 @@ class Problem:
         for order, key, topo in ((2, "dirich", "dsurf"), (1, "dirich_line", "dline"), (0, "dirich_point", "dnode")):
             for c in fx.get(key, []):
                 assert not any(c["val"]) or dyn.get("DYNAMICTYPE", "GenAlpha") == "Statics"
-                for n in fx[topo][str(c["E"])]:
+                for n in (m for m in fx[topo][str(c["E"])] if m in self.index):
                     for d in range(3):
                         lid = 3 * self.index[n] + d
                         if c["onoff"][d]:
@@ -162,7 +166,7 @@ class Problem:
         self.faces = []
         for c in fx["neumann"]:
             assert c["type"] == "Live" and not any(c["onoff"][3:])
-            sset = {self.index[n] for n in fx["dsurf"][str(c["E"])]}
+            sset = {self.index[n] for n in fx["dsurf"][str(c["E"])] if n in self.index}
             for e, en in enumerate(self.conn):
                 if self.ct == 8:
                     for sid, loc in enumerate(NURBS27_FACES):
@@ -193,7 +197,7 @@ class Problem:
             self.face_lists.append((c, {4: 0, 9: 1, 6: 2}[len(fl[0])], np.array(fl, np.int32)))
         for c in fx.get("vol_neumann", []):
             assert c["type"] == "Live" and not any(c["onoff"][3:])
-            vset = {self.index[n] for n in fx["dvol"][str(c["E"])]}
+            vset = {self.index[n] for n in fx["dvol"][str(c["E"])] if n in self.index}
             els = [e for e, en in enumerate(self.conn) if all(int(a) in vset for a in en)]
             assert els
             self.vol_lists.append((c, np.array(els, np.int32)))

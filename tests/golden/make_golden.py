@@ -168,6 +168,8 @@ CASES = [
     "error_analytical_beam_cantilever_end_surface_load_with_poissons_effect.dat",
     "error_analytical_beam_cantilever_with_bodyload_without_poissons_effect.dat",
     "sohex20_patchtest_nl_cost_drt.dat",  # hex20 elements on the node set of a hex27 mesh: the unused nodes are dropped by the replay
+    "sosh8_cooks_nl.dat",  # Cook's membrane with 16 eas_mild elements
+    "sohex8_easmild_cooks_nl_dynsta.dat",  # the 64-element one with TOLRES 1e-6
     "soweg6_disp_patchtest.dat",  # 4 hex8 + 6 wedge6 in one discretization (tests/test_mixed_cells.py)
     "prestress_new.dat",  # six bodies: tet4, tet10, hex8, hex8 F-bar, hex20, hex27, all with PRESTRESS_TECH mulf (tests/test_mixed_cells.py)
     "sohex8_incompr_block.dat",

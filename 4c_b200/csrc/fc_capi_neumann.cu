@@ -32,7 +32,8 @@ namespace
 
   // shared body: mode 0 = add the load into f_ext, 1 = hand out the Gauss-point reference coordinates
   int neumann_run(fc_ctx* ctx, bool surface, int face_type, int n_items, const int* items, const int* onoff, const double* val,
-      const double* gp_factor, double* out, bool coords, const int* surface_id = nullptr /* faces of nurbs27: items = parent elements */)
+      const double* gp_factor, double* out, bool coords, const int* surface_id = nullptr /* faces of nurbs27: items = parent elements */,
+      bool ortho = false, const double* u_col = nullptr /* orthopressure: the configuration is X + u */)
   {
     const bool nurbs_face = surface && surface_id != nullptr;
     if (!ctx || ctx->celltype < 0) return fail(ctx, FC_ERR_INVALID, "set_mesh must precede the Neumann evaluation");
@@ -63,6 +64,10 @@ namespace
     d_items = t_items;
     int* t_sid = nullptr;
     if (nurbs_face) FC_CUDA(dev_upload(t_sid, surface_id, (size_t)n_items, ctx->stream));
+    const double* d_u = nullptr;
+    double* t_u = nullptr;
+    if (ortho && u_col)
+      if (int rcu = stage_in(ctx, u_col, (size_t)ctx->n_col_dof, &d_u, &t_u)) return rcu;
     const double* d_fac = nullptr;
     double* t_fac = nullptr;
     int rc = coords ? FC_OK : stage_in(ctx, gp_factor, (size_t)n_items * ngp * 3, &d_fac, &t_fac);
@@ -86,7 +91,11 @@ namespace
       else if (surface)
       {
         const unsigned gs = (unsigned)((n_items + bs - 1) / bs);
-#define FC_NEUMANN_SURFACE(FT) fc::k_neumann_surface<FT><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc)
+#define FC_NEUMANN_SURFACE(FT)                                                                                                     \
+  if (ortho)                                                                                                                       \
+    fc::k_neumann_surface<FT, true><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc, d_u); \
+  else                                                                                                                             \
+    fc::k_neumann_surface<FT><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, d_items, n_items, V, d_fac, ctx->n_row_nodes, f, xc)
         switch (face_type)
         {
           case FC_FACE_QUAD4: FC_NEUMANN_SURFACE(fc::QUAD4); break;
@@ -121,6 +130,7 @@ namespace
     if (e == cudaSuccess) e = es;
     cudaFree(t_items);
     if (t_sid) cudaFree(t_sid);
+    if (t_u) cudaFree(t_u);
     if (t_fac) cudaFree(t_fac);
     if (t_out) cudaFree(t_out);
     if (rc != FC_OK) return rc;
@@ -150,6 +160,14 @@ extern "C"
   int fc_solid_neumann_volume_gp_coords(fc_ctx* ctx, int n_ele, const int* ele_lids, double* gp_coords)
   {
     return neumann_run(ctx, false, 0, n_ele, ele_lids, nullptr, nullptr, nullptr, gp_coords, true);
+  }
+
+  int fc_solid_neumann_surface_orthopressure(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, const double* u_col,
+      double pressure, const double* gp_factor, double* f_ext)
+  {
+    const int onoff[3] = {1, 0, 0};
+    const double val[3] = {pressure, 0.0, 0.0};
+    return neumann_run(ctx, true, face_type, n_faces, face_nodes, onoff, val, gp_factor, f_ext, false, nullptr, true, u_col);
   }
 
   int fc_solid_neumann_surface_nurbs(fc_ctx* ctx, int n_faces, const int* parent_ele, const int* surface_id, const int* onoff,

@@ -22,9 +22,14 @@ namespace fc
   // One instance per face type: every loop bound is a compile-time constant.  (A single kernel with the face type as a
   // run-time argument - bounds read from a table - was miscompiled by nvcc 12.9 -O3 for tri6: illegal address in the
   // accumulation loop, clean with -G.)
-  template <int FT>
+  // ORTHO: TYPE pseudo_orthopressure / orthopressure (4C_solid_3D_ele_surface_evaluate.cpp:84-96, 139-176, 318-358): the pressure
+  // V.val[0] acts along the normal of the configuration X + u (u = the last converged displacements for pseudo_orthopressure, the
+  // current iterate for orthopressure, none while MULF prestressing is active); the normal is the cross product of the two
+  // tangents, its length the area element (surface_integration, :382-394):  f[a][dim] += N_a normal[dim] w functfac val[0]
+  template <int FT, bool ORTHO = false>
   static __global__ void k_neumann_surface(const double* __restrict__ X, const int* __restrict__ face_nodes, int n_faces, NeumannVal V,
-      const double* __restrict__ gp_factor, int n_row_nodes, double* __restrict__ f, double* __restrict__ gp_coords)
+      const double* __restrict__ gp_factor, int n_row_nodes, double* __restrict__ f, double* __restrict__ gp_coords,
+      const double* __restrict__ u = nullptr)
   {
     const int face = blockIdx.x * blockDim.x + threadIdx.x;
     if (face >= n_faces) return;
@@ -34,7 +39,7 @@ namespace fc
     for (int a = 0; a < nen; ++a)
     {
       nodes[a] = face_nodes[(size_t)face * nen + a];
-      for (int i = 0; i < 3; ++i) P[a][i] = X[3 * (size_t)nodes[a] + i];
+      for (int i = 0; i < 3; ++i) P[a][i] = X[3 * (size_t)nodes[a] + i] + (ORTHO && u ? u[3 * (size_t)nodes[a] + i] : 0.0);
     }
     double fa[nen][3];
     for (int a = 0; a < nen; ++a) fa[a][0] = fa[a][1] = fa[a][2] = 0.0;
@@ -60,6 +65,15 @@ namespace fc
           g1[i] += dr[a] * P[a][i];
           g2[i] += ds[a] * P[a][i];
         }
+      if (ORTHO)
+      {
+        const double normal[3] = {g1[1] * g2[2] - g1[2] * g2[1], g1[2] * g2[0] - g1[0] * g2[2], g1[0] * g2[1] - g1[1] * g2[0]};
+        const double functfac = gp_factor ? gp_factor[((size_t)face * ngp + g) * 3] : 1.0;
+        const double fac = w * functfac * V.val[0];
+        for (int a = 0; a < nen; ++a)
+          for (int dim = 0; dim < 3; ++dim) fa[a][dim] += N[a] * normal[dim] * fac;
+        continue;
+      }
       const double m11 = g1[0] * g1[0] + g1[1] * g1[1] + g1[2] * g1[2];
       const double m22 = g2[0] * g2[0] + g2[1] * g2[1] + g2[2] * g2[2];
       const double m12 = g1[0] * g2[0] + g1[1] * g2[1] + g1[2] * g2[2];
@@ -76,7 +90,7 @@ namespace fc
     for (int a = 0; a < nen; ++a)
       if (nodes[a] < n_row_nodes)
         for (int dof = 0; dof < 3; ++dof)
-          if (V.onoff[dof]) red_add(f + 3 * (size_t)nodes[a] + dof, fa[a][dof]);
+          if (ORTHO || V.onoff[dof]) red_add(f + 3 * (size_t)nodes[a] + dof, fa[a][dof]);
   }
 
   // Faces of nurbs27 elements (nurbs9, quad_9point): one thread per face, named by parent element and surface number like the

@@ -136,6 +136,12 @@ extern "C"
       surface_neumann_live(ft, x + (size_t)k * nn * 3, onoff, val, functfac ? functfac + (size_t)k * ng * 3 : nullptr,
           fe ? fe + (size_t)k * nn * 3 : nullptr, gp_coord ? gp_coord + (size_t)k * ng * 3 : nullptr);
   }
+  void oracle_surface_neumann_orthopressure(int ft, int n, const double* xc, double value, const double* functfac, double* fe)
+  {
+    const int nn = face_num_nodes(ft), ng = face_num_gp(ft);
+    for (int k = 0; k < n; ++k)
+      surface_neumann_orthopressure(ft, xc + (size_t)k * nn * 3, value, functfac ? functfac + (size_t)k * ng * 3 : nullptr, fe + (size_t)k * nn * 3);
+  }
   void oracle_volume_neumann(int ct, int n, const double* X, const int* onoff, const double* val, const double* functfac, double* fe,
       double* gp_coord)
   {

@@ -294,6 +294,29 @@ namespace fc_oracle
     }
   }
 
+  // TYPE pseudo_orthopressure / orthopressure (4C_solid_3D_ele_surface_evaluate.cpp:318-358): xc [numnode][3] = the configuration the
+  // load type asks for (:139-176); ortho_value = val[0]; normal of surface_integration (:382-394), its length the area element
+  inline void surface_neumann_orthopressure(int ft, const double* xc, double ortho_value, const double* functfac, double* elevec1)
+  {
+    const int numnode = face_num_nodes(ft), nquad = face_num_gp(ft);
+    double qxg[9][2], qwgt[9];
+    gauss_rule_2d(ft, qxg, qwgt);
+    for (int gp = 0; gp < nquad; ++gp)
+    {
+      double funct[9], deriv[2][9];
+      shape_function_2d(ft, qxg[gp][0], qxg[gp][1], funct, deriv[0], deriv[1]);
+      double dxyzdrs[2][3] = {{0, 0, 0}, {0, 0, 0}};
+      for (int a = 0; a < 2; ++a)
+        for (int i = 0; i < 3; ++i)
+          for (int n = 0; n < numnode; ++n) dxyzdrs[a][i] += deriv[a][n] * xc[3 * n + i];
+      const double normal[3] = {dxyzdrs[0][1] * dxyzdrs[1][2] - dxyzdrs[0][2] * dxyzdrs[1][1],
+          dxyzdrs[0][2] * dxyzdrs[1][0] - dxyzdrs[0][0] * dxyzdrs[1][2], dxyzdrs[0][0] * dxyzdrs[1][1] - dxyzdrs[0][1] * dxyzdrs[1][0]};
+      const double fac = qwgt[gp] * (functfac ? functfac[3 * gp] : 1.0) * ortho_value;  // normalfac = 1 off NURBS
+      for (int node = 0; node < numnode; ++node)
+        for (int dim = 0; dim < 3; ++dim) elevec1[node * 3 + dim] += funct[node] * normal[dim] * fac;
+    }
+  }
+
   // X [nen][3]; element_force_vector [nen][3] +=; gauss rule = get_gauss_rule_stiffness_matrix<celltype>
   inline void volume_neumann_live(int ct, const double* X, const int* onoff, const double* value, const double* functfac,
       double* element_force_vector, double* gp_coord)

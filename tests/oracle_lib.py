@@ -189,6 +189,15 @@ def surface_neumann(ft, x, onoff, val, functfac=None, want_coords=False):
     return (fe, gc) if want_coords else fe
 
 
+def surface_neumann_orthopressure(ft, xc, value, functfac=None):
+    """xc: (n, nfn, 3) coordinates of the configuration the load type asks for -> fe (n, nfn, 3)"""
+    xc = _d(xc)
+    fe = np.zeros((xc.shape[0], FACE_NEN[ft], 3))
+    ff = _d(functfac) if functfac is not None else None
+    lib.oracle_surface_neumann_orthopressure(C.c_int(ft), C.c_int(xc.shape[0]), _p(xc), C.c_double(value), _p(ff), _p(fe))
+    return fe
+
+
 def volume_neumann(ct, X, onoff, val, functfac=None, want_coords=False):
     """X: (n, nen, 3) -> fe (n, nen, 3) [, gp_coord (n, ngp, 3)]"""
     X = _d(X)

@@ -165,7 +165,8 @@ class Problem:
         self.xi_nodes = np.asarray(node_param_coords(self.ct), float)
         self.faces = []
         for c in fx["neumann"]:
-            assert c["type"] == "Live" and not any(c["onoff"][3:])
+            # Live, or pseudo_orthopressure: pressure VAL[0] along the normal of the last converged configuration
+            assert c["type"] in ("Live", "pseudo_orthopressure") and not any(c["onoff"][3:])
             sset = {self.index[n] for n in fx["dsurf"][str(c["E"])] if n in self.index}
             for e, en in enumerate(self.conn):
                 if self.ct == 8:
@@ -202,6 +203,7 @@ class Problem:
             assert els
             self.vol_lists.append((c, np.array(els, np.int32)))
         self._gp_cache = {}
+        self.has_ortho = any(c["type"] != "Live" for c in fx["neumann"])
 
     # faces of the parent cell as (local node ids, in-face parameter coordinates of those nodes)
     def _element_faces(self):
@@ -306,7 +308,8 @@ class Problem:
                 fac[..., d] = [[self.funct(cond["funct"][d], x, t) for x in row] for row in coords]
         return fac
 
-    def f_ext(self, t):
+    def f_ext(self, t, d_conv=None):
+        """d_conv: the last converged displacements (the configuration of pseudo_orthopressure loads)"""
         if self.neumann is not None:
             # Neumann backend (oracle restatement or the CUDA library): the driver only evaluates the FUNCT expressions at the
             # Gauss-point coordinates the backend hands out
@@ -314,6 +317,9 @@ class Problem:
             f = np.zeros(self.n_dof)
             for i, (c, ft, fn) in enumerate(self.face_lists):
                 xg = self._gp_cache.setdefault(("s", i), nb.surface_coords(ft, fn))
+                if c["type"] == "pseudo_orthopressure":
+                    nb.surface_orthopressure(ft, fn, d_conv, c["val"][0], self._factors(("s", i), c, xg, t), f)
+                    continue
                 nb.surface(ft, fn, c["onoff"], c["val"], self._factors(("s", i), c, xg, t), f)
             for i, (c, els) in enumerate(self.vol_lists):
                 xg = self._gp_cache.setdefault(("v", i), nb.volume_coords(els))
@@ -371,6 +377,10 @@ class OracleNeumann:
     def volume_coords(self, els):
         return self.o.volume_neumann(self.p.ct, self.p.X[self.p.conn[els]], [0, 0, 0], [0.0, 0.0, 0.0], want_coords=True)[1]
 
+    def surface_orthopressure(self, ft, fn, d, value, fac, f):
+        xc = self.p.X[fn] + (0.0 if d is None else d.reshape(-1, 3)[fn])
+        np.add.at(f.reshape(-1, 3), fn, self.o.surface_neumann_orthopressure(ft, xc, value, fac))
+
     def surface(self, ft, fn, onoff, val, fac, f):
         if ft == 6:
             for nodes, fe in self._nurbs_faces(fn, onoff, val, fac, False):
@@ -396,6 +406,9 @@ class CudaNeumann:
     def volume_coords(self, els):
         return self.s.neumann_volume_gp_coords(els)
 
+    def surface_orthopressure(self, ft, fn, d, value, fac, f):
+        self.s.neumann_surface_orthopressure(ft, fn, d, value, f, gp_factor=fac)
+
     def surface(self, ft, fn, onoff, val, fac, f):
         if ft == 6:
             return self.s.neumann_surface_nurbs(fn[:, 0], fn[:, 1], onoff, val, f, gp_factor=fac)
@@ -411,6 +424,10 @@ def _solve(A, rhs, fixed):
     A[fixed, :] = 0.0
     A[fixed, fixed] = 1.0
     rhs[fixed] = 0.0
+    if len(rhs) > 1500:  # the larger meshes: sparse LU instead of a dense one (minutes -> seconds)
+        import scipy.sparse as sp
+        import scipy.sparse.linalg as spla
+        return spla.splu(sp.csc_matrix(A), permc_spec="MMD_AT_PLUS_A", diag_pivot_thresh=0.0, options=dict(SymmetricMode=True)).solve(rhs)
     return np.linalg.solve(A, rhs)
 
 
@@ -439,7 +456,7 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, 
     history = []
     if p.dynamic == "Statics":
         for step in range(1, p.numstep + 1):
-            fext = p.f_ext(step * dt)
+            fext = p.f_ext(step * dt, d.copy()) if p.has_ortho else p.f_ext(step * dt)
             norms = []
             for lid, v, fid in p.prescribed:  # prescribed displacements of this step
                 d[lid] = v * p.funct(fid, p.X[lid // 3], step * dt)

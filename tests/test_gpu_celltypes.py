@@ -126,6 +126,28 @@ def test_mass_and_neumann_parity(fc, oracle, name):
     s.close()
 
 
+@pytest.mark.parametrize("name", ["solid_ele_hex8_Standard_eas_none_dynamic", "solid_ele_hex20_Standard_dynamic", "solid_ele_tet10_Standard_dynamic",
+                                  "solid_ele_hex18_Standard_dynamic"])
+def test_orthopressure_parity(fc, oracle, name):
+    """TYPE (pseudo_)orthopressure on the loaded faces of the reference's inputs: pressure along the normal of X + u, and of X"""
+    p, X, u = distorted(oracle, name)
+    s = fc.Solid(0)
+    s.set_mesh(p.ct, DISP, X, p.node_gid, np.zeros(len(X), np.int32), p.conn, p.ele_gid)
+    n_row = 3 * len(X)
+    rng = np.random.default_rng(4)
+    assert p.face_lists
+    for c, ft, faces in p.face_lists:
+        fac = 1.0 + rng.random((len(faces), fc.FACE_NGP[ft], 3))
+        for uu in (u, None):
+            xc = X[faces] + (0.0 if uu is None else uu[faces])
+            f_ref = np.full(n_row, 0.5)
+            np.add.at(f_ref.reshape(-1, 3), faces, oracle.surface_neumann_orthopressure(ft, xc, -1.7, fac))
+            f = np.full(n_row, 0.5)
+            s.neumann_surface_orthopressure(ft, faces, None if uu is None else uu.reshape(-1), -1.7, f, gp_factor=fac)
+            assert np.max(np.abs(f - f_ref)) <= 1e-14 * np.max(np.abs(f_ref))
+    s.close()
+
+
 @pytest.mark.parametrize("name,form", [("solid_ele_hex20_Standard_dynamic", DISP), ("solid_ele_tet4_Standard_dynamic", DISP),
                                        ("solid_ele_wedge6_Standard_dynamic", DISP), ("solid_ele_pyramid5_Standard_dynamic", DISP),
                                        ("solid_ele_pyramid5_Standard_dynamic", FBAR), ("solid_ele_hex18_Standard_dynamic", DISP)])

@@ -39,6 +39,16 @@ FACE_TABLES = {
 }
 
 
+# the same for hex8 / hex27 / tet10 (:45-63), used where the orientation of a face matters (orthopressure loads: outward normals);
+# their Live loads keep the orientation-free search of Problem._element_faces
+ORIENTED_FACES = {
+    0: [(0, f) for f in ([0, 3, 2, 1], [0, 1, 5, 4], [1, 2, 6, 5], [2, 3, 7, 6], [0, 4, 7, 3], [4, 5, 6, 7])],
+    1: [(1, f) for f in ([0, 3, 2, 1, 11, 10, 9, 8, 20], [0, 1, 5, 4, 8, 13, 16, 12, 21], [1, 2, 6, 5, 9, 14, 17, 13, 22],
+                         [2, 3, 7, 6, 10, 15, 18, 14, 23], [0, 4, 7, 3, 12, 19, 15, 11, 24], [4, 5, 6, 7, 16, 17, 18, 19, 25])],
+    2: [(2, f) for f in ([0, 1, 3, 4, 8, 7], [1, 2, 3, 5, 9, 8], [0, 3, 2, 7, 9, 6], [0, 2, 1, 6, 5, 4])],
+}
+
+
 def load(name):
     with open(os.path.join(GOLDEN, name + ".json")) as f:
         return json.load(f)
@@ -164,6 +174,8 @@ class Problem:
         self.prescribed = [(lid, v, f) for lid, (v, f) in sorted(prescribed.items()) if toggle[lid] and v != 0.0]
         self.xi_nodes = np.asarray(node_param_coords(self.ct), float)
         self.faces = []
+        self.has_ortho = any(c["type"] != "Live" for c in fx["neumann"])
+        face_tables = {**FACE_TABLES, **ORIENTED_FACES} if self.has_ortho else FACE_TABLES
         for c in fx["neumann"]:
             # Live, or pseudo_orthopressure: pressure VAL[0] along the normal of the last converged configuration
             assert c["type"] in ("Live", "pseudo_orthopressure") and not any(c["onoff"][3:])
@@ -174,8 +186,8 @@ class Problem:
                         if all(int(en[a]) in sset for a in loc):
                             self.faces.append((c, (e, sid), 6))  # nurbs9 face: named by parent element and surface number
                     continue
-                if self.ct in FACE_TABLES:
-                    for ft, loc in FACE_TABLES[self.ct]:
+                if self.ct in face_tables:
+                    for ft, loc in face_tables[self.ct]:
                         if all(int(en[a]) in sset for a in loc):
                             self.faces.append((c, en[loc], ft))  # already in the surface cell's node order
                     continue
@@ -188,7 +200,7 @@ class Problem:
         self.neumann = None  # backend with surface(), volume(), *_coords(); None = the numpy restatement below (surfaces only)
         self.face_lists, self.vol_lists = [], []
         for c in fx["neumann"]:
-            if self.ct in FACE_TABLES or self.ct == 8:
+            if self.ct in face_tables or self.ct == 8:
                 for ft in sorted({ft for cc, _, ft in self.faces if cc is c}):
                     self.face_lists.append((c, ft, np.array([nodes for cc, nodes, f in self.faces if cc is c and f == ft], np.int32)))
                 continue
@@ -203,7 +215,6 @@ class Problem:
             assert els
             self.vol_lists.append((c, np.array(els, np.int32)))
         self._gp_cache = {}
-        self.has_ortho = any(c["type"] != "Live" for c in fx["neumann"])
 
     # faces of the parent cell as (local node ids, in-face parameter coordinates of those nodes)
     def _element_faces(self):

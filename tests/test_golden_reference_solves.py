@@ -178,6 +178,11 @@ SHELL_CASES = ["solid_ele_hex8_Standard_shell_ans", "solid_ele_hex8_Standard_she
                "solid_ele_wedge6_Standard_shell_eas_ans"]
 
 
+# the two largest replays (6 048 and 6 855 DOFs, 15 load steps, 45 s each on the oracle) run with the GPU tests only, where the
+# CUDA-driven and the oracle-driven solve are both compared with the reference's value
+LARGE_CASES = ["prestress_hex27", "prestress_tet10"]
+
+
 @pytest.mark.parametrize("case", CASES + SHELL_CASES)
 def test_reference_result_description_oracle(oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
@@ -217,7 +222,7 @@ def cuda_backend(fc, p):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("case", CASES + SHELL_CASES)
+@pytest.mark.parametrize("case", CASES + SHELL_CASES + LARGE_CASES)
 def test_reference_result_description_cuda(fc, oracle, case):
     p = sd.Problem(sd.load(case), oracle.node_param_coords)
     s, assemble, mass = cuda_backend(fc, p)

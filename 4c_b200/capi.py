@@ -37,7 +37,7 @@ EXPORTS = [
     "fc_solid_graph_sizes", "fc_solid_get_graph", "fc_solid_set_dirichlet_rows", "fc_solid_evaluate",
     "fc_solid_error_state", "fc_solid_error_allreduce", "fc_solid_zero", "fc_solid_evaluate_mass", "fc_solid_evaluate_stress", "fc_solid_evaluate_stress_noalloc", "fc_solid_neumann_surface", "fc_solid_neumann_volume",
     "fc_solid_neumann_surface_gp_coords", "fc_solid_neumann_volume_gp_coords", "fc_solid_evaluate_elements",
-    "fc_solid_set_nurbs", "fc_solid_neumann_surface_nurbs", "fc_solid_neumann_surface_nurbs_gp_coords", "fc_solid_neumann_surface_orthopressure",
+    "fc_solid_set_nurbs", "fc_solid_neumann_surface_nurbs", "fc_solid_neumann_surface_nurbs_gp_coords", "fc_solid_neumann_surface_orthopressure", "fc_solid_neumann_surface_orthopressure_linearization",
     "fc_solid_set_element_kernel_flags", "fc_solid_halo_set_send", "fc_solid_halo_pack", "fc_solid_halo_set_counts", "fc_solid_halo_exchange",
     "fc_solid_last_kernel_ms", "fc_solid_kernel_ms_history", "fc_solid_kernel_launch_count", "fc_grid_create", "fc_grid_destroy",
     "fc_grid_sizes", "fc_grid_subdivisions", "fc_grid_get_nodes", "fc_grid_get_elements",
@@ -446,6 +446,14 @@ class Solid:
         gf = None if gp_factor is None else (_f64(gp_factor) if isinstance(gp_factor, np.ndarray) else gp_factor)
         self._chk(lib().fc_solid_neumann_surface_orthopressure(self.h, C.c_int(face_type), C.c_int(len(fn)), _ptr(fn), _ptr(uu),
                                                               C.c_double(pressure), _ptr(gf), _ptr(f_ext)))
+
+    def neumann_surface_orthopressure_linearization(self, face_type, face_nodes, u_col, pressure, K_values, gp_factor=None):
+        """LOADLIN yes: adds the load stiffness of the orthopressure load into K_values [nnz]"""
+        fn = _i32(face_nodes).reshape(-1, FACE_NEN[face_type])
+        uu = None if u_col is None else (u_col if hasattr(u_col, "data_ptr") else _f64(u_col))
+        gf = None if gp_factor is None else (_f64(gp_factor) if isinstance(gp_factor, np.ndarray) else gp_factor)
+        self._chk(lib().fc_solid_neumann_surface_orthopressure_linearization(self.h, C.c_int(face_type), C.c_int(len(fn)), _ptr(fn), _ptr(uu),
+                                                                            C.c_double(pressure), _ptr(gf), _ptr(K_values)))
 
     def neumann_surface_nurbs(self, parent_ele, surface_id, onoff, val, f_ext, gp_factor=None):
         """faces of nurbs27 elements, named by parent column element and the parent's surface number 0..5"""

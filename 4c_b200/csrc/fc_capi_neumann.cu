@@ -170,6 +170,70 @@ extern "C"
     return neumann_run(ctx, true, face_type, n_faces, face_nodes, onoff, val, gp_factor, f_ext, false, nullptr, true, u_col);
   }
 
+  int fc_solid_neumann_surface_orthopressure_linearization(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, const double* u_col,
+      double pressure, const double* gp_factor, double* K_values)
+  {
+    if (!ctx || ctx->celltype < 0 || !ctx->have_graph) return fail(ctx, FC_ERR_INVALID, "mesh and graph are required");
+    if (face_type < FC_FACE_QUAD4 || face_type > FC_FACE_QUAD6) return fail(ctx, FC_ERR_UNSUPPORTED, "surface cell type");
+    if (n_faces < 0 || (n_faces > 0 && !face_nodes) || !K_values) return fail(ctx, FC_ERR_INVALID, "faces and K_values are required");
+    if (n_faces == 0) return FC_OK;
+    FC_CUDA(cudaSetDevice(ctx->device));
+    const int per = fc::face_nen(face_type), ngp = fc::face_ngp(face_type);
+    for (size_t i = 0; i < (size_t)n_faces * per; ++i)
+      if (face_nodes[i] < 0 || face_nodes[i] >= ctx->n_col_nodes) return fail(ctx, FC_ERR_INVALID, "face node out of range");
+    int* d_faces = nullptr;
+    FC_CUDA(dev_upload(d_faces, face_nodes, (size_t)n_faces * per, ctx->stream));
+    const double *d_u = nullptr, *d_fac = nullptr;
+    double *t_u = nullptr, *t_fac = nullptr;
+    int rc = u_col ? stage_in(ctx, u_col, (size_t)ctx->n_col_dof, &d_u, &t_u) : FC_OK;
+    if (rc == FC_OK) rc = stage_in(ctx, gp_factor, (size_t)n_faces * ngp * 3, &d_fac, &t_fac);
+    const bool K_dev = is_device_ptr(K_values);
+    double* d_K = K_values;
+    cudaError_t e = cudaSuccess;
+    if (rc == FC_OK && !K_dev)
+    {
+      e = ensure_cap(ctx->d_stage_K, ctx->stage_K_cap, (size_t)ctx->nnz);
+      d_K = ctx->d_stage_K;
+      if (e == cudaSuccess) e = cudaMemcpyAsync(d_K, K_values, sizeof(double) * (size_t)ctx->nnz, cudaMemcpyHostToDevice, ctx->stream);  // +=
+    }
+    int missing = 0;
+    if (rc == FC_OK && e == cudaSuccess)
+    {
+      ctx->h_err_pinned[0] = 0;
+      e = cudaMemcpyAsync(ctx->d_err, ctx->h_err_pinned, sizeof(int), cudaMemcpyHostToDevice, ctx->stream);
+      const int bs = 64;
+      const unsigned gs = (unsigned)((n_faces + bs - 1) / bs);
+      const unsigned char* dbc = ctx->have_dbc ? ctx->d_dbc : nullptr;
+#define FC_ORTHO_LIN(FT)                                                                                                                 \
+  fc::k_orthopressure_linearization<FT><<<gs, bs, 0, ctx->stream>>>(ctx->d_X, d_u, d_faces, n_faces, pressure, d_fac, ctx->n_row_nodes, \
+      ctx->d_nodeptr, ctx->d_nodeadj, ctx->d_node_rowbase, ctx->d_node_rowlen, dbc, d_K, ctx->d_err)
+      switch (face_type)
+      {
+        case FC_FACE_QUAD4: FC_ORTHO_LIN(fc::QUAD4); break;
+        case FC_FACE_QUAD9: FC_ORTHO_LIN(fc::QUAD9); break;
+        case FC_FACE_TRI6: FC_ORTHO_LIN(fc::TRI6); break;
+        case FC_FACE_QUAD8: FC_ORTHO_LIN(fc::QUAD8); break;
+        case FC_FACE_QUAD6: FC_ORTHO_LIN(fc::QUAD6); break;
+        default: FC_ORTHO_LIN(fc::TRI3); break;
+      }
+#undef FC_ORTHO_LIN
+      ctx->launches++;
+      if (e == cudaSuccess) e = cudaGetLastError();
+      if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->h_err_pinned, ctx->d_err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+      if (e == cudaSuccess && !K_dev) e = cudaMemcpyAsync(K_values, d_K, sizeof(double) * (size_t)ctx->nnz, cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    const cudaError_t es = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess) e = es;
+    missing = ctx->h_err_pinned[0];
+    cudaFree(d_faces);
+    if (t_u) cudaFree(t_u);
+    if (t_fac) cudaFree(t_fac);
+    if (rc != FC_OK) return rc;
+    FC_CUDA(e);
+    if (missing > 0) return fail(ctx, FC_ERR_INVALID, "the graph does not couple all nodes of a loaded face");
+    return FC_OK;
+  }
+
   int fc_solid_neumann_surface_nurbs(fc_ctx* ctx, int n_faces, const int* parent_ele, const int* surface_id, const int* onoff,
       const double* val, const double* gp_factor, double* f_ext)
   {

@@ -93,6 +93,86 @@ namespace fc
           if (ORTHO || V.onoff[dof]) red_add(f + 3 * (size_t)nodes[a] + dof, fa[a][dof]);
   }
 
+  // Load linearization of the orthopressure load (LOADLIN yes; 4C_solid_3D_ele_surface_evaluate.cpp:358-376 with
+  // analytical_d_surface_integration :502-549): K[(a, dim)][(b, k)] -= N_a d normal[dim] / d x_(b,k) w functfac val[0], the
+  // derivative of the cross product g1 x g2 with g1 = sum_b dr_b x_b, g2 = sum_b ds_b x_b.  One thread per face; every Gauss point
+  // adds its entries into the owned, non-Dirichlet rows of the CSR values (position of node b in the row of node a by bisection
+  // in the node graph).  Unsymmetric, like the reference's.
+  template <int FT>
+  static __global__ void k_orthopressure_linearization(const double* __restrict__ X, const double* __restrict__ u, const int* __restrict__ face_nodes,
+      int n_faces, double pressure, const double* __restrict__ gp_factor, int n_row_nodes, const long long* __restrict__ nodeptr,
+      const int* __restrict__ nodeadj, const int64_t* __restrict__ node_rowbase, const int* __restrict__ node_rowlen,
+      const unsigned char* __restrict__ dbc, double* __restrict__ K, int* __restrict__ missing)
+  {
+    const int face = blockIdx.x * blockDim.x + threadIdx.x;
+    if (face >= n_faces) return;
+    constexpr int ft = FT, nen = FaceCell<FT>::nen, ngp = FaceCell<FT>::ngp;
+    double P[nen][3];
+    int nodes[nen], pos[nen][nen];
+    for (int a = 0; a < nen; ++a)
+    {
+      nodes[a] = face_nodes[(size_t)face * nen + a];
+      for (int i = 0; i < 3; ++i) P[a][i] = X[3 * (size_t)nodes[a] + i] + (u ? u[3 * (size_t)nodes[a] + i] : 0.0);
+    }
+    for (int a = 0; a < nen; ++a)
+      for (int b = 0; b < nen; ++b)
+      {
+        pos[a][b] = -1;
+        if (nodes[a] >= n_row_nodes) continue;
+        long long lo = nodeptr[nodes[a]], hi = nodeptr[nodes[a] + 1] - 1;
+        const long long base = lo;
+        while (lo <= hi)
+        {
+          const long long mid = (lo + hi) >> 1;
+          const int v = nodeadj[mid];
+          if (v == nodes[b])
+          {
+            pos[a][b] = (int)(mid - base);
+            break;
+          }
+          if (v < nodes[b])
+            lo = mid + 1;
+          else
+            hi = mid - 1;
+        }
+        if (pos[a][b] < 0) atomicAdd(missing, 1);
+      }
+    for (int g = 0; g < ngp; ++g)
+    {
+      double rs[2], w, N[nen], dr[nen], ds[nen];
+      face_gauss_point(ft, g, rs, &w);
+      face_shape(ft, rs, N, dr, ds);
+      double g1[3] = {0, 0, 0}, g2[3] = {0, 0, 0};
+      for (int a = 0; a < nen; ++a)
+        for (int i = 0; i < 3; ++i)
+        {
+          g1[i] += dr[a] * P[a][i];
+          g2[i] += ds[a] * P[a][i];
+        }
+      const double fac = w * (gp_factor ? gp_factor[((size_t)face * ngp + g) * 3] : 1.0) * pressure;
+      for (int a = 0; a < nen; ++a)
+      {
+        if (nodes[a] >= n_row_nodes) continue;
+        const int64_t rb = node_rowbase[nodes[a]];
+        const int rl = node_rowlen[nodes[a]];
+        for (int b = 0; b < nen; ++b)
+        {
+          if (pos[a][b] < 0) continue;
+          // D[dim][k] = d normal[dim] / d x_(b,k)
+          const double D[3][3] = {{0.0, dr[b] * g2[2] - ds[b] * g1[2], ds[b] * g1[1] - dr[b] * g2[1]},
+              {ds[b] * g1[2] - dr[b] * g2[2], 0.0, dr[b] * g2[0] - ds[b] * g1[0]},
+              {dr[b] * g2[1] - ds[b] * g1[1], ds[b] * g1[0] - dr[b] * g2[0], 0.0}};
+          for (int dim = 0; dim < 3; ++dim)
+          {
+            if (dbc && dbc[3 * nodes[a] + dim]) continue;
+            for (int k = 0; k < 3; ++k)
+              if (k != dim) red_add(K + rb + (int64_t)dim * rl + 3 * pos[a][b] + k, -N[a] * D[dim][k] * fac);
+          }
+        }
+      }
+    }
+  }
+
   // Faces of nurbs27 elements (nurbs9, quad_9point): one thread per face, named by parent element and surface number like the
   // reference's surface element; its knot vectors are two of the parent's knot spans
   // (Knotvector::get_boundary_ele_and_parent_knots, 4C_fem_nurbs_discretization_knotvector.cpp:265-413).

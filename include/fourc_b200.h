@@ -279,10 +279,15 @@ extern "C"
    * along the normal of the configuration X + u, f[a][dim] += N_a normal[dim] w functfac VAL[0] with the area-weighted normal
    * of surface_integration (:382-394).  u_col [n_col_dof] (host|device): the last converged displacements for
    * pseudo_orthopressure, the current iterate for orthopressure, NULL = material configuration (what the reference uses while
-   * MULF prestressing is active).  gp_factor as above, its first component is used.  Force only: the load linearization of
-   * LOADLIN yes (analytical_d_surface_integration) is not built. */
+   * MULF prestressing is active).  gp_factor as above, its first component is used.
+   * _linearization: the load stiffness of LOADLIN yes (:358-376 with analytical_d_surface_integration :502-549),
+   * K[(a, dim)][(b, k)] -= N_a d normal[dim] / d x_(b,k) w functfac VAL[0], added into K_values [nnz] (host|device) in the layout of the
+   * stiffness graph: owned rows, Dirichlet rows skipped like the element scatter.  The reference adds it to the tangent with the
+   * same sign (the external force enters the residual with a minus). */
   int fc_solid_neumann_surface_orthopressure(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, const double* u_col,
       double pressure, const double* gp_factor, double* f_ext);
+  int fc_solid_neumann_surface_orthopressure_linearization(fc_ctx* ctx, int face_type, int n_faces, const int* face_nodes, const double* u_col,
+      double pressure, const double* gp_factor, double* K_values);
   /* Surface loads on faces of nurbs27 elements (nurbs9, quad_9point): a face is named like the reference's surface element
    * names it - by its parent column element and the parent's surface number 0..5 (eleNodeNumbering_nurbs27_surfaces,
    * 4C_fem_general_utils_local_connectivity_matrices.hpp:250-253) - because its two knot vectors come from the parent's

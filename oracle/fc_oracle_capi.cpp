@@ -142,6 +142,13 @@ extern "C"
     for (int k = 0; k < n; ++k)
       surface_neumann_orthopressure(ft, xc + (size_t)k * nn * 3, value, functfac ? functfac + (size_t)k * ng * 3 : nullptr, fe + (size_t)k * nn * 3);
   }
+  void oracle_surface_neumann_orthopressure_linearization(int ft, int n, const double* xc, double value, const double* functfac, double* Ke)
+  {
+    const int nn = face_num_nodes(ft), ng = face_num_gp(ft);
+    for (int k = 0; k < n; ++k)
+      surface_neumann_orthopressure_linearization(ft, xc + (size_t)k * nn * 3, value, functfac ? functfac + (size_t)k * ng * 3 : nullptr,
+          Ke + (size_t)k * 9 * nn * nn);
+  }
   void oracle_volume_neumann(int ct, int n, const double* X, const int* onoff, const double* val, const double* functfac, double* fe,
       double* gp_coord)
   {

@@ -317,6 +317,39 @@ namespace fc_oracle
     }
   }
 
+  // Load linearization of the orthopressure load (LOADLIN yes; surface_evaluate.cpp:358-376, analytical_d_surface_integration :502-549):
+  // elemat1 [3 numnode][3 numnode] row-major, (node*3 + dim, dof) -= funct[node] * Dnormal(dim, dof) * fac
+  inline void surface_neumann_orthopressure_linearization(int ft, const double* xc, double ortho_value, const double* functfac, double* elemat1)
+  {
+    const int numnode = face_num_nodes(ft), nquad = face_num_gp(ft), numdof = 3 * numnode;
+    double qxg[9][2], qwgt[9];
+    gauss_rule_2d(ft, qxg, qwgt);
+    for (int gp = 0; gp < nquad; ++gp)
+    {
+      double funct[9], deriv[2][9];
+      shape_function_2d(ft, qxg[gp][0], qxg[gp][1], funct, deriv[0], deriv[1]);
+      double g1[3] = {0, 0, 0}, g2[3] = {0, 0, 0};
+      for (int i = 0; i < 3; ++i)
+        for (int n = 0; n < numnode; ++n)
+        {
+          g1[i] += deriv[0][n] * xc[3 * n + i];
+          g2[i] += deriv[1][n] * xc[3 * n + i];
+        }
+      const double fac = qwgt[gp] * (functfac ? functfac[3 * gp] : 1.0) * ortho_value;
+      for (int dof = 0; dof < numdof; ++dof)
+      {
+        const int nb = dof / 3, k = dof % 3;
+        double dg1[3] = {0, 0, 0}, dg2[3] = {0, 0, 0};
+        dg1[k] = deriv[0][nb];
+        dg2[k] = deriv[1][nb];
+        const double dn[3] = {dg1[1] * g2[2] + g1[1] * dg2[2] - dg1[2] * g2[1] - g1[2] * dg2[1],
+            dg1[2] * g2[0] + g1[2] * dg2[0] - dg1[0] * g2[2] - g1[0] * dg2[2], dg1[0] * g2[1] + g1[0] * dg2[1] - dg1[1] * g2[0] - g1[1] * dg2[0]};
+        for (int node = 0; node < numnode; ++node)
+          for (int dim = 0; dim < 3; ++dim) elemat1[(size_t)(node * 3 + dim) * numdof + dof] -= funct[node] * dn[dim] * fac;
+      }
+    }
+  }
+
   // X [nen][3]; element_force_vector [nen][3] +=; gauss rule = get_gauss_rule_stiffness_matrix<celltype>
   inline void volume_neumann_live(int ct, const double* X, const int* onoff, const double* value, const double* functfac,
       double* element_force_vector, double* gp_coord)

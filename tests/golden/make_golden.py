@@ -170,6 +170,7 @@ CASES = [
     "sohex20_patchtest_nl_cost_drt.dat",  # hex20 elements on the node set of a hex27 mesh: the unused nodes are dropped by the replay
     "sosh8_cooks_nl.dat",  # Cook's membrane with 16 eas_mild elements
     "sohex8_easmild_cooks_nl_dynsta.dat",  # the 64-element one with TOLRES 1e-6
+    "loadlin.dat",  # 300 eas_full hex8 under TYPE orthopressure with LOADLIN yes (follower load and its stiffness)
     "prestress_hex27.dat",  # the same on 144 hex27 (quad9 faces) and
     "prestress_tet10.dat",  # on 1029 tet10 (tri6 faces)
     "prestress_hex20.dat",  # 144 hex20 with MULF under a pseudo_orthopressure load (pressure along the last converged normal)

@@ -198,6 +198,16 @@ def surface_neumann_orthopressure(ft, xc, value, functfac=None):
     return fe
 
 
+def surface_neumann_orthopressure_linearization(ft, xc, value, functfac=None):
+    """LOADLIN yes: load stiffness (n, 3 nfn, 3 nfn) of the orthopressure load on the configuration xc"""
+    xc = _d(xc)
+    nd = 3 * FACE_NEN[ft]
+    Ke = np.zeros((xc.shape[0], nd, nd))
+    ff = _d(functfac) if functfac is not None else None
+    lib.oracle_surface_neumann_orthopressure_linearization(C.c_int(ft), C.c_int(xc.shape[0]), _p(xc), C.c_double(value), _p(ff), _p(Ke))
+    return Ke
+
+
 def volume_neumann(ct, X, onoff, val, functfac=None, want_coords=False):
     """X: (n, nen, 3) -> fe (n, nen, 3) [, gp_coord (n, ngp, 3)]"""
     X = _d(X)

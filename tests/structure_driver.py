@@ -175,10 +175,13 @@ class Problem:
         self.xi_nodes = np.asarray(node_param_coords(self.ct), float)
         self.faces = []
         self.has_ortho = any(c["type"] != "Live" for c in fx["neumann"])
+        self.has_follower = any(c["type"] == "orthopressure" for c in fx["neumann"])  # loads that depend on the current iterate
+        self.loadlin = fx["dynamic"].get("LOADLIN", "no").lower() in ("yes", "true", "1")
         face_tables = {**FACE_TABLES, **ORIENTED_FACES} if self.has_ortho else FACE_TABLES
         for c in fx["neumann"]:
             # Live, or pseudo_orthopressure: pressure VAL[0] along the normal of the last converged configuration
-            assert c["type"] in ("Live", "pseudo_orthopressure") and not any(c["onoff"][3:])
+            # or orthopressure: along the normal of the current iterate, with its load stiffness when LOADLIN is yes
+            assert c["type"] in ("Live", "pseudo_orthopressure", "orthopressure") and not any(c["onoff"][3:])
             sset = {self.index[n] for n in fx["dsurf"][str(c["E"])] if n in self.index}
             for e, en in enumerate(self.conn):
                 if self.ct == 8:
@@ -328,7 +331,7 @@ class Problem:
             f = np.zeros(self.n_dof)
             for i, (c, ft, fn) in enumerate(self.face_lists):
                 xg = self._gp_cache.setdefault(("s", i), nb.surface_coords(ft, fn))
-                if c["type"] == "pseudo_orthopressure":
+                if c["type"] in ("pseudo_orthopressure", "orthopressure"):  # d_conv: last converged state / current iterate
                     nb.surface_orthopressure(ft, fn, d_conv, c["val"][0], self._factors(("s", i), c, xg, t), f)
                     continue
                 nb.surface(ft, fn, c["onoff"], c["val"], self._factors(("s", i), c, xg, t), f)
@@ -351,6 +354,15 @@ class Problem:
                         fac = w * detA * c["val"][dof] * self.funct(c["funct"][dof], xgp, t)
                         f[nodes, dof] += N * fac
         return f.reshape(-1)
+
+    def k_load(self, t, d):
+        """load stiffness of the orthopressure loads at the iterate d (LOADLIN yes), dense"""
+        K = np.zeros((self.n_dof, self.n_dof))
+        for i, (c, ft, fn) in enumerate(self.face_lists):
+            if c["type"] == "orthopressure":
+                xg = self._gp_cache.setdefault(("s", i), self.neumann.surface_coords(ft, fn))
+                K += self.neumann.surface_orthopressure_linearization(ft, fn, d, c["val"][0], self._factors(("s", i), c, xg, t))
+        return K
 
     def result_error(self, d):
         """max (|d - VALUE| / TOLERANCE) over the displacement results, and the number compared"""
@@ -392,6 +404,15 @@ class OracleNeumann:
         xc = self.p.X[fn] + (0.0 if d is None else d.reshape(-1, 3)[fn])
         np.add.at(f.reshape(-1, 3), fn, self.o.surface_neumann_orthopressure(ft, xc, value, fac))
 
+    def surface_orthopressure_linearization(self, ft, fn, d, value, fac):
+        n = self.p.n_dof
+        K = np.zeros((n, n))
+        Ke = self.o.surface_neumann_orthopressure_linearization(ft, self.p.X[fn] + d.reshape(-1, 3)[fn], value, fac)
+        for nodes, ke in zip(fn, Ke):
+            dofs = (3 * nodes[:, None] + np.arange(3)).reshape(-1)
+            K[np.ix_(dofs, dofs)] += ke
+        return K
+
     def surface(self, ft, fn, onoff, val, fac, f):
         if ft == 6:
             for nodes, fe in self._nurbs_faces(fn, onoff, val, fac, False):
@@ -419,6 +440,12 @@ class CudaNeumann:
 
     def surface_orthopressure(self, ft, fn, d, value, fac, f):
         self.s.neumann_surface_orthopressure(ft, fn, d, value, f, gp_factor=fac)
+
+    def surface_orthopressure_linearization(self, ft, fn, d, value, fac):
+        rowptr, colind = self.s.get_graph()
+        K = np.zeros(len(colind))
+        self.s.neumann_surface_orthopressure_linearization(ft, fn, d, value, K, gp_factor=fac)
+        return csr_to_dense(rowptr, colind, K, len(rowptr) - 1)
 
     def surface(self, ft, fn, onoff, val, fac, f):
         if ft == 6:
@@ -475,8 +502,15 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, 
                 # the reference's loop: solve, update, recover, new residual, test (converged if the residual OR / AND the increment
                 # is below its tolerance)
                 tolres, toldisp, combi = p.ref_stop
-                fint, K = assemble(d)
-                r = fint - fext
+
+                def system(dd):  # follower loads: external force and load stiffness of the iterate
+                    fi, Kt = assemble(dd)
+                    fe = p.f_ext(step * dt, dd) if p.has_follower else fext
+                    if p.has_follower and p.loadlin:
+                        Kt = Kt + p.k_load(step * dt, dd)
+                    return fi, Kt, fe
+                fint, K, fe = system(d)
+                r = fint - fe
                 r[fixed] = 0.0
                 for _ in range(p.ref_maxiter or maxiter):
                     norms.append(float(np.linalg.norm(r)))
@@ -484,8 +518,8 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, 
                     d = d + inc
                     if recover is not None:
                         recover(inc)
-                    fint, K = assemble(d)
-                    r = fint - fext
+                    fint, K, fe = system(d)
+                    r = fint - fe
                     r[fixed] = 0.0
                     a, b = np.linalg.norm(r) < tolres, np.linalg.norm(inc) < toldisp
                     if (a or b) if combi == "Or" else (a and b):
@@ -497,6 +531,10 @@ def run(problem, assemble, mass=None, newton_tol=1e-13, maxiter=30, solve=None, 
                 continue
             for _ in range(maxiter):
                 fint, K = assemble(d)
+                if p.has_follower:
+                    fext = p.f_ext(step * dt, d)
+                    if p.loadlin:
+                        K = K + p.k_load(step * dt, d)
                 r = fint - fext
                 r[fixed] = 0.0
                 norms.append(float(np.linalg.norm(r)))

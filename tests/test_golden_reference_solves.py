@@ -111,6 +111,7 @@ CASES = [
     "error_analytical_beam_cantilever_end_surface_load_with_poissons_effect",
     "error_analytical_beam_cantilever_with_bodyload_without_poissons_effect",
     "sosh8_cooks_nl", "sohex8_easmild_cooks_nl_dynsta",  # more Cook membranes (nu = 0.4999): 16 elements; 64 with TOLRES 1e-6
+    "loadlin",  # TYPE orthopressure with LOADLIN yes on 300 eas_full elements: follower load + load stiffness, ten load steps
     "prestress_hex20",  # MULF on 144 hex20 under TYPE pseudo_orthopressure (fc_solid_neumann_surface_orthopressure), 15 load steps
     "sohex20_patchtest_nl_cost_drt",  # (its NODE COORDS keep the face and centre nodes of a hex27 mesh, unused by the hex20 elements)
 ]

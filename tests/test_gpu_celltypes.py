@@ -145,6 +145,17 @@ def test_orthopressure_parity(fc, oracle, name):
             f = np.full(n_row, 0.5)
             s.neumann_surface_orthopressure(ft, faces, None if uu is None else uu.reshape(-1), -1.7, f, gp_factor=fac)
             assert np.max(np.abs(f - f_ref)) <= 1e-14 * np.max(np.abs(f_ref))
+        # LOADLIN yes: the load stiffness in the CSR layout of the graph against the oracle's face matrices
+        n_dof, n_col, nnz = s.build_graph() if not getattr(s, "_g", None) else s._g
+        s._g = (n_dof, n_col, nnz)
+        rowptr, colind = s.get_graph()
+        K = np.zeros(nnz)
+        s.neumann_surface_orthopressure_linearization(ft, faces, u.reshape(-1), -1.7, K, gp_factor=fac)
+        K_ref = np.zeros((n_dof, n_dof))
+        for nodes, ke in zip(faces, oracle.surface_neumann_orthopressure_linearization(ft, X[faces] + u[faces], -1.7, fac)):
+            dofs = (3 * nodes[:, None] + np.arange(3)).reshape(-1)
+            K_ref[np.ix_(dofs, dofs)] += ke
+        assert np.max(np.abs(sd.csr_to_dense(rowptr, colind, K, n_dof) - K_ref)) <= 1e-14 * np.max(np.abs(K_ref))
     s.close()
 
 

@@ -415,8 +415,8 @@ extern "C"
     {
       FC_CUDA(cudaMalloc((void**)&ctx->d_dNtab, sizeof(double) * (size_t)fc::NurbsTab::stride * n_ele));
       FC_CUDA(cudaMemsetAsync(ctx->d_dNtab, 0, sizeof(double) * (size_t)fc::NurbsTab::stride * n_ele, ctx->stream));
-      unsigned char* d_zero = nullptr;
-      FC_CUDA(cudaMalloc((void**)&d_zero, (size_t)n_ele));
+      FC_CUDA(cudaMemsetAsync(ctx->d_ele_bad, 0, (size_t)n_ele, ctx->stream));
+      unsigned char* const d_zero = ctx->d_ele_bad;  // scratch for the zero-size flags; the node-Jacobian check below rewrites it
       const long long nt = (long long)n_ele * (fc::NurbsTab::ngp + fc::NurbsTab::nen + 1);
       fc::k_nurbs_tables<<<(unsigned)((nt + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_nurbs_knots, ctx->d_nurbs_weights, ctx->d_conn, n_ele,
           ctx->d_dNtab, d_zero);
@@ -424,7 +424,6 @@ extern "C"
       cudaError_t e = cudaGetLastError();
       if (e == cudaSuccess) e = cudaMemcpyAsync(zero.data(), d_zero, (size_t)n_ele, cudaMemcpyDeviceToHost, ctx->stream);
       if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-      cudaFree(d_zero);
       FC_CUDA(e);
       for (int el = 0; el < n_ele; ++el)
         if (zero[el]) return fail(ctx, FC_ERR_INVALID, "nurbs27 element with a zero-sized knot span (the reference throws, 4C_solid_3D_ele_calc_lib.hpp:196-199)");

@@ -66,11 +66,10 @@ namespace
     if (nurbs_face) FC_CUDA(dev_upload(t_sid, surface_id, (size_t)n_items, ctx->stream));
     const double* d_u = nullptr;
     double* t_u = nullptr;
-    if (ortho && u_col)
-      if (int rcu = stage_in(ctx, u_col, (size_t)ctx->n_col_dof, &d_u, &t_u)) return rcu;
     const double* d_fac = nullptr;
     double* t_fac = nullptr;
-    int rc = coords ? FC_OK : stage_in(ctx, gp_factor, (size_t)n_items * ngp * 3, &d_fac, &t_fac);
+    int rc = ortho && u_col ? stage_in(ctx, u_col, (size_t)ctx->n_col_dof, &d_u, &t_u) : FC_OK;
+    if (rc == FC_OK && !coords) rc = stage_in(ctx, gp_factor, (size_t)n_items * ngp * 3, &d_fac, &t_fac);
     double *d_out = out, *t_out = nullptr;
     const bool out_dev = is_device_ptr(out);
     cudaError_t e = cudaSuccess;

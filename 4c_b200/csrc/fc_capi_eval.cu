@@ -192,7 +192,9 @@ namespace
   template <bool WANT_K>
   cudaError_t dispatch(fc_ctx* ctx, const fc::EvalArgs& A, int flags)
   {
-    if (ctx->formulation == FC_FORM_LINEAR)  // KINEM linear: the generic B-operator kernel for every cell
+    if (ctx->formulation == FC_FORM_LINEAR && ctx->celltype == FC_HEX8 && ctx->mat.kind == fc::MAT_SVK && !(flags & FC_EVAL_FORCE_GENERIC))
+      return launch_hex8_ext<fc::VAR_SVK_LINEAR, WANT_K>(ctx, A);  // tensor-core closed form
+    if (ctx->formulation == FC_FORM_LINEAR)  // KINEM linear: the generic B-operator kernel for every other combination
       switch (ctx->celltype)
       {
         case FC_HEX8: return launch_generic<fc::HEX8, fc::FORM_LINEAR, WANT_K>(ctx, A);

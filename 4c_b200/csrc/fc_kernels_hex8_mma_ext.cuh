@@ -30,7 +30,11 @@ namespace fc
   enum
   {
     VAR_NH_FBAR = 0,
-    VAR_SVK_DISP = 1
+    VAR_SVK_DISP = 1,
+    // KINEM linear with St.Venant-Kirchhoff (4C_solid_3D_ele_calc_displacement_based_linear_kinematics.hpp:36-155): the SVK form
+    // with the B-operator at F = I (p_a = grad N_a, b = I), the stress of the linear strain sym(grad u), no geometric
+    // stiffness, and f_a = sum_b s_ab X_b on the reference coordinates (sum_b grad N_b X_b^T = I)
+    VAR_SVK_LINEAR = 2
   };
 
   struct Hex8MmaExtCfg
@@ -247,6 +251,21 @@ namespace fc
 #pragma unroll
         for (int v = 3; v < 6; ++v) S[v] = mu * C[v];
         bad = active && (!(detJ > 0.0) || detF == 0.0 || !isfinite(detF) || (ele_bad && ele_bad[e]));
+        if (VAR == VAR_SVK_LINEAR)
+        {
+          const double tr = (F[0] - 1.0) + (F[4] - 1.0) + (F[8] - 1.0);
+          S[0] = lame * tr + 2.0 * mu * (F[0] - 1.0);
+          S[1] = lame * tr + 2.0 * mu * (F[4] - 1.0);
+          S[2] = lame * tr + 2.0 * mu * (F[8] - 1.0);
+          S[3] = mu * (F[1] + F[3]);
+          S[4] = mu * (F[5] + F[7]);
+          S[5] = mu * (F[2] + F[6]);
+#pragma unroll
+          for (int v = 0; v < 6; ++v) b[v] = v < 3 ? 1.0 : 0.0;
+#pragma unroll
+          for (int i = 0; i < 9; ++i) F[i] = (i % 4 == 0) ? 1.0 : 0.0;
+          bad = active && (!(detJ > 0.0) || (ele_bad && ele_bad[e]));
+        }
         const double sw = sqrt(detJ);
         if (active)
         {
@@ -260,7 +279,7 @@ namespace fc
         }
       }
       if (active)
-        for (int i = 0; i < 3; ++i) E[Cfg::oX + 3 * t + i] = xr[i];
+        for (int i = 0; i < 3; ++i) E[Cfg::oX + 3 * t + i] = VAR == VAR_SVK_LINEAR ? Xr[i] : xr[i];
     }
     const unsigned badmask = __ballot_sync(0xFFFFFFFFu, bad);
     const unsigned actmask = __ballot_sync(0xFFFFFFFFu, active);
@@ -364,8 +383,8 @@ namespace fc
 #pragma unroll
           for (int j = 0; j < 3; ++j)
           {
-            Kb[0][3 * i + j] = c1 * W[i][j][0] + c2 * W[j][i][0] + (i == j ? s0 : 0.0);
-            Kb[1][3 * i + j] = c1 * W[i][j][1] + c2 * W[j][i][1] + (i == j ? s1 : 0.0);
+            Kb[0][3 * i + j] = c1 * W[i][j][0] + c2 * W[j][i][0] + (i == j && VAR != VAR_SVK_LINEAR ? s0 : 0.0);
+            Kb[1][3 * i + j] = c1 * W[i][j][1] + c2 * W[j][i][1] + (i == j && VAR != VAR_SVK_LINEAR ? s1 : 0.0);
           }
       }
       if (VAR == VAR_NH_FBAR)
@@ -397,7 +416,7 @@ namespace fc
         // mu w detJ b_ij (grad N_a . grad N_b): six weighted tiles, the weight rides on the A fragment
         const int vi[6] = {0, 1, 2, 0, 1, 0}, vj[6] = {0, 1, 2, 1, 2, 2};
 #pragma unroll
-        for (int v = 0; v < 6; ++v)
+        for (int v = 0; v < (VAR == VAR_SVK_LINEAR ? 3 : 6); ++v)  // b = I with linear kinematics: the diagonal tiles only
         {
           double t0 = 0.0, t1 = 0.0;
           const double w0 = R0[18 + v], w1 = R1[18 + v];

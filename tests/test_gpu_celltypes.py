@@ -76,6 +76,11 @@ def test_element_and_assembly_parity(fc, oracle, name, form, mat, nue):
     f2 = np.zeros(n_row)
     assert s.evaluate(fc.FC_ACTION_INTERNALFORCE, u.reshape(-1), f2, None, flags=fc.FC_EVAL_ZERO_FIRST) == (0, -1)
     assert np.max(np.abs(f2 - f)) <= 1e-14 * np.max(np.abs(f))
+    if (ct, form, mat) == (0, LINEAR, SVK):  # default: the tensor-core closed form (k_hex8_mma_ext<VAR_SVK_LINEAR>); also the generic kernel
+        K3, f3 = np.zeros(nnz), np.zeros(n_row)
+        assert s.evaluate(fc.FC_ACTION_NLNSTIFF, u.reshape(-1), f3, K3, flags=fc.FC_EVAL_ZERO_FIRST | fc.FC_EVAL_FORCE_GENERIC) == (0, -1)
+        assert np.max(np.maximum.reduceat(np.abs(K3 - K_ref), starts) / rmax) <= TOL
+        assert np.max(np.abs(f3 - f_ref)) <= TOL * max(np.max(np.abs(f_ref)), np.max(np.abs(K_ref)))
     s.close()
 
 
